@@ -1,0 +1,212 @@
+/* libslamcuda.so -- C ABI of the B200-native EKF-SLAM hot path.
+ *
+ * Drop-in boundary for the filter half of andrewadare/SLAM.jl's `module SLAM`
+ * (reference paths are under /root/reference):
+ *
+ *   slam_predict             replaces  predict(state, vehicle, Q, dt)            src/ekf.jl:8-43
+ *   slam_associate           replaces  associate(state, z, R, gate1, gate2)      src/data-association.jl:1-51
+ *   slam_compute_association replaces  compute_association(x, P, z, R, idf)      src/data-association.jl:53-63
+ *   slam_predict_observation replaces  predict_observation(x, idf)               src/common.jl:139-165
+ *   slam_update              replaces  update(state, z, R, idf)                  src/ekf.jl:46-77
+ *   slam_add_features        replaces  add_features(state, z, R)                 src/ekf.jl:84-122
+ *   slam_set_state/get_state carry     EKFSlamState{T}.x / .cov                  src/common.jl:25-28
+ *
+ * The reference has no FFI of its own: its caller is sim! (sim/ekfslam-sim.jl:100,114,
+ * 117,120), which re-binds `state.x, state.cov = f(state, ...)`.  A Julia `SLAM` module
+ * keeping those names ccall()s these entry points.
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes; every pointer is HOST memory unless the
+ *    parameter name starts with d_.
+ *  - Matrices are column-major (Julia layout).  z/zf/zn are 2 x count, column i at
+ *    z[2*i], z[2*i+1] = (range, bearing).  R and Q are 2 x 2 column-major.
+ *  - Landmark ids `idf` are 1-based int64 (Julia Int), exactly as the reference passes
+ *    them; state index of landmark id is 3 + 2*(id-1) (0-based).
+ *  - Every function returns 0 on success or a negative SLAM_ERR_* code;
+ *    slam_last_error() gives the message of the last failure on the calling thread.
+ *  - There is no CPU fallback: every call fails with SLAM_ERR_CUDA when no sm_100
+ *    device is usable.
+ *  - A handle is not re-entrant; distinct handles may be driven from distinct threads.
+ *
+ * Covariance storage: P lives on the device as a column-major n x n array with a fixed
+ * leading dimension chosen at slam_create (capacity n_max), so augmentation is an
+ * in-place append.  The upper triangle (i <= j) is authoritative; slam_get_state
+ * mirrors it into the lower triangle on export.  slam_set_state reads the upper
+ * triangle of the matrix it is given (the reference keeps P symmetric up to rounding in
+ * its 3x3 / 2x2 diagonal blocks, src/ekf.jl:32,112).
+ */
+#ifndef SLAMCUDA_H
+#define SLAMCUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SLAM_OK 0
+#define SLAM_ERR_NOT_PD    (-1) /* innovation covariance S not positive definite (Julia: chol throws) */
+#define SLAM_ERR_BAD_INDEX (-2) /* idf outside 1..Nf (Julia: BoundsError)                            */
+#define SLAM_ERR_CAPACITY  (-3) /* n + 2k exceeds n_max, or a count exceeds a fixed limit            */
+#define SLAM_ERR_CUDA      (-4) /* CUDA runtime failure, or no usable device                         */
+#define SLAM_ERR_NCCL      (-5) /* NCCL failure / libnccl not loadable                               */
+#define SLAM_ERR_ARG       (-6) /* NULL handle, negative size, ...                                   */
+
+#define SLAM_MAX_OBS 1024       /* upper limit on nz / m / k per call                                */
+
+typedef struct slam_filter slam_t;
+
+const char *slam_last_error(void);
+/* "libslamcuda <version> sm_100a"; never fails, needs no device. */
+const char *slam_version(void);
+/* Number of CUDA devices visible (0 when none / no driver); never fails. */
+int slam_device_count(void);
+
+/* ---- single filter, state resident on one device ------------------------------------ */
+
+/* EKFSlamState(x, cov) -- src/common.jl:25-28, as built by sim/ekfslam-sim.jl:42.
+ * Allocates device state with capacity n_max (>= 3).  State starts as n = 3, x = 0, P = 0. */
+int slam_create(int device, int n_max, slam_t **out);
+int slam_destroy(slam_t *h);
+
+/* state.x / state.cov <- host arrays.  P is n x n column-major with leading dim ldp. */
+int slam_set_state(slam_t *h, const double *x, const double *P, int n, int ldp);
+/* host arrays <- state.x / state.cov (full symmetric matrix).  x or P may be NULL. */
+int slam_get_state(slam_t *h, double *x, double *P, int ldp);
+/* state.x[1:3], read by sim! every step (sim/ekfslam-sim.jl:128). */
+int slam_get_pose(slam_t *h, double pose[3]);
+/* length(state.x); negative on error. */
+int slam_n(slam_t *h);
+/* A sub-block cov[i0:i0+ni, j0:j0+nj] (0-based, full symmetric view) for front ends that
+ * must not pull all of P (resident mode). */
+int slam_get_cov_block(slam_t *h, int i0, int ni, int j0, int nj, double *out, int ldo);
+
+/* predict -- src/ekf.jl:8-43.  g, v = vehicle.measured_gamma / measured_speed (:14-15),
+ * wheelbase = vehicle.wheelbase (:16), Q 2x2 control covariance, dt timestep. In place. */
+int slam_predict(slam_t *h, double g, double v, double wheelbase, const double Q[4], double dt);
+
+/* associate -- src/data-association.jl:1-51.  z is 2 x nz.  Outputs (caller buffers of
+ * capacity nz columns): zf 2 x *m, idf[*m] (1-based), zn 2 x *k; observation order kept. */
+int slam_associate(slam_t *h, const double *z, int nz, const double R[4], double gate1,
+                   double gate2, double *zf, int64_t *idf, int *m, double *zn, int *k);
+
+/* compute_association -- src/data-association.jl:53-63 for one (z, landmark) pair. */
+int slam_compute_association(slam_t *h, const double z[2], const double R[4], int64_t idf,
+                             double *nis, double *nd);
+
+/* predict_observation -- src/common.jl:139-165.  zp = [range; bearing] (bearing not wrapped).
+ * H is the dense 2 x n Jacobian, column-major with leading dimension 2 (may be NULL). */
+int slam_predict_observation(slam_t *h, int64_t idf, double zp[2], double *H);
+
+/* update -- src/ekf.jl:46-77: batch Cholesky-form update with all m associated
+ * observations.  m == 0 is a no-op (first observation step of every run).  Duplicate ids
+ * in idf are legal.  In place on the device state. */
+int slam_update(slam_t *h, const double *zf, int m, const double R[4], const int64_t *idf);
+
+/* add_features -- src/ekf.jl:84-122: append k new landmarks in place (n += 2k). */
+int slam_add_features(slam_t *h, const double *zn, int k, const double R[4]);
+
+/* Resident-mode variants: inputs already on the device, nothing is copied back and the
+ * call does not synchronise.  Errors (not-PD, bad index) are latched on the device and
+ * returned by the next slam_sync().  Used by bench.py's device-resident timing. */
+int slam_update_resident(slam_t *h, const double *d_zf, int m, const double R[4],
+                         const int64_t *d_idf);
+int slam_sync(slam_t *h);
+/* The CUDA stream (cudaStream_t) all work of this handle is issued on. */
+void *slam_stream(slam_t *h);
+/* Downdate kernel choice for update: 0 = auto (FMA kernel below the rank threshold, DMMA
+ * tiles above), 1 = force FP64 FMA kernel, 2 = force FP64 DMMA tensor-core kernel. */
+int slam_set_downdate_variant(slam_t *h, int variant);
+/* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
+long long slam_launch_count(slam_t *h);
+/* Kernel timing for roofline reports: while on, every update records a CUDA event pair
+ * around its downdate (K6) launches on the handle's stream.  slam_profile_read synchronises
+ * and returns the summed K6 milliseconds and the number of timed updates since it was
+ * switched on (at most 4096 are kept), then clears them. */
+int slam_profile(slam_t *h, int on);
+int slam_profile_read(slam_t *h, double *k6_ms, int *k6_updates);
+
+/* Synthetic large-map state generated ON the device:
+ * landmarks uniform on a side x side square, x_landmark = truth + N(0, 0.1^2),
+ * P = D + L L' with D = diag U(0.01, 0.1), L n x 8 N(0, 0.05^2), vehicle at the centre
+ * with heading 0.  All draws are Philox4x32-10 keyed by (seed, stream, index) so a CPU
+ * mirror reproduces any entry.  Sets n = 3 + 2*n_landmarks (<= n_max). */
+int slam_synth_state(slam_t *h, int n_landmarks, double side, uint64_t seed);
+/* Observations of the m nearest landmarks ahead of the vehicle (truth position, no
+ * noise added) followed by `spurious` observations far beyond gate2; writes 2 x (m+spurious)
+ * to z (host) and the true 1-based ids of the first m to ids (may be NULL). */
+int slam_synth_observations(slam_t *h, int n_landmarks, double side, uint64_t seed, int m,
+                            int spurious, double *z, int64_t *ids);
+
+/* ---- ensemble of independent course runs (one CTA per filter) ------------------------ */
+
+typedef struct slam_ensemble slam_ens_t;
+
+/* Precomputes the noise-free truth track and visibility tables of sim! on the host
+ * (sim/ekfslam-sim.jl:80-142 with src/common.jl:172-230, sim/sim-utils.jl:12-28,53-75) and
+ * uploads them.  waypoints 2 x nwp, landmarks 2 x nl, both column-major.  Members are
+ * run ids [run0, run0 + n_runs); member r draws Philox normals keyed by (seed, r). */
+int slam_ens_create(int device, const double *waypoints, int nwp, const double *landmarks,
+                    int nl, int nlaps, uint64_t seed, uint32_t run0, int n_runs,
+                    slam_ens_t **out);
+int slam_ens_destroy(slam_ens_t *e);
+/* Steps of one run and number of observation steps (2801 / 311 for 2 laps of course1). */
+int slam_ens_steps(slam_ens_t *e, int *nsteps, int *nupdates);
+/* Runs every member from its initial state to the end of the course in one launch.
+ * Asynchronous; slam_ens_sync() waits and returns the number of failed members (< 0 on
+ * CUDA error). */
+int slam_ens_run(slam_ens_t *e);
+int slam_ens_sync(slam_ens_t *e);
+/* Results: final_pose 3 x n_runs; n_final[n_runs] = final state length per member;
+ * status[n_runs] (0 ok, SLAM_ERR_*).  Any pointer may be NULL. */
+int slam_ens_get_results(slam_ens_t *e, double *final_pose, int *n_final, int *status);
+/* slam_track (3 x nsteps) of one member (sim/ekfslam-sim.jl:128); requires tracks to have
+ * been enabled before the run with slam_ens_keep_tracks(e, 1). */
+int slam_ens_keep_tracks(slam_ens_t *e, int on);
+int slam_ens_get_track(slam_ens_t *e, int member, double *track);
+/* Final x (n_final) and P (n_final^2, ldp) of one member. */
+int slam_ens_get_state(slam_ens_t *e, int member, double *x, double *P, int ldp);
+/* Host-supplied noise instead of Philox (parity runs): ctrl 2 x nsteps per member,
+ * obs: pool of `obs_per_member` normals per member consumed in draw order. */
+int slam_ens_set_noise(slam_ens_t *e, const double *ctrl, const double *obs, int obs_per_member);
+void *slam_ens_stream(slam_ens_t *e);
+long long slam_ens_launch_count(slam_ens_t *e);
+
+/* ---- large map, P row-block-sharded over the ranks of one NCCL communicator ---------- */
+
+typedef struct slam_shard slam_shard_t;
+
+/* 128-byte NCCL unique id created on rank 0 and handed to every rank by the host
+ * launcher (torch.distributed / MPI / a file). */
+int slam_shard_unique_id(char id[128]);
+/* Rank `rank` of `world` owns row blocks rank and 2*world-1-rank of the 2*world equal row
+ * blocks of P (balanced upper-triangle work).  world == 1 needs no NCCL. */
+int slam_shard_create(int device, int rank, int world, const char id[128], int n_max,
+                      slam_shard_t **out);
+int slam_shard_destroy(slam_shard_t *s);
+/* Pure partition arithmetic (no device needed): rows [lo[b], hi[b]) of the two blocks b = 0, 1
+ * owned by `rank` for state size n. */
+int slam_shard_plan(int n, int world, int rank, int lo[2], int hi[2]);
+int slam_shard_synth_state(slam_shard_t *s, int n_landmarks, double side, uint64_t seed);
+int slam_shard_n(slam_shard_t *s);
+int slam_shard_get_pose(slam_shard_t *s, double pose[3]);
+int slam_shard_get_x(slam_shard_t *s, double *x);
+/* Rows [i0, i0+ni) x cols [j0, j0+nj) of the authoritative upper triangle owned by this
+ * rank (entries not owned / below the diagonal are left untouched); returns count copied. */
+int slam_shard_get_cov_block(slam_shard_t *s, int i0, int ni, int j0, int nj, double *out, int ldo);
+int slam_shard_predict(slam_shard_t *s, double g, double v, double wheelbase, const double Q[4],
+                       double dt);
+int slam_shard_associate(slam_shard_t *s, const double *z, int nz, const double R[4], double gate1,
+                         double gate2, double *zf, int64_t *idf, int *m, double *zn, int *k);
+int slam_shard_update(slam_shard_t *s, const double *zf, int m, const double R[4],
+                      const int64_t *idf);
+int slam_shard_update_resident(slam_shard_t *s, const double *d_zf, int m, const double R[4],
+                               const int64_t *d_idf);
+int slam_shard_sync(slam_shard_t *s);
+void *slam_shard_stream(slam_shard_t *s);
+long long slam_shard_launch_count(slam_shard_t *s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SLAMCUDA_H */

@@ -1,0 +1,884 @@
+// Single-filter device-resident EKF-SLAM: handle lifecycle, state I/O and the kernels
+// K1 (predict), K3 (P*H' gather), K4 (innovation Cholesky), K5 (gain, x update),
+// K7 (in-place augmentation).  K2 lives in gate.cu, K6 in downdate.cu.
+// Compiled with -fmad=false: products and sums round separately, in the operation order of
+// the CPU oracle's plain-C twin.  Reference citations: file:line under /root/reference.
+#include <stdarg.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+#include "kernels.cuh"
+
+// ---------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+void slam_set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char *slam_last_error(void) { return g_err; }
+extern "C" const char *slam_version(void) { return "libslamcuda 0.1 sm_100a"; }
+extern "C" int slam_device_count(void) {
+    int c = 0;
+    if (cudaGetDeviceCount(&c) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return c;
+}
+
+int slam_require_device(int device) {
+    int c = slam_device_count();
+    if (device < 0 || device >= c) {
+        slam_set_error("no usable CUDA device %d (%d visible); libslamcuda has no CPU fallback", device, c);
+        return SLAM_ERR_CUDA;
+    }
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        slam_set_error("device %d is sm_%d%d; libslamcuda is built for sm_100a only", device, prop.major,
+                       prop.minor);
+        return SLAM_ERR_CUDA;
+    }
+    CUDA_TRY(cudaSetDevice(device));
+    return SLAM_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// handle
+// ---------------------------------------------------------------------------------------
+struct slam_filter {
+    int device = 0;
+    int n_max = 0, n = 3;
+    size_t ld = 0;
+    cudaStream_t stream = nullptr;
+    double *d_x = nullptr;
+    double *d_P = nullptr;
+    double *d_pose = nullptr;  // 2 x 4 doubles: pose snapshot double buffer read by K1
+    int pose_slot = 0;
+    int *d_err = nullptr;      // latched device-side error code
+    // observation staging (device) and pinned host mirror
+    double *d_z = nullptr, *d_zf = nullptr, *d_zn = nullptr;
+    int64_t *d_idf = nullptr;
+    int *d_counts = nullptr;
+    double *d_small = nullptr;  // 16 doubles of misc outputs
+    void *h_pin = nullptr;      // pinned host staging
+    size_t h_pin_bytes = 0;
+    void *d_gate_scratch = nullptr;
+    size_t gate_scratch = 0;
+    // update workspace, grown on demand
+    int ws_R = 0, ws_npad = 0;
+    double *d_PHt = nullptr, *d_W1c = nullptr, *d_S = nullptr, *d_C = nullptr, *d_u = nullptr,
+           *d_v = nullptr, *d_Hn = nullptr;
+    int *d_fp = nullptr;
+    double *d_block = nullptr;  // cov-block staging
+    size_t block_cap = 0;
+    int variant = 0;
+    long long launches = 0;
+    // K6 event timing (slam_profile)
+    bool profiling = false;
+    std::vector<cudaEvent_t> ev;   // pairs
+    int ev_used = 0;
+};
+
+#define H_CHECK(h)                                                        \
+    do {                                                                  \
+        ARG_CHECK((h) != nullptr, "NULL handle");                         \
+        CUDA_TRY(cudaSetDevice((h)->device));                             \
+    } while (0)
+
+static int ensure_update_ws(slam_t *h, int R) {
+    int npad = round_up(h->n_max, DD_ROW_PAD);
+    int RC = downdate_chunk_width(R);
+    int Rpad = round_up(R, RC);
+    if (h->ws_R >= Rpad && h->ws_npad == npad) return SLAM_OK;
+    cudaFree(h->d_PHt); cudaFree(h->d_W1c); cudaFree(h->d_S); cudaFree(h->d_C);
+    cudaFree(h->d_u); cudaFree(h->d_v); cudaFree(h->d_Hn); cudaFree(h->d_fp);
+    h->d_PHt = h->d_W1c = h->d_S = h->d_C = h->d_u = h->d_v = h->d_Hn = nullptr;
+    h->d_fp = nullptr;
+    h->ws_R = 0;
+    int Rw = std::max(Rpad, 32);
+    CUDA_TRY(cudaMalloc(&h->d_PHt, sizeof(double) * (size_t)npad * Rw));
+    CUDA_TRY(cudaMalloc(&h->d_W1c, sizeof(double) * (size_t)npad * Rw));
+    CUDA_TRY(cudaMalloc(&h->d_S, sizeof(double) * (size_t)Rw * Rw));
+    CUDA_TRY(cudaMalloc(&h->d_C, sizeof(double) * (size_t)Rw * Rw));
+    CUDA_TRY(cudaMalloc(&h->d_u, sizeof(double) * Rw));
+    CUDA_TRY(cudaMalloc(&h->d_v, sizeof(double) * Rw));
+    CUDA_TRY(cudaMalloc(&h->d_Hn, sizeof(double) * 10 * (Rw / 2)));
+    CUDA_TRY(cudaMalloc(&h->d_fp, sizeof(int) * (Rw / 2)));
+    h->ws_R = Rw;
+    h->ws_npad = npad;
+    return SLAM_OK;
+}
+
+extern "C" int slam_create(int device, int n_max, slam_t **out) {
+    ARG_CHECK(out != nullptr, "out is NULL");
+    ARG_CHECK(n_max >= 3, "n_max must be >= 3");
+    *out = nullptr;
+    int rc = slam_require_device(device);
+    if (rc) return rc;
+    slam_t *h = new slam_t();
+    h->device = device;
+    h->n_max = n_max;
+    h->ld = (size_t)round_up(n_max, 16);
+    h->n = 3;
+#define CREATE_TRY(expr)                                                                         \
+    do {                                                                                         \
+        cudaError_t e__ = (expr);                                                                \
+        if (e__ != cudaSuccess) {                                                                \
+            slam_set_error("%s failed: %s", #expr, cudaGetErrorString(e__));                     \
+            slam_destroy(h);                                                                     \
+            return SLAM_ERR_CUDA;                                                                \
+        }                                                                                        \
+    } while (0)
+    CREATE_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CREATE_TRY(cudaMalloc(&h->d_x, sizeof(double) * h->ld));
+    CREATE_TRY(cudaMalloc(&h->d_P, sizeof(double) * h->ld * (size_t)n_max));
+    CREATE_TRY(cudaMalloc(&h->d_pose, sizeof(double) * 8));
+    CREATE_TRY(cudaMalloc(&h->d_err, sizeof(int)));
+    const size_t no = SLAM_MAX_OBS;
+    CREATE_TRY(cudaMalloc(&h->d_z, sizeof(double) * 2 * no));
+    CREATE_TRY(cudaMalloc(&h->d_zf, sizeof(double) * 2 * no));
+    CREATE_TRY(cudaMalloc(&h->d_zn, sizeof(double) * 2 * no));
+    CREATE_TRY(cudaMalloc(&h->d_idf, sizeof(int64_t) * no));
+    CREATE_TRY(cudaMalloc(&h->d_counts, sizeof(int) * 4));
+    CREATE_TRY(cudaMalloc(&h->d_small, sizeof(double) * 16));
+    h->h_pin_bytes = sizeof(double) * 8 * no + 256;
+    CREATE_TRY(cudaMallocHost(&h->h_pin, h->h_pin_bytes));
+    h->gate_scratch = gate_scratch_bytes(SLAM_MAX_OBS);
+    CREATE_TRY(cudaMalloc(&h->d_gate_scratch, h->gate_scratch));
+    CREATE_TRY(cudaMemsetAsync(h->d_gate_scratch, 0, 256, h->stream));
+    CREATE_TRY(cudaMemsetAsync(h->d_x, 0, sizeof(double) * h->ld, h->stream));
+    CREATE_TRY(cudaMemsetAsync(h->d_P, 0, sizeof(double) * h->ld * (size_t)std::min(n_max, 64), h->stream));
+    CREATE_TRY(cudaMemsetAsync(h->d_pose, 0, sizeof(double) * 8, h->stream));
+    CREATE_TRY(cudaMemsetAsync(h->d_err, 0, sizeof(int), h->stream));
+    CREATE_TRY(cudaStreamSynchronize(h->stream));
+#undef CREATE_TRY
+    *out = h;
+    return SLAM_OK;
+}
+
+extern "C" int slam_destroy(slam_t *h) {
+    if (!h) return SLAM_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    cudaFree(h->d_x); cudaFree(h->d_P); cudaFree(h->d_pose); cudaFree(h->d_err);
+    cudaFree(h->d_z); cudaFree(h->d_zf); cudaFree(h->d_zn); cudaFree(h->d_idf);
+    cudaFree(h->d_counts); cudaFree(h->d_small); cudaFree(h->d_gate_scratch);
+    cudaFree(h->d_PHt); cudaFree(h->d_W1c); cudaFree(h->d_S); cudaFree(h->d_C);
+    cudaFree(h->d_u); cudaFree(h->d_v); cudaFree(h->d_Hn); cudaFree(h->d_fp);
+    cudaFree(h->d_block);
+    if (h->h_pin) cudaFreeHost(h->h_pin);
+    for (auto &e : h->ev) cudaEventDestroy(e);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    cudaGetLastError();
+    delete h;
+    return SLAM_OK;
+}
+
+extern "C" int slam_n(slam_t *h) {
+    if (!h) {
+        slam_set_error("slam_n: NULL handle");
+        return SLAM_ERR_ARG;
+    }
+    return h->n;
+}
+extern "C" void *slam_stream(slam_t *h) { return h ? (void *)h->stream : nullptr; }
+extern "C" long long slam_launch_count(slam_t *h) { return h ? h->launches : 0; }
+extern "C" int slam_set_downdate_variant(slam_t *h, int variant) {
+    ARG_CHECK(h != nullptr, "NULL handle");
+    ARG_CHECK(variant >= 0 && variant <= 2, "variant must be 0, 1 or 2");
+    h->variant = variant;
+    return SLAM_OK;
+}
+
+static int check_latched(slam_t *h) {
+    int *he = (int *)h->h_pin;
+    CUDA_TRY(cudaMemcpyAsync(he, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    int e = *he;
+    if (e != 0) {
+        CUDA_TRY(cudaMemsetAsync(h->d_err, 0, sizeof(int), h->stream));
+        slam_set_error(e == SLAM_ERR_NOT_PD      ? "innovation covariance not positive definite"
+                       : e == SLAM_ERR_BAD_INDEX ? "landmark id out of range"
+                                                 : "device-side error %d",
+                       e);
+        return e;
+    }
+    return SLAM_OK;
+}
+
+extern "C" int slam_sync(slam_t *h) {
+    H_CHECK(h);
+    return check_latched(h);
+}
+
+// ---------------------------------------------------------------------------------------
+// state I/O
+// ---------------------------------------------------------------------------------------
+// lower := upper' on the device copy (only for export; the lower triangle is not authoritative)
+__global__ void k_mirror_lower(double *P, size_t ld, int n) {
+    __shared__ double t[32][33];
+    int bi = blockIdx.x, bj = blockIdx.y;
+    if (bi > bj) return;
+    int i = bi * 32 + threadIdx.y, j = bj * 32 + threadIdx.x;
+    // read upper tile (rows bi, cols bj) transposed access pattern: coalesce along i
+    int ii = bi * 32 + threadIdx.x, jj = bj * 32 + threadIdx.y;
+    t[threadIdx.y][threadIdx.x] = (ii < n && jj < n && ii <= jj) ? P[(size_t)ii + (size_t)jj * ld] : 0.0;
+    __syncthreads();
+    // element (row = j, col = i) of the lower tile equals upper (i, j) = t[jloc... ]
+    // t[a][b] holds upper(row = bi*32 + b, col = bj*32 + a); lower target (row = bj*32 + a', col = bi*32 + b')
+    int r = bj * 32 + threadIdx.x;   // row of the lower element (contiguous across threads)
+    int c = bi * 32 + threadIdx.y;   // its column
+    (void)i; (void)j;
+    if (r < n && c < n && r > c) P[(size_t)r + (size_t)c * ld] = t[threadIdx.x][threadIdx.y];
+}
+
+__global__ void k_set_pose_snapshot(const double *x, double *pose_slot) {
+    if (threadIdx.x < 3) pose_slot[threadIdx.x] = x[threadIdx.x];
+}
+
+extern "C" int slam_set_state(slam_t *h, const double *x, const double *P, int n, int ldp) {
+    H_CHECK(h);
+    ARG_CHECK(x && P, "NULL x or P");
+    ARG_CHECK(n >= 3 && (n - 3) % 2 == 0, "n must be 3 + 2*Nf");
+    ARG_CHECK(ldp >= n, "ldp < n");
+    if (n > h->n_max) {
+        slam_set_error("slam_set_state: n = %d exceeds capacity n_max = %d", n, h->n_max);
+        return SLAM_ERR_CAPACITY;
+    }
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    CUDA_TRY(cudaMemcpyAsync(h->d_x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaMemcpy2DAsync(h->d_P, sizeof(double) * h->ld, P, sizeof(double) * (size_t)ldp,
+                               sizeof(double) * n, n, cudaMemcpyHostToDevice, h->stream));
+    h->n = n;
+    k_set_pose_snapshot<<<1, 32, 0, h->stream>>>(h->d_x, h->d_pose + 4 * h->pose_slot);
+    h->launches++;
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return SLAM_OK;
+}
+
+extern "C" int slam_get_state(slam_t *h, double *x, double *P, int ldp) {
+    H_CHECK(h);
+    int n = h->n;
+    if (P) {
+        ARG_CHECK(ldp >= n, "ldp < n");
+        dim3 grid((n + 31) / 32, (n + 31) / 32), blk(32, 32);
+        k_mirror_lower<<<grid, blk, 0, h->stream>>>(h->d_P, h->ld, n);
+        h->launches++;
+        CUDA_TRY(cudaGetLastError());
+        CUDA_TRY(cudaMemcpy2DAsync(P, sizeof(double) * (size_t)ldp, h->d_P, sizeof(double) * h->ld,
+                                   sizeof(double) * n, n, cudaMemcpyDeviceToHost, h->stream));
+    }
+    if (x) CUDA_TRY(cudaMemcpyAsync(x, h->d_x, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
+    return check_latched(h);
+}
+
+extern "C" int slam_get_pose(slam_t *h, double pose[3]) {
+    H_CHECK(h);
+    ARG_CHECK(pose != nullptr, "NULL pose");
+    double *hp = (double *)h->h_pin + 8;
+    CUDA_TRY(cudaMemcpyAsync(hp, h->d_x, sizeof(double) * 3, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    pose[0] = hp[0]; pose[1] = hp[1]; pose[2] = hp[2];
+    return SLAM_OK;
+}
+
+__global__ void k_cov_block(const double *P, size_t ld, int i0, int ni, int j0, int nj, double *out) {
+    int a = blockIdx.y * blockDim.x + threadIdx.x;
+    int b = blockIdx.x;
+    if (a < ni && b < nj) out[(size_t)a + (size_t)b * ni] = sym_at(P, ld, i0 + a, j0 + b);
+}
+
+extern "C" int slam_get_cov_block(slam_t *h, int i0, int ni, int j0, int nj, double *out, int ldo) {
+    H_CHECK(h);
+    ARG_CHECK(out != nullptr, "NULL out");
+    ARG_CHECK(i0 >= 0 && j0 >= 0 && ni >= 0 && nj >= 0 && i0 + ni <= h->n && j0 + nj <= h->n,
+              "block outside the state");
+    ARG_CHECK(ldo >= ni, "ldo < ni");
+    if (ni == 0 || nj == 0) return SLAM_OK;
+    size_t need = (size_t)ni * nj;
+    if (need > h->block_cap) {
+        cudaFree(h->d_block);
+        h->d_block = nullptr;
+        h->block_cap = 0;
+        CUDA_TRY(cudaMalloc(&h->d_block, sizeof(double) * need));
+        h->block_cap = need;
+    }
+    dim3 grid(nj, (ni + 127) / 128);
+    k_cov_block<<<grid, 128, 0, h->stream>>>(h->d_P, h->ld, i0, ni, j0, nj, h->d_block);
+    h->launches++;
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpy2DAsync(out, sizeof(double) * (size_t)ldo, h->d_block, sizeof(double) * ni,
+                               sizeof(double) * ni, nj, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return SLAM_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// K1 predict -- src/ekf.jl:8-43.  O(n): rows 1:3 of every column.
+// Bytes: 24 read + 16 written per map column (+ the 3x3 block and x[1:3]).
+// ---------------------------------------------------------------------------------------
+struct PredictParams {
+    double g, v, w, dt, Q[4];
+};
+
+__global__ void __launch_bounds__(256)
+k_predict(double *x, double *P, size_t ld, int n, PredictParams p, const double *pose_in, double *pose_out) {
+    const double phi = pose_in[2];
+    const double s = sin(p.g + phi), c = cos(p.g + phi);
+    const double vts = p.v * p.dt * s, vtc = p.v * p.dt * c;
+    int j = 3 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n) {
+        double *col = P + (size_t)j * ld;
+        double p0 = col[0], p1 = col[1], p2 = col[2];
+        col[0] = p0 + (-vts) * p2;   // Gv*P[1:3,4:end], Gv = [1 0 -vts; 0 1 vtc; 0 0 1]   (:24-26,34)
+        col[1] = p1 + vtc * p2;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        const double Gv[3][3] = {{1, 0, -vts}, {0, 1, vtc}, {0, 0, 1}};
+        const double Gu[3][2] = {{p.dt * c, -vts}, {p.dt * s, vtc},
+                                 {p.dt * sin(p.g) / p.w, p.v * p.dt * cos(p.g) / p.w}};
+        double Pv[3][3], A[3][3], B[3][3], GQ[3][2];
+        for (int i = 0; i < 3; i++)
+            for (int q = 0; q < 3; q++) Pv[i][q] = sym_at(P, ld, i, q);
+        for (int i = 0; i < 3; i++)
+            for (int q = 0; q < 3; q++) {
+                double a = 0;
+                for (int k = 0; k < 3; k++) a += Gv[i][k] * Pv[k][q];
+                A[i][q] = a;
+            }
+        for (int i = 0; i < 3; i++)
+            for (int q = 0; q < 3; q++) {
+                double a = 0;
+                for (int k = 0; k < 3; k++) a += A[i][k] * Gv[q][k];
+                B[i][q] = a;
+            }
+        for (int i = 0; i < 3; i++)
+            for (int q = 0; q < 2; q++) GQ[i][q] = Gu[i][0] * p.Q[0 + 2 * q] + Gu[i][1] * p.Q[1 + 2 * q];
+        for (int i = 0; i < 3; i++)
+            for (int q = 0; q < 3; q++) B[i][q] += GQ[i][0] * Gu[q][0] + GQ[i][1] * Gu[q][1];
+        for (int i = 0; i < 3; i++)
+            for (int q = i; q < 3; q++) P[(size_t)i + (size_t)q * ld] = B[i][q];
+        double x0 = pose_in[0] + vtc, x1 = pose_in[1] + vts;
+        double x2 = mpi_to_pi(phi + p.v * p.dt * sin(p.g) / p.w);
+        x[0] = x0; x[1] = x1; x[2] = x2;
+        pose_out[0] = x0; pose_out[1] = x1; pose_out[2] = x2;
+    }
+}
+
+extern "C" int slam_predict(slam_t *h, double g, double v, double wheelbase, const double Q[4], double dt) {
+    H_CHECK(h);
+    ARG_CHECK(Q != nullptr, "NULL Q");
+    PredictParams p;
+    p.g = g; p.v = v; p.w = wheelbase; p.dt = dt;
+    memcpy(p.Q, Q, sizeof(p.Q));
+    int cols = h->n - 3;
+    int blocks = std::max(1, (cols + 255) / 256);
+    k_predict<<<blocks, 256, 0, h->stream>>>(h->d_x, h->d_P, h->ld, h->n, p, h->d_pose + 4 * h->pose_slot,
+                                             h->d_pose + 4 * (h->pose_slot ^ 1));
+    h->pose_slot ^= 1;
+    h->launches++;
+    CUDA_TRY(cudaGetLastError());
+    return SLAM_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// associate / compute_association / predict_observation host wrappers (kernels in gate.cu)
+// ---------------------------------------------------------------------------------------
+extern "C" int slam_associate(slam_t *h, const double *z, int nz, const double R[4], double gate1,
+                              double gate2, double *zf, int64_t *idf, int *m, double *zn, int *k) {
+    H_CHECK(h);
+    ARG_CHECK(R && m && k, "NULL argument");
+    ARG_CHECK(nz >= 0, "nz < 0");
+    *m = 0;
+    *k = 0;
+    if (nz == 0) return SLAM_OK;
+    ARG_CHECK(z && zf && idf && zn, "NULL observation buffer");
+    if (nz > SLAM_MAX_OBS) {
+        slam_set_error("slam_associate: nz = %d exceeds SLAM_MAX_OBS = %d", nz, SLAM_MAX_OBS);
+        return SLAM_ERR_CAPACITY;
+    }
+    double *hz = (double *)((char *)h->h_pin + 256);
+    memcpy(hz, z, sizeof(double) * 2 * nz);
+    CUDA_TRY(cudaMemcpyAsync(h->d_z, hz, sizeof(double) * 2 * nz, cudaMemcpyHostToDevice, h->stream));
+    int Nf = (h->n - 3) / 2;
+    int rc = launch_gate(h->d_x, h->d_P, h->ld, Nf, h->d_z, nz, R, gate1, gate2, h->d_gate_scratch,
+                         h->gate_scratch, h->d_zf, h->d_idf, h->d_zn, h->d_counts, h->stream, &h->launches);
+    if (rc) return rc;
+    // results: counts, zf, idf, zn -> pinned staging
+    int *hc = (int *)h->h_pin;
+    double *hzf = hz + 2 * SLAM_MAX_OBS;
+    double *hzn = hzf + 2 * SLAM_MAX_OBS;
+    int64_t *hid = (int64_t *)(hzn + 2 * SLAM_MAX_OBS);
+    CUDA_TRY(cudaMemcpyAsync(hc, h->d_counts, sizeof(int) * 2, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaMemcpyAsync(hzf, h->d_zf, sizeof(double) * 2 * nz, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaMemcpyAsync(hzn, h->d_zn, sizeof(double) * 2 * nz, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaMemcpyAsync(hid, h->d_idf, sizeof(int64_t) * nz, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    *m = hc[0];
+    *k = hc[1];
+    memcpy(zf, hzf, sizeof(double) * 2 * (*m));
+    memcpy(idf, hid, sizeof(int64_t) * (*m));
+    memcpy(zn, hzn, sizeof(double) * 2 * (*k));
+    return SLAM_OK;
+}
+
+extern "C" int slam_compute_association(slam_t *h, const double z[2], const double R[4], int64_t idf,
+                                        double *nis, double *nd) {
+    H_CHECK(h);
+    ARG_CHECK(z && R && nis && nd, "NULL argument");
+    int rc = launch_compute_association(h->d_x, h->d_P, h->ld, h->n, z, R, idf, h->d_small, h->d_err,
+                                        h->stream, &h->launches);
+    if (rc) return rc;
+    double *ho = (double *)h->h_pin + 16;
+    CUDA_TRY(cudaMemcpyAsync(ho, h->d_small, sizeof(double) * 2, cudaMemcpyDeviceToHost, h->stream));
+    rc = check_latched(h);
+    if (rc) return rc;
+    *nis = ho[0];
+    *nd = ho[1];
+    return SLAM_OK;
+}
+
+__global__ void k_predict_observation(const double *x, int n, int64_t idf, double *out, int *err) {
+    int Nf = (n - 3) / 2;
+    if (idf < 1 || idf > Nf) {
+        atomicCAS(err, 0, SLAM_ERR_BAD_INDEX);
+        return;
+    }
+    int f = 3 + 2 * ((int)idf - 1);
+    observe_model(x[0], x[1], x[2], x[f], x[f + 1], out, out + 2);
+}
+
+extern "C" int slam_predict_observation(slam_t *h, int64_t idf, double zp[2], double *H) {
+    H_CHECK(h);
+    ARG_CHECK(zp != nullptr, "NULL zp");
+    k_predict_observation<<<1, 1, 0, h->stream>>>(h->d_x, h->n, idf, h->d_small, h->d_err);
+    h->launches++;
+    CUDA_TRY(cudaGetLastError());
+    double *ho = (double *)h->h_pin + 16;
+    CUDA_TRY(cudaMemcpyAsync(ho, h->d_small, sizeof(double) * 12, cudaMemcpyDeviceToHost, h->stream));
+    int rc = check_latched(h);
+    if (rc) return rc;
+    zp[0] = ho[0];
+    zp[1] = ho[1];
+    if (H) {   // dense 2 x n, column-major (leading dimension 2), zeros elsewhere (src/common.jl:160-162)
+        const double *hn = ho + 2;
+        int n = h->n, f = 3 + 2 * ((int)idf - 1);
+        memset(H, 0, sizeof(double) * 2 * n);
+        for (int c = 0; c < 3; c++) {
+            H[2 * c] = hn[c];
+            H[2 * c + 1] = hn[3 + c];
+        }
+        H[2 * f] = hn[6];     H[2 * f + 1] = hn[8];
+        H[2 * (f + 1)] = hn[7]; H[2 * (f + 1) + 1] = hn[9];
+    }
+    return SLAM_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// K3 -- PHt = P*H' (src/ekf.jl:67) as a gather of 5 columns per observation, plus the
+// innovation v (:59).  Thread = row i.  PHt is stored k-major: PHt[k*npad + i].
+// Bytes: 8n(3 + 2m) read (5 columns per observation, the 3 pose columns shared), 16nm written.
+// ---------------------------------------------------------------------------------------
+constexpr int K3_THREADS = 256;
+constexpr int K3_OT = 64;   // observations staged per shared-memory tile
+
+__global__ void __launch_bounds__(K3_THREADS)
+k_pht(const double *__restrict__ x, const double *__restrict__ P, size_t ld, int n, int npad,
+      const double *__restrict__ zf, const int64_t *__restrict__ idf, int m, double *__restrict__ PHt,
+      double *__restrict__ v_out, double *__restrict__ Hn_out, int *__restrict__ fp_out, int *err) {
+    __shared__ double sH[K3_OT][10];
+    __shared__ int sF[K3_OT];
+    const int i = blockIdx.x * K3_THREADS + threadIdx.x;
+    const int Nf = (n - 3) / 2;
+    const double xv = x[0], yv = x[1], phi = x[2];
+    double p0 = 0, p1 = 0, p2 = 0;
+    if (i < n) {
+        p0 = sym_at(P, ld, i, 0);
+        p1 = sym_at(P, ld, i, 1);
+        p2 = sym_at(P, ld, i, 2);
+    }
+    for (int ot = 0; ot < m; ot += K3_OT) {
+        int cnt = min(K3_OT, m - ot);
+        __syncthreads();
+        if (threadIdx.x < cnt) {
+            int o = ot + threadIdx.x;
+            int64_t id = idf[o];
+            if (id < 1 || id > Nf) {
+                atomicCAS(err, 0, SLAM_ERR_BAD_INDEX);
+                id = 1;
+            }
+            int f = 3 + 2 * ((int)id - 1);
+            double zp[2];
+            observe_model(xv, yv, phi, x[f], x[f + 1], zp, sH[threadIdx.x]);
+            sF[threadIdx.x] = f;
+            if (blockIdx.x == 0) {
+                v_out[2 * o] = zf[2 * o] - zp[0];
+                v_out[2 * o + 1] = mpi_to_pi(zf[2 * o + 1] - zp[1]);
+                fp_out[o] = f;
+                for (int q = 0; q < 10; q++) Hn_out[10 * o + q] = sH[threadIdx.x][q];
+            }
+        }
+        __syncthreads();
+        if (i < n) {
+            for (int t = 0; t < cnt; t++) {
+                const double *hh = sH[t];
+                int f = sF[t];
+                double p3, p4;
+                if (i <= f) {
+                    p3 = P[(size_t)i + (size_t)f * ld];
+                    p4 = P[(size_t)i + (size_t)(f + 1) * ld];
+                } else {
+                    const double *ci = P + (size_t)i * ld;
+                    p3 = ci[f];
+                    p4 = (i == f + 1) ? P[(size_t)i + (size_t)(f + 1) * ld] : ci[f + 1];
+                }
+                int o = ot + t;
+                PHt[(size_t)(2 * o) * npad + i] = p0 * hh[0] + p1 * hh[1] + p2 * hh[2] + p3 * hh[6] + p4 * hh[7];
+                PHt[(size_t)(2 * o + 1) * npad + i] = p0 * hh[3] + p1 * hh[4] + p2 * hh[5] + p3 * hh[8] + p4 * hh[9];
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// K4 -- S = H*PHt + RR, S = (S+S')/2, C = inv(chol(S)) (src/ekf.jl:68-70), u = C'v.
+// One CTA.  Right-looking upper Cholesky (same subtraction order per entry as the
+// left-looking twin), then one thread per column of the triangular inverse.
+// ---------------------------------------------------------------------------------------
+constexpr int K4_THREADS = 512;
+
+__global__ void __launch_bounds__(K4_THREADS)
+k_innov_chol(const double *__restrict__ PHt, int npad, const double *__restrict__ Hn,
+             const int *__restrict__ fp, const double *__restrict__ v, int m, double R0, double R1,
+             double R2, double R3, double *S, double *C, double *u, int *err) {
+    const int R = 2 * m;
+    const int tid = threadIdx.x;
+    __shared__ int s_fail;
+    if (tid == 0) s_fail = 0;
+    for (int idx = tid; idx < m * R; idx += K4_THREADS) {
+        int o = idx / R, k = idx % R;
+        const double *h = Hn + 10 * o;
+        int f = fp[o];
+        const double *col = PHt + (size_t)k * npad;
+        double a0 = col[0], a1 = col[1], a2 = col[2], a3 = col[f], a4 = col[f + 1];
+        double s0 = h[0] * a0 + h[1] * a1 + h[2] * a2 + h[6] * a3 + h[7] * a4;
+        double s1 = h[3] * a0 + h[4] * a1 + h[5] * a2 + h[8] * a3 + h[9] * a4;
+        if (k == 2 * o) { s0 += R0; s1 += R1; }          // RR[ii,ii] = R (:60), R column-major
+        if (k == 2 * o + 1) { s0 += R2; s1 += R3; }
+        S[(size_t)(2 * o) + (size_t)k * R] = s0;
+        S[(size_t)(2 * o + 1) + (size_t)k * R] = s1;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < R * R; idx += K4_THREADS) {
+        int a = idx % R, b = idx / R;
+        if (a < b) {
+            double s = (S[(size_t)a + (size_t)b * R] + S[(size_t)b + (size_t)a * R]) * 0.5;
+            S[(size_t)a + (size_t)b * R] = s;
+            S[(size_t)b + (size_t)a * R] = s;
+        } else if (a == b) {
+            S[(size_t)a + (size_t)a * R] = (S[(size_t)a + (size_t)a * R] + S[(size_t)a + (size_t)a * R]) * 0.5;
+        }
+    }
+    __syncthreads();
+    for (int k = 0; k < R; k++) {
+        if (tid == 0) {
+            double d = S[(size_t)k + (size_t)k * R];
+            if (!(d > 0)) s_fail = 1;
+            else S[(size_t)k + (size_t)k * R] = sqrt(d);
+        }
+        __syncthreads();
+        if (s_fail) break;
+        double ukk = S[(size_t)k + (size_t)k * R];
+        for (int j = k + 1 + tid; j < R; j += K4_THREADS) S[(size_t)k + (size_t)j * R] /= ukk;
+        __syncthreads();
+        int rem = R - k - 1;
+        for (int idx = tid; idx < rem * rem; idx += K4_THREADS) {
+            int i = k + 1 + idx % rem, j = k + 1 + idx / rem;
+            if (i <= j) S[(size_t)i + (size_t)j * R] -= S[(size_t)k + (size_t)i * R] * S[(size_t)k + (size_t)j * R];
+        }
+        __syncthreads();
+    }
+    if (s_fail) {
+        if (tid == 0) atomicCAS(err, 0, SLAM_ERR_NOT_PD);
+        for (int idx = tid; idx < R * R; idx += K4_THREADS) C[idx] = 0.0;   // update becomes a no-op
+        for (int k = tid; k < R; k += K4_THREADS) u[k] = 0.0;
+        return;
+    }
+    // C = inv(U), upper triangular, column by column
+    for (int j = tid; j < R; j += K4_THREADS) {
+        C[(size_t)j + (size_t)j * R] = 1.0 / S[(size_t)j + (size_t)j * R];
+        for (int i = j - 1; i >= 0; i--) {
+            double a = 0;
+            for (int k = i + 1; k <= j; k++) a += S[(size_t)i + (size_t)k * R] * C[(size_t)k + (size_t)j * R];
+            C[(size_t)i + (size_t)j * R] = -a / S[(size_t)i + (size_t)i * R];
+        }
+        for (int i = j + 1; i < R; i++) C[(size_t)i + (size_t)j * R] = 0.0;
+        double a = 0;
+        for (int l = 0; l <= j; l++) a += C[(size_t)l + (size_t)j * R] * v[l];
+        u[j] = a;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// K5 -- W1 = PHt*C (src/ekf.jl:71) and x += W*v = W1*(C'v) (:72-74).  Thread = row i.
+// W1 is written in the chunked row-major layout K6 stages with bulk copies.
+// ---------------------------------------------------------------------------------------
+constexpr int K5_THREADS = 128;
+
+__global__ void __launch_bounds__(K5_THREADS)
+k_gain(const double *__restrict__ PHt, int npad, int n, int R, const double *__restrict__ C,
+       const double *__restrict__ u, int RC, double *__restrict__ W1c, double *__restrict__ x,
+       double *pose_snapshot) {
+    extern __shared__ double sC[];   // R*R when it fits, else unused
+    const bool use_s = (size_t)R * R * sizeof(double) <= 32768;
+    if (use_s) {
+        for (int idx = threadIdx.x; idx < R * R; idx += K5_THREADS) sC[idx] = C[idx];
+        __syncthreads();
+    }
+    const double *Cm = use_s ? sC : C;
+    const int i = blockIdx.x * K5_THREADS + threadIdx.x;
+    if (i >= npad) return;
+    const int nch = (R + RC - 1) / RC;
+    if (i >= n) {
+        for (int c = 0; c < nch; c++)
+            for (int kk = 0; kk < RC; kk++) W1c[((size_t)c * npad + i) * RC + kk] = 0.0;
+        return;
+    }
+    double dxi = 0;
+    for (int k = 0; k < nch * RC; k++) {
+        double a = 0;
+        if (k < R)
+            for (int l = 0; l <= k; l++) a += PHt[(size_t)l * npad + i] * Cm[(size_t)l + (size_t)k * R];
+        W1c[((size_t)(k / RC) * npad + i) * RC + (k % RC)] = a;
+        if (k < R) dxi += a * u[k];
+    }
+    double xi = x[i] + dxi;
+    x[i] = xi;
+    if (i < 3) pose_snapshot[i] = xi;
+}
+
+static int update_device(slam_t *h, const double *d_zf, int m, const double R[4], const int64_t *d_idf) {
+    if (m == 0) return SLAM_OK;   // first observation step of every run (sim/ekfslam-sim.jl:114-117)
+    if (m > SLAM_MAX_OBS) {
+        slam_set_error("slam_update: m = %d exceeds SLAM_MAX_OBS = %d", m, SLAM_MAX_OBS);
+        return SLAM_ERR_CAPACITY;
+    }
+    if (h->n <= 3) {
+        slam_set_error("slam_update: %d observations but the map is empty", m);
+        return SLAM_ERR_BAD_INDEX;
+    }
+    const int Rk = 2 * m;
+    int rc = ensure_update_ws(h, Rk);
+    if (rc) return rc;
+    const int n = h->n, npad = h->ws_npad;
+    const int RC = downdate_chunk_width(Rk);
+    k_pht<<<(n + K3_THREADS - 1) / K3_THREADS, K3_THREADS, 0, h->stream>>>(
+        h->d_x, h->d_P, h->ld, n, npad, d_zf, d_idf, m, h->d_PHt, h->d_v, h->d_Hn, h->d_fp, h->d_err);
+    k_innov_chol<<<1, K4_THREADS, 0, h->stream>>>(h->d_PHt, npad, h->d_Hn, h->d_fp, h->d_v, m, R[0], R[1],
+                                                  R[2], R[3], h->d_S, h->d_C, h->d_u, h->d_err);
+    size_t sm = (size_t)Rk * Rk * sizeof(double) <= 32768 ? (size_t)Rk * Rk * sizeof(double) : 0;
+    int npad_used = round_up(n, DD_ROW_PAD);
+    k_gain<<<(npad_used + K5_THREADS - 1) / K5_THREADS, K5_THREADS, sm, h->stream>>>(
+        h->d_PHt, npad, n, Rk, h->d_C, h->d_u, RC, h->d_W1c, h->d_x, h->d_pose + 4 * h->pose_slot);
+    h->launches += 3;
+    CUDA_TRY(cudaGetLastError());
+    const bool timed = h->profiling && h->ev_used + 2 <= (int)h->ev.size();
+    if (timed) CUDA_TRY(cudaEventRecord(h->ev[h->ev_used], h->stream));
+    rc = launch_downdate(h->d_P, h->ld, n, h->d_W1c, npad, Rk, h->variant, h->stream, &h->launches);
+    if (timed) {
+        CUDA_TRY(cudaEventRecord(h->ev[h->ev_used + 1], h->stream));
+        h->ev_used += 2;
+    }
+    return rc;
+}
+
+extern "C" int slam_profile(slam_t *h, int on) {
+    H_CHECK(h);
+    if (on && h->ev.empty()) {
+        h->ev.resize(2 * 4096);
+        for (auto &e : h->ev) CUDA_TRY(cudaEventCreate(&e));
+    }
+    h->profiling = on != 0;
+    h->ev_used = 0;
+    return SLAM_OK;
+}
+
+extern "C" int slam_profile_read(slam_t *h, double *k6_ms, int *k6_updates) {
+    H_CHECK(h);
+    ARG_CHECK(k6_ms && k6_updates, "NULL argument");
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    double tot = 0;
+    for (int i = 0; i + 1 < h->ev_used; i += 2) {
+        float ms = 0;
+        CUDA_TRY(cudaEventElapsedTime(&ms, h->ev[i], h->ev[i + 1]));
+        tot += ms;
+    }
+    *k6_ms = tot;
+    *k6_updates = h->ev_used / 2;
+    h->ev_used = 0;
+    return SLAM_OK;
+}
+
+extern "C" int slam_update_resident(slam_t *h, const double *d_zf, int m, const double R[4],
+                                    const int64_t *d_idf) {
+    H_CHECK(h);
+    ARG_CHECK(m >= 0 && R, "bad argument");
+    ARG_CHECK(m == 0 || (d_zf && d_idf), "NULL device buffer");
+    return update_device(h, d_zf, m, R, d_idf);
+}
+
+extern "C" int slam_update(slam_t *h, const double *zf, int m, const double R[4], const int64_t *idf) {
+    H_CHECK(h);
+    ARG_CHECK(m >= 0 && R, "bad argument");
+    if (m == 0) return SLAM_OK;
+    ARG_CHECK(zf && idf, "NULL observation buffer");
+    if (m > SLAM_MAX_OBS) {
+        slam_set_error("slam_update: m = %d exceeds SLAM_MAX_OBS = %d", m, SLAM_MAX_OBS);
+        return SLAM_ERR_CAPACITY;
+    }
+    double *hz = (double *)((char *)h->h_pin + 256);
+    int64_t *hid = (int64_t *)(hz + 6 * SLAM_MAX_OBS);
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    memcpy(hz, zf, sizeof(double) * 2 * m);
+    memcpy(hid, idf, sizeof(int64_t) * m);
+    CUDA_TRY(cudaMemcpyAsync(h->d_zf, hz, sizeof(double) * 2 * m, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaMemcpyAsync(h->d_idf, hid, sizeof(int64_t) * m, cudaMemcpyHostToDevice, h->stream));
+    int rc = update_device(h, h->d_zf, m, R, h->d_idf);
+    if (rc) return rc;
+    return check_latched(h);
+}
+
+// ---------------------------------------------------------------------------------------
+// K7 -- add_features (src/ekf.jl:84-122) as an in-place strided append into spare capacity.
+// A launch handles up to K7_Q new landmarks; thread (j, q) writes the two new entries of
+// existing column/row j for new landmark q.  Bytes per landmark: 24n read, 16n written.
+// ---------------------------------------------------------------------------------------
+constexpr int K7_Q = 32;
+constexpr int K7_THREADS = 256;
+
+__global__ void __launch_bounds__(K7_THREADS)
+k_augment(double *x, double *P, size_t ld, int n0, const double *__restrict__ zn, int kq, double R0,
+          double R1, double R2, double R3) {
+    // n0: state length before this launch's first landmark; kq <= K7_Q landmarks
+    __shared__ double sGv[K7_Q][2];     // Gv = [1 0 g0; 0 1 g1]
+    __shared__ double sGP[K7_Q][2][3];  // Gv*Pvv
+    __shared__ double sPvv[9];
+    if (threadIdx.x < 9) sPvv[threadIdx.x] = sym_at(P, ld, threadIdx.x / 3, threadIdx.x % 3);
+    __syncthreads();
+    const double xv = x[0], yv = x[1], phi = x[2];
+    if (threadIdx.x < kq) {
+        int q = threadIdx.x;
+        double r = zn[2 * q], b = zn[2 * q + 1];
+        double s = sin(phi + b), c = cos(phi + b);
+        double g0 = -r * s, g1 = r * c;
+        sGv[q][0] = g0;
+        sGv[q][1] = g1;
+        const double Gv[2][3] = {{1, 0, g0}, {0, 1, g1}};
+        for (int a = 0; a < 2; a++)
+            for (int j = 0; j < 3; j++)
+                sGP[q][a][j] = Gv[a][0] * sPvv[0 * 3 + j] + Gv[a][1] * sPvv[1 * 3 + j] + Gv[a][2] * sPvv[2 * 3 + j];
+        if (blockIdx.x == 0 && blockIdx.y == q) {
+            // x and the new diagonal block, written once
+            int len = n0 + 2 * q;
+            x[len] = xv + r * c;
+            x[len + 1] = yv + r * s;
+            const double Gz[2][2] = {{c, -r * s}, {s, r * c}};
+            const double Rm[4] = {R0, R1, R2, R3};
+            double GR[2][2];
+            for (int a = 0; a < 2; a++)
+                for (int j = 0; j < 2; j++) GR[a][j] = Gz[a][0] * Rm[0 + 2 * j] + Gz[a][1] * Rm[1 + 2 * j];
+            for (int a = 0; a < 2; a++)
+                for (int bb = a; bb < 2; bb++) {
+                    double t1 = sGP[q][a][0] * Gv[bb][0] + sGP[q][a][1] * Gv[bb][1] + sGP[q][a][2] * Gv[bb][2];
+                    double t2 = GR[a][0] * Gz[bb][0] + GR[a][1] * Gz[bb][1];
+                    P[(size_t)(len + a) + (size_t)(len + bb) * ld] = t1 + t2;
+                }
+        }
+    }
+    __syncthreads();
+    const int q = blockIdx.y;
+    if (q >= kq) return;
+    const int len = n0 + 2 * q;
+    const int j = blockIdx.x * K7_THREADS + threadIdx.x;
+    if (j >= len) return;
+    double c0, c1, c2;   // P[1:3, j]
+    if (j < 3) {
+        c0 = sPvv[0 * 3 + j]; c1 = sPvv[1 * 3 + j]; c2 = sPvv[2 * 3 + j];
+    } else if (j < n0) {
+        const double *col = P + (size_t)j * ld;
+        c0 = col[0]; c1 = col[1]; c2 = col[2];
+    } else {   // a landmark added earlier in this launch: P[1:3, j] = (Gv'*Pvv)' of that landmark
+        int qq = (j - n0) / 2, a = (j - n0) % 2;
+        c0 = sGP[qq][a][0]; c1 = sGP[qq][a][1]; c2 = sGP[qq][a][2];
+    }
+    double g0 = sGv[q][0], g1 = sGv[q][1];
+    // Gv = [1 0 g0; 0 1 g1]: t_a = Gv[a][0]*c0 + Gv[a][1]*c1 + Gv[a][2]*c2
+    double t0 = 1.0 * c0 + 0.0 * c1 + g0 * c2;
+    double t1 = 0.0 * c0 + 1.0 * c1 + g1 * c2;
+    P[(size_t)j + (size_t)len * ld] = t0;
+    P[(size_t)j + (size_t)(len + 1) * ld] = t1;
+}
+
+extern "C" int slam_add_features(slam_t *h, const double *zn, int k, const double R[4]) {
+    H_CHECK(h);
+    ARG_CHECK(k >= 0 && R, "bad argument");
+    if (k == 0) return SLAM_OK;
+    ARG_CHECK(zn != nullptr, "NULL zn");
+    if (k > SLAM_MAX_OBS || h->n + 2 * k > h->n_max) {
+        slam_set_error("slam_add_features: n + 2k = %d exceeds capacity n_max = %d", h->n + 2 * k, h->n_max);
+        return SLAM_ERR_CAPACITY;
+    }
+    double *hz = (double *)((char *)h->h_pin + 256);
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    memcpy(hz, zn, sizeof(double) * 2 * k);
+    CUDA_TRY(cudaMemcpyAsync(h->d_zn, hz, sizeof(double) * 2 * k, cudaMemcpyHostToDevice, h->stream));
+    for (int q0 = 0; q0 < k; q0 += K7_Q) {
+        int kq = std::min(K7_Q, k - q0);
+        int n0 = h->n;
+        dim3 grid((n0 + 2 * kq + K7_THREADS - 1) / K7_THREADS, kq);
+        k_augment<<<grid, K7_THREADS, 0, h->stream>>>(h->d_x, h->d_P, h->ld, n0, h->d_zn + 2 * q0, kq, R[0],
+                                                      R[1], R[2], R[3]);
+        h->launches++;
+        h->n = n0 + 2 * kq;
+    }
+    CUDA_TRY(cudaGetLastError());
+    return SLAM_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// synthetic large-map state (synth.cu)
+// ---------------------------------------------------------------------------------------
+extern "C" int slam_synth_state(slam_t *h, int n_landmarks, double side, uint64_t seed) {
+    H_CHECK(h);
+    ARG_CHECK(n_landmarks >= 0 && side > 0, "bad argument");
+    int n = 3 + 2 * n_landmarks;
+    if (n > h->n_max) {
+        slam_set_error("slam_synth_state: n = %d exceeds capacity n_max = %d", n, h->n_max);
+        return SLAM_ERR_CAPACITY;
+    }
+    int rc = synth_fill(h->d_x, h->d_P, h->ld, 0, n, n_landmarks, side, seed, h->stream, &h->launches);
+    if (rc) return rc;
+    h->n = n;
+    k_set_pose_snapshot<<<1, 32, 0, h->stream>>>(h->d_x, h->d_pose + 4 * h->pose_slot);
+    h->launches++;
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return SLAM_OK;
+}
+
+extern "C" int slam_synth_observations(slam_t *h, int n_landmarks, double side, uint64_t seed, int m,
+                                       int spurious, double *z, int64_t *ids) {
+    (void)h;
+    ARG_CHECK(z != nullptr, "NULL z");
+    return synth_observations_host(n_landmarks, side, seed, m, spurious, z, ids);
+}

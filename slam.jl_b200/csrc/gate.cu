@@ -1,0 +1,300 @@
+// K2 -- Mahalanobis nearest-neighbour gating: associate() and compute_association()
+// (src/data-association.jl:1-63).  This translation unit is compiled with -fmad=false so that
+// every product/sum rounds exactly as the plain-C oracle twin does (gate tests are strict
+// FP64 comparisons, :30-31,38,46).
+//
+// The reference forms S = H*P*H' + R with a dense 2 x n Jacobian; H has nonzeros only in
+// columns {1,2,3,fpos,fpos+1} (src/common.jl:160-162), so S depends on a 5 x 5 sub-block of P.
+// One thread owns a landmark j: it gathers that sub-block once, forms S, det(S) and inv(S)
+// in closed form, then scores up to OB observations held in registers.  Per observation
+// the running (nd, j) minimum over gated landmarks and the minimum nis are reduced with warp
+// shuffles (lowest j wins ties, NaN never wins -- the strict `<` of the reference), then
+// across warps in shared memory, then across CTAs by the last CTA to finish, which also
+// classifies each observation {matched, new, dropped} and compacts zf / idf / zn in
+// observation order.
+//
+// Equivalence of the parallel reduction with the reference's sequential scan: `outer` is
+// only consulted when jbest == 0 (:43-46), i.e. when no landmark ever passed
+// `nis < gate1 && nd < nbest`; then every landmark fell to the `elseif nis < outer` branch,
+// so outer = min_j nis_j independent of scan order.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace {
+
+constexpr int GATE_THREADS = 256;
+constexpr int OB = 8;            // observations scored per thread per pass
+constexpr int GATE_MAX_BLOCKS = 592;
+
+struct Innov {     // per-landmark quantities that do not depend on the observation
+    double zp0, zp1, i11, i12, i21, i22, logdet;
+};
+
+// 2x2 innovation covariance from the 5x5 sub-block; Pvv is the symmetric 3x3 pose block.
+__device__ __forceinline__ Innov landmark_innov(const double *__restrict__ x, const double *__restrict__ P,
+                                                size_t ld, int f, const double *Pvv, double xv, double yv,
+                                                double phi, const double *R) {
+    double zp[2], h[10];
+    observe_model(xv, yv, phi, x[f], x[f + 1], zp, h);
+    double P5[5][5];
+#pragma unroll
+    for (int p = 0; p < 3; p++)
+#pragma unroll
+        for (int q = 0; q < 3; q++) P5[p][q] = Pvv[p * 3 + q];
+    const double *c0 = P + (size_t)f * ld;
+    const double *c1 = c0 + ld;
+#pragma unroll
+    for (int p = 0; p < 3; p++) {
+        P5[p][3] = c0[p];
+        P5[p][4] = c1[p];
+        P5[3][p] = P5[p][3];
+        P5[4][p] = P5[p][4];
+    }
+    P5[3][3] = c0[f];
+    P5[3][4] = c1[f];
+    P5[4][3] = P5[3][4];
+    P5[4][4] = c1[f + 1];
+    const double Hr[2][5] = {{h[0], h[1], h[2], h[6], h[7]}, {h[3], h[4], h[5], h[8], h[9]}};
+    double HP[2][5];
+#pragma unroll
+    for (int a = 0; a < 2; a++)
+#pragma unroll
+        for (int q = 0; q < 5; q++) {
+            double acc = 0;
+#pragma unroll
+            for (int p = 0; p < 5; p++) acc += Hr[a][p] * P5[p][q];
+            HP[a][q] = acc;
+        }
+    double S[4];
+#pragma unroll
+    for (int a = 0; a < 2; a++)
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            double acc = 0;
+#pragma unroll
+            for (int q = 0; q < 5; q++) acc += HP[a][q] * Hr[b][q];
+            S[2 * a + b] = acc + R[a + 2 * b];
+        }
+    double det = S[0] * S[3] - S[1] * S[2];
+    Innov o;
+    o.zp0 = zp[0];
+    o.zp1 = zp[1];
+    o.i11 = S[3] / det;
+    o.i12 = -S[1] / det;
+    o.i21 = -S[2] / det;
+    o.i22 = S[0] / det;
+    o.logdet = log(det);
+    return o;
+}
+
+__device__ __forceinline__ void score(const Innov &L, double z0, double z1, double *nis, double *nd) {
+    double v0 = z0 - L.zp0;
+    double v1 = mpi_to_pi(z1 - L.zp1);
+    double t0 = L.i11 * v0 + L.i12 * v1;
+    double t1 = L.i21 * v0 + L.i22 * v1;
+    *nis = v0 * t0 + v1 * t1;
+    *nd = *nis + L.logdet;
+}
+
+struct GateParams {
+    double R[4];
+    double gate1, gate2;
+};
+
+// scratch: [0] unsigned counter, then part_nd / part_outer (double) and part_j (int) of
+// nblocks*nz entries each
+__global__ void __launch_bounds__(GATE_THREADS)
+k_gate(const double *__restrict__ x, const double *__restrict__ P, size_t ld, int Nf,
+       const double *__restrict__ z, int nz, GateParams prm, unsigned *counter, double *part_nd,
+       double *part_outer, int *part_j, double *zf, int64_t *idf, double *zn, int *counts) {
+    __shared__ double sPvv[9];
+    __shared__ double s_nd[GATE_THREADS / 32][OB], s_outer[GATE_THREADS / 32][OB];
+    __shared__ int s_j[GATE_THREADS / 32][OB];
+    __shared__ bool s_last;
+    const int nblocks = gridDim.x;
+    const int ob0 = blockIdx.y * OB;
+    if (threadIdx.x < 9) {
+        int p = threadIdx.x / 3, q = threadIdx.x % 3;
+        sPvv[threadIdx.x] = sym_at(P, ld, p, q);
+    }
+    __syncthreads();
+    const double xv = x[0], yv = x[1], phi = x[2];
+    double zr[OB], zb[OB], best[OB], outer[OB];
+    int jb[OB];
+#pragma unroll
+    for (int o = 0; o < OB; o++) {
+        int io = ob0 + o;
+        zr[o] = io < nz ? z[2 * io] : 0.0;
+        zb[o] = io < nz ? z[2 * io + 1] : 0.0;
+        best[o] = INFINITY;
+        outer[o] = INFINITY;
+        jb[o] = 0;
+    }
+    for (int j = blockIdx.x * GATE_THREADS + threadIdx.x + 1; j <= Nf; j += nblocks * GATE_THREADS) {
+        Innov L = landmark_innov(x, P, ld, 3 + 2 * (j - 1), sPvv, xv, yv, phi, prm.R);
+#pragma unroll
+        for (int o = 0; o < OB; o++) {
+            double nis, nd;
+            score(L, zr[o], zb[o], &nis, &nd);
+            if (nis < prm.gate1 && nd < best[o]) {
+                best[o] = nd;
+                jb[o] = j;
+            }
+            if (nis < outer[o]) outer[o] = nis;
+        }
+    }
+    // warp reduction: (nd, j) lexicographic minimum, and min outer
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 0; o < OB; o++) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            double nd2 = __shfl_down_sync(0xffffffffu, best[o], off);
+            int j2 = __shfl_down_sync(0xffffffffu, jb[o], off);
+            double ou2 = __shfl_down_sync(0xffffffffu, outer[o], off);
+            if (j2 != 0 && (jb[o] == 0 || nd2 < best[o] || (nd2 == best[o] && j2 < jb[o]))) {
+                best[o] = nd2;
+                jb[o] = j2;
+            }
+            if (ou2 < outer[o]) outer[o] = ou2;
+        }
+        if (lane == 0) {
+            s_nd[warp][o] = best[o];
+            s_j[warp][o] = jb[o];
+            s_outer[warp][o] = outer[o];
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < OB && ob0 + threadIdx.x < nz) {
+        int o = threadIdx.x;
+        double b = s_nd[0][o], ou = s_outer[0][o];
+        int jj = s_j[0][o];
+        for (int w = 1; w < GATE_THREADS / 32; w++) {
+            double nd2 = s_nd[w][o];
+            int j2 = s_j[w][o];
+            if (j2 != 0 && (jj == 0 || nd2 < b || (nd2 == b && j2 < jj))) {
+                b = nd2;
+                jj = j2;
+            }
+            if (s_outer[w][o] < ou) ou = s_outer[w][o];
+        }
+        size_t slot = (size_t)blockIdx.x * nz + ob0 + o;
+        part_nd[slot] = b;
+        part_j[slot] = jj;
+        part_outer[slot] = ou;
+    }
+    // last CTA to finish reduces across CTAs, classifies and compacts
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned total = gridDim.x * gridDim.y;
+        unsigned t = atomicAdd(counter, 1u);
+        s_last = (t == total - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    __shared__ int s_cls[SLAM_MAX_OBS];   // >0: matched landmark id, 0: dropped, -1: new
+    for (int i = threadIdx.x; i < nz; i += GATE_THREADS) {
+        double b = INFINITY, ou = INFINITY;
+        int jj = 0;
+        for (int blk = 0; blk < nblocks; blk++) {
+            size_t slot = (size_t)blk * nz + i;
+            double nd2 = part_nd[slot];
+            int j2 = part_j[slot];
+            if (j2 != 0 && (jj == 0 || nd2 < b || (nd2 == b && j2 < jj))) {
+                b = nd2;
+                jj = j2;
+            }
+            if (part_outer[slot] < ou) ou = part_outer[slot];
+        }
+        s_cls[i] = jj != 0 ? jj : (ou > prm.gate2 ? -1 : 0);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int m = 0, k = 0;
+        for (int i = 0; i < nz; i++) {
+            int c = s_cls[i];
+            if (c > 0) {
+                zf[2 * m] = z[2 * i];
+                zf[2 * m + 1] = z[2 * i + 1];
+                idf[m] = c;
+                m++;
+            } else if (c < 0) {
+                zn[2 * k] = z[2 * i];
+                zn[2 * k + 1] = z[2 * i + 1];
+                k++;
+            }
+        }
+        counts[0] = m;
+        counts[1] = k;
+        *counter = 0;
+    }
+}
+
+__global__ void k_compute_association(const double *__restrict__ x, const double *__restrict__ P,
+                                      size_t ld, int n, double z0, double z1, GateParams prm, int64_t idf,
+                                      double *out, int *err) {
+    int Nf = (n - 3) / 2;
+    if (idf < 1 || idf > Nf) {
+        atomicCAS(err, 0, SLAM_ERR_BAD_INDEX);
+        out[0] = out[1] = nan("");
+        return;
+    }
+    double Pvv[9];
+    for (int p = 0; p < 3; p++)
+        for (int q = 0; q < 3; q++) Pvv[p * 3 + q] = sym_at(P, ld, p, q);
+    Innov L = landmark_innov(x, P, ld, 3 + 2 * ((int)idf - 1), Pvv, x[0], x[1], x[2], prm.R);
+    score(L, z0, z1, &out[0], &out[1]);
+}
+
+}  // namespace
+
+static int gate_nblocks(int Nf) {
+    int nb = (Nf + GATE_THREADS - 1) / GATE_THREADS;
+    if (nb < 1) nb = 1;
+    if (nb > GATE_MAX_BLOCKS) nb = GATE_MAX_BLOCKS;
+    return nb;
+}
+
+size_t gate_scratch_bytes(int nz) {
+    size_t per = (size_t)GATE_MAX_BLOCKS * (size_t)(nz > 0 ? nz : 1);
+    return 256 + per * (8 + 8 + 4);
+}
+
+int launch_gate(const double *d_x, const double *d_P, size_t ld, int Nf, const double *d_z, int nz,
+                const double R[4], double gate1, double gate2, void *d_scratch, size_t scratch_bytes,
+                double *d_zf, int64_t *d_idf, double *d_zn, int *d_counts, cudaStream_t s,
+                long long *launches) {
+    if (scratch_bytes < gate_scratch_bytes(nz)) {
+        slam_set_error("launch_gate: scratch too small");
+        return SLAM_ERR_ARG;
+    }
+    GateParams prm;
+    memcpy(prm.R, R, sizeof(prm.R));
+    prm.gate1 = gate1;
+    prm.gate2 = gate2;
+    size_t per = (size_t)GATE_MAX_BLOCKS * (size_t)nz;
+    unsigned *counter = (unsigned *)d_scratch;
+    double *part_nd = (double *)((char *)d_scratch + 256);
+    double *part_outer = part_nd + per;
+    int *part_j = (int *)(part_outer + per);
+    dim3 grid(gate_nblocks(Nf), (nz + OB - 1) / OB);
+    k_gate<<<grid, GATE_THREADS, 0, s>>>(d_x, d_P, ld, Nf, d_z, nz, prm, counter, part_nd, part_outer,
+                                        part_j, d_zf, d_idf, d_zn, d_counts);
+    if (launches) (*launches)++;
+    CUDA_TRY(cudaGetLastError());
+    return SLAM_OK;
+}
+
+int launch_compute_association(const double *d_x, const double *d_P, size_t ld, int n, const double z[2],
+                               const double R[4], int64_t idf, double *d_out2, int *d_err,
+                               cudaStream_t s, long long *launches) {
+    GateParams prm;
+    memcpy(prm.R, R, sizeof(prm.R));
+    prm.gate1 = prm.gate2 = 0;
+    k_compute_association<<<1, 1, 0, s>>>(d_x, d_P, ld, n, z[0], z[1], prm, idf, d_out2, d_err);
+    if (launches) (*launches)++;
+    CUDA_TRY(cudaGetLastError());
+    return SLAM_OK;
+}

@@ -1,0 +1,285 @@
+"""Host-side mirror of the reference's `module SLAM` filter surface (src/SLAM.jl:5-30) over
+the C ABI of libslamcuda.so.  Same names, positional arguments and return conventions as
+the Julia functions so the parity tests read like calls into the reference:
+
+    state.x, state.cov = predict(state, vehicle, Q, dt)          # src/ekf.jl:8
+    zf, idf, zn        = associate(state, z, R, gate1, gate2)    # src/data-association.jl:1
+    state.x, state.cov = update(state, zf, R, idf)               # src/ekf.jl:46
+    state.x, state.cov = add_features(state, zn, R)              # src/ekf.jl:84
+
+Two state types:
+  * EKFSlamState        -- host-mirror mode: x / cov are numpy arrays; every call uploads
+                           them, runs the CUDA kernels and downloads the result.
+  * DeviceEKFSlamState  -- resident mode: x / cov stay on the device behind a handle;
+                           calls return the state object's lazy views.
+All arithmetic of the filter runs in the CUDA library; there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _ffi
+from ._ffi import lib, check, dptr, iptr
+
+PI = math.pi
+
+
+def mpi_to_pi(phi: float) -> float:
+    """src/common.jl:102-110 (scalar host helper; the device has its own copy)."""
+    if phi > PI:
+        return phi - 2 * PI
+    if phi < -PI:
+        return phi + 2 * PI
+    return phi
+
+
+@dataclass
+class Vehicle:
+    """The fields of src/common.jl:36-55 that `predict` reads (src/ekf.jl:14-16)."""
+    wheelbase: float = 4.0
+    measured_gamma: float = 0.0
+    measured_speed: float = 0.0
+    pose: np.ndarray = field(default_factory=lambda: np.zeros(3))
+
+
+def _f64(a, shape=None):
+    a = np.ascontiguousarray(np.asarray(a, dtype=np.float64))
+    return a if shape is None else a.reshape(shape)
+
+
+def _cols(z):
+    """2 x k Julia matrix -> flat column-major buffer and k."""
+    z = np.asarray(z, dtype=np.float64)
+    if z.size == 0:
+        return np.zeros(0), 0
+    z = z.reshape(2, -1)
+    return np.ascontiguousarray(z.T).reshape(-1), z.shape[1]
+
+
+def _mat2(M):
+    """2 x 2 matrix -> column-major 4-vector."""
+    return np.ascontiguousarray(np.asarray(M, dtype=np.float64).reshape(2, 2).T).reshape(-1)
+
+
+class _Handle:
+    """Owns a slam_t*; grows capacity by re-creating the device state."""
+
+    def __init__(self, device: int = 0, n_max: int = 256):
+        self.device = device
+        self.n_max = n_max
+        self.ptr = C.c_void_p()
+        check(lib.slam_create(device, n_max, C.byref(self.ptr)))
+
+    def close(self):
+        if self.ptr:
+            lib.slam_destroy(self.ptr)
+            self.ptr = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def n(self) -> int:
+        return check(lib.slam_n(self.ptr))
+
+    def set_state(self, x, P):
+        x = _f64(x)
+        n = x.shape[0]
+        Pf = np.asfortranarray(np.asarray(P, dtype=np.float64))
+        assert Pf.shape == (n, n)
+        check(lib.slam_set_state(self.ptr, dptr(x), dptr(Pf), n, n))
+
+    def get_state(self):
+        n = self.n
+        x = np.empty(n)
+        P = np.empty((n, n), order="F")
+        check(lib.slam_get_state(self.ptr, dptr(x), dptr(P), n))
+        return x, np.ascontiguousarray(P)
+
+    def get_x(self):
+        x = np.empty(self.n)
+        check(lib.slam_get_state(self.ptr, dptr(x), None, 0))
+        return x
+
+    def get_pose(self):
+        p = np.empty(3)
+        check(lib.slam_get_pose(self.ptr, dptr(p)))
+        return p
+
+    def cov_block(self, i0, ni, j0, nj):
+        out = np.empty((ni, nj), order="F")
+        check(lib.slam_get_cov_block(self.ptr, i0, ni, j0, nj, dptr(out), max(ni, 1)))
+        return np.ascontiguousarray(out)
+
+    # -- raw operations ------------------------------------------------------------------
+    def predict(self, g, v, w, Q, dt):
+        q = _mat2(Q)
+        check(lib.slam_predict(self.ptr, float(g), float(v), float(w), dptr(q), float(dt)))
+
+    def associate(self, z, R, gate1, gate2):
+        zc, nz = _cols(z)
+        r = _mat2(R)
+        zf = np.zeros(2 * max(nz, 1))
+        zn = np.zeros(2 * max(nz, 1))
+        idf = np.zeros(max(nz, 1), dtype=np.int64)
+        m, k = C.c_int(0), C.c_int(0)
+        check(lib.slam_associate(self.ptr, dptr(zc), nz, dptr(r), float(gate1), float(gate2), dptr(zf),
+                                 iptr(idf), C.byref(m), dptr(zn), C.byref(k)))
+        m, k = m.value, k.value
+        return (zf[:2 * m].reshape(m, 2).T.copy(), idf[:m].copy(), zn[:2 * k].reshape(k, 2).T.copy())
+
+    def update(self, zf, R, idf):
+        zc, m = _cols(zf)
+        ids = np.ascontiguousarray(np.asarray(idf, dtype=np.int64).reshape(-1))
+        assert ids.shape[0] == m, "idf must have one id per column of z"
+        r = _mat2(R)
+        check(lib.slam_update(self.ptr, dptr(zc), m, dptr(r), iptr(ids)))
+
+    def add_features(self, zn, R):
+        zc, k = _cols(zn)
+        r = _mat2(R)
+        check(lib.slam_add_features(self.ptr, dptr(zc), k, dptr(r)))
+
+    def compute_association(self, z, R, idf):
+        zc = _f64(z).reshape(-1)
+        r = _mat2(R)
+        nis, nd = C.c_double(), C.c_double()
+        check(lib.slam_compute_association(self.ptr, dptr(zc), dptr(r), int(idf), C.byref(nis), C.byref(nd)))
+        return nis.value, nd.value
+
+    def predict_observation(self, idf):
+        n = self.n
+        zp = np.empty(2)
+        H = np.empty((2, n), order="F")
+        check(lib.slam_predict_observation(self.ptr, int(idf), dptr(zp), dptr(H)))
+        return zp, np.ascontiguousarray(H)
+
+    def sync(self):
+        check(lib.slam_sync(self.ptr))
+
+    def launch_count(self) -> int:
+        return int(lib.slam_launch_count(self.ptr))
+
+
+_SCRATCH: dict[tuple[int, int], _Handle] = {}
+
+
+def _scratch_handle(n_needed: int, device: int = 0) -> _Handle:
+    """A cached handle with capacity >= n_needed for host-mirror calls."""
+    cap = 128
+    while cap < n_needed:
+        cap *= 2
+    key = (device, cap)
+    h = _SCRATCH.get(key)
+    if h is None:
+        h = _Handle(device, cap)
+        _SCRATCH[key] = h
+    return h
+
+
+class SlamState:
+    """abstract SlamState (src/common.jl:22)."""
+
+
+class EKFSlamState(SlamState):
+    """EKFSlamState{T}(x, cov) -- src/common.jl:25-28.  Host-mirror mode."""
+
+    def __init__(self, x, cov, device: int = 0):
+        self.x = np.array(x, dtype=np.float64).reshape(-1)
+        self.cov = np.array(cov, dtype=np.float64)
+        self.device = device
+
+    def _upload(self, extra: int = 0) -> _Handle:
+        h = _scratch_handle(len(self.x) + extra, self.device)
+        h.set_state(self.x, self.cov)
+        return h
+
+
+class DeviceEKFSlamState(SlamState):
+    """Resident mode: the state lives on the device; `.x` / `.cov` fetch on access."""
+
+    def __init__(self, x, cov, n_max: int, device: int = 0):
+        self.h = _Handle(device, n_max)
+        self.h.set_state(np.asarray(x, dtype=np.float64), np.asarray(cov, dtype=np.float64))
+
+    @property
+    def x(self):
+        return self.h.get_x()
+
+    @x.setter
+    def x(self, value):   # `state.x, state.cov = f(state, ...)` re-binds; the data is already in place
+        pass
+
+    @property
+    def cov(self):
+        return self.h.get_state()[1]
+
+    @cov.setter
+    def cov(self, value):
+        pass
+
+    def _upload(self, extra: int = 0) -> _Handle:
+        return self.h
+
+
+def _result(state, h: _Handle):
+    if isinstance(state, DeviceEKFSlamState):
+        return state, state       # placeholders accepted by the setters above
+    return h.get_state()
+
+
+def predict(state, vehicle, Q, dt):
+    """src/ekf.jl:8-43.  Mutates the state in place (as the reference does) and returns (x, P)."""
+    h = state._upload()
+    h.predict(vehicle.measured_gamma, vehicle.measured_speed, vehicle.wheelbase, Q, dt)
+    if isinstance(state, DeviceEKFSlamState):
+        return state, state
+    x, P = h.get_state()
+    state.x[:] = x
+    state.cov[:, :] = P
+    return state.x, state.cov
+
+
+def associate(state, z, R, gate1, gate2):
+    """src/data-association.jl:1-51 -> (zf 2 x m, idf 1 x m Int (1-based), zn 2 x k)."""
+    h = state._upload()
+    zf, idf, zn = h.associate(z, R, gate1, gate2)
+    return zf, idf.reshape(1, -1), zn
+
+
+def update(state, z, R, idf):
+    """src/ekf.jl:46-77 -> new (x, P)."""
+    h = state._upload()
+    h.update(z, R, idf)
+    return _result(state, h)
+
+
+def add_features(state, z, R):
+    """src/ekf.jl:84-122 -> augmented (x, P)."""
+    k = 0 if np.size(z) == 0 else np.asarray(z).reshape(2, -1).shape[1]
+    h = state._upload(extra=2 * k)
+    h.add_features(z, R)
+    return _result(state, h)
+
+
+def predict_observation(x, idf: int):
+    """src/common.jl:139-165 -> (z [range; bearing], H 2 x n)."""
+    x = np.asarray(x, dtype=np.float64).reshape(-1)
+    h = _scratch_handle(len(x))
+    h.set_state(x, np.zeros((len(x), len(x))))
+    return h.predict_observation(idf)
+
+
+def compute_association(x, P, z, R, idf: int):
+    """src/data-association.jl:53-63 -> (nis, nd)."""
+    x = np.asarray(x, dtype=np.float64).reshape(-1)
+    h = _scratch_handle(len(x))
+    h.set_state(x, P)
+    return h.compute_association(z, R, idf)

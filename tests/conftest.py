@@ -1,0 +1,62 @@
+"""Test configuration: registers the `gpu` marker, puts the package and the oracle on the
+path and builds the native pieces (libslamcuda.so by nvcc cross-compilation, the oracle's C
+twin by gcc).  The oracle is test infrastructure: only tests/ (and smoke / bench baselines)
+import it."""
+import ctypes
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "slam.jl_b200"))
+sys.path.insert(0, str(ROOT / "tests"))
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def _build_native():
+    lib = ROOT / "slam.jl_b200" / "lib" / "libslamcuda.so"
+    if not lib.exists() or os.environ.get("SLAMCUDA_REBUILD"):
+        subprocess.check_call([sys.executable, str(ROOT / "slam.jl_b200" / "build.py")])
+    twin = ROOT / "oracle" / "libslamtwin.so"
+    if not twin.exists():
+        subprocess.check_call(["make", "-C", str(ROOT / "oracle")])
+
+
+_build_native()
+
+
+def has_gpu() -> bool:
+    import slamcuda
+    return slamcuda.device_count() > 0
+
+
+@pytest.fixture(scope="session")
+def twin():
+    """ctypes handle of the oracle's plain-C twin."""
+    from twin_ffi import load_twin
+    return load_twin()
+
+
+@pytest.fixture(scope="session")
+def course1():
+    """sim/course1.txt of the reference, committed as a golden fixture (2 x 19 waypoints)."""
+    return np.loadtxt(ROOT / "tests" / "golden" / "course1.txt", skiprows=1).T.copy()
+
+
+def rel_err(a, b):
+    """max-norm relative error of a against reference b."""
+    a, b = np.asarray(a, dtype=float), np.asarray(b, dtype=float)
+    if a.shape != b.shape:
+        return float("inf")
+    if a.size == 0:
+        return 0.0
+    scale = max(float(np.max(np.abs(b))), 1e-300)
+    return float(np.max(np.abs(a - b))) / scale

@@ -1,0 +1,253 @@
+"""GPU parity of the single-filter path (K1-K7) through the C ABI against the CPU oracle.
+
+Tolerances (BASELINE.json north_star): association indices bit-exact; x and P within 1e-9
+relative (max-norm) per step when every step is re-seeded from the oracle; 1e-6 on
+end-of-run trajectories in closed loop.
+"""
+import math
+
+import numpy as np
+import pytest
+
+from conftest import rel_err
+from oracle import slam_ref as ref
+
+pytestmark = pytest.mark.gpu
+
+STEP_TOL = 1e-9
+TRACK_TOL = 1e-6
+
+
+@pytest.fixture(scope="module")
+def sc():
+    import slamcuda
+    if slamcuda.device_count() == 0:
+        pytest.fail("no CUDA device: the gpu tests must run on the B200 box")
+    return slamcuda
+
+
+@pytest.fixture(scope="module")
+def traces(course1):
+    out = {}
+    for nl in (10, 35):
+        lm, ctrl, obs = ref.make_inputs(nl, 0, 0)
+        rec = []
+        res = ref.sim(course1, lm, ctrl, obs, record=rec)
+        out[nl] = (lm, ctrl, obs, rec, res)
+    return out
+
+
+def test_mpi_to_pi(sc):
+    for phi in (0.0, 3.0, -3.0, math.pi, -math.pi, 3.5, -3.5, 7.0, -7.0, 10.0):
+        assert sc.mpi_to_pi(phi) == ref.mpi_to_pi(phi)
+
+
+@pytest.mark.parametrize("nl", [10, 35])
+def test_step_reseeded_parity(sc, traces, nl):
+    """Every recorded call of a course1 run: seed the device from the oracle's input state,
+    run the CUDA op, compare with the oracle's output."""
+    _lm, _ctrl, _obs, rec, _res = traces[nl]
+    k = ref.sim_constants()
+    Q, R, dt = k["Q"], k["R"], k["dt"]
+    veh = sc.Vehicle()
+    worst = dict(predict=0.0, update=0.0, add=0.0)
+    min_margin = math.inf
+    n_obs = 0
+    for i, e in enumerate(rec):
+        if e["op"] == "predict":
+            if i % 7 and len(e["x"]) > 3:   # sample the 2800 predict steps, keep all n = 3 ones
+                continue
+            st = sc.EKFSlamState(e["x"], e["P"])
+            veh.measured_gamma, veh.measured_speed = e["g"], e["v"]
+            x, P = sc.predict(st, veh, Q, dt)
+            worst["predict"] = max(worst["predict"], rel_err(x, e["x_out"]), rel_err(P, e["P_out"]))
+        else:
+            n_obs += 1
+            st = sc.EKFSlamState(e["x"], e["P"])
+            zf, idf, zn = sc.associate(st, e["z"], R, k["gate1"], k["gate2"])
+            assert np.array_equal(idf.reshape(-1), e["idf"]), f"association differs at record {i}"
+            assert np.array_equal(zf, e["zf"]) and np.array_equal(zn, e["zn"])
+            min_margin = min(min_margin, e["margin"])
+            x, P = sc.update(st, e["zf"], R, e["idf"])
+            worst["update"] = max(worst["update"], rel_err(x, e["x_upd"]), rel_err(P, e["P_upd"]))
+            st2 = sc.EKFSlamState(e["x_upd"], e["P_upd"])
+            x, P = sc.add_features(st2, e["zn"], R)
+            assert len(x) == len(e["x_out"])
+            worst["add"] = max(worst["add"], rel_err(x, e["x_out"]), rel_err(P, e["P_out"]))
+    print(f"\n[parity nl={nl}] worst rel err {worst}; {n_obs} observation steps; "
+          f"smallest association margin {min_margin:.3e}")
+    assert n_obs > 300
+    assert max(worst.values()) < STEP_TOL
+
+
+@pytest.mark.parametrize("nl", [10, 35])
+def test_closed_loop_course1(sc, traces, course1, nl):
+    """sim! driven end to end through the CUDA library, state resident on the device."""
+    lm, ctrl, obs, _rec, res = traces[nl]
+    from slamcuda import sim as gsim
+    out = gsim.run(course1, lm, ctrl, obs, n_max=3 + 2 * nl)
+    assert out["nsteps"] == res["nsteps"] and out["nupdates"] == res["nupdates"]
+    assert len(out["x"]) == len(res["x"])
+    e_track = float(np.max(np.abs(out["slam_track"] - res["slam_track"])))
+    scale = float(np.max(np.abs(res["slam_track"])))
+    print(f"\n[closed loop nl={nl}] track max abs err {e_track:.3e} (scale {scale:.1f}), "
+          f"x rel {rel_err(out['x'], res['x']):.3e}, P rel {rel_err(out['P'], res['P']):.3e}")
+    assert e_track / scale < TRACK_TOL
+    assert np.array_equal(out["true_track"], res["true_track"])
+    assert rel_err(out["x"], res["x"]) < TRACK_TOL
+    assert rel_err(out["P"], res["P"]) < TRACK_TOL
+    # P stays symmetric positive semi-definite
+    assert np.array_equal(out["P"], out["P"].T)
+    assert np.min(np.linalg.eigvalsh(out["P"])) > -1e-12
+
+
+def _random_state(rng, nf):
+    n = 3 + 2 * nf
+    x = np.concatenate([[50.0, 50.0, 0.3], rng.uniform(20, 80, size=2 * nf)])
+    L = rng.normal(0, 0.05, size=(n, 8))
+    P = L @ L.T + np.diag(rng.uniform(0.01, 0.1, size=n))
+    return x, P
+
+
+def test_edge_cases(sc):
+    k = ref.sim_constants()
+    R = k["R"]
+    rng = np.random.default_rng(5)
+    x, P = _random_state(rng, 4)
+    st = sc.EKFSlamState(x, P)
+    # update with m = 0 is the identity (first observation step of every run)
+    x1, P1 = sc.update(st, np.zeros((2, 0)), R, np.zeros(0, dtype=np.int64))
+    assert np.array_equal(x1, x) and rel_err(P1, P) == 0.0
+    # add_features with zero columns is the identity
+    x1, P1 = sc.add_features(st, np.zeros((2, 0)), R)
+    assert np.array_equal(x1, x) and rel_err(P1, P) == 0.0
+    # associate with Nf = 0 sends every observation to zn (outer = Inf > gate2)
+    st0 = sc.EKFSlamState(x[:3], P[:3, :3])
+    z = np.array([[10.0, 20.0, 5.0], [0.1, -0.2, 3.0]])
+    zf, idf, zn = sc.associate(st0, z, R, 4.0, 25.0)
+    assert zf.shape == (2, 0) and idf.size == 0 and np.array_equal(zn, z)
+    # associate with no observations
+    zf, idf, zn = sc.associate(st, np.zeros((2, 0)), R, 4.0, 25.0)
+    assert zf.shape == (2, 0) and zn.shape == (2, 0)
+    # duplicate landmark ids in one update are legal
+    zp, _ = ref.predict_observation(x, 2)
+    zdup = np.array([[zp[0] + 0.05, zp[0] - 0.03], [zp[1] + 0.01, zp[1] - 0.02]])
+    xg, Pg = sc.update(st, zdup, R, np.array([2, 2]))
+    xo, Po = ref.update(x, P, zdup, R, np.array([2, 2]))
+    assert rel_err(xg, xo) < STEP_TOL and rel_err(Pg, Po) < STEP_TOL
+    # bearing innovation that crosses +-pi
+    x2 = x.copy()
+    x2[2] = 3.1
+    x2[3:5] = [x2[0] - 10.0, x2[1] - 0.5]
+    zp, _ = ref.predict_observation(x2, 1)
+    zc = np.array([[zp[0]], [zp[1] + 2 * math.pi - 0.01]])
+    st2 = sc.EKFSlamState(x2, P)
+    xg, Pg = sc.update(st2, zc, R, np.array([1]))
+    xo, Po = ref.update(x2, P, zc, R, np.array([1]))
+    assert rel_err(xg, xo) < STEP_TOL and rel_err(Pg, Po) < STEP_TOL
+    # out-of-range landmark id -> BadIndex (Julia: BoundsError)
+    with pytest.raises(sc.BadIndex):
+        sc.update(st, zdup[:, :1], R, np.array([99]))
+    # non-PD innovation covariance -> NotPositiveDefinite (Julia: chol throws)
+    with pytest.raises(sc.NotPositiveDefinite):
+        sc.update(sc.EKFSlamState(x, -P), zdup[:, :1], -R, np.array([2]))
+    # capacity
+    from slamcuda.slam import _Handle
+    h = _Handle(0, 5)
+    h.set_state(x[:5], P[:5, :5])
+    with pytest.raises(sc.CapacityError):
+        h.add_features(np.array([[5.0], [0.1]]), R)
+    h.close()
+
+
+def test_observation_model_and_association_values(sc):
+    k = ref.sim_constants()
+    R = k["R"]
+    rng = np.random.default_rng(11)
+    x, P = _random_state(rng, 6)
+    for idf in (1, 3, 6):
+        zg, Hg = sc.predict_observation(x, idf)
+        zo, Ho = ref.predict_observation(x, idf)
+        assert rel_err(zg, zo) < 1e-14 and rel_err(Hg, Ho) < 1e-14
+        z = zo + np.array([0.1, -0.01])
+        nis_g, nd_g = sc.compute_association(x, P, z, R, idf)
+        nis_o, nd_o = ref.compute_association(x, P, z, R, idf)
+        assert abs(nis_g - nis_o) < 1e-9 * max(1.0, abs(nis_o))
+        assert abs(nd_g - nd_o) < 1e-9 * max(1.0, abs(nd_o))
+    with pytest.raises(sc.BadIndex):
+        sc.predict_observation(x, 7)
+
+
+def test_association_outcomes_all_three(sc):
+    """One call in which a matched, a dropped (gate1 <= nis, outer <= gate2) and a new
+    observation all occur, and two observations pick the same landmark."""
+    k = ref.sim_constants()
+    R = k["R"]
+    rng = np.random.default_rng(3)
+    x, P = _random_state(rng, 5)
+    P = P * 0.2
+    zp2, _ = ref.predict_observation(x, 2)
+    zp4, _ = ref.predict_observation(x, 4)
+    cand = []
+    for dr in np.linspace(0.0, 3.0, 61):
+        z = np.array([zp4[0] + dr, zp4[1]])
+        nis, _ = ref.compute_association(x, P, z, R, 4)
+        cand.append((dr, nis))
+    drop = [dr for dr, nis in cand if 6.0 < nis < 20.0]
+    assert drop, "no drop-zone candidate"
+    z = np.array([[zp2[0] + 0.02, zp2[0] - 0.02, zp4[0] + drop[0], 200.0],
+                  [zp2[1], zp2[1] + 0.002, zp4[1], 1.0]])
+    zf_o, idf_o, zn_o = ref.associate(x, P, z, R, 4.0, 25.0)
+    assert list(idf_o) == [2, 2] and zn_o.shape[1] == 1
+    zf, idf, zn = sc.associate(sc.EKFSlamState(x, P), z, R, 4.0, 25.0)
+    assert np.array_equal(idf.reshape(-1), idf_o)
+    assert np.array_equal(zf, zf_o) and np.array_equal(zn, zn_o)
+
+
+@pytest.mark.parametrize("nf,m", [(1000, 1), (1000, 8), (1000, 12), (1000, 16), (1000, 40), (300, 3)])
+def test_update_large_parity(sc, nf, m):
+    """update at n = 2003 (all K6 rank-chunk widths incl. the multi-pass path) vs the numpy
+    literal oracle."""
+    k = ref.sim_constants()
+    R = k["R"]
+    rng = np.random.default_rng(nf + m)
+    x, P = _random_state(rng, nf)
+    ids = rng.choice(nf, size=m, replace=False) + 1
+    z = np.zeros((2, m))
+    for c, idf in enumerate(ids):
+        zp, _ = ref.predict_observation(x, int(idf))
+        z[:, c] = zp + rng.normal(0, [0.1, 0.01])
+    xo, Po = ref.update(x, P, z, R, ids)
+    from slamcuda.slam import _Handle
+    h = _Handle(0, len(x))
+    h.set_state(x, P)
+    h.update(z, R, ids)
+    xg, Pg = h.get_state()
+    h.close()
+    print(f"\n[update n={len(x)} m={m}] x rel {rel_err(xg, xo):.2e}  P rel {rel_err(Pg, Po):.2e}")
+    assert rel_err(xg, xo) < STEP_TOL and rel_err(Pg, Po) < STEP_TOL
+    assert np.array_equal(Pg, Pg.T)
+
+
+def test_associate_large_parity(sc, twin):
+    """Gating over 1000 landmarks x 20 observations vs the twin (the literal oracle is
+    O(nz*Nf*n^2)); indices bit-exact."""
+    from twin_ffi import Twin
+    tw = Twin(twin)
+    k = ref.sim_constants()
+    R = k["R"]
+    rng = np.random.default_rng(77)
+    nf = 1000
+    x, P = _random_state(rng, nf)
+    ids = rng.choice(nf, size=14, replace=False) + 1
+    z = np.zeros((2, 20))
+    for c, idf in enumerate(ids):
+        zp, _ = ref.predict_observation(x, int(idf))
+        z[:, c] = zp + rng.normal(0, [0.1, 0.01])
+    z[:, 14:] = np.array([rng.uniform(100, 200, 6), rng.uniform(-1, 1, 6)])
+    zf_o, idf_o, zn_o = tw.associate(x, P, z, R, 4.0, 25.0)
+    zf, idf, zn = sc.associate(sc.EKFSlamState(x, P), z, R, 4.0, 25.0)
+    print(f"\n[associate Nf={nf}] matched {len(idf_o)}, new {zn_o.shape[1]}, twin margin {tw.last_margin:.3e}")
+    assert np.array_equal(idf.reshape(-1), idf_o)
+    assert np.array_equal(zf, zf_o) and np.array_equal(zn, zn_o)
+    assert len(idf_o) >= 10
