@@ -77,7 +77,8 @@ def build(verbose: bool = False, force: bool = False) -> Path:
     with ThreadPoolExecutor(max_workers=min(8, max(1, len(jobs)))) as ex:
         for src, r in ex.map(run, jobs):
             if r.returncode != 0:
-                sys.stderr.write(r.stdout + r.stderr)
+                sys.stderr.write("\n".join(l for l in (r.stdout + r.stderr).splitlines()
+                                           if "ptxas info" not in l and "bytes stack frame" not in l) + "\n")
                 raise RuntimeError(f"nvcc failed on {src.name}")
             if verbose:
                 sys.stderr.write(r.stderr)

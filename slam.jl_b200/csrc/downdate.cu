@@ -11,7 +11,10 @@
 //     and are staged into shared memory by a single 1-D bulk async copy (TMA engine,
 //     cp.async.bulk + mbarrier); the inner loop reads them as warp-wide broadcasts;
 //   * P is streamed column by column: for a fixed column the 128 threads read 128*ROWS
-//     consecutive doubles (16-byte vector loads for ROWS = 2), U columns in flight;
+//     consecutive doubles (16-byte vector loads for ROWS = 2).  Columns move through a
+//     two-deep register pipeline of U columns each: the loads of batch b+1 are issued
+//     before the FMAs of batch b, so every warp keeps U*ROWS*8*32 bytes in flight while
+//     it computes;
 //   * each element is a chain  a = fma(-W1[i,k], W1[j,k], a), k ascending -- the same
 //     order as the CPU oracle's twin, so results agree to the last bit for equal W1.
 //   Entries below the diagonal are never read by any consumer, so diagonal-crossing tiles
@@ -19,19 +22,86 @@
 //
 // Ranks above 32 run as ceil(R/32) passes of the FMA kernel or through the DMMA kernel
 // (mma.sync.m8n8k4.f64), chosen by launch_downdate().
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "kernels.cuh"
 
 namespace {
 
 constexpr int DD_THREADS = 128;
-constexpr int DD_BJ = 64;
+
+// streaming (evict-first) vector accesses; volatile asm keeps the issue order: all loads of
+// the next batch before the FMAs of the current one
+template <int ROWS>
+__device__ __forceinline__ void ld_rows(double (&a)[ROWS], const double *p) {
+    if (ROWS == 2) {
+        asm volatile("ld.global.cs.v2.f64 {%0, %1}, [%2];" : "=d"(a[0]), "=d"(a[ROWS - 1]) : "l"(p));
+    } else {
+        asm volatile("ld.global.cs.f64 %0, [%1];" : "=d"(a[0]) : "l"(p));
+    }
+}
+template <int ROWS>
+__device__ __forceinline__ void st_rows(const double (&a)[ROWS], double *p) {
+    if (ROWS == 2) {
+        asm volatile("st.global.cs.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(a[0]), "d"(a[ROWS - 1]) : "memory");
+    } else {
+        asm volatile("st.global.cs.f64 [%0], %1;" ::"l"(p), "d"(a[0]) : "memory");
+    }
+}
 
 template <int RC, int ROWS, int U>
+__device__ __forceinline__ void load_batch(double (&a)[U][ROWS], const double *col, size_t ld) {
+#pragma unroll
+    for (int u = 0; u < U; u++) ld_rows<ROWS>(a[u], col + (size_t)u * ld);
+}
+
+template <int RC, int ROWS, int U>
+__device__ __forceinline__ void fma_store_batch(double (&a)[U][ROWS], const double (&wi)[ROWS][RC],
+                                                const double *sWj, double *col, size_t ld) {
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+        const double2 *wj = reinterpret_cast<const double2 *>(sWj + (size_t)u * RC);
+#pragma unroll
+        for (int k = 0; k < RC / 2; k++) {
+            double2 w = wj[k];
+#pragma unroll
+            for (int r = 0; r < ROWS; r++) {
+                a[u][r] = fma(wi[r][2 * k], w.x, a[u][r]);
+                a[u][r] = fma(wi[r][2 * k + 1], w.y, a[u][r]);
+            }
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) st_rows<ROWS>(a[u], col + (size_t)u * ld);
+}
+
+constexpr int DD_BJ = 128;    // columns per tile (W1 column-side rows staged in shared memory)
+
+// One warp-wide L2 prefetch covers a whole batch: lane l asks for 128-byte line (l % LINES) of
+// column (l / LINES) of the batch, LINES = lines of this warp's row segment per column.
+template <int ROWS, int U>
+__device__ __forceinline__ void prefetch_batch(const double *warp_col, size_t ld, int lane, int cols_left) {
+    constexpr int LINES = ROWS * 2;            // 32 lanes * ROWS * 8 B = ROWS*256 B per column
+    constexpr int COLS_PER_INSTR = 32 / LINES;
+#pragma unroll
+    for (int u0 = 0; u0 < U; u0 += COLS_PER_INSTR) {
+        const int u = u0 + lane / LINES;
+        const double *p = warp_col + (size_t)u * ld + (lane % LINES) * 16;
+        if (u < cols_left) asm volatile("prefetch.global.L2::evict_last [%0];" ::"l"(p));
+    }
+}
+
+// Rows [r0, r1) of the upper triangle; element (i, j) lives at Pb[(i - r0) + j*ldb].
+// The single-filter path passes r0 = 0, r1 = n, Pb = P.
+// W1r: [n_pad][RC] row-major (column-side rows, staged by one bulk copy per tile);
+// W1t: [RC][n_pad] rank-major (row-side values, coalesced register loads).
+template <int RC, int ROWS, int U, int PD>
 __global__ void __launch_bounds__(DD_THREADS)
-k_downdate_fma(double *__restrict__ P, size_t ld, int n, const double *__restrict__ W1) {
+k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n_pad,
+               const double *__restrict__ W1r, const double *__restrict__ W1t) {
     constexpr int BI = DD_THREADS * ROWS;
-    const int i0 = blockIdx.x * BI;
+    const int i0 = r0 + blockIdx.x * BI;
     const int j0 = blockIdx.y * DD_BJ;
     const int jend = min(j0 + DD_BJ, n);
     if (i0 >= jend) return;  // tile entirely below the diagonal
@@ -45,86 +115,101 @@ k_downdate_fma(double *__restrict__ P, size_t ld, int n, const double *__restric
     __syncthreads();
     if (threadIdx.x == 0) {
         mbar_expect_tx(&bar, DD_BJ * RC * 8);
-        bulk_g2s(sW, W1 + (size_t)j0 * RC, DD_BJ * RC * 8, &bar);
+        bulk_g2s(sW, W1r + (size_t)j0 * RC, DD_BJ * RC * 8, &bar);
     }
 
+    const int lane = threadIdx.x & 31;
+    const int iw = i0 + (threadIdx.x & ~31) * ROWS;   // first row of this warp
+    if (iw >= jend || iw >= r1) return;               // whole warp below the tile / outside the block
     const int i = i0 + threadIdx.x * ROWS;
-    if (i >= jend) return;  // this thread's rows lie below every column of the tile
+
+    // the warp walks the columns from its own diagonal (rounded down to a batch) to the tile end
+    int jstart = max(j0, iw);
+    jstart = j0 + ((jstart - j0) / U) * U;
+    const int nfull = (jend - jstart) / U;
+    const double *wcol = Pb + (size_t)(iw - r0) + (size_t)jstart * ldb;
+    if (PD > 0) {
+#pragma unroll
+        for (int b = 0; b < PD; b++)
+            if (b < nfull) prefetch_batch<ROWS, U>(wcol + (size_t)(b * U) * ldb, ldb, lane, jend - jstart - b * U);
+    }
 
     double wi[ROWS][RC];
 #pragma unroll
-    for (int r = 0; r < ROWS; r++) {
-        const double2 *src = reinterpret_cast<const double2 *>(W1 + (size_t)(i + r) * RC);
-#pragma unroll
-        for (int k = 0; k < RC / 2; k++) {
-            double2 t = __ldg(src + k);
-            wi[r][2 * k] = -t.x;
-            wi[r][2 * k + 1] = -t.y;
+    for (int k = 0; k < RC; k++) {
+        if (ROWS == 2) {
+            double2 t = __ldg(reinterpret_cast<const double2 *>(W1t + (size_t)k * n_pad + i));
+            wi[0][k] = -t.x;
+            wi[ROWS - 1][k] = -t.y;
+        } else {
+            wi[0][k] = -__ldg(W1t + (size_t)k * n_pad + i);
         }
     }
     mbar_wait(&bar, 0);
 
-    // first column this thread touches: its own diagonal, rounded down to the unroll
-    int jstart = max(j0, i);
-    jstart = j0 + ((jstart - j0) / U) * U;
-    double *col = P + (size_t)i + (size_t)jstart * ld;
-
-    for (int j = jstart; j < jend; j += U) {
-        if (j + U <= jend) {
+    double *col = Pb + (size_t)(i - r0) + (size_t)jstart * ldb;
+    const double *sWj = sW + (size_t)(jstart - j0) * RC;
+    const bool row_ok = i < r1;   // rows past the block end (ragged last warp) do nothing
+    for (int b = 0; b < nfull; b++) {
+        if (PD > 0 && b + PD < nfull) prefetch_batch<ROWS, U>(wcol + (size_t)((b + PD) * U) * ldb, ldb, lane, jend - jstart - (b + PD) * U);
+        if (row_ok) {
             double a[U][ROWS];
-#pragma unroll
-            for (int u = 0; u < U; u++) {
-                if (ROWS == 2) {
-                    double2 t = __ldcs(reinterpret_cast<const double2 *>(col + (size_t)u * ld));
-                    a[u][0] = t.x;
-                    a[u][ROWS - 1] = t.y;
-                } else {
-                    a[u][0] = __ldcs(col + (size_t)u * ld);
-                }
-            }
-#pragma unroll
-            for (int u = 0; u < U; u++) {
-                const double2 *wj = reinterpret_cast<const double2 *>(sW + (size_t)(j - j0 + u) * RC);
-#pragma unroll
-                for (int k = 0; k < RC / 2; k++) {
-                    double2 w = wj[k];
-#pragma unroll
-                    for (int r = 0; r < ROWS; r++) {
-                        a[u][r] = fma(wi[r][2 * k], w.x, a[u][r]);
-                        a[u][r] = fma(wi[r][2 * k + 1], w.y, a[u][r]);
-                    }
-                }
-            }
-#pragma unroll
-            for (int u = 0; u < U; u++) {
-                if (ROWS == 2) {
-                    __stcs(reinterpret_cast<double2 *>(col + (size_t)u * ld),
-                           make_double2(a[u][0], a[u][ROWS - 1]));
-                } else {
-                    __stcs(col + (size_t)u * ld, a[u][0]);
-                }
-            }
-        } else {
-            for (int u = 0; j + u < jend; u++) {
-                const double *wj = sW + (size_t)(j - j0 + u) * RC;
-#pragma unroll
-                for (int r = 0; r < ROWS; r++) {
-                    double acc = col[(size_t)u * ld + r];
-#pragma unroll
-                    for (int k = 0; k < RC; k++) acc = fma(wi[r][k], wj[k], acc);
-                    col[(size_t)u * ld + r] = acc;
-                }
-            }
+            load_batch<RC, ROWS, U>(a, col, ldb);
+            fma_store_batch<RC, ROWS, U>(a, wi, sWj, col, ldb);
         }
-        col += (size_t)U * ld;
+        col += (size_t)U * ldb;
+        sWj += (size_t)U * RC;
+    }
+    if (row_ok) {
+        for (int j = jstart + nfull * U; j < jend; j++) {   // leftover columns of the last tile
+#pragma unroll
+            for (int r = 0; r < ROWS; r++) {
+                double acc = col[r];
+#pragma unroll
+                for (int k = 0; k < RC; k++) acc = fma(wi[r][k], sWj[k], acc);
+                col[r] = acc;
+            }
+            col += ldb;
+            sWj += RC;
+        }
     }
 }
 
-template <int RC, int ROWS, int U>
-void launch_fma(double *P, size_t ld, int n, const double *W1c, cudaStream_t s) {
+struct DdCfg { int rows, u, pd; };
+
+// experiment hook: SLAM_K6_CFG="rows,u,pd" overrides the tuned choice
+DdCfg pick_cfg(int RC) {
+    // measured on B200 at n = 20003 (profiles/r1_k6_sweep.md): the L2 prefetch pays once the FMA phase
+    // is long enough to starve the register-staged loads (rank >= 8)
+    DdCfg c = RC <= 4 ? DdCfg{2, 8, 0} : RC <= 16 ? DdCfg{2, 8, 1} : DdCfg{2, 4, 4};
+    if (const char *e = getenv("SLAM_K6_CFG")) {
+        int r, u, pd;
+        if (sscanf(e, "%d,%d,%d", &r, &u, &pd) == 3) c = DdCfg{r, u, pd};
+    }
+    return c;
+}
+
+template <int RC, int ROWS, int U, int PD>
+void launch_one(double *Pb, size_t ldb, int r0, int r1, int n, int n_pad, const double *W1r,
+                const double *W1t, cudaStream_t s) {
     constexpr int BI = DD_THREADS * ROWS;
-    dim3 grid((n + BI - 1) / BI, (n + DD_BJ - 1) / DD_BJ);
-    k_downdate_fma<RC, ROWS, U><<<grid, DD_THREADS, 0, s>>>(P, ld, n, W1c);
+    dim3 grid((r1 - r0 + BI - 1) / BI, (n + DD_BJ - 1) / DD_BJ);
+    k_downdate_fma<RC, ROWS, U, PD><<<grid, DD_THREADS, 0, s>>>(Pb, ldb, r0, r1, n, n_pad, W1r, W1t);
+}
+
+template <int RC>
+bool launch_cfg(const DdCfg &c, double *Pb, size_t ldb, int r0, int r1, int n, int n_pad, const double *W1r,
+                const double *W1t, cudaStream_t s) {
+#define TRY_CFG(R_, U_, PD_)                                                   \
+    if (c.rows == R_ && c.u == U_ && c.pd == PD_) {                            \
+        launch_one<RC, R_, U_, PD_>(Pb, ldb, r0, r1, n, n_pad, W1r, W1t, s);   \
+        return true;                                                           \
+    }
+    TRY_CFG(2, 8, 0) TRY_CFG(2, 8, 1) TRY_CFG(2, 8, 2)
+    TRY_CFG(2, 4, 1) TRY_CFG(2, 4, 2) TRY_CFG(2, 4, 4)
+    TRY_CFG(1, 8, 2)
+#undef TRY_CFG
+    return false;
 }
 
 }  // namespace
@@ -139,26 +224,41 @@ int downdate_chunk_width(int R) {
     return 32;
 }
 
-// W1c: nchunks blocks of [n_pad][RC] row-major (chunk c holds rank columns c*RC .. c*RC+RC-1,
-// zero padded); n_pad is a multiple of DD_ROW_PAD and rows >= n are zero.
-int launch_downdate(double *P, size_t ld, int n, const double *W1c, int n_pad, int R, int variant,
-                    cudaStream_t s, long long *launches) {
+// W1c: per rank chunk c (RC columns, zero padded) two copies of W1's chunk:
+//   W1c + c*2*n_pad*RC              : [n_pad][RC] row-major
+//   W1c + c*2*n_pad*RC + n_pad*RC   : [RC][n_pad] rank-major
+// n_pad is a multiple of DD_ROW_PAD and rows >= n are zero.
+int launch_downdate_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad,
+                         int R, int variant, cudaStream_t s, long long *launches) {
     (void)variant;
+    if (r1 <= r0) return SLAM_OK;
     const int RC = downdate_chunk_width(R);
     const int nchunks = (R + RC - 1) / RC;
+    const DdCfg cfg = pick_cfg(RC);
     for (int c = 0; c < nchunks; c++) {
-        const double *Wc = W1c + (size_t)c * n_pad * RC;
+        const double *Wr = W1c + (size_t)c * 2 * n_pad * RC;
+        const double *Wt = Wr + (size_t)n_pad * RC;
+        bool ok = false;
         switch (RC) {
-            case 2: launch_fma<2, 2, 8>(P, ld, n, Wc, s); break;
-            case 4: launch_fma<4, 2, 8>(P, ld, n, Wc, s); break;
-            case 8: launch_fma<8, 2, 8>(P, ld, n, Wc, s); break;
-            case 12: launch_fma<12, 2, 8>(P, ld, n, Wc, s); break;
-            case 16: launch_fma<16, 2, 8>(P, ld, n, Wc, s); break;
-            case 24: launch_fma<24, 1, 8>(P, ld, n, Wc, s); break;
-            default: launch_fma<32, 1, 8>(P, ld, n, Wc, s); break;
+            case 2: ok = launch_cfg<2>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
+            case 4: ok = launch_cfg<4>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
+            case 8: ok = launch_cfg<8>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
+            case 12: ok = launch_cfg<12>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
+            case 16: ok = launch_cfg<16>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
+            case 24: ok = launch_cfg<24>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
+            default: ok = launch_cfg<32>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
+        }
+        if (!ok) {
+            slam_set_error("launch_downdate: no kernel for config rows=%d u=%d pd=%d", cfg.rows, cfg.u, cfg.pd);
+            return SLAM_ERR_ARG;
         }
         if (launches) (*launches)++;
     }
     CUDA_TRY(cudaGetLastError());
     return SLAM_OK;
+}
+
+int launch_downdate(double *P, size_t ld, int n, const double *W1c, int n_pad, int R, int variant,
+                    cudaStream_t s, long long *launches) {
+    return launch_downdate_rows(P, ld, 0, n, n, W1c, n_pad, R, variant, s, launches);
 }

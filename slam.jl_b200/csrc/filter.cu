@@ -106,7 +106,7 @@ static int ensure_update_ws(slam_t *h, int R) {
     h->ws_R = 0;
     int Rw = std::max(Rpad, 32);
     CUDA_TRY(cudaMalloc(&h->d_PHt, sizeof(double) * (size_t)npad * Rw));
-    CUDA_TRY(cudaMalloc(&h->d_W1c, sizeof(double) * (size_t)npad * Rw));
+    CUDA_TRY(cudaMalloc(&h->d_W1c, sizeof(double) * 2 * (size_t)npad * Rw));   // both layouts
     CUDA_TRY(cudaMalloc(&h->d_S, sizeof(double) * (size_t)Rw * Rw));
     CUDA_TRY(cudaMalloc(&h->d_C, sizeof(double) * (size_t)Rw * Rw));
     CUDA_TRY(cudaMalloc(&h->d_u, sizeof(double) * Rw));
@@ -631,7 +631,8 @@ k_innov_chol(const double *__restrict__ PHt, int npad, const double *__restrict_
 
 // ---------------------------------------------------------------------------------------
 // K5 -- W1 = PHt*C (src/ekf.jl:71) and x += W*v = W1*(C'v) (:72-74).  Thread = row i.
-// W1 is written in the chunked row-major layout K6 stages with bulk copies.
+// W1 is written per rank chunk in both layouts K6 reads: row-major [npad][RC] (staged with
+// bulk copies for the column side) and rank-major [RC][npad] (coalesced row-side loads).
 // ---------------------------------------------------------------------------------------
 constexpr int K5_THREADS = 128;
 
@@ -651,7 +652,11 @@ k_gain(const double *__restrict__ PHt, int npad, int n, int R, const double *__r
     const int nch = (R + RC - 1) / RC;
     if (i >= n) {
         for (int c = 0; c < nch; c++)
-            for (int kk = 0; kk < RC; kk++) W1c[((size_t)c * npad + i) * RC + kk] = 0.0;
+            for (int kk = 0; kk < RC; kk++) {
+                double *chunk = W1c + (size_t)c * 2 * npad * RC;
+                chunk[(size_t)i * RC + kk] = 0.0;                          // [npad][RC] row-major
+                chunk[(size_t)npad * RC + (size_t)kk * npad + i] = 0.0;    // [RC][npad] rank-major
+            }
         return;
     }
     double dxi = 0;
@@ -659,7 +664,9 @@ k_gain(const double *__restrict__ PHt, int npad, int n, int R, const double *__r
         double a = 0;
         if (k < R)
             for (int l = 0; l <= k; l++) a += PHt[(size_t)l * npad + i] * Cm[(size_t)l + (size_t)k * R];
-        W1c[((size_t)(k / RC) * npad + i) * RC + (k % RC)] = a;
+        double *chunk = W1c + (size_t)(k / RC) * 2 * npad * RC;
+        chunk[(size_t)i * RC + (k % RC)] = a;
+        chunk[(size_t)npad * RC + (size_t)(k % RC) * npad + i] = a;
         if (k < R) dxi += a * u[k];
     }
     double xi = x[i] + dxi;
