@@ -1,0 +1,357 @@
+#!/usr/bin/env python
+"""bench.py -- EKF update steps/s of the B200-native EKF-SLAM hot path.
+
+A "step" is one `update` call (src/ekf.jl:46-77: K3 P*H' gather, K4 innovation Cholesky,
+K5 gain, K6 in-place symmetric downdate) with m associated observations on a synthetic
+landmark field.  Workload, per GPU count N (see DESIGN.md "Measurement"):
+  N = 1 : the 100k-landmark config's per-GPU slice: P of 40 GB on one GPU
+          (n = 70711, 35354 landmarks); `update_10k` (BASELINE config 3) is reported beside it.
+  N > 1 : one filter whose P is row-block-sharded over N ranks, 40 GB per rank (N = 8 is the
+          100k-landmark config, P = 320 GB), NCCL allgather of the H rows and of W1.
+`value`    : update steps/s with zf / idf already in HBM, no host sync between steps.
+`e2e`      : the same through the host C ABI call slam_update() with HOST buffers (H2D of
+             zf / idf inside, status + pose read back every step).
+`roofline` : K6, algorithmic bytes 8 n (n+1) / ranks over CUDA-event time of the K6 launches.
+`--impl reference` times the CPU restatement of the reference (oracle/slam_ref.py, numpy +
+OpenBLAS on all host cores) on a bounded sample; Julia is not available on this box.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "slam.jl_b200"))
+
+DENSITY = 0.0035            # landmarks per m^2 (course1 with 35 landmarks)
+SEED = 2
+R_OBS = np.array([0.1 ** 2, 0.0, 0.0, (math.pi / 180) ** 2])   # column-major 2x2
+GB_PER_RANK = 40.0          # P bytes per GPU of the 100k-landmark / 8-GPU config
+
+
+def n_for_bytes(gbytes: float) -> int:
+    """Largest n = 3 + 2*Nf with 8 n^2 <= gbytes."""
+    n = int(math.sqrt(gbytes * 1e9 / 8.0))
+    nf = (n - 3) // 2
+    return 3 + 2 * nf
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines: list[str] = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [a.strip() for a in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        hi = [s for s in sm if s > 0.5 * (mx or 1)] or sm
+        return {"sm_mhz": hi[len(hi) // 2] if hi else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------
+# CPU arm: the reference-literal numpy restatement (oracle/slam_ref.py), timed, never shipped
+# ----------------------------------------------------------------------------------------
+def cpu_reference_update(n_landmarks: int, m: int, steps: int, warmup: int):
+    """Times oracle.slam_ref.update (dense H, P @ H.T, Cholesky, P - W1 @ W1.T) with numpy's
+    OpenBLAS on all host cores.  Returns (median seconds per step, cores)."""
+    from oracle import slam_ref as ref
+    rng = np.random.default_rng(SEED)
+    n = 3 + 2 * n_landmarks
+    side = math.sqrt(n_landmarks / DENSITY)
+    x = np.empty(n)
+    x[:3] = [side / 2, side / 2, 0.0]
+    x[3:] = rng.uniform(0, side, 2 * n_landmarks)
+    L = rng.normal(0, 0.05, (n, 8))
+    P = L @ L.T
+    P[np.diag_indices(n)] += rng.uniform(0.01, 0.1, n)
+    d2 = (x[3::2] - x[0]) ** 2 + (x[4::2] - x[1]) ** 2
+    ids = np.argsort(d2)[:m] + 1
+    z = np.zeros((2, m))
+    for c, idf in enumerate(ids):
+        zp, _ = ref.predict_observation(x, int(idf))
+        z[:, c] = zp + rng.normal(0, [0.1, 0.01])
+    R = R_OBS.reshape(2, 2)
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        x, P = ref.update(x, P, z, R, ids)
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+    times.sort()
+    return times[len(times) // 2], os.cpu_count() or 1
+
+
+def cpu_baseline_block(n_workload: int, m: int, steps: int = 3, warmup: int = 1, sample_landmarks: int = 10000):
+    n_s = 3 + 2 * sample_landmarks
+    sec, cores = cpu_reference_update(sample_landmarks, m, steps, warmup)
+    scale = (n_s / n_workload) ** 2
+    return {
+        "value": (1.0 / sec) * scale, "unit": "update steps/s", "cores": cores, "kind": "port",
+        "measured_steps_per_s_at_sample": 1.0 / sec,
+        "sample": (f"oracle/slam_ref.py update (numpy literal restatement of src/ekf.jl:46-77, OpenBLAS "
+                   f"{cores} threads) at n = {n_s} ({sample_landmarks} landmarks), m = {m}, median of {steps} "
+                   f"steps after {warmup} warm-up; scaled by (n_sample/n)^2 = {scale:.4g} to n = {n_workload} "
+                   f"(extrapolated: cost is O(n^2 m); the workload's P does not fit host RAM as numpy needs 3 copies)"),
+    }
+
+
+# ----------------------------------------------------------------------------------------
+# GPU arm, one filter on one GPU
+# ----------------------------------------------------------------------------------------
+def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_steps: int, device: int = 0,
+                      barrier=None):
+    """Returns timing of `update` on a synthetic n_landmarks map resident on `device`."""
+    import torch
+    from slamcuda._ffi import lib, check, dptr, iptr
+
+    n = 3 + 2 * n_landmarks
+    side = math.sqrt(n_landmarks / DENSITY)
+    h = C.c_void_p()
+    check(lib.slam_create(device, n, C.byref(h)))
+    try:
+        check(lib.slam_synth_state(h, n_landmarks, side, SEED))
+        nz = m + 4
+        z = np.zeros(2 * nz)
+        ids = np.zeros(m, dtype=np.int64)
+        check(lib.slam_synth_observations(h, n_landmarks, side, SEED, m, 4, dptr(z), iptr(ids)))
+        zf, zn = np.zeros(2 * nz), np.zeros(2 * nz)
+        idf = np.zeros(nz, dtype=np.int64)
+        mm, kk = C.c_int(), C.c_int()
+        t0 = time.perf_counter()
+        check(lib.slam_associate(h, dptr(z), nz, dptr(R_OBS), 4.0, 25.0, dptr(zf), iptr(idf), C.byref(mm),
+                                 dptr(zn), C.byref(kk)))
+        t_assoc = time.perf_counter() - t0
+        if mm.value != m or not np.array_equal(idf[:m], ids):
+            raise RuntimeError(f"association of the synthetic observations is wrong: {idf[:mm.value]} vs {ids}")
+        zf, idf = zf[:2 * m].copy(), idf[:m].copy()
+        stream = torch.cuda.ExternalStream(lib.slam_stream(h), device=device)
+        d_zf = torch.tensor(zf, device=f"cuda:{device}")
+        d_idf = torch.tensor(idf, device=f"cuda:{device}")
+        torch.cuda.synchronize(device)
+        for _ in range(warmup):
+            check(lib.slam_update_resident(h, d_zf.data_ptr(), m, dptr(R_OBS), d_idf.data_ptr()))
+        check(lib.slam_sync(h))
+        l0 = lib.slam_launch_count(h)
+        check(lib.slam_profile(h, 1))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if barrier:
+            barrier()
+        e0.record(stream)
+        for _ in range(steps):
+            check(lib.slam_update_resident(h, d_zf.data_ptr(), m, dptr(R_OBS), d_idf.data_ptr()))
+        e1.record(stream)
+        check(lib.slam_sync(h))
+        ms_total = e0.elapsed_time(e1)
+        k6, cnt = C.c_double(), C.c_int()
+        check(lib.slam_profile_read(h, C.byref(k6), C.byref(cnt)))
+        check(lib.slam_profile(h, 0))
+        launches = lib.slam_launch_count(h) - l0
+        out = dict(n=n, m=m, ms_per_step=ms_total / steps, k6_ms=k6.value / max(cnt.value, 1),
+                   launches=int(launches), assoc_ms=t_assoc * 1e3, nz=nz, new=kk.value)
+        # end to end through the host C ABI: host zf / idf in, status and pose out, every step
+        if e2e_steps > 0:
+            pose = np.zeros(3)
+            check(lib.slam_update(h, dptr(zf), m, dptr(R_OBS), iptr(idf)))
+            torch.cuda.synchronize(device)
+            t0 = time.perf_counter()
+            for _ in range(e2e_steps):
+                check(lib.slam_update(h, dptr(zf), m, dptr(R_OBS), iptr(idf)))
+                check(lib.slam_get_pose(h, dptr(pose)))
+            torch.cuda.synchronize(device)
+            out["e2e_ms_per_step"] = (time.perf_counter() - t0) / e2e_steps * 1e3
+            out["h2d_bytes"] = 16 * m + 8 * m
+            out["d2h_bytes"] = 4 + 24
+        return out
+    finally:
+        lib.slam_destroy(h)
+
+
+def gpu_update_sharded(*a, **k):   # replaced below once the sharded path is imported
+    raise NotImplementedError
+
+
+def reference_arm(args, rank: int):
+    """--impl reference: the reference's CPU path (numpy restatement; Julia unavailable)."""
+    if rank != 0:
+        return
+    n_w = n_for_bytes(GB_PER_RANK * args.gpus)
+    t0 = time.perf_counter()
+    sec, cores = cpu_reference_update(args.sample_landmarks, args.m, max(args.steps, 1), max(args.warmup, 1))
+    n_s = 3 + 2 * args.sample_landmarks
+    scale = (n_s / n_w) ** 2
+    val = scale / sec
+    sample = (f"oracle/slam_ref.py update (numpy literal restatement of src/ekf.jl:46-77; Julia <= 0.6 is not "
+              f"installable here) at n = {n_s}, m = {args.m}, OpenBLAS {cores} threads, median of {max(args.steps, 1)} "
+              f"steps; scaled by (n_sample/n)^2 = {scale:.4g} to the workload n = {n_w} (extrapolated)")
+    line = {
+        "impl": "reference", "metric": "EKF update steps/s", "value": val, "unit": "update steps/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / val,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.gpus, args.m),
+        "cpu_baseline": {"value": val, "unit": "update steps/s", "cores": cores, "kind": "port", "sample": sample,
+                         "measured_steps_per_s_at_sample": 1.0 / sec},
+        "e2e": {"value": val, "unit": "update steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "wall_s": time.perf_counter() - t0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(n_gpus: int, m: int):
+    n = n_for_bytes(GB_PER_RANK * n_gpus)
+    return {
+        "workload": (f"single EKF-SLAM filter, synthetic {(n - 3) // 2}-landmark 2-D rangefinder field, n = {n}, "
+                     f"P = {8.0 * n * n / 1e9:.1f} GB FP64 ({GB_PER_RANK:.0f} GB per GPU; 8 GPUs = the 100k-landmark config), "
+                     f"update with m = {m} associated observations of nz = {m + 4}"),
+        "n": n, "landmarks": (n - 3) // 2, "m": m, "P_bytes_per_gpu": 8.0 * n * n / n_gpus,
+        "parallelism": "single GPU" if n_gpus == 1 else f"P row-block-sharded over {n_gpus} ranks, NCCL allgather of H rows and W1",
+        "cache": "inputs larger than L2 (P per GPU >> 126 MB); no flush needed",
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--m", type=int, default=8, help="associated observations per update")
+    ap.add_argument("--sample-landmarks", type=int, default=10000, help="CPU baseline sample size")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extras", action="store_true", help="skip update_10k / ensemble side measurements")
+    ap.add_argument("--gb-per-gpu", type=float, default=None, help="override P bytes per GPU (GB)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    global GB_PER_RANK
+    if args.gb_per_gpu:
+        GB_PER_RANK = args.gb_per_gpu
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        reference_arm(args, rank)
+        return
+
+    import torch
+    import slamcuda
+    if slamcuda.device_count() == 0:
+        raise SystemExit("bench.py needs a CUDA device: libslamcuda has no CPU fallback")
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE = {world}: launch with torch.distributed.run")
+    torch.cuda.set_device(local_rank)
+    peak, peak_src = peaks()
+    n = n_for_bytes(GB_PER_RANK * args.gpus)
+    nl = (n - 3) // 2
+    sampler = ClockSampler(local_rank)
+    extras = {}
+
+    if args.gpus == 1:
+        sampler.start()
+        r = gpu_update_single(nl, args.m, args.steps, args.warmup, e2e_steps=min(args.steps, 20))
+        clocks = sampler.stop()
+        ms = r["ms_per_step"]
+        alg_bytes = 8.0 * n * (n + 1)
+        if not args.no_extras:
+            r10 = gpu_update_single(10000, args.m, max(args.steps, 50), args.warmup, e2e_steps=20)
+            b10 = 8.0 * 20003 * 20004
+            extras["update_10k"] = {
+                "workload": "BASELINE config 3: single filter, 10k landmarks (n = 20003, P = 3.2 GB), 1 B200",
+                "value": 1e3 / r10["ms_per_step"], "unit": "update steps/s", "m": args.m,
+                "e2e": 1e3 / r10["e2e_ms_per_step"], "k6_ms": r10["k6_ms"],
+                "k6_gbs": b10 / (r10["k6_ms"] * 1e-3) / 1e9, "k6_frac": b10 / (r10["k6_ms"] * 1e-3) / 1e9 / peak,
+                "associate_ms": r10["assoc_ms"]}
+    else:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+        sampler.start()
+        r = gpu_update_sharded(nl, args.m, args.steps, args.warmup, e2e_steps=min(args.steps, 20),
+                               rank=rank, world=world, device=local_rank)
+        clocks = sampler.stop()
+        ms = r["ms_per_step"]
+        alg_bytes = 8.0 * n * (n + 1) / world
+
+    if rank != 0:
+        return
+    k6_gbs = alg_bytes / (r["k6_ms"] * 1e-3) / 1e9
+    line = {
+        "metric": "EKF update steps/s", "value": 1e3 / ms, "unit": "update steps/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.gpus, args.m), "clocks": clocks,
+        "e2e": {"value": 1e3 / r["e2e_ms_per_step"], "unit": "update steps/s",
+                "h2d_bytes_per_step": r["h2d_bytes"], "d2h_bytes_per_step": r["d2h_bytes"],
+                "path": "slam_update() with host zf/idf (resident mode: P stays in HBM, as sim! re-binds it)"},
+        "gpu_launches": r["launches"],
+        "roofline": {"bound": "hbm", "kernel": "k_downdate_fma (K6, P -= W1*W1' over the upper triangle)",
+                     "achieved": k6_gbs, "peak": peak, "unit": "GB/s", "frac": k6_gbs / peak,
+                     "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": alg_bytes, "k6_ms": r["k6_ms"],
+                     "k6_share_of_step": r["k6_ms"] / ms},
+    }
+    if not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline_block(n, args.m, sample_landmarks=args.sample_landmarks)
+    line.update(extras)
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()
