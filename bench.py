@@ -332,6 +332,12 @@ def main():
     if rank != 0:
         return
     k6_gbs = alg_bytes / (r["k6_ms"] * 1e-3) / 1e9
+    traffic = None   # dram bytes per launch from the committed ncu --set full capture of this workload
+    tf = ROOT / "profiles" / "k6_traffic.json"
+    if tf.exists():
+        t = json.loads(tf.read_text())
+        if t.get("n") == n and t.get("m") == args.m and args.gpus == 1:
+            traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
     line = {
         "metric": "EKF update steps/s", "value": 1e3 / ms, "unit": "update steps/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
@@ -343,7 +349,7 @@ def main():
         "gpu_launches": r["launches"],
         "roofline": {"bound": "hbm", "kernel": "k_downdate_fma (K6, P -= W1*W1' over the upper triangle)",
                      "achieved": k6_gbs, "peak": peak, "unit": "GB/s", "frac": k6_gbs / peak,
-                     "traffic": None, "peak_source": peak_src,
+                     "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "k6_ms": r["k6_ms"],
                      "k6_share_of_step": r["k6_ms"] / ms},
     }
