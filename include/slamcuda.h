@@ -205,6 +205,9 @@ int slam_shard_update_resident(slam_shard_t *s, const double *d_zf, int m, const
 int slam_shard_sync(slam_shard_t *s);
 void *slam_shard_stream(slam_shard_t *s);
 long long slam_shard_launch_count(slam_shard_t *s);
+/* As slam_profile / slam_profile_read: CUDA events around this rank's K6 launches. */
+int slam_shard_profile(slam_shard_t *s, int on);
+int slam_shard_profile_read(slam_shard_t *s, double *k6_ms, int *k6_updates);
 
 #ifdef __cplusplus
 }

@@ -137,10 +137,13 @@ k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n
     double wi[ROWS][RC];
 #pragma unroll
     for (int k = 0; k < RC; k++) {
-        if (ROWS == 2) {
+        if (ROWS == 2 && (r0 & 1) == 0) {
             double2 t = __ldg(reinterpret_cast<const double2 *>(W1t + (size_t)k * n_pad + i));
             wi[0][k] = -t.x;
             wi[ROWS - 1][k] = -t.y;
+        } else if (ROWS == 2) {   // row blocks of the sharded path start at odd rows
+            wi[0][k] = -__ldg(W1t + (size_t)k * n_pad + i);
+            wi[ROWS - 1][k] = -__ldg(W1t + (size_t)k * n_pad + i + 1);
         } else {
             wi[0][k] = -__ldg(W1t + (size_t)k * n_pad + i);
         }

@@ -674,6 +674,13 @@ k_gain(const double *__restrict__ PHt, int npad, int n, int R, const double *__r
     if (i < 3) pose_snapshot[i] = xi;
 }
 
+int launch_innov_chol(const double *PHt, int npad, const double *Hn, const int *fp, const double *v, int m,
+                      const double R[4], double *S, double *C, double *u, int *err, cudaStream_t s) {
+    k_innov_chol<<<1, K4_THREADS, 0, s>>>(PHt, npad, Hn, fp, v, m, R[0], R[1], R[2], R[3], S, C, u, err);
+    CUDA_TRY(cudaGetLastError());
+    return SLAM_OK;
+}
+
 static int update_device(slam_t *h, const double *d_zf, int m, const double R[4], const int64_t *d_idf) {
     if (m == 0) return SLAM_OK;   // first observation step of every run (sim/ekfslam-sim.jl:114-117)
     if (m > SLAM_MAX_OBS) {

@@ -30,10 +30,29 @@ struct Innov {     // per-landmark quantities that do not depend on the observat
     double zp0, zp1, i11, i12, i21, i22, logdet;
 };
 
+// Where a landmark's 5x5 sub-block comes from.  Single filter: everything from the one
+// column-major P.  Sharded filter: rows 0..2 of every column from P3 (broadcast from rank 0,
+// P3[p*npad + j]) and the landmark's 2x2 diagonal block from the owning row block.
+struct GateSrc {
+    const double *P;      // single: full matrix; sharded: nullptr
+    size_t ld;
+    const double *P3;     // sharded: rows 0..2, stride npad
+    int npad;
+    const double *Pb[2];  // sharded: the rank's two row blocks
+    size_t ldb;
+    int lo[2];
+    int j_first[2], j_count[2];   // landmark ids (1-based) owned: j_first[q] .. j_first[q]+j_count[q]-1
+};
+
+__device__ __forceinline__ double gate_pvv(const GateSrc &g, int p, int q) {
+    int a = p <= q ? p : q, b = p <= q ? q : p;
+    return g.P ? g.P[(size_t)a + (size_t)b * g.ld] : g.P3[(size_t)a * g.npad + b];
+}
+
 // 2x2 innovation covariance from the 5x5 sub-block; Pvv is the symmetric 3x3 pose block.
-__device__ __forceinline__ Innov landmark_innov(const double *__restrict__ x, const double *__restrict__ P,
-                                                size_t ld, int f, const double *Pvv, double xv, double yv,
-                                                double phi, const double *R) {
+__device__ __forceinline__ Innov landmark_innov(const double *__restrict__ x, const GateSrc &g, int blk, int f,
+                                                const double *Pvv, double xv, double yv, double phi,
+                                                const double *R) {
     double zp[2], h[10];
     observe_model(xv, yv, phi, x[f], x[f + 1], zp, h);
     double P5[5][5];
@@ -41,19 +60,34 @@ __device__ __forceinline__ Innov landmark_innov(const double *__restrict__ x, co
     for (int p = 0; p < 3; p++)
 #pragma unroll
         for (int q = 0; q < 3; q++) P5[p][q] = Pvv[p * 3 + q];
-    const double *c0 = P + (size_t)f * ld;
-    const double *c1 = c0 + ld;
+    if (g.P) {
+        const double *c0 = g.P + (size_t)f * g.ld;
+        const double *c1 = c0 + g.ld;
+#pragma unroll
+        for (int p = 0; p < 3; p++) {
+            P5[p][3] = c0[p];
+            P5[p][4] = c1[p];
+        }
+        P5[3][3] = c0[f];
+        P5[3][4] = c1[f];
+        P5[4][4] = c1[f + 1];
+    } else {
+#pragma unroll
+        for (int p = 0; p < 3; p++) {
+            P5[p][3] = g.P3[(size_t)p * g.npad + f];
+            P5[p][4] = g.P3[(size_t)p * g.npad + f + 1];
+        }
+        const double *d0 = g.Pb[blk] + (size_t)(f - g.lo[blk]) + (size_t)f * g.ldb;
+        P5[3][3] = d0[0];
+        P5[3][4] = d0[g.ldb];
+        P5[4][4] = d0[g.ldb + 1];
+    }
 #pragma unroll
     for (int p = 0; p < 3; p++) {
-        P5[p][3] = c0[p];
-        P5[p][4] = c1[p];
         P5[3][p] = P5[p][3];
         P5[4][p] = P5[p][4];
     }
-    P5[3][3] = c0[f];
-    P5[3][4] = c1[f];
     P5[4][3] = P5[3][4];
-    P5[4][4] = c1[f + 1];
     const double Hr[2][5] = {{h[0], h[1], h[2], h[6], h[7]}, {h[3], h[4], h[5], h[8], h[9]}};
     double HP[2][5];
 #pragma unroll
@@ -101,12 +135,58 @@ struct GateParams {
     double gate1, gate2;
 };
 
+struct GateRes {   // one rank's reduction for one observation (24 bytes, allgathered as bytes)
+    double nd, outer;
+    long long j;
+};
+
+__device__ void gate_compact(const int *cls, const double *z, int nz, double *zf, int64_t *idf, double *zn,
+                             int *counts) {
+    int m = 0, k = 0;
+    for (int i = 0; i < nz; i++) {
+        int c = cls[i];
+        if (c > 0) {
+            zf[2 * m] = z[2 * i];
+            zf[2 * m + 1] = z[2 * i + 1];
+            idf[m] = c;
+            m++;
+        } else if (c < 0) {
+            zn[2 * k] = z[2 * i];
+            zn[2 * k + 1] = z[2 * i + 1];
+            k++;
+        }
+    }
+    counts[0] = m;
+    counts[1] = k;
+}
+
+// sharded path: every rank reduces the allgathered per-rank results identically
+__global__ void k_gate_finalize(const GateRes *__restrict__ all, int world, const double *__restrict__ z, int nz,
+                                GateParams prm, double *zf, int64_t *idf, double *zn, int *counts) {
+    __shared__ int s_cls[SLAM_MAX_OBS];
+    for (int i = threadIdx.x; i < nz; i += blockDim.x) {
+        double b = INFINITY, ou = INFINITY;
+        long long jj = 0;
+        for (int r = 0; r < world; r++) {
+            GateRes g = all[(size_t)r * nz + i];
+            if (g.j != 0 && (jj == 0 || g.nd < b || (g.nd == b && g.j < jj))) {
+                b = g.nd;
+                jj = g.j;
+            }
+            if (g.outer < ou) ou = g.outer;
+        }
+        s_cls[i] = jj != 0 ? (int)jj : (ou > prm.gate2 ? -1 : 0);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) gate_compact(s_cls, z, nz, zf, idf, zn, counts);
+}
+
 // scratch: [0] unsigned counter, then part_nd / part_outer (double) and part_j (int) of
 // nblocks*nz entries each
 __global__ void __launch_bounds__(GATE_THREADS)
-k_gate(const double *__restrict__ x, const double *__restrict__ P, size_t ld, int Nf,
-       const double *__restrict__ z, int nz, GateParams prm, unsigned *counter, double *part_nd,
-       double *part_outer, int *part_j, double *zf, int64_t *idf, double *zn, int *counts) {
+k_gate(const double *__restrict__ x, GateSrc src, int Ntot, const double *__restrict__ z, int nz, GateParams prm,
+       unsigned *counter, double *part_nd, double *part_outer, int *part_j, double *zf, int64_t *idf, double *zn,
+       int *counts, GateRes *rank_res) {
     __shared__ double sPvv[9];
     __shared__ double s_nd[GATE_THREADS / 32][OB], s_outer[GATE_THREADS / 32][OB];
     __shared__ int s_j[GATE_THREADS / 32][OB];
@@ -115,7 +195,7 @@ k_gate(const double *__restrict__ x, const double *__restrict__ P, size_t ld, in
     const int ob0 = blockIdx.y * OB;
     if (threadIdx.x < 9) {
         int p = threadIdx.x / 3, q = threadIdx.x % 3;
-        sPvv[threadIdx.x] = sym_at(P, ld, p, q);
+        sPvv[threadIdx.x] = gate_pvv(src, p, q);
     }
     __syncthreads();
     const double xv = x[0], yv = x[1], phi = x[2];
@@ -130,8 +210,10 @@ k_gate(const double *__restrict__ x, const double *__restrict__ P, size_t ld, in
         outer[o] = INFINITY;
         jb[o] = 0;
     }
-    for (int j = blockIdx.x * GATE_THREADS + threadIdx.x + 1; j <= Nf; j += nblocks * GATE_THREADS) {
-        Innov L = landmark_innov(x, P, ld, 3 + 2 * (j - 1), sPvv, xv, yv, phi, prm.R);
+    for (int t = blockIdx.x * GATE_THREADS + threadIdx.x; t < Ntot; t += nblocks * GATE_THREADS) {
+        const int blk = t < src.j_count[0] ? 0 : 1;
+        const int j = blk == 0 ? src.j_first[0] + t : src.j_first[1] + (t - src.j_count[0]);
+        Innov L = landmark_innov(x, src, blk, 3 + 2 * (j - 1), sPvv, xv, yv, phi, prm.R);
 #pragma unroll
         for (int o = 0; o < OB; o++) {
             double nis, nd;
@@ -209,25 +291,19 @@ k_gate(const double *__restrict__ x, const double *__restrict__ P, size_t ld, in
             if (part_outer[slot] < ou) ou = part_outer[slot];
         }
         s_cls[i] = jj != 0 ? jj : (ou > prm.gate2 ? -1 : 0);
+        if (rank_res) {   // sharded: this rank's result; classification happens after the allgather
+            rank_res[i].nd = b;
+            rank_res[i].outer = ou;
+            rank_res[i].j = jj;
+        }
     }
     __syncthreads();
+    if (rank_res) {
+        if (threadIdx.x == 0) *counter = 0;
+        return;
+    }
     if (threadIdx.x == 0) {
-        int m = 0, k = 0;
-        for (int i = 0; i < nz; i++) {
-            int c = s_cls[i];
-            if (c > 0) {
-                zf[2 * m] = z[2 * i];
-                zf[2 * m + 1] = z[2 * i + 1];
-                idf[m] = c;
-                m++;
-            } else if (c < 0) {
-                zn[2 * k] = z[2 * i];
-                zn[2 * k + 1] = z[2 * i + 1];
-                k++;
-            }
-        }
-        counts[0] = m;
-        counts[1] = k;
+        gate_compact(s_cls, z, nz, zf, idf, zn, counts);
         *counter = 0;
     }
 }
@@ -241,10 +317,13 @@ __global__ void k_compute_association(const double *__restrict__ x, const double
         out[0] = out[1] = nan("");
         return;
     }
+    GateSrc src = {};
+    src.P = P;
+    src.ld = ld;
     double Pvv[9];
     for (int p = 0; p < 3; p++)
-        for (int q = 0; q < 3; q++) Pvv[p * 3 + q] = sym_at(P, ld, p, q);
-    Innov L = landmark_innov(x, P, ld, 3 + 2 * ((int)idf - 1), Pvv, x[0], x[1], x[2], prm.R);
+        for (int q = 0; q < 3; q++) Pvv[p * 3 + q] = gate_pvv(src, p, q);
+    Innov L = landmark_innov(x, src, 0, 3 + 2 * ((int)idf - 1), Pvv, x[0], x[1], x[2], prm.R);
     score(L, z0, z1, &out[0], &out[1]);
 }
 
@@ -279,9 +358,14 @@ int launch_gate(const double *d_x, const double *d_P, size_t ld, int Nf, const d
     double *part_nd = (double *)((char *)d_scratch + 256);
     double *part_outer = part_nd + per;
     int *part_j = (int *)(part_outer + per);
+    GateSrc src = {};
+    src.P = d_P;
+    src.ld = ld;
+    src.j_first[0] = 1;
+    src.j_count[0] = Nf;
     dim3 grid(gate_nblocks(Nf), (nz + OB - 1) / OB);
-    k_gate<<<grid, GATE_THREADS, 0, s>>>(d_x, d_P, ld, Nf, d_z, nz, prm, counter, part_nd, part_outer,
-                                        part_j, d_zf, d_idf, d_zn, d_counts);
+    k_gate<<<grid, GATE_THREADS, 0, s>>>(d_x, src, Nf, d_z, nz, prm, counter, part_nd, part_outer, part_j, d_zf,
+                                        d_idf, d_zn, d_counts, nullptr);
     if (launches) (*launches)++;
     CUDA_TRY(cudaGetLastError());
     return SLAM_OK;
@@ -294,6 +378,57 @@ int launch_compute_association(const double *d_x, const double *d_P, size_t ld, 
     memcpy(prm.R, R, sizeof(prm.R));
     prm.gate1 = prm.gate2 = 0;
     k_compute_association<<<1, 1, 0, s>>>(d_x, d_P, ld, n, z[0], z[1], prm, idf, d_out2, d_err);
+    if (launches) (*launches)++;
+    CUDA_TRY(cudaGetLastError());
+    return SLAM_OK;
+}
+
+// Sharded gating, phase 1: this rank's landmarks -> d_rank_res[nz] (GateRes, 24 bytes each).
+int launch_gate_shard(const double *d_x, const double *d_P3, int npad, const double *const d_Pb[2], size_t ldb,
+                      const int lo[2], const int hi[2], const double *d_z, int nz, const double R[4], double gate1,
+                      double gate2, void *d_scratch, size_t scratch_bytes, void *d_rank_res, cudaStream_t s,
+                      long long *launches) {
+    if (scratch_bytes < gate_scratch_bytes(nz)) {
+        slam_set_error("launch_gate_shard: scratch too small");
+        return SLAM_ERR_ARG;
+    }
+    GateParams prm;
+    memcpy(prm.R, R, sizeof(prm.R));
+    prm.gate1 = gate1;
+    prm.gate2 = gate2;
+    GateSrc src = {};
+    src.P3 = d_P3;
+    src.npad = npad;
+    src.ldb = ldb;
+    int total = 0;
+    for (int q = 0; q < 2; q++) {
+        src.Pb[q] = d_Pb[q];
+        src.lo[q] = lo[q];
+        int f0 = lo[q] < 3 ? 3 : lo[q];          // block starts are 0 or odd; landmark rows start at 3
+        int cnt = hi[q] > f0 ? (hi[q] - f0) / 2 : 0;
+        src.j_first[q] = (f0 - 3) / 2 + 1;
+        src.j_count[q] = cnt;
+        total += cnt;
+    }
+    size_t per = (size_t)GATE_MAX_BLOCKS * (size_t)nz;
+    unsigned *counter = (unsigned *)d_scratch;
+    double *part_nd = (double *)((char *)d_scratch + 256);
+    double *part_outer = part_nd + per;
+    int *part_j = (int *)(part_outer + per);
+    dim3 grid(gate_nblocks(total), (nz + OB - 1) / OB);
+    k_gate<<<grid, GATE_THREADS, 0, s>>>(d_x, src, total, d_z, nz, prm, counter, part_nd, part_outer, part_j, nullptr,
+                                        nullptr, nullptr, nullptr, (GateRes *)d_rank_res);
+    if (launches) (*launches)++;
+    CUDA_TRY(cudaGetLastError());
+    return SLAM_OK;
+}
+
+// phase 2 (after the allgather of the per-rank results): classify and compact, identically on every rank
+int launch_gate_finalize(const void *d_all_res, int world, const double *d_z, int nz, double gate2, double *d_zf,
+                         int64_t *d_idf, double *d_zn, int *d_counts, cudaStream_t s, long long *launches) {
+    GateParams prm = {};
+    prm.gate2 = gate2;
+    k_gate_finalize<<<1, 256, 0, s>>>((const GateRes *)d_all_res, world, d_z, nz, prm, d_zf, d_idf, d_zn, d_counts);
     if (launches) (*launches)++;
     CUDA_TRY(cudaGetLastError());
     return SLAM_OK;

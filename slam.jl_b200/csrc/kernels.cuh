@@ -35,3 +35,16 @@ int synth_fill(double *d_x, double *d_Pb, size_t ldb, int r0, int r1, int n_land
 int synth_observations_host(int n_landmarks, double side, uint64_t seed, int m, int spurious, double *z,
                             int64_t *ids);
 int slam_require_device(int device);
+
+// ---- K4 (filter.cu): S = H*PHt + RR, C = inv(chol(S)), u = C'v; PHt is rank-major with stride npad
+int launch_innov_chol(const double *PHt, int npad, const double *Hn, const int *fp, const double *v, int m,
+                      const double R[4], double *S, double *C, double *u, int *err, cudaStream_t s);
+
+// ---- K2 on a row-block-sharded filter (gate.cu) ------------------------------------------
+constexpr int GATE_RES_BYTES = 24;
+int launch_gate_shard(const double *d_x, const double *d_P3, int npad, const double *const d_Pb[2], size_t ldb,
+                      const int lo[2], const int hi[2], const double *d_z, int nz, const double R[4], double gate1,
+                      double gate2, void *d_scratch, size_t scratch_bytes, void *d_rank_res, cudaStream_t s,
+                      long long *launches);
+int launch_gate_finalize(const void *d_all_res, int world, const double *d_z, int nz, double gate2, double *d_zf,
+                         int64_t *d_idf, double *d_zn, int *d_counts, cudaStream_t s, long long *launches);

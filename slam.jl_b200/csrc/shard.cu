@@ -1,0 +1,752 @@
+// Large-map mode: one EKF-SLAM filter whose covariance is row-block-sharded over the ranks of
+// one NCCL communicator (one process per GPU).  Rank r of W owns row blocks r and 2W-1-r of
+// 2W equal blocks, so the upper-triangle work of K6 is balanced.  Each block stores rows
+// [lo, hi) of every column (element (i, j) at Pb[(i - lo) + j*ldb]); only i <= j is live.
+//
+// update (src/ekf.jl:46-77) per rank:
+//   1. prep      Hn / fp / v from the replicated x (every rank, identical)
+//   2. extract   the S = 3 + 2m rows of P named by H (pose rows + observed landmark rows): the
+//                owner of row c writes P[c, c:n], others write zeros            -> rowbuf[S][n]
+//   3. ncclAllReduce(sum) of rowbuf  (x + 0 is exact; needs no host knowledge of idf)
+//   4. PHt for the rank's own rows (5 columns per observation; P[i,c] = local for c >= i, else
+//      rowbuf), and PHt at the S rows from rowbuf alone -> S, Cholesky, C, u on every rank
+//   5. W1 = PHt*C for the rank's rows                                           -> send buffer
+//   6. ncclAllGather of W1 (n x 2m doubles in total)
+//   7. unpermute into K6's two W1 layouts, x += W1*u for every row (x stays replicated)
+//   8. K6 on the two owned row blocks.
+// Reference citations are file:line under /root/reference.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+#include "kernels.cuh"
+
+// ---------------------------------------------------------------------------------------
+// NCCL through dlopen: the library loads (and the single-GPU paths run) without libnccl
+// ---------------------------------------------------------------------------------------
+namespace {
+struct NcclApi {
+    void *handle = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                              cudaStream_t) = nullptr;
+    ncclResult_t (*Broadcast)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+NcclApi g_nccl;
+
+int load_nccl() {
+    if (g_nccl.handle) return SLAM_OK;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    void *h = nullptr;
+    for (const char *nm : names) {
+        h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (h) break;
+    }
+    if (!h) {
+        slam_set_error("cannot dlopen libnccl.so.2: %s", dlerror());
+        return SLAM_ERR_NCCL;
+    }
+#define LOAD(field, sym)                                                \
+    *(void **)(&g_nccl.field) = dlsym(h, sym);                          \
+    if (!g_nccl.field) {                                                \
+        slam_set_error("libnccl lacks %s", sym);                        \
+        return SLAM_ERR_NCCL;                                           \
+    }
+    LOAD(GetUniqueId, "ncclGetUniqueId")
+    LOAD(CommInitRank, "ncclCommInitRank")
+    LOAD(CommDestroy, "ncclCommDestroy")
+    LOAD(AllGather, "ncclAllGather")
+    LOAD(AllReduce, "ncclAllReduce")
+    LOAD(Broadcast, "ncclBroadcast")
+    LOAD(GetErrorString, "ncclGetErrorString")
+#undef LOAD
+    g_nccl.handle = h;
+    return SLAM_OK;
+}
+}  // namespace
+
+#define NCCL_TRY(expr)                                                                      \
+    do {                                                                                    \
+        ncclResult_t r__ = (expr);                                                          \
+        if (r__ != ncclSuccess) {                                                           \
+            slam_set_error("%s failed: %s", #expr, g_nccl.GetErrorString(r__));             \
+            return SLAM_ERR_NCCL;                                                           \
+        }                                                                                   \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------
+// partition arithmetic (no device needed)
+// ---------------------------------------------------------------------------------------
+static int block_height(int n, int world) {
+    int hb = (n + 2 * world - 1) / (2 * world);
+    return round_up(hb, 256);   // K6 row tiles never straddle two blocks
+}
+
+// Block b covers rows [block_lo(b), block_lo(b+1)).  Boundaries other than 0 are odd, so a
+// landmark's two rows (3 + 2k, 4 + 2k) never straddle two blocks (the gating kernel reads the
+// landmark's 2x2 diagonal block from one owner).
+__host__ __device__ static inline int block_lo(int b, int hb, int n) {
+    if (b <= 0) return 0;
+    long long v = (long long)b * hb + 1;
+    return v < n ? (int)v : n;
+}
+
+static void plan_blocks(int n, int hb, int world, int rank, int lo[2], int hi[2]) {
+    const int b[2] = {rank, 2 * world - 1 - rank};
+    for (int q = 0; q < 2; q++) {
+        lo[q] = block_lo(b[q], hb, n);
+        hi[q] = b[q] == 2 * world - 1 ? n : block_lo(b[q] + 1, hb, n);
+    }
+}
+
+extern "C" int slam_shard_plan(int n, int world, int rank, int lo[2], int hi[2]) {
+    ARG_CHECK(n >= 3 && world >= 1 && rank >= 0 && rank < world && lo && hi, "bad argument");
+    plan_blocks(n, block_height(n, world), world, rank, lo, hi);
+    return SLAM_OK;
+}
+
+extern "C" int slam_shard_unique_id(char id[128]) {
+    ARG_CHECK(id != nullptr, "NULL id");
+    int rc = load_nccl();
+    if (rc) return rc;
+    ncclUniqueId u;
+    NCCL_TRY(g_nccl.GetUniqueId(&u));
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    memcpy(id, &u, 128);
+    return SLAM_OK;
+}
+
+struct slam_shard {
+    int device = 0, rank = 0, world = 1;
+    int n_max = 0, n = 3, hb = 0;
+    int lo[2] = {0, 0}, hi[2] = {0, 0};
+    size_t ldb = 0;
+    ncclComm_t comm = nullptr;
+    cudaStream_t stream = nullptr;
+    double *d_x = nullptr;
+    double *d_Pb[2] = {nullptr, nullptr};
+    int *d_err = nullptr;
+    void *h_pin = nullptr;
+    double *d_zf = nullptr, *d_z = nullptr, *d_zn = nullptr;
+    int64_t *d_idf = nullptr;
+    // update workspace
+    int ws_R = 0, npad = 0;
+    double *d_rowbuf = nullptr, *d_PHtloc = nullptr, *d_PHtH = nullptr, *d_S = nullptr, *d_C = nullptr,
+           *d_u = nullptr, *d_v = nullptr, *d_Hn = nullptr, *d_W1send = nullptr, *d_W1gath = nullptr,
+           *d_W1c = nullptr;
+    int *d_fp = nullptr, *d_fpH = nullptr, *d_cs = nullptr;
+    // gating workspace
+    double *d_P3 = nullptr;      // rows 0..2 of every column, broadcast from rank 0
+    void *d_gate = nullptr;
+    size_t gate_bytes = 0;
+    long long launches = 0;
+    bool profiling = false;
+    std::vector<cudaEvent_t> ev;
+    int ev_used = 0;
+};
+
+#define S_CHECK(s)                                                        \
+    do {                                                                  \
+        ARG_CHECK((s) != nullptr, "NULL handle");                         \
+        CUDA_TRY(cudaSetDevice((s)->device));                             \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------
+// lifecycle
+// ---------------------------------------------------------------------------------------
+extern "C" int slam_shard_destroy(slam_shard_t *s) {
+    if (!s) return SLAM_OK;
+    cudaSetDevice(s->device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    if (s->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(s->comm);
+    cudaFree(s->d_x); cudaFree(s->d_Pb[0]); cudaFree(s->d_Pb[1]); cudaFree(s->d_err);
+    cudaFree(s->d_zf); cudaFree(s->d_z); cudaFree(s->d_zn); cudaFree(s->d_idf);
+    cudaFree(s->d_rowbuf); cudaFree(s->d_PHtloc); cudaFree(s->d_PHtH); cudaFree(s->d_S); cudaFree(s->d_C);
+    cudaFree(s->d_u); cudaFree(s->d_v); cudaFree(s->d_Hn); cudaFree(s->d_W1send); cudaFree(s->d_W1gath);
+    cudaFree(s->d_W1c); cudaFree(s->d_fp); cudaFree(s->d_fpH); cudaFree(s->d_cs);
+    cudaFree(s->d_P3); cudaFree(s->d_gate);
+    if (s->h_pin) cudaFreeHost(s->h_pin);
+    for (auto &e : s->ev) cudaEventDestroy(e);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    cudaGetLastError();
+    delete s;
+    return SLAM_OK;
+}
+
+extern "C" int slam_shard_create(int device, int rank, int world, const char id[128], int n_max,
+                                 slam_shard_t **out) {
+    ARG_CHECK(out != nullptr, "out is NULL");
+    *out = nullptr;
+    ARG_CHECK(world >= 1 && rank >= 0 && rank < world && n_max >= 3, "bad rank / world / n_max");
+    ARG_CHECK(world == 1 || id != nullptr, "NULL unique id");
+    int rc = slam_require_device(device);
+    if (rc) return rc;
+    slam_shard_t *s = new slam_shard();
+    s->device = device; s->rank = rank; s->world = world; s->n_max = n_max;
+    s->hb = block_height(n_max, world);
+    s->ldb = (size_t)s->hb + 16;
+    s->npad = round_up(n_max, DD_ROW_PAD);
+#define SH_TRY(expr)                                                                             \
+    do {                                                                                         \
+        cudaError_t e__ = (expr);                                                                \
+        if (e__ != cudaSuccess) {                                                                \
+            slam_set_error("%s failed: %s", #expr, cudaGetErrorString(e__));                     \
+            slam_shard_destroy(s);                                                               \
+            return SLAM_ERR_CUDA;                                                                \
+        }                                                                                        \
+    } while (0)
+    SH_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    SH_TRY(cudaMalloc(&s->d_x, sizeof(double) * (size_t)s->npad));
+    for (int q = 0; q < 2; q++) SH_TRY(cudaMalloc(&s->d_Pb[q], sizeof(double) * s->ldb * (size_t)n_max));
+    SH_TRY(cudaMalloc(&s->d_err, sizeof(int)));
+    SH_TRY(cudaMemsetAsync(s->d_err, 0, sizeof(int), s->stream));
+    SH_TRY(cudaMemsetAsync(s->d_x, 0, sizeof(double) * (size_t)s->npad, s->stream));
+    const size_t no = SLAM_MAX_OBS;
+    SH_TRY(cudaMalloc(&s->d_z, sizeof(double) * 2 * no));
+    SH_TRY(cudaMalloc(&s->d_zf, sizeof(double) * 2 * no));
+    SH_TRY(cudaMalloc(&s->d_zn, sizeof(double) * 2 * no));
+    SH_TRY(cudaMalloc(&s->d_idf, sizeof(int64_t) * no));
+    SH_TRY(cudaMallocHost(&s->h_pin, sizeof(double) * 8 * no + 256));
+    SH_TRY(cudaMalloc(&s->d_P3, sizeof(double) * 4 * (size_t)s->npad));
+    SH_TRY(cudaStreamSynchronize(s->stream));
+#undef SH_TRY
+    if (world > 1) {
+        rc = load_nccl();
+        if (rc) { slam_shard_destroy(s); return rc; }
+        ncclUniqueId u;
+        memcpy(&u, id, 128);
+        ncclResult_t r = g_nccl.CommInitRank(&s->comm, world, u, rank);
+        if (r != ncclSuccess) {
+            slam_set_error("ncclCommInitRank failed: %s", g_nccl.GetErrorString(r));
+            s->comm = nullptr;
+            slam_shard_destroy(s);
+            return SLAM_ERR_NCCL;
+        }
+    }
+    plan_blocks(3, s->hb, world, rank, s->lo, s->hi);
+    s->n = 3;
+    *out = s;
+    return SLAM_OK;
+}
+
+extern "C" int slam_shard_n(slam_shard_t *s) {
+    if (!s) { slam_set_error("slam_shard_n: NULL handle"); return SLAM_ERR_ARG; }
+    return s->n;
+}
+extern "C" void *slam_shard_stream(slam_shard_t *s) { return s ? (void *)s->stream : nullptr; }
+extern "C" long long slam_shard_launch_count(slam_shard_t *s) { return s ? s->launches : 0; }
+
+static int shard_check_latched(slam_shard_t *s) {
+    int *he = (int *)s->h_pin;
+    CUDA_TRY(cudaMemcpyAsync(he, s->d_err, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    int e = *he;
+    if (e != 0) {
+        CUDA_TRY(cudaMemsetAsync(s->d_err, 0, sizeof(int), s->stream));
+        slam_set_error(e == SLAM_ERR_NOT_PD      ? "innovation covariance not positive definite"
+                       : e == SLAM_ERR_BAD_INDEX ? "landmark id out of range"
+                                                 : "device-side error %d", e);
+        return e;
+    }
+    return SLAM_OK;
+}
+
+extern "C" int slam_shard_sync(slam_shard_t *s) {
+    S_CHECK(s);
+    return shard_check_latched(s);
+}
+
+extern "C" int slam_shard_synth_state(slam_shard_t *s, int n_landmarks, double side, uint64_t seed) {
+    S_CHECK(s);
+    ARG_CHECK(n_landmarks >= 0 && side > 0, "bad argument");
+    const int n = 3 + 2 * n_landmarks;
+    if (n > s->n_max) {
+        slam_set_error("slam_shard_synth_state: n = %d exceeds capacity n_max = %d", n, s->n_max);
+        return SLAM_ERR_CAPACITY;
+    }
+    s->n = n;
+    // block boundaries follow the capacity's block height so that growth never moves rows
+    plan_blocks(n, s->hb, s->world, s->rank, s->lo, s->hi);
+    for (int q = 0; q < 2; q++) {
+        int rc = synth_fill(s->d_x, s->d_Pb[q], s->ldb, s->lo[q], s->hi[q], n_landmarks, side, seed, s->stream,
+                            &s->launches);
+        if (rc) return rc;
+    }
+    return SLAM_OK;
+}
+
+extern "C" int slam_shard_get_pose(slam_shard_t *s, double pose[3]) {
+    S_CHECK(s);
+    ARG_CHECK(pose != nullptr, "NULL pose");
+    double *hp = (double *)s->h_pin + 8;
+    CUDA_TRY(cudaMemcpyAsync(hp, s->d_x, sizeof(double) * 3, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    pose[0] = hp[0]; pose[1] = hp[1]; pose[2] = hp[2];
+    return SLAM_OK;
+}
+
+extern "C" int slam_shard_get_x(slam_shard_t *s, double *x) {
+    S_CHECK(s);
+    ARG_CHECK(x != nullptr, "NULL x");
+    CUDA_TRY(cudaMemcpyAsync(x, s->d_x, sizeof(double) * s->n, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return SLAM_OK;
+}
+
+// owned entries (i <= j, row i in one of this rank's blocks) of the requested window; others untouched
+extern "C" int slam_shard_get_cov_block(slam_shard_t *s, int i0, int ni, int j0, int nj, double *out, int ldo) {
+    S_CHECK(s);
+    ARG_CHECK(out && i0 >= 0 && j0 >= 0 && ni >= 0 && nj >= 0 && i0 + ni <= s->n && j0 + nj <= s->n && ldo >= ni,
+              "bad window");
+    int copied = 0;
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    for (int q = 0; q < 2; q++) {
+        int a = std::max(i0, s->lo[q]), b = std::min(i0 + ni, s->hi[q]);
+        if (a >= b) continue;
+        // rows [a, b) of columns [j0, j0+nj): strided 2-D copy out of the block
+        CUDA_TRY(cudaMemcpy2D(out + (a - i0), sizeof(double) * (size_t)ldo,
+                              s->d_Pb[q] + (size_t)(a - s->lo[q]) + (size_t)j0 * s->ldb, sizeof(double) * s->ldb,
+                              sizeof(double) * (b - a), nj, cudaMemcpyDeviceToHost));
+        copied += (b - a) * nj;
+    }
+    return copied;
+}
+
+// ---------------------------------------------------------------------------------------
+// update kernels
+// ---------------------------------------------------------------------------------------
+struct ShardGeom {
+    int rank, world, hb, slot, n, npad;   // slot = rows reserved per block in rank-local buffers
+    int lo[2], hi[2];
+    size_t ldb;
+    double *Pb[2];
+};
+
+__device__ __forceinline__ void row_owner(const ShardGeom &g, int i, int *owner, int *q, int *li) {
+    int b = i <= 0 ? 0 : (i - 1) / g.hb;
+    if (b > 2 * g.world - 1) b = 2 * g.world - 1;
+    *q = b < g.world ? 0 : 1;
+    *owner = b < g.world ? b : 2 * g.world - 1 - b;
+    *li = *q * g.slot + (i - block_lo(b, g.hb, g.n));
+}
+
+// step 1: observation model for every associated observation, innovation v, and the list cs of
+// the S = 3 + 2m state rows that H touches (src/ekf.jl:55-61, src/common.jl:139-165)
+__global__ void k_sh_prep(const double *__restrict__ x, int n, const double *__restrict__ zf,
+                          const int64_t *__restrict__ idf, int m, double *Hn, int *fp, int *fpH, int *cs,
+                          double *v, int *err) {
+    const int Nf = (n - 3) / 2;
+    if (threadIdx.x < 3 && blockIdx.x == 0) cs[threadIdx.x] = threadIdx.x;
+    for (int o = blockIdx.x * blockDim.x + threadIdx.x; o < m; o += gridDim.x * blockDim.x) {
+        int64_t id = idf[o];
+        if (id < 1 || id > Nf) {
+            atomicCAS(err, 0, SLAM_ERR_BAD_INDEX);
+            id = 1;
+        }
+        int f = 3 + 2 * ((int)id - 1);
+        double zp[2];
+        observe_model(x[0], x[1], x[2], x[f], x[f + 1], zp, Hn + 10 * o);
+        fp[o] = f;
+        fpH[o] = 3 + 2 * o;
+        cs[3 + 2 * o] = f;
+        cs[3 + 2 * o + 1] = f + 1;
+        v[2 * o] = zf[2 * o] - zp[0];
+        v[2 * o + 1] = mpi_to_pi(zf[2 * o + 1] - zp[1]);
+    }
+}
+
+// step 2: rowbuf[s][j] = P[cs[s], j] for j >= cs[s] if this rank owns row cs[s], else 0
+__global__ void k_sh_extract(ShardGeom g, const int *__restrict__ cs, double *__restrict__ rowbuf) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int s = blockIdx.y;
+    if (j >= g.npad) return;
+    const int c = cs[s];
+    int owner, q, li;
+    row_owner(g, c, &owner, &q, &li);
+    double val = 0.0;
+    if (owner == g.rank && j >= c && j < g.n) val = g.Pb[q][(size_t)(c - g.lo[q]) + (size_t)j * g.ldb];
+    rowbuf[(size_t)s * g.npad + j] = val;
+}
+
+// P[i, cs[s]] for a row i this rank owns (block q): local when cs[s] >= i, else from the gathered row
+__device__ __forceinline__ double sh_get(const ShardGeom &g, const double *rowbuf, int q, int i, int s, int c) {
+    return c >= i ? g.Pb[q][(size_t)(i - g.lo[q]) + (size_t)c * g.ldb] : rowbuf[(size_t)s * g.npad + i];
+}
+
+// step 4a: PHt rows of the rank's own rows (src/ekf.jl:67), rank-major over the local row index
+__global__ void __launch_bounds__(256)
+k_sh_pht(ShardGeom g, const double *__restrict__ rowbuf, const double *__restrict__ Hn, const int *__restrict__ fp,
+         int m, double *__restrict__ PHtloc) {
+    const int li = blockIdx.x * blockDim.x + threadIdx.x;
+    const int nloc = 2 * g.slot;
+    if (li >= nloc) return;
+    const int q = li / g.slot;
+    const int i = g.lo[q] + (li - q * g.slot);
+    const bool live = i < g.hi[q];
+    double p0 = 0, p1 = 0, p2 = 0;
+    if (live) {
+        p0 = sh_get(g, rowbuf, q, i, 0, 0);
+        p1 = sh_get(g, rowbuf, q, i, 1, 1);
+        p2 = sh_get(g, rowbuf, q, i, 2, 2);
+    }
+    for (int o = 0; o < m; o++) {
+        double a0 = 0, a1 = 0;
+        if (live) {
+            const double *hh = Hn + 10 * o;
+            const int f = fp[o];
+            double p3 = sh_get(g, rowbuf, q, i, 3 + 2 * o, f);
+            double p4 = sh_get(g, rowbuf, q, i, 3 + 2 * o + 1, f + 1);
+            a0 = p0 * hh[0] + p1 * hh[1] + p2 * hh[2] + p3 * hh[6] + p4 * hh[7];
+            a1 = p0 * hh[3] + p1 * hh[4] + p2 * hh[5] + p3 * hh[8] + p4 * hh[9];
+        }
+        PHtloc[(size_t)(2 * o) * nloc + li] = a0;
+        PHtloc[(size_t)(2 * o + 1) * nloc + li] = a1;
+    }
+}
+
+// step 4b: PHt at the S rows named by H, from rowbuf alone (identical on every rank)
+__global__ void k_sh_pht_hset(int npad, int S, const int *__restrict__ cs, const double *__restrict__ rowbuf,
+                              const double *__restrict__ Hn, int m, double *__restrict__ PHtH) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= S * m) return;
+    const int s = idx % S, o = idx / S;
+    const int i = cs[s];
+    auto at = [&](int s2) {   // P[i, cs[s2]]
+        int c = cs[s2];
+        return c >= i ? rowbuf[(size_t)s * npad + c] : rowbuf[(size_t)s2 * npad + i];
+    };
+    const double *hh = Hn + 10 * o;
+    double p0 = at(0), p1 = at(1), p2 = at(2), p3 = at(3 + 2 * o), p4 = at(3 + 2 * o + 1);
+    PHtH[(size_t)(2 * o) * S + s] = p0 * hh[0] + p1 * hh[1] + p2 * hh[2] + p3 * hh[6] + p4 * hh[7];
+    PHtH[(size_t)(2 * o + 1) * S + s] = p0 * hh[3] + p1 * hh[4] + p2 * hh[5] + p3 * hh[8] + p4 * hh[9];
+}
+
+// step 5: W1 rows of the rank's own rows (src/ekf.jl:71) into the allgather send buffer
+// [chunk][local row][RC]
+__global__ void __launch_bounds__(128)
+k_sh_gain(int nloc, int R, int RC, const double *__restrict__ PHtloc, const double *__restrict__ Cm,
+          double *__restrict__ W1send) {
+    const int li = blockIdx.x * blockDim.x + threadIdx.x;
+    if (li >= nloc) return;
+    const int nch = (R + RC - 1) / RC;
+    for (int k = 0; k < nch * RC; k++) {
+        double a = 0;
+        if (k < R)
+            for (int l = 0; l <= k; l++) a += PHtloc[(size_t)l * nloc + li] * Cm[(size_t)l + (size_t)k * R];
+        W1send[((size_t)(k / RC) * nloc + li) * RC + (k % RC)] = a;
+    }
+}
+
+// step 7: gathered W1 -> K6's two layouts in global row order; x += W1*u (src/ekf.jl:72-74)
+__global__ void __launch_bounds__(128)
+k_sh_unpermute(ShardGeom g, int R, int RC, const double *__restrict__ W1gath, const double *__restrict__ u,
+               double *__restrict__ W1c, double *__restrict__ x) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.npad) return;
+    const int nch = (R + RC - 1) / RC, nloc = 2 * g.slot;
+    int owner = 0, q = 0, li = 0;
+    const bool live = i < g.n;
+    if (live) row_owner(g, i, &owner, &q, &li);
+    double dx = 0;
+    for (int k = 0; k < nch * RC; k++) {
+        const int c = k / RC, kk = k % RC;
+        double a = live ? W1gath[(((size_t)owner * nch + c) * nloc + li) * RC + kk] : 0.0;
+        double *chunk = W1c + (size_t)c * 2 * g.npad * RC;
+        chunk[(size_t)i * RC + kk] = a;
+        chunk[(size_t)g.npad * RC + (size_t)kk * g.npad + i] = a;
+        if (k < R) dx += a * u[k];
+    }
+    if (live) x[i] += dx;
+}
+
+// ---------------------------------------------------------------------------------------
+// update driver
+// ---------------------------------------------------------------------------------------
+static ShardGeom geom(const slam_shard_t *s) {
+    ShardGeom g;
+    g.rank = s->rank; g.world = s->world; g.hb = s->hb; g.slot = s->hb + 2; g.n = s->n; g.npad = s->npad;
+    for (int q = 0; q < 2; q++) { g.lo[q] = s->lo[q]; g.hi[q] = s->hi[q]; g.Pb[q] = s->d_Pb[q]; }
+    g.ldb = s->ldb;
+    return g;
+}
+
+static int shard_ensure_ws(slam_shard_t *s, int R) {
+    const int RC = downdate_chunk_width(R);
+    const int Rw = std::max(round_up(R, RC), 32);
+    if (s->ws_R >= Rw) return SLAM_OK;
+    double **bufs[] = {&s->d_rowbuf, &s->d_PHtloc, &s->d_PHtH, &s->d_S, &s->d_C, &s->d_u, &s->d_v, &s->d_Hn,
+                       &s->d_W1send, &s->d_W1gath, &s->d_W1c};
+    for (auto b : bufs) { cudaFree(*b); *b = nullptr; }
+    cudaFree(s->d_fp); cudaFree(s->d_fpH); cudaFree(s->d_cs);
+    s->d_fp = s->d_fpH = s->d_cs = nullptr;
+    s->ws_R = 0;
+    const size_t S = 3 + Rw, nloc = 2 * ((size_t)s->hb + 2), npad = s->npad;
+    CUDA_TRY(cudaMalloc(&s->d_rowbuf, sizeof(double) * S * npad));
+    CUDA_TRY(cudaMalloc(&s->d_PHtloc, sizeof(double) * Rw * nloc));
+    CUDA_TRY(cudaMalloc(&s->d_PHtH, sizeof(double) * Rw * S));
+    CUDA_TRY(cudaMalloc(&s->d_S, sizeof(double) * Rw * Rw));
+    CUDA_TRY(cudaMalloc(&s->d_C, sizeof(double) * Rw * Rw));
+    CUDA_TRY(cudaMalloc(&s->d_u, sizeof(double) * Rw));
+    CUDA_TRY(cudaMalloc(&s->d_v, sizeof(double) * Rw));
+    CUDA_TRY(cudaMalloc(&s->d_Hn, sizeof(double) * 10 * (Rw / 2)));
+    CUDA_TRY(cudaMalloc(&s->d_W1send, sizeof(double) * Rw * nloc));
+    if (s->world > 1) CUDA_TRY(cudaMalloc(&s->d_W1gath, sizeof(double) * Rw * nloc * s->world));
+    CUDA_TRY(cudaMalloc(&s->d_W1c, sizeof(double) * 2 * npad * Rw));
+    CUDA_TRY(cudaMalloc(&s->d_fp, sizeof(int) * (Rw / 2)));
+    CUDA_TRY(cudaMalloc(&s->d_fpH, sizeof(int) * (Rw / 2)));
+    CUDA_TRY(cudaMalloc(&s->d_cs, sizeof(int) * S));
+    s->ws_R = Rw;
+    return SLAM_OK;
+}
+
+static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const double R[4],
+                               const int64_t *d_idf) {
+    if (m == 0) return SLAM_OK;
+    if (m > SLAM_MAX_OBS) {
+        slam_set_error("slam_shard_update: m = %d exceeds SLAM_MAX_OBS", m);
+        return SLAM_ERR_CAPACITY;
+    }
+    if (s->n <= 3) {
+        slam_set_error("slam_shard_update: %d observations but the map is empty", m);
+        return SLAM_ERR_BAD_INDEX;
+    }
+    const int Rk = 2 * m, S = 3 + Rk;
+    int rc = shard_ensure_ws(s, Rk);
+    if (rc) return rc;
+    const int RC = downdate_chunk_width(Rk), nch = (Rk + RC - 1) / RC;
+    const int nloc = 2 * (s->hb + 2), npad = s->npad;
+    const ShardGeom g = geom(s);
+    cudaStream_t st = s->stream;
+    k_sh_prep<<<(m + 255) / 256, 256, 0, st>>>(s->d_x, s->n, d_zf, d_idf, m, s->d_Hn, s->d_fp, s->d_fpH, s->d_cs,
+                                              s->d_v, s->d_err);
+    k_sh_extract<<<dim3((npad + 255) / 256, S), 256, 0, st>>>(g, s->d_cs, s->d_rowbuf);
+    s->launches += 2;
+    if (s->world > 1)
+        NCCL_TRY(g_nccl.AllReduce(s->d_rowbuf, s->d_rowbuf, (size_t)S * npad, ncclFloat64, ncclSum, s->comm, st));
+    k_sh_pht<<<(nloc + 255) / 256, 256, 0, st>>>(g, s->d_rowbuf, s->d_Hn, s->d_fp, m, s->d_PHtloc);
+    k_sh_pht_hset<<<(S * m + 127) / 128, 128, 0, st>>>(npad, S, s->d_cs, s->d_rowbuf, s->d_Hn, m, s->d_PHtH);
+    rc = launch_innov_chol(s->d_PHtH, S, s->d_Hn, s->d_fpH, s->d_v, m, R, s->d_S, s->d_C, s->d_u, s->d_err, st);
+    if (rc) return rc;
+    k_sh_gain<<<(nloc + 127) / 128, 128, 0, st>>>(nloc, Rk, RC, s->d_PHtloc, s->d_C, s->d_W1send);
+    s->launches += 4;
+    const double *gathered = s->d_W1send;
+    if (s->world > 1) {
+        NCCL_TRY(g_nccl.AllGather(s->d_W1send, s->d_W1gath, (size_t)nch * nloc * RC, ncclFloat64, s->comm, st));
+        gathered = s->d_W1gath;
+    }
+    const int npad_used = round_up(s->n, DD_ROW_PAD);
+    k_sh_unpermute<<<(npad_used + 127) / 128, 128, 0, st>>>(g, Rk, RC, gathered, s->d_u, s->d_W1c, s->d_x);
+    s->launches++;
+    CUDA_TRY(cudaGetLastError());
+    const bool timed = s->profiling && s->ev_used + 2 <= (int)s->ev.size();
+    if (timed) CUDA_TRY(cudaEventRecord(s->ev[s->ev_used], st));
+    for (int q = 0; q < 2 && rc == SLAM_OK; q++)
+        rc = launch_downdate_rows(s->d_Pb[q], s->ldb, s->lo[q], s->hi[q], s->n, s->d_W1c, npad, Rk, 0, st,
+                                  &s->launches);
+    if (timed) {
+        CUDA_TRY(cudaEventRecord(s->ev[s->ev_used + 1], st));
+        s->ev_used += 2;
+    }
+    return rc;
+}
+
+extern "C" int slam_shard_update_resident(slam_shard_t *s, const double *d_zf, int m, const double R[4],
+                                          const int64_t *d_idf) {
+    S_CHECK(s);
+    ARG_CHECK(m >= 0 && R, "bad argument");
+    ARG_CHECK(m == 0 || (d_zf && d_idf), "NULL device buffer");
+    return shard_update_device(s, d_zf, m, R, d_idf);
+}
+
+extern "C" int slam_shard_update(slam_shard_t *s, const double *zf, int m, const double R[4], const int64_t *idf) {
+    S_CHECK(s);
+    ARG_CHECK(m >= 0 && R, "bad argument");
+    if (m == 0) return SLAM_OK;
+    ARG_CHECK(zf && idf, "NULL observation buffer");
+    if (m > SLAM_MAX_OBS) {
+        slam_set_error("slam_shard_update: m = %d exceeds SLAM_MAX_OBS", m);
+        return SLAM_ERR_CAPACITY;
+    }
+    double *hz = (double *)((char *)s->h_pin + 256);
+    int64_t *hid = (int64_t *)(hz + 6 * SLAM_MAX_OBS);
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    memcpy(hz, zf, sizeof(double) * 2 * m);
+    memcpy(hid, idf, sizeof(int64_t) * m);
+    CUDA_TRY(cudaMemcpyAsync(s->d_zf, hz, sizeof(double) * 2 * m, cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(cudaMemcpyAsync(s->d_idf, hid, sizeof(int64_t) * m, cudaMemcpyHostToDevice, s->stream));
+    int rc = shard_update_device(s, s->d_zf, m, R, s->d_idf);
+    if (rc) return rc;
+    return shard_check_latched(s);
+}
+
+extern "C" int slam_shard_profile(slam_shard_t *s, int on) {
+    S_CHECK(s);
+    if (on && s->ev.empty()) {
+        s->ev.resize(2 * 4096);
+        for (auto &e : s->ev) CUDA_TRY(cudaEventCreate(&e));
+    }
+    s->profiling = on != 0;
+    s->ev_used = 0;
+    return SLAM_OK;
+}
+
+extern "C" int slam_shard_profile_read(slam_shard_t *s, double *k6_ms, int *k6_updates) {
+    S_CHECK(s);
+    ARG_CHECK(k6_ms && k6_updates, "NULL argument");
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    double tot = 0;
+    for (int i = 0; i + 1 < s->ev_used; i += 2) {
+        float ms = 0;
+        CUDA_TRY(cudaEventElapsedTime(&ms, s->ev[i], s->ev[i + 1]));
+        tot += ms;
+    }
+    *k6_ms = tot;
+    *k6_updates = s->ev_used / 2;
+    s->ev_used = 0;
+    return SLAM_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// predict (src/ekf.jl:8-43): rank 0 owns rows 0..2 of P; x is replicated
+// ---------------------------------------------------------------------------------------
+struct ShPredict { double g, v, w, dt, Q[4]; };
+
+__global__ void __launch_bounds__(256)
+k_sh_predict_P(const double *__restrict__ x, double *Pb0, size_t ldb, int n, ShPredict p) {
+    const double phi = x[2];
+    const double s = sin(p.g + phi), c = cos(p.g + phi);
+    const double vts = p.v * p.dt * s, vtc = p.v * p.dt * c;
+    int j = 3 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n) {
+        double *col = Pb0 + (size_t)j * ldb;
+        double p0 = col[0], p1 = col[1], p2 = col[2];
+        col[0] = p0 + (-vts) * p2;
+        col[1] = p1 + vtc * p2;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        const double Gv[3][3] = {{1, 0, -vts}, {0, 1, vtc}, {0, 0, 1}};
+        const double Gu[3][2] = {{p.dt * c, -vts}, {p.dt * s, vtc},
+                                 {p.dt * sin(p.g) / p.w, p.v * p.dt * cos(p.g) / p.w}};
+        double Pv[3][3], A[3][3], B[3][3], GQ[3][2];
+        for (int i = 0; i < 3; i++)
+            for (int q = 0; q < 3; q++) Pv[i][q] = i <= q ? Pb0[i + q * ldb] : Pb0[q + i * ldb];
+        for (int i = 0; i < 3; i++)
+            for (int q = 0; q < 3; q++) {
+                double a = 0;
+                for (int k = 0; k < 3; k++) a += Gv[i][k] * Pv[k][q];
+                A[i][q] = a;
+            }
+        for (int i = 0; i < 3; i++)
+            for (int q = 0; q < 3; q++) {
+                double a = 0;
+                for (int k = 0; k < 3; k++) a += A[i][k] * Gv[q][k];
+                B[i][q] = a;
+            }
+        for (int i = 0; i < 3; i++)
+            for (int q = 0; q < 2; q++) GQ[i][q] = Gu[i][0] * p.Q[0 + 2 * q] + Gu[i][1] * p.Q[1 + 2 * q];
+        for (int i = 0; i < 3; i++)
+            for (int q = 0; q < 3; q++) B[i][q] += GQ[i][0] * Gu[q][0] + GQ[i][1] * Gu[q][1];
+        for (int i = 0; i < 3; i++)
+            for (int q = i; q < 3; q++) Pb0[i + q * ldb] = B[i][q];
+    }
+}
+
+__global__ void k_sh_predict_x(double *x, ShPredict p) {
+    const double phi = x[2];
+    const double s = sin(p.g + phi), c = cos(p.g + phi);
+    double x0 = x[0] + p.v * p.dt * c, x1 = x[1] + p.v * p.dt * s;
+    double x2 = mpi_to_pi(phi + p.v * p.dt * sin(p.g) / p.w);
+    x[0] = x0; x[1] = x1; x[2] = x2;
+}
+
+extern "C" int slam_shard_predict(slam_shard_t *s, double g, double v, double wheelbase, const double Q[4],
+                                  double dt) {
+    S_CHECK(s);
+    ARG_CHECK(Q != nullptr, "NULL Q");
+    ShPredict p;
+    p.g = g; p.v = v; p.w = wheelbase; p.dt = dt;
+    memcpy(p.Q, Q, sizeof(p.Q));
+    if (s->rank == 0) {
+        int blocks = std::max(1, (s->n - 3 + 255) / 256);
+        k_sh_predict_P<<<blocks, 256, 0, s->stream>>>(s->d_x, s->d_Pb[0], s->ldb, s->n, p);
+        s->launches++;
+    }
+    k_sh_predict_x<<<1, 1, 0, s->stream>>>(s->d_x, p);   // stream order: after the columns read x[2]
+    s->launches++;
+    CUDA_TRY(cudaGetLastError());
+    return SLAM_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// associate (src/data-association.jl:1-51): rows 0..2 broadcast from rank 0, every rank gates the
+// landmarks whose 2x2 diagonal block it owns, (nd, j, min nis) per observation allgathered
+// ---------------------------------------------------------------------------------------
+__global__ void k_sh_rows012(const double *__restrict__ Pb0, size_t ldb, int n, int npad, double *P3) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= npad) return;
+    for (int p = 0; p < 3; p++) P3[(size_t)p * npad + j] = (j < n && j >= p) ? Pb0[p + (size_t)j * ldb] : 0.0;
+}
+
+extern "C" int slam_shard_associate(slam_shard_t *s, const double *z, int nz, const double R[4], double gate1,
+                                    double gate2, double *zf, int64_t *idf, int *m, double *zn, int *k) {
+    S_CHECK(s);
+    ARG_CHECK(R && m && k && nz >= 0, "bad argument");
+    *m = 0;
+    *k = 0;
+    if (nz == 0) return SLAM_OK;
+    ARG_CHECK(z && zf && idf && zn, "NULL observation buffer");
+    if (nz > SLAM_MAX_OBS) {
+        slam_set_error("slam_shard_associate: nz = %d exceeds SLAM_MAX_OBS", nz);
+        return SLAM_ERR_CAPACITY;
+    }
+    if (!s->d_gate) {
+        s->gate_bytes = gate_scratch_bytes(SLAM_MAX_OBS) + (size_t)GATE_RES_BYTES * SLAM_MAX_OBS * (s->world + 1) + 64;
+        CUDA_TRY(cudaMalloc(&s->d_gate, s->gate_bytes));
+        CUDA_TRY(cudaMemsetAsync(s->d_gate, 0, 256, s->stream));
+    }
+    char *res_mine = (char *)s->d_gate + gate_scratch_bytes(SLAM_MAX_OBS);
+    char *res_all = res_mine + (size_t)GATE_RES_BYTES * SLAM_MAX_OBS;
+    int *d_counts = (int *)(res_all + (size_t)GATE_RES_BYTES * SLAM_MAX_OBS * s->world);
+    cudaStream_t st = s->stream;
+    double *hz = (double *)((char *)s->h_pin + 256);
+    CUDA_TRY(cudaStreamSynchronize(st));
+    memcpy(hz, z, sizeof(double) * 2 * nz);
+    CUDA_TRY(cudaMemcpyAsync(s->d_z, hz, sizeof(double) * 2 * nz, cudaMemcpyHostToDevice, st));
+    if (s->rank == 0) {
+        k_sh_rows012<<<(s->npad + 255) / 256, 256, 0, st>>>(s->d_Pb[0], s->ldb, s->n, s->npad, s->d_P3);
+        s->launches++;
+    }
+    if (s->world > 1) NCCL_TRY(g_nccl.Broadcast(s->d_P3, s->d_P3, (size_t)3 * s->npad, ncclFloat64, 0, s->comm, st));
+    int rc = launch_gate_shard(s->d_x, s->d_P3, s->npad, s->d_Pb, s->ldb, s->lo, s->hi, s->d_z, nz, R, gate1, gate2,
+                               s->d_gate, gate_scratch_bytes(SLAM_MAX_OBS), res_mine, st, &s->launches);
+    if (rc) return rc;
+    const void *all = res_mine;
+    if (s->world > 1) {
+        NCCL_TRY(g_nccl.AllGather(res_mine, res_all, (size_t)GATE_RES_BYTES * nz, ncclChar, s->comm, st));
+        all = res_all;
+    }
+    rc = launch_gate_finalize(all, s->world, s->d_z, nz, gate2, s->d_zf, s->d_idf, s->d_zn, d_counts, st,
+                              &s->launches);
+    if (rc) return rc;
+    int *hc = (int *)s->h_pin;
+    double *hzf = hz + 2 * SLAM_MAX_OBS, *hzn = hzf + 2 * SLAM_MAX_OBS;
+    int64_t *hid = (int64_t *)(hzn + 2 * SLAM_MAX_OBS);
+    CUDA_TRY(cudaMemcpyAsync(hc, d_counts, sizeof(int) * 2, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(hzf, s->d_zf, sizeof(double) * 2 * nz, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(hzn, s->d_zn, sizeof(double) * 2 * nz, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(hid, s->d_idf, sizeof(int64_t) * nz, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    *m = hc[0];
+    *k = hc[1];
+    memcpy(zf, hzf, sizeof(double) * 2 * (*m));
+    memcpy(idf, hid, sizeof(int64_t) * (*m));
+    memcpy(zn, hzn, sizeof(double) * 2 * (*k));
+    return SLAM_OK;
+}

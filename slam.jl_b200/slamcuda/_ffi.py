@@ -121,6 +121,8 @@ _sig("slam_shard_update_resident", I, vp, vp, I, c_double_p, vp)
 _sig("slam_shard_sync", I, vp)
 _sig("slam_shard_stream", vp, vp)
 _sig("slam_shard_launch_count", C.c_longlong, vp)
+_sig("slam_shard_profile", I, vp, I)
+_sig("slam_shard_profile_read", I, vp, c_double_p, c_int_p)
 
 # every symbol include/slamcuda.h declares (tests/test_abi.py checks the header against this)
 SYMBOLS = sorted(n for n in dir(lib) if n.startswith("slam_"))
