@@ -225,8 +225,73 @@ def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_ste
         lib.slam_destroy(h)
 
 
-def gpu_update_sharded(*a, **k):   # replaced below once the sharded path is imported
-    raise NotImplementedError
+def gpu_update_sharded(n_landmarks: int, m: int, steps: int, warmup: int, e2e_steps: int, rank: int, world: int,
+                       device: int):
+    """One filter, P row-block-sharded over `world` ranks (one process per GPU)."""
+    import torch
+    import torch.distributed as dist
+    from slamcuda._ffi import lib, check, dptr, iptr
+    from slamcuda.shard import ShardedFilter
+
+    n = 3 + 2 * n_landmarks
+    side = math.sqrt(n_landmarks / DENSITY)
+    sf = ShardedFilter(device, rank, world, n)
+    try:
+        sf.synth_state(n_landmarks, side, SEED)
+        nz = m + 4
+        z = np.zeros(2 * nz)
+        ids = np.zeros(m, dtype=np.int64)
+        check(lib.slam_synth_observations(None, n_landmarks, side, SEED, m, 4, dptr(z), iptr(ids)))
+        t0 = time.perf_counter()
+        zf2, idf, zn2 = sf.associate(z.reshape(nz, 2).T, R_OBS.reshape(2, 2), 4.0, 25.0)
+        t_assoc = time.perf_counter() - t0
+        if len(idf) != m or not np.array_equal(idf, ids):
+            raise RuntimeError(f"rank {rank}: sharded association wrong: {idf} vs {ids}")
+        zf = np.ascontiguousarray(zf2.T).reshape(-1)
+        stream = torch.cuda.ExternalStream(lib.slam_shard_stream(sf.ptr), device=device)
+        d_zf = torch.tensor(zf, device=f"cuda:{device}")
+        d_idf = torch.tensor(idf, device=f"cuda:{device}")
+        torch.cuda.synchronize(device)
+        for _ in range(warmup):
+            check(lib.slam_shard_update_resident(sf.ptr, d_zf.data_ptr(), m, dptr(R_OBS), d_idf.data_ptr()))
+        check(lib.slam_shard_sync(sf.ptr))
+        l0 = lib.slam_shard_launch_count(sf.ptr)
+        check(lib.slam_shard_profile(sf.ptr, 1))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        dist.barrier()
+        torch.cuda.synchronize(device)
+        e0.record(stream)
+        for _ in range(steps):
+            check(lib.slam_shard_update_resident(sf.ptr, d_zf.data_ptr(), m, dptr(R_OBS), d_idf.data_ptr()))
+        e1.record(stream)
+        check(lib.slam_shard_sync(sf.ptr))
+        torch.cuda.synchronize(device)
+        dist.barrier()
+        ms_total = e0.elapsed_time(e1)
+        k6, cnt = C.c_double(), C.c_int()
+        check(lib.slam_shard_profile_read(sf.ptr, C.byref(k6), C.byref(cnt)))
+        check(lib.slam_shard_profile(sf.ptr, 0))
+        launches = lib.slam_shard_launch_count(sf.ptr) - l0
+        # end to end: host zf / idf in, status + pose out, every step
+        pose = np.zeros(3)
+        check(lib.slam_shard_update(sf.ptr, dptr(zf), m, dptr(R_OBS), iptr(idf)))
+        dist.barrier()
+        torch.cuda.synchronize(device)
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            check(lib.slam_shard_update(sf.ptr, dptr(zf), m, dptr(R_OBS), iptr(idf)))
+            check(lib.slam_shard_get_pose(sf.ptr, dptr(pose)))
+        torch.cuda.synchronize(device)
+        e2e_ms = (time.perf_counter() - t0) / max(e2e_steps, 1) * 1e3
+        # max over ranks of every timing
+        t = torch.tensor([ms_total / steps, k6.value / max(cnt.value, 1), e2e_ms], device=f"cuda:{device}",
+                         dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, k6ms, e2e_ms = (float(v) for v in t.cpu())
+        return dict(n=n, m=m, ms_per_step=ms, k6_ms=k6ms, launches=int(launches) * world, assoc_ms=t_assoc * 1e3,
+                    e2e_ms_per_step=e2e_ms, h2d_bytes=(16 * m + 8 * m) * world, d2h_bytes=(4 + 24) * world)
+    finally:
+        sf.close()
 
 
 def reference_arm(args, rank: int):

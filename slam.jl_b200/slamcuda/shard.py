@@ -1,0 +1,106 @@
+"""Large-map mode: one filter whose covariance is row-block-sharded over the ranks of a
+torch.distributed job (one process per GPU).  torch.distributed is only the launcher-side
+plumbing (it hands the NCCL unique id to every rank); the collectives on the data path are
+issued by libslamcuda itself on its own stream."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from ._ffi import lib, check, dptr, iptr
+
+
+def shard_plan(n: int, world: int, rank: int):
+    """Rows [lo[q], hi[q]) of the two blocks rank owns (pure arithmetic, no device)."""
+    lo = (C.c_int * 2)()
+    hi = (C.c_int * 2)()
+    check(lib.slam_shard_plan(n, world, rank, lo, hi))
+    return [(lo[0], hi[0]), (lo[1], hi[1])]
+
+
+def exchange_unique_id(rank: int, world: int) -> bytes:
+    """Rank 0 creates the NCCL unique id; torch.distributed (any backend) broadcasts it."""
+    if world == 1:
+        return b"\0" * 128
+    import torch.distributed as dist
+    box = [None]
+    if rank == 0:
+        buf = C.create_string_buffer(128)
+        check(lib.slam_shard_unique_id(buf))
+        box[0] = buf.raw
+    dist.broadcast_object_list(box, src=0)
+    return box[0]
+
+
+class ShardedFilter:
+    def __init__(self, device: int, rank: int, world: int, n_max: int, unique_id: bytes | None = None):
+        self.rank, self.world, self.device = rank, world, device
+        uid = unique_id if unique_id is not None else exchange_unique_id(rank, world)
+        self.ptr = C.c_void_p()
+        check(lib.slam_shard_create(device, rank, world, uid, n_max, C.byref(self.ptr)))
+
+    def close(self):
+        if self.ptr:
+            lib.slam_shard_destroy(self.ptr)
+            self.ptr = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def n(self) -> int:
+        return check(lib.slam_shard_n(self.ptr))
+
+    def synth_state(self, n_landmarks: int, side: float, seed: int):
+        check(lib.slam_shard_synth_state(self.ptr, n_landmarks, float(side), seed))
+
+    def get_x(self):
+        x = np.empty(self.n)
+        check(lib.slam_shard_get_x(self.ptr, dptr(x)))
+        return x
+
+    def get_pose(self):
+        p = np.empty(3)
+        check(lib.slam_shard_get_pose(self.ptr, dptr(p)))
+        return p
+
+    def cov_block(self, i0, ni, j0, nj):
+        """Window of P with NaN where this rank does not own the row; returns (block, count)."""
+        out = np.full((ni, nj), np.nan, order="F")
+        cnt = check(lib.slam_shard_get_cov_block(self.ptr, i0, ni, j0, nj, dptr(out), max(ni, 1)))
+        return np.ascontiguousarray(out), cnt
+
+    def predict(self, g, v, w, Q, dt):
+        q = np.ascontiguousarray(np.asarray(Q, dtype=float).reshape(2, 2).T).reshape(-1)
+        check(lib.slam_shard_predict(self.ptr, float(g), float(v), float(w), dptr(q), float(dt)))
+
+    def associate(self, z, R, gate1, gate2):
+        z = np.asarray(z, dtype=float).reshape(2, -1)
+        nz = z.shape[1]
+        zc = np.ascontiguousarray(z.T).reshape(-1)
+        r = np.ascontiguousarray(np.asarray(R, dtype=float).reshape(2, 2).T).reshape(-1)
+        zf, zn = np.zeros(2 * max(nz, 1)), np.zeros(2 * max(nz, 1))
+        idf = np.zeros(max(nz, 1), dtype=np.int64)
+        m, k = C.c_int(), C.c_int()
+        check(lib.slam_shard_associate(self.ptr, dptr(zc), nz, dptr(r), float(gate1), float(gate2), dptr(zf),
+                                       iptr(idf), C.byref(m), dptr(zn), C.byref(k)))
+        m, k = m.value, k.value
+        return zf[:2 * m].reshape(m, 2).T.copy(), idf[:m].copy(), zn[:2 * k].reshape(k, 2).T.copy()
+
+    def update(self, zf, R, idf):
+        zf = np.asarray(zf, dtype=float).reshape(2, -1)
+        m = zf.shape[1]
+        zc = np.ascontiguousarray(zf.T).reshape(-1)
+        ids = np.ascontiguousarray(np.asarray(idf, dtype=np.int64).reshape(-1))
+        r = np.ascontiguousarray(np.asarray(R, dtype=float).reshape(2, 2).T).reshape(-1)
+        check(lib.slam_shard_update(self.ptr, dptr(zc), m, dptr(r), iptr(ids)))
+
+    def sync(self):
+        check(lib.slam_shard_sync(self.ptr))
+
+    def launch_count(self) -> int:
+        return int(lib.slam_shard_launch_count(self.ptr))

@@ -1,0 +1,64 @@
+"""torchrun check of the sharded path on W GPUs against the single-filter path on rank 0.
+usage: python -m torch.distributed.run --nproc-per-node W tools/shard_check.py [nl] [m]"""
+import math
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT / "slam.jl_b200"))
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+from slamcuda._ffi import lib, check, dptr, iptr  # noqa: E402
+from slamcuda.shard import ShardedFilter, shard_plan  # noqa: E402
+from slamcuda.slam import _Handle  # noqa: E402
+
+rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(lr)
+dist.init_process_group("gloo")
+nl = int(sys.argv[1]) if len(sys.argv) > 1 else 3000
+m = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+n = 3 + 2 * nl
+side = math.sqrt(nl / 0.0035)
+R = np.array([[0.01, 0.0], [0.0, (math.pi / 180) ** 2]])
+Q = np.array([[0.25, 0.0], [0.0, (3 * math.pi / 180) ** 2]])
+sf = ShardedFilter(lr, rank, world, n)
+sf.synth_state(nl, side, 7)
+h = _Handle(lr, n)
+check(lib.slam_synth_state(h.ptr, nl, side, 7))
+nz = m + 4
+z = np.zeros(2 * nz)
+ids = np.zeros(m, dtype=np.int64)
+check(lib.slam_synth_observations(h.ptr, nl, side, 7, m, 4, dptr(z), iptr(ids)))
+z2 = z.reshape(nz, 2).T
+zf_a, idf_a, zn_a = h.associate(z2, R, 4.0, 25.0)
+zf_b, idf_b, zn_b = sf.associate(z2, R, 4.0, 25.0)
+ok = np.array_equal(idf_a, idf_b) and np.array_equal(zf_a, zf_b) and np.array_equal(zn_a, zn_b)
+for _ in range(2):
+    h.predict(0.03, 7.7, 4.0, Q, 0.025)
+    sf.predict(0.03, 7.7, 4.0, Q, 0.025)
+    h.update(zf_a, R, idf_a)
+    sf.update(zf_a, R, idf_a)
+x1, P1 = h.get_state()
+ex = float(np.max(np.abs(sf.get_x() - x1)) / np.max(np.abs(x1)))
+eP = 0.0
+cnt_total = 0
+for lo, hi in shard_plan(n, world, rank):
+    if hi > lo:
+        blk, cnt = sf.cov_block(lo, hi - lo, 0, n)
+        cnt_total += cnt
+        ref = P1[lo:hi, :]
+        mask = np.arange(n)[None, :] >= np.arange(lo, hi)[:, None]
+        eP = max(eP, float(np.max(np.abs(blk - ref)[mask]) / np.max(np.abs(P1))))
+res = [None] * world
+dist.all_gather_object(res, (rank, ok, ex, eP, cnt_total, shard_plan(n, world, rank)))
+if rank == 0:
+    for r in res:
+        print("rank %d assoc_ok=%s x_rel=%.2e P_rel=%.2e rows*cols=%d blocks=%s" % r)
+    good = all(r[1] and r[2] < 1e-12 and r[3] < 1e-12 for r in res)
+    print("SHARD_CHECK", "PASS" if good else "FAIL", f"world={world} n={n} m={m}")
+sf.close()
+h.close()
+dist.destroy_process_group()
