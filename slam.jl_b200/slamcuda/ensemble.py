@@ -1,0 +1,77 @@
+"""Ensemble mode: many independent runs of the reference's simulator loop in one kernel launch
+(one CTA per filter); members are sharded by run across GPUs by giving each rank its own
+Ensemble with a different run0 (no collective)."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from ._ffi import lib, check, dptr
+
+
+class Ensemble:
+    def __init__(self, waypoints, landmarks, n_runs: int, seed: int = 0, run0: int = 0, nlaps: int = 2,
+                 device: int = 0):
+        wp = np.ascontiguousarray(np.asarray(waypoints, dtype=np.float64).T).reshape(-1)   # 2 x nwp column-major
+        lm = np.asarray(landmarks, dtype=np.float64).reshape(2, -1)
+        lmf = np.ascontiguousarray(lm.T).reshape(-1)
+        self.n_runs, self.nl = n_runs, lm.shape[1]
+        self.ptr = C.c_void_p()
+        check(lib.slam_ens_create(device, dptr(wp), len(wp) // 2, dptr(lmf) if lm.shape[1] else None, lm.shape[1],
+                                  nlaps, seed, run0, n_runs, C.byref(self.ptr)))
+        ns, nu = C.c_int(), C.c_int()
+        check(lib.slam_ens_steps(self.ptr, C.byref(ns), C.byref(nu)))
+        self.nsteps, self.nupdates = ns.value, nu.value
+
+    def close(self):
+        if self.ptr:
+            lib.slam_ens_destroy(self.ptr)
+            self.ptr = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def keep_tracks(self, on: bool = True):
+        check(lib.slam_ens_keep_tracks(self.ptr, int(on)))
+
+    def set_noise(self, ctrl, obs):
+        """ctrl: (n_runs, 2, nsteps) standard normals (speed, steering); obs: (n_runs, pool)."""
+        ctrl = np.asarray(ctrl, dtype=np.float64)
+        assert ctrl.shape == (self.n_runs, 2, self.nsteps)
+        c = np.ascontiguousarray(ctrl.transpose(0, 2, 1)).reshape(-1)      # per member: (speed, steer) per step
+        o = np.ascontiguousarray(np.asarray(obs, dtype=np.float64).reshape(self.n_runs, -1))
+        check(lib.slam_ens_set_noise(self.ptr, dptr(c), dptr(o.reshape(-1)), o.shape[1]))
+
+    def run(self):
+        check(lib.slam_ens_run(self.ptr))
+
+    def sync(self) -> int:
+        """Waits for the run; returns the number of members that stopped early."""
+        return check(lib.slam_ens_sync(self.ptr))
+
+    def results(self):
+        pose = np.empty((self.n_runs, 3))
+        nf = np.empty(self.n_runs, dtype=np.int32)
+        st = np.empty(self.n_runs, dtype=np.int32)
+        check(lib.slam_ens_get_results(self.ptr, dptr(pose), nf.ctypes.data_as(C.POINTER(C.c_int)),
+                                       st.ctypes.data_as(C.POINTER(C.c_int))))
+        return pose, nf, st
+
+    def track(self, member: int):
+        t = np.empty((self.nsteps, 3))
+        check(lib.slam_ens_get_track(self.ptr, member, dptr(t)))
+        return t.T.copy()
+
+    def state(self, member: int, with_cov: bool = True):
+        cap = 3 + 2 * self.nl
+        x = np.empty(cap)
+        P = np.empty((cap, cap), order="F") if with_cov else None
+        n = check(lib.slam_ens_get_state(self.ptr, member, dptr(x), dptr(P) if with_cov else None, cap))
+        return x[:n].copy(), (np.ascontiguousarray(P[:n, :n]) if with_cov else None)
+
+    def launch_count(self) -> int:
+        return int(lib.slam_ens_launch_count(self.ptr))

@@ -1,0 +1,99 @@
+"""GPU parity of the ensemble kernel (one CTA per filter, whole run per launch).
+
+(a) injected noise: member r gets the same numpy PCG64 normals as the numpy literal oracle's
+    run r -> end-of-run trajectories within 1e-6, final state within 1e-6, identical map sizes;
+(b) Philox noise: against the oracle's C twin running the same counter-based generator.
+Members whose filter outgrows the fixed capacity 3 + 2*nl (spurious landmarks after an
+association failure of the algorithm itself) stop with SLAM_ERR_CAPACITY exactly where the twin
+returns -2."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import rel_err
+from oracle import slam_ref as ref
+from twin_ffi import d
+
+pytestmark = pytest.mark.gpu
+TRACK_TOL = 1e-6
+
+
+@pytest.mark.parametrize("nl,nruns", [(10, 6), (35, 6)])
+def test_ensemble_injected_noise_vs_numpy_oracle(course1, nl, nruns):
+    from slamcuda.ensemble import Ensemble
+    lm = ref.make_inputs(nl, 0, 0)[0]
+    ens = Ensemble(course1, lm, nruns)
+    ctrl = np.zeros((nruns, 2, ens.nsteps))
+    runs, obs_all = [], []
+    for r in range(nruns):
+        _lm, c, o = ref.make_inputs(nl, 0, r)
+        runs.append(ref.sim(course1, lm, c, o))
+        ctrl[r] = c[:, :ens.nsteps]
+        obs_all.append(o[:runs[-1]["obs_used"]])
+    assert all(rr["nsteps"] == ens.nsteps and rr["nupdates"] == ens.nupdates for rr in runs)
+    ens.set_noise(ctrl, np.array(obs_all))
+    ens.keep_tracks(True)
+    ens.run()
+    bad = ens.sync()
+    pose, nf, st = ens.results()
+    cap = 3 + 2 * nl
+    worst = 0.0
+    for r, rr in enumerate(runs):
+        if len(rr["x"]) > cap:                      # the oracle's map outgrew the fixed capacity
+            assert st[r] == -3, (r, st[r])
+            continue
+        assert st[r] == 0 and nf[r] == len(rr["x"])
+        tr = ens.track(r)
+        e = float(np.max(np.abs(tr - rr["slam_track"]))) / float(np.max(np.abs(rr["slam_track"])))
+        x, P = ens.state(r)
+        worst = max(worst, e, rel_err(x, rr["x"]), rel_err(P, rr["P"]))
+        assert np.array_equal(pose[r], x[:3])
+    print(f"\n[ensemble nl={nl}] {nruns} members, {bad} stopped early, worst rel err {worst:.3e}")
+    assert worst < TRACK_TOL
+    assert bad == sum(len(rr["x"]) > cap for rr in runs)
+    ens.close()
+
+
+def test_ensemble_philox_vs_twin(course1, twin):
+    from slamcuda.ensemble import Ensemble
+    nl, nruns, seed, run0 = 35, 48, 1234, 7
+    lm = ref.make_inputs(nl, 0, 0)[0]
+    ens = Ensemble(course1, lm, nruns, seed=seed, run0=run0)
+    ens.keep_tracks(True)
+    ens.run()
+    bad = ens.sync()
+    pose, nf, st = ens.results()
+    ms = ens.nsteps
+    wp = np.ascontiguousarray(course1.T).reshape(-1)
+    lmf = np.ascontiguousarray(lm.T).reshape(-1)
+    fp = np.zeros(3 * nruns)
+    trk = np.zeros(3 * ms * nruns)
+    nfin = np.zeros(nruns, dtype=np.int32)
+    tbad = twin.twin_ensemble(d(wp), course1.shape[1], d(lmf), nl, seed, run0, nruns, 2, ms, d(fp), d(trk),
+                              nfin.ctypes.data_as(C.POINTER(C.c_int)), 8)
+    worst, compared = 0.0, 0
+    for r in range(nruns):
+        tt = trk[3 * ms * r:3 * ms * (r + 1)].reshape(ms, 3).T
+        if st[r] != 0:
+            continue
+        compared += 1
+        assert nf[r] == nfin[r]
+        e = float(np.max(np.abs(ens.track(r) - tt))) / float(np.max(np.abs(tt)))
+        worst = max(worst, e)
+    print(f"\n[ensemble philox] {nruns} members: gpu stopped early {bad}, twin {tbad}; compared {compared}, "
+          f"worst track rel err {worst:.3e}")
+    assert bad == tbad and compared >= nruns // 2
+    assert worst < TRACK_TOL
+    ens.close()
+
+
+def test_ensemble_empty_map(course1):
+    """No landmarks: every update step has nz = 0; the run is pure dead reckoning."""
+    from slamcuda.ensemble import Ensemble
+    ens = Ensemble(course1, np.zeros((2, 0)), 3, seed=5)
+    ens.run()
+    assert ens.sync() == 0
+    pose, nf, st = ens.results()
+    assert list(nf) == [3, 3, 3] and np.all(np.isfinite(pose))
+    ens.close()
