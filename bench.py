@@ -225,6 +225,86 @@ def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_ste
         lib.slam_destroy(h)
 
 
+# ----------------------------------------------------------------------------------------
+# ensemble side measurement (BASELINE configs 2 and 4): filter-steps/s
+# ----------------------------------------------------------------------------------------
+ENS_LANDMARKS = 35
+ENS_RUNS_PER_GPU = 8192     # 8 GPUs -> the 65536-run config; config 2 (4096 runs) is reported at N = 1 too
+
+
+def course1_inputs():
+    wp = np.loadtxt(ROOT / "tests" / "golden" / "course1.txt", skiprows=1).T.copy()
+    lm = np.random.Generator(np.random.PCG64(0)).integers(5, 96, size=(2, ENS_LANDMARKS)).astype(float)
+    return wp, lm
+
+
+def gpu_ensemble(n_runs: int, rank: int, world: int, device: int, reps: int = 3):
+    """n_runs members on this rank (run ids rank*n_runs ..), whole course per launch."""
+    import torch
+    from slamcuda._ffi import lib
+    from slamcuda.ensemble import Ensemble
+    wp, lm = course1_inputs()
+    ens = Ensemble(wp, lm, n_runs, seed=SEED, run0=rank * n_runs, device=device)
+    try:
+        stream = torch.cuda.ExternalStream(lib.slam_ens_stream(ens.ptr), device=device)
+        ens.run()
+        bad = ens.sync()
+        times = []
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if world > 1:
+                import torch.distributed as dist
+                dist.barrier()
+            torch.cuda.synchronize(device)
+            e0.record(stream)
+            ens.run()
+            e1.record(stream)
+            ens.sync()
+            times.append(e0.elapsed_time(e1))
+        # end to end: launch + wait + final poses / status back on the host
+        t0 = time.perf_counter()
+        ens.run()
+        ens.sync()
+        pose, nf, st = ens.results()
+        e2e_ms = (time.perf_counter() - t0) * 1e3
+        ms = sorted(times)[len(times) // 2]
+        if world > 1:
+            import torch.distributed as dist
+            t = torch.tensor([ms, e2e_ms], device=f"cuda:{device}", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms, e2e_ms = (float(v) for v in t.cpu())
+        total = n_runs * world
+        return {"workload": f"{total} independent course1 runs ({ENS_LANDMARKS} landmarks, 2 laps, {ens.nsteps} steps, "
+                            f"{ens.nupdates} observation steps each), {n_runs} per GPU, one CTA per filter, "
+                            f"Philox noise keyed by (seed, run)",
+                "value": total * ens.nsteps / (ms * 1e-3), "unit": "filter-steps/s", "ms_per_launch": ms,
+                "e2e": total * ens.nsteps / (e2e_ms * 1e-3), "runs": total, "steps_per_run": ens.nsteps,
+                "stopped_early_on_rank0": int(bad), "gpu_launches_per_run_batch": 1}
+    finally:
+        ens.close()
+
+
+def cpu_ensemble_baseline(n_runs: int = 64):
+    """The oracle's C twin (plain C, -O2 -ffp-contract=off, OpenMP over runs) on the host cores."""
+    import ctypes
+    lib = ctypes.CDLL(str(ROOT / "oracle" / "libslamtwin.so"))
+    dp = ctypes.POINTER(ctypes.c_double)
+    wp, lm = course1_inputs()
+    wpf = np.ascontiguousarray(wp.T).reshape(-1)
+    lmf = np.ascontiguousarray(lm.T).reshape(-1)
+    fp = np.zeros(3 * n_runs)
+    cores = os.cpu_count() or 1
+    lib.twin_ensemble.restype = ctypes.c_int
+    lib.twin_ensemble.argtypes = [dp, ctypes.c_int, dp, ctypes.c_int, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_int,
+                                  ctypes.c_int, ctypes.c_int, dp, dp, ctypes.POINTER(ctypes.c_int), ctypes.c_int]
+    t0 = time.perf_counter()
+    lib.twin_ensemble(wpf.ctypes.data_as(dp), wp.shape[1], lmf.ctypes.data_as(dp), ENS_LANDMARKS, SEED, 0, n_runs, 2,
+                      10000, fp.ctypes.data_as(dp), None, None, cores)
+    sec = time.perf_counter() - t0
+    return {"value": n_runs * 2802 / sec, "unit": "filter-steps/s", "cores": cores, "kind": "port",
+            "sample": f"oracle/slam_twin.c twin_ensemble, {n_runs} runs over {cores} OpenMP threads, {sec:.2f} s"}
+
+
 def gpu_update_sharded(n_landmarks: int, m: int, steps: int, warmup: int, e2e_steps: int, rank: int, world: int,
                        device: int):
     """One filter, P row-block-sharded over `world` ranks (one process per GPU)."""
@@ -387,6 +467,10 @@ def main():
                 "e2e": 1e3 / r10["e2e_ms_per_step"], "k6_ms": r10["k6_ms"],
                 "k6_gbs": b10 / (r10["k6_ms"] * 1e-3) / 1e9, "k6_frac": b10 / (r10["k6_ms"] * 1e-3) / 1e9 / peak,
                 "associate_ms": r10["assoc_ms"]}
+            extras["ensemble"] = gpu_ensemble(ENS_RUNS_PER_GPU, 0, 1, 0)
+            extras["ensemble_4096"] = gpu_ensemble(4096, 0, 1, 0)
+            if not args.no_cpu:
+                extras["ensemble"]["cpu_baseline"] = cpu_ensemble_baseline()
     else:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
@@ -396,6 +480,8 @@ def main():
         clocks = sampler.stop()
         ms = r["ms_per_step"]
         alg_bytes = 8.0 * n * (n + 1) / world
+        if not args.no_extras:
+            extras["ensemble"] = gpu_ensemble(ENS_RUNS_PER_GPU, rank, world, local_rank)
 
     if rank != 0:
         return
