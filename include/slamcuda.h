@@ -81,6 +81,15 @@ int slam_n(slam_t *h);
  * must not pull all of P (resident mode). */
 int slam_get_cov_block(slam_t *h, int i0, int ni, int j0, int nj, double *out, int ldo);
 
+/* compute_landmark_ellipses -- src/common.jl:236-262 (with ellipse, :236-244), computed on the
+ * device from the 2x2 diagonal blocks only: out is (2*Nf) x (nsegs+1) column-major with leading
+ * dimension ldo >= 2*Nf; rows 2i-1:2i hold nsigma*sqrtm(P_ii)*[cos(phi)'; sin(phi)'] .+ x_i for
+ * phi = 0:2pi/nsegs:2pi.  The reference uses nsigma = 2, nsegs = 12 (:248-249). */
+int slam_compute_landmark_ellipses(slam_t *h, double nsigma, int nsegs, double *out, int ldo);
+/* The vehicle's position ellipse, ellipse(x[1:2], P[1:2,1:2], nsigma, nsegs) as drawn by
+ * sim/gr-draw.jl:112-117: out is 2 x (nsegs+1) column-major. */
+int slam_vehicle_ellipse(slam_t *h, double nsigma, int nsegs, double *out);
+
 /* predict -- src/ekf.jl:8-43.  g, v = vehicle.measured_gamma / measured_speed (:14-15),
  * wheelbase = vehicle.wheelbase (:16), Q 2x2 control covariance, dt timestep. In place. */
 int slam_predict(slam_t *h, double g, double v, double wheelbase, const double Q[4], double dt);

@@ -272,6 +272,28 @@ def associate(x, P, z, R, gate1: float, gate2: float, margins: list | None = Non
 # --------------------------------------------------------------------------------------
 # sim/sim-utils.jl and sim/ekfslam-sim.jl -- headless loop with injected noise
 # --------------------------------------------------------------------------------------
+def ellipse(x, P, nsigma, nsegs):
+    """src/common.jl:236-244 -- nsigma*sqrtm(P)*[cos(phi)'; sin(phi)'] .+ x[1:2],
+    phi = 0:2*pi/nsegs:2*pi (nsegs + 1 points).  sqrtm of the symmetric 2 x 2 through its
+    eigen-decomposition, as Julia's sqrtm does for a symmetric argument."""
+    phi = np.arange(nsegs + 1) * (2 * PI / nsegs)
+    A = np.asarray(P, dtype=float)
+    w, V = np.linalg.eigh((A + A.T) * 0.5)
+    sq = (V * np.sqrt(w)) @ V.T
+    return nsigma * sq @ np.vstack([np.cos(phi), np.sin(phi)]) + np.asarray(x, dtype=float)[0:2].reshape(2, 1)
+
+
+def compute_landmark_ellipses(x, P):
+    """src/common.jl:247-262 -- 2nf x (nsegs+1); rows 2i-1:2i are landmark i's contour."""
+    nsigma, nsegs = 2, 12
+    nf = (len(x) - 3) // 2
+    out = np.zeros((2 * nf, nsegs + 1))
+    for i in range(1, nf + 1):
+        j0 = 2 * i + 1          # 0-based start of (2i+2):(2i+3)
+        out[2 * i - 2:2 * i, :] = ellipse(x[j0:j0 + 2], P[j0:j0 + 2, j0:j0 + 2], nsigma, nsegs)
+    return out
+
+
 def nearby_landmark_indices(pose, lm, rmax):
     """sim/sim-utils.jl:12-28 (returns 0-based indices)."""
     phi = pose[2]

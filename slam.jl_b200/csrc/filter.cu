@@ -870,6 +870,69 @@ extern "C" int slam_add_features(slam_t *h, const double *zn, int k, const doubl
 }
 
 // ---------------------------------------------------------------------------------------
+// State export for front ends: compute_landmark_ellipses / ellipse,
+// src/common.jl:236-262 -- nsigma*sqrtm(P_jj)*[cos(phi)'; sin(phi)'] .+ x_j with
+// phi = 0:2pi/nsegs:2pi, per landmark.  Only the 2x2 diagonal blocks are read (24 B per
+// landmark) instead of the whole P the reference's monitor pulls (sim/run-ekfsim.jl:22).
+// sqrtm of a symmetric positive-definite 2x2 in closed form: (A + sqrt(det) I) / sqrt(tr + 2 sqrt(det)).
+// Block 0 is the vehicle (x[1:2], P[1:2,1:2], sim/gr-draw.jl:112-117), block b >= 1 landmark b.
+// ---------------------------------------------------------------------------------------
+__global__ void k_ellipses(const double *__restrict__ x, const double *__restrict__ P, size_t ld, int b0, int nb,
+                           double nsigma, int nsegs, double *__restrict__ out, int ldo) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nb) return;
+    const int blk = b0 + b;
+    const int r = blk == 0 ? 0 : 3 + 2 * (blk - 1);
+    const double a = P[(size_t)r + (size_t)r * ld], c = P[(size_t)r + (size_t)(r + 1) * ld],
+                 d = P[(size_t)(r + 1) + (size_t)(r + 1) * ld];
+    const double s = sqrt(a * d - c * c);
+    const double t = sqrt(a + d + 2.0 * s);
+    const double m00 = (a + s) / t, m01 = c / t, m11 = (d + s) / t;
+    const double cx = x[r], cy = x[r + 1];
+    const double step = 2.0 * SLAM_PI / nsegs;
+    for (int p = 0; p <= nsegs; p++) {
+        const double ph = p * step;
+        const double cp = cos(ph), sp = sin(ph);
+        out[(size_t)(2 * b) + (size_t)p * ldo] = nsigma * (m00 * cp + m01 * sp) + cx;
+        out[(size_t)(2 * b + 1) + (size_t)p * ldo] = nsigma * (m01 * cp + m11 * sp) + cy;
+    }
+}
+
+static int ellipses_common(slam_t *h, int b0, int nb, double nsigma, int nsegs, double *out, int ldo) {
+    if (nb == 0) return SLAM_OK;
+    const size_t need = (size_t)2 * nb * (nsegs + 1);
+    if (need > h->block_cap) {
+        cudaFree(h->d_block);
+        h->d_block = nullptr;
+        h->block_cap = 0;
+        CUDA_TRY(cudaMalloc(&h->d_block, sizeof(double) * need));
+        h->block_cap = need;
+    }
+    k_ellipses<<<(nb + 127) / 128, 128, 0, h->stream>>>(h->d_x, h->d_P, h->ld, b0, nb, nsigma, nsegs, h->d_block,
+                                                        2 * nb);
+    h->launches++;
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpy2DAsync(out, sizeof(double) * (size_t)ldo, h->d_block, sizeof(double) * 2 * nb,
+                               sizeof(double) * 2 * nb, nsegs + 1, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return SLAM_OK;
+}
+
+extern "C" int slam_compute_landmark_ellipses(slam_t *h, double nsigma, int nsegs, double *out, int ldo) {
+    H_CHECK(h);
+    const int nf = (h->n - 3) / 2;
+    ARG_CHECK(nsegs >= 1 && (nf == 0 || out != nullptr), "bad argument");
+    ARG_CHECK(ldo >= 2 * nf, "ldo < 2*nf");
+    return ellipses_common(h, 1, nf, nsigma, nsegs, out, ldo);
+}
+
+extern "C" int slam_vehicle_ellipse(slam_t *h, double nsigma, int nsegs, double *out) {
+    H_CHECK(h);
+    ARG_CHECK(nsegs >= 1 && out != nullptr, "bad argument");
+    return ellipses_common(h, 0, 1, nsigma, nsegs, out, 2);
+}
+
+// ---------------------------------------------------------------------------------------
 // synthetic large-map state (synth.cu)
 // ---------------------------------------------------------------------------------------
 extern "C" int slam_synth_state(slam_t *h, int n_landmarks, double side, uint64_t seed) {

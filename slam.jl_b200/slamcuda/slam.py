@@ -161,6 +161,17 @@ class _Handle:
         check(lib.slam_predict_observation(self.ptr, int(idf), dptr(zp), dptr(H)))
         return zp, np.ascontiguousarray(H)
 
+    def landmark_ellipses(self, nsigma=2.0, nsegs=12):
+        nf = (self.n - 3) // 2
+        out = np.zeros((2 * nf, nsegs + 1), order="F")
+        check(lib.slam_compute_landmark_ellipses(self.ptr, float(nsigma), int(nsegs), dptr(out), max(2 * nf, 1)))
+        return np.ascontiguousarray(out)
+
+    def vehicle_ellipse(self, nsigma=2.0, nsegs=12):
+        out = np.zeros((2, nsegs + 1), order="F")
+        check(lib.slam_vehicle_ellipse(self.ptr, float(nsigma), int(nsegs), dptr(out)))
+        return np.ascontiguousarray(out)
+
     def sync(self):
         check(lib.slam_sync(self.ptr))
 
@@ -283,3 +294,26 @@ def compute_association(x, P, z, R, idf: int):
     h = _scratch_handle(len(x))
     h.set_state(x, P)
     return h.compute_association(z, R, idf)
+
+
+def compute_landmark_ellipses(x, P=None):
+    """src/common.jl:247-262 -> 2nf x 13 contour points (nsigma = 2, nsegs = 12).  Accepts
+    (x, P) arrays like the reference, or a state object (resident states read only the 2 x 2
+    diagonal blocks on the device)."""
+    if isinstance(x, SlamState):
+        return x._upload().landmark_ellipses()
+    x = np.asarray(x, dtype=np.float64).reshape(-1)
+    h = _scratch_handle(len(x))
+    h.set_state(x, P)
+    return h.landmark_ellipses()
+
+
+def ellipse(x, P, nsigma, nsegs):
+    """src/common.jl:236-244 for the vehicle block: x[1:2], P[1:2,1:2] -> 2 x (nsegs+1)."""
+    xs = np.zeros(3)
+    xs[:2] = np.asarray(x, dtype=np.float64).reshape(-1)[:2]
+    Ps = np.zeros((3, 3))
+    Ps[:2, :2] = np.asarray(P, dtype=np.float64)[:2, :2]
+    h = _scratch_handle(3)
+    h.set_state(xs, Ps)
+    return h.vehicle_ellipse(nsigma, nsegs)

@@ -57,3 +57,23 @@ def test_host_mpi_to_pi():
     assert slamcuda.mpi_to_pi(3.5) == 3.5 - 2 * math.pi
     assert slamcuda.mpi_to_pi(-3.5) == -3.5 + 2 * math.pi
     assert slamcuda.mpi_to_pi(1.0) == 1.0
+
+
+def test_julia_wrapper_matches_header():
+    """julia/ekf-cuda.jl cannot be executed here (no Julia): check that every ccall names a symbol
+    the header declares and passes as many arguments as the C prototype has."""
+    hdr = (ROOT / "include" / "slamcuda.h").read_text()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    protos = {}
+    for m in re.finditer(r"\b(slam_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", hdr, flags=re.S):
+        args = m.group(2).strip()
+        protos[m.group(1)] = 0 if args in ("", "void") else args.count(",") + 1
+    jl = (ROOT / "julia" / "ekf-cuda.jl").read_text()
+    calls = re.findall(r"ccall\(\(:(slam_[a-z0-9_]+), libslamcuda\),\s*\w+,\s*\(([^)]*)\)", jl, flags=re.S)
+    assert len(calls) >= 12
+    for name, argt in calls:
+        assert name in protos, f"{name} is not declared in include/slamcuda.h"
+        n = len([a for a in argt.split(",") if a.strip()])
+        assert n == protos[name], f"{name}: ccall passes {n} arguments, the header declares {protos[name]}"
+    for f in ("predict", "associate", "update", "add_features", "compute_association"):
+        assert re.search(rf"^function {f}\(", jl, flags=re.M), f

@@ -251,3 +251,23 @@ def test_associate_large_parity(sc, twin):
     assert np.array_equal(idf.reshape(-1), idf_o)
     assert np.array_equal(zf, zf_o) and np.array_equal(zn, zn_o)
     assert len(idf_o) >= 10
+
+
+@pytest.mark.parametrize("nf", [0, 1, 35, 700])
+def test_landmark_ellipses(sc, nf):
+    """compute_landmark_ellipses / ellipse (src/common.jl:236-262) from the 2x2 diagonal blocks on
+    the device vs the oracle's eigen-decomposition sqrtm; FP64, 1e-9 relative."""
+    rng = np.random.default_rng(5 + nf)
+    x, P = _random_state(rng, nf)
+    ell_o = ref.compute_landmark_ellipses(x, P)
+    ell = sc.compute_landmark_ellipses(x, P)
+    assert ell.shape == (2 * nf, 13)
+    if nf:
+        assert rel_err(ell, ell_o) < STEP_TOL
+    veh_o = ref.ellipse(x[0:2], P[0:2, 0:2], 2, 12)
+    veh = sc.ellipse(x[0:2], P[0:2, 0:2], 2, 12)
+    assert rel_err(veh, veh_o) < STEP_TOL
+    # resident state: same numbers without pulling P
+    st = sc.DeviceEKFSlamState(x, P, n_max=len(x))
+    assert np.array_equal(sc.compute_landmark_ellipses(st), ell)
+    st.h.close()
