@@ -159,13 +159,26 @@ int slam_ens_create(int device, const double *waypoints, int nwp, const double *
                     int nl, int nlaps, uint64_t seed, uint32_t run0, int n_runs,
                     slam_ens_t **out);
 int slam_ens_destroy(slam_ens_t *e);
-/* Steps of one run and number of observation steps (2801 / 311 for 2 laps of course1). */
+/* Member capacity.  The reference's state grows without bound (hcat / vcat, src/ekf.jl:108-109);
+ * a member holds 3 + 2*(nl + extra) states: `extra` (default 5) leaves room for the spurious
+ * landmarks the algorithm itself creates when an observation of a mapped landmark fails both gates
+ * (src/data-association.jl:45-47).  A member that outgrows it stops with SLAM_ERR_CAPACITY in
+ * status[].  Call before slam_ens_run / slam_ens_keep_tracks results are read. */
+int slam_ens_set_extra_landmarks(slam_ens_t *e, int extra);
+/* 3 + 2*(nl + extra); negative on error. */
+int slam_ens_capacity(slam_ens_t *e);
+/* Threads per member CTA: 64, 128 (default) or 256. */
+int slam_ens_set_threads(slam_ens_t *e, int threads);
+/* Steps of one run and number of observation steps (2802 / 311 for 2 laps of course1). */
 int slam_ens_steps(slam_ens_t *e, int *nsteps, int *nupdates);
 /* Runs every member from its initial state to the end of the course in one launch.
  * Asynchronous; slam_ens_sync() waits and returns the number of failed members (< 0 on
  * CUDA error). */
 int slam_ens_run(slam_ens_t *e);
 int slam_ens_sync(slam_ens_t *e);
+/* Filter-steps actually completed by the last run: *total over all members (a member that stopped
+ * early counts only the steps it ran) and per_member[n_runs]; either may be NULL. */
+int slam_ens_steps_done(slam_ens_t *e, long long *total, int *per_member);
 /* Results: final_pose 3 x n_runs; n_final[n_runs] = final state length per member;
  * status[n_runs] (0 ok, SLAM_ERR_*).  Any pointer may be NULL. */
 int slam_ens_get_results(slam_ens_t *e, double *final_pose, int *n_final, int *status);
@@ -173,7 +186,7 @@ int slam_ens_get_results(slam_ens_t *e, double *final_pose, int *n_final, int *s
  * been enabled before the run with slam_ens_keep_tracks(e, 1). */
 int slam_ens_keep_tracks(slam_ens_t *e, int on);
 int slam_ens_get_track(slam_ens_t *e, int member, double *track);
-/* Final x (n_final) and P (n_final^2, ldp) of one member. */
+/* Final x (n_final) and P (n_final^2, ldp, full symmetric) of one member; returns n_final. */
 int slam_ens_get_state(slam_ens_t *e, int member, double *x, double *P, int ldp);
 /* Host-supplied noise instead of Philox (parity runs): ctrl 2 x nsteps per member,
  * obs: pool of `obs_per_member` normals per member consumed in draw order. */

@@ -367,10 +367,10 @@ static void steer(veh_t *v, const double *wp, int nwp, double d_min, double dt,
  * Outputs (any may be NULL): true_track / slam_track 3 x max_steps col-major; x_out (3+2nl),
  * P_out ((3+2nl)^2 col-major, ld = 3+2nl); counts[4] = {nsteps, nupdates, n_final, obs_used};
  * *min_margin = smallest association margin of the run.  Returns 0, -1 not PD, -2 overflow. */
-int twin_sim(const double *wp, int nwp, const double *lm, int nl, const double *ctrl_noise,
-             const double *obs_noise, int nobs, uint64_t seed, uint32_t run, int nlaps,
-             int max_steps, double *true_track, double *slam_track, double *x_out, double *P_out,
-             int *counts, double *min_margin) {
+int twin_sim_cap(const double *wp, int nwp, const double *lm, int nl, const double *ctrl_noise,
+                 const double *obs_noise, int nobs, uint64_t seed, uint32_t run, int nlaps,
+                 int max_steps, double *true_track, double *slam_track, double *x_out, double *P_out,
+                 int *counts, double *min_margin, int extra) {
     const double wheelbase = 4.0, max_gamma = 60 * M_PI / 180, steer_rate = 60 * M_PI / 180;
     const double sensor_range = 30.0, target_speed = 8.0, d_min = 1.0;
     const double sigma_speed = 0.5, sigma_steer = 3.0 * M_PI / 180;
@@ -378,7 +378,10 @@ int twin_sim(const double *wp, int nwp, const double *lm, int nl, const double *
     const double Q[4] = {sigma_speed * sigma_speed, 0, 0, sigma_steer * sigma_steer};
     const double R[4] = {sigmaR * sigmaR, 0, 0, sigmaB * sigmaB};
     const double dt = 0.025, dt_obs = 8 * dt;
-    int ld = 3 + 2 * nl, n = 3, rc = 0;
+    /* the reference's state simply grows (hcat/vcat, src/ekf.jl:108-109); here the capacity is
+     * fixed at 3 + 2*(nl + extra): `extra` leaves room for spurious landmarks (an observation of a
+     * mapped landmark that fails both gates becomes a new one, src/data-association.jl:45-47) */
+    int ld = 3 + 2 * (nl + extra), n = 3, rc = 0;
     double *x = calloc(ld, sizeof(double));
     double *P = calloc((size_t)ld * ld, sizeof(double));
     double *z = malloc(sizeof(double) * 2 * (nl + 1)), *zf = malloc(sizeof(double) * 2 * (nl + 1));
@@ -445,26 +448,42 @@ int twin_sim(const double *wp, int nwp, const double *lm, int nl, const double *
     return rc;
 }
 
+/* capacity 3 + 2*nl (no head-room): the original entry point, x_out / P_out sized by that */
+int twin_sim(const double *wp, int nwp, const double *lm, int nl, const double *ctrl_noise,
+             const double *obs_noise, int nobs, uint64_t seed, uint32_t run, int nlaps,
+             int max_steps, double *true_track, double *slam_track, double *x_out, double *P_out,
+             int *counts, double *min_margin) {
+    return twin_sim_cap(wp, nwp, lm, nl, ctrl_noise, obs_noise, nobs, seed, run, nlaps, max_steps,
+                        true_track, slam_track, x_out, P_out, counts, min_margin, 0);
+}
+
 /* Ensemble on the host cores: runs [run0, run0+nruns) with Philox noise, one run per OpenMP
  * thread.  final_pose: 3 x nruns; slam_tracks (may be NULL): 3 x max_steps x nruns;
  * n_final (may be NULL): nruns.  Returns the number of failed runs. */
-int twin_ensemble(const double *wp, int nwp, const double *lm, int nl, uint64_t seed,
-                  uint32_t run0, int nruns, int nlaps, int max_steps, double *final_pose,
-                  double *slam_tracks, int *n_final, int nthreads) {
+int twin_ensemble_cap(const double *wp, int nwp, const double *lm, int nl, uint64_t seed,
+                      uint32_t run0, int nruns, int nlaps, int max_steps, double *final_pose,
+                      double *slam_tracks, int *n_final, int nthreads, int extra) {
     int bad = 0;
 #ifdef _OPENMP
 #pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads) reduction(+ : bad)
 #endif
     for (int r = 0; r < nruns; r++) {
-        double *xo = malloc(sizeof(double) * (3 + 2 * nl));
+        double *xo = malloc(sizeof(double) * (3 + 2 * (nl + extra)));
         int counts[4];
         double *trk = slam_tracks ? slam_tracks + (size_t)3 * max_steps * r : NULL;
-        int rc = twin_sim(wp, nwp, lm, nl, NULL, NULL, 0, seed, run0 + r, nlaps, max_steps, NULL,
-                          trk, xo, NULL, counts, NULL);
+        int rc = twin_sim_cap(wp, nwp, lm, nl, NULL, NULL, 0, seed, run0 + r, nlaps, max_steps, NULL,
+                              trk, xo, NULL, counts, NULL, extra);
         if (rc != 0) bad++;
         memcpy(final_pose + 3 * r, xo, 3 * sizeof(double));
         if (n_final) n_final[r] = counts[2];
         free(xo);
     }
     return bad;
+}
+
+int twin_ensemble(const double *wp, int nwp, const double *lm, int nl, uint64_t seed,
+                  uint32_t run0, int nruns, int nlaps, int max_steps, double *final_pose,
+                  double *slam_tracks, int *n_final, int nthreads) {
+    return twin_ensemble_cap(wp, nwp, lm, nl, seed, run0, nruns, nlaps, max_steps, final_pose,
+                             slam_tracks, n_final, nthreads, 0);
 }

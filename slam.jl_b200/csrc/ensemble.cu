@@ -7,8 +7,11 @@
 // They are computed once on the host (steer!, step_vehicle!, nearby_landmark_indices,
 // get_observations; src/common.jl:172-230, sim/sim-utils.jl:12-28,53-66) and uploaded as tables.
 // Each member then runs predict / associate / update / add_features for all steps with its
-// state (x, full symmetric P, update workspace) resident in shared memory; only the noise
-// (Philox4x32-10 keyed by (seed, run), or host-supplied arrays) and the optional track cross HBM.
+// state (x, the packed upper triangle of P, update workspace) resident in shared memory; only the
+// noise (Philox4x32-10 keyed by (seed, run), or host-supplied arrays) and the optional track cross
+// HBM.  The reference's state grows without bound (hcat / vcat, src/ekf.jl:108-109); a member's
+// capacity is 3 + 2*(landmarks + extra): `extra` leaves room for the spurious landmarks the
+// algorithm itself creates when an observation fails both gates (src/data-association.jl:45-47).
 //
 // The device functions follow the operation order of the oracle's plain-C twin; compiled with
 // -fmad=false, so the only differences from the twin are the device libm's sin/cos/atan2/log.
@@ -35,6 +38,7 @@ constexpr double SIGMA_B = 1.0 * SLAM_PI / 180;
 constexpr double DT = 0.025;
 constexpr double DT_OBS = 8 * DT;
 constexpr double GATE1 = 4.0, GATE2 = 25.0;
+constexpr int ENS_DEFAULT_EXTRA = 5;   // spare landmarks per member beyond the true map
 constexpr int MAX_STEPS = 10000;   // the reference's track buffers (sim/ekfslam-sim.jl:24-25)
 
 double sgn(double a) { return (double)(a > 0) - (double)(a < 0); }
@@ -46,10 +50,11 @@ struct TruthTables {
     std::vector<int> obs_start;      // per observation step: offset into z_true (nupd + 1 entries)
     std::vector<double> z_true;      // 2 x total noise-free observations
     std::vector<double> true_track;  // 3 x nsteps
+    std::vector<int> blocks;         // per block {first step, one-past-last step, observation index or -1}
 };
 
 // Noise-free half of sim! (sleep, monitor and the filter calls removed).
-int build_truth(const double *wp, int nwp, const double *lm, int nl, int nlaps, TruthTables &t) {
+int build_truth(const double *wp, int nwp, const double *lm, int nl, int nlaps, int max_block, TruthTables &t) {
     double pose[3] = {wp[0], wp[1], atan2(wp[3] - wp[1], wp[2] - wp[0])};   // initial_pose, src/common.jl:93-96
     double g = 0.0;
     int iwp = 1;
@@ -115,6 +120,17 @@ int build_truth(const double *wp, int nwp, const double *lm, int nl, int nlaps, 
         t.nsteps++;
     }
     t.obs_start.push_back((int)t.z_true.size() / 2);
+    // blocks of consecutive steps ending with an observation step, at most max_block steps each
+    int s0 = 0;
+    for (int s = 0; s < t.nsteps; s++) {
+        const bool last = s + 1 == t.nsteps;
+        if (t.upd_at[s] >= 0 || s + 1 - s0 == max_block || last) {
+            t.blocks.push_back(s0);
+            t.blocks.push_back(s + 1);
+            t.blocks.push_back(t.upd_at[s]);
+            s0 = s + 1;
+        }
+    }
     return SLAM_OK;
 }
 
@@ -123,57 +139,81 @@ int build_truth(const double *wp, int nwp, const double *lm, int nl, int nlaps, 
 // ---------------------------------------------------------------------------------------
 // device side
 // ---------------------------------------------------------------------------------------
+// A run is cut into BLOCKS of consecutive steps that end with an observation step (every 9th
+// step for the reference's dt / dt_observe; at most ENS_MAXB steps).  Inside a block the
+// predict steps decouple into three chains that depend on each other only through per-step
+// scalars, so they are evaluated without a CTA barrier per step and with bit-identical results
+// to the step-by-step loop (same operations on the same operands in the same order):
+//   (a) heading  phi_{s+1} = mpi_to_pi(phi_s + v_s*dt*sin(g_s)/wheelbase)   -- needs no sin(g+phi)
+//       then all sin/cos(g_s + phi_s) of the block in parallel lanes, then x, y prefix sums;
+//   (b) the 3x3 pose block  Pvv <- Gv*Pvv*Gv' + Gu*Q*Gu'  on 9 lanes of warp 0 (register chain,
+//       shuffles); the noise term Gu*Q*Gu' of every step is precomputed in parallel lanes;
+//   (c) rows 0..2 of every map column: thread j applies the block's Gv_s one after the other
+//       to its own three values in registers.
+// Multiplications by the literal 1 / 0 entries of Gv (src/ekf.jl:24-26) are exact and are
+// skipped: a + 0*b == a and 1*a == a for finite operands.
 struct EnsArgs {
-    int n_runs, nsteps, nl, ncap, mmax;      // ncap = 3 + 2*nl (the twin's fixed capacity), mmax = max nz
+    int n_runs, nsteps, nl, ncap, mmax, nblocks;
+    int ldw;                   // row stride of the rank-major W1 / PHt workspace (multiple of 4)
+    int npk;                   // doubles of the packed upper triangle, rounded up to 4
+    int wdoubles;              // doubles of the workspace shared by W1 and the association tables
     uint64_t seed;
     uint32_t run0;
-    const double *gamma;       // [nsteps]
-    const int *upd_at;         // [nsteps]
+    const double *gamma;       // [nsteps]   target steering angle after steer!
+    const int *blk;            // [nblocks][3] = {first step, one-past-last step, observation index or -1}
     const int *obs_start;      // [nupd + 1]
-    const double *z_true;      // [2 * total]
+    const double *z_true;      // [2 * total]; the three doubles in front hold the initial pose
     const double *ctrl_noise;  // optional [n_runs][2*nsteps] (speed, steering per step)
     const double *obs_noise;   // optional [n_runs][obs_per_member]
     int obs_per_member;
     double *final_x;           // [n_runs][ncap]
     int *n_final;              // [n_runs]
     int *status;               // [n_runs]
+    int *steps_done;           // [n_runs]
     double *tracks;            // optional [n_runs][3*nsteps]
-    double *final_P;           // optional [n_runs][ncap*ncap]
+    double *final_P;           // optional [n_runs][ncap*ncap], full symmetric
 };
 
-constexpr int ENS_THREADS = 128;
+constexpr int ENS_MAXB = 16;      // steps per block
+constexpr int BS = 24;            // doubles of block scratch per step
+// block scratch slots (per step of the block)
+constexpr int B_V = 0, B_G = 1, B_SG = 2, B_CG = 3, B_TPHI = 4, B_PHI0 = 5, B_VTS = 7, B_VTC = 8, B_N = 9,
+              B_X0 = 18, B_X1 = 19, B_PHI = 20;
+constexpr int LM_STRIDE = 17;     // association table per landmark: zp[2], inv(S)[4], log det, h[10]
 
-struct EnsSmem {   // carve-up of the dynamic shared memory of one member
-    double *x, *P, *PHt, *S, *C, *u, *v, *Hn, *z, *zf, *zn, *nis, *nd, *par;
+struct EnsSmem {
+    double *x, *P, *W, *S, *C, *u, *v, *Hn, *z, *zf, *zn, *bs, *par;
     int *fp, *idf, *cls;
 };
 
-__host__ __device__ inline size_t ens_smem_doubles(int ncap, int mmax, int nl) {
-    const size_t R = 2 * (size_t)mmax;
-    return (size_t)ncap + (size_t)ncap * ncap + (size_t)ncap * R + 2 * R * R + 2 * R + 10 * (size_t)mmax +
-           6 * (size_t)mmax + 2 * (size_t)mmax * (nl > 0 ? nl : 1) + 32;
+__host__ __device__ inline int ens_ru4(int a) { return (a + 3) & ~3; }
+__host__ __device__ inline int ens_wdoubles(int ncap, int mmax) {
+    const int a = 2 * mmax * ens_ru4(ncap), b = ((ncap - 3) / 2) * LM_STRIDE;
+    return ens_ru4(a > b ? a : b);
 }
-__host__ __device__ inline size_t ens_smem_bytes(int ncap, int mmax, int nl) {
-    return ens_smem_doubles(ncap, mmax, nl) * 8 + 3 * (size_t)(mmax > 0 ? mmax : 1) * 4 + 64;
+__host__ __device__ inline size_t ens_smem_bytes(int ncap, int mmax) {
+    const size_t R = 2 * (size_t)mmax;
+    size_t d = ens_ru4(ncap) + ens_ru4(ncap * (ncap + 1) / 2) + ens_wdoubles(ncap, mmax) + 2 * ens_ru4((int)(R * R)) +
+               2 * ens_ru4((int)R) + ens_ru4(10 * mmax) + 3 * ens_ru4(2 * mmax) + ENS_MAXB * BS + 32;
+    return d * 8 + 3 * (size_t)mmax * 4 + 64;
 }
 
-__device__ inline EnsSmem ens_carve(double *base, int ncap, int mmax, int nl) {
+__device__ inline EnsSmem ens_carve(double *base, int ncap, int mmax) {
     EnsSmem s;
-    const size_t R = 2 * (size_t)mmax, nlm = nl > 0 ? nl : 1;
+    const int R = 2 * mmax;
     double *p = base;
-    s.x = p;   p += ncap;
-    s.P = p;   p += (size_t)ncap * ncap;
-    s.PHt = p; p += (size_t)ncap * R;
-    s.S = p;   p += R * R;
-    s.C = p;   p += R * R;
-    s.u = p;   p += R;
-    s.v = p;   p += R;
-    s.Hn = p;  p += 10 * (size_t)mmax;
-    s.z = p;   p += 2 * (size_t)mmax;
-    s.zf = p;  p += 2 * (size_t)mmax;
-    s.zn = p;  p += 2 * (size_t)mmax;
-    s.nis = p; p += (size_t)mmax * nlm;
-    s.nd = p;  p += (size_t)mmax * nlm;
+    s.x = p;   p += ens_ru4(ncap);
+    s.P = p;   p += ens_ru4(ncap * (ncap + 1) / 2);
+    s.W = p;   p += ens_wdoubles(ncap, mmax);
+    s.S = p;   p += ens_ru4(R * R);
+    s.C = p;   p += ens_ru4(R * R);
+    s.u = p;   p += ens_ru4(R);
+    s.v = p;   p += ens_ru4(R);
+    s.Hn = p;  p += ens_ru4(10 * mmax);
+    s.z = p;   p += ens_ru4(2 * mmax);
+    s.zf = p;  p += ens_ru4(2 * mmax);
+    s.zn = p;  p += ens_ru4(2 * mmax);
+    s.bs = p;  p += ENS_MAXB * BS;
     s.par = p; p += 32;
     int *q = reinterpret_cast<int *>(p);
     s.fp = q;  q += mmax;
@@ -182,129 +222,218 @@ __device__ inline EnsSmem ens_carve(double *base, int ncap, int mmax, int nl) {
     return s;
 }
 
-#define EP(i, j) sm.P[(size_t)(i) + (size_t)(j) * ld]
+// packed upper triangle, column-major: P(i, j), i <= j, at j(j+1)/2 + i
+__device__ __forceinline__ int cofs(int j) { return (j * (j + 1)) >> 1; }
+__device__ __forceinline__ double psym(const double *P, int i, int j) {
+    return i <= j ? P[cofs(j) + i] : P[cofs(i) + j];
+}
 
-// predict, src/ekf.jl:8-43, on the member's shared-memory state (both triangles kept, as the
-// reference does with P[4:end,1:3] = P[1:3,4:end]')
-__device__ void ens_predict(const EnsSmem &sm, int n, int ld, double g, double v) {
-    const int tid = threadIdx.x;
-    double *par = sm.par;
-    if (tid == 0) {
-        const double phi = sm.x[2];
-        const double s = sin(g + phi), c = cos(g + phi);
-        const double vts = v * DT * s, vtc = v * DT * c;
-        par[0] = vts;
-        par[1] = vtc;
-        const double Q[4] = {SIGMA_SPEED * SIGMA_SPEED, 0, 0, SIGMA_STEER * SIGMA_STEER};
-        const double Gv[3][3] = {{1, 0, -vts}, {0, 1, vtc}, {0, 0, 1}};
-        const double Gu[3][2] = {{DT * c, -vts}, {DT * s, vtc}, {DT * sin(g) / WHEELBASE, v * DT * cos(g) / WHEELBASE}};
-        double A[3][3], B[3][3], GQ[3][2];
-        for (int i = 0; i < 3; i++)
-            for (int j = 0; j < 3; j++) {
-                double a = 0;
-                for (int k = 0; k < 3; k++) a += Gv[i][k] * EP(k, j);
-                A[i][j] = a;
+// ---- predict for all steps [s0, s0 + len) of a block, src/ekf.jl:8-43 ---------------------
+template <int T>
+__device__ void ens_predict_block(const EnsSmem &sm, const EnsArgs &a, int n, int s0, int len, uint32_t run,
+                                  const double *ctrl) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    double *bs = sm.bs;
+    // add_control_noise!, sim/sim-utils.jl:35-38 (speed first, then steering): one normal per lane
+    if (warp == 0) {
+        if (lane < 2 * len) {
+            const int s = lane >> 1, which = lane & 1, step = s0 + s;
+            const double nrm = ctrl ? ctrl[2 * step + which] : philox_normal(a.seed, run, (uint32_t)which, (uint32_t)step);
+            bs[s * BS + which] = which == 0 ? TARGET_SPEED + nrm * sqrt(SIGMA_SPEED * SIGMA_SPEED)
+                                            : a.gamma[step] + nrm * sqrt(SIGMA_STEER * SIGMA_STEER);
+        }
+        __syncwarp();
+        if (lane < len) {   // the part of the step that does not depend on the state
+            const double v = bs[lane * BS + B_V], g = bs[lane * BS + B_G];
+            const double sg = sin(g), cg = cos(g);
+            bs[lane * BS + B_SG] = sg;
+            bs[lane * BS + B_CG] = cg;
+            bs[lane * BS + B_TPHI] = v * DT * sg / WHEELBASE;
+        }
+        __syncwarp();
+        if (lane == 0) {    // chain (a): heading
+            double phi = sm.x[2];
+            for (int s = 0; s < len; s++) {
+                bs[s * BS + B_PHI0] = phi;
+                phi = mpi_to_pi(phi + bs[s * BS + B_TPHI]);
+                bs[s * BS + B_PHI] = phi;
             }
-        for (int i = 0; i < 3; i++)
-            for (int j = 0; j < 3; j++) {
-                double a = 0;
-                for (int k = 0; k < 3; k++) a += A[i][k] * Gv[j][k];
-                B[i][j] = a;
-            }
-        for (int i = 0; i < 3; i++)
-            for (int j = 0; j < 2; j++) GQ[i][j] = Gu[i][0] * Q[0 + 2 * j] + Gu[i][1] * Q[1 + 2 * j];
-        for (int i = 0; i < 3; i++)
-            for (int j = 0; j < 3; j++) B[i][j] += GQ[i][0] * Gu[j][0] + GQ[i][1] * Gu[j][1];
-        for (int i = 0; i < 3; i++)
-            for (int j = 0; j < 3; j++) EP(i, j) = B[i][j];
-        double x0 = sm.x[0] + vtc, x1 = sm.x[1] + vts;
-        sm.x[2] = mpi_to_pi(phi + v * DT * sin(g) / WHEELBASE);
-        sm.x[0] = x0;
-        sm.x[1] = x1;
+        }
+        __syncwarp();
+        if (lane < len) {
+            double *b = bs + lane * BS;
+            const double v = b[B_V], g = b[B_G], phi = b[B_PHI0];
+            const double s = sin(g + phi), c = cos(g + phi);
+            const double vts = v * DT * s, vtc = v * DT * c;
+            b[B_VTS] = vts;
+            b[B_VTC] = vtc;
+            // Gu*Q*Gu' (src/ekf.jl:27-29,32)
+            const double Q[4] = {SIGMA_SPEED * SIGMA_SPEED, 0, 0, SIGMA_STEER * SIGMA_STEER};
+            const double Gu[3][2] = {{DT * c, -vts}, {DT * s, vtc}, {DT * b[B_SG] / WHEELBASE, v * DT * b[B_CG] / WHEELBASE}};
+            double GQ[3][2];
+#pragma unroll
+            for (int i = 0; i < 3; i++)
+#pragma unroll
+                for (int j = 0; j < 2; j++) GQ[i][j] = Gu[i][0] * Q[0 + 2 * j] + Gu[i][1] * Q[1 + 2 * j];
+#pragma unroll
+            for (int i = 0; i < 3; i++)
+#pragma unroll
+                for (int j = 0; j < 3; j++) b[B_N + 3 * i + j] = GQ[i][0] * Gu[j][0] + GQ[i][1] * Gu[j][1];
+        }
     }
     __syncthreads();
-    const double vts = par[0], vtc = par[1];
-    for (int j = 3 + tid; j < n; j += ENS_THREADS) {
-        double p0 = EP(0, j), p1 = EP(1, j), p2 = EP(2, j);
-        double q0 = p0 + (-vts) * p2;
-        double q1 = p1 + vtc * p2;
-        EP(0, j) = q0; EP(1, j) = q1;
-        EP(j, 0) = q0; EP(j, 1) = q1; EP(j, 2) = p2;
+    if (warp == 0) {
+        // chain (b): lane = 3*i + j holds Pvv[i][j]; the upper triangle is authoritative
+        const int l9 = lane < 9 ? lane : 0;
+        const int i = l9 / 3, j = l9 % 3;
+        double p = psym(sm.P, i, j);
+        // lanes 9 / 10 carry the x (+= vtc) and y (+= vts) prefix sums through the same loop
+        double acc = (lane == 9 || lane == 10) ? sm.x[lane - 9] : 0.0;
+        for (int s = 0; s < len; s++) {
+            const double nvts = -bs[s * BS + B_VTS], vtc = bs[s * BS + B_VTC];
+            if (lane == 9 || lane == 10) {
+                acc = acc + (lane == 9 ? vtc : -nvts);
+                bs[s * BS + B_X0 + lane - 9] = acc;
+            }
+            // A = Gv*Pvv: A[0][c] = P[0][c] + (-vts)*P[2][c], A[1][c] = P[1][c] + vtc*P[2][c], A[2][c] = P[2][c]
+            const double gi = i == 0 ? nvts : vtc;
+            const double pi0 = __shfl_sync(0xffffffffu, p, 3 * i + 0), pi1 = __shfl_sync(0xffffffffu, p, 3 * i + 1),
+                         pi2 = __shfl_sync(0xffffffffu, p, 3 * i + 2);
+            const double p20 = __shfl_sync(0xffffffffu, p, 6), p21 = __shfl_sync(0xffffffffu, p, 7),
+                         p22 = __shfl_sync(0xffffffffu, p, 8);
+            double a0, a1, a2;
+            if (i < 2) {
+                a0 = pi0 + gi * p20;
+                a1 = pi1 + gi * p21;
+                a2 = pi2 + gi * p22;
+            } else {
+                a0 = pi0; a1 = pi1; a2 = pi2;
+            }
+            // B = A*Gv': B[r][0] = A[r][0] + A[r][2]*(-vts), B[r][1] = A[r][1] + A[r][2]*vtc, B[r][2] = A[r][2]
+            double bq = j == 0 ? a0 + a2 * nvts : j == 1 ? a1 + a2 * vtc : a2;
+            bq += bs[s * BS + B_N + l9];
+            // keep the block symmetric the way the upper-authoritative storage reads it
+            const double up = __shfl_sync(0xffffffffu, bq, 3 * j + i);
+            p = i <= j ? bq : up;
+        }
+        if (lane < 9 && i <= j) sm.P[cofs(j) + i] = p;
+        if (lane == 9 || lane == 10) sm.x[lane - 9] = acc;
+        if (lane == 11) sm.x[2] = bs[(len - 1) * BS + B_PHI];
+    } else {
+        // chain (c): rows 0..2 of map column jc
+        for (int jc = 3 + tid - 32; jc < n; jc += T - 32) {
+            double *col = sm.P + cofs(jc);
+            double p0 = col[0], p1 = col[1];
+            const double p2 = col[2];
+            for (int s = 0; s < len; s++) {
+                p0 = p0 + (-bs[s * BS + B_VTS]) * p2;
+                p1 = p1 + bs[s * BS + B_VTC] * p2;
+            }
+            col[0] = p0;
+            col[1] = p1;
+        }
     }
     __syncthreads();
 }
 
-// 2x2 innovation statistics of (observation, landmark), src/data-association.jl:53-63, on the 5x5
-// sub-block of the member's P (same operation order as twin_compute_association)
-__device__ void ens_pair(const EnsSmem &sm, int ld, double z0, double z1, int j, double *nis, double *nd) {
-    double zp[2], h[10];
-    const int f = 3 + 2 * (j - 1);
-    observe_model(sm.x[0], sm.x[1], sm.x[2], sm.x[f], sm.x[f + 1], zp, h);
-    const int c[5] = {0, 1, 2, f, f + 1};
-    const double Hr[2][5] = {{h[0], h[1], h[2], h[6], h[7]}, {h[3], h[4], h[5], h[8], h[9]}};
-    double HP[2][5];
-    for (int a = 0; a < 2; a++)
-        for (int q = 0; q < 5; q++) {
-            double acc = 0;
-            for (int p = 0; p < 5; p++) acc += Hr[a][p] * EP(c[p], c[q]);
-            HP[a][q] = acc;
-        }
-    const double R[4] = {SIGMA_R * SIGMA_R, 0, 0, SIGMA_B * SIGMA_B};
-    double S[4];
-    for (int a = 0; a < 2; a++)
-        for (int b = 0; b < 2; b++) {
-            double acc = 0;
-            for (int q = 0; q < 5; q++) acc += HP[a][q] * Hr[b][q];
-            S[2 * a + b] = acc + R[a + 2 * b];
-        }
-    double v0 = z0 - zp[0];
-    double v1 = mpi_to_pi(z1 - zp[1]);
-    double det = S[0] * S[3] - S[1] * S[2];
-    double i11 = S[3] / det, i12 = -S[1] / det, i21 = -S[2] / det, i22 = S[0] / det;
-    double t0 = i11 * v0 + i12 * v1;
-    double t1 = i21 * v0 + i22 * v1;
-    *nis = v0 * t0 + v1 * t1;
-    *nd = *nis + log(det);
-}
-
-// associate, src/data-association.jl:1-51.  All (observation, landmark) pairs in parallel, then
-// one thread per observation replays the reference's sequential scan over j literally.
-// Returns m (matched) and k (new) through par[8], par[9].
-__device__ void ens_associate(const EnsSmem &sm, int n, int ld, int nz, int nl) {
-    const int tid = threadIdx.x;
+// ---- associate, src/data-association.jl:1-63 ---------------------------------------------
+// Phase A: one thread per landmark builds everything of compute_association that does not
+// depend on the observation (zp, H, S = H*P*H' + R from the 5x5 sub-block, inv(S), log det S);
+// phase B: one warp per observation scores all landmarks and reduces (nd, j) / min nis with
+// shuffles -- strict '<' everywhere, lowest j wins ties, NaN never wins, which is the result of
+// the reference's sequential scan (`outer` is only consulted when no landmark was ever gated).
+// Leaves m, k in par[8], par[9], zf / idf / zn compacted in observation order, and Hn / fp / v
+// of the matched observations ready for update (the same values update recomputes, src/ekf.jl:55-59).
+template <int T>
+__device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int Nf = (n - 3) / 2;
-    const int nlm = nl > 0 ? nl : 1;
-    for (int idx = tid; idx < nz * Nf; idx += ENS_THREADS) {
-        int i = idx / Nf, j = idx % Nf + 1;
-        double nis, nd;
-        ens_pair(sm, ld, sm.z[2 * i], sm.z[2 * i + 1], j, &nis, &nd);
-        sm.nis[(size_t)i * nlm + (j - 1)] = nis;
-        sm.nd[(size_t)i * nlm + (j - 1)] = nd;
+    double *LM = sm.W;
+    const double Rm[4] = {SIGMA_R * SIGMA_R, 0, 0, SIGMA_B * SIGMA_B};
+    for (int jl = tid; jl < Nf; jl += T) {
+        const int f = 3 + 2 * jl;
+        double zp[2], h[10];
+        observe_model(sm.x[0], sm.x[1], sm.x[2], sm.x[f], sm.x[f + 1], zp, h);
+        const int c[5] = {0, 1, 2, f, f + 1};
+        const double Hr[2][5] = {{h[0], h[1], h[2], h[6], h[7]}, {h[3], h[4], h[5], h[8], h[9]}};
+        double P5[5][5];
+#pragma unroll
+        for (int p = 0; p < 5; p++)
+#pragma unroll
+            for (int q = p; q < 5; q++) {
+                const double val = sm.P[cofs(c[q]) + c[p]];
+                P5[p][q] = val;
+                P5[q][p] = val;
+            }
+        double HP[2][5];
+#pragma unroll
+        for (int a = 0; a < 2; a++)
+#pragma unroll
+            for (int q = 0; q < 5; q++) {
+                double acc = 0;
+#pragma unroll
+                for (int p = 0; p < 5; p++) acc += Hr[a][p] * P5[p][q];
+                HP[a][q] = acc;
+            }
+        double S[4];
+#pragma unroll
+        for (int a = 0; a < 2; a++)
+#pragma unroll
+            for (int b = 0; b < 2; b++) {
+                double acc = 0;
+#pragma unroll
+                for (int q = 0; q < 5; q++) acc += HP[a][q] * Hr[b][q];
+                S[2 * a + b] = acc + Rm[a + 2 * b];
+            }
+        const double det = S[0] * S[3] - S[1] * S[2];
+        double *t = LM + jl * LM_STRIDE;
+        t[0] = zp[0];
+        t[1] = zp[1];
+        t[2] = S[3] / det;
+        t[3] = -S[1] / det;
+        t[4] = -S[2] / det;
+        t[5] = S[0] / det;
+        t[6] = log(det);
+#pragma unroll
+        for (int q = 0; q < 10; q++) t[7 + q] = h[q];
     }
     __syncthreads();
-    for (int i = tid; i < nz; i += ENS_THREADS) {
-        int jbest = 0;
+    for (int i = warp; i < nz; i += T / 32) {
+        const double z0 = sm.z[2 * i], z1 = sm.z[2 * i + 1];
         double nbest = INFINITY, outer = INFINITY;
-        for (int j = 1; j <= Nf; j++) {
-            double nis = sm.nis[(size_t)i * nlm + (j - 1)], nd = sm.nd[(size_t)i * nlm + (j - 1)];
-            bool ingate = false;
-            if (nis < GATE1) {
-                if (nd < nbest) ingate = true;
-            }
-            if (ingate) {
+        int jbest = 0;
+        for (int jl = lane; jl < Nf; jl += 32) {
+            const double *t = LM + jl * LM_STRIDE;
+            const double v0 = z0 - t[0];
+            const double v1 = mpi_to_pi(z1 - t[1]);
+            const double t0 = t[2] * v0 + t[3] * v1;
+            const double t1 = t[4] * v0 + t[5] * v1;
+            const double nis = v0 * t0 + v1 * t1;
+            const double nd = nis + t[6];
+            if (nis < GATE1 && nd < nbest) {
                 nbest = nd;
-                jbest = j;
-            } else if (nis < outer) {
-                outer = nis;
+                jbest = jl + 1;
             }
+            if (nis < outer) outer = nis;
         }
-        sm.cls[i] = jbest != 0 ? jbest : (outer > GATE2 ? -1 : 0);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double onb = __shfl_xor_sync(0xffffffffu, nbest, o);
+            const int ojb = __shfl_xor_sync(0xffffffffu, jbest, o);
+            const double oout = __shfl_xor_sync(0xffffffffu, outer, o);
+            if (ojb != 0 && (jbest == 0 || onb < nbest || (onb == nbest && ojb < jbest))) {
+                nbest = onb;
+                jbest = ojb;
+            }
+            if (oout < outer) outer = oout;
+        }
+        if (lane == 0) sm.cls[i] = jbest != 0 ? jbest : (outer > GATE2 ? -1 : 0);
     }
     __syncthreads();
     if (tid == 0) {
         int m = 0, k = 0;
         for (int i = 0; i < nz; i++) {
-            int c = sm.cls[i];
+            const int c = sm.cls[i];
             if (c > 0) {
                 sm.zf[2 * m] = sm.z[2 * i];
                 sm.zf[2 * m + 1] = sm.z[2 * i + 1];
@@ -320,55 +449,65 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int ld, int nz, int nl) 
         sm.par[9] = k;
     }
     __syncthreads();
+    const int m = (int)sm.par[8];
+    if (tid < m) {
+        const int jl = sm.idf[tid] - 1;
+        const double *t = LM + jl * LM_STRIDE;
+        sm.fp[tid] = 3 + 2 * jl;
+        sm.v[2 * tid] = sm.zf[2 * tid] - t[0];
+        sm.v[2 * tid + 1] = mpi_to_pi(sm.zf[2 * tid + 1] - t[1]);
+#pragma unroll
+        for (int q = 0; q < 10; q++) sm.Hn[10 * tid + q] = t[7 + q];
+    }
+    __syncthreads();
 }
 
-// update, src/ekf.jl:46-77, in the operation order of twin_update.  The 2m x 2m innovation
-// Cholesky and the triangular inverse run in ONE warp (lane = column, __syncwarp between the
-// column steps) while the other warps wait at a single barrier.  Returns false if S is not PD.
-__device__ bool ens_update(const EnsSmem &sm, int n, int ld, int m) {
+// ---- update, src/ekf.jl:46-77, in the operation order of the oracle's C twin ---------------
+// PHt / W1 are rank-major (W[k*ldw + i]).  The 2m x 2m Cholesky, the triangular inverse and
+// u = C'v run in ONE warp (lane = column, __syncwarp between the column steps).
+template <int T>
+__device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m) {
     const int tid = threadIdx.x;
     const int R = 2 * m;
     const double Rm[4] = {SIGMA_R * SIGMA_R, 0, 0, SIGMA_B * SIGMA_B};
-    if (tid < m) {
-        double zp[2];
-        const int f = 3 + 2 * (sm.idf[tid] - 1);
-        observe_model(sm.x[0], sm.x[1], sm.x[2], sm.x[f], sm.x[f + 1], zp, sm.Hn + 10 * tid);
-        sm.fp[tid] = f;
-        sm.v[2 * tid] = sm.zf[2 * tid] - zp[0];
-        sm.v[2 * tid + 1] = mpi_to_pi(sm.zf[2 * tid + 1] - zp[1]);
-    }
-    __syncthreads();
-    // PHt = P*H' (five terms per entry, columns 1,2,3,f,f+1)
-    for (int idx = tid; idx < n * m; idx += ENS_THREADS) {
-        const int i = idx % n, o = idx / n;
-        const double *h = sm.Hn + 10 * o;
-        const int f = sm.fp[o];
-        const double p0 = EP(i, 0), p1 = EP(i, 1), p2 = EP(i, 2), p3 = EP(i, f), p4 = EP(i, f + 1);
-        sm.PHt[(size_t)i * R + 2 * o] = p0 * h[0] + p1 * h[1] + p2 * h[2] + p3 * h[6] + p4 * h[7];
-        sm.PHt[(size_t)i * R + 2 * o + 1] = p0 * h[3] + p1 * h[4] + p2 * h[5] + p3 * h[8] + p4 * h[9];
+    double *W = sm.W;
+    // PHt = P*H' (five terms per entry, columns 1,2,3,f,f+1); rows n..ldw-1 are zeroed for K6's tiles
+    for (int idx = tid; idx < ldw * m; idx += T) {
+        const int o = idx / ldw, i = idx - o * ldw;
+        double w0 = 0.0, w1 = 0.0;
+        if (i < n) {
+            const double *h = sm.Hn + 10 * o;
+            const int f = sm.fp[o];
+            const double p0 = psym(sm.P, i, 0), p1 = psym(sm.P, i, 1), p2 = psym(sm.P, i, 2), p3 = psym(sm.P, i, f),
+                         p4 = psym(sm.P, i, f + 1);
+            w0 = p0 * h[0] + p1 * h[1] + p2 * h[2] + p3 * h[6] + p4 * h[7];
+            w1 = p0 * h[3] + p1 * h[4] + p2 * h[5] + p3 * h[8] + p4 * h[9];
+        }
+        W[(2 * o) * ldw + i] = w0;
+        W[(2 * o + 1) * ldw + i] = w1;
     }
     __syncthreads();
     // S = H*PHt + RR
-    for (int idx = tid; idx < m * R; idx += ENS_THREADS) {
-        const int o = idx / R, k = idx % R;
+    for (int idx = tid; idx < m * R; idx += T) {
+        const int o = idx / R, k = idx - o * R;
         const double *h = sm.Hn + 10 * o;
         const int f = sm.fp[o];
-        const double a0 = sm.PHt[k], a1 = sm.PHt[(size_t)R + k], a2 = sm.PHt[(size_t)2 * R + k];
-        const double a3 = sm.PHt[(size_t)f * R + k], a4 = sm.PHt[(size_t)(f + 1) * R + k];
+        const double *wk = W + k * ldw;
+        const double a0 = wk[0], a1 = wk[1], a2 = wk[2], a3 = wk[f], a4 = wk[f + 1];
         double s0 = h[0] * a0 + h[1] * a1 + h[2] * a2 + h[6] * a3 + h[7] * a4;
         double s1 = h[3] * a0 + h[4] * a1 + h[5] * a2 + h[8] * a3 + h[9] * a4;
         if (k == 2 * o) { s0 += Rm[0]; s1 += Rm[1]; }
         if (k == 2 * o + 1) { s0 += Rm[2]; s1 += Rm[3]; }
-        sm.S[(size_t)(2 * o) + (size_t)k * R] = s0;
-        sm.S[(size_t)(2 * o + 1) + (size_t)k * R] = s1;
+        sm.S[(2 * o) + k * R] = s0;
+        sm.S[(2 * o + 1) + k * R] = s1;
     }
     __syncthreads();
-    for (int idx = tid; idx < R * R; idx += ENS_THREADS) {   // S = (S + S')*0.5
+    for (int idx = tid; idx < R * R; idx += T) {   // S = (S + S')*0.5
         const int a = idx % R, b = idx / R;
         if (a < b) {
-            double s = (sm.S[(size_t)a + (size_t)b * R] + sm.S[(size_t)b + (size_t)a * R]) * 0.5;
-            sm.S[(size_t)a + (size_t)b * R] = s;
-            sm.S[(size_t)b + (size_t)a * R] = s;
+            const double s = (sm.S[a + b * R] + sm.S[b + a * R]) * 0.5;
+            sm.S[a + b * R] = s;
+            sm.S[b + a * R] = s;
         }
     }
     __syncthreads();
@@ -376,30 +515,33 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ld, int m) {
         const int lane = tid;
         int fail = 0;
         for (int k = 0; k < R; k++) {
-            double d = sm.S[(size_t)k + (size_t)k * R];
+            const double d = sm.S[k + k * R];
             if (!(d > 0)) { fail = 1; break; }    // uniform: every lane reads the same d
-            double ukk = sqrt(d);
+            const double ukk = sqrt(d);
             __syncwarp();
-            if (lane == 0) sm.S[(size_t)k + (size_t)k * R] = ukk;
-            for (int j = k + 1 + lane; j < R; j += 32) sm.S[(size_t)k + (size_t)j * R] /= ukk;
+            if (lane == 0) sm.S[k + k * R] = ukk;
+            for (int j = k + 1 + lane; j < R; j += 32) {
+                const double ukj = sm.S[k + j * R] / ukk;
+                sm.S[k + j * R] = ukj;
+            }
             __syncwarp();
             for (int j = k + 1 + lane; j < R; j += 32) {
-                const double ukj = sm.S[(size_t)k + (size_t)j * R];
-                for (int i = k + 1; i <= j; i++) sm.S[(size_t)i + (size_t)j * R] -= sm.S[(size_t)k + (size_t)i * R] * ukj;
+                const double ukj = sm.S[k + j * R];
+                for (int i = k + 1; i <= j; i++) sm.S[i + j * R] -= sm.S[k + i * R] * ukj;
             }
             __syncwarp();
         }
         if (lane == 0) sm.par[10] = fail;
         if (!fail) {
             for (int j = lane; j < R; j += 32) {
-                sm.C[(size_t)j + (size_t)j * R] = 1.0 / sm.S[(size_t)j + (size_t)j * R];
+                sm.C[j + j * R] = 1.0 / sm.S[j + j * R];
                 for (int i = j - 1; i >= 0; i--) {
                     double a = 0;
-                    for (int k = i + 1; k <= j; k++) a += sm.S[(size_t)i + (size_t)k * R] * sm.C[(size_t)k + (size_t)j * R];
-                    sm.C[(size_t)i + (size_t)j * R] = -a / sm.S[(size_t)i + (size_t)i * R];
+                    for (int k = i + 1; k <= j; k++) a += sm.S[i + k * R] * sm.C[k + j * R];
+                    sm.C[i + j * R] = -a / sm.S[i + i * R];
                 }
                 double a = 0;
-                for (int l = 0; l <= j; l++) a += sm.C[(size_t)l + (size_t)j * R] * sm.v[l];
+                for (int l = 0; l <= j; l++) a += sm.C[l + j * R] * sm.v[l];
                 sm.u[j] = a;
             }
         }
@@ -407,32 +549,61 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ld, int m) {
     __syncthreads();
     if (sm.par[10] != 0.0) return false;
     // W1 = PHt*C in place (k descending keeps PHt[i, l <= k] intact), x += W1*u
-    for (int i = tid; i < n; i += ENS_THREADS) {
-        double *row = sm.PHt + (size_t)i * R;
+    for (int i = tid; i < n; i += T) {
         for (int k = R - 1; k >= 0; k--) {
             double a = 0;
-            for (int l = 0; l <= k; l++) a += row[l] * sm.C[(size_t)l + (size_t)k * R];
-            row[k] = a;
+            for (int l = 0; l <= k; l++) a += W[l * ldw + i] * sm.C[l + k * R];
+            W[k * ldw + i] = a;
         }
         double dxi = 0;
-        for (int k = 0; k < R; k++) dxi += row[k] * sm.u[k];
+        for (int k = 0; k < R; k++) dxi += W[k * ldw + i] * sm.u[k];
         sm.x[i] += dxi;
     }
     __syncthreads();
-    // P -= W1*W1' over the full matrix (the reference subtracts the full symmetric product)
-    for (int idx = tid; idx < n * n; idx += ENS_THREADS) {
-        const int i = idx % n, j = idx / n;
-        const double *wi = sm.PHt + (size_t)i * R, *wj = sm.PHt + (size_t)j * R;
-        double a = EP(i, j);
-        for (int k = 0; k < R; k++) a = fma(-wi[k], wj[k], a);
-        EP(i, j) = a;
+    // P -= W1*W1' over the packed upper triangle in 4 x 4 register tiles: tile (bi, bj), bi <= bj,
+    // covers rows 4bi.. and columns 4bj..; tiles are numbered column by column so that the lanes
+    // of a warp mostly share bj (W1 column-side loads broadcast) and walk bi (conflict-free).
+    // Each element is the chain a = fma(-W1[i,k], W1[j,k], a), k ascending, as the twin does.
+    const int nb = (n + 3) >> 2;
+    for (int t = tid; t < nb * (nb + 1) / 2; t += T) {
+        int bj = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
+        while (bj * (bj + 1) / 2 > t) bj--;
+        while ((bj + 1) * (bj + 2) / 2 <= t) bj++;
+        const int bi = t - bj * (bj + 1) / 2;
+        const int i0 = 4 * bi, j0 = 4 * bj;
+        double acc[4][4];
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int i = i0 + r, j = j0 + c;
+                acc[c][r] = (i <= j && j < n) ? sm.P[cofs(j) + i] : 0.0;
+            }
+        for (int k = 0; k < R; k++) {
+            const double4 wi = *reinterpret_cast<const double4 *>(W + k * ldw + i0);
+            const double4 wj = *reinterpret_cast<const double4 *>(W + k * ldw + j0);
+            const double wir[4] = {-wi.x, -wi.y, -wi.z, -wi.w};
+            const double wjc[4] = {wj.x, wj.y, wj.z, wj.w};
+#pragma unroll
+            for (int c = 0; c < 4; c++)
+#pragma unroll
+                for (int r = 0; r < 4; r++) acc[c][r] = fma(wir[r], wjc[c], acc[c][r]);
+        }
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int i = i0 + r, j = j0 + c;
+                if (i <= j && j < n) sm.P[cofs(j) + i] = acc[c][r];
+            }
     }
     __syncthreads();
     return true;
 }
 
-// add_features, src/ekf.jl:84-122, in place (the member's capacity is fixed); returns the new n
-__device__ int ens_add_features(const EnsSmem &sm, int n, int ld, int k) {
+// ---- add_features, src/ekf.jl:84-122, in place (the member's capacity is fixed) --------------
+template <int T>
+__device__ int ens_add_features(const EnsSmem &sm, int n, int k) {
     const int tid = threadIdx.x;
     const double phi = sm.x[2];
     const double Rm[4] = {SIGMA_R * SIGMA_R, 0, 0, SIGMA_B * SIGMA_B};
@@ -441,35 +612,30 @@ __device__ int ens_add_features(const EnsSmem &sm, int n, int ld, int k) {
         const double r = sm.zn[2 * q], b = sm.zn[2 * q + 1];
         const double s = sin(phi + b), c = cos(phi + b);
         const double Gv[2][3] = {{1, 0, -r * s}, {0, 1, r * c}};
-        double *GP = sm.par + 16;   // 2 x 3
         if (tid == 0) {
             sm.x[len] = sm.x[0] + r * c;
             sm.x[len + 1] = sm.x[1] + r * s;
             const double Gz[2][2] = {{c, -r * s}, {s, r * c}};
-            double GR[2][2];
+            double GP[2][3], GR[2][2];
             for (int a = 0; a < 2; a++)
                 for (int j = 0; j < 3; j++)
-                    GP[a * 3 + j] = Gv[a][0] * EP(0, j) + Gv[a][1] * EP(1, j) + Gv[a][2] * EP(2, j);
+                    GP[a][j] = Gv[a][0] * psym(sm.P, 0, j) + Gv[a][1] * psym(sm.P, 1, j) + Gv[a][2] * psym(sm.P, 2, j);
             for (int a = 0; a < 2; a++)
                 for (int j = 0; j < 2; j++) GR[a][j] = Gz[a][0] * Rm[0 + 2 * j] + Gz[a][1] * Rm[1 + 2 * j];
             for (int a = 0; a < 2; a++)
-                for (int bb = 0; bb < 2; bb++) {
-                    double t1 = GP[a * 3 + 0] * Gv[bb][0] + GP[a * 3 + 1] * Gv[bb][1] + GP[a * 3 + 2] * Gv[bb][2];
-                    double t2 = GR[a][0] * Gz[bb][0] + GR[a][1] * Gz[bb][1];
-                    EP(len + a, len + bb) = t1 + t2;
+                for (int bb = a; bb < 2; bb++) {
+                    const double t1 = GP[a][0] * Gv[bb][0] + GP[a][1] * Gv[bb][1] + GP[a][2] * Gv[bb][2];
+                    const double t2 = GR[a][0] * Gz[bb][0] + GR[a][1] * Gz[bb][1];
+                    sm.P[cofs(len + bb) + len + a] = t1 + t2;
                 }
             for (int a = 0; a < 2; a++)
-                for (int j = 0; j < 3; j++) {
-                    EP(len + a, j) = GP[a * 3 + j];
-                    EP(j, len + a) = GP[a * 3 + j];
-                }
+                for (int j = 0; j < 3; j++) sm.P[cofs(len + a) + j] = GP[a][j];
         }
-        for (int j = 3 + tid; j < len; j += ENS_THREADS)
-            for (int a = 0; a < 2; a++) {
-                double t = Gv[a][0] * EP(0, j) + Gv[a][1] * EP(1, j) + Gv[a][2] * EP(2, j);
-                EP(len + a, j) = t;
-                EP(j, len + a) = t;
-            }
+        for (int j = 3 + tid; j < len; j += T) {
+            const double c0 = sm.P[cofs(j)], c1 = sm.P[cofs(j) + 1], c2 = sm.P[cofs(j) + 2];
+            for (int a = 0; a < 2; a++)
+                sm.P[cofs(len + a) + j] = Gv[a][0] * c0 + Gv[a][1] * c1 + Gv[a][2] * c2;
+        }
         __syncthreads();
         n += 2;
     }
@@ -477,17 +643,17 @@ __device__ int ens_add_features(const EnsSmem &sm, int n, int ld, int k) {
 }
 
 // One CTA = one member = one whole run of sim!.
-__global__ void __launch_bounds__(ENS_THREADS)
+template <int T>
+__global__ void __launch_bounds__(T)
 k_ensemble(EnsArgs a) {
-    extern __shared__ __align__(16) double ens_smem[];
+    extern __shared__ __align__(32) double ens_smem[];
     const int member = blockIdx.x;
     if (member >= a.n_runs) return;
     const int tid = threadIdx.x;
-    const int ld = a.ncap;
-    const EnsSmem sm = ens_carve(ens_smem, a.ncap, a.mmax, a.nl);
+    const EnsSmem sm = ens_carve(ens_smem, a.ncap, a.mmax);
     const uint32_t run = a.run0 + (uint32_t)member;
-    for (int idx = tid; idx < a.ncap * a.ncap; idx += ENS_THREADS) sm.P[idx] = 0.0;   // zeros(3,3), capacity zeroed
-    for (int idx = tid; idx < a.ncap; idx += ENS_THREADS) sm.x[idx] = 0.0;
+    for (int idx = tid; idx < a.npk; idx += T) sm.P[idx] = 0.0;   // zeros(3,3); spare capacity zeroed
+    for (int idx = tid; idx < a.ncap; idx += T) sm.x[idx] = 0.0;
     __syncthreads();
     int n = 3;
     int status = SLAM_OK;
@@ -498,44 +664,57 @@ k_ensemble(EnsArgs a) {
     // three doubles in front of z_true
     if (tid < 3) sm.x[tid] = a.z_true[-3 + tid];
     __syncthreads();
-    int step = 0;
-    for (; step < a.nsteps; step++) {
-        // add_control_noise!, sim/sim-utils.jl:35-38 (speed first, then steering)
-        const double n0 = ctrl ? ctrl[2 * step] : philox_normal(a.seed, run, 0u, (uint32_t)step);
-        const double n1 = ctrl ? ctrl[2 * step + 1] : philox_normal(a.seed, run, 1u, (uint32_t)step);
-        const double mspeed = TARGET_SPEED + n0 * sqrt(SIGMA_SPEED * SIGMA_SPEED);
-        const double mgamma = a.gamma[step] + n1 * sqrt(SIGMA_STEER * SIGMA_STEER);
-        ens_predict(sm, n, ld, mgamma, mspeed);
-        const int u = a.upd_at[step];
+    int done = 0;
+    for (int b = 0; b < a.nblocks; b++) {
+        const int s0 = a.blk[3 * b], s1 = a.blk[3 * b + 1], u = a.blk[3 * b + 2];
+        const int len = s1 - s0;
+        int nz = 0;
         if (u >= 0) {
-            const int o0 = a.obs_start[u], nz = a.obs_start[u + 1] - o0;
-            const int cursor = 2 * o0;   // draw order: all range noises of the step, then all bearing noises
+            // get_observations, sim/sim-utils.jl:53-75: noise-free table + this member's noise, draw
+            // order = all range noises of the step, then all bearing noises.  Done by the warps that
+            // idle during the predict chains.
+            const int o0 = a.obs_start[u];
+            nz = a.obs_start[u + 1] - o0;
+            const int cursor = 2 * o0;
             if (obsn && cursor + 2 * nz > a.obs_per_member) { status = SLAM_ERR_CAPACITY; break; }
-            for (int c = tid; c < nz; c += ENS_THREADS) {
-                const double e0 = obsn ? obsn[cursor + c] : philox_normal(a.seed, run, 2u, (uint32_t)(cursor + c));
-                const double e1 = obsn ? obsn[cursor + nz + c] : philox_normal(a.seed, run, 2u, (uint32_t)(cursor + nz + c));
-                sm.z[2 * c] = a.z_true[2 * (o0 + c)] + e0 * sqrt(SIGMA_R * SIGMA_R);
-                sm.z[2 * c + 1] = a.z_true[2 * (o0 + c) + 1] + e1 * sqrt(SIGMA_B * SIGMA_B);
+            for (int c = tid - 32; c < 2 * nz; c += T - 32) {
+                if (c < 0) continue;
+                const int ob = c < nz ? c : c - nz, comp = c < nz ? 0 : 1;
+                const double e = obsn ? obsn[cursor + c] : philox_normal(a.seed, run, 2u, (uint32_t)(cursor + c));
+                sm.z[2 * ob + comp] = a.z_true[2 * (o0 + ob) + comp] +
+                                      e * (comp == 0 ? sqrt(SIGMA_R * SIGMA_R) : sqrt(SIGMA_B * SIGMA_B));
             }
-            __syncthreads();
-            ens_associate(sm, n, ld, nz, a.nl);
-            const int m = (int)sm.par[8], k = (int)sm.par[9];
-            if (m > 0 && !ens_update(sm, n, ld, m)) { status = SLAM_ERR_NOT_PD; break; }
-            if (n + 2 * k > a.ncap) { status = SLAM_ERR_CAPACITY; break; }   // as the twin: rc = -2
-            n = ens_add_features(sm, n, ld, k);
         }
-        if (track && tid < 3) track[3 * step + tid] = sm.x[tid];
+        ens_predict_block<T>(sm, a, n, s0, len, run, ctrl);
+        if (nz > 0) {
+            ens_associate<T>(sm, n, nz);
+            const int m = (int)sm.par[8], k = (int)sm.par[9];
+            if (m > 0 && !ens_update<T>(sm, n, a.ldw, m)) { status = SLAM_ERR_NOT_PD; break; }
+            if (n + 2 * k > a.ncap) { status = SLAM_ERR_CAPACITY; break; }
+            n = ens_add_features<T>(sm, n, k);
+        }
+        // slam_track[:, step] = state.x[1:3] (sim/ekfslam-sim.jl:128): after predict for the inner
+        // steps, after update / add_features for the block's last step
+        if (track && tid < 3 * len) {
+            const int s = tid / 3, comp = tid - 3 * s;
+            track[3 * (s0 + s) + comp] = s == len - 1 ? sm.x[comp] : sm.bs[s * BS + B_X0 + comp];
+        }
+        done = s1;
+        __syncthreads();
     }
     __syncthreads();
-    for (int idx = tid; idx < a.ncap; idx += ENS_THREADS) a.final_x[(size_t)member * a.ncap + idx] = sm.x[idx];
-    if (a.final_P)
-        for (int idx = tid; idx < a.ncap * a.ncap; idx += ENS_THREADS)
-            a.final_P[(size_t)member * a.ncap * a.ncap + idx] = sm.P[idx];
+    for (int idx = tid; idx < a.ncap; idx += T) a.final_x[(size_t)member * a.ncap + idx] = sm.x[idx];
+    if (a.final_P)   // exported as the full symmetric matrix
+        for (int idx = tid; idx < a.ncap * a.ncap; idx += T) {
+            const int i = idx % a.ncap, j = idx / a.ncap;
+            a.final_P[(size_t)member * a.ncap * a.ncap + idx] = psym(sm.P, i, j);
+        }
     if (tid == 0) {
         a.n_final[member] = n;
         a.status[member] = status;
-        if (track)   // steps not run (failed member) are marked NaN
-            for (int s2 = step; s2 < a.nsteps; s2++) track[3 * s2] = track[3 * s2 + 1] = track[3 * s2 + 2] = nan("");
+        a.steps_done[member] = done;
+        if (track)   // steps not run (stopped member) are marked NaN
+            for (int s2 = done; s2 < a.nsteps; s2++) track[3 * s2] = track[3 * s2 + 1] = track[3 * s2 + 2] = nan("");
     }
 }
 
@@ -543,13 +722,13 @@ k_ensemble(EnsArgs a) {
 // host API
 // ---------------------------------------------------------------------------------------
 struct slam_ensemble {
-    int device = 0, n_runs = 0, nl = 0, ncap = 0;
+    int device = 0, n_runs = 0, nl = 0, ncap = 0, extra = 0, threads = 128;
     uint64_t seed = 0;
     uint32_t run0 = 0;
     TruthTables t;
     cudaStream_t stream = nullptr;
     double *d_gamma = nullptr, *d_ztrue = nullptr;   // d_ztrue[0..2] = initial pose, tables from +3
-    int *d_upd_at = nullptr, *d_obs_start = nullptr;
+    int *d_blk = nullptr, *d_obs_start = nullptr, *d_steps_done = nullptr;
     double *d_ctrl = nullptr, *d_obs = nullptr;
     int obs_per_member = 0;
     double *d_final_x = nullptr, *d_tracks = nullptr, *d_final_P = nullptr;
@@ -569,12 +748,39 @@ extern "C" int slam_ens_destroy(slam_ens_t *e) {
     if (!e) return SLAM_OK;
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
-    cudaFree(e->d_gamma); cudaFree(e->d_ztrue); cudaFree(e->d_upd_at); cudaFree(e->d_obs_start);
+    cudaFree(e->d_gamma); cudaFree(e->d_ztrue); cudaFree(e->d_blk); cudaFree(e->d_steps_done); cudaFree(e->d_obs_start);
     cudaFree(e->d_ctrl); cudaFree(e->d_obs); cudaFree(e->d_final_x); cudaFree(e->d_tracks);
     cudaFree(e->d_final_P); cudaFree(e->d_n_final); cudaFree(e->d_status);
     if (e->stream) cudaStreamDestroy(e->stream);
     cudaGetLastError();
     delete e;
+    return SLAM_OK;
+}
+
+// (re)sizes everything that depends on the member capacity 3 + 2*(nl + extra)
+static int ens_resize(slam_ens_t *e, int extra) {
+    const int ncap = 3 + 2 * (e->nl + extra);
+    const int mmax = std::max(e->t.max_nz, 1);
+    const size_t smem = ens_smem_bytes(ncap, mmax);
+    int max_optin = 0;
+    cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, e->device);
+    if (smem > (size_t)max_optin) {
+        slam_set_error("ensemble: a member needs %zu bytes of shared memory (%d + %d landmarks, up to %d "
+                       "observations per step); the device offers %d", smem, e->nl, extra, e->t.max_nz, max_optin);
+        return SLAM_ERR_CAPACITY;
+    }
+    CUDA_TRY(cudaFuncSetAttribute(k_ensemble<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CUDA_TRY(cudaFuncSetAttribute(k_ensemble<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CUDA_TRY(cudaFuncSetAttribute(k_ensemble<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaFree(e->d_final_x);
+    cudaFree(e->d_final_P);
+    e->d_final_x = e->d_final_P = nullptr;
+    CUDA_TRY(cudaMalloc(&e->d_final_x, sizeof(double) * (size_t)e->n_runs * ncap));
+    if (e->keep) CUDA_TRY(cudaMalloc(&e->d_final_P, sizeof(double) * (size_t)e->n_runs * ncap * ncap));
+    e->extra = extra;
+    e->ncap = ncap;
+    e->smem = smem;
+    e->ran = false;
     return SLAM_OK;
 }
 
@@ -586,16 +792,11 @@ extern "C" int slam_ens_create(int device, const double *waypoints, int nwp, con
     int rc = slam_require_device(device);
     if (rc) return rc;
     slam_ens_t *e = new slam_ensemble();
-    e->device = device; e->n_runs = n_runs; e->nl = nl; e->ncap = 3 + 2 * nl; e->seed = seed; e->run0 = run0;
-    rc = build_truth(waypoints, nwp, landmarks, nl, nlaps, e->t);
+    e->device = device; e->n_runs = n_runs; e->nl = nl; e->extra = ENS_DEFAULT_EXTRA; e->ncap = 3 + 2 * (nl + e->extra); e->seed = seed; e->run0 = run0;
+    rc = build_truth(waypoints, nwp, landmarks, nl, nlaps, ENS_MAXB, e->t);
     if (rc) { delete e; return rc; }
-    const int mmax = std::max(e->t.max_nz, 1);
-    e->smem = ens_smem_bytes(e->ncap, mmax, nl);
-    int max_optin = 0;
-    cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
-    if (e->smem > (size_t)max_optin) {
-        slam_set_error("slam_ens_create: a member needs %zu bytes of shared memory (%d landmarks, up to %d "
-                       "observations per step); the device offers %d", e->smem, nl, e->t.max_nz, max_optin);
+    if (e->t.max_nz > 128) {
+        slam_set_error("slam_ens_create: %d landmarks visible in one step; the ensemble kernel handles 128", e->t.max_nz);
         delete e;
         return SLAM_ERR_CAPACITY;
     }
@@ -610,25 +811,45 @@ extern "C" int slam_ens_create(int device, const double *waypoints, int nwp, con
     } while (0)
     const TruthTables &t = e->t;
     EN_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
-    EN_TRY(cudaFuncSetAttribute(k_ensemble, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e->smem));
     EN_TRY(cudaMalloc(&e->d_gamma, sizeof(double) * t.nsteps));
-    EN_TRY(cudaMalloc(&e->d_upd_at, sizeof(int) * t.nsteps));
+    EN_TRY(cudaMalloc(&e->d_blk, sizeof(int) * t.blocks.size()));
     EN_TRY(cudaMalloc(&e->d_obs_start, sizeof(int) * (t.nupd + 1)));
     EN_TRY(cudaMalloc(&e->d_ztrue, sizeof(double) * (3 + t.z_true.size() + 2)));
-    EN_TRY(cudaMalloc(&e->d_final_x, sizeof(double) * (size_t)n_runs * e->ncap));
     EN_TRY(cudaMalloc(&e->d_n_final, sizeof(int) * n_runs));
+    EN_TRY(cudaMalloc(&e->d_steps_done, sizeof(int) * n_runs));
     EN_TRY(cudaMalloc(&e->d_status, sizeof(int) * n_runs));
     const double pose0[3] = {waypoints[0], waypoints[1],
                              atan2(waypoints[3] - waypoints[1], waypoints[2] - waypoints[0])};
     EN_TRY(cudaMemcpy(e->d_gamma, t.gamma.data(), sizeof(double) * t.nsteps, cudaMemcpyHostToDevice));
-    EN_TRY(cudaMemcpy(e->d_upd_at, t.upd_at.data(), sizeof(int) * t.nsteps, cudaMemcpyHostToDevice));
+    EN_TRY(cudaMemcpy(e->d_blk, t.blocks.data(), sizeof(int) * t.blocks.size(), cudaMemcpyHostToDevice));
     EN_TRY(cudaMemcpy(e->d_obs_start, t.obs_start.data(), sizeof(int) * (t.nupd + 1), cudaMemcpyHostToDevice));
     EN_TRY(cudaMemcpy(e->d_ztrue, pose0, sizeof(pose0), cudaMemcpyHostToDevice));
     if (!t.z_true.empty())
         EN_TRY(cudaMemcpy(e->d_ztrue + 3, t.z_true.data(), sizeof(double) * t.z_true.size(), cudaMemcpyHostToDevice));
 #undef EN_TRY
+    rc = ens_resize(e, ENS_DEFAULT_EXTRA);
+    if (rc) { slam_ens_destroy(e); return rc; }
     *out = e;
     return SLAM_OK;
+}
+
+extern "C" int slam_ens_set_extra_landmarks(slam_ens_t *e, int extra) {
+    E_CHECK(e);
+    ARG_CHECK(extra >= 0, "extra < 0");
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    return ens_resize(e, extra);
+}
+
+extern "C" int slam_ens_set_threads(slam_ens_t *e, int threads) {
+    ARG_CHECK(e != nullptr, "NULL handle");
+    ARG_CHECK(threads == 64 || threads == 128 || threads == 256, "threads must be 64, 128 or 256");
+    e->threads = threads;
+    return SLAM_OK;
+}
+
+extern "C" int slam_ens_capacity(slam_ens_t *e) {
+    if (!e) { slam_set_error("slam_ens_capacity: NULL handle"); return SLAM_ERR_ARG; }
+    return e->ncap;
 }
 
 extern "C" int slam_ens_steps(slam_ens_t *e, int *nsteps, int *nupdates) {
@@ -641,10 +862,10 @@ extern "C" int slam_ens_steps(slam_ens_t *e, int *nsteps, int *nupdates) {
 extern "C" int slam_ens_keep_tracks(slam_ens_t *e, int on) {
     E_CHECK(e);
     e->keep = on != 0;
-    if (e->keep && !e->d_tracks) {
+    if (e->keep && !e->d_tracks)
         CUDA_TRY(cudaMalloc(&e->d_tracks, sizeof(double) * (size_t)e->n_runs * 3 * e->t.nsteps));
+    if (e->keep && !e->d_final_P)
         CUDA_TRY(cudaMalloc(&e->d_final_P, sizeof(double) * (size_t)e->n_runs * e->ncap * e->ncap));
-    }
     return SLAM_OK;
 }
 
@@ -668,12 +889,20 @@ extern "C" int slam_ens_run(slam_ens_t *e) {
     a.n_runs = e->n_runs; a.nsteps = e->t.nsteps; a.nl = e->nl; a.ncap = e->ncap;
     a.mmax = std::max(e->t.max_nz, 1);
     a.seed = e->seed; a.run0 = e->run0;
-    a.gamma = e->d_gamma; a.upd_at = e->d_upd_at; a.obs_start = e->d_obs_start; a.z_true = e->d_ztrue + 3;
+    a.nblocks = (int)e->t.blocks.size() / 3;
+    a.ldw = ens_ru4(e->ncap);
+    a.npk = ens_ru4(e->ncap * (e->ncap + 1) / 2);
+    a.wdoubles = ens_wdoubles(e->ncap, a.mmax);
+    a.gamma = e->d_gamma; a.blk = e->d_blk; a.obs_start = e->d_obs_start; a.z_true = e->d_ztrue + 3;
     a.ctrl_noise = e->d_ctrl; a.obs_noise = e->d_obs; a.obs_per_member = e->obs_per_member;
-    a.final_x = e->d_final_x; a.n_final = e->d_n_final; a.status = e->d_status;
+    a.final_x = e->d_final_x; a.n_final = e->d_n_final; a.status = e->d_status; a.steps_done = e->d_steps_done;
     a.tracks = e->keep ? e->d_tracks : nullptr;
     a.final_P = e->keep ? e->d_final_P : nullptr;
-    k_ensemble<<<e->n_runs, ENS_THREADS, e->smem, e->stream>>>(a);
+    switch (e->threads) {
+        case 64: k_ensemble<64><<<e->n_runs, 64, e->smem, e->stream>>>(a); break;
+        case 256: k_ensemble<256><<<e->n_runs, 256, e->smem, e->stream>>>(a); break;
+        default: k_ensemble<128><<<e->n_runs, 128, e->smem, e->stream>>>(a); break;
+    }
     e->launches++;
     e->ran = true;
     CUDA_TRY(cudaGetLastError());
@@ -689,6 +918,20 @@ extern "C" int slam_ens_sync(slam_ens_t *e) {
     int bad = 0;
     for (int v : st) bad += v != 0;
     return bad;
+}
+
+// Filter-steps actually completed: *total over all members (members that stopped early count the
+// steps they ran), per_member[n_runs] (may be NULL).
+extern "C" int slam_ens_steps_done(slam_ens_t *e, long long *total, int *per_member) {
+    E_CHECK(e);
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    std::vector<int> sd(e->n_runs, 0);
+    if (e->ran) CUDA_TRY(cudaMemcpy(sd.data(), e->d_steps_done, sizeof(int) * e->n_runs, cudaMemcpyDeviceToHost));
+    long long tot = 0;
+    for (int v : sd) tot += v;
+    if (total) *total = tot;
+    if (per_member) memcpy(per_member, sd.data(), sizeof(int) * e->n_runs);
+    return SLAM_OK;
 }
 
 extern "C" int slam_ens_get_results(slam_ens_t *e, double *final_pose, int *n_final, int *status) {

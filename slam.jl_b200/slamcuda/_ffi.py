@@ -96,6 +96,10 @@ _sig("slam_synth_observations", I, vp, I, D, U64, I, I, c_double_p, c_int64_p)
 _sig("slam_ens_create", I, I, c_double_p, I, c_double_p, I, I, U64, U32, I, C.POINTER(vp))
 _sig("slam_ens_destroy", I, vp)
 _sig("slam_ens_steps", I, vp, c_int_p, c_int_p)
+_sig("slam_ens_set_extra_landmarks", I, vp, I)
+_sig("slam_ens_capacity", I, vp)
+_sig("slam_ens_set_threads", I, vp, I)
+_sig("slam_ens_steps_done", I, vp, C.POINTER(C.c_longlong), c_int_p)
 _sig("slam_ens_run", I, vp)
 _sig("slam_ens_sync", I, vp)
 _sig("slam_ens_get_results", I, vp, c_double_p, c_int_p, c_int_p)

@@ -12,7 +12,7 @@ from ._ffi import lib, check, dptr
 
 class Ensemble:
     def __init__(self, waypoints, landmarks, n_runs: int, seed: int = 0, run0: int = 0, nlaps: int = 2,
-                 device: int = 0):
+                 device: int = 0, extra_landmarks: int | None = None, threads: int | None = None):
         wp = np.ascontiguousarray(np.asarray(waypoints, dtype=np.float64).T).reshape(-1)   # 2 x nwp column-major
         lm = np.asarray(landmarks, dtype=np.float64).reshape(2, -1)
         lmf = np.ascontiguousarray(lm.T).reshape(-1)
@@ -23,6 +23,22 @@ class Ensemble:
         ns, nu = C.c_int(), C.c_int()
         check(lib.slam_ens_steps(self.ptr, C.byref(ns), C.byref(nu)))
         self.nsteps, self.nupdates = ns.value, nu.value
+        if extra_landmarks is not None:
+            check(lib.slam_ens_set_extra_landmarks(self.ptr, int(extra_landmarks)))
+        if threads is not None:
+            check(lib.slam_ens_set_threads(self.ptr, int(threads)))
+
+    @property
+    def capacity(self) -> int:
+        """3 + 2*(landmarks + extra_landmarks): the largest state a member can hold."""
+        return check(lib.slam_ens_capacity(self.ptr))
+
+    def steps_done(self):
+        """(total filter-steps completed by the last run, per-member array)."""
+        tot = C.c_longlong()
+        per = np.zeros(self.n_runs, dtype=np.int32)
+        check(lib.slam_ens_steps_done(self.ptr, C.byref(tot), per.ctypes.data_as(C.POINTER(C.c_int))))
+        return int(tot.value), per
 
     def close(self):
         if self.ptr:
@@ -67,7 +83,7 @@ class Ensemble:
         return t.T.copy()
 
     def state(self, member: int, with_cov: bool = True):
-        cap = 3 + 2 * self.nl
+        cap = self.capacity
         x = np.empty(cap)
         P = np.empty((cap, cap), order="F") if with_cov else None
         n = check(lib.slam_ens_get_state(self.ptr, member, dptr(x), dptr(P) if with_cov else None, cap))
