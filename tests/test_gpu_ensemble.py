@@ -3,9 +3,10 @@
 (a) injected noise: member r gets the same numpy PCG64 normals as the numpy literal oracle's
     run r -> end-of-run trajectories within 1e-6, final state within 1e-6, identical map sizes;
 (b) Philox noise: against the oracle's C twin running the same counter-based generator.
-Members whose filter outgrows the fixed capacity 3 + 2*nl (spurious landmarks after an
-association failure of the algorithm itself) stop with SLAM_ERR_CAPACITY exactly where the twin
-returns -2."""
+A member holds 3 + 2*(nl + extra) states (the reference's state grows without bound); members
+whose filter outgrows that (spurious landmarks the algorithm itself creates, diverged filters)
+stop with SLAM_ERR_CAPACITY exactly where the twin returns -2, and only the steps they ran are
+counted by steps_done()."""
 import ctypes as C
 
 import numpy as np
@@ -37,13 +38,15 @@ def test_ensemble_injected_noise_vs_numpy_oracle(course1, nl, nruns):
     ens.run()
     bad = ens.sync()
     pose, nf, st = ens.results()
-    cap = 3 + 2 * nl
+    cap = ens.capacity
+    assert cap == 3 + 2 * (nl + 5)
+    total, per = ens.steps_done()
     worst = 0.0
     for r, rr in enumerate(runs):
         if len(rr["x"]) > cap:                      # the oracle's map outgrew the fixed capacity
-            assert st[r] == -3, (r, st[r])
+            assert st[r] == -3 and per[r] < ens.nsteps, (r, st[r])
             continue
-        assert st[r] == 0 and nf[r] == len(rr["x"])
+        assert st[r] == 0 and nf[r] == len(rr["x"]) and per[r] == ens.nsteps
         tr = ens.track(r)
         e = float(np.max(np.abs(tr - rr["slam_track"]))) / float(np.max(np.abs(rr["slam_track"])))
         x, P = ens.state(r)
@@ -52,14 +55,16 @@ def test_ensemble_injected_noise_vs_numpy_oracle(course1, nl, nruns):
     print(f"\n[ensemble nl={nl}] {nruns} members, {bad} stopped early, worst rel err {worst:.3e}")
     assert worst < TRACK_TOL
     assert bad == sum(len(rr["x"]) > cap for rr in runs)
+    assert total == int(per.sum())
     ens.close()
 
 
-def test_ensemble_philox_vs_twin(course1, twin):
+@pytest.mark.parametrize("extra,threads", [(0, 128), (5, 128), (5, 64), (5, 256), (12, 256)])
+def test_ensemble_philox_vs_twin(course1, twin, extra, threads):
     from slamcuda.ensemble import Ensemble
     nl, nruns, seed, run0 = 35, 48, 1234, 7
     lm = ref.make_inputs(nl, 0, 0)[0]
-    ens = Ensemble(course1, lm, nruns, seed=seed, run0=run0)
+    ens = Ensemble(course1, lm, nruns, seed=seed, run0=run0, extra_landmarks=extra, threads=threads)
     ens.keep_tracks(True)
     ens.run()
     bad = ens.sync()
@@ -70,8 +75,10 @@ def test_ensemble_philox_vs_twin(course1, twin):
     fp = np.zeros(3 * nruns)
     trk = np.zeros(3 * ms * nruns)
     nfin = np.zeros(nruns, dtype=np.int32)
-    tbad = twin.twin_ensemble(d(wp), course1.shape[1], d(lmf), nl, seed, run0, nruns, 2, ms, d(fp), d(trk),
-                              nfin.ctypes.data_as(C.POINTER(C.c_int)), 8)
+    twin.twin_ensemble_cap.restype = C.c_int
+    twin.twin_ensemble_cap.argtypes = twin.twin_ensemble.argtypes + [C.c_int]
+    tbad = twin.twin_ensemble_cap(d(wp), course1.shape[1], d(lmf), nl, seed, run0, nruns, 2, ms, d(fp), d(trk),
+                                  nfin.ctypes.data_as(C.POINTER(C.c_int)), 8, extra)
     worst, compared = 0.0, 0
     for r in range(nruns):
         tt = trk[3 * ms * r:3 * ms * (r + 1)].reshape(ms, 3).T
