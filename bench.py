@@ -268,23 +268,30 @@ def gpu_ensemble(n_runs: int, rank: int, world: int, device: int, reps: int = 3)
         pose, nf, st = ens.results()
         e2e_ms = (time.perf_counter() - t0) * 1e3
         ms = sorted(times)[len(times) // 2]
+        done, _per = ens.steps_done()          # members that outgrow their capacity count only the steps they ran
+        stopped = int((st != 0).sum())
         if world > 1:
             import torch.distributed as dist
             t = torch.tensor([ms, e2e_ms], device=f"cuda:{device}", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms, e2e_ms = (float(v) for v in t.cpu())
+            c = torch.tensor([done, stopped], device=f"cuda:{device}", dtype=torch.int64)
+            dist.all_reduce(c, op=dist.ReduceOp.SUM)
+            done, stopped = (int(v) for v in c.cpu())
         total = n_runs * world
         return {"workload": f"{total} independent course1 runs ({ENS_LANDMARKS} landmarks, 2 laps, {ens.nsteps} steps, "
                             f"{ens.nupdates} observation steps each), {n_runs} per GPU, one CTA per filter, "
-                            f"Philox noise keyed by (seed, run)",
-                "value": total * ens.nsteps / (ms * 1e-3), "unit": "filter-steps/s", "ms_per_launch": ms,
-                "e2e": total * ens.nsteps / (e2e_ms * 1e-3), "runs": total, "steps_per_run": ens.nsteps,
-                "stopped_early_on_rank0": int(bad), "gpu_launches_per_run_batch": 1}
+                            f"Philox noise keyed by (seed, run), capacity {ens.capacity} states per member",
+                "value": done / (ms * 1e-3), "unit": "filter-steps/s", "ms_per_launch": ms,
+                "e2e": done / (e2e_ms * 1e-3), "runs": total, "steps_per_run": ens.nsteps,
+                "filter_steps_done": done, "member_capacity": ens.capacity,
+                "members_stopped_at_capacity": stopped, "gpu_launches_per_run_batch": 1,
+                "streaming_model_hbm_equiv_gbs": done * 12.4e3 / (ms * 1e-3) / 1e9}
     finally:
         ens.close()
 
 
-def cpu_ensemble_baseline(n_runs: int = 64):
+def cpu_ensemble_baseline(n_runs: int = 2048, extra: int = 5):
     """The oracle's C twin (plain C, -O2 -ffp-contract=off, OpenMP over runs) on the host cores."""
     import ctypes
     lib = ctypes.CDLL(str(ROOT / "oracle" / "libslamtwin.so"))
@@ -294,15 +301,17 @@ def cpu_ensemble_baseline(n_runs: int = 64):
     lmf = np.ascontiguousarray(lm.T).reshape(-1)
     fp = np.zeros(3 * n_runs)
     cores = os.cpu_count() or 1
-    lib.twin_ensemble.restype = ctypes.c_int
-    lib.twin_ensemble.argtypes = [dp, ctypes.c_int, dp, ctypes.c_int, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_int,
-                                  ctypes.c_int, ctypes.c_int, dp, dp, ctypes.POINTER(ctypes.c_int), ctypes.c_int]
+    lib.twin_ensemble_cap.restype = ctypes.c_int
+    lib.twin_ensemble_cap.argtypes = [dp, ctypes.c_int, dp, ctypes.c_int, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_int,
+                                      ctypes.c_int, ctypes.c_int, dp, dp, ctypes.POINTER(ctypes.c_int), ctypes.c_int,
+                                      ctypes.c_int]
     t0 = time.perf_counter()
-    lib.twin_ensemble(wpf.ctypes.data_as(dp), wp.shape[1], lmf.ctypes.data_as(dp), ENS_LANDMARKS, SEED, 0, n_runs, 2,
-                      10000, fp.ctypes.data_as(dp), None, None, cores)
+    lib.twin_ensemble_cap(wpf.ctypes.data_as(dp), wp.shape[1], lmf.ctypes.data_as(dp), ENS_LANDMARKS, SEED, 0, n_runs, 2,
+                          10000, fp.ctypes.data_as(dp), None, None, cores, extra)
     sec = time.perf_counter() - t0
     return {"value": n_runs * 2802 / sec, "unit": "filter-steps/s", "cores": cores, "kind": "port",
-            "sample": f"oracle/slam_twin.c twin_ensemble, {n_runs} runs over {cores} OpenMP threads, {sec:.2f} s"}
+            "sample": f"oracle/slam_twin.c twin_ensemble_cap, {n_runs} runs (same {extra}-landmark head-room) over {cores} "
+                      f"OpenMP threads, {sec:.2f} s; upper bound: runs that stop at capacity are counted in full"}
 
 
 def gpu_update_sharded(n_landmarks: int, m: int, steps: int, warmup: int, e2e_steps: int, rank: int, world: int,
