@@ -65,6 +65,7 @@ def build(verbose: bool = False, force: bool = False) -> Path:
         obj = OBJ / (src.stem + ".o")
         if force or _stale(obj, [src] + headers):
             cmd = [nvcc, *ARCH, *COMMON, *_host_compiler(), *PER_FILE.get(src.name, []),
+                   *os.environ.get("SLAMCUDA_DEFS", "").split(),
                    "-Xptxas", "-v", "-c", str(src), "-o", str(obj)]
             jobs.append((src, cmd))
 

@@ -179,6 +179,22 @@ constexpr int BS = 24;            // doubles of block scratch per step
 // block scratch slots (per step of the block)
 constexpr int B_V = 0, B_G = 1, B_SG = 2, B_CG = 3, B_TPHI = 4, B_PHI0 = 5, B_VTS = 7, B_VTC = 8, B_N = 9,
               B_X0 = 18, B_X1 = 19, B_PHI = 20;
+#ifdef ENS_TIMING   // developer build (SLAMCUDA_DEFS=-DENS_TIMING): cycles per phase of member 0, thread 0
+__device__ long long g_ens_phase[24];
+__device__ __forceinline__ void ens_mark(int k) {
+    __shared__ long long tlast, acc[24];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        const long long t = clock64();
+        if (k == -1) { for (int q = 0; q < 24; q++) acc[q] = 0; }
+        else if (k == -2) { for (int q = 0; q < 24; q++) g_ens_phase[q] += acc[q]; }
+        else acc[k] += t - tlast;
+        tlast = clock64();
+    }
+}
+#define ENS_MARK(k) ens_mark(k)
+#else
+#define ENS_MARK(k)
+#endif
 constexpr int LM_STRIDE = 17;     // association table per landmark: zp[2], inv(S)[4], log det, h[10]
 
 struct EnsSmem {
@@ -222,35 +238,85 @@ __device__ inline EnsSmem ens_carve(double *base, int ncap, int mmax) {
     return s;
 }
 
+// One copy of the FP64 sin / cos / normal code for all call sites: the kernel streams through its
+// whole instruction footprint once per block, so code size is fetch latency.
+__device__ __noinline__ void ens_sincos(double t, double *s, double *c) {
+    *s = sin(t);
+    *c = cos(t);
+}
+__device__ __noinline__ double ens_normal(uint64_t seed, uint32_t run, uint32_t stream, uint32_t idx) {
+    return philox_normal(seed, run, stream, idx);
+}
+
 // packed upper triangle, column-major: P(i, j), i <= j, at j(j+1)/2 + i
 __device__ __forceinline__ int cofs(int j) { return (j * (j + 1)) >> 1; }
 __device__ __forceinline__ double psym(const double *P, int i, int j) {
     return i <= j ? P[cofs(j) + i] : P[cofs(i) + j];
 }
 
-// ---- predict for all steps [s0, s0 + len) of a block, src/ekf.jl:8-43 ---------------------
+// ---- the part of a block that does not depend on the filter state ----------------------------
+// add_control_noise! (sim/sim-utils.jl:35-38: speed first, then steering) and the noisy
+// observations of get_observations (sim/sim-utils.jl:53-75: noise-free table + this member's
+// noise, draw order = all range noises of the step, then all bearing noises), plus sin / cos of
+// the measured steering angle.  Run by the HELPER warps (tid >= 32) while warp 0 is busy with a
+// serial phase of the previous block (the innovation Cholesky), so its latency is hidden.
 template <int T>
-__device__ void ens_predict_block(const EnsSmem &sm, const EnsArgs &a, int n, int s0, int len, uint32_t run,
-                                  const double *ctrl) {
+__device__ __noinline__ void ens_stage_block(const EnsSmem &sm, const EnsArgs &a, int b, uint32_t run,
+                                             const double *ctrl, const double *obsn) {
+    const int ht = (int)threadIdx.x - 32;
+    const int s0 = a.blk[3 * b], len = a.blk[3 * b + 1] - s0, u = a.blk[3 * b + 2];
+    int nz = 0, o0 = 0;
+    if (u >= 0) {
+        o0 = a.obs_start[u];
+        nz = a.obs_start[u + 1] - o0;
+        if (obsn && 2 * o0 + 2 * nz > a.obs_per_member) nz = 0;   // the block loop reports the overflow
+    }
+    const int cursor = 2 * o0;
+    // one standard normal per item: 2*len control items (step, speed | steering), then 2*nz observation items
+#pragma unroll 1
+    for (int item = ht; item < 2 * len + 2 * nz; item += T - 32) {
+        const bool is_ctrl = item < 2 * len;
+        const int c = is_ctrl ? item : item - 2 * len;
+        double e;
+        if (is_ctrl ? ctrl != nullptr : obsn != nullptr) {
+            e = is_ctrl ? ctrl[2 * s0 + c] : obsn[cursor + c];
+        } else {
+            e = is_ctrl ? ens_normal(a.seed, run, (uint32_t)(c & 1), (uint32_t)(s0 + (c >> 1)))
+                        : ens_normal(a.seed, run, 2u, (uint32_t)(cursor + c));
+        }
+        if (is_ctrl) {
+            const int which = c & 1;
+            sm.bs[(c >> 1) * BS + which] = which == 0 ? TARGET_SPEED + e * sqrt(SIGMA_SPEED * SIGMA_SPEED)
+                                                      : a.gamma[s0 + (c >> 1)] + e * sqrt(SIGMA_STEER * SIGMA_STEER);
+        } else {
+            const int ob = c < nz ? c : c - nz, comp = c < nz ? 0 : 1;
+            sm.z[2 * ob + comp] = a.z_true[2 * (o0 + ob) + comp] +
+                                  e * (comp == 0 ? sqrt(SIGMA_R * SIGMA_R) : sqrt(SIGMA_B * SIGMA_B));
+        }
+    }
+    asm volatile("bar.sync 1, %0;" ::"r"(T - 32) : "memory");   // helper warps only
+#pragma unroll 1
+    for (int st = ht; st < len; st += T - 32) {
+        double *bq = sm.bs + st * BS;
+        const double v = bq[B_V], g = bq[B_G];
+        double sg, cg;
+        ens_sincos(g, &sg, &cg);
+        bq[B_SG] = sg;
+        bq[B_CG] = cg;
+        bq[B_TPHI] = v * DT * sg / WHEELBASE;
+    }
+}
+
+// ---- predict for all steps [s0, s0 + len) of a staged block, src/ekf.jl:8-43 ------------------
+// On return x, P hold the state after the block's last predict; the pose after every step is in
+// bs[..][B_X0..B_PHI].  If nz > 0 the helper warps also fill zp / H of every mapped landmark
+// (predict_observation, src/common.jl:139-165) into the association table while warp 0 runs the
+// 3x3 chain.
+template <int T>
+__device__ void ens_predict_block(const EnsSmem &sm, int n, int len, int nz) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     double *bs = sm.bs;
-    // add_control_noise!, sim/sim-utils.jl:35-38 (speed first, then steering): one normal per lane
     if (warp == 0) {
-        if (lane < 2 * len) {
-            const int s = lane >> 1, which = lane & 1, step = s0 + s;
-            const double nrm = ctrl ? ctrl[2 * step + which] : philox_normal(a.seed, run, (uint32_t)which, (uint32_t)step);
-            bs[s * BS + which] = which == 0 ? TARGET_SPEED + nrm * sqrt(SIGMA_SPEED * SIGMA_SPEED)
-                                            : a.gamma[step] + nrm * sqrt(SIGMA_STEER * SIGMA_STEER);
-        }
-        __syncwarp();
-        if (lane < len) {   // the part of the step that does not depend on the state
-            const double v = bs[lane * BS + B_V], g = bs[lane * BS + B_G];
-            const double sg = sin(g), cg = cos(g);
-            bs[lane * BS + B_SG] = sg;
-            bs[lane * BS + B_CG] = cg;
-            bs[lane * BS + B_TPHI] = v * DT * sg / WHEELBASE;
-        }
-        __syncwarp();
         if (lane == 0) {    // chain (a): heading
             double phi = sm.x[2];
             for (int s = 0; s < len; s++) {
@@ -260,11 +326,14 @@ __device__ void ens_predict_block(const EnsSmem &sm, const EnsArgs &a, int n, in
             }
         }
         __syncwarp();
+        double vts = 0.0, vtc = 0.0;
         if (lane < len) {
             double *b = bs + lane * BS;
             const double v = b[B_V], g = b[B_G], phi = b[B_PHI0];
-            const double s = sin(g + phi), c = cos(g + phi);
-            const double vts = v * DT * s, vtc = v * DT * c;
+            double s, c;
+            ens_sincos(g + phi, &s, &c);
+            vts = v * DT * s;
+            vtc = v * DT * c;
             b[B_VTS] = vts;
             b[B_VTC] = vtc;
             // Gu*Q*Gu' (src/ekf.jl:27-29,32)
@@ -280,45 +349,45 @@ __device__ void ens_predict_block(const EnsSmem &sm, const EnsArgs &a, int n, in
 #pragma unroll
                 for (int j = 0; j < 3; j++) b[B_N + 3 * i + j] = GQ[i][0] * Gu[j][0] + GQ[i][1] * Gu[j][1];
         }
+        // x += vtc_s, y += vts_s one step after the other (every lane runs both chains; lane s keeps
+        // the pose after step s)
+        double ax = sm.x[0], ay = sm.x[1], kx = 0.0, ky = 0.0;
+        for (int s = 0; s < len; s++) {
+            ax = ax + __shfl_sync(0xffffffffu, vtc, s);
+            ay = ay + __shfl_sync(0xffffffffu, vts, s);
+            if (lane == s) { kx = ax; ky = ay; }
+        }
+        if (lane < len) {
+            bs[lane * BS + B_X0] = kx;
+            bs[lane * BS + B_X1] = ky;
+        }
+        if (lane == 0) {
+            sm.x[0] = ax;
+            sm.x[1] = ay;
+            sm.x[2] = bs[(len - 1) * BS + B_PHI];
+        }
     }
     __syncthreads();
+    ENS_MARK(1);
     if (warp == 0) {
-        // chain (b): lane = 3*i + j holds Pvv[i][j]; the upper triangle is authoritative
+        // chain (b): lane 3*i + j holds Pvv[i][j]; only the upper lanes (i <= j) matter and they read
+        // upper lanes only: A[i][j] = P[i][j] + gi*P[j][2], A[i][2] = P[i][2] + gi*P[2][2] with
+        // gi = Gv[i][2] = (-vts, vtc, 0); B[i][j] = A[i][j] + A[i][2]*gj; then + (Gu*Q*Gu')[i][j].
         const int l9 = lane < 9 ? lane : 0;
         const int i = l9 / 3, j = l9 % 3;
         double p = psym(sm.P, i, j);
-        // lanes 9 / 10 carry the x (+= vtc) and y (+= vts) prefix sums through the same loop
-        double acc = (lane == 9 || lane == 10) ? sm.x[lane - 9] : 0.0;
         for (int s = 0; s < len; s++) {
             const double nvts = -bs[s * BS + B_VTS], vtc = bs[s * BS + B_VTC];
-            if (lane == 9 || lane == 10) {
-                acc = acc + (lane == 9 ? vtc : -nvts);
-                bs[s * BS + B_X0 + lane - 9] = acc;
-            }
-            // A = Gv*Pvv: A[0][c] = P[0][c] + (-vts)*P[2][c], A[1][c] = P[1][c] + vtc*P[2][c], A[2][c] = P[2][c]
-            const double gi = i == 0 ? nvts : vtc;
-            const double pi0 = __shfl_sync(0xffffffffu, p, 3 * i + 0), pi1 = __shfl_sync(0xffffffffu, p, 3 * i + 1),
-                         pi2 = __shfl_sync(0xffffffffu, p, 3 * i + 2);
-            const double p20 = __shfl_sync(0xffffffffu, p, 6), p21 = __shfl_sync(0xffffffffu, p, 7),
+            const double nn = bs[s * BS + B_N + l9];
+            const double gi = i == 0 ? nvts : (i == 1 ? vtc : 0.0);
+            const double gj = j == 0 ? nvts : (j == 1 ? vtc : 0.0);
+            const double pj2 = __shfl_sync(0xffffffffu, p, 3 * j + 2), pi2 = __shfl_sync(0xffffffffu, p, 3 * i + 2),
                          p22 = __shfl_sync(0xffffffffu, p, 8);
-            double a0, a1, a2;
-            if (i < 2) {
-                a0 = pi0 + gi * p20;
-                a1 = pi1 + gi * p21;
-                a2 = pi2 + gi * p22;
-            } else {
-                a0 = pi0; a1 = pi1; a2 = pi2;
-            }
-            // B = A*Gv': B[r][0] = A[r][0] + A[r][2]*(-vts), B[r][1] = A[r][1] + A[r][2]*vtc, B[r][2] = A[r][2]
-            double bq = j == 0 ? a0 + a2 * nvts : j == 1 ? a1 + a2 * vtc : a2;
-            bq += bs[s * BS + B_N + l9];
-            // keep the block symmetric the way the upper-authoritative storage reads it
-            const double up = __shfl_sync(0xffffffffu, bq, 3 * j + i);
-            p = i <= j ? bq : up;
+            const double aj = p + gi * pj2;
+            const double a2 = pi2 + gi * p22;
+            p = (aj + a2 * gj) + nn;
         }
         if (lane < 9 && i <= j) sm.P[cofs(j) + i] = p;
-        if (lane == 9 || lane == 10) sm.x[lane - 9] = acc;
-        if (lane == 11) sm.x[2] = bs[(len - 1) * BS + B_PHI];
     } else {
         // chain (c): rows 0..2 of map column jc
         for (int jc = 3 + tid - 32; jc < n; jc += T - 32) {
@@ -332,13 +401,23 @@ __device__ void ens_predict_block(const EnsSmem &sm, const EnsArgs &a, int n, in
             col[0] = p0;
             col[1] = p1;
         }
+        if (nz > 0) {
+            const int Nf = (n - 3) / 2;
+            for (int jl = tid - 32; jl < Nf; jl += T - 32) {
+                const int f = 3 + 2 * jl;
+                double *t = sm.W + jl * LM_STRIDE;
+                observe_model(sm.x[0], sm.x[1], sm.x[2], sm.x[f], sm.x[f + 1], t, t + 7);
+            }
+        }
     }
     __syncthreads();
+    ENS_MARK(2);
 }
 
 // ---- associate, src/data-association.jl:1-63 ---------------------------------------------
 // Phase A: one thread per landmark builds everything of compute_association that does not
-// depend on the observation (zp, H, S = H*P*H' + R from the 5x5 sub-block, inv(S), log det S);
+// depend on the observation (S = H*P*H' + R from the 5x5 sub-block, inv(S), log det S; zp and H
+// come from ens_predict_block);
 // phase B: one warp per observation scores all landmarks and reduces (nd, j) / min nis with
 // shuffles -- strict '<' everywhere, lowest j wins ties, NaN never wins, which is the result of
 // the reference's sequential scan (`outer` is only consulted when no landmark was ever gated).
@@ -352,8 +431,10 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
     const double Rm[4] = {SIGMA_R * SIGMA_R, 0, 0, SIGMA_B * SIGMA_B};
     for (int jl = tid; jl < Nf; jl += T) {
         const int f = 3 + 2 * jl;
-        double zp[2], h[10];
-        observe_model(sm.x[0], sm.x[1], sm.x[2], sm.x[f], sm.x[f + 1], zp, h);
+        double *t = LM + jl * LM_STRIDE;     // zp and h were filled by ens_predict_block
+        double h[10];
+#pragma unroll
+        for (int q = 0; q < 10; q++) h[q] = t[7 + q];
         const int c[5] = {0, 1, 2, f, f + 1};
         const double Hr[2][5] = {{h[0], h[1], h[2], h[6], h[7]}, {h[3], h[4], h[5], h[8], h[9]}};
         double P5[5][5];
@@ -386,18 +467,14 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
                 S[2 * a + b] = acc + Rm[a + 2 * b];
             }
         const double det = S[0] * S[3] - S[1] * S[2];
-        double *t = LM + jl * LM_STRIDE;
-        t[0] = zp[0];
-        t[1] = zp[1];
         t[2] = S[3] / det;
         t[3] = -S[1] / det;
         t[4] = -S[2] / det;
         t[5] = S[0] / det;
         t[6] = log(det);
-#pragma unroll
-        for (int q = 0; q < 10; q++) t[7 + q] = h[q];
     }
     __syncthreads();
+    ENS_MARK(3);
     for (int i = warp; i < nz; i += T / 32) {
         const double z0 = sm.z[2 * i], z1 = sm.z[2 * i + 1];
         double nbest = INFINITY, outer = INFINITY;
@@ -430,6 +507,7 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
         if (lane == 0) sm.cls[i] = jbest != 0 ? jbest : (outer > GATE2 ? -1 : 0);
     }
     __syncthreads();
+    ENS_MARK(4);
     if (tid == 0) {
         int m = 0, k = 0;
         for (int i = 0; i < nz; i++) {
@@ -449,6 +527,7 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
         sm.par[9] = k;
     }
     __syncthreads();
+    ENS_MARK(5);
     const int m = (int)sm.par[8];
     if (tid < m) {
         const int jl = sm.idf[tid] - 1;
@@ -460,13 +539,15 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
         for (int q = 0; q < 10; q++) sm.Hn[10 * tid + q] = t[7 + q];
     }
     __syncthreads();
+    ENS_MARK(6);
 }
 
 // ---- update, src/ekf.jl:46-77, in the operation order of the oracle's C twin ---------------
 // PHt / W1 are rank-major (W[k*ldw + i]).  The 2m x 2m Cholesky, the triangular inverse and
 // u = C'v run in ONE warp (lane = column, __syncwarp between the column steps).
 template <int T>
-__device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m) {
+__device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsArgs &a, int stage_b, uint32_t run,
+                           const double *ctrl, const double *obsn) {
     const int tid = threadIdx.x;
     const int R = 2 * m;
     const double Rm[4] = {SIGMA_R * SIGMA_R, 0, 0, SIGMA_B * SIGMA_B};
@@ -487,6 +568,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m) {
         W[(2 * o + 1) * ldw + i] = w1;
     }
     __syncthreads();
+    ENS_MARK(7);
     // S = H*PHt + RR
     for (int idx = tid; idx < m * R; idx += T) {
         const int o = idx / R, k = idx - o * R;
@@ -502,6 +584,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m) {
         sm.S[(2 * o + 1) + k * R] = s1;
     }
     __syncthreads();
+    ENS_MARK(8);
     for (int idx = tid; idx < R * R; idx += T) {   // S = (S + S')*0.5
         const int a = idx % R, b = idx / R;
         if (a < b) {
@@ -511,6 +594,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m) {
         }
     }
     __syncthreads();
+    ENS_MARK(9);
     if (tid < 32) {   // one warp: right-looking upper Cholesky, then C = inv(U) and u = C'v
         const int lane = tid;
         int fail = 0;
@@ -527,6 +611,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m) {
             __syncwarp();
             for (int j = k + 1 + lane; j < R; j += 32) {
                 const double ukj = sm.S[k + j * R];
+#pragma unroll 1
                 for (int i = k + 1; i <= j; i++) sm.S[i + j * R] -= sm.S[k + i * R] * ukj;
             }
             __syncwarp();
@@ -537,29 +622,37 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m) {
                 sm.C[j + j * R] = 1.0 / sm.S[j + j * R];
                 for (int i = j - 1; i >= 0; i--) {
                     double a = 0;
+#pragma unroll 1
                     for (int k = i + 1; k <= j; k++) a += sm.S[i + k * R] * sm.C[k + j * R];
                     sm.C[i + j * R] = -a / sm.S[i + i * R];
                 }
                 double a = 0;
+#pragma unroll 1
                 for (int l = 0; l <= j; l++) a += sm.C[l + j * R] * sm.v[l];
                 sm.u[j] = a;
             }
         }
+    } else if (stage_b < a.nblocks) {
+        ens_stage_block<T>(sm, a, stage_b, run, ctrl, obsn);   // hidden behind the Cholesky
     }
     __syncthreads();
+    ENS_MARK(10);
     if (sm.par[10] != 0.0) return false;
     // W1 = PHt*C in place (k descending keeps PHt[i, l <= k] intact), x += W1*u
     for (int i = tid; i < n; i += T) {
         for (int k = R - 1; k >= 0; k--) {
             double a = 0;
+#pragma unroll 1
             for (int l = 0; l <= k; l++) a += W[l * ldw + i] * sm.C[l + k * R];
             W[k * ldw + i] = a;
         }
         double dxi = 0;
+#pragma unroll 1
         for (int k = 0; k < R; k++) dxi += W[k * ldw + i] * sm.u[k];
         sm.x[i] += dxi;
     }
     __syncthreads();
+    ENS_MARK(11);
     // P -= W1*W1' over the packed upper triangle in 4 x 4 register tiles: tile (bi, bj), bi <= bj,
     // covers rows 4bi.. and columns 4bj..; tiles are numbered column by column so that the lanes
     // of a warp mostly share bj (W1 column-side loads broadcast) and walk bi (conflict-free).
@@ -598,6 +691,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m) {
             }
     }
     __syncthreads();
+    ENS_MARK(12);
     return true;
 }
 
@@ -610,7 +704,8 @@ __device__ int ens_add_features(const EnsSmem &sm, int n, int k) {
     for (int q = 0; q < k; q++) {
         const int len = n;
         const double r = sm.zn[2 * q], b = sm.zn[2 * q + 1];
-        const double s = sin(phi + b), c = cos(phi + b);
+        double s, c;
+        ens_sincos(phi + b, &s, &c);
         const double Gv[2][3] = {{1, 0, -r * s}, {0, 1, r * c}};
         if (tid == 0) {
             sm.x[len] = sm.x[0] + r * c;
@@ -664,34 +759,34 @@ k_ensemble(EnsArgs a) {
     // three doubles in front of z_true
     if (tid < 3) sm.x[tid] = a.z_true[-3 + tid];
     __syncthreads();
-    int done = 0;
+    int done = 0, staged = -1;
+    ENS_MARK(-1);
     for (int b = 0; b < a.nblocks; b++) {
+        ENS_MARK(0);
         const int s0 = a.blk[3 * b], s1 = a.blk[3 * b + 1], u = a.blk[3 * b + 2];
         const int len = s1 - s0;
         int nz = 0;
         if (u >= 0) {
-            // get_observations, sim/sim-utils.jl:53-75: noise-free table + this member's noise, draw
-            // order = all range noises of the step, then all bearing noises.  Done by the warps that
-            // idle during the predict chains.
             const int o0 = a.obs_start[u];
             nz = a.obs_start[u + 1] - o0;
-            const int cursor = 2 * o0;
-            if (obsn && cursor + 2 * nz > a.obs_per_member) { status = SLAM_ERR_CAPACITY; break; }
-            for (int c = tid - 32; c < 2 * nz; c += T - 32) {
-                if (c < 0) continue;
-                const int ob = c < nz ? c : c - nz, comp = c < nz ? 0 : 1;
-                const double e = obsn ? obsn[cursor + c] : philox_normal(a.seed, run, 2u, (uint32_t)(cursor + c));
-                sm.z[2 * ob + comp] = a.z_true[2 * (o0 + ob) + comp] +
-                                      e * (comp == 0 ? sqrt(SIGMA_R * SIGMA_R) : sqrt(SIGMA_B * SIGMA_B));
-            }
+            if (obsn && 2 * o0 + 2 * nz > a.obs_per_member) { status = SLAM_ERR_CAPACITY; break; }
         }
-        ens_predict_block<T>(sm, a, n, s0, len, run, ctrl);
+        if (staged != b) {   // not staged during the previous block's update (first block, blocks after
+                             // an observation step without matches): do it now
+            if (tid >= 32) ens_stage_block<T>(sm, a, b, run, ctrl, obsn);
+            __syncthreads();
+        }
+        ens_predict_block<T>(sm, n, len, nz);
         if (nz > 0) {
             ens_associate<T>(sm, n, nz);
             const int m = (int)sm.par[8], k = (int)sm.par[9];
-            if (m > 0 && !ens_update<T>(sm, n, a.ldw, m)) { status = SLAM_ERR_NOT_PD; break; }
+            if (m > 0) {
+                if (!ens_update<T>(sm, n, a.ldw, m, a, b + 1, run, ctrl, obsn)) { status = SLAM_ERR_NOT_PD; break; }
+                staged = b + 1;
+            }
             if (n + 2 * k > a.ncap) { status = SLAM_ERR_CAPACITY; break; }
             n = ens_add_features<T>(sm, n, k);
+            ENS_MARK(13);
         }
         // slam_track[:, step] = state.x[1:3] (sim/ekfslam-sim.jl:128): after predict for the inner
         // steps, after update / add_features for the block's last step
@@ -701,6 +796,7 @@ k_ensemble(EnsArgs a) {
         }
         done = s1;
         __syncthreads();
+        ENS_MARK(14);
     }
     __syncthreads();
     for (int idx = tid; idx < a.ncap; idx += T) a.final_x[(size_t)member * a.ncap + idx] = sm.x[idx];
@@ -709,6 +805,7 @@ k_ensemble(EnsArgs a) {
             const int i = idx % a.ncap, j = idx / a.ncap;
             a.final_P[(size_t)member * a.ncap * a.ncap + idx] = psym(sm.P, i, j);
         }
+    ENS_MARK(-2);
     if (tid == 0) {
         a.n_final[member] = n;
         a.status[member] = status;
@@ -973,3 +1070,14 @@ extern "C" int slam_ens_get_state(slam_ens_t *e, int member, double *x, double *
 
 extern "C" void *slam_ens_stream(slam_ens_t *e) { return e ? (void *)e->stream : nullptr; }
 extern "C" long long slam_ens_launch_count(slam_ens_t *e) { return e ? e->launches : 0; }
+
+#ifdef ENS_TIMING
+extern "C" int slam_ens_debug_phases(long long *out, int reset) {
+    if (out) cudaMemcpyFromSymbol(out, g_ens_phase, sizeof(long long) * 24);
+    if (reset) {
+        long long z[24] = {0};
+        cudaMemcpyToSymbol(g_ens_phase, z, sizeof(z));
+    }
+    return SLAM_OK;
+}
+#endif
