@@ -50,7 +50,7 @@ struct TruthTables {
     std::vector<int> obs_start;      // per observation step: offset into z_true (nupd + 1 entries)
     std::vector<double> z_true;      // 2 x total noise-free observations
     std::vector<double> true_track;  // 3 x nsteps
-    std::vector<int> blocks;         // per block {first step, one-past-last step, observation index or -1}
+    std::vector<int> blocks;         // per block {first step, one-past-last step, first observation, nz}
 };
 
 // Noise-free half of sim! (sleep, monitor and the filter calls removed).
@@ -125,9 +125,11 @@ int build_truth(const double *wp, int nwp, const double *lm, int nl, int nlaps, 
     for (int s = 0; s < t.nsteps; s++) {
         const bool last = s + 1 == t.nsteps;
         if (t.upd_at[s] >= 0 || s + 1 - s0 == max_block || last) {
+            const int u = t.upd_at[s];
             t.blocks.push_back(s0);
             t.blocks.push_back(s + 1);
-            t.blocks.push_back(t.upd_at[s]);
+            t.blocks.push_back(u >= 0 ? t.obs_start[u] : 0);
+            t.blocks.push_back(u >= 0 ? t.obs_start[u + 1] - t.obs_start[u] : 0);
             s0 = s + 1;
         }
     }
@@ -160,8 +162,7 @@ struct EnsArgs {
     uint64_t seed;
     uint32_t run0;
     const double *gamma;       // [nsteps]   target steering angle after steer!
-    const int *blk;            // [nblocks][3] = {first step, one-past-last step, observation index or -1}
-    const int *obs_start;      // [nupd + 1]
+    const int4 *blk;           // [nblocks] = {first step, one-past-last step, first observation, nz}
     const double *z_true;      // [2 * total]; the three doubles in front hold the initial pose
     const double *ctrl_noise;  // optional [n_runs][2*nsteps] (speed, steering per step)
     const double *obs_noise;   // optional [n_runs][obs_per_member]
@@ -264,13 +265,10 @@ template <int T>
 __device__ __noinline__ void ens_stage_block(const EnsSmem &sm, const EnsArgs &a, int b, uint32_t run,
                                              const double *ctrl, const double *obsn) {
     const int ht = (int)threadIdx.x - 32;
-    const int s0 = a.blk[3 * b], len = a.blk[3 * b + 1] - s0, u = a.blk[3 * b + 2];
-    int nz = 0, o0 = 0;
-    if (u >= 0) {
-        o0 = a.obs_start[u];
-        nz = a.obs_start[u + 1] - o0;
-        if (obsn && 2 * o0 + 2 * nz > a.obs_per_member) nz = 0;   // the block loop reports the overflow
-    }
+    const int4 d = a.blk[b];
+    const int s0 = d.x, len = d.y - d.x, o0 = d.z;
+    int nz = d.w;
+    if (obsn && 2 * o0 + 2 * nz > a.obs_per_member) nz = 0;   // the block loop reports the overflow
     const int cursor = 2 * o0;
     // one standard normal per item: 2*len control items (step, speed | steering), then 2*nz observation items
 #pragma unroll 1
@@ -317,15 +315,24 @@ __device__ void ens_predict_block(const EnsSmem &sm, int n, int len, int nz) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     double *bs = sm.bs;
     if (warp == 0) {
-        if (lane == 0) {    // chain (a): heading
-            double phi = sm.x[2];
+        {   // chain (a): heading.  Every lane runs the chain (branch-free wrap, the step's increment
+            // comes by shuffle); lane s keeps the heading before / after step s.
+            const double tph = lane < len ? bs[lane * BS + B_TPHI] : 0.0;
+            double phi = sm.x[2], k0 = 0.0, k1 = 0.0;
+#pragma unroll 1
             for (int s = 0; s < len; s++) {
-                bs[s * BS + B_PHI0] = phi;
-                phi = mpi_to_pi(phi + bs[s * BS + B_TPHI]);
-                bs[s * BS + B_PHI] = phi;
+                const double t = phi + __shfl_sync(0xffffffffu, tph, s);
+                const double tm = t - 2 * SLAM_PI, tp = t + 2 * SLAM_PI;      // mpi_to_pi, src/common.jl:102-110
+                const double w = t > SLAM_PI ? tm : (t < -SLAM_PI ? tp : t);
+                if (lane == s) { k0 = phi; k1 = w; }
+                phi = w;
+            }
+            if (lane < len) {
+                bs[lane * BS + B_PHI0] = k0;
+                bs[lane * BS + B_PHI] = k1;
             }
         }
-        __syncwarp();
+        ENS_MARK(18);   // heading chain done
         double vts = 0.0, vtc = 0.0;
         if (lane < len) {
             double *b = bs + lane * BS;
@@ -349,9 +356,11 @@ __device__ void ens_predict_block(const EnsSmem &sm, int n, int len, int nz) {
 #pragma unroll
                 for (int j = 0; j < 3; j++) b[B_N + 3 * i + j] = GQ[i][0] * Gu[j][0] + GQ[i][1] * Gu[j][1];
         }
+        ENS_MARK(15);   // heading chain + sin/cos + Gu*Q*Gu' done (prefix sums follow)
         // x += vtc_s, y += vts_s one step after the other (every lane runs both chains; lane s keeps
         // the pose after step s)
         double ax = sm.x[0], ay = sm.x[1], kx = 0.0, ky = 0.0;
+#pragma unroll 1
         for (int s = 0; s < len; s++) {
             ax = ax + __shfl_sync(0xffffffffu, vtc, s);
             ay = ay + __shfl_sync(0xffffffffu, vts, s);
@@ -376,24 +385,36 @@ __device__ void ens_predict_block(const EnsSmem &sm, int n, int len, int nz) {
         const int l9 = lane < 9 ? lane : 0;
         const int i = l9 / 3, j = l9 % 3;
         double p = psym(sm.P, i, j);
+        // the step's scalars are loaded one iteration ahead so that only shuffle + 5 FP64 operations
+        // sit on the loop-carried chain
+        double nvts = -bs[B_VTS], vtc = bs[B_VTC], nn = bs[B_N + l9];
+        const long long mi_n = i == 0 ? -1LL : 0LL, mi_v = i == 1 ? -1LL : 0LL;
+        const long long mj_n = j == 0 ? -1LL : 0LL, mj_v = j == 1 ? -1LL : 0LL;
+#pragma unroll 1
         for (int s = 0; s < len; s++) {
-            const double nvts = -bs[s * BS + B_VTS], vtc = bs[s * BS + B_VTC];
-            const double nn = bs[s * BS + B_N + l9];
-            const double gi = i == 0 ? nvts : (i == 1 ? vtc : 0.0);
-            const double gj = j == 0 ? nvts : (j == 1 ? vtc : 0.0);
+            const int sn = s + 1 < len ? s + 1 : s;
+            const double nvts_n = -bs[sn * BS + B_VTS], vtc_n = bs[sn * BS + B_VTC], nn_n = bs[sn * BS + B_N + l9];
+            // gi = Gv[i][2], gj = Gv[j][2] picked with bit masks (no branches inside the chain)
+            const long long bn = __double_as_longlong(nvts), bv = __double_as_longlong(vtc);
+            const double gi = __longlong_as_double((bn & mi_n) | (bv & mi_v));
+            const double gj = __longlong_as_double((bn & mj_n) | (bv & mj_v));
             const double pj2 = __shfl_sync(0xffffffffu, p, 3 * j + 2), pi2 = __shfl_sync(0xffffffffu, p, 3 * i + 2),
                          p22 = __shfl_sync(0xffffffffu, p, 8);
             const double aj = p + gi * pj2;
             const double a2 = pi2 + gi * p22;
             p = (aj + a2 * gj) + nn;
+            nvts = nvts_n; vtc = vtc_n; nn = nn_n;
         }
         if (lane < 9 && i <= j) sm.P[cofs(j) + i] = p;
+        ENS_MARK(16);   // 3x3 chain done (barrier wait for the helper warps follows)
     } else {
         // chain (c): rows 0..2 of map column jc
+#pragma unroll 1
         for (int jc = 3 + tid - 32; jc < n; jc += T - 32) {
             double *col = sm.P + cofs(jc);
             double p0 = col[0], p1 = col[1];
             const double p2 = col[2];
+#pragma unroll 1
             for (int s = 0; s < len; s++) {
                 p0 = p0 + (-bs[s * BS + B_VTS]) * p2;
                 p1 = p1 + bs[s * BS + B_VTC] * p2;
@@ -403,6 +424,7 @@ __device__ void ens_predict_block(const EnsSmem &sm, int n, int len, int nz) {
         }
         if (nz > 0) {
             const int Nf = (n - 3) / 2;
+#pragma unroll 1
             for (int jl = tid - 32; jl < Nf; jl += T - 32) {
                 const int f = 3 + 2 * jl;
                 double *t = sm.W + jl * LM_STRIDE;
@@ -429,6 +451,7 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
     const int Nf = (n - 3) / 2;
     double *LM = sm.W;
     const double Rm[4] = {SIGMA_R * SIGMA_R, 0, 0, SIGMA_B * SIGMA_B};
+#pragma unroll 1
     for (int jl = tid; jl < Nf; jl += T) {
         const int f = 3 + 2 * jl;
         double *t = LM + jl * LM_STRIDE;     // zp and h were filled by ens_predict_block
@@ -475,10 +498,12 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
     }
     __syncthreads();
     ENS_MARK(3);
+#pragma unroll 1
     for (int i = warp; i < nz; i += T / 32) {
         const double z0 = sm.z[2 * i], z1 = sm.z[2 * i + 1];
         double nbest = INFINITY, outer = INFINITY;
         int jbest = 0;
+#pragma unroll 1
         for (int jl = lane; jl < Nf; jl += 32) {
             const double *t = LM + jl * LM_STRIDE;
             const double v0 = z0 - t[0];
@@ -510,6 +535,7 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
     ENS_MARK(4);
     if (tid == 0) {
         int m = 0, k = 0;
+#pragma unroll 1
         for (int i = 0; i < nz; i++) {
             const int c = sm.cls[i];
             if (c > 0) {
@@ -553,6 +579,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
     const double Rm[4] = {SIGMA_R * SIGMA_R, 0, 0, SIGMA_B * SIGMA_B};
     double *W = sm.W;
     // PHt = P*H' (five terms per entry, columns 1,2,3,f,f+1); rows n..ldw-1 are zeroed for K6's tiles
+#pragma unroll 1
     for (int idx = tid; idx < ldw * m; idx += T) {
         const int o = idx / ldw, i = idx - o * ldw;
         double w0 = 0.0, w1 = 0.0;
@@ -570,6 +597,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
     __syncthreads();
     ENS_MARK(7);
     // S = H*PHt + RR
+#pragma unroll 1
     for (int idx = tid; idx < m * R; idx += T) {
         const int o = idx / R, k = idx - o * R;
         const double *h = sm.Hn + 10 * o;
@@ -585,6 +613,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
     }
     __syncthreads();
     ENS_MARK(8);
+#pragma unroll 1
     for (int idx = tid; idx < R * R; idx += T) {   // S = (S + S')*0.5
         const int a = idx % R, b = idx / R;
         if (a < b) {
@@ -598,17 +627,20 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
     if (tid < 32) {   // one warp: right-looking upper Cholesky, then C = inv(U) and u = C'v
         const int lane = tid;
         int fail = 0;
+#pragma unroll 1
         for (int k = 0; k < R; k++) {
             const double d = sm.S[k + k * R];
             if (!(d > 0)) { fail = 1; break; }    // uniform: every lane reads the same d
             const double ukk = sqrt(d);
             __syncwarp();
             if (lane == 0) sm.S[k + k * R] = ukk;
+#pragma unroll 1
             for (int j = k + 1 + lane; j < R; j += 32) {
                 const double ukj = sm.S[k + j * R] / ukk;
                 sm.S[k + j * R] = ukj;
             }
             __syncwarp();
+#pragma unroll 1
             for (int j = k + 1 + lane; j < R; j += 32) {
                 const double ukj = sm.S[k + j * R];
 #pragma unroll 1
@@ -617,9 +649,12 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
             __syncwarp();
         }
         if (lane == 0) sm.par[10] = fail;
+        ENS_MARK(17);   // Cholesky done (inverse + u follow)
         if (!fail) {
+#pragma unroll 1
             for (int j = lane; j < R; j += 32) {
                 sm.C[j + j * R] = 1.0 / sm.S[j + j * R];
+#pragma unroll 1
                 for (int i = j - 1; i >= 0; i--) {
                     double a = 0;
 #pragma unroll 1
@@ -639,7 +674,9 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
     ENS_MARK(10);
     if (sm.par[10] != 0.0) return false;
     // W1 = PHt*C in place (k descending keeps PHt[i, l <= k] intact), x += W1*u
+#pragma unroll 1
     for (int i = tid; i < n; i += T) {
+#pragma unroll 1
         for (int k = R - 1; k >= 0; k--) {
             double a = 0;
 #pragma unroll 1
@@ -658,6 +695,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
     // of a warp mostly share bj (W1 column-side loads broadcast) and walk bi (conflict-free).
     // Each element is the chain a = fma(-W1[i,k], W1[j,k], a), k ascending, as the twin does.
     const int nb = (n + 3) >> 2;
+#pragma unroll 1
     for (int t = tid; t < nb * (nb + 1) / 2; t += T) {
         int bj = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
         while (bj * (bj + 1) / 2 > t) bj--;
@@ -672,6 +710,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
                 const int i = i0 + r, j = j0 + c;
                 acc[c][r] = (i <= j && j < n) ? sm.P[cofs(j) + i] : 0.0;
             }
+#pragma unroll 1
         for (int k = 0; k < R; k++) {
             const double4 wi = *reinterpret_cast<const double4 *>(W + k * ldw + i0);
             const double4 wj = *reinterpret_cast<const double4 *>(W + k * ldw + j0);
@@ -701,6 +740,7 @@ __device__ int ens_add_features(const EnsSmem &sm, int n, int k) {
     const int tid = threadIdx.x;
     const double phi = sm.x[2];
     const double Rm[4] = {SIGMA_R * SIGMA_R, 0, 0, SIGMA_B * SIGMA_B};
+#pragma unroll 1
     for (int q = 0; q < k; q++) {
         const int len = n;
         const double r = sm.zn[2 * q], b = sm.zn[2 * q + 1];
@@ -726,6 +766,7 @@ __device__ int ens_add_features(const EnsSmem &sm, int n, int k) {
             for (int a = 0; a < 2; a++)
                 for (int j = 0; j < 3; j++) sm.P[cofs(len + a) + j] = GP[a][j];
         }
+#pragma unroll 1
         for (int j = 3 + tid; j < len; j += T) {
             const double c0 = sm.P[cofs(j)], c1 = sm.P[cofs(j) + 1], c2 = sm.P[cofs(j) + 2];
             for (int a = 0; a < 2; a++)
@@ -761,16 +802,13 @@ k_ensemble(EnsArgs a) {
     __syncthreads();
     int done = 0, staged = -1;
     ENS_MARK(-1);
+    int4 dnext = a.blk[0];
     for (int b = 0; b < a.nblocks; b++) {
         ENS_MARK(0);
-        const int s0 = a.blk[3 * b], s1 = a.blk[3 * b + 1], u = a.blk[3 * b + 2];
-        const int len = s1 - s0;
-        int nz = 0;
-        if (u >= 0) {
-            const int o0 = a.obs_start[u];
-            nz = a.obs_start[u + 1] - o0;
-            if (obsn && 2 * o0 + 2 * nz > a.obs_per_member) { status = SLAM_ERR_CAPACITY; break; }
-        }
+        const int4 d = dnext;      // the next block's descriptor is fetched a whole block ahead
+        if (b + 1 < a.nblocks) dnext = a.blk[b + 1];
+        const int s0 = d.x, s1 = d.y, len = d.y - d.x, nz = d.w;
+        if (obsn && 2 * d.z + 2 * nz > a.obs_per_member) { status = SLAM_ERR_CAPACITY; break; }
         if (staged != b) {   // not staged during the previous block's update (first block, blocks after
                              // an observation step without matches): do it now
             if (tid >= 32) ens_stage_block<T>(sm, a, b, run, ctrl, obsn);
@@ -986,11 +1024,11 @@ extern "C" int slam_ens_run(slam_ens_t *e) {
     a.n_runs = e->n_runs; a.nsteps = e->t.nsteps; a.nl = e->nl; a.ncap = e->ncap;
     a.mmax = std::max(e->t.max_nz, 1);
     a.seed = e->seed; a.run0 = e->run0;
-    a.nblocks = (int)e->t.blocks.size() / 3;
+    a.nblocks = (int)e->t.blocks.size() / 4;
     a.ldw = ens_ru4(e->ncap);
     a.npk = ens_ru4(e->ncap * (e->ncap + 1) / 2);
     a.wdoubles = ens_wdoubles(e->ncap, a.mmax);
-    a.gamma = e->d_gamma; a.blk = e->d_blk; a.obs_start = e->d_obs_start; a.z_true = e->d_ztrue + 3;
+    a.gamma = e->d_gamma; a.blk = reinterpret_cast<const int4 *>(e->d_blk); a.z_true = e->d_ztrue + 3;
     a.ctrl_noise = e->d_ctrl; a.obs_noise = e->d_obs; a.obs_per_member = e->obs_per_member;
     a.final_x = e->d_final_x; a.n_final = e->d_n_final; a.status = e->d_status; a.steps_done = e->d_steps_done;
     a.tracks = e->keep ? e->d_tracks : nullptr;

@@ -22,8 +22,11 @@ lib.slam_ens_debug_phases(out, 1)
 ens.run(); ens.sync()
 lib.slam_ens_debug_phases(out, 0)
 names = ["gap", "predict(i) noise+heading+sincos", "predict(ii) Pvv chain | columns", "assoc A per-landmark", "assoc B score+argmin",
-         "classify", "Hn/v copy", "PHt", "S", "symmetrise", "chol+inv+u", "W1, x", "downdate", "add_features", "track/end"]
-tot = sum(out[:15])
+         "classify", "Hn/v copy", "PHt", "S", "symmetrise", "inverse+u (after chol)", "W1, x", "downdate", "add_features", "track/end",
+         "  (i): sincos + GuQGu'", "  (ii): 3x3 chain", "  chol", "  (i): heading chain"]
+names[1] = "predict(i) tail: prefix sums"
+names[2] = "predict(ii) tail: wait helpers"
+tot = sum(out[:19])
 nb = ens.nupdates + 1
 print(f"members {n_runs}: {tot} cycles for member 0, {tot / nb:.0f} per block")
 for k, nm in enumerate(names):
