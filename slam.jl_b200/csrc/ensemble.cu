@@ -196,11 +196,13 @@ __device__ __forceinline__ void ens_mark(int k) {
 #else
 #define ENS_MARK(k)
 #endif
+constexpr int ENS_TRI = 32 * 33 / 2;   // entries of the triangle table
 constexpr int LM_STRIDE = 17;     // association table per landmark: zp[2], inv(S)[4], log det, h[10]
 
 struct EnsSmem {
     double *x, *P, *W, *S, *C, *u, *v, *Hn, *z, *zf, *zn, *bs, *par;
     int *fp, *idf, *cls;
+    unsigned short *tri;   // (i', j' << 8), j' <= i' < 32, row by row: the Cholesky's element order
 };
 
 __host__ __device__ inline int ens_ru4(int a) { return (a + 3) & ~3; }
@@ -212,7 +214,7 @@ __host__ __device__ inline size_t ens_smem_bytes(int ncap, int mmax) {
     const size_t R = 2 * (size_t)mmax;
     size_t d = ens_ru4(ncap) + ens_ru4(ncap * (ncap + 1) / 2) + ens_wdoubles(ncap, mmax) + 2 * ens_ru4((int)(R * R)) +
                2 * ens_ru4((int)R) + ens_ru4(10 * mmax) + 3 * ens_ru4(2 * mmax) + ENS_MAXB * BS + 32;
-    return d * 8 + 3 * (size_t)mmax * 4 + 64;
+    return d * 8 + ens_ru4(3 * mmax) * 4 + ENS_TRI * 2 + 64;
 }
 
 __device__ inline EnsSmem ens_carve(double *base, int ncap, int mmax) {
@@ -235,7 +237,8 @@ __device__ inline EnsSmem ens_carve(double *base, int ncap, int mmax) {
     int *q = reinterpret_cast<int *>(p);
     s.fp = q;  q += mmax;
     s.idf = q; q += mmax;
-    s.cls = q;
+    s.cls = q; q += ens_ru4(3 * mmax) - 2 * mmax;
+    s.tri = reinterpret_cast<unsigned short *>(q);
     return s;
 }
 
@@ -248,6 +251,11 @@ __device__ __noinline__ void ens_sincos(double t, double *s, double *c) {
 __device__ __noinline__ double ens_normal(uint64_t seed, uint32_t run, uint32_t stream, uint32_t idx) {
     return philox_normal(seed, run, stream, idx);
 }
+
+// idx / d for the small index ranges of this kernel (idx < 2^17, quotient < 2^8) without the
+// ~70-cycle integer division: (idx + 0.5) / d is at least 0.5 / d away from an integer, far more
+// than the float rounding error.
+__device__ __forceinline__ int ens_div(int idx, float rinv) { return (int)(((float)idx + 0.5f) * rinv); }
 
 // packed upper triangle, column-major: P(i, j), i <= j, at j(j+1)/2 + i
 __device__ __forceinline__ int cofs(int j) { return (j * (j + 1)) >> 1; }
@@ -533,36 +541,40 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
     }
     __syncthreads();
     ENS_MARK(4);
-    if (tid == 0) {
+    if (warp == 0) {
+        // stable compaction in observation order (src/data-association.jl:43-48) by ballot / popc, and
+        // what update needs of the matched observations: fpos, innovation, the Jacobian's nonzeros
         int m = 0, k = 0;
 #pragma unroll 1
-        for (int i = 0; i < nz; i++) {
-            const int c = sm.cls[i];
+        for (int base = 0; base < nz; base += 32) {
+            const int i = base + lane;
+            const int c = i < nz ? sm.cls[i] : 0;
+            const unsigned mf = __ballot_sync(0xffffffffu, c > 0), mn = __ballot_sync(0xffffffffu, c < 0);
+            const unsigned below = (1u << lane) - 1u;
             if (c > 0) {
-                sm.zf[2 * m] = sm.z[2 * i];
-                sm.zf[2 * m + 1] = sm.z[2 * i + 1];
-                sm.idf[m] = c;
-                m++;
+                const int o = m + __popc(mf & below), jl = c - 1;
+                const double z0 = sm.z[2 * i], z1 = sm.z[2 * i + 1];
+                const double *t = LM + jl * LM_STRIDE;
+                sm.zf[2 * o] = z0;
+                sm.zf[2 * o + 1] = z1;
+                sm.idf[o] = c;
+                sm.fp[o] = 3 + 2 * jl;
+                sm.v[2 * o] = z0 - t[0];
+                sm.v[2 * o + 1] = mpi_to_pi(z1 - t[1]);
+#pragma unroll 1
+                for (int q = 0; q < 10; q++) sm.Hn[10 * o + q] = t[7 + q];
             } else if (c < 0) {
-                sm.zn[2 * k] = sm.z[2 * i];
-                sm.zn[2 * k + 1] = sm.z[2 * i + 1];
-                k++;
+                const int o = k + __popc(mn & below);
+                sm.zn[2 * o] = sm.z[2 * i];
+                sm.zn[2 * o + 1] = sm.z[2 * i + 1];
             }
+            m += __popc(mf);
+            k += __popc(mn);
         }
-        sm.par[8] = m;
-        sm.par[9] = k;
-    }
-    __syncthreads();
-    ENS_MARK(5);
-    const int m = (int)sm.par[8];
-    if (tid < m) {
-        const int jl = sm.idf[tid] - 1;
-        const double *t = LM + jl * LM_STRIDE;
-        sm.fp[tid] = 3 + 2 * jl;
-        sm.v[2 * tid] = sm.zf[2 * tid] - t[0];
-        sm.v[2 * tid + 1] = mpi_to_pi(sm.zf[2 * tid + 1] - t[1]);
-#pragma unroll
-        for (int q = 0; q < 10; q++) sm.Hn[10 * tid + q] = t[7 + q];
+        if (lane == 0) {
+            sm.par[8] = m;
+            sm.par[9] = k;
+        }
     }
     __syncthreads();
     ENS_MARK(6);
@@ -579,9 +591,10 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
     const double Rm[4] = {SIGMA_R * SIGMA_R, 0, 0, SIGMA_B * SIGMA_B};
     double *W = sm.W;
     // PHt = P*H' (five terms per entry, columns 1,2,3,f,f+1); rows n..ldw-1 are zeroed for K6's tiles
+    const float rinv_ldw = 1.0f / (float)ldw, rinv_R = 1.0f / (float)R;
 #pragma unroll 1
     for (int idx = tid; idx < ldw * m; idx += T) {
-        const int o = idx / ldw, i = idx - o * ldw;
+        const int o = ens_div(idx, rinv_ldw), i = idx - o * ldw;
         double w0 = 0.0, w1 = 0.0;
         if (i < n) {
             const double *h = sm.Hn + 10 * o;
@@ -599,7 +612,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
     // S = H*PHt + RR
 #pragma unroll 1
     for (int idx = tid; idx < m * R; idx += T) {
-        const int o = idx / R, k = idx - o * R;
+        const int o = ens_div(idx, rinv_R), k = idx - o * R;
         const double *h = sm.Hn + 10 * o;
         const int f = sm.fp[o];
         const double *wk = W + k * ldw;
@@ -615,7 +628,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
     ENS_MARK(8);
 #pragma unroll 1
     for (int idx = tid; idx < R * R; idx += T) {   // S = (S + S')*0.5
-        const int a = idx % R, b = idx / R;
+        const int b = ens_div(idx, rinv_R), a = idx - b * R;
         if (a < b) {
             const double s = (sm.S[a + b * R] + sm.S[b + a * R]) * 0.5;
             sm.S[a + b * R] = s;
@@ -640,11 +653,24 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
                 sm.S[k + j * R] = ukj;
             }
             __syncwarp();
+            if (R <= 32) {
+                // trailing update, one ELEMENT per lane: entry e of the triangle table is (i', j') with
+                // j' <= i', rows counted from the bottom (i = R-1-i'), so the elements below row k are the
+                // first r(r+1)/2 entries, r = R-1-k.  Same subtraction per element as the column loop.
+                const int r = R - 1 - k;
 #pragma unroll 1
-            for (int j = k + 1 + lane; j < R; j += 32) {
-                const double ukj = sm.S[k + j * R];
+                for (int e = lane; e < r * (r + 1) / 2; e += 32) {
+                    const int t = sm.tri[e];
+                    const int i = R - 1 - (t & 0xff), j = R - 1 - (t >> 8);
+                    sm.S[i + j * R] -= sm.S[k + i * R] * sm.S[k + j * R];
+                }
+            } else {
 #pragma unroll 1
-                for (int i = k + 1; i <= j; i++) sm.S[i + j * R] -= sm.S[k + i * R] * ukj;
+                for (int j = k + 1 + lane; j < R; j += 32) {
+                    const double ukj = sm.S[k + j * R];
+#pragma unroll 1
+                    for (int i = k + 1; i <= j; i++) sm.S[i + j * R] -= sm.S[k + i * R] * ukj;
+                }
             }
             __syncwarp();
         }
@@ -657,12 +683,12 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
 #pragma unroll 1
                 for (int i = j - 1; i >= 0; i--) {
                     double a = 0;
-#pragma unroll 1
+#pragma unroll 4
                     for (int k = i + 1; k <= j; k++) a += sm.S[i + k * R] * sm.C[k + j * R];
                     sm.C[i + j * R] = -a / sm.S[i + i * R];
                 }
                 double a = 0;
-#pragma unroll 1
+#pragma unroll 4
                 for (int l = 0; l <= j; l++) a += sm.C[l + j * R] * sm.v[l];
                 sm.u[j] = a;
             }
@@ -679,7 +705,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
 #pragma unroll 1
         for (int k = R - 1; k >= 0; k--) {
             double a = 0;
-#pragma unroll 1
+#pragma unroll 4
             for (int l = 0; l <= k; l++) a += W[l * ldw + i] * sm.C[l + k * R];
             W[k * ldw + i] = a;
         }
@@ -790,6 +816,13 @@ k_ensemble(EnsArgs a) {
     const uint32_t run = a.run0 + (uint32_t)member;
     for (int idx = tid; idx < a.npk; idx += T) sm.P[idx] = 0.0;   // zeros(3,3); spare capacity zeroed
     for (int idx = tid; idx < a.ncap; idx += T) sm.x[idx] = 0.0;
+#pragma unroll 1
+    for (int e = tid; e < ENS_TRI; e += T) {
+        int ip = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
+        while (ip * (ip + 1) / 2 > e) ip--;
+        while ((ip + 1) * (ip + 2) / 2 <= e) ip++;
+        sm.tri[e] = (unsigned short)(ip | ((e - ip * (ip + 1) / 2) << 8));
+    }
     __syncthreads();
     int n = 3;
     int status = SLAM_OK;
