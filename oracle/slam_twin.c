@@ -230,13 +230,18 @@ int twin_update(double *x, double *P, int n, int ld, const double *zf, int m, co
         S[j + (size_t)j * r] = sqrt(d);
     }
     if (rc == 0) {
-        /* C = inv(U), upper triangular, column by column */
+        /* C = inv(U), upper triangular, in the order of LAPACK's unblocked dtrti2 ('U', 'N'), which
+         * is what inv(::UpperTriangular) reaches for these sizes: column j = the already inverted
+         * leading block times U[0:j, j] (reference dtrmv: y_i = x_i*T_ii + sum_{jj>i} x_jj*T_i,jj,
+         * jj ascending), scaled by -1/U[j][j]. */
         for (int j = 0; j < r; j++) {
-            C[j + (size_t)j * r] = 1.0 / S[j + (size_t)j * r];
-            for (int i = j - 1; i >= 0; i--) {
-                double a = 0;
-                for (int k = i + 1; k <= j; k++) a += S[i + (size_t)k * r] * C[k + (size_t)j * r];
-                C[i + (size_t)j * r] = -a / S[i + (size_t)i * r];
+            double cjj = 1.0 / S[j + (size_t)j * r];
+            C[j + (size_t)j * r] = cjj;
+            double ajj = -cjj;
+            for (int i = 0; i < j; i++) {
+                double y = S[i + (size_t)j * r] * C[i + (size_t)i * r];
+                for (int jj = i + 1; jj < j; jj++) y += S[jj + (size_t)j * r] * C[i + (size_t)jj * r];
+                C[i + (size_t)j * r] = y * ajj;
             }
         }
         /* W1 = PHt*C ; u = C'*v ; x += W1*u  ( = W*v with W = W1*C' ) */

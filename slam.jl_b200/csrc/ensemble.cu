@@ -179,7 +179,7 @@ constexpr int ENS_MAXB = 16;      // steps per block
 constexpr int BS = 24;            // doubles of block scratch per step
 // block scratch slots (per step of the block)
 constexpr int B_V = 0, B_G = 1, B_SG = 2, B_CG = 3, B_TPHI = 4, B_PHI0 = 5, B_VTS = 7, B_VTC = 8, B_N = 9,
-              B_X0 = 18, B_X1 = 19, B_PHI = 20;
+              B_X0 = 18, B_X1 = 19, B_PHI = 20, B_GT = 21;
 #ifdef ENS_TIMING   // developer build (SLAMCUDA_DEFS=-DENS_TIMING): cycles per phase of member 0, thread 0
 __device__ long long g_ens_phase[24];
 __device__ __forceinline__ void ens_mark(int k) {
@@ -323,34 +323,33 @@ __device__ void ens_predict_block(const EnsSmem &sm, int n, int len, int nz) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     double *bs = sm.bs;
     if (warp == 0) {
-        {   // chain (a): heading.  Every lane runs the chain (branch-free wrap, the step's increment
-            // comes by shuffle); lane s keeps the heading before / after step s.
-            const double tph = lane < len ? bs[lane * BS + B_TPHI] : 0.0;
-            double phi = sm.x[2], k0 = 0.0, k1 = 0.0;
+        if (lane == 0) {   // chain (a): heading; one lane, branch-free wrap, increments loaded a step ahead
+            double phi = sm.x[2], tn = bs[B_TPHI];
 #pragma unroll 1
             for (int s = 0; s < len; s++) {
-                const double t = phi + __shfl_sync(0xffffffffu, tph, s);
+                const double t = phi + tn;
+                tn = bs[(s + 1 < len ? s + 1 : s) * BS + B_TPHI];
                 const double tm = t - 2 * SLAM_PI, tp = t + 2 * SLAM_PI;      // mpi_to_pi, src/common.jl:102-110
                 const double w = t > SLAM_PI ? tm : (t < -SLAM_PI ? tp : t);
-                if (lane == s) { k0 = phi; k1 = w; }
+                bs[s * BS + B_PHI0] = phi;
+                bs[s * BS + B_PHI] = w;
                 phi = w;
             }
-            if (lane < len) {
-                bs[lane * BS + B_PHI0] = k0;
-                bs[lane * BS + B_PHI] = k1;
-            }
+            sm.x[2] = phi;
         }
+        __syncwarp();
         ENS_MARK(18);   // heading chain done
-        double vts = 0.0, vtc = 0.0;
         if (lane < len) {
             double *b = bs + lane * BS;
             const double v = b[B_V], g = b[B_G], phi = b[B_PHI0];
             double s, c;
             ens_sincos(g + phi, &s, &c);
-            vts = v * DT * s;
-            vtc = v * DT * c;
+            const double vts = v * DT * s, vtc = v * DT * c;
             b[B_VTS] = vts;
             b[B_VTC] = vtc;
+            b[B_GT] = -vts;       // Gv[0][2], Gv[1][2], Gv[2][2] - 1 of this step for the 3x3 chain
+            b[B_GT + 1] = vtc;
+            b[B_GT + 2] = 0.0;
             // Gu*Q*Gu' (src/ekf.jl:27-29,32)
             const double Q[4] = {SIGMA_SPEED * SIGMA_SPEED, 0, 0, SIGMA_STEER * SIGMA_STEER};
             const double Gu[3][2] = {{DT * c, -vts}, {DT * s, vtc}, {DT * b[B_SG] / WHEELBASE, v * DT * b[B_CG] / WHEELBASE}};
@@ -364,25 +363,7 @@ __device__ void ens_predict_block(const EnsSmem &sm, int n, int len, int nz) {
 #pragma unroll
                 for (int j = 0; j < 3; j++) b[B_N + 3 * i + j] = GQ[i][0] * Gu[j][0] + GQ[i][1] * Gu[j][1];
         }
-        ENS_MARK(15);   // heading chain + sin/cos + Gu*Q*Gu' done (prefix sums follow)
-        // x += vtc_s, y += vts_s one step after the other (every lane runs both chains; lane s keeps
-        // the pose after step s)
-        double ax = sm.x[0], ay = sm.x[1], kx = 0.0, ky = 0.0;
-#pragma unroll 1
-        for (int s = 0; s < len; s++) {
-            ax = ax + __shfl_sync(0xffffffffu, vtc, s);
-            ay = ay + __shfl_sync(0xffffffffu, vts, s);
-            if (lane == s) { kx = ax; ky = ay; }
-        }
-        if (lane < len) {
-            bs[lane * BS + B_X0] = kx;
-            bs[lane * BS + B_X1] = ky;
-        }
-        if (lane == 0) {
-            sm.x[0] = ax;
-            sm.x[1] = ay;
-            sm.x[2] = bs[(len - 1) * BS + B_PHI];
-        }
+        ENS_MARK(15);   // heading chain + sin/cos + Gu*Q*Gu' done
     }
     __syncthreads();
     ENS_MARK(1);
@@ -393,29 +374,35 @@ __device__ void ens_predict_block(const EnsSmem &sm, int n, int len, int nz) {
         const int l9 = lane < 9 ? lane : 0;
         const int i = l9 / 3, j = l9 % 3;
         double p = psym(sm.P, i, j);
-        // the step's scalars are loaded one iteration ahead so that only shuffle + 5 FP64 operations
-        // sit on the loop-carried chain
-        double nvts = -bs[B_VTS], vtc = bs[B_VTC], nn = bs[B_N + l9];
-        const long long mi_n = i == 0 ? -1LL : 0LL, mi_v = i == 1 ? -1LL : 0LL;
-        const long long mj_n = j == 0 ? -1LL : 0LL, mj_v = j == 1 ? -1LL : 0LL;
+        // the step's scalars (gi, gj from the table phase (i) left, the noise term) are loaded one
+        // iteration ahead so that only shuffle + 5 FP64 operations sit on the loop-carried chain
+        double gi = bs[B_GT + i], gj = bs[B_GT + j], nn = bs[B_N + l9];
 #pragma unroll 1
         for (int s = 0; s < len; s++) {
-            const int sn = s + 1 < len ? s + 1 : s;
-            const double nvts_n = -bs[sn * BS + B_VTS], vtc_n = bs[sn * BS + B_VTC], nn_n = bs[sn * BS + B_N + l9];
-            // gi = Gv[i][2], gj = Gv[j][2] picked with bit masks (no branches inside the chain)
-            const long long bn = __double_as_longlong(nvts), bv = __double_as_longlong(vtc);
-            const double gi = __longlong_as_double((bn & mi_n) | (bv & mi_v));
-            const double gj = __longlong_as_double((bn & mj_n) | (bv & mj_v));
+            const double *bn = bs + (s + 1 < len ? s + 1 : s) * BS;
+            const double gi_n = bn[B_GT + i], gj_n = bn[B_GT + j], nn_n = bn[B_N + l9];
             const double pj2 = __shfl_sync(0xffffffffu, p, 3 * j + 2), pi2 = __shfl_sync(0xffffffffu, p, 3 * i + 2),
                          p22 = __shfl_sync(0xffffffffu, p, 8);
             const double aj = p + gi * pj2;
             const double a2 = pi2 + gi * p22;
             p = (aj + a2 * gj) + nn;
-            nvts = nvts_n; vtc = vtc_n; nn = nn_n;
+            gi = gi_n; gj = gj_n; nn = nn_n;
         }
         if (lane < 9 && i <= j) sm.P[cofs(j) + i] = p;
         ENS_MARK(16);   // 3x3 chain done (barrier wait for the helper warps follows)
     } else {
+        // x += vtc_s (lane 0), y += vts_s (lane 1) of the first helper warp, one step after the other
+        if (tid - 32 < 2) {
+            const int slot = tid == 32 ? B_VTC : B_VTS;
+            double acc = sm.x[tid - 32], vn = bs[slot];
+#pragma unroll 1
+            for (int s = 0; s < len; s++) {
+                acc = acc + vn;
+                vn = bs[(s + 1 < len ? s + 1 : s) * BS + slot];
+                bs[s * BS + B_X0 + (tid - 32)] = acc;
+            }
+            sm.x[tid - 32] = acc;
+        }
         // chain (c): rows 0..2 of map column jc
 #pragma unroll 1
         for (int jc = 3 + tid - 32; jc < n; jc += T - 32) {
@@ -431,6 +418,7 @@ __device__ void ens_predict_block(const EnsSmem &sm, int n, int len, int nz) {
             col[1] = p1;
         }
         if (nz > 0) {
+            asm volatile("bar.sync 1, %0;" ::"r"(T - 32) : "memory");   // helper warps: the pose is final
             const int Nf = (n - 3) / 2;
 #pragma unroll 1
             for (int jl = tid - 32; jl < Nf; jl += T - 32) {
@@ -509,8 +497,9 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
 #pragma unroll 1
     for (int i = warp; i < nz; i += T / 32) {
         const double z0 = sm.z[2 * i], z1 = sm.z[2 * i + 1];
-        double nbest = INFINITY, outer = INFINITY;
+        double nbest = INFINITY;
         int jbest = 0;
+        bool near = false;   // some landmark has nis <= gate2  <=>  !(outer > gate2) for outer = min nis
 #pragma unroll 1
         for (int jl = lane; jl < Nf; jl += 32) {
             const double *t = LM + jl * LM_STRIDE;
@@ -524,19 +513,19 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
                 nbest = nd;
                 jbest = jl + 1;
             }
-            if (nis < outer) outer = nis;
+            near = near || nis <= GATE2;
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const double onb = __shfl_xor_sync(0xffffffffu, nbest, o);
-            const int ojb = __shfl_xor_sync(0xffffffffu, jbest, o);
-            const double oout = __shfl_xor_sync(0xffffffffu, outer, o);
-            if (ojb != 0 && (jbest == 0 || onb < nbest || (onb == nbest && ojb < jbest))) {
-                nbest = onb;
-                jbest = ojb;
-            }
-            if (oout < outer) outer = oout;
-        }
+        // warp argmin of (nd, j) with three 32-bit min reductions (REDUX): nd as an order-preserving
+        // 64-bit key (hi word, then lo word among the hi winners), then the lowest j among equal keys
+        const long long nb = __double_as_longlong(nbest + 0.0);   // -0 -> +0
+        const unsigned long long key =
+            jbest ? (nb < 0 ? ~(unsigned long long)nb : ((unsigned long long)nb | 0x8000000000000000ull)) : ~0ull;
+        const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+        const unsigned mhi = __reduce_min_sync(0xffffffffu, hi);
+        const unsigned mlo = __reduce_min_sync(0xffffffffu, hi == mhi ? lo : 0xffffffffu);
+        const unsigned jm = __reduce_min_sync(0xffffffffu, (jbest && hi == mhi && lo == mlo) ? (unsigned)jbest : 0xffffffffu);
+        jbest = jm == 0xffffffffu ? 0 : (int)jm;
+        const double outer = __any_sync(0xffffffffu, near) ? 0.0 : INFINITY;
         if (lane == 0) sm.cls[i] = jbest != 0 ? jbest : (outer > GATE2 ? -1 : 0);
     }
     __syncthreads();
@@ -561,7 +550,7 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
                 sm.fp[o] = 3 + 2 * jl;
                 sm.v[2 * o] = z0 - t[0];
                 sm.v[2 * o + 1] = mpi_to_pi(z1 - t[1]);
-#pragma unroll 1
+#pragma unroll
                 for (int q = 0; q < 10; q++) sm.Hn[10 * o + q] = t[7 + q];
             } else if (c < 0) {
                 const int o = k + __popc(mn & below);
@@ -677,20 +666,34 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
         if (lane == 0) sm.par[10] = fail;
         ENS_MARK(17);   // Cholesky done (inverse + u follow)
         if (!fail) {
+            // C = inv(U) in the order of LAPACK's unblocked dtrti2: C[i][j] = (U[i][j]*C[i][i] +
+            // sum_{i<jj<j} U[jj][j]*C[i][jj]) * (-1/U[j][j]).  Row i of C depends on row i alone, so
+            // lane i builds its own row with no exchange; the reciprocals are taken up front.
 #pragma unroll 1
             for (int j = lane; j < R; j += 32) {
-                sm.C[j + j * R] = 1.0 / sm.S[j + j * R];
+                const double cjj = 1.0 / sm.S[j + j * R];
+                sm.C[j + j * R] = cjj;
+                sm.u[j] = -cjj;   // ajj, parked in u until u is formed below
+            }
+            __syncwarp();
 #pragma unroll 1
-                for (int i = j - 1; i >= 0; i--) {
-                    double a = 0;
+            for (int i = lane; i < R; i += 32) {
+                const double cii = sm.C[i + i * R];
+#pragma unroll 1
+                for (int j = i + 1; j < R; j++) {
+                    double y = sm.S[i + j * R] * cii;
 #pragma unroll 4
-                    for (int k = i + 1; k <= j; k++) a += sm.S[i + k * R] * sm.C[k + j * R];
-                    sm.C[i + j * R] = -a / sm.S[i + i * R];
+                    for (int jj = i + 1; jj < j; jj++) y += sm.S[jj + j * R] * sm.C[i + jj * R];
+                    sm.C[i + j * R] = y * sm.u[j];
                 }
+            }
+            __syncwarp();
+#pragma unroll 1
+            for (int j = lane; j < R; j += 32) {
                 double a = 0;
 #pragma unroll 4
                 for (int l = 0; l <= j; l++) a += sm.C[l + j * R] * sm.v[l];
-                sm.u[j] = a;
+                sm.u[j] = a;          // ajj is dead after the barrier above
             }
         }
     } else if (stage_b < a.nblocks) {
