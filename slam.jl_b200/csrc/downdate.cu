@@ -233,8 +233,13 @@ int downdate_chunk_width(int R) {
 // n_pad is a multiple of DD_ROW_PAD and rows >= n are zero.
 int launch_downdate_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad,
                          int R, int variant, cudaStream_t s, long long *launches) {
-    (void)variant;
     if (r1 <= r0) return SLAM_OK;
+    // variant 0 = auto: the DMMA tile kernel once the rank makes the update a dense contraction
+    // (measured cross-over, profiles/r1_k6_dmma.md), the FMA kernel below it; 1 / 2 force one.
+    int min_rank = 33;   // above one FMA pass (32 ranks): 19-30 TFLOP/s DMMA vs 13-18 TFLOP/s FMA
+    if (const char *e = getenv("SLAM_K6_DMMA_MIN_RANK")) min_rank = atoi(e);
+    if ((variant == 2 || (variant == 0 && R >= min_rank)) && downdate_dmma_usable(R, ldb))
+        return launch_downdate_dmma_rows(Pb, ldb, r0, r1, n, W1c, n_pad, R, s, launches);
     const int RC = downdate_chunk_width(R);
     const int nchunks = (R + RC - 1) / RC;
     const DdCfg cfg = pick_cfg(RC);

@@ -14,6 +14,11 @@ int launch_downdate(double *P, size_t ld, int n, const double *W1c, int n_pad, i
 int launch_downdate_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad,
                          int R, int variant, cudaStream_t s, long long *launches);
 
+// FP64 tensor-core variant (downdate_dmma.cu): same contract; usable for the 32-wide chunk layout
+bool downdate_dmma_usable(int R, size_t ldb);
+int launch_downdate_dmma_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad, int R,
+                              cudaStream_t s, long long *launches);
+
 // ---- K2 (gate.cu, compiled with -fmad=false) ---------------------------------------------
 struct GateOut {           // device-side result of one associate() call
     int m, k;              // counts

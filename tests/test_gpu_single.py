@@ -271,3 +271,37 @@ def test_landmark_ellipses(sc, nf):
     st = sc.DeviceEKFSlamState(x, P, n_max=len(x))
     assert np.array_equal(sc.compute_landmark_ellipses(st), ell)
     st.h.close()
+
+
+@pytest.mark.parametrize("nf,m", [(1000, 13), (1000, 16), (1000, 20), (1000, 32), (1000, 64), (333, 16)])
+def test_update_rank_sweep_dmma(sc, nf, m):
+    """The FP64 tensor-core downdate (mma.sync m8n8k4) against the FMA kernel and the numpy literal
+    oracle at ranks 26..128; the MMA's internal summation order differs from the k-ascending fma
+    chain, so FMA vs DMMA agree to rounding (1e-12 relative), both within 1e-9 of the oracle."""
+    from slamcuda._ffi import lib, check
+    from slamcuda.slam import _Handle
+    k = ref.sim_constants()
+    R = k["R"]
+    rng = np.random.default_rng(7 * nf + m)
+    x, P = _random_state(rng, nf)
+    ids = rng.choice(nf, size=m, replace=False) + 1
+    z = np.zeros((2, m))
+    for c, idf in enumerate(ids):
+        zp, _ = ref.predict_observation(x, int(idf))
+        z[:, c] = zp + rng.normal(0, [0.1, 0.01])
+    xo, Po = ref.update(x, P, z, R, ids)
+    out = {}
+    for variant in (1, 2):
+        h = _Handle(0, len(x))
+        check(lib.slam_set_downdate_variant(h.ptr, variant))
+        h.set_state(x, P)
+        h.update(z, R, ids)
+        out[variant] = h.get_state()
+        h.close()
+    e_fd = rel_err(out[2][1], out[1][1])
+    print(f"\n[dmma n={len(x)} R={2 * m}] FMA vs DMMA P rel {e_fd:.2e}; DMMA vs oracle x {rel_err(out[2][0], xo):.2e} "
+          f"P {rel_err(out[2][1], Po):.2e}")
+    assert np.array_equal(out[1][0], out[2][0])          # x does not depend on the downdate kernel
+    assert e_fd < 1e-12
+    assert rel_err(out[2][0], xo) < STEP_TOL and rel_err(out[2][1], Po) < STEP_TOL
+    assert np.array_equal(out[2][1], out[2][1].T)

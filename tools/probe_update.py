@@ -15,11 +15,13 @@ from slamcuda._ffi import lib, check, dptr, iptr  # noqa: E402
 nl = int(sys.argv[1]) if len(sys.argv) > 1 else 10000
 ms_list = [int(a) for a in sys.argv[2].split(",")] if len(sys.argv) > 2 else [1, 4, 8, 16]
 steps = int(sys.argv[3]) if len(sys.argv) > 3 else 20
+variant = int(sys.argv[4]) if len(sys.argv) > 4 else 0     # 0 auto, 1 FMA kernel, 2 DMMA kernel
 n = 3 + 2 * nl
 side = (nl / 0.0035) ** 0.5
 R = np.array([0.01, 0, 0, (np.pi / 180) ** 2])
 h = C.c_void_p()
 check(lib.slam_create(0, n, C.byref(h)))
+check(lib.slam_set_downdate_variant(h, variant))
 stream = torch.cuda.ExternalStream(lib.slam_stream(h))
 for m in ms_list:
     check(lib.slam_synth_state(h, nl, side, 2))
@@ -51,6 +53,8 @@ for m in ms_list:
     check(lib.slam_profile(h, 0))
     k6ms = k6.value / max(cnt.value, 1)
     gb = 8.0 * n * (n + 1) / 1e9
+    tf = 2.0 * m * n * (n + 1) / (k6ms * 1e-3) / 1e12
+    print(f"variant={variant} K6 {tf:.1f} TFLOP/s  ", end="")
     print(f"nl={nl} n={n} m={m}: assoc_ok={ok} (m={mm.value},k={kk.value}, {t_assoc*1e3:.2f} ms)  "
           f"step {ms:.3f} ms  K6 {k6ms:.3f} ms  K6 {gb / (k6ms * 1e-3):.0f} GB/s  step {1e3/ms:.1f} upd/s", flush=True)
 lib.slam_destroy(h)
