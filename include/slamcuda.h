@@ -222,6 +222,9 @@ int slam_shard_associate(slam_shard_t *s, const double *z, int nz, const double 
                          double gate2, double *zf, int64_t *idf, int *m, double *zn, int *k);
 int slam_shard_update(slam_shard_t *s, const double *zf, int m, const double R[4],
                       const int64_t *idf);
+/* add_features -- src/ekf.jl:84-122 on the sharded covariance: rows 0..2 of P are broadcast from
+ * rank 0, every rank fills its own rows of the 2k new columns.  Collective: call on every rank. */
+int slam_shard_add_features(slam_shard_t *s, const double *zn, int k, const double R[4]);
 int slam_shard_update_resident(slam_shard_t *s, const double *d_zf, int m, const double R[4],
                                const int64_t *d_idf);
 int slam_shard_sync(slam_shard_t *s);

@@ -750,3 +750,117 @@ extern "C" int slam_shard_associate(slam_shard_t *s, const double *z, int nz, co
     memcpy(zn, hzn, sizeof(double) * 2 * (*k));
     return SLAM_OK;
 }
+
+// ---------------------------------------------------------------------------------------
+// add_features (src/ekf.jl:84-122) on the sharded covariance.  The new columns are local on every
+// rank (a block stores its rows of EVERY column); what a rank lacks are rows 0..2 of the existing
+// columns, which rank 0 broadcasts (the same 24 n bytes associate uses).  Every rank then fills its
+// own rows of the 2k new columns; the owner of the new rows writes the 2x2 diagonal blocks.  x is
+// replicated and every rank appends the same values.  Same expressions as the single-filter K7
+// (filter.cu k_augment), so x and P stay bit-identical to the single-filter path.
+// ---------------------------------------------------------------------------------------
+constexpr int SHA_Q = 32;        // new landmarks per launch
+constexpr int SHA_THREADS = 256;
+
+__global__ void __launch_bounds__(SHA_THREADS)
+k_sh_augment(double *x, const double *__restrict__ P3, int npad, double *Pb, size_t ldb, int lo, int hi_new, int n0,
+             const double *__restrict__ zn, int kq, double R0, double R1, double R2, double R3, int write_x) {
+    __shared__ double sGv[SHA_Q][2];
+    __shared__ double sGP[SHA_Q][2][3];
+    __shared__ double sPvv[9];
+    if (threadIdx.x < 9) {
+        const int r = threadIdx.x / 3, c = threadIdx.x % 3;
+        sPvv[threadIdx.x] = r <= c ? P3[(size_t)r * npad + c] : P3[(size_t)c * npad + r];
+    }
+    __syncthreads();
+    const double xv = x[0], yv = x[1], phi = x[2];
+    if (threadIdx.x < kq) {
+        const int q = threadIdx.x;
+        const double r = zn[2 * q], b = zn[2 * q + 1];
+        const double s = sin(phi + b), c = cos(phi + b);
+        const double g0 = -r * s, g1 = r * c;
+        sGv[q][0] = g0;
+        sGv[q][1] = g1;
+        const double Gv[2][3] = {{1, 0, g0}, {0, 1, g1}};
+        for (int a = 0; a < 2; a++)
+            for (int j = 0; j < 3; j++)
+                sGP[q][a][j] = Gv[a][0] * sPvv[0 * 3 + j] + Gv[a][1] * sPvv[1 * 3 + j] + Gv[a][2] * sPvv[2 * 3 + j];
+        const int len = n0 + 2 * q;
+        if (write_x && blockIdx.x == 0 && blockIdx.y == q) {
+            x[len] = xv + r * c;
+            x[len + 1] = yv + r * s;
+        }
+        // the 2x2 diagonal block, by the owner of row len (a landmark's two rows never straddle blocks)
+        if (blockIdx.x == 0 && blockIdx.y == q && len >= lo && len < hi_new) {
+            const double Gz[2][2] = {{c, -r * s}, {s, r * c}};
+            const double Rm[4] = {R0, R1, R2, R3};
+            double GR[2][2];
+            for (int a = 0; a < 2; a++)
+                for (int j = 0; j < 2; j++) GR[a][j] = Gz[a][0] * Rm[0 + 2 * j] + Gz[a][1] * Rm[1 + 2 * j];
+            for (int a = 0; a < 2; a++)
+                for (int bb = a; bb < 2; bb++) {
+                    const double t1 = sGP[q][a][0] * Gv[bb][0] + sGP[q][a][1] * Gv[bb][1] + sGP[q][a][2] * Gv[bb][2];
+                    const double t2 = GR[a][0] * Gz[bb][0] + GR[a][1] * Gz[bb][1];
+                    Pb[(size_t)(len + a - lo) + (size_t)(len + bb) * ldb] = t1 + t2;
+                }
+        }
+    }
+    __syncthreads();
+    const int q = blockIdx.y;
+    if (q >= kq) return;
+    const int len = n0 + 2 * q;
+    const int j = lo + blockIdx.x * SHA_THREADS + threadIdx.x;   // an existing row of this block
+    if (j >= len || j >= hi_new) return;
+    double c0, c1, c2;   // P[1:3, j]
+    if (j < 3) {
+        c0 = sPvv[0 * 3 + j]; c1 = sPvv[1 * 3 + j]; c2 = sPvv[2 * 3 + j];
+    } else if (j < n0) {
+        c0 = P3[j]; c1 = P3[(size_t)npad + j]; c2 = P3[(size_t)2 * npad + j];
+    } else {   // a landmark added earlier in this launch
+        const int qq = (j - n0) / 2, a = (j - n0) % 2;
+        c0 = sGP[qq][a][0]; c1 = sGP[qq][a][1]; c2 = sGP[qq][a][2];
+    }
+    const double g0 = sGv[q][0], g1 = sGv[q][1];
+    const double t0 = 1.0 * c0 + 0.0 * c1 + g0 * c2;
+    const double t1 = 0.0 * c0 + 1.0 * c1 + g1 * c2;
+    Pb[(size_t)(j - lo) + (size_t)len * ldb] = t0;
+    Pb[(size_t)(j - lo) + (size_t)(len + 1) * ldb] = t1;
+}
+
+extern "C" int slam_shard_add_features(slam_shard_t *s, const double *zn, int k, const double R[4]) {
+    S_CHECK(s);
+    ARG_CHECK(k >= 0 && R, "bad argument");
+    if (k == 0) return SLAM_OK;
+    ARG_CHECK(zn != nullptr, "NULL zn");
+    if (k > SLAM_MAX_OBS || s->n + 2 * k > s->n_max) {
+        slam_set_error("slam_shard_add_features: n + 2k = %d exceeds capacity n_max = %d", s->n + 2 * k, s->n_max);
+        return SLAM_ERR_CAPACITY;
+    }
+    cudaStream_t st = s->stream;
+    double *hz = (double *)((char *)s->h_pin + 256);
+    CUDA_TRY(cudaStreamSynchronize(st));
+    memcpy(hz, zn, sizeof(double) * 2 * k);
+    CUDA_TRY(cudaMemcpyAsync(s->d_zn, hz, sizeof(double) * 2 * k, cudaMemcpyHostToDevice, st));
+    for (int q0 = 0; q0 < k; q0 += SHA_Q) {
+        const int kq = std::min(SHA_Q, k - q0);
+        const int n0 = s->n, n1 = n0 + 2 * kq;
+        if (s->rank == 0) {
+            k_sh_rows012<<<(s->npad + 255) / 256, 256, 0, st>>>(s->d_Pb[0], s->ldb, n0, s->npad, s->d_P3);
+            s->launches++;
+        }
+        if (s->world > 1) NCCL_TRY(g_nccl.Broadcast(s->d_P3, s->d_P3, (size_t)3 * s->npad, ncclFloat64, 0, s->comm, st));
+        int lo[2], hi[2];
+        plan_blocks(n1, s->hb, s->world, s->rank, lo, hi);   // ownership once the new rows exist
+        for (int b = 0; b < 2; b++) {
+            const int rows = std::max(hi[b] - lo[b], 0);
+            dim3 grid(std::max(1, (rows + SHA_THREADS - 1) / SHA_THREADS), kq);
+            k_sh_augment<<<grid, SHA_THREADS, 0, st>>>(s->d_x, s->d_P3, s->npad, s->d_Pb[b], s->ldb, lo[b], hi[b], n0,
+                                                       s->d_zn + 2 * q0, kq, R[0], R[1], R[2], R[3], b == 0);
+            s->launches++;
+        }
+        s->n = n1;
+        s->lo[0] = lo[0]; s->lo[1] = lo[1]; s->hi[0] = hi[0]; s->hi[1] = hi[1];
+    }
+    CUDA_TRY(cudaGetLastError());
+    return SLAM_OK;
+}

@@ -10,6 +10,16 @@ import numpy as np
 from ._ffi import lib, check, dptr
 
 
+def member_range(total_runs: int, world: int, rank: int):
+    """(run0, count) of the members rank runs when total_runs are split over world ranks: contiguous
+    run ids, the first total_runs % world ranks take one more.  A member's Philox streams are keyed
+    by its run id alone, so the split does not change any member's result (no collective)."""
+    if world < 1 or not 0 <= rank < world or total_runs < 0:
+        raise ValueError("member_range: need 0 <= rank < world and total_runs >= 0")
+    base, rem = divmod(total_runs, world)
+    return rank * base + min(rank, rem), base + (1 if rank < rem else 0)
+
+
 class Ensemble:
     def __init__(self, waypoints, landmarks, n_runs: int, seed: int = 0, run0: int = 0, nlaps: int = 2,
                  device: int = 0, extra_landmarks: int | None = None, threads: int | None = None):

@@ -99,6 +99,14 @@ class ShardedFilter:
         r = np.ascontiguousarray(np.asarray(R, dtype=float).reshape(2, 2).T).reshape(-1)
         check(lib.slam_shard_update(self.ptr, dptr(zc), m, dptr(r), iptr(ids)))
 
+    def add_features(self, zn, R):
+        """src/ekf.jl:84-122 on the sharded covariance (collective: every rank calls it)."""
+        zn = np.asarray(zn, dtype=float).reshape(2, -1)
+        k = zn.shape[1]
+        zc = np.ascontiguousarray(zn.T).reshape(-1)
+        r = np.ascontiguousarray(np.asarray(R, dtype=float).reshape(2, 2).T).reshape(-1)
+        check(lib.slam_shard_add_features(self.ptr, dptr(zc), k, dptr(r)))
+
     def sync(self):
         check(lib.slam_shard_sync(self.ptr))
 

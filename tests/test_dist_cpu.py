@@ -1,0 +1,107 @@
+"""world_size-2 (and 3) `gloo` tests of the host logic behind the two multi-GPU modes, on CPU:
+the row-block partition of the sharded covariance, the NCCL-unique-id hand-off, the ensemble's
+run-id split, and the bench contract's reference arm under torch.distributed.run (rank 0 alone
+works and prints).  The device side of the same paths is tests/test_gpu_shard.py and
+tools/shard_check.py (torchrun on 2+ GPUs)."""
+import json
+import os
+import socket
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def torchrun(world: int, script: str, *args: str, timeout: int = 600):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(free_port()), script, *args]
+    env = dict(os.environ, OMP_NUM_THREADS="2")
+    p = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=timeout)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-4000:]
+    return p.stdout
+
+
+@pytest.fixture(scope="module", params=[2, 3])
+def dist_result(request):
+    world = request.param
+    out = torchrun(world, "tests/dist_worker.py")
+    lines = [ln for ln in out.splitlines() if ln.startswith("DIST_CHECK ")]
+    assert len(lines) == 1, out[-2000:]
+    return world, json.loads(lines[0][len("DIST_CHECK "):])
+
+
+def test_row_block_partition(dist_result):
+    """2W blocks, rank r owns blocks r and 2W-1-r: rows covered exactly once, block edges never
+    split a landmark's two rows, and the upper-triangle work per rank is balanced."""
+    world, res = dist_result
+    for n_str, plans in res["plans"].items():
+        n = int(n_str)
+        owner = np.full(n, -1)
+        work = np.zeros(world)
+        for r, blocks in enumerate(plans):
+            assert len(blocks) == 2
+            for lo, hi in blocks:
+                if hi <= lo:
+                    continue
+                assert 0 <= lo < hi <= n
+                assert np.all(owner[lo:hi] == -1), (n, r, lo, hi)
+                owner[lo:hi] = r
+                if lo > 0:
+                    assert (lo - 3) % 2 == 0 or lo < 3, (n, lo)      # lo is a landmark's first row
+                work[r] += sum(n - i for i in (lo, hi - 1)) * (hi - lo) / 2.0   # entries j >= i
+        assert np.all(owner >= 0), n
+        if n >= 20003:
+            assert work.max() / work.mean() < 1.05, (n, work)
+
+
+def test_unique_id_handoff(dist_result):
+    world, res = dist_result
+    uids = res["uids"]
+    assert len(uids) == world and len(set(uids)) == 1
+    assert len(bytes.fromhex(uids[0])) == 128 and any(bytes.fromhex(uids[0]))
+
+
+def test_member_split_is_result_neutral(dist_result):
+    world, res = dist_result
+    poses, nfin, cover = [], [], []
+    for r0, cnt, fp, nf in res["members"]:
+        cover += list(range(r0, r0 + cnt))
+        poses += fp
+        nfin += nf
+    one_fp, one_nf = res["members_one_process"]
+    assert cover == list(range(len(one_nf)))
+    assert poses == one_fp and nfin == one_nf     # bit-equal: JSON round-trips doubles exactly
+
+
+def test_member_range_edges():
+    sys.path.insert(0, str(ROOT / "slam.jl_b200"))
+    from slamcuda.ensemble import member_range
+    for total in (0, 1, 7, 8, 8192, 8193):
+        for world in (1, 2, 3, 8):
+            spans = [member_range(total, world, r) for r in range(world)]
+            assert spans[0][0] == 0 and sum(c for _, c in spans) == total
+            assert all(spans[i][0] + spans[i][1] == spans[i + 1][0] for i in range(world - 1))
+            assert max(c for _, c in spans) - min(c for _, c in spans) <= 1
+    with pytest.raises(ValueError):
+        member_range(8, 2, 2)
+
+
+def test_reference_arm_prints_once_under_torchrun():
+    """bench.py --impl reference at N = 2: rank 0 alone runs and prints, the other rank exits 0."""
+    out = torchrun(2, "bench.py", "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "1",
+                   "--sample-landmarks", "300")
+    lines = [json.loads(ln) for ln in out.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    line = lines[0]
+    assert line["impl"] == "reference" and line["n_gpus"] == 2 and line["value"] > 0
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["cpu_baseline"]["kind"] == "port"

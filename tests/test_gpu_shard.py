@@ -58,3 +58,60 @@ def test_sharded_world1_matches_single_filter(nl, m):
     assert ex < 1e-12 and eP < 1e-12
     sf.close()
     h.close()
+
+
+@pytest.mark.parametrize("nl,knew", [(300, 4), (700, 40)])
+def test_sharded_add_features_matches_single_filter(nl, knew):
+    """associate -> update -> add_features -> predict -> update on both paths; the new rows and
+    columns (and everything the later update makes of them) must agree.  knew = 40 takes two
+    augment launches (32 landmarks per launch) and crosses the first block boundary at nl = 700."""
+    from slamcuda._ffi import lib, check, dptr, iptr
+    from slamcuda.shard import ShardedFilter, shard_plan
+    from slamcuda.slam import _Handle
+    n0 = 3 + 2 * nl
+    ncap = n0 + 2 * knew
+    side = math.sqrt(nl / 0.0035)
+    h = _Handle(0, ncap)
+    check(lib.slam_synth_state(h.ptr, nl, side, 11))
+    sf = ShardedFilter(0, 0, 1, ncap)
+    sf.synth_state(nl, side, 11)
+    m = 6
+    z = np.zeros(2 * (m + knew))
+    ids = np.zeros(m, dtype=np.int64)
+    check(lib.slam_synth_observations(h.ptr, nl, side, 11, m, knew, dptr(z), iptr(ids)))
+    z2 = z.reshape(m + knew, 2).T
+    zf_a, idf_a, zn_a = h.associate(z2, R, 4.0, 25.0)
+    zf_b, idf_b, zn_b = sf.associate(z2, R, 4.0, 25.0)
+    assert np.array_equal(idf_a, idf_b) and np.array_equal(zn_a, zn_b)
+    assert 0 < zn_a.shape[1] <= knew
+    # add_features takes whatever the caller hands it: use all knew spurious observations (not only
+    # the ones outside the outer gate) so that the count is fixed
+    zn_a = zn_b = z2[:, m:].copy()
+    k = knew
+    h.update(zf_a, R, idf_a)
+    sf.update(zf_a, R, idf_a)
+    h.add_features(zn_a, R)
+    sf.add_features(zn_b, R)
+    assert sf.n == h.n == n0 + 2 * k
+    xa, Pa = h.get_state()
+    nn = sf.n
+    blk, cnt = sf.cov_block(0, nn, 0, nn)
+    assert cnt == nn * nn
+    assert np.array_equal(sf.get_x(), xa)
+    assert np.array_equal(np.triu(blk), np.triu(Pa))
+    # the new landmarks take part in the next cycle
+    h.predict(0.03, 7.7, 4.0, Q, 0.025)
+    sf.predict(0.03, 7.7, 4.0, Q, 0.025)
+    idn = np.array([nl + 1, nl + k, 1], dtype=np.int64)
+    zq = np.stack([h.predict_observation(int(i))[0] for i in idn], axis=1) + 0.01
+    h.update(zq, R, idn)
+    sf.update(zq, R, idn)
+    xb, Pb = h.get_state()
+    blk, _ = sf.cov_block(0, nn, 0, nn)
+    ex, eP = rel_err(sf.get_x(), xb), rel_err(np.triu(blk), np.triu(Pb))
+    print(f"\n[shard add_features n0={n0} k={k}] x rel {ex:.2e}  P rel {eP:.2e}; blocks {shard_plan(ncap, 1, 0)}")
+    assert ex < 1e-12 and eP < 1e-12
+    with pytest.raises(Exception):
+        sf.add_features(np.tile(zn_b[:, :1], (1, knew + 1)), R)   # more than the capacity left
+    sf.close()
+    h.close()

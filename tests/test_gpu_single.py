@@ -305,3 +305,77 @@ def test_update_rank_sweep_dmma(sc, nf, m):
     assert e_fd < 1e-12
     assert rel_err(out[2][0], xo) < STEP_TOL and rel_err(out[2][1], Po) < STEP_TOL
     assert np.array_equal(out[2][1], out[2][1].T)
+
+
+def _gather(h, segs):
+    """Principal submatrix of the resident P over the index segments [(start, len), ...]."""
+    tot = sum(ln for _, ln in segs)
+    out = np.empty((tot, tot))
+    oi = 0
+    for i0, ni in segs:
+        oj = 0
+        for j0, nj in segs:
+            out[oi:oi + ni, oj:oj + nj] = h.cov_block(i0, ni, j0, nj)
+            oj += nj
+        oi += ni
+    return out
+
+
+def test_full_size_properties(sc):
+    """n = 20003 (the 10k-landmark config; P = 3.2 GB stays on the device).  H is zero outside the
+    vehicle and the observed landmarks, so the update restricted to any principal submatrix that
+    contains those columns IS the update of that sub-state: the literal oracle runs on a sample
+    (vehicle + observed pairs + four 150-row windows) and must agree with the same windows of the
+    full-size result.  Plus the size-independent properties: symmetric export, m = 0 identity,
+    idempotent association, non-increasing diagonal, PD observed block."""
+    from slamcuda._ffi import lib, check, dptr, iptr
+    from slamcuda.slam import _Handle
+    k = ref.sim_constants()
+    R = k["R"]
+    nl, m, seed = 10000, 8, 3
+    n = 3 + 2 * nl
+    side = math.sqrt(nl / 0.0035)
+    h = _Handle(0, n)
+    check(lib.slam_synth_state(h.ptr, nl, side, seed))
+    z = np.zeros(2 * (m + 4))
+    ids = np.zeros(m, dtype=np.int64)
+    check(lib.slam_synth_observations(h.ptr, nl, side, seed, m, 4, dptr(z), iptr(ids)))
+    z2 = z.reshape(m + 4, 2).T
+    # association: exact ids, idempotent
+    zf, idf, zn = h.associate(z2, R, 4.0, 25.0)
+    zf2, idf2, zn2 = h.associate(z2, R, 4.0, 25.0)
+    assert list(idf) == list(ids)
+    assert np.array_equal(zf, zf2) and np.array_equal(idf, idf2) and np.array_equal(zn, zn2)
+    # sample: vehicle, observed landmark pairs, four windows
+    rng = np.random.default_rng(1)
+    segs = [(0, 3)] + [(3 + 2 * (int(i) - 1), 2) for i in sorted(ids)]
+    taken = {3 + 2 * (int(i) - 1) for i in ids}
+    for w0 in (3, 5001, 12345, n - 150):
+        w0 = w0 if (w0 - 3) % 2 == 0 else w0 + 1
+        assert not any(w0 <= t < w0 + 150 for t in taken)
+        segs.append((w0, 150))
+    index = np.concatenate([np.arange(s, s + ln) for s, ln in segs])
+    x0 = h.get_x()
+    P0 = _gather(h, segs)
+    assert np.array_equal(P0, P0.T)                         # export mirrors the upper triangle
+    # m = 0 is the identity at full size too
+    h.update(np.zeros((2, 0)), R, np.zeros(0, dtype=np.int64))
+    assert np.array_equal(h.get_x(), x0) and np.array_equal(_gather(h, segs), P0)
+    # the oracle on the sub-state
+    pos = {int(i): 1 + c for c, i in enumerate(sorted(ids))}    # landmark id inside the sample
+    ids_sub = np.array([pos[int(i)] for i in idf])
+    xo, Po = ref.update(x0[index], P0, zf, R, ids_sub)
+    h.update(zf, R, idf)
+    x1 = h.get_x()
+    P1 = _gather(h, segs)
+    ex, eP = rel_err(x1[index], xo), rel_err(P1, Po)
+    print(f"\n[full size n={n} m={m}] sampled {len(index)} states: x rel {ex:.2e}  P rel {eP:.2e}")
+    assert ex < STEP_TOL and eP < STEP_TOL
+    assert np.array_equal(P1, P1.T)
+    d0, d1 = np.diag(P0), np.diag(P1)
+    assert np.all(d1 <= d0 * (1 + 1e-12)) and d1.sum() < d0.sum()   # P - W S W' never grows a variance
+    nobs = 3 + 2 * m
+    np.linalg.cholesky(P1[:nobs, :nobs])                              # observed block stays PD
+    # states outside the sample moved too (the update is dense): spot-check that x changed there
+    assert np.any(x1 != x0)
+    h.close()

@@ -24,14 +24,16 @@ n = 3 + 2 * nl
 side = math.sqrt(nl / 0.0035)
 R = np.array([[0.01, 0.0], [0.0, (math.pi / 180) ** 2]])
 Q = np.array([[0.25, 0.0], [0.0, (3 * math.pi / 180) ** 2]])
-sf = ShardedFilter(lr, rank, world, n)
+knew = 40
+ncap = n + 2 * knew
+sf = ShardedFilter(lr, rank, world, ncap)
 sf.synth_state(nl, side, 7)
-h = _Handle(lr, n)
+h = _Handle(lr, ncap)
 check(lib.slam_synth_state(h.ptr, nl, side, 7))
-nz = m + 4
+nz = m + knew
 z = np.zeros(2 * nz)
 ids = np.zeros(m, dtype=np.int64)
-check(lib.slam_synth_observations(h.ptr, nl, side, 7, m, 4, dptr(z), iptr(ids)))
+check(lib.slam_synth_observations(h.ptr, nl, side, 7, m, knew, dptr(z), iptr(ids)))
 z2 = z.reshape(nz, 2).T
 zf_a, idf_a, zn_a = h.associate(z2, R, 4.0, 25.0)
 zf_b, idf_b, zn_b = sf.associate(z2, R, 4.0, 25.0)
@@ -41,6 +43,18 @@ for _ in range(2):
     sf.predict(0.03, 7.7, 4.0, Q, 0.025)
     h.update(zf_a, R, idf_a)
     sf.update(zf_a, R, idf_a)
+zn_all = z2[:, m:].copy()
+h.add_features(zn_all, R)
+sf.add_features(zn_all, R)
+kk = knew
+ok = ok and sf.n == h.n == n + 2 * kk
+idn = np.array([nl + 1, nl + kk, 1], dtype=np.int64)
+zq = np.stack([h.predict_observation(int(i))[0] for i in idn], axis=1) + 0.01
+h.predict(0.03, 7.7, 4.0, Q, 0.025)
+sf.predict(0.03, 7.7, 4.0, Q, 0.025)
+h.update(zq, R, idn)
+sf.update(zq, R, idn)
+n = sf.n
 x1, P1 = h.get_state()
 ex = float(np.max(np.abs(sf.get_x() - x1)) / np.max(np.abs(x1)))
 eP = 0.0
