@@ -269,6 +269,7 @@ def gpu_ensemble(n_runs: int, rank: int, world: int, device: int, reps: int = 3)
         e2e_ms = (time.perf_counter() - t0) * 1e3
         ms = sorted(times)[len(times) // 2]
         done, _per = ens.steps_done()          # members that outgrow their capacity count only the steps they ran
+        first_extra, redone = ens.pass_info()   # two-pass capacity: work on re-run members is paid once more, counted once
         stopped = int((st != 0).sum())
         if world > 1:
             import torch.distributed as dist
@@ -285,7 +286,8 @@ def gpu_ensemble(n_runs: int, rank: int, world: int, device: int, reps: int = 3)
                 "value": done / (ms * 1e-3), "unit": "filter-steps/s", "ms_per_launch": ms,
                 "e2e": done / (e2e_ms * 1e-3), "runs": total, "steps_per_run": ens.nsteps,
                 "filter_steps_done": done, "member_capacity": ens.capacity,
-                "members_stopped_at_capacity": stopped, "gpu_launches_per_run_batch": 1,
+                "members_stopped_at_capacity": stopped, "gpu_launches_per_run_batch": 1 if first_extra < 0 else 2,
+                "first_pass_extra_landmarks": None if first_extra < 0 else first_extra, "members_rerun_by_second_pass": redone,
                 "streaming_model_hbm_equiv_gbs": done * 12.4e3 / (ms * 1e-3) / 1e9}
     finally:
         ens.close()

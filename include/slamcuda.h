@@ -167,6 +167,15 @@ int slam_ens_destroy(slam_ens_t *e);
 int slam_ens_set_extra_landmarks(slam_ens_t *e, int extra);
 /* 3 + 2*(nl + extra); negative on error. */
 int slam_ens_capacity(slam_ens_t *e);
+/* Two-pass capacity.  The kernel's throughput follows the member CTAs resident per SM, which the
+ * member's shared memory (i.e. its capacity) decides, and few members ever use the head-room.  A run
+ * may therefore take two launches: a first pass with `first_extra` < extra landmarks of head-room,
+ * and a second one that re-runs, from their first step and with the full capacity, only the members
+ * whose map outgrew the first.  A member's noise is keyed by its run id, so every result is the same
+ * as in a single pass.  first_extra = -1 (default): chosen from the occupancy; >= extra: single pass. */
+int slam_ens_set_first_pass_extra(slam_ens_t *e, int first_extra);
+/* After slam_ens_run: *first_extra the first pass used (-1 = single pass), *redone = members re-run. */
+int slam_ens_pass_info(slam_ens_t *e, int *first_extra, int *redone);
 /* Threads per member CTA: 64, 128 (default) or 256. */
 int slam_ens_set_threads(slam_ens_t *e, int threads);
 /* Steps of one run and number of observation steps (2802 / 311 for 2 laps of course1). */

@@ -167,15 +167,22 @@ struct EnsArgs {
     const double *ctrl_noise;  // optional [n_runs][2*nsteps] (speed, steering per step)
     const double *obs_noise;   // optional [n_runs][obs_per_member]
     int obs_per_member;
-    double *final_x;           // [n_runs][ncap]
+    int ocap;                  // capacity the outputs are laid out for (>= ncap; the second pass's ncap)
+    double *final_x;           // [n_runs][ocap]
     int *n_final;              // [n_runs]
     int *status;               // [n_runs]
     int *steps_done;           // [n_runs]
     double *tracks;            // optional [n_runs][3*nsteps]
-    double *final_P;           // optional [n_runs][ncap*ncap], full symmetric
+    double *final_P;           // optional [n_runs][ocap*ocap], full symmetric
+    // Two-pass capacity: the first pass runs every member with a small map capacity (more CTAs per
+    // SM); members whose map outgrows it are appended to over_list and run again, from the start, by
+    // a second launch with the full capacity (redo_list / redo_count = the first pass's over_*).
+    int *over_list, *over_count;
+    const int *redo_list, *redo_count;
 };
 
-constexpr int ENS_MAXB = 16;      // steps per block
+constexpr int ENS_MAXB = 9;       // steps per block (dt_observe = 8 dt: an observation every 9th step)
+constexpr int ENS_PAR = 8;        // scalars handed between phases: [0] m, [1] k, [2] Cholesky failed
 constexpr int BS = 24;            // doubles of block scratch per step
 // block scratch slots (per step of the block)
 constexpr int B_V = 0, B_G = 1, B_SG = 2, B_CG = 3, B_TPHI = 4, B_PHI0 = 5, B_VTS = 7, B_VTC = 8, B_N = 9,
@@ -196,11 +203,10 @@ __device__ __forceinline__ void ens_mark(int k) {
 #else
 #define ENS_MARK(k)
 #endif
-constexpr int ENS_TRI = 32 * 33 / 2;   // entries of the triangle table
 constexpr int LM_STRIDE = 17;     // association table per landmark: zp[2], inv(S)[4], log det, h[10]
 
 struct EnsSmem {
-    double *x, *P, *W, *S, *C, *u, *v, *Hn, *z, *zf, *zn, *bs, *par;
+    double *x, *P, *W, *S, *cd, *u, *v, *Hn, *z, *zf, *zn, *bs, *par;   // cd: diagonal of inv(U)
     int *fp, *idf, *cls;
     unsigned short *tri;   // (i', j' << 8), j' <= i' < 32, row by row: the Cholesky's element order
 };
@@ -210,11 +216,22 @@ __host__ __device__ inline int ens_wdoubles(int ncap, int mmax) {
     const int a = 2 * mmax * ens_ru4(ncap), b = ((ncap - 3) / 2) * LM_STRIDE;
     return ens_ru4(a > b ? a : b);
 }
+// S (then U in its upper triangle, inv(U) transposed in its strict lower triangle) has the leading
+// dimension R + 2: even, so that two inverse entries of a row load as one 16-byte word, and with two
+// columns to spare for the four-column groups of the W1 product.
+__host__ __device__ inline int ens_lds(int R) { return R + 2; }
+// The triangle table: entry e = (row a, column b <= a) of a lower triangle numbered row by row.  The
+// Cholesky reads it as its trailing elements (R <= 32), the downdate as its 4 x 4 tiles (bj = a, bi = b).
+__host__ __device__ inline int ens_ntri(int ncap, int mmax) {
+    const int R = 2 * mmax < 32 ? 2 * mmax : 32, nb = (ncap + 3) >> 2;
+    const int a = R * (R - 1) / 2, b = nb * (nb + 1) / 2;
+    return ens_ru4(a > b ? a : b);
+}
 __host__ __device__ inline size_t ens_smem_bytes(int ncap, int mmax) {
-    const size_t R = 2 * (size_t)mmax;
-    size_t d = ens_ru4(ncap) + ens_ru4(ncap * (ncap + 1) / 2) + ens_wdoubles(ncap, mmax) + 2 * ens_ru4((int)(R * R)) +
-               2 * ens_ru4((int)R) + ens_ru4(10 * mmax) + 3 * ens_ru4(2 * mmax) + ENS_MAXB * BS + 32;
-    return d * 8 + ens_ru4(3 * mmax) * 4 + ENS_TRI * 2 + 64;
+    const int R = 2 * mmax;
+    size_t d = ens_ru4(ncap) + ens_ru4(ncap * (ncap + 1) / 2) + ens_wdoubles(ncap, mmax) + ens_ru4(R * ens_lds(R)) +
+               3 * ens_ru4(R) + ens_ru4(10 * mmax) + 3 * ens_ru4(2 * mmax) + ENS_MAXB * BS + ENS_PAR;
+    return d * 8 + ens_ru4(3 * mmax) * 4 + ens_ntri(ncap, mmax) * 2 + 64;
 }
 
 __device__ inline EnsSmem ens_carve(double *base, int ncap, int mmax) {
@@ -224,8 +241,8 @@ __device__ inline EnsSmem ens_carve(double *base, int ncap, int mmax) {
     s.x = p;   p += ens_ru4(ncap);
     s.P = p;   p += ens_ru4(ncap * (ncap + 1) / 2);
     s.W = p;   p += ens_wdoubles(ncap, mmax);
-    s.S = p;   p += ens_ru4(R * R);
-    s.C = p;   p += ens_ru4(R * R);
+    s.S = p;   p += ens_ru4(R * ens_lds(R));
+    s.cd = p;  p += ens_ru4(R);
     s.u = p;   p += ens_ru4(R);
     s.v = p;   p += ens_ru4(R);
     s.Hn = p;  p += ens_ru4(10 * mmax);
@@ -233,7 +250,7 @@ __device__ inline EnsSmem ens_carve(double *base, int ncap, int mmax) {
     s.zf = p;  p += ens_ru4(2 * mmax);
     s.zn = p;  p += ens_ru4(2 * mmax);
     s.bs = p;  p += ENS_MAXB * BS;
-    s.par = p; p += 32;
+    s.par = p; p += ENS_PAR;
     int *q = reinterpret_cast<int *>(p);
     s.fp = q;  q += mmax;
     s.idf = q; q += mmax;
@@ -439,7 +456,7 @@ __device__ void ens_predict_block(const EnsSmem &sm, int n, int len, int nz) {
 // phase B: one warp per observation scores all landmarks and reduces (nd, j) / min nis with
 // shuffles -- strict '<' everywhere, lowest j wins ties, NaN never wins, which is the result of
 // the reference's sequential scan (`outer` is only consulted when no landmark was ever gated).
-// Leaves m, k in par[8], par[9], zf / idf / zn compacted in observation order, and Hn / fp / v
+// Leaves m, k in par[0], par[1], zf / idf / zn compacted in observation order, and Hn / fp / v
 // of the matched observations ready for update (the same values update recomputes, src/ekf.jl:55-59).
 template <int T>
 __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
@@ -561,8 +578,8 @@ __device__ void ens_associate(const EnsSmem &sm, int n, int nz) {
             k += __popc(mn);
         }
         if (lane == 0) {
-            sm.par[8] = m;
-            sm.par[9] = k;
+            sm.par[0] = m;
+            sm.par[1] = k;
         }
     }
     __syncthreads();
@@ -576,7 +593,7 @@ template <int T>
 __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsArgs &a, int stage_b, uint32_t run,
                            const double *ctrl, const double *obsn) {
     const int tid = threadIdx.x;
-    const int R = 2 * m;
+    const int R = 2 * m, lds = ens_lds(R);
     const double Rm[4] = {SIGMA_R * SIGMA_R, 0, 0, SIGMA_B * SIGMA_B};
     double *W = sm.W;
     // PHt = P*H' (five terms per entry, columns 1,2,3,f,f+1); rows n..ldw-1 are zeroed for K6's tiles
@@ -610,19 +627,15 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
         double s1 = h[3] * a0 + h[4] * a1 + h[5] * a2 + h[8] * a3 + h[9] * a4;
         if (k == 2 * o) { s0 += Rm[0]; s1 += Rm[1]; }
         if (k == 2 * o + 1) { s0 += Rm[2]; s1 += Rm[3]; }
-        sm.S[(2 * o) + k * R] = s0;
-        sm.S[(2 * o + 1) + k * R] = s1;
+        sm.S[(2 * o) + k * lds] = s0;
+        sm.S[(2 * o + 1) + k * lds] = s1;
     }
     __syncthreads();
     ENS_MARK(8);
 #pragma unroll 1
-    for (int idx = tid; idx < R * R; idx += T) {   // S = (S + S')*0.5
+    for (int idx = tid; idx < R * R; idx += T) {   // S = (S + S')*0.5; only the upper triangle is used
         const int b = ens_div(idx, rinv_R), a = idx - b * R;
-        if (a < b) {
-            const double s = (sm.S[a + b * R] + sm.S[b + a * R]) * 0.5;
-            sm.S[a + b * R] = s;
-            sm.S[b + a * R] = s;
-        }
+        if (a < b) sm.S[a + b * lds] = (sm.S[a + b * lds] + sm.S[b + a * lds]) * 0.5;
     }
     __syncthreads();
     ENS_MARK(9);
@@ -631,60 +644,65 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
         int fail = 0;
 #pragma unroll 1
         for (int k = 0; k < R; k++) {
-            const double d = sm.S[k + k * R];
+            const double d = sm.S[k + k * lds];
             if (!(d > 0)) { fail = 1; break; }    // uniform: every lane reads the same d
             const double ukk = sqrt(d);
             __syncwarp();
-            if (lane == 0) sm.S[k + k * R] = ukk;
+            if (lane == 0) sm.S[k + k * lds] = ukk;
 #pragma unroll 1
             for (int j = k + 1 + lane; j < R; j += 32) {
-                const double ukj = sm.S[k + j * R] / ukk;
-                sm.S[k + j * R] = ukj;
+                const double ukj = sm.S[k + j * lds] / ukk;
+                sm.S[k + j * lds] = ukj;
             }
             __syncwarp();
             if (R <= 32) {
                 // trailing update, one ELEMENT per lane: entry e of the triangle table is (i', j') with
                 // j' <= i', rows counted from the bottom (i = R-1-i'), so the elements below row k are the
                 // first r(r+1)/2 entries, r = R-1-k.  Same subtraction per element as the column loop.
+                // (Keeping a lane's table entries in registers was tried: fewer cycles for a lone CTA,
+                // but more instructions and registers, and 6 % less throughput at full occupancy.)
                 const int r = R - 1 - k;
 #pragma unroll 1
                 for (int e = lane; e < r * (r + 1) / 2; e += 32) {
                     const int t = sm.tri[e];
                     const int i = R - 1 - (t & 0xff), j = R - 1 - (t >> 8);
-                    sm.S[i + j * R] -= sm.S[k + i * R] * sm.S[k + j * R];
+                    sm.S[i + j * lds] -= sm.S[k + i * lds] * sm.S[k + j * lds];
                 }
             } else {
 #pragma unroll 1
                 for (int j = k + 1 + lane; j < R; j += 32) {
-                    const double ukj = sm.S[k + j * R];
+                    const double ukj = sm.S[k + j * lds];
 #pragma unroll 1
-                    for (int i = k + 1; i <= j; i++) sm.S[i + j * R] -= sm.S[k + i * R] * ukj;
+                    for (int i = k + 1; i <= j; i++) sm.S[i + j * lds] -= sm.S[k + i * lds] * ukj;
                 }
             }
             __syncwarp();
         }
-        if (lane == 0) sm.par[10] = fail;
+        if (lane == 0) sm.par[2] = fail;
         ENS_MARK(17);   // Cholesky done (inverse + u follow)
         if (!fail) {
             // C = inv(U) in the order of LAPACK's unblocked dtrti2: C[i][j] = (U[i][j]*C[i][i] +
             // sum_{i<jj<j} U[jj][j]*C[i][jj]) * (-1/U[j][j]).  Row i of C depends on row i alone, so
             // lane i builds its own row with no exchange; the reciprocals are taken up front.
+            // Storage: C[i][j], i < j, goes to the strict LOWER triangle of S at (j, i) -- row i of C is
+            // the contiguous column i there -- and the diagonal to cd; U stays in the upper triangle.
 #pragma unroll 1
             for (int j = lane; j < R; j += 32) {
-                const double cjj = 1.0 / sm.S[j + j * R];
-                sm.C[j + j * R] = cjj;
+                const double cjj = 1.0 / sm.S[j + j * lds];
+                sm.cd[j] = cjj;
                 sm.u[j] = -cjj;   // ajj, parked in u until u is formed below
             }
             __syncwarp();
 #pragma unroll 1
             for (int i = lane; i < R; i += 32) {
-                const double cii = sm.C[i + i * R];
+                const double cii = sm.cd[i];
+                double *ci = sm.S + i * lds;     // ci[jj] = C[i][jj]
 #pragma unroll 1
                 for (int j = i + 1; j < R; j++) {
-                    double y = sm.S[i + j * R] * cii;
+                    double y = sm.S[i + j * lds] * cii;
 #pragma unroll 4
-                    for (int jj = i + 1; jj < j; jj++) y += sm.S[jj + j * R] * sm.C[i + jj * R];
-                    sm.C[i + j * R] = y * sm.u[j];
+                    for (int jj = i + 1; jj < j; jj++) y += sm.S[jj + j * lds] * ci[jj];
+                    ci[j] = y * sm.u[j];
                 }
             }
             __syncwarp();
@@ -692,7 +710,8 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
             for (int j = lane; j < R; j += 32) {
                 double a = 0;
 #pragma unroll 4
-                for (int l = 0; l <= j; l++) a += sm.C[l + j * R] * sm.v[l];
+                for (int l = 0; l < j; l++) a += sm.S[j + l * lds] * sm.v[l];
+                a += sm.cd[j] * sm.v[j];
                 sm.u[j] = a;          // ajj is dead after the barrier above
             }
         }
@@ -701,20 +720,51 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
     }
     __syncthreads();
     ENS_MARK(10);
-    if (sm.par[10] != 0.0) return false;
-    // W1 = PHt*C in place (k descending keeps PHt[i, l <= k] intact), x += W1*u
+    if (sm.par[2] != 0.0) return false;
+    // W1 = PHt*C in place, x += W1*u.  Four columns k at a time, groups descending (a group needs
+    // PHt[i, l <= its last column] only, which later groups leave intact); the columns of a group share
+    // the loads of PHt[i, l], and each keeps its own sum (l ascending, the diagonal term last), i.e.
+    // the result of one column at a time.  R is even, so a group holds four or two columns; the
+    // operands a two-column group reads past column R-1 stay inside the workspace and are not used.
 #pragma unroll 1
     for (int i = tid; i < n; i += T) {
+        double *wi = W + i;
 #pragma unroll 1
-        for (int k = R - 1; k >= 0; k--) {
-            double a = 0;
-#pragma unroll 4
-            for (int l = 0; l <= k; l++) a += W[l * ldw + i] * sm.C[l + k * R];
-            W[k * ldw + i] = a;
+        for (int kg = (R - 1) & ~3; kg >= 0; kg -= 4) {
+            double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+            const double *cl = sm.S + kg;          // C[l][kg + q] at cl[l*lds + q]
+#pragma unroll 2
+            for (int l = 0; l < kg; l++) {
+                const double w = wi[l * ldw];
+                const double2 c01 = *reinterpret_cast<const double2 *>(cl + l * lds);
+                const double2 c23 = *reinterpret_cast<const double2 *>(cl + l * lds + 2);
+                a0 += w * c01.x;
+                a1 += w * c01.y;
+                a2 += w * c23.x;
+                a3 += w * c23.y;
+            }
+            const double w0 = wi[kg * ldw], w1 = wi[(kg + 1) * ldw], w2 = wi[(kg + 2) * ldw], w3 = wi[(kg + 3) * ldw];
+            const double *c0 = cl + kg * lds, *c1 = c0 + lds, *c2 = c1 + lds;
+            a0 += w0 * sm.cd[kg];
+            a1 += w0 * c0[1];
+            a1 += w1 * sm.cd[kg + 1];
+            a2 += w0 * c0[2];
+            a2 += w1 * c1[2];
+            a2 += w2 * sm.cd[kg + 2];
+            a3 += w0 * c0[3];
+            a3 += w1 * c1[3];
+            a3 += w2 * c2[3];
+            a3 += w3 * sm.cd[kg + 3];
+            wi[kg * ldw] = a0;
+            wi[(kg + 1) * ldw] = a1;
+            if (kg + 2 < R) {
+                wi[(kg + 2) * ldw] = a2;
+                wi[(kg + 3) * ldw] = a3;
+            }
         }
         double dxi = 0;
 #pragma unroll 1
-        for (int k = 0; k < R; k++) dxi += W[k * ldw + i] * sm.u[k];
+        for (int k = 0; k < R; k++) dxi += wi[k * ldw] * sm.u[k];
         sm.x[i] += dxi;
     }
     __syncthreads();
@@ -726,19 +776,30 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
     const int nb = (n + 3) >> 2;
 #pragma unroll 1
     for (int t = tid; t < nb * (nb + 1) / 2; t += T) {
-        int bj = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
-        while (bj * (bj + 1) / 2 > t) bj--;
-        while ((bj + 1) * (bj + 2) / 2 <= t) bj++;
-        const int bi = t - bj * (bj + 1) / 2;
+        const int tt = sm.tri[t];
+        const int bj = tt & 0xff, bi = tt >> 8;
         const int i0 = 4 * bi, j0 = 4 * bj;
+        const bool inner = bi < bj && j0 + 3 < n;     // every element of the tile exists
+        double *pc = sm.P + cofs(j0) + i0;             // column j0 + c of the tile at pc + c*j0 + c(c+1)/2
+        const int o1 = j0 + 1, o2 = 2 * j0 + 3, o3 = 3 * j0 + 6;
         double acc[4][4];
-#pragma unroll
-        for (int c = 0; c < 4; c++)
+        if (inner) {
 #pragma unroll
             for (int r = 0; r < 4; r++) {
-                const int i = i0 + r, j = j0 + c;
-                acc[c][r] = (i <= j && j < n) ? sm.P[cofs(j) + i] : 0.0;
+                acc[0][r] = pc[r];
+                acc[1][r] = pc[o1 + r];
+                acc[2][r] = pc[o2 + r];
+                acc[3][r] = pc[o3 + r];
             }
+        } else {
+#pragma unroll
+            for (int c = 0; c < 4; c++)
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    const int i = i0 + r, j = j0 + c;
+                    acc[c][r] = (i <= j && j < n) ? sm.P[cofs(j) + i] : 0.0;
+                }
+        }
 #pragma unroll 1
         for (int k = 0; k < R; k++) {
             const double4 wi = *reinterpret_cast<const double4 *>(W + k * ldw + i0);
@@ -750,13 +811,23 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
 #pragma unroll
                 for (int r = 0; r < 4; r++) acc[c][r] = fma(wir[r], wjc[c], acc[c][r]);
         }
-#pragma unroll
-        for (int c = 0; c < 4; c++)
+        if (inner) {
 #pragma unroll
             for (int r = 0; r < 4; r++) {
-                const int i = i0 + r, j = j0 + c;
-                if (i <= j && j < n) sm.P[cofs(j) + i] = acc[c][r];
+                pc[r] = acc[0][r];
+                pc[o1 + r] = acc[1][r];
+                pc[o2 + r] = acc[2][r];
+                pc[o3 + r] = acc[3][r];
             }
+        } else {
+#pragma unroll
+            for (int c = 0; c < 4; c++)
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    const int i = i0 + r, j = j0 + c;
+                    if (i <= j && j < n) sm.P[cofs(j) + i] = acc[c][r];
+                }
+        }
     }
     __syncthreads();
     ENS_MARK(12);
@@ -812,15 +883,20 @@ template <int T>
 __global__ void __launch_bounds__(T)
 k_ensemble(EnsArgs a) {
     extern __shared__ __align__(32) double ens_smem[];
-    const int member = blockIdx.x;
-    if (member >= a.n_runs) return;
+    int member = blockIdx.x;
+    if (a.redo_list) {
+        if (member >= *a.redo_count) return;
+        member = a.redo_list[member];
+    } else if (member >= a.n_runs) {
+        return;
+    }
     const int tid = threadIdx.x;
     const EnsSmem sm = ens_carve(ens_smem, a.ncap, a.mmax);
     const uint32_t run = a.run0 + (uint32_t)member;
     for (int idx = tid; idx < a.npk; idx += T) sm.P[idx] = 0.0;   // zeros(3,3); spare capacity zeroed
     for (int idx = tid; idx < a.ncap; idx += T) sm.x[idx] = 0.0;
 #pragma unroll 1
-    for (int e = tid; e < ENS_TRI; e += T) {
+    for (int e = tid; e < ens_ntri(a.ncap, a.mmax); e += T) {
         int ip = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
         while (ip * (ip + 1) / 2 > e) ip--;
         while ((ip + 1) * (ip + 2) / 2 <= e) ip++;
@@ -837,6 +913,7 @@ k_ensemble(EnsArgs a) {
     if (tid < 3) sm.x[tid] = a.z_true[-3 + tid];
     __syncthreads();
     int done = 0, staged = -1;
+    bool outgrown = false;
     ENS_MARK(-1);
     int4 dnext = a.blk[0];
     for (int b = 0; b < a.nblocks; b++) {
@@ -853,12 +930,12 @@ k_ensemble(EnsArgs a) {
         ens_predict_block<T>(sm, n, len, nz);
         if (nz > 0) {
             ens_associate<T>(sm, n, nz);
-            const int m = (int)sm.par[8], k = (int)sm.par[9];
+            const int m = (int)sm.par[0], k = (int)sm.par[1];
             if (m > 0) {
                 if (!ens_update<T>(sm, n, a.ldw, m, a, b + 1, run, ctrl, obsn)) { status = SLAM_ERR_NOT_PD; break; }
                 staged = b + 1;
             }
-            if (n + 2 * k > a.ncap) { status = SLAM_ERR_CAPACITY; break; }
+            if (n + 2 * k > a.ncap) { status = SLAM_ERR_CAPACITY; outgrown = true; break; }
             n = ens_add_features<T>(sm, n, k);
             ENS_MARK(13);
         }
@@ -873,14 +950,15 @@ k_ensemble(EnsArgs a) {
         ENS_MARK(14);
     }
     __syncthreads();
-    for (int idx = tid; idx < a.ncap; idx += T) a.final_x[(size_t)member * a.ncap + idx] = sm.x[idx];
+    for (int idx = tid; idx < a.ocap; idx += T) a.final_x[(size_t)member * a.ocap + idx] = idx < a.ncap ? sm.x[idx] : 0.0;
     if (a.final_P)   // exported as the full symmetric matrix
-        for (int idx = tid; idx < a.ncap * a.ncap; idx += T) {
-            const int i = idx % a.ncap, j = idx / a.ncap;
-            a.final_P[(size_t)member * a.ncap * a.ncap + idx] = psym(sm.P, i, j);
+        for (int idx = tid; idx < a.ocap * a.ocap; idx += T) {
+            const int i = idx % a.ocap, j = idx / a.ocap;
+            a.final_P[(size_t)member * a.ocap * a.ocap + idx] = (i < a.ncap && j < a.ncap) ? psym(sm.P, i, j) : 0.0;
         }
     ENS_MARK(-2);
     if (tid == 0) {
+        if (outgrown && a.over_list) a.over_list[atomicAdd(a.over_count, 1)] = member;
         a.n_final[member] = n;
         a.status[member] = status;
         a.steps_done[member] = done;
@@ -906,6 +984,9 @@ struct slam_ensemble {
     int *d_n_final = nullptr, *d_status = nullptr;
     bool keep = false, ran = false;
     size_t smem = 0;
+    int first_extra = -1;          // first-pass head-room: -1 = chosen by occupancy, >= extra = single pass
+    int *d_over = nullptr;         // [0] = count, [1 + i] = members the first pass could not hold
+    int last_first_extra = -1;     // what the last run used (-1 = single pass)
     long long launches = 0;
 };
 
@@ -921,7 +1002,7 @@ extern "C" int slam_ens_destroy(slam_ens_t *e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     cudaFree(e->d_gamma); cudaFree(e->d_ztrue); cudaFree(e->d_blk); cudaFree(e->d_steps_done); cudaFree(e->d_obs_start);
     cudaFree(e->d_ctrl); cudaFree(e->d_obs); cudaFree(e->d_final_x); cudaFree(e->d_tracks);
-    cudaFree(e->d_final_P); cudaFree(e->d_n_final); cudaFree(e->d_status);
+    cudaFree(e->d_final_P); cudaFree(e->d_n_final); cudaFree(e->d_status); cudaFree(e->d_over);
     if (e->stream) cudaStreamDestroy(e->stream);
     cudaGetLastError();
     delete e;
@@ -989,6 +1070,7 @@ extern "C" int slam_ens_create(int device, const double *waypoints, int nwp, con
     EN_TRY(cudaMalloc(&e->d_n_final, sizeof(int) * n_runs));
     EN_TRY(cudaMalloc(&e->d_steps_done, sizeof(int) * n_runs));
     EN_TRY(cudaMalloc(&e->d_status, sizeof(int) * n_runs));
+    EN_TRY(cudaMalloc(&e->d_over, sizeof(int) * (n_runs + 1)));
     const double pose0[3] = {waypoints[0], waypoints[1],
                              atan2(waypoints[3] - waypoints[1], waypoints[2] - waypoints[0])};
     EN_TRY(cudaMemcpy(e->d_gamma, t.gamma.data(), sizeof(double) * t.nsteps, cudaMemcpyHostToDevice));
@@ -1054,29 +1136,113 @@ extern "C" int slam_ens_set_noise(slam_ens_t *e, const double *ctrl, const doubl
     return SLAM_OK;
 }
 
+template <int T>
+static int ens_occupancy(size_t smem) {
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_ensemble<T>, T, smem) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return nb;
+}
+static int ens_ctas_per_sm(const slam_ens_t *e, int extra) {
+    const size_t smem = ens_smem_bytes(3 + 2 * (e->nl + extra), std::max(e->t.max_nz, 1));
+    switch (e->threads) {
+        case 64: return ens_occupancy<64>(smem);
+        case 256: return ens_occupancy<256>(smem);
+        default: return ens_occupancy<128>(smem);
+    }
+}
+
+// First-pass head-room.  The kernel is latency-bound and its throughput follows the resident CTAs per
+// SM, which the member's shared memory decides; few members ever need the full head-room.  Auto: the
+// largest head-room that still gives the best occupancy, if that beats the full capacity's and the
+// ensemble is longer than one wave (a second pass costs about one member's run time).
+static int ens_first_extra(const slam_ens_t *e) {
+    if (e->first_extra >= 0) return std::min(e->first_extra, e->extra);
+    const int full = ens_ctas_per_sm(e, e->extra);
+    int best = e->extra, best_occ = full;
+    for (int x = e->extra - 1; x >= 0; x--) {
+        const int occ = ens_ctas_per_sm(e, x);
+        if (occ > best_occ) { best = x; best_occ = occ; }
+    }
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device);
+    if (best_occ == full || e->n_runs <= full * sms) return e->extra;
+    return best;
+}
+
+static void ens_launch(const slam_ens_t *e, const EnsArgs &a, int grid, size_t smem) {
+    switch (e->threads) {
+        case 64: k_ensemble<64><<<grid, 64, smem, e->stream>>>(a); break;
+        case 256: k_ensemble<256><<<grid, 256, smem, e->stream>>>(a); break;
+        default: k_ensemble<128><<<grid, 128, smem, e->stream>>>(a); break;
+    }
+}
+
 extern "C" int slam_ens_run(slam_ens_t *e) {
     E_CHECK(e);
     EnsArgs a;
-    a.n_runs = e->n_runs; a.nsteps = e->t.nsteps; a.nl = e->nl; a.ncap = e->ncap;
+    a.n_runs = e->n_runs; a.nsteps = e->t.nsteps; a.nl = e->nl;
     a.mmax = std::max(e->t.max_nz, 1);
     a.seed = e->seed; a.run0 = e->run0;
     a.nblocks = (int)e->t.blocks.size() / 4;
-    a.ldw = ens_ru4(e->ncap);
-    a.npk = ens_ru4(e->ncap * (e->ncap + 1) / 2);
-    a.wdoubles = ens_wdoubles(e->ncap, a.mmax);
     a.gamma = e->d_gamma; a.blk = reinterpret_cast<const int4 *>(e->d_blk); a.z_true = e->d_ztrue + 3;
     a.ctrl_noise = e->d_ctrl; a.obs_noise = e->d_obs; a.obs_per_member = e->obs_per_member;
+    a.ocap = e->ncap;
     a.final_x = e->d_final_x; a.n_final = e->d_n_final; a.status = e->d_status; a.steps_done = e->d_steps_done;
     a.tracks = e->keep ? e->d_tracks : nullptr;
     a.final_P = e->keep ? e->d_final_P : nullptr;
-    switch (e->threads) {
-        case 64: k_ensemble<64><<<e->n_runs, 64, e->smem, e->stream>>>(a); break;
-        case 256: k_ensemble<256><<<e->n_runs, 256, e->smem, e->stream>>>(a); break;
-        default: k_ensemble<128><<<e->n_runs, 128, e->smem, e->stream>>>(a); break;
+    auto set_capacity = [&](int ncap) {
+        a.ncap = ncap;
+        a.ldw = ens_ru4(ncap);
+        a.npk = ens_ru4(ncap * (ncap + 1) / 2);
+        a.wdoubles = ens_wdoubles(ncap, a.mmax);
+    };
+    const int x1 = ens_first_extra(e);
+    if (x1 >= e->extra) {   // single pass
+        set_capacity(e->ncap);
+        a.over_list = a.over_count = nullptr;
+        a.redo_list = a.redo_count = nullptr;
+        ens_launch(e, a, e->n_runs, e->smem);
+        e->launches++;
+        e->last_first_extra = -1;
+    } else {
+        const int ncap1 = 3 + 2 * (e->nl + x1);
+        CUDA_TRY(cudaMemsetAsync(e->d_over, 0, sizeof(int), e->stream));
+        set_capacity(ncap1);
+        a.over_count = e->d_over; a.over_list = e->d_over + 1;
+        a.redo_list = a.redo_count = nullptr;
+        ens_launch(e, a, e->n_runs, ens_smem_bytes(ncap1, a.mmax));
+        set_capacity(e->ncap);
+        a.over_list = a.over_count = nullptr;
+        a.redo_count = e->d_over; a.redo_list = e->d_over + 1;
+        ens_launch(e, a, e->n_runs, e->smem);   // CTAs past the count exit at once
+        e->launches += 2;
+        e->last_first_extra = x1;
     }
-    e->launches++;
     e->ran = true;
     CUDA_TRY(cudaGetLastError());
+    return SLAM_OK;
+}
+
+// Head-room of the first pass: -1 = automatic, >= the full head-room = always a single pass.
+extern "C" int slam_ens_set_first_pass_extra(slam_ens_t *e, int extra) {
+    ARG_CHECK(e != nullptr, "NULL handle");
+    ARG_CHECK(extra >= -1, "extra < -1");
+    e->first_extra = extra;
+    return SLAM_OK;
+}
+
+// What the last slam_ens_run did: *first_extra = the first pass's head-room (-1: single pass),
+// *redone = members the second pass ran again.
+extern "C" int slam_ens_pass_info(slam_ens_t *e, int *first_extra, int *redone) {
+    E_CHECK(e);
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    int cnt = 0;
+    if (e->ran && e->last_first_extra >= 0) CUDA_TRY(cudaMemcpy(&cnt, e->d_over, sizeof(int), cudaMemcpyDeviceToHost));
+    if (first_extra) *first_extra = e->ran ? e->last_first_extra : -1;
+    if (redone) *redone = cnt;
     return SLAM_OK;
 }
 

@@ -99,6 +99,8 @@ _sig("slam_ens_steps", I, vp, c_int_p, c_int_p)
 _sig("slam_ens_set_extra_landmarks", I, vp, I)
 _sig("slam_ens_capacity", I, vp)
 _sig("slam_ens_set_threads", I, vp, I)
+_sig("slam_ens_set_first_pass_extra", I, vp, I)
+_sig("slam_ens_pass_info", I, vp, c_int_p, c_int_p)
 _sig("slam_ens_steps_done", I, vp, C.POINTER(C.c_longlong), c_int_p)
 _sig("slam_ens_run", I, vp)
 _sig("slam_ens_sync", I, vp)

@@ -22,7 +22,8 @@ def member_range(total_runs: int, world: int, rank: int):
 
 class Ensemble:
     def __init__(self, waypoints, landmarks, n_runs: int, seed: int = 0, run0: int = 0, nlaps: int = 2,
-                 device: int = 0, extra_landmarks: int | None = None, threads: int | None = None):
+                 device: int = 0, extra_landmarks: int | None = None, threads: int | None = None,
+                 first_pass_extra: int | None = None):
         wp = np.ascontiguousarray(np.asarray(waypoints, dtype=np.float64).T).reshape(-1)   # 2 x nwp column-major
         lm = np.asarray(landmarks, dtype=np.float64).reshape(2, -1)
         lmf = np.ascontiguousarray(lm.T).reshape(-1)
@@ -37,11 +38,19 @@ class Ensemble:
             check(lib.slam_ens_set_extra_landmarks(self.ptr, int(extra_landmarks)))
         if threads is not None:
             check(lib.slam_ens_set_threads(self.ptr, int(threads)))
+        if first_pass_extra is not None:
+            check(lib.slam_ens_set_first_pass_extra(self.ptr, int(first_pass_extra)))
 
     @property
     def capacity(self) -> int:
         """3 + 2*(landmarks + extra_landmarks): the largest state a member can hold."""
         return check(lib.slam_ens_capacity(self.ptr))
+
+    def pass_info(self):
+        """(head-room of the last run's first pass or -1 for a single pass, members the second pass re-ran)."""
+        fe, redone = C.c_int(), C.c_int()
+        check(lib.slam_ens_pass_info(self.ptr, C.byref(fe), C.byref(redone)))
+        return fe.value, redone.value
 
     def steps_done(self):
         """(total filter-steps completed by the last run, per-member array)."""

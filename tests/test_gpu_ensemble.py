@@ -59,16 +59,26 @@ def test_ensemble_injected_noise_vs_numpy_oracle(course1, nl, nruns):
     ens.close()
 
 
-@pytest.mark.parametrize("extra,threads", [(0, 128), (5, 128), (5, 64), (5, 256), (12, 256)])
-def test_ensemble_philox_vs_twin(course1, twin, extra, threads):
+@pytest.mark.parametrize("extra,threads,first", [(0, 128, None), (5, 128, 5), (5, 128, 0), (5, 128, 2), (5, 64, None),
+                                                  (5, 256, 1), (12, 256, None), (12, 128, 0)])
+def test_ensemble_philox_vs_twin(course1, twin, extra, threads, first):
+    """`first` forces the head-room of the first pass (two-pass capacity): members that outgrow it are
+    re-run by the second launch and must come out as in a single pass."""
     from slamcuda.ensemble import Ensemble
     nl, nruns, seed, run0 = 35, 48, 1234, 7
     lm = ref.make_inputs(nl, 0, 0)[0]
-    ens = Ensemble(course1, lm, nruns, seed=seed, run0=run0, extra_landmarks=extra, threads=threads)
+    ens = Ensemble(course1, lm, nruns, seed=seed, run0=run0, extra_landmarks=extra, threads=threads,
+                   first_pass_extra=first)
     ens.keep_tracks(True)
     ens.run()
     bad = ens.sync()
     pose, nf, st = ens.results()
+    fe, redone = ens.pass_info()
+    if first is not None and first < extra:
+        assert fe == first and ens.launch_count() == 2
+        assert redone == int(np.sum((nf > 3 + 2 * (nl + first)) | (st == -3)))   # everyone who needed more room
+    else:
+        assert redone == 0 and ens.launch_count() == 1
     ms = ens.nsteps
     wp = np.ascontiguousarray(course1.T).reshape(-1)
     lmf = np.ascontiguousarray(lm.T).reshape(-1)
@@ -88,7 +98,8 @@ def test_ensemble_philox_vs_twin(course1, twin, extra, threads):
         assert nf[r] == nfin[r]
         e = float(np.max(np.abs(ens.track(r) - tt))) / float(np.max(np.abs(tt)))
         worst = max(worst, e)
-    print(f"\n[ensemble philox] {nruns} members: gpu stopped early {bad}, twin {tbad}; compared {compared}, "
+    print(f"\n[ensemble philox extra={extra} first={first}] {nruns} members (second pass re-ran {redone}): "
+          f"gpu stopped early {bad}, twin {tbad}; compared {compared}, "
           f"worst track rel err {worst:.3e}")
     assert bad == tbad and compared >= nruns // 2
     assert worst < TRACK_TOL

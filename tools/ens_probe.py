@@ -1,4 +1,4 @@
-"""Quick GPU probe of the ensemble kernel: `ens_probe.py <n_runs> [reps] [landmarks] [threads] [extra]` runs n_runs
+"""Quick GPU probe of the ensemble kernel: `ens_probe.py <n_runs> [reps] [landmarks] [threads] [extra] [first_pass_extra]` runs n_runs
 course1 members in one launch and prints the launch time, filter-steps/s and how many members
 stopped early.  Used under ncu for the k_ensemble captures in profiles/."""
 import sys
@@ -17,9 +17,10 @@ reps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 nl = int(sys.argv[3]) if len(sys.argv) > 3 else 35
 threads = int(sys.argv[4]) if len(sys.argv) > 4 else None
 extra = int(sys.argv[5]) if len(sys.argv) > 5 else None
+first = int(sys.argv[6]) if len(sys.argv) > 6 else None
 wp = np.loadtxt(ROOT / "tests" / "golden" / "course1.txt", skiprows=1).T.copy()
 lm = np.random.Generator(np.random.PCG64(0)).integers(5, 96, size=(2, nl)).astype(float)
-ens = Ensemble(wp, lm, n_runs, seed=2, run0=0, threads=threads, extra_landmarks=extra)
+ens = Ensemble(wp, lm, n_runs, seed=2, run0=0, threads=threads, extra_landmarks=extra, first_pass_extra=first)
 stream = torch.cuda.ExternalStream(lib.slam_ens_stream(ens.ptr))
 ens.run()
 bad = ens.sync()
@@ -36,5 +37,5 @@ pose, nf, st = ens.results()
 total, per = ens.steps_done()
 print(f"runs {n_runs} nl {nl} steps {ens.nsteps} threads {threads} cap {ens.capacity}: {ms:.3f} ms/launch, "
       f"{total / ms / 1e3:.2f} M filter-steps/s ({total} steps done of {n_runs * ens.nsteps}), "
-      f"stopped early {bad}, n_final max {nf.max()}, status counts {dict(zip(*np.unique(st, return_counts=True)))}")
+      f"passes {ens.pass_info()}, stopped early {bad}, n_final max {nf.max()}, status counts {dict(zip(*np.unique(st, return_counts=True)))}")
 ens.close()
