@@ -231,6 +231,10 @@ int slam_shard_associate(slam_shard_t *s, const double *z, int nz, const double 
                          double gate2, double *zf, int64_t *idf, int *m, double *zn, int *k);
 int slam_shard_update(slam_shard_t *s, const double *zf, int m, const double R[4],
                       const int64_t *idf);
+/* 1 when the update exchanges the H rows and W1 through peer memory (one kernel computes and stores
+ * into every rank's buffers over NVLink, CUDA IPC mappings, flag barrier), 0 when it uses NCCL
+ * collectives (SLAM_SHARD_P2P=0, world = 1, or IPC refused).  Both give bit-identical results. */
+int slam_shard_p2p(slam_shard_t *s);
 /* add_features -- src/ekf.jl:84-122 on the sharded covariance: rows 0..2 of P are broadcast from
  * rank 0, every rank fills its own rows of the 2k new columns.  Collective: call on every rank. */
 int slam_shard_add_features(slam_shard_t *s, const double *zn, int k, const double R[4]);

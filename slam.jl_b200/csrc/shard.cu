@@ -14,6 +14,16 @@
 //   6. ncclAllGather of W1 (n x 2m doubles in total)
 //   7. unpermute into K6's two W1 layouts, x += W1*u for every row (x stays replicated)
 //   8. K6 on the two owned row blocks.
+//
+// Peer-memory exchange (default when the ranks can map each other's memory: CUDA IPC over NVLink /
+// NVSwitch).  Steps 2+3 and 5+6+7 become one kernel each that STORES its result into every rank's
+// buffer, followed by a flag barrier in peer memory:
+//   2'. extract_p2p   the owner of row c writes P[c, c:n] into rowbuf[s] of every rank (1.6 MB per row at
+//                     n = 200k, instead of an allreduce of S x n mostly-zero doubles)
+//   5'. gain_p2p      W1 for the rank's own rows, written straight into every rank's two K6 layouts, and
+//                     x += W1*u into every rank's x (no send buffer, no gathered copy, no unpermute pass)
+// The arithmetic per element is the NCCL path's, so both give bit-identical x and P; SLAM_SHARD_P2P=0
+// keeps the NCCL path (also the fallback when IPC is refused).
 // Reference citations are file:line under /root/reference.
 #include <dlfcn.h>
 #include <nccl.h>
@@ -123,9 +133,19 @@ extern "C" int slam_shard_unique_id(char id[128]) {
     return SLAM_OK;
 }
 
+constexpr int SH_MAXW = 16;   // ranks the peer-memory exchange handles (one NVSwitch domain)
+
 struct slam_shard {
     int device = 0, rank = 0, world = 1;
     int n_max = 0, n = 3, hb = 0;
+    // peer-memory exchange
+    bool p2p = false;
+    void *arenaA = nullptr, *arenaB = nullptr;          // peer-visible: [x | flags], [rowbuf | W1c]
+    void *peerA[SH_MAXW] = {nullptr}, *peerB[SH_MAXW] = {nullptr};
+    unsigned long long *flags = nullptr;                // [SH_MAXW] in arena A: flags[r] = rank r's last epoch
+    unsigned long long epoch = 0;
+    char *d_ipc = nullptr;
+    int *d_agree = nullptr;
     int lo[2] = {0, 0}, hi[2] = {0, 0};
     size_t ldb = 0;
     ncclComm_t comm = nullptr;
@@ -159,18 +179,71 @@ struct slam_shard {
     } while (0)
 
 // ---------------------------------------------------------------------------------------
+// peer memory: every rank maps `base` of every other rank (CUDA IPC; the 64-byte handles travel by
+// ncclAllGather, so the host launcher needs nothing new).  *ok is the ranks' common verdict (an
+// allreduce(min) of the local outcomes): either everyone uses the peer path or no one does.
+// ---------------------------------------------------------------------------------------
+static int shard_share(slam_shard_t *s, void *base, void **peers, bool want, bool *ok) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    cudaStream_t st = s->stream;
+    const size_t hb = sizeof(cudaIpcMemHandle_t);
+    cudaIpcMemHandle_t mine;
+    memset(&mine, 0, sizeof(mine));
+    int good = want ? 1 : 0;
+    if (good && cudaIpcGetMemHandle(&mine, base) != cudaSuccess) {
+        cudaGetLastError();
+        good = 0;
+    }
+    CUDA_TRY(cudaMemcpyAsync(s->d_ipc + hb * s->rank, &mine, hb, cudaMemcpyHostToDevice, st));
+    NCCL_TRY(g_nccl.AllGather(s->d_ipc + hb * s->rank, s->d_ipc, hb, ncclChar, s->comm, st));
+    std::vector<cudaIpcMemHandle_t> all(s->world);
+    CUDA_TRY(cudaMemcpyAsync(all.data(), s->d_ipc, hb * s->world, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    for (int r = 0; r < s->world; r++) peers[r] = nullptr;
+    peers[s->rank] = base;
+    for (int r = 0; r < s->world && good; r++) {
+        if (r == s->rank) continue;
+        if (cudaIpcOpenMemHandle(&peers[r], all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            cudaGetLastError();
+            peers[r] = nullptr;
+            good = 0;
+        }
+    }
+    CUDA_TRY(cudaMemcpyAsync(s->d_agree, &good, sizeof(int), cudaMemcpyHostToDevice, st));
+    NCCL_TRY(g_nccl.AllReduce(s->d_agree, s->d_agree, 1, ncclInt32, ncclMin, s->comm, st));
+    int all_good = 0;
+    CUDA_TRY(cudaMemcpyAsync(&all_good, s->d_agree, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    if (!all_good) {
+        for (int r = 0; r < s->world; r++) {
+            if (r != s->rank && peers[r]) cudaIpcCloseMemHandle(peers[r]);
+            peers[r] = nullptr;
+        }
+        peers[s->rank] = base;
+    }
+    *ok = all_good != 0;
+    return SLAM_OK;
+}
+
+// ---------------------------------------------------------------------------------------
 // lifecycle
 // ---------------------------------------------------------------------------------------
 extern "C" int slam_shard_destroy(slam_shard_t *s) {
     if (!s) return SLAM_OK;
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
-    if (s->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(s->comm);
-    cudaFree(s->d_x); cudaFree(s->d_Pb[0]); cudaFree(s->d_Pb[1]); cudaFree(s->d_err);
+    for (int r = 0; r < s->world && r < SH_MAXW; r++) {
+        if (r == s->rank) continue;
+        if (s->peerA[r]) cudaIpcCloseMemHandle(s->peerA[r]);
+        if (s->peerB[r]) cudaIpcCloseMemHandle(s->peerB[r]);
+    }
+    if (s->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(s->comm);   // the ranks meet here before anything is freed
+    cudaFree(s->arenaA); cudaFree(s->arenaB); cudaFree(s->d_ipc); cudaFree(s->d_agree);
+    cudaFree(s->d_Pb[0]); cudaFree(s->d_Pb[1]); cudaFree(s->d_err);
     cudaFree(s->d_zf); cudaFree(s->d_z); cudaFree(s->d_zn); cudaFree(s->d_idf);
-    cudaFree(s->d_rowbuf); cudaFree(s->d_PHtloc); cudaFree(s->d_PHtH); cudaFree(s->d_S); cudaFree(s->d_C);
+    cudaFree(s->d_PHtloc); cudaFree(s->d_PHtH); cudaFree(s->d_S); cudaFree(s->d_C);
     cudaFree(s->d_u); cudaFree(s->d_v); cudaFree(s->d_Hn); cudaFree(s->d_W1send); cudaFree(s->d_W1gath);
-    cudaFree(s->d_W1c); cudaFree(s->d_fp); cudaFree(s->d_fpH); cudaFree(s->d_cs);
+    cudaFree(s->d_fp); cudaFree(s->d_fpH); cudaFree(s->d_cs);
     cudaFree(s->d_P3); cudaFree(s->d_gate);
     if (s->h_pin) cudaFreeHost(s->h_pin);
     for (auto &e : s->ev) cudaEventDestroy(e);
@@ -203,7 +276,12 @@ extern "C" int slam_shard_create(int device, int rank, int world, const char id[
         }                                                                                        \
     } while (0)
     SH_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-    SH_TRY(cudaMalloc(&s->d_x, sizeof(double) * (size_t)s->npad));
+    SH_TRY(cudaMalloc(&s->arenaA, sizeof(double) * (size_t)s->npad + sizeof(unsigned long long) * SH_MAXW));
+    s->d_x = (double *)s->arenaA;
+    s->flags = (unsigned long long *)(s->d_x + s->npad);
+    SH_TRY(cudaMemsetAsync(s->flags, 0, sizeof(unsigned long long) * SH_MAXW, s->stream));
+    SH_TRY(cudaMalloc(&s->d_ipc, (size_t)SH_MAXW * sizeof(cudaIpcMemHandle_t)));
+    SH_TRY(cudaMalloc(&s->d_agree, sizeof(int)));
     for (int q = 0; q < 2; q++) SH_TRY(cudaMalloc(&s->d_Pb[q], sizeof(double) * s->ldb * (size_t)n_max));
     SH_TRY(cudaMalloc(&s->d_err, sizeof(int)));
     SH_TRY(cudaMemsetAsync(s->d_err, 0, sizeof(int), s->stream));
@@ -230,10 +308,22 @@ extern "C" int slam_shard_create(int device, int rank, int world, const char id[
             return SLAM_ERR_NCCL;
         }
     }
+    if (world > 1) {
+        const char *env = getenv("SLAM_SHARD_P2P");
+        const bool want = world <= SH_MAXW && !(env && atoi(env) == 0);
+        rc = shard_share(s, s->arenaA, s->peerA, want, &s->p2p);
+        if (rc) { slam_shard_destroy(s); return rc; }
+    }
     plan_blocks(3, s->hb, world, rank, s->lo, s->hi);
     s->n = 3;
     *out = s;
     return SLAM_OK;
+}
+
+// 1 when the update exchanges rows and W1 through peer memory, 0 when it uses NCCL collectives.
+extern "C" int slam_shard_p2p(slam_shard_t *s) {
+    if (!s) { slam_set_error("slam_shard_p2p: NULL handle"); return SLAM_ERR_ARG; }
+    return s->p2p ? 1 : 0;
 }
 
 extern "C" int slam_shard_n(slam_shard_t *s) {
@@ -467,8 +557,126 @@ k_sh_unpermute(ShardGeom g, int R, int RC, const double *__restrict__ W1gath, co
 }
 
 // ---------------------------------------------------------------------------------------
+// peer-memory variants of steps 2+3 and 5+6+7
+// ---------------------------------------------------------------------------------------
+struct ShardPeers {
+    double *x[SH_MAXW];
+    double *rowbuf[SH_MAXW];
+    double *W1c[SH_MAXW];
+    unsigned long long *flags[SH_MAXW];
+};
+
+// step 2': the owner of row cs[s] stores P[cs[s], j], j >= cs[s], into rowbuf[s] of every rank
+// (entries j < cs[s] are never read: P[i, c] with c >= i comes from the reader's own block)
+__global__ void __launch_bounds__(256)
+k_sh_extract_p2p(ShardGeom g, const int *__restrict__ cs, ShardPeers pr) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int s = blockIdx.y;
+    const int c = cs[s];
+    int owner, q, li;
+    row_owner(g, c, &owner, &q, &li);
+    if (owner != g.rank || j < c || j >= g.npad) return;
+    const double val = j < g.n ? g.Pb[q][(size_t)(c - g.lo[q]) + (size_t)j * g.ldb] : 0.0;
+    for (int r = 0; r < g.world; r++) pr.rowbuf[r][(size_t)s * g.npad + j] = val;
+}
+
+// Barrier over peer memory: rank `rank` publishes `epoch` in flags[rank] of every rank, then waits
+// until its own flags show `epoch` from everyone.  Stream order puts the kernel after this rank's
+// stores to its peers; the release / acquire pair at system scope makes them visible to whoever
+// sees the flag.  A rank that never arrives turns into SLAM_ERR_NCCL after ~60 s instead of a hang.
+__global__ void k_sh_barrier(ShardPeers pr, int rank, int world, unsigned long long epoch, int *err) {
+    const int t = threadIdx.x;
+    if (t >= world) return;
+    __threadfence_system();
+    unsigned long long *dst = pr.flags[t] + rank;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(epoch) : "memory");
+    const unsigned long long *src = pr.flags[rank] + t;
+    const long long t0 = clock64();
+    unsigned long long seen = 0;
+    while (true) {
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(src) : "memory");
+        if (seen >= epoch) break;
+        if (clock64() - t0 > 120000000000LL) {
+            atomicCAS(err, 0, SLAM_ERR_NCCL);
+            break;
+        }
+        __nanosleep(200);
+    }
+}
+
+// step 5': W1 rows of the rank's own rows (src/ekf.jl:71), stored into both K6 layouts of EVERY rank in
+// global row order, and x += W1*u (src/ekf.jl:72-74) into every rank's x.  One CTA = 128 consecutive
+// rows of one block; a chunk's row-major tile is staged in shared memory so that the remote stores are
+// whole contiguous lines.  Same sums as k_sh_gain / k_sh_unpermute.
+constexpr int SHG_ROWS = 128;
+__global__ void __launch_bounds__(SHG_ROWS)
+k_sh_gain_p2p(ShardGeom g, int R, int RC, const double *__restrict__ PHtloc, const double *__restrict__ Cm,
+              const double *__restrict__ u, ShardPeers pr) {
+    extern __shared__ double sh_tile[];          // [SHG_ROWS][RC]
+    const int q = blockIdx.y;
+    const int r0 = blockIdx.x * SHG_ROWS;        // first local row of the CTA inside block q
+    const int rows = min(SHG_ROWS, g.hi[q] - g.lo[q] - r0);
+    if (rows <= 0) return;
+    const int t = threadIdx.x;
+    const int li = q * g.slot + r0 + t, nloc = 2 * g.slot;
+    const int i0 = g.lo[q] + r0, i = i0 + t;
+    const bool live = t < rows;
+    const int nch = (R + RC - 1) / RC;
+    double dx = 0;
+    for (int c = 0; c < nch; c++) {
+        for (int kk = 0; kk < RC; kk++) {
+            const int k = c * RC + kk;
+            double a = 0;
+            if (live && k < R)
+                for (int l = 0; l <= k; l++) a += PHtloc[(size_t)l * nloc + li] * Cm[(size_t)l + (size_t)k * R];
+            sh_tile[t * RC + kk] = a;
+            if (live) {
+                const size_t o2 = (size_t)c * 2 * g.npad * RC + (size_t)g.npad * RC + (size_t)kk * g.npad + i;
+                for (int r = 0; r < g.world; r++) pr.W1c[r][o2] = a;      // rank-major copy: lanes = rows
+                if (k < R) dx += a * u[k];
+            }
+        }
+        __syncthreads();
+        const size_t o1 = (size_t)c * 2 * g.npad * RC + (size_t)i0 * RC;   // row-major copy: the tile is contiguous
+        for (int e = t; e < rows * RC; e += SHG_ROWS) {
+            const double a = sh_tile[e];
+            for (int r = 0; r < g.world; r++) pr.W1c[r][o1 + e] = a;
+        }
+        __syncthreads();
+    }
+    if (live) {
+        const double xn = pr.x[g.rank][i] + dx;
+        for (int r = 0; r < g.world; r++) pr.x[r][i] = xn;
+    }
+}
+
+// rows [n, npad_used) of the local K6 layouts are zero (the tiles of the last row block read them)
+__global__ void k_sh_zero_tail(int n, int npad_used, int npad, int RC, int nch, double *W1c) {
+    const int i = n + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npad_used) return;
+    for (int c = 0; c < nch; c++) {
+        double *chunk = W1c + (size_t)c * 2 * npad * RC;
+        for (int kk = 0; kk < RC; kk++) {
+            chunk[(size_t)i * RC + kk] = 0.0;
+            chunk[(size_t)npad * RC + (size_t)kk * npad + i] = 0.0;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
 // update driver
 // ---------------------------------------------------------------------------------------
+static ShardPeers shard_peers(const slam_shard_t *s, size_t rowbuf_doubles) {
+    ShardPeers pr;
+    for (int r = 0; r < SH_MAXW; r++) {
+        const bool on = r < s->world;
+        pr.x[r] = on ? (double *)s->peerA[r] : nullptr;
+        pr.flags[r] = on ? (unsigned long long *)((double *)s->peerA[r] + s->npad) : nullptr;
+        pr.rowbuf[r] = on ? (double *)s->peerB[r] : nullptr;
+        pr.W1c[r] = on ? (double *)s->peerB[r] + rowbuf_doubles : nullptr;
+    }
+    return pr;
+}
 static ShardGeom geom(const slam_shard_t *s) {
     ShardGeom g;
     g.rank = s->rank; g.world = s->world; g.hb = s->hb; g.slot = s->hb + 2; g.n = s->n; g.npad = s->npad;
@@ -481,14 +689,37 @@ static int shard_ensure_ws(slam_shard_t *s, int R) {
     const int RC = downdate_chunk_width(R);
     const int Rw = std::max(round_up(R, RC), 32);
     if (s->ws_R >= Rw) return SLAM_OK;
-    double **bufs[] = {&s->d_rowbuf, &s->d_PHtloc, &s->d_PHtH, &s->d_S, &s->d_C, &s->d_u, &s->d_v, &s->d_Hn,
-                       &s->d_W1send, &s->d_W1gath, &s->d_W1c};
+    double **bufs[] = {&s->d_PHtloc, &s->d_PHtH, &s->d_S, &s->d_C, &s->d_u, &s->d_v, &s->d_Hn, &s->d_W1send, &s->d_W1gath};
     for (auto b : bufs) { cudaFree(*b); *b = nullptr; }
+    // rowbuf and W1c live in the peer-visible arena B.  Growing it is collective (every rank sees the
+    // same m): unmap the peers' old arenas, meet, free, allocate, share again.
+    if (s->arenaB) {
+        CUDA_TRY(cudaStreamSynchronize(s->stream));
+        for (int r = 0; r < s->world && r < SH_MAXW; r++) {
+            if (r != s->rank && s->peerB[r]) cudaIpcCloseMemHandle(s->peerB[r]);
+            s->peerB[r] = nullptr;
+        }
+        if (s->world > 1) {
+            NCCL_TRY(g_nccl.AllReduce(s->d_agree, s->d_agree, 1, ncclInt32, ncclMin, s->comm, s->stream));
+            CUDA_TRY(cudaStreamSynchronize(s->stream));
+        }
+        cudaFree(s->arenaB);
+        s->arenaB = nullptr;
+    }
+    s->d_rowbuf = s->d_W1c = nullptr;
     cudaFree(s->d_fp); cudaFree(s->d_fpH); cudaFree(s->d_cs);
     s->d_fp = s->d_fpH = s->d_cs = nullptr;
     s->ws_R = 0;
     const size_t S = 3 + Rw, nloc = 2 * ((size_t)s->hb + 2), npad = s->npad;
-    CUDA_TRY(cudaMalloc(&s->d_rowbuf, sizeof(double) * S * npad));
+    CUDA_TRY(cudaMalloc(&s->arenaB, sizeof(double) * (S * npad + 2 * npad * Rw)));
+    s->d_rowbuf = (double *)s->arenaB;
+    s->d_W1c = s->d_rowbuf + S * npad;
+    if (s->world > 1 && s->p2p) {
+        bool ok = false;
+        int rc = shard_share(s, s->arenaB, s->peerB, true, &ok);
+        if (rc) return rc;
+        s->p2p = ok;   // refused for this arena: every rank falls back to the NCCL path together
+    }
     CUDA_TRY(cudaMalloc(&s->d_PHtloc, sizeof(double) * Rw * nloc));
     CUDA_TRY(cudaMalloc(&s->d_PHtH, sizeof(double) * Rw * S));
     CUDA_TRY(cudaMalloc(&s->d_S, sizeof(double) * Rw * Rw));
@@ -498,7 +729,6 @@ static int shard_ensure_ws(slam_shard_t *s, int R) {
     CUDA_TRY(cudaMalloc(&s->d_Hn, sizeof(double) * 10 * (Rw / 2)));
     CUDA_TRY(cudaMalloc(&s->d_W1send, sizeof(double) * Rw * nloc));
     if (s->world > 1) CUDA_TRY(cudaMalloc(&s->d_W1gath, sizeof(double) * Rw * nloc * s->world));
-    CUDA_TRY(cudaMalloc(&s->d_W1c, sizeof(double) * 2 * npad * Rw));
     CUDA_TRY(cudaMalloc(&s->d_fp, sizeof(int) * (Rw / 2)));
     CUDA_TRY(cudaMalloc(&s->d_fpH, sizeof(int) * (Rw / 2)));
     CUDA_TRY(cudaMalloc(&s->d_cs, sizeof(int) * S));
@@ -526,24 +756,44 @@ static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const
     cudaStream_t st = s->stream;
     k_sh_prep<<<(m + 255) / 256, 256, 0, st>>>(s->d_x, s->n, d_zf, d_idf, m, s->d_Hn, s->d_fp, s->d_fpH, s->d_cs,
                                               s->d_v, s->d_err);
-    k_sh_extract<<<dim3((npad + 255) / 256, S), 256, 0, st>>>(g, s->d_cs, s->d_rowbuf);
-    s->launches += 2;
-    if (s->world > 1)
-        NCCL_TRY(g_nccl.AllReduce(s->d_rowbuf, s->d_rowbuf, (size_t)S * npad, ncclFloat64, ncclSum, s->comm, st));
+    const bool p2p = s->world > 1 && s->p2p;
+    const int npad_used = round_up(s->n, DD_ROW_PAD);
+    ShardPeers pr;
+    if (p2p) {
+        pr = shard_peers(s, (size_t)(s->d_W1c - s->d_rowbuf));
+        if (npad_used > s->n) {
+            k_sh_zero_tail<<<(npad_used - s->n + 127) / 128, 128, 0, st>>>(s->n, npad_used, npad, RC, nch, s->d_W1c);
+            s->launches++;
+        }
+        k_sh_extract_p2p<<<dim3((npad + 255) / 256, S), 256, 0, st>>>(g, s->d_cs, pr);
+        k_sh_barrier<<<1, 32, 0, st>>>(pr, s->rank, s->world, ++s->epoch, s->d_err);
+        s->launches += 3;
+    } else {
+        k_sh_extract<<<dim3((npad + 255) / 256, S), 256, 0, st>>>(g, s->d_cs, s->d_rowbuf);
+        s->launches += 2;
+        if (s->world > 1)
+            NCCL_TRY(g_nccl.AllReduce(s->d_rowbuf, s->d_rowbuf, (size_t)S * npad, ncclFloat64, ncclSum, s->comm, st));
+    }
     k_sh_pht<<<(nloc + 255) / 256, 256, 0, st>>>(g, s->d_rowbuf, s->d_Hn, s->d_fp, m, s->d_PHtloc);
     k_sh_pht_hset<<<(S * m + 127) / 128, 128, 0, st>>>(npad, S, s->d_cs, s->d_rowbuf, s->d_Hn, m, s->d_PHtH);
     rc = launch_innov_chol(s->d_PHtH, S, s->d_Hn, s->d_fpH, s->d_v, m, R, s->d_S, s->d_C, s->d_u, s->d_err, st);
     if (rc) return rc;
-    k_sh_gain<<<(nloc + 127) / 128, 128, 0, st>>>(nloc, Rk, RC, s->d_PHtloc, s->d_C, s->d_W1send);
-    s->launches += 4;
-    const double *gathered = s->d_W1send;
-    if (s->world > 1) {
-        NCCL_TRY(g_nccl.AllGather(s->d_W1send, s->d_W1gath, (size_t)nch * nloc * RC, ncclFloat64, s->comm, st));
-        gathered = s->d_W1gath;
+    s->launches += 3;
+    if (p2p) {
+        k_sh_gain_p2p<<<dim3((s->hb + 2 + SHG_ROWS - 1) / SHG_ROWS, 2), SHG_ROWS, sizeof(double) * SHG_ROWS * RC, st>>>(
+            g, Rk, RC, s->d_PHtloc, s->d_C, s->d_u, pr);
+        k_sh_barrier<<<1, 32, 0, st>>>(pr, s->rank, s->world, ++s->epoch, s->d_err);
+        s->launches += 2;
+    } else {
+        k_sh_gain<<<(nloc + 127) / 128, 128, 0, st>>>(nloc, Rk, RC, s->d_PHtloc, s->d_C, s->d_W1send);
+        const double *gathered = s->d_W1send;
+        if (s->world > 1) {
+            NCCL_TRY(g_nccl.AllGather(s->d_W1send, s->d_W1gath, (size_t)nch * nloc * RC, ncclFloat64, s->comm, st));
+            gathered = s->d_W1gath;
+        }
+        k_sh_unpermute<<<(npad_used + 127) / 128, 128, 0, st>>>(g, Rk, RC, gathered, s->d_u, s->d_W1c, s->d_x);
+        s->launches += 2;
     }
-    const int npad_used = round_up(s->n, DD_ROW_PAD);
-    k_sh_unpermute<<<(npad_used + 127) / 128, 128, 0, st>>>(g, Rk, RC, gathered, s->d_u, s->d_W1c, s->d_x);
-    s->launches++;
     CUDA_TRY(cudaGetLastError());
     const bool timed = s->profiling && s->ev_used + 2 <= (int)s->ev.size();
     if (timed) CUDA_TRY(cudaEventRecord(s->ev[s->ev_used], st));

@@ -55,6 +55,11 @@ class ShardedFilter:
     def n(self) -> int:
         return check(lib.slam_shard_n(self.ptr))
 
+    @property
+    def p2p(self) -> bool:
+        """True when the update exchanges rows / W1 through peer memory instead of NCCL collectives."""
+        return check(lib.slam_shard_p2p(self.ptr)) == 1
+
     def synth_state(self, n_landmarks: int, side: float, seed: int):
         check(lib.slam_shard_synth_state(self.ptr, n_landmarks, float(side), seed))
 

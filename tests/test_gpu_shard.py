@@ -115,3 +115,28 @@ def test_sharded_add_features_matches_single_filter(nl, knew):
         sf.add_features(np.tile(zn_b[:, :1], (1, knew + 1)), R)   # more than the capacity left
     sf.close()
     h.close()
+
+
+@pytest.mark.parametrize("p2p", ["1", "0"])
+def test_sharded_two_ranks_match_single_filter(p2p):
+    """tools/shard_check.py under torch.distributed.run on two GPUs: predict / associate / update /
+    add_features sharded over two ranks vs the single filter on rank 0, bit-equal -- once with the
+    peer-memory exchange (fused compute + store into every rank's buffers over NVLink) and once with
+    the NCCL collectives.  Skipped on a one-GPU box (the driver's `-m gpu` run); run by `gpurun --gpus 2`."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+    import slamcuda
+    if slamcuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    root = Path(__file__).resolve().parent.parent
+    env = dict(os.environ, SLAM_SHARD_P2P=p2p)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", "29533" if p2p == "1" else "29534", str(root / "tools" / "shard_check.py"),
+           "3000", "8"]
+    out = subprocess.run(cmd, cwd=root, env=env, capture_output=True, text=True, timeout=300)
+    tail = out.stdout[-1500:] + out.stderr[-1500:]
+    assert out.returncode == 0, tail
+    assert "SHARD_CHECK PASS" in out.stdout, tail
+    assert f"p2p={'True' if p2p == '1' else 'False'}" in out.stdout, tail

@@ -72,7 +72,7 @@ if rank == 0:
     for r in res:
         print("rank %d assoc_ok=%s x_rel=%.2e P_rel=%.2e rows*cols=%d blocks=%s" % r)
     good = all(r[1] and r[2] < 1e-12 and r[3] < 1e-12 for r in res)
-    print("SHARD_CHECK", "PASS" if good else "FAIL", f"world={world} n={n} m={m}")
+    print("SHARD_CHECK", "PASS" if good else "FAIL", f"world={world} n={n} m={m} p2p={sf.p2p}")
 sf.close()
 h.close()
 dist.destroy_process_group()
