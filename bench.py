@@ -362,10 +362,16 @@ def gpu_update_sharded(n_landmarks: int, m: int, steps: int, warmup: int, e2e_st
         torch.cuda.synchronize(device)
         dist.barrier()
         ms_total = e0.elapsed_time(e1)
-        k6, cnt = C.c_double(), C.c_int()
-        check(lib.slam_shard_profile_read(sf.ptr, C.byref(k6), C.byref(cnt)))
+        ph, cnt = (C.c_double * 4)(), C.c_int()
+        check(lib.slam_shard_profile_phases(sf.ptr, ph, C.byref(cnt)))
         check(lib.slam_shard_profile(sf.ptr, 0))
+        k6 = C.c_double(ph[3])
         launches = lib.slam_shard_launch_count(sf.ptr) - l0
+        # per-rank phase times (ms per update): H-row exchange, PHt/S/Cholesky, gain + W1 exchange, K6
+        pt = torch.tensor([v / max(cnt.value, 1) for v in ph], device=f"cuda:{device}", dtype=torch.float64)
+        allp = [torch.zeros_like(pt) for _ in range(world)]
+        dist.all_gather(allp, pt)
+        phases = np.array([[float(v) for v in a.cpu()] for a in allp])
         # end to end: host zf / idf in, status + pose out, every step
         pose = np.zeros(3)
         check(lib.slam_shard_update(sf.ptr, dptr(zf), m, dptr(R_OBS), iptr(idf)))
@@ -382,7 +388,10 @@ def gpu_update_sharded(n_landmarks: int, m: int, steps: int, warmup: int, e2e_st
                          dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, k6ms, e2e_ms = (float(v) for v in t.cpu())
-        return dict(n=n, m=m, ms_per_step=ms, k6_ms=k6ms, launches=int(launches) * world, assoc_ms=t_assoc * 1e3,
+        names = ["h_row_exchange", "pht_s_cholesky", "gain_w1_exchange", "k6"]
+        phase_ms = {nm: {"min": float(phases[:, i].min()), "max": float(phases[:, i].max())} for i, nm in enumerate(names)}
+        return dict(n=n, m=m, ms_per_step=ms, k6_ms=k6ms, launches=int(launches) * world, assoc_ms=t_assoc * 1e3, p2p=sf.p2p,
+                    phase_ms=phase_ms,
                     e2e_ms_per_step=e2e_ms, h2d_bytes=(16 * m + 8 * m) * world, d2h_bytes=(4 + 24) * world)
     finally:
         sf.close()
@@ -414,14 +423,17 @@ def reference_arm(args, rank: int):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(n_gpus: int, m: int):
+def workload_config(n_gpus: int, m: int, p2p: bool = True):
     n = n_for_bytes(GB_PER_RANK * n_gpus)
     return {
         "workload": (f"single EKF-SLAM filter, synthetic {(n - 3) // 2}-landmark 2-D rangefinder field, n = {n}, "
                      f"P = {8.0 * n * n / 1e9:.1f} GB FP64 ({GB_PER_RANK:.0f} GB per GPU; 8 GPUs = the 100k-landmark config), "
                      f"update with m = {m} associated observations of nz = {m + 4}"),
         "n": n, "landmarks": (n - 3) // 2, "m": m, "P_bytes_per_gpu": 8.0 * n * n / n_gpus,
-        "parallelism": "single GPU" if n_gpus == 1 else f"P row-block-sharded over {n_gpus} ranks, NCCL allgather of H rows and W1",
+        "parallelism": "single GPU" if n_gpus == 1 else (
+            f"P row-block-sharded over {n_gpus} ranks; H rows and W1 stored into every rank's buffers by the producing "
+            f"kernels over peer memory (NVLink, CUDA IPC), flag barrier" if p2p else
+            f"P row-block-sharded over {n_gpus} ranks, NCCL allreduce of the H rows and allgather of W1"),
         "cache": "inputs larger than L2 (P per GPU >> 126 MB); no flush needed",
     }
 
@@ -507,7 +519,7 @@ def main():
         "metric": "EKF update steps/s", "value": 1e3 / ms, "unit": "update steps/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args.gpus, args.m), "clocks": clocks,
+        "config": workload_config(args.gpus, args.m, bool(r.get("p2p", False))), "clocks": clocks,
         "e2e": {"value": 1e3 / r["e2e_ms_per_step"], "unit": "update steps/s",
                 "h2d_bytes_per_step": r["h2d_bytes"], "d2h_bytes_per_step": r["d2h_bytes"],
                 "path": "slam_update() with host zf/idf (resident mode: P stays in HBM, as sim! re-binds it)"},
@@ -516,7 +528,8 @@ def main():
                      "achieved": k6_gbs, "peak": peak, "unit": "GB/s", "frac": k6_gbs / peak,
                      "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "k6_ms": r["k6_ms"],
-                     "k6_share_of_step": r["k6_ms"] / ms},
+                     "k6_share_of_step": r["k6_ms"] / ms,
+                     **({"phase_ms_over_ranks": r["phase_ms"]} if "phase_ms" in r else {})},
     }
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline_block(n, args.m, sample_landmarks=args.sample_landmarks)

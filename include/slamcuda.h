@@ -246,6 +246,8 @@ long long slam_shard_launch_count(slam_shard_t *s);
 /* As slam_profile / slam_profile_read: CUDA events around this rank's K6 launches. */
 int slam_shard_profile(slam_shard_t *s, int on);
 int slam_shard_profile_read(slam_shard_t *s, double *k6_ms, int *k6_updates);
+/* Same window, split: [0] H-row exchange, [1] PHt / S / Cholesky, [2] gain + W1 exchange, [3] K6 (ms). */
+int slam_shard_profile_phases(slam_shard_t *s, double phases_ms[4], int *updates);
 
 #ifdef __cplusplus
 }

@@ -754,6 +754,10 @@ static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const
     const int nloc = 2 * (s->hb + 2), npad = s->npad;
     const ShardGeom g = geom(s);
     cudaStream_t st = s->stream;
+    // profiling: five events per update -- start, H rows exchanged, before the gain, K6 start, end
+    const bool timed = s->profiling && s->ev_used + 5 <= (int)s->ev.size();
+    cudaEvent_t *ev = timed ? &s->ev[s->ev_used] : nullptr;
+    if (timed) CUDA_TRY(cudaEventRecord(ev[0], st));
     k_sh_prep<<<(m + 255) / 256, 256, 0, st>>>(s->d_x, s->n, d_zf, d_idf, m, s->d_Hn, s->d_fp, s->d_fpH, s->d_cs,
                                               s->d_v, s->d_err);
     const bool p2p = s->world > 1 && s->p2p;
@@ -774,11 +778,13 @@ static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const
         if (s->world > 1)
             NCCL_TRY(g_nccl.AllReduce(s->d_rowbuf, s->d_rowbuf, (size_t)S * npad, ncclFloat64, ncclSum, s->comm, st));
     }
+    if (timed) CUDA_TRY(cudaEventRecord(ev[1], st));
     k_sh_pht<<<(nloc + 255) / 256, 256, 0, st>>>(g, s->d_rowbuf, s->d_Hn, s->d_fp, m, s->d_PHtloc);
     k_sh_pht_hset<<<(S * m + 127) / 128, 128, 0, st>>>(npad, S, s->d_cs, s->d_rowbuf, s->d_Hn, m, s->d_PHtH);
     rc = launch_innov_chol(s->d_PHtH, S, s->d_Hn, s->d_fpH, s->d_v, m, R, s->d_S, s->d_C, s->d_u, s->d_err, st);
     if (rc) return rc;
     s->launches += 3;
+    if (timed) CUDA_TRY(cudaEventRecord(ev[2], st));
     if (p2p) {
         k_sh_gain_p2p<<<dim3((s->hb + 2 + SHG_ROWS - 1) / SHG_ROWS, 2), SHG_ROWS, sizeof(double) * SHG_ROWS * RC, st>>>(
             g, Rk, RC, s->d_PHtloc, s->d_C, s->d_u, pr);
@@ -795,14 +801,13 @@ static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const
         s->launches += 2;
     }
     CUDA_TRY(cudaGetLastError());
-    const bool timed = s->profiling && s->ev_used + 2 <= (int)s->ev.size();
-    if (timed) CUDA_TRY(cudaEventRecord(s->ev[s->ev_used], st));
+    if (timed) CUDA_TRY(cudaEventRecord(ev[3], st));
     for (int q = 0; q < 2 && rc == SLAM_OK; q++)
         rc = launch_downdate_rows(s->d_Pb[q], s->ldb, s->lo[q], s->hi[q], s->n, s->d_W1c, npad, Rk, 0, st,
                                   &s->launches);
     if (timed) {
-        CUDA_TRY(cudaEventRecord(s->ev[s->ev_used + 1], st));
-        s->ev_used += 2;
+        CUDA_TRY(cudaEventRecord(ev[4], st));
+        s->ev_used += 5;
     }
     return rc;
 }
@@ -839,7 +844,7 @@ extern "C" int slam_shard_update(slam_shard_t *s, const double *zf, int m, const
 extern "C" int slam_shard_profile(slam_shard_t *s, int on) {
     S_CHECK(s);
     if (on && s->ev.empty()) {
-        s->ev.resize(2 * 4096);
+        s->ev.resize(5 * 2048);
         for (auto &e : s->ev) CUDA_TRY(cudaEventCreate(&e));
     }
     s->profiling = on != 0;
@@ -847,19 +852,30 @@ extern "C" int slam_shard_profile(slam_shard_t *s, int on) {
     return SLAM_OK;
 }
 
-extern "C" int slam_shard_profile_read(slam_shard_t *s, double *k6_ms, int *k6_updates) {
+// Sums over the updates since the last read: phases[0] H-row exchange (prep, extract, allreduce or
+// peer stores + barrier), [1] PHt / S / Cholesky, [2] gain + W1 exchange, [3] K6.  Also clears.
+extern "C" int slam_shard_profile_phases(slam_shard_t *s, double phases_ms[4], int *updates) {
     S_CHECK(s);
-    ARG_CHECK(k6_ms && k6_updates, "NULL argument");
+    ARG_CHECK(phases_ms && updates, "NULL argument");
     CUDA_TRY(cudaStreamSynchronize(s->stream));
-    double tot = 0;
-    for (int i = 0; i + 1 < s->ev_used; i += 2) {
-        float ms = 0;
-        CUDA_TRY(cudaEventElapsedTime(&ms, s->ev[i], s->ev[i + 1]));
-        tot += ms;
-    }
-    *k6_ms = tot;
-    *k6_updates = s->ev_used / 2;
+    for (int p = 0; p < 4; p++) phases_ms[p] = 0;
+    for (int i = 0; i + 4 < s->ev_used; i += 5)
+        for (int p = 0; p < 4; p++) {
+            float ms = 0;
+            CUDA_TRY(cudaEventElapsedTime(&ms, s->ev[i + p], s->ev[i + p + 1]));
+            phases_ms[p] += ms;
+        }
+    *updates = s->ev_used / 5;
     s->ev_used = 0;
+    return SLAM_OK;
+}
+
+extern "C" int slam_shard_profile_read(slam_shard_t *s, double *k6_ms, int *k6_updates) {
+    ARG_CHECK(k6_ms && k6_updates, "NULL argument");
+    double ph[4];
+    int rc = slam_shard_profile_phases(s, ph, k6_updates);
+    if (rc) return rc;
+    *k6_ms = ph[3];
     return SLAM_OK;
 }
 

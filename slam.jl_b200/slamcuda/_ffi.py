@@ -126,6 +126,7 @@ _sig("slam_shard_associate", I, vp, c_double_p, I, c_double_p, D, D, c_double_p,
      c_double_p, c_int_p)
 _sig("slam_shard_update", I, vp, c_double_p, I, c_double_p, c_int64_p)
 _sig("slam_shard_p2p", I, vp)
+_sig("slam_shard_profile_phases", I, vp, c_double_p, c_int_p)
 _sig("slam_shard_add_features", I, vp, c_double_p, I, c_double_p)
 _sig("slam_shard_update_resident", I, vp, vp, I, c_double_p, vp)
 _sig("slam_shard_sync", I, vp)
