@@ -75,8 +75,13 @@ __device__ __forceinline__ double sym_at(const double *P, size_t ld, int i, int 
 // (sim/sim-utils.jl:5,36-37,68), which cannot be reproduced without Julia; "same seeds"
 // is defined at this generator.  Counter = (idx, stream, run, 0), key = seed.
 // ---------------------------------------------------------------------------------------
+#define SLAM_PRAGMA_(x) _Pragma(#x)
+#define SLAM_UNROLL(n) SLAM_PRAGMA_(unroll n)
+#ifndef PHILOX_UNROLL
+#define PHILOX_UNROLL 2    // rolled: the ensemble kernel is bound by instruction fetch, not by these 70 instructions
+#endif
 __host__ __device__ __forceinline__ void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
-#pragma unroll
+    SLAM_UNROLL(PHILOX_UNROLL)
     for (int r = 0; r < 10; r++) {
         uint64_t p0 = (uint64_t)0xD2511F53u * c[0];
         uint64_t p1 = (uint64_t)0xCD9E8D57u * c[2];

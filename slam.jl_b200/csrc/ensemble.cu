@@ -182,6 +182,12 @@ struct EnsArgs {
 };
 
 constexpr int ENS_MAXB = 9;       // steps per block (dt_observe = 8 dt: an observation every 9th step)
+#ifndef ENS_UNROLL_INV
+#define ENS_UNROLL_INV 1
+#endif
+#ifndef ENS_UNROLL_W1
+#define ENS_UNROLL_W1 2
+#endif
 constexpr int ENS_PAR = 8;        // scalars handed between phases: [0] m, [1] k, [2] Cholesky failed
 constexpr int BS = 24;            // doubles of block scratch per step
 // block scratch slots (per step of the block)
@@ -212,6 +218,11 @@ struct EnsSmem {
 };
 
 __host__ __device__ inline int ens_ru4(int a) { return (a + 3) & ~3; }
+// doubles of the packed upper triangle of a member's P (layout: see cofs)
+__host__ __device__ inline int ens_pdoubles(int ncap) {
+    const int nbc = (ncap + 3) >> 2;
+    return 8 * nbc * (nbc + 1);
+}
 __host__ __device__ inline int ens_wdoubles(int ncap, int mmax) {
     const int a = 2 * mmax * ens_ru4(ncap), b = ((ncap - 3) / 2) * LM_STRIDE;
     return ens_ru4(a > b ? a : b);
@@ -229,7 +240,7 @@ __host__ __device__ inline int ens_ntri(int ncap, int mmax) {
 }
 __host__ __device__ inline size_t ens_smem_bytes(int ncap, int mmax) {
     const int R = 2 * mmax;
-    size_t d = ens_ru4(ncap) + ens_ru4(ncap * (ncap + 1) / 2) + ens_wdoubles(ncap, mmax) + ens_ru4(R * ens_lds(R)) +
+    size_t d = ens_ru4(ncap) + ens_pdoubles(ncap) + ens_wdoubles(ncap, mmax) + ens_ru4(R * ens_lds(R)) +
                3 * ens_ru4(R) + ens_ru4(10 * mmax) + 3 * ens_ru4(2 * mmax) + ENS_MAXB * BS + ENS_PAR;
     return d * 8 + ens_ru4(3 * mmax) * 4 + ens_ntri(ncap, mmax) * 2 + 64;
 }
@@ -239,7 +250,7 @@ __device__ inline EnsSmem ens_carve(double *base, int ncap, int mmax) {
     const int R = 2 * mmax;
     double *p = base;
     s.x = p;   p += ens_ru4(ncap);
-    s.P = p;   p += ens_ru4(ncap * (ncap + 1) / 2);
+    s.P = p;   p += ens_pdoubles(ncap);
     s.W = p;   p += ens_wdoubles(ncap, mmax);
     s.S = p;   p += ens_ru4(R * ens_lds(R));
     s.cd = p;  p += ens_ru4(R);
@@ -262,8 +273,7 @@ __device__ inline EnsSmem ens_carve(double *base, int ncap, int mmax) {
 // One copy of the FP64 sin / cos / normal code for all call sites: the kernel streams through its
 // whole instruction footprint once per block, so code size is fetch latency.
 __device__ __noinline__ void ens_sincos(double t, double *s, double *c) {
-    *s = sin(t);
-    *c = cos(t);
+    sincos(t, s, c);   // one argument reduction for both
 }
 __device__ __noinline__ double ens_normal(uint64_t seed, uint32_t run, uint32_t stream, uint32_t idx) {
     return philox_normal(seed, run, stream, idx);
@@ -275,7 +285,14 @@ __device__ __noinline__ double ens_normal(uint64_t seed, uint32_t run, uint32_t 
 __device__ __forceinline__ int ens_div(int idx, float rinv) { return (int)(((float)idx + 0.5f) * rinv); }
 
 // packed upper triangle, column-major: P(i, j), i <= j, at j(j+1)/2 + i
-__device__ __forceinline__ int cofs(int j) { return (j * (j + 1)) >> 1; }
+// Columns are grouped in fours; the four columns of group b = j/4 all hold rows 0 .. 4b+3, so every
+// 4 x 4 tile of the upper triangle -- the diagonal ones too -- is a full, 32-byte-aligned block:
+// column j starts at 8b(b+1) + (j%4)(4b+4) = 4(b+1)(2b + j%4).  The entries below the diagonal inside
+// a diagonal tile are scratch (the downdate updates them blindly; nothing reads them).
+__device__ __forceinline__ int cofs(int j) {
+    const int b = j >> 2;
+    return 4 * (b + 1) * (2 * b + (j & 3));
+}
 __device__ __forceinline__ double psym(const double *P, int i, int j) {
     return i <= j ? P[cofs(j) + i] : P[cofs(i) + j];
 }
@@ -700,7 +717,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
 #pragma unroll 1
                 for (int j = i + 1; j < R; j++) {
                     double y = sm.S[i + j * lds] * cii;
-#pragma unroll 4
+                    SLAM_UNROLL(ENS_UNROLL_INV)
                     for (int jj = i + 1; jj < j; jj++) y += sm.S[jj + j * lds] * ci[jj];
                     ci[j] = y * sm.u[j];
                 }
@@ -709,7 +726,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
 #pragma unroll 1
             for (int j = lane; j < R; j += 32) {
                 double a = 0;
-#pragma unroll 4
+                    SLAM_UNROLL(ENS_UNROLL_INV)
                 for (int l = 0; l < j; l++) a += sm.S[j + l * lds] * sm.v[l];
                 a += sm.cd[j] * sm.v[j];
                 sm.u[j] = a;          // ajj is dead after the barrier above
@@ -733,7 +750,7 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
         for (int kg = (R - 1) & ~3; kg >= 0; kg -= 4) {
             double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
             const double *cl = sm.S + kg;          // C[l][kg + q] at cl[l*lds + q]
-#pragma unroll 2
+            SLAM_UNROLL(ENS_UNROLL_W1)
             for (int l = 0; l < kg; l++) {
                 const double w = wi[l * ldw];
                 const double2 c01 = *reinterpret_cast<const double2 *>(cl + l * lds);
@@ -772,33 +789,21 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
     // P -= W1*W1' over the packed upper triangle in 4 x 4 register tiles: tile (bi, bj), bi <= bj,
     // covers rows 4bi.. and columns 4bj..; tiles are numbered column by column so that the lanes
     // of a warp mostly share bj (W1 column-side loads broadcast) and walk bi (conflict-free).
+    // Every tile is a full aligned block of the layout (see cofs): no predicates, 32-byte accesses;
+    // columns n .. 4nb-1 of the last group have W1 = 0 and keep their zeros.
     // Each element is the chain a = fma(-W1[i,k], W1[j,k], a), k ascending, as the twin does.
     const int nb = (n + 3) >> 2;
 #pragma unroll 1
     for (int t = tid; t < nb * (nb + 1) / 2; t += T) {
         const int tt = sm.tri[t];
         const int bj = tt & 0xff, bi = tt >> 8;
-        const int i0 = 4 * bi, j0 = 4 * bj;
-        const bool inner = bi < bj && j0 + 3 < n;     // every element of the tile exists
-        double *pc = sm.P + cofs(j0) + i0;             // column j0 + c of the tile at pc + c*j0 + c(c+1)/2
-        const int o1 = j0 + 1, o2 = 2 * j0 + 3, o3 = 3 * j0 + 6;
+        const int i0 = 4 * bi, j0 = 4 * bj, L = j0 + 4;     // L: rows held by the columns of group bj
+        double *pc = sm.P + 2 * bj * L + i0;                 // 8 bj (bj+1) + i0: column j0 + c of the tile at pc + c*L
         double acc[4][4];
-        if (inner) {
 #pragma unroll
-            for (int r = 0; r < 4; r++) {
-                acc[0][r] = pc[r];
-                acc[1][r] = pc[o1 + r];
-                acc[2][r] = pc[o2 + r];
-                acc[3][r] = pc[o3 + r];
-            }
-        } else {
-#pragma unroll
-            for (int c = 0; c < 4; c++)
-#pragma unroll
-                for (int r = 0; r < 4; r++) {
-                    const int i = i0 + r, j = j0 + c;
-                    acc[c][r] = (i <= j && j < n) ? sm.P[cofs(j) + i] : 0.0;
-                }
+        for (int c = 0; c < 4; c++) {
+            const double4 v = *reinterpret_cast<const double4 *>(pc + c * L);
+            acc[c][0] = v.x; acc[c][1] = v.y; acc[c][2] = v.z; acc[c][3] = v.w;
         }
 #pragma unroll 1
         for (int k = 0; k < R; k++) {
@@ -811,23 +816,9 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
 #pragma unroll
                 for (int r = 0; r < 4; r++) acc[c][r] = fma(wir[r], wjc[c], acc[c][r]);
         }
-        if (inner) {
 #pragma unroll
-            for (int r = 0; r < 4; r++) {
-                pc[r] = acc[0][r];
-                pc[o1 + r] = acc[1][r];
-                pc[o2 + r] = acc[2][r];
-                pc[o3 + r] = acc[3][r];
-            }
-        } else {
-#pragma unroll
-            for (int c = 0; c < 4; c++)
-#pragma unroll
-                for (int r = 0; r < 4; r++) {
-                    const int i = i0 + r, j = j0 + c;
-                    if (i <= j && j < n) sm.P[cofs(j) + i] = acc[c][r];
-                }
-        }
+        for (int c = 0; c < 4; c++)
+            *reinterpret_cast<double4 *>(pc + c * L) = make_double4(acc[c][0], acc[c][1], acc[c][2], acc[c][3]);
     }
     __syncthreads();
     ENS_MARK(12);
@@ -1196,7 +1187,7 @@ extern "C" int slam_ens_run(slam_ens_t *e) {
     auto set_capacity = [&](int ncap) {
         a.ncap = ncap;
         a.ldw = ens_ru4(ncap);
-        a.npk = ens_ru4(ncap * (ncap + 1) / 2);
+        a.npk = ens_pdoubles(ncap);
         a.wdoubles = ens_wdoubles(ncap, a.mmax);
     };
     const int x1 = ens_first_extra(e);
