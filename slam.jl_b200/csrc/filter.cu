@@ -560,7 +560,11 @@ constexpr int K4_THREADS = 512;
 __global__ void __launch_bounds__(K4_THREADS)
 k_innov_chol(const double *__restrict__ PHt, int npad, const double *__restrict__ Hn,
              const int *__restrict__ fp, const double *__restrict__ v, int m, double R0, double R1,
-             double R2, double R3, double *S, double *C, double *u, int *err) {
+             double R2, double R3, double *Sg, double *C, double *u, int *err, int s_in_smem) {
+    // S (then its Cholesky factor) lives in dynamic shared memory when it fits (the launcher decides):
+    // the factorisation is a chain of R barrier-separated steps whose cost is the latency of S.
+    extern __shared__ __align__(16) double k4_smem[];
+    double *S = s_in_smem ? k4_smem : Sg;
     const int R = 2 * m;
     const int tid = threadIdx.x;
     __shared__ int s_fail;
@@ -674,11 +678,227 @@ k_gain(const double *__restrict__ PHt, int npad, int n, int R, const double *__r
     if (i < 3) pose_snapshot[i] = xi;
 }
 
+// K4 for ranks above 32.  Same S, same right-looking Cholesky element by element (so U is bit-identical to
+// k_innov_chol's), but laid out for a 2m x 2m problem that is no longer tiny:
+//  * 1024 threads as a 32 x 32 grid over the trailing block (no index division); the square lives in
+//    shared memory with an odd leading dimension, so walking a row is as conflict-free as a column;
+//  * inv(U) by rows from the bottom with every (i, j) sum advancing in parallel -- row k is finished,
+//    then every entry above it takes its term U[i][k]*C[k][j].  That is k_innov_chol's sum taken k
+//    DESCENDING instead of ascending: R barrier-separated steps of O(R^2) parallel work instead of one
+//    thread per column walking j^2/2 dependent terms.  The running sums sit transposed in the lower
+//    triangle of the same square (entry (i, j), i < j, at row j, column i), the diagonal in cd.
+// Rounding of C differs from the small-rank kernel at the 1e-16 level; the oracle tolerance is 1e-9.
+constexpr int K4W_THREADS = 1024;
+
+__global__ void __launch_bounds__(K4W_THREADS)
+k_innov_chol_wide(const double *__restrict__ PHt, int npad, const double *__restrict__ Hn,
+                  const int *__restrict__ fp, const double *__restrict__ v, int m, double R0, double R1,
+                  double R2, double R3, double *Sg, double *C, double *u, int *err, int s_in_smem) {
+    extern __shared__ __align__(16) double k4_smem[];
+    const int R = 2 * m;
+    const int ld = s_in_smem ? (R | 1) : R;          // the global workspace is R x R
+    double *S = s_in_smem ? k4_smem : Sg;
+    double *cd = s_in_smem ? k4_smem + (size_t)ld * R : u;   // 1/U[k][k]; u is free until the very end
+    const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
+    __shared__ int s_fail;
+    if (tid == 0) s_fail = 0;
+    for (int idx = tid; idx < m * R; idx += K4W_THREADS) {
+        int o = idx / R, k = idx % R;
+        const double *h = Hn + 10 * o;
+        int f = fp[o];
+        const double *col = PHt + (size_t)k * npad;
+        double a0 = col[0], a1 = col[1], a2 = col[2], a3 = col[f], a4 = col[f + 1];
+        double s0 = h[0] * a0 + h[1] * a1 + h[2] * a2 + h[6] * a3 + h[7] * a4;
+        double s1 = h[3] * a0 + h[4] * a1 + h[5] * a2 + h[8] * a3 + h[9] * a4;
+        if (k == 2 * o) { s0 += R0; s1 += R1; }
+        if (k == 2 * o + 1) { s0 += R2; s1 += R3; }
+        S[(size_t)(2 * o) + (size_t)k * ld] = s0;
+        S[(size_t)(2 * o + 1) + (size_t)k * ld] = s1;
+    }
+    __syncthreads();
+    for (int b = ty; b < R; b += 32)
+        for (int a = tx; a <= b; a += 32) {
+            const double sv = (S[(size_t)a + (size_t)b * ld] + S[(size_t)b + (size_t)a * ld]) * 0.5;
+            S[(size_t)a + (size_t)b * ld] = sv;      // only the upper triangle is used below
+        }
+    __syncthreads();
+    for (int k = 0; k < R; k++) {
+        const double d = S[(size_t)k + (size_t)k * ld];
+        if (!(d > 0)) {              // uniform: every thread reads the same d
+            if (tid == 0) s_fail = 1;
+            break;
+        }
+        const double ukk = sqrt(d);
+        __syncthreads();             // everyone has read d
+        if (tid == 0) S[(size_t)k + (size_t)k * ld] = ukk;
+        for (int j = k + 1 + tid; j < R; j += K4W_THREADS) S[(size_t)k + (size_t)j * ld] /= ukk;
+        __syncthreads();
+        for (int j = k + 1 + ty; j < R; j += 32) {
+            const double ukj = S[(size_t)k + (size_t)j * ld];
+            for (int i = k + 1 + tx; i <= j; i += 32)
+                S[(size_t)i + (size_t)j * ld] -= S[(size_t)k + (size_t)i * ld] * ukj;
+        }
+        __syncthreads();
+    }
+    __syncthreads();
+    if (s_fail) {
+        if (tid == 0) atomicCAS(err, 0, SLAM_ERR_NOT_PD);
+        for (int idx = tid; idx < R * R; idx += K4W_THREADS) C[idx] = 0.0;   // update becomes a no-op
+        for (int k = tid; k < R; k += K4W_THREADS) u[k] = 0.0;
+        return;
+    }
+    // running sums of inv(U) start at zero: entry (i, j), i < j, at S[j + i*ld]
+    for (int i = ty; i < R; i += 32)
+        for (int j = i + 1 + tx; j < R; j += 32) S[(size_t)j + (size_t)i * ld] = 0.0;
+    __syncthreads();
+    for (int k = R - 1; k >= 0; k--) {
+        const double ukk = S[(size_t)k + (size_t)k * ld];
+        for (int j = k + tid; j < R; j += K4W_THREADS) {
+            if (j == k) {
+                cd[k] = 1.0 / ukk;
+            } else {
+                const size_t e = (size_t)j + (size_t)k * ld;
+                S[e] = -S[e] / ukk;
+            }
+        }
+        __syncthreads();
+        const double ckk = cd[k];
+        for (int i = ty; i < k; i += 32) {
+            const double uik = S[(size_t)i + (size_t)k * ld];
+            for (int j = k + tx; j < R; j += 32) {
+                const double ckj = j == k ? ckk : S[(size_t)j + (size_t)k * ld];
+                S[(size_t)j + (size_t)i * ld] += uik * ckj;
+            }
+        }
+        __syncthreads();
+    }
+    // u = C'v (l ascending, as k_innov_chol), then C out in the layout K5 reads: upper, zeros below
+    double uj = 0;
+    const int j1 = tid;
+    if (j1 < R) {
+        for (int l = 0; l < j1; l++) uj += S[(size_t)j1 + (size_t)l * ld] * v[l];
+        uj += cd[j1] * v[j1];
+    }
+    for (int j = ty; j < R; j += 32)
+        for (int i = tx; i < R; i += 32)
+            C[(size_t)i + (size_t)j * R] = i < j ? S[(size_t)j + (size_t)i * ld] : (i == j ? cd[i] : 0.0);
+    __syncthreads();                 // cd may alias u: everyone has read it
+    if (j1 < R) u[j1] = uj;
+}
+
 int launch_innov_chol(const double *PHt, int npad, const double *Hn, const int *fp, const double *v, int m,
                       const double R[4], double *S, double *C, double *u, int *err, cudaStream_t s) {
-    k_innov_chol<<<1, K4_THREADS, 0, s>>>(PHt, npad, Hn, fp, v, m, R[0], R[1], R[2], R[3], S, C, u, err);
+    const size_t need = sizeof(double) * (size_t)(2 * m) * (2 * m);
+    int in_smem = need <= 48 * 1024;
+    if (!in_smem && need <= 200 * 1024) {   // opt in per call: the attribute belongs to the current device
+        if (cudaFuncSetAttribute(k_innov_chol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need) == cudaSuccess)
+            in_smem = 1;
+        else
+            cudaGetLastError();
+    }
+    if (2 * m > 32) {
+        const int Rr = 2 * m;
+        const size_t needw = sizeof(double) * ((size_t)(Rr | 1) * Rr + Rr);
+        in_smem = needw <= 48 * 1024;
+        if (!in_smem && needw <= 200 * 1024) {
+            if (cudaFuncSetAttribute(k_innov_chol_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)needw) ==
+                cudaSuccess)
+                in_smem = 1;
+            else
+                cudaGetLastError();
+        }
+        k_innov_chol_wide<<<1, K4W_THREADS, in_smem ? needw : 0, s>>>(PHt, npad, Hn, fp, v, m, R[0], R[1], R[2], R[3], S, C,
+                                                                      u, err, in_smem);
+    } else {
+        k_innov_chol<<<1, K4_THREADS, in_smem ? need : 0, s>>>(PHt, npad, Hn, fp, v, m, R[0], R[1], R[2], R[3], S, C, u,
+                                                             err, in_smem);
+    }
     CUDA_TRY(cudaGetLastError());
     return SLAM_OK;
+}
+
+// K5 for ranks above 32 (the DMMA range): the one-row-per-thread loop above re-reads a row of PHt
+// R/2 times and C no longer fits shared memory.  Here a CTA owns 128 rows x one 32-column chunk of W1
+// (= one K6 rank chunk): thread = row, 32 accumulators, C staged 32 x 32 at a time in shared memory
+// and read as warp-wide broadcasts, PHt read once per chunk.  Each W1[i, k] is still the sum over
+// l = 0..k in ascending order with separate multiply and add, i.e. bit-identical to k_gain.
+// x += W1*u needs all chunks of a row in order and follows in k_gain_x.
+constexpr int K5T_ROWS = 128;
+constexpr int K5T_KC = 32;
+
+__global__ void __launch_bounds__(K5T_ROWS)
+k_gain_tiled(const double *__restrict__ PHt, int npad, int n, int R, const double *__restrict__ C,
+             double *__restrict__ W1c) {
+    __shared__ __align__(16) double sC[K5T_KC * K5T_KC];   // sC[ll][kk] = C[l0 + ll][k0 + kk], 0 where l > k
+    const int i = blockIdx.x * K5T_ROWS + threadIdx.x;
+    const int k0 = blockIdx.y * K5T_KC;
+    const bool live = i < n;
+    double acc[K5T_KC];
+#pragma unroll
+    for (int kk = 0; kk < K5T_KC; kk++) acc[kk] = 0.0;
+    const int lend = min(k0 + K5T_KC, R);          // l runs to the chunk's last column
+    for (int l0 = 0; l0 < lend; l0 += K5T_KC) {
+        __syncthreads();
+        for (int e = threadIdx.x; e < K5T_KC * K5T_KC; e += K5T_ROWS) {
+            const int ll = e % K5T_KC, kk = e / K5T_KC;      // consecutive threads walk l: C is column-major
+            const int l = l0 + ll, k = k0 + kk;
+            sC[ll * K5T_KC + kk] = (l <= k && k < R) ? C[(size_t)l + (size_t)k * R] : 0.0;
+        }
+        __syncthreads();
+        if (!live) continue;
+        const int lcnt = min(K5T_KC, lend - l0);
+        if (l0 < k0) {
+            // every l of this block precedes every column of the chunk: no guards
+#pragma unroll 2
+            for (int ll = 0; ll < lcnt; ll++) {
+                const double p = PHt[(size_t)(l0 + ll) * npad + i];
+                const double4 *c4 = reinterpret_cast<const double4 *>(sC + ll * K5T_KC);
+#pragma unroll
+                for (int q = 0; q < K5T_KC / 4; q++) {
+                    const double4 c = c4[q];
+                    acc[4 * q + 0] += p * c.x;
+                    acc[4 * q + 1] += p * c.y;
+                    acc[4 * q + 2] += p * c.z;
+                    acc[4 * q + 3] += p * c.w;
+                }
+            }
+        } else {
+            // the diagonal block: column kk takes l = l0 .. l0 + kk only (a skipped term is not the
+            // same as adding p*0 when p is not finite)
+            for (int ll = 0; ll < lcnt; ll++) {
+                const double p = PHt[(size_t)(l0 + ll) * npad + i];
+#pragma unroll
+                for (int kk = 0; kk < K5T_KC; kk++)
+                    if (kk >= ll) acc[kk] += p * sC[ll * K5T_KC + kk];
+            }
+        }
+    }
+    if (i >= npad) return;
+    double *chunk = W1c + (size_t)blockIdx.y * 2 * npad * K5T_KC;
+    double4 *row = reinterpret_cast<double4 *>(chunk + (size_t)i * K5T_KC);      // [npad][32] row-major
+#pragma unroll
+    for (int q = 0; q < K5T_KC / 4; q++)
+        row[q] = live ? make_double4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3])
+                      : make_double4(0.0, 0.0, 0.0, 0.0);
+#pragma unroll
+    for (int kk = 0; kk < K5T_KC; kk++)                                             // [32][npad] rank-major
+        chunk[(size_t)npad * K5T_KC + (size_t)kk * npad + i] = live ? acc[kk] : 0.0;
+}
+
+// x += W1*u (src/ekf.jl:72-74), k ascending over all chunks as k_gain does
+__global__ void __launch_bounds__(128)
+k_gain_x(const double *__restrict__ W1c, int npad, int n, int R, const double *__restrict__ u, double *__restrict__ x,
+         double *pose_snapshot) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double dxi = 0;
+    for (int k = 0; k < R; k++) {
+        const double *chunk = W1c + (size_t)(k / K5T_KC) * 2 * npad * K5T_KC;
+        dxi += chunk[(size_t)npad * K5T_KC + (size_t)(k % K5T_KC) * npad + i] * u[k];
+    }
+    const double xi = x[i] + dxi;
+    x[i] = xi;
+    if (i < 3) pose_snapshot[i] = xi;
 }
 
 static int update_device(slam_t *h, const double *d_zf, int m, const double R[4], const int64_t *d_idf) {
@@ -698,12 +918,20 @@ static int update_device(slam_t *h, const double *d_zf, int m, const double R[4]
     const int RC = downdate_chunk_width(Rk);
     k_pht<<<(n + K3_THREADS - 1) / K3_THREADS, K3_THREADS, 0, h->stream>>>(
         h->d_x, h->d_P, h->ld, n, npad, d_zf, d_idf, m, h->d_PHt, h->d_v, h->d_Hn, h->d_fp, h->d_err);
-    k_innov_chol<<<1, K4_THREADS, 0, h->stream>>>(h->d_PHt, npad, h->d_Hn, h->d_fp, h->d_v, m, R[0], R[1],
-                                                  R[2], R[3], h->d_S, h->d_C, h->d_u, h->d_err);
+    rc = launch_innov_chol(h->d_PHt, npad, h->d_Hn, h->d_fp, h->d_v, m, R, h->d_S, h->d_C, h->d_u, h->d_err, h->stream);
+    if (rc) return rc;
     size_t sm = (size_t)Rk * Rk * sizeof(double) <= 32768 ? (size_t)Rk * Rk * sizeof(double) : 0;
     int npad_used = round_up(n, DD_ROW_PAD);
-    k_gain<<<(npad_used + K5_THREADS - 1) / K5_THREADS, K5_THREADS, sm, h->stream>>>(
-        h->d_PHt, npad, n, Rk, h->d_C, h->d_u, RC, h->d_W1c, h->d_x, h->d_pose + 4 * h->pose_slot);
+    if (Rk > 32 && RC == K5T_KC) {
+        k_gain_tiled<<<dim3((npad_used + K5T_ROWS - 1) / K5T_ROWS, (Rk + K5T_KC - 1) / K5T_KC), K5T_ROWS, 0, h->stream>>>(
+            h->d_PHt, npad, n, Rk, h->d_C, h->d_W1c);
+        k_gain_x<<<(n + 127) / 128, 128, 0, h->stream>>>(h->d_W1c, npad, n, Rk, h->d_u, h->d_x,
+                                                        h->d_pose + 4 * h->pose_slot);
+        h->launches++;
+    } else {
+        k_gain<<<(npad_used + K5_THREADS - 1) / K5_THREADS, K5_THREADS, sm, h->stream>>>(
+            h->d_PHt, npad, n, Rk, h->d_C, h->d_u, RC, h->d_W1c, h->d_x, h->d_pose + 4 * h->pose_slot);
+    }
     h->launches += 3;
     CUDA_TRY(cudaGetLastError());
     const bool timed = h->profiling && h->ev_used + 2 <= (int)h->ev.size();
