@@ -183,7 +183,7 @@ __global__ void k_gate_finalize(const GateRes *__restrict__ all, int world, cons
 
 // scratch: [0] unsigned counter, then part_nd / part_outer (double) and part_j (int) of
 // nblocks*nz entries each
-__global__ void __launch_bounds__(GATE_THREADS)
+__global__ void __launch_bounds__(GATE_THREADS, 2)
 k_gate(const double *__restrict__ x, GateSrc src, int Ntot, const double *__restrict__ z, int nz, GateParams prm,
        unsigned *counter, double *part_nd, double *part_outer, int *part_j, double *zf, int64_t *idf, double *zn,
        int *counts, GateRes *rank_res) {

@@ -54,6 +54,12 @@ h.predict(0.03, 7.7, 4.0, Q, 0.025)
 sf.predict(0.03, 7.7, 4.0, Q, 0.025)
 h.update(zq, R, idn)
 sf.update(zq, R, idn)
+# a high-rank update (R = 80): the workspace grows, so the peer-visible arena is re-allocated and
+# re-shared collectively, and K4 takes its wide variant
+idw = np.array([1 + (7 * c) % nl for c in range(40)], dtype=np.int64)
+zw = np.stack([h.predict_observation(int(i))[0] for i in idw], axis=1) + 0.02
+h.update(zw, R, idw)
+sf.update(zw, R, idw)
 n = sf.n
 x1, P1 = h.get_state()
 ex = float(np.max(np.abs(sf.get_x() - x1)) / np.max(np.abs(x1)))
