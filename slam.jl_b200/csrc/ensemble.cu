@@ -978,6 +978,7 @@ struct slam_ensemble {
     int first_extra = -1;          // first-pass head-room: -1 = chosen by occupancy, >= extra = single pass
     int *d_over = nullptr;         // [0] = count, [1 + i] = members the first pass could not hold
     int last_first_extra = -1;     // what the last run used (-1 = single pass)
+    int auto_first = -1, auto_key = -1;   // cached automatic choice and the (extra, threads) it was made for
     long long launches = 0;
 };
 
@@ -1145,12 +1146,22 @@ static int ens_ctas_per_sm(const slam_ens_t *e, int extra) {
     }
 }
 
+static int ens_first_extra_auto(const slam_ens_t *e);
+
 // First-pass head-room.  The kernel is latency-bound and its throughput follows the resident CTAs per
 // SM, which the member's shared memory decides; few members ever need the full head-room.  Auto: the
 // largest head-room that still gives the best occupancy, if that beats the full capacity's and the
 // ensemble is longer than one wave (a second pass costs about one member's run time).
-static int ens_first_extra(const slam_ens_t *e) {
+static int ens_first_extra(slam_ens_t *e) {
     if (e->first_extra >= 0) return std::min(e->first_extra, e->extra);
+    const int key = e->extra * 1024 + e->threads;
+    if (e->auto_key == key) return e->auto_first;
+    e->auto_key = key;
+    e->auto_first = ens_first_extra_auto(e);
+    return e->auto_first;
+}
+
+static int ens_first_extra_auto(const slam_ens_t *e) {
     const int full = ens_ctas_per_sm(e, e->extra);
     int best = e->extra, best_occ = full;
     for (int x = e->extra - 1; x >= 0; x--) {

@@ -60,7 +60,7 @@ def main():
     wp = ref.load_waypoints(str(OUT / "course1.txt"))
     runs = {}
     for nl in (10, 35):
-        for seed in range(4):
+        for seed in range(8):
             lm, ctrl, obs = ref.make_inputs(nl, 0, seed)
             rec = []
             r = ref.sim(wp, lm, ctrl, obs, record=rec)

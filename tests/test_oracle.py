@@ -92,7 +92,7 @@ def test_properties():
 @pytest.mark.parametrize("nl", [10, 35])
 def test_course1_runs_match_golden_and_twin(course1, twin, nl):
     g = np.load(GOLD / "course1_runs.npz")
-    for seed in range(2):
+    for seed in range(4):     # the golden file holds seeds 0..7; four of them are re-run here (time)
         lm, ctrl, obs = ref.make_inputs(nl, 0, seed)
         rec = []
         r = ref.sim(course1, lm, ctrl, obs, record=rec)
