@@ -137,3 +137,93 @@ def test_update_cadence_every_ninth_step(course1):
     lm, ctrl, obs = ref.make_inputs(10, 0, 0)
     r = ref.sim(course1, lm, ctrl, obs)
     assert r["nupdates"] == r["nsteps"] // 9
+
+
+def _fd_jacobian(f, x0, eps=1e-6):
+    """Central finite differences of f: R^n -> R^k at x0 (angles in f's output are compared unwrapped)."""
+    f0 = np.asarray(f(x0), dtype=float)
+    J = np.zeros((f0.size, x0.size))
+    for q in range(x0.size):
+        dx = np.zeros_like(x0)
+        dx[q] = eps
+        J[:, q] = (np.asarray(f(x0 + dx)) - np.asarray(f(x0 - dx))) / (2 * eps)
+    return J
+
+
+def test_oracle_against_textbook_identities():
+    """The reference ships no known answers (parity unpinned), so besides following its text line by
+    line the oracle is checked against what an EKF must satisfy, derived independently of the text:
+    Jacobians against finite differences of the models, the update against the information form, the
+    augmentation against first-order propagation through the inverse observation model."""
+    k = ref.sim_constants()
+    Q, R, dt = k["Q"], k["R"], k["dt"]
+    rng = np.random.default_rng(42)
+    nf = 6
+    n = 3 + 2 * nf
+    x = np.concatenate([[20.0, 30.0, 0.4], rng.uniform(0, 60, 2 * nf)])
+    L = rng.normal(0, 0.2, (n, n))
+    P = L @ L.T + 0.1 * np.eye(n)
+    g, v, w = 0.12, 7.3, 4.0
+
+    # observation model: H = dh/dx
+    for idf in (1, 4, 6):
+        zp, H = ref.predict_observation(x, idf)
+        J = _fd_jacobian(lambda xx: ref.predict_observation(xx, idf)[0], x)
+        assert np.max(np.abs(H - J)) < 1e-7
+        f = 3 + 2 * (idf - 1)
+        assert abs(zp[0] - np.hypot(x[f] - x[0], x[f + 1] - x[1])) < 1e-12
+
+    # predict: x' = f(x, u), P' = F P F' + Gu Q Gu' with F, Gu the Jacobians of f
+    def motion(xu):
+        xx, gg, vv = xu[:3], xu[3], xu[4]
+        return np.array([xx[0] + vv * dt * math.cos(gg + xx[2]), xx[1] + vv * dt * math.sin(gg + xx[2]),
+                         xx[2] + vv * dt * math.sin(gg) / w])
+    Jm = _fd_jacobian(motion, np.array([x[0], x[1], x[2], g, v]))
+    Fv, Gu = Jm[:, :3], Jm[:, [4, 3]]                    # Q is ordered (speed, steering): src/ekf.jl:27-29
+    F = np.eye(n)
+    F[:3, :3] = Fv
+    Pexp = F @ P @ F.T
+    Pexp[:3, :3] += Gu @ Q @ Gu.T
+    xp, Pp = ref.predict(x.copy(), P.copy(), g, v, w, Q, dt)
+    assert np.max(np.abs(Pp - Pexp)) < 1e-6 * np.max(np.abs(Pexp))
+    assert np.max(np.abs(xp[:3] - motion(np.array([x[0], x[1], x[2], g, v])))) < 1e-12
+    assert np.array_equal(xp[3:], x[3:])
+
+    # update: information form  inv(P+) = inv(P) + H' inv(RR) H,  x+ = x + P+ H' inv(RR) v
+    ids = np.array([2, 5, 3])
+    z = np.zeros((2, len(ids)))
+    Hs, vs = [], []
+    for c, idf in enumerate(ids):
+        zp, H = ref.predict_observation(x, int(idf))
+        z[:, c] = zp + rng.normal(0, [0.1, 0.01])
+        Hs.append(H)
+        vs.append([z[0, c] - zp[0], ref.mpi_to_pi(z[1, c] - zp[1])])
+    Hall, vall = np.vstack(Hs), np.concatenate(vs)
+    RRi = np.kron(np.eye(len(ids)), np.linalg.inv(R))
+    xu, Pu = ref.update(x, P, z, R, ids)
+    info = np.linalg.inv(P) + Hall.T @ RRi @ Hall
+    assert np.max(np.abs(np.linalg.inv(Pu) - info)) < 1e-7 * np.max(np.abs(info))
+    assert np.max(np.abs(xu - (x + Pu @ Hall.T @ RRi @ vall))) < 1e-9
+
+    # add_features: [x; g(x_v, z)] with covariance J blkdiag(P, R) J'
+    zn = np.array([[12.0], [0.7]])
+    def augment(xz):
+        xx, r, b = xz[:n], xz[n], xz[n + 1]
+        return np.concatenate([xx, [xx[0] + r * math.cos(xx[2] + b), xx[1] + r * math.sin(xx[2] + b)]])
+    Ja = _fd_jacobian(augment, np.concatenate([x, zn[:, 0]]))
+    big = np.zeros((n + 2, n + 2))
+    big[:n, :n] = P
+    big[n:, n:] = R
+    xa, Pa = ref.add_features(x, P, zn, R)
+    assert np.max(np.abs(xa - augment(np.concatenate([x, zn[:, 0]])))) < 1e-12
+    assert np.max(np.abs(Pa - Ja @ big @ Ja.T)) < 1e-6 * np.max(np.abs(Pa))
+
+    # association distances: nis = v' inv(S) v, nd = nis + log det S with S = H P H' + R
+    zq = z[:, 0]
+    for j in (1, 2, 6):
+        zp, H = ref.predict_observation(x, j)
+        vv = np.array([zq[0] - zp[0], ref.mpi_to_pi(zq[1] - zp[1])])
+        S = H @ P @ H.T + R
+        nis, nd = ref.compute_association(x, P, zq, R, j)
+        assert abs(nis - vv @ np.linalg.solve(S, vv)) < 1e-9 * max(1.0, nis)
+        assert abs(nd - (nis + math.log(np.linalg.det(S)))) < 1e-9 * max(1.0, abs(nd))
