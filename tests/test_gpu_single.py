@@ -321,8 +321,10 @@ def _gather(h, segs):
     return out
 
 
-def test_full_size_properties(sc):
-    """n = 20003 (the 10k-landmark config; P = 3.2 GB stays on the device).  H is zero outside the
+@pytest.mark.parametrize("nl", [10000, 35353])
+def test_full_size_properties(sc, nl):
+    """n = 20003 (the 10k-landmark config, P = 3.2 GB) and n = 70709 (bench.py's N = 1 workload, P = 40 GB);
+    P stays on the device.  H is zero outside the
     vehicle and the observed landmarks, so the update restricted to any principal submatrix that
     contains those columns IS the update of that sub-state: the literal oracle runs on a sample
     (vehicle + observed pairs + four 150-row windows) and must agree with the same windows of the
@@ -332,7 +334,7 @@ def test_full_size_properties(sc):
     from slamcuda.slam import _Handle
     k = ref.sim_constants()
     R = k["R"]
-    nl, m, seed = 10000, 8, 3
+    m, seed = 8, 3
     n = 3 + 2 * nl
     side = math.sqrt(nl / 0.0035)
     h = _Handle(0, n)
@@ -355,7 +357,8 @@ def test_full_size_properties(sc):
     taken = {3 + 2 * (i - 1) for i in seen}
     for w0 in (3, 5001, 12345, n - 150):
         w0 = w0 if (w0 - 3) % 2 == 0 else w0 + 1
-        assert not any(w0 <= t < w0 + 150 for t in taken)
+        while any(w0 - 2 <= t < w0 + 150 for t in taken):    # keep the windows clear of the observed pairs
+            w0 = w0 + 200 if w0 + 400 < n else w0 - 200
         segs.append((w0, 150))
     index = np.concatenate([np.arange(s, s + ln) for s, ln in segs])
     x0 = h.get_x()
