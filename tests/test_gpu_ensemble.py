@@ -115,3 +115,38 @@ def test_ensemble_empty_map(course1):
     pose, nf, st = ens.results()
     assert list(nf) == [3, 3, 3] and np.all(np.isfinite(pose))
     ens.close()
+
+
+def test_ensemble_full_size_is_batch_invariant(course1):
+    """bench.py's ensemble (8192 members, two-pass capacity, 4-5 CTAs per SM) against small single-pass
+    launches of the same run ids: a member's result depends on (seed, run id) alone -- not on the batch
+    it ran in, the launch configuration, or whether the second pass re-ran it.  Bit-equal."""
+    from slamcuda.ensemble import Ensemble
+    nl, seed = 35, 20240
+    lm = np.random.Generator(np.random.PCG64(0)).integers(5, 96, size=(2, nl)).astype(float)
+    big = Ensemble(course1, lm, 8192, seed=seed, run0=1000)
+    big.run()
+    bad = big.sync()
+    pose, nf, st = big.results()
+    fe, redone = big.pass_info()
+    total, per = big.steps_done()
+    assert fe >= 0 and redone > 0, "the bench-size ensemble is expected to take two passes"
+    assert total == int(per.sum()) and bad == int((st != 0).sum())
+    redo_members = np.flatnonzero((nf > 3 + 2 * (nl + fe)) | (st == -3))
+    assert len(redo_members) == redone
+    # a window of ordinary members, plus members the second pass re-ran
+    for start in (0, 4096, int(redo_members[0]), int(redo_members[-1])):
+        cnt = min(8, 8192 - start)
+        small = Ensemble(course1, lm, cnt, seed=seed, run0=1000 + start, first_pass_extra=5)
+        small.run()
+        small.sync()
+        p2, nf2, st2 = small.results()
+        _t2, per2 = small.steps_done()
+        assert small.pass_info() == (-1, 0)
+        assert np.array_equal(p2, pose[start:start + cnt])
+        assert np.array_equal(nf2, nf[start:start + cnt]) and np.array_equal(st2, st[start:start + cnt])
+        assert np.array_equal(per2, per[start:start + cnt])
+        small.close()
+    print(f"\n[ensemble 8192] first pass extra {fe}, re-ran {redone}, stopped {bad}, "
+          f"{total} of {8192 * big.nsteps} filter-steps done")
+    big.close()
