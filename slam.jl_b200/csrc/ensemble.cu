@@ -232,9 +232,9 @@ __host__ __device__ inline int ens_wdoubles(int ncap, int mmax) {
 // columns to spare for the four-column groups of the W1 product.
 __host__ __device__ inline int ens_lds(int R) { return R + 2; }
 // The triangle table: entry e = (row a, column b <= a) of a lower triangle numbered row by row.  The
-// Cholesky reads it as its trailing elements (R <= 32), the downdate as its 4 x 4 tiles (bj = a, bi = b).
+// Cholesky reads it as its trailing elements (R <= 32), the downdate as its 16 x 16 warp regions (bj = a, bi = b).
 __host__ __device__ inline int ens_ntri(int ncap, int mmax) {
-    const int R = 2 * mmax < 32 ? 2 * mmax : 32, nb = (ncap + 3) >> 2;
+    const int R = 2 * mmax < 32 ? 2 * mmax : 32, nb = (ncap + 15) >> 4;
     const int a = R * (R - 1) / 2, b = nb * (nb + 1) / 2;
     return ens_ru4(a > b ? a : b);
 }
@@ -283,6 +283,14 @@ __device__ __noinline__ double ens_normal(uint64_t seed, uint32_t run, uint32_t 
 // ~70-cycle integer division: (idx + 0.5) / d is at least 0.5 / d away from an integer, far more
 // than the float rounding error.
 __device__ __forceinline__ int ens_div(int idx, float rinv) { return (int)(((float)idx + 0.5f) * rinv); }
+
+// D (8 x 8, a lane holds d.x = D[lane/4][2(lane%4)], d.y the next column) += A (8 x 4, a = A[lane/4][lane%4])
+// * B (4 x 8, b = B[lane%4][lane/4])
+__device__ __forceinline__ void ens_dmma(double2 &d, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                 : "+d"(d.x), "+d"(d.y)
+                 : "d"(a), "d"(b));
+}
 
 // packed upper triangle, column-major: P(i, j), i <= j, at j(j+1)/2 + i
 // Columns are grouped in fours; the four columns of group b = j/4 all hold rows 0 .. 4b+3, so every
@@ -786,39 +794,60 @@ __device__ bool ens_update(const EnsSmem &sm, int n, int ldw, int m, const EnsAr
     }
     __syncthreads();
     ENS_MARK(11);
-    // P -= W1*W1' over the packed upper triangle in 4 x 4 register tiles: tile (bi, bj), bi <= bj,
-    // covers rows 4bi.. and columns 4bj..; tiles are numbered column by column so that the lanes
-    // of a warp mostly share bj (W1 column-side loads broadcast) and walk bi (conflict-free).
-    // Every tile is a full aligned block of the layout (see cofs): no predicates, 32-byte accesses;
-    // columns n .. 4nb-1 of the last group have W1 = 0 and keep their zeros.
-    // Each element is the chain a = fma(-W1[i,k], W1[j,k], a), k ascending, as the twin does.
-    const int nb = (n + 3) >> 2;
+    // P -= W1*W1' over the packed upper triangle on the FP64 tensor pipe (mma.sync m8n8k4, SASS DMMA): a
+    // warp owns a 16 x 16 region = 2 x 2 MMA tiles, four ranks per instruction.  The MMA is issued on the
+    // TRANSPOSED tile, D'[j][i] -= W1[j][k] W1[i][k], so a lane's accumulator pair is two consecutive rows
+    // (i, i+1) of one column j of P: one 16-byte access of the packed layout.  A = -W1[j][k], B = W1[i][k]
+    // both come from the rank-major workspace (one 8-byte load per lane each); ranks past R are fed
+    // as zeros.  On this hardware the four products of an MMA accumulate as a k-ascending fma chain (the
+    // measured difference to the FMA kernel K6 is 0, downdate_dmma.cu), so the result is the chain
+    // a = fma(-W1[i,k], W1[j,k], a), k ascending, of the twin.  An MMA replaces 8 warp-wide DFMAs: the
+    // kernel is bound by instruction issue and fetch, not by the FP64 pipe.
+    // Entries that do not exist in the packed layout (the part of a diagonal region below its 4 x 4 diagonal
+    // blocks, columns past the allocation) are neither loaded nor stored; columns n .. ldw-1 have W1 = 0.
+    {
+        const int lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+        const int nb16 = (n + 15) >> 4;
 #pragma unroll 1
-    for (int t = tid; t < nb * (nb + 1) / 2; t += T) {
-        const int tt = sm.tri[t];
-        const int bj = tt & 0xff, bi = tt >> 8;
-        const int i0 = 4 * bi, j0 = 4 * bj, L = j0 + 4;     // L: rows held by the columns of group bj
-        double *pc = sm.P + 2 * bj * L + i0;                 // 8 bj (bj+1) + i0: column j0 + c of the tile at pc + c*L
-        double acc[4][4];
+        for (int tl = warp; tl < nb16 * (nb16 + 1) / 2; tl += T / 32) {
+            const int tt = sm.tri[tl];
+            const int bj = tt & 0xff, bi = tt >> 8;
+            const int i0 = 16 * bi, j0 = 16 * bj;
+            const bool diag = bi == bj;
+            double2 c[2][2];
+            bool ok[2][2];
+            int off[2][2];
 #pragma unroll
-        for (int c = 0; c < 4; c++) {
-            const double4 v = *reinterpret_cast<const double4 *>(pc + c * L);
-            acc[c][0] = v.x; acc[c][1] = v.y; acc[c][2] = v.z; acc[c][3] = v.w;
-        }
+            for (int sj = 0; sj < 2; sj++)
+#pragma unroll
+                for (int si = 0; si < 2; si++) {
+                    const int j = j0 + 8 * sj + g, i = i0 + 8 * si + 2 * t;
+                    ok[sj][si] = j < ldw && i + 1 <= (j | 3) && !(diag && si > sj);
+                    off[sj][si] = cofs(j) + i;
+                    c[sj][si] = ok[sj][si] ? *reinterpret_cast<const double2 *>(sm.P + off[sj][si]) : make_double2(0.0, 0.0);
+                }
 #pragma unroll 1
-        for (int k = 0; k < R; k++) {
-            const double4 wi = *reinterpret_cast<const double4 *>(W + k * ldw + i0);
-            const double4 wj = *reinterpret_cast<const double4 *>(W + k * ldw + j0);
-            const double wir[4] = {-wi.x, -wi.y, -wi.z, -wi.w};
-            const double wjc[4] = {wj.x, wj.y, wj.z, wj.w};
+            for (int k0 = 0; k0 < R; k0 += 4) {
+                const int k = k0 + t;
+                const double *wk = W + k * ldw;
+                double a[2], b[2];
 #pragma unroll
-            for (int c = 0; c < 4; c++)
+                for (int q = 0; q < 2; q++) {
+                    const int j = j0 + 8 * q + g, i = i0 + 8 * q + g;
+                    a[q] = (k < R && j < ldw) ? -wk[j] : 0.0;
+                    b[q] = (k < R && i < ldw) ? wk[i] : 0.0;
+                }
+                ens_dmma(c[0][0], a[0], b[0]);
+                ens_dmma(c[1][0], a[1], b[0]);
+                ens_dmma(c[1][1], a[1], b[1]);
+                if (!diag) ens_dmma(c[0][1], a[0], b[1]);
+            }
 #pragma unroll
-                for (int r = 0; r < 4; r++) acc[c][r] = fma(wir[r], wjc[c], acc[c][r]);
+            for (int sj = 0; sj < 2; sj++)
+#pragma unroll
+                for (int si = 0; si < 2; si++)
+                    if (ok[sj][si]) *reinterpret_cast<double2 *>(sm.P + off[sj][si]) = c[sj][si];
         }
-#pragma unroll
-        for (int c = 0; c < 4; c++)
-            *reinterpret_cast<double4 *>(pc + c * L) = make_double4(acc[c][0], acc[c][1], acc[c][2], acc[c][3]);
     }
     __syncthreads();
     ENS_MARK(12);
@@ -871,7 +900,7 @@ __device__ int ens_add_features(const EnsSmem &sm, int n, int k) {
 
 // One CTA = one member = one whole run of sim!.
 template <int T>
-__global__ void __launch_bounds__(T)
+__global__ void __launch_bounds__(T, T == 128 ? 5 : 1)
 k_ensemble(EnsArgs a) {
     extern __shared__ __align__(32) double ens_smem[];
     int member = blockIdx.x;
