@@ -99,6 +99,18 @@ int slam_predict(slam_t *h, double g, double v, double wheelbase, const double Q
 int slam_associate(slam_t *h, const double *z, int nz, const double R[4], double gate1,
                    double gate2, double *zf, int64_t *idf, int *m, double *zn, int *k);
 
+/* Spatial pre-gate of slam_associate (the reference's TODO at
+ * src/data-association.jl:18-20).  On (the default), a landmark is scored against an
+ * observation only if it lies inside the annulus around the vehicle outside which
+ * nis > max(gate1, gate2) is certain (Cauchy-Schwarz bound on the range innovation with a
+ * device-resident upper bound of the landmark variances, x 4 head-room); results are identical
+ * to the exhaustive scan for any positive semidefinite P.  on = 0 restores the exhaustive scan. */
+int slam_set_pregate(slam_t *h, int on);
+/* Cumulative counters of slam_associate since slam_create: landmarks scanned (annulus test on
+ * x only) and landmarks scored (5 x 5 gather + Mahalanobis distances), and the current bound
+ * on the landmark variances.  Any pointer may be NULL.  Synchronises the handle's stream. */
+int slam_gate_stats(slam_t *h, long long *scanned, long long *scored, double *sig2max);
+
 /* compute_association -- src/data-association.jl:53-63 for one (z, landmark) pair. */
 int slam_compute_association(slam_t *h, const double z[2], const double R[4], int64_t idf,
                              double *nis, double *nd);

@@ -73,6 +73,10 @@ struct slam_filter {
     size_t h_pin_bytes = 0;
     void *d_gate_scratch = nullptr;
     size_t gate_scratch = 0;
+    // spatial pre-gate of associate (gate.cu): [0] bit pattern of sig2max, [1] landmarks scanned,
+    // [2] landmarks scored (cumulative)
+    unsigned long long *d_sig2 = nullptr;
+    bool pregate = true;
     // update workspace, grown on demand
     int ws_R = 0, ws_npad = 0;
     double *d_PHt = nullptr, *d_W1c = nullptr, *d_S = nullptr, *d_C = nullptr, *d_u = nullptr,
@@ -155,6 +159,8 @@ extern "C" int slam_create(int device, int n_max, slam_t **out) {
     h->gate_scratch = gate_scratch_bytes(SLAM_MAX_OBS);
     CREATE_TRY(cudaMalloc(&h->d_gate_scratch, h->gate_scratch));
     CREATE_TRY(cudaMemsetAsync(h->d_gate_scratch, 0, 256, h->stream));
+    CREATE_TRY(cudaMalloc(&h->d_sig2, sizeof(unsigned long long) * 4));
+    CREATE_TRY(cudaMemsetAsync(h->d_sig2, 0, sizeof(unsigned long long) * 4, h->stream));
     CREATE_TRY(cudaMemsetAsync(h->d_x, 0, sizeof(double) * h->ld, h->stream));
     CREATE_TRY(cudaMemsetAsync(h->d_P, 0, sizeof(double) * h->ld * (size_t)std::min(n_max, 64), h->stream));
     CREATE_TRY(cudaMemsetAsync(h->d_pose, 0, sizeof(double) * 8, h->stream));
@@ -171,7 +177,7 @@ extern "C" int slam_destroy(slam_t *h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     cudaFree(h->d_x); cudaFree(h->d_P); cudaFree(h->d_pose); cudaFree(h->d_err);
     cudaFree(h->d_z); cudaFree(h->d_zf); cudaFree(h->d_zn); cudaFree(h->d_idf);
-    cudaFree(h->d_counts); cudaFree(h->d_small); cudaFree(h->d_gate_scratch);
+    cudaFree(h->d_counts); cudaFree(h->d_small); cudaFree(h->d_gate_scratch); cudaFree(h->d_sig2);
     cudaFree(h->d_PHt); cudaFree(h->d_W1c); cudaFree(h->d_S); cudaFree(h->d_C);
     cudaFree(h->d_u); cudaFree(h->d_v); cudaFree(h->d_Hn); cudaFree(h->d_fp);
     cudaFree(h->d_block);
@@ -262,6 +268,8 @@ extern "C" int slam_set_state(slam_t *h, const double *x, const double *P, int n
     k_set_pose_snapshot<<<1, 32, 0, h->stream>>>(h->d_x, h->d_pose + 4 * h->pose_slot);
     h->launches++;
     CUDA_TRY(cudaGetLastError());
+    int rc = launch_sig2_refresh(h->d_P, h->ld, n, h->d_sig2, h->stream, &h->launches);
+    if (rc) return rc;
     CUDA_TRY(cudaStreamSynchronize(h->stream));
     return SLAM_OK;
 }
@@ -412,7 +420,8 @@ extern "C" int slam_associate(slam_t *h, const double *z, int nz, const double R
     CUDA_TRY(cudaMemcpyAsync(h->d_z, hz, sizeof(double) * 2 * nz, cudaMemcpyHostToDevice, h->stream));
     int Nf = (h->n - 3) / 2;
     int rc = launch_gate(h->d_x, h->d_P, h->ld, Nf, h->d_z, nz, R, gate1, gate2, h->d_gate_scratch,
-                         h->gate_scratch, h->d_zf, h->d_idf, h->d_zn, h->d_counts, h->stream, &h->launches);
+                         h->gate_scratch, h->d_zf, h->d_idf, h->d_zn, h->d_counts,
+                         h->pregate ? h->d_sig2 : nullptr, h->d_sig2 + 1, h->stream, &h->launches);
     if (rc) return rc;
     // results: counts, zf, idf, zn -> pinned staging
     int *hc = (int *)h->h_pin;
@@ -429,6 +438,23 @@ extern "C" int slam_associate(slam_t *h, const double *z, int nz, const double R
     memcpy(zf, hzf, sizeof(double) * 2 * (*m));
     memcpy(idf, hid, sizeof(int64_t) * (*m));
     memcpy(zn, hzn, sizeof(double) * 2 * (*k));
+    return SLAM_OK;
+}
+
+extern "C" int slam_set_pregate(slam_t *h, int on) {
+    ARG_CHECK(h != nullptr, "NULL handle");
+    h->pregate = on != 0;
+    return SLAM_OK;
+}
+
+extern "C" int slam_gate_stats(slam_t *h, long long *scanned, long long *scored, double *sig2max) {
+    H_CHECK(h);
+    unsigned long long v[3];
+    CUDA_TRY(cudaMemcpyAsync(v, h->d_sig2, sizeof(v), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (sig2max) memcpy(sig2max, &v[0], sizeof(double));
+    if (scanned) *scanned = (long long)v[1];
+    if (scored) *scored = (long long)v[2];
     return SLAM_OK;
 }
 
@@ -1010,7 +1036,7 @@ constexpr int K7_THREADS = 256;
 
 __global__ void __launch_bounds__(K7_THREADS)
 k_augment(double *x, double *P, size_t ld, int n0, const double *__restrict__ zn, int kq, double R0,
-          double R1, double R2, double R3) {
+          double R1, double R2, double R3, unsigned long long *sig2bits) {
     // n0: state length before this launch's first landmark; kq <= K7_Q landmarks
     __shared__ double sGv[K7_Q][2];     // Gv = [1 0 g0; 0 1 g1]
     __shared__ double sGP[K7_Q][2][3];  // Gv*Pvv
@@ -1043,7 +1069,13 @@ k_augment(double *x, double *P, size_t ld, int n0, const double *__restrict__ zn
                 for (int bb = a; bb < 2; bb++) {
                     double t1 = sGP[q][a][0] * Gv[bb][0] + sGP[q][a][1] * Gv[bb][1] + sGP[q][a][2] * Gv[bb][2];
                     double t2 = GR[a][0] * Gz[bb][0] + GR[a][1] * Gz[bb][1];
-                    P[(size_t)(len + a) + (size_t)(len + bb) * ld] = t1 + t2;
+                    double pv = t1 + t2;
+                    P[(size_t)(len + a) + (size_t)(len + bb) * ld] = pv;
+                    if (a == bb) {   // keep the pre-gate's bound on the landmark variances valid (gate.cu)
+                        unsigned long long bits = (unsigned long long)__double_as_longlong(pv);
+                        if (pv != pv) bits = 0x7ff8000000000000ull;
+                        if (!(pv < 0.0)) atomicMax(sig2bits, bits);
+                    }
                 }
         }
     }
@@ -1089,7 +1121,7 @@ extern "C" int slam_add_features(slam_t *h, const double *zn, int k, const doubl
         int n0 = h->n;
         dim3 grid((n0 + 2 * kq + K7_THREADS - 1) / K7_THREADS, kq);
         k_augment<<<grid, K7_THREADS, 0, h->stream>>>(h->d_x, h->d_P, h->ld, n0, h->d_zn + 2 * q0, kq, R[0],
-                                                      R[1], R[2], R[3]);
+                                                      R[1], R[2], R[3], h->d_sig2);
         h->launches++;
         h->n = n0 + 2 * kq;
     }
@@ -1177,6 +1209,8 @@ extern "C" int slam_synth_state(slam_t *h, int n_landmarks, double side, uint64_
     k_set_pose_snapshot<<<1, 32, 0, h->stream>>>(h->d_x, h->d_pose + 4 * h->pose_slot);
     h->launches++;
     CUDA_TRY(cudaGetLastError());
+    rc = launch_sig2_refresh(h->d_P, h->ld, n, h->d_sig2, h->stream, &h->launches);
+    if (rc) return rc;
     CUDA_TRY(cudaStreamSynchronize(h->stream));
     return SLAM_OK;
 }

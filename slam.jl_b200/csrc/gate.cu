@@ -17,6 +17,24 @@
 // only consulted when jbest == 0 (:43-46), i.e. when no landmark ever passed
 // `nis < gate1 && nd < nbest`; then every landmark fell to the `elseif nis < outer` branch,
 // so outer = min_j nis_j independent of scan order.
+//
+// Spatial pre-gate (the reference's own TODO at src/data-association.jl:18-20).
+// A pair (observation i, landmark j) may be skipped without changing any output iff its
+// nis exceeds G = max(gate1, gate2): it can then neither pass `nis < gate1` (:30) nor pull
+// `outer` to or below gate2 (:38,46).  For a positive definite S, Cauchy-Schwarz gives
+//     nis = v' inv(S) v >= v_r^2 / S_rr                       (v_r = range innovation)
+// and S_rr = h P5 h' + R_rr with h = [-u, 0, u], |u| = 1, is the variance of (landmark -
+// vehicle) along u plus R_rr, so for a positive semidefinite 5 x 5 sub-block
+//     S_rr <= 2 (P_xx + P_yy) + 4 sig2max + R_rr =: S_rr_max,
+// sig2max being an upper bound of every landmark's diagonal entries of P.  The kernel skips
+// landmark j for observation i when (z_r - d_j)^2 > PREGATE_SAFETY * G * S_rr_max (a factor 4
+// of head-room over the exact bound covers every rounding of the FP64 evaluation): the
+// landmark lies outside an annulus around the vehicle.  That test needs x only (16 coalesced
+// bytes per landmark); the scattered 5 x 5 gather, atan2, log and the scoring are done for the
+// survivors, compacted per CTA so that they fill whole warps.  sig2max lives on the device: an
+// exact diagonal reduction at slam_set_state / slam_synth_state, raised by K7 for new
+// landmarks, and never lowered by update (P_ii - sum W1_ik^2 <= P_ii also in floating point).
+// NaN anywhere makes the test false, i.e. the landmark is kept.
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -130,9 +148,13 @@ __device__ __forceinline__ void score(const Innov &L, double z0, double z1, doub
     *nd = *nis + L.logdet;
 }
 
+constexpr double PREGATE_SAFETY = 4.0;
+
 struct GateParams {
     double R[4];
     double gate1, gate2;
+    const unsigned long long *sig2bits;   // bit pattern of sig2max (non-negative double); nullptr: no pre-gate
+    unsigned long long *stats;            // [0] landmarks scanned, [1] landmarks scored (cumulative); may be nullptr
 };
 
 struct GateRes {   // one rank's reduction for one observation (24 bytes, allgathered as bytes)
@@ -191,6 +213,8 @@ k_gate(const double *__restrict__ x, GateSrc src, int Ntot, const double *__rest
     __shared__ double s_nd[GATE_THREADS / 32][OB], s_outer[GATE_THREADS / 32][OB];
     __shared__ int s_j[GATE_THREADS / 32][OB];
     __shared__ bool s_last;
+    __shared__ int s_list[GATE_THREADS];
+    __shared__ int s_cnt;
     const int nblocks = gridDim.x;
     const int ob0 = blockIdx.y * OB;
     if (threadIdx.x < 9) {
@@ -199,71 +223,129 @@ k_gate(const double *__restrict__ x, GateSrc src, int Ntot, const double *__rest
     }
     __syncthreads();
     const double xv = x[0], yv = x[1], phi = x[2];
+    // pre-gate radius^2; +inf (keep everything) when there is no bound or no positive gate
+    double rho2 = INFINITY;
+    if (prm.sig2bits) {
+        double G = prm.gate1 > prm.gate2 ? prm.gate1 : prm.gate2;
+        double sig2 = __longlong_as_double((long long)*prm.sig2bits);
+        double srr = 2.0 * (fabs(sPvv[0]) + fabs(sPvv[4])) + 4.0 * sig2 + fabs(prm.R[0]);
+        double r2 = PREGATE_SAFETY * G * srr;
+        if (G > 0.0 && r2 >= 0.0) rho2 = r2;   // NaN fails the test and leaves +inf
+    }
     double zr[OB], zb[OB], best[OB], outer[OB];
     int jb[OB];
 #pragma unroll
     for (int o = 0; o < OB; o++) {
         int io = ob0 + o;
-        zr[o] = io < nz ? z[2 * io] : 0.0;
+        zr[o] = io < nz ? z[2 * io] : INFINITY;   // a padded slot never keeps a landmark; its scores are not stored
         zb[o] = io < nz ? z[2 * io + 1] : 0.0;
         best[o] = INFINITY;
         outer[o] = INFINITY;
         jb[o] = 0;
     }
-    for (int t = blockIdx.x * GATE_THREADS + threadIdx.x; t < Ntot; t += nblocks * GATE_THREADS) {
-        const int blk = t < src.j_count[0] ? 0 : 1;
-        const int j = blk == 0 ? src.j_first[0] + t : src.j_first[1] + (t - src.j_count[0]);
-        Innov L = landmark_innov(x, src, blk, 3 + 2 * (j - 1), sPvv, xv, yv, phi, prm.R);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned scored = 0;
+    for (int base = blockIdx.x * GATE_THREADS; base < Ntot; base += nblocks * GATE_THREADS) {
+        if (threadIdx.x == 0) s_cnt = 0;
+        __syncthreads();
+        // phase A: the annulus test on x alone; survivors are compacted (warp-aggregated)
+        const int t = base + threadIdx.x;
+        bool keep = false;
+        if (t < Ntot) {
+            const int j = t < src.j_count[0] ? src.j_first[0] + t : src.j_first[1] + (t - src.j_count[0]);
+            const int f = 3 + 2 * (j - 1);
+            const double dx = x[f] - xv, dy = x[f + 1] - yv;
+            const double d = sqrt(dx * dx + dy * dy);
+#pragma unroll
+            for (int o = 0; o < OB; o++) {
+                double vr = zr[o] - d;
+                keep = keep || !(vr * vr > rho2);
+            }
+        }
+        const unsigned mask = __ballot_sync(0xffffffffu, keep);
+        int wbase = 0;
+        if (lane == 0 && mask) wbase = atomicAdd(&s_cnt, __popc(mask));
+        wbase = __shfl_sync(0xffffffffu, wbase, 0);
+        if (keep) s_list[wbase + __popc(mask & ((1u << lane) - 1u))] = t;
+        __syncthreads();
+        // phase B: full scoring of the survivors, one per thread
+        const int cnt = s_cnt;
+        if (threadIdx.x < cnt) {
+            const int tt = s_list[threadIdx.x];
+            const int blk = tt < src.j_count[0] ? 0 : 1;
+            const int j = blk == 0 ? src.j_first[0] + tt : src.j_first[1] + (tt - src.j_count[0]);
+            Innov L = landmark_innov(x, src, blk, 3 + 2 * (j - 1), sPvv, xv, yv, phi, prm.R);
+#pragma unroll
+            for (int o = 0; o < OB; o++) {
+                double nis, nd;
+                score(L, zr[o], zb[o], &nis, &nd);
+                if (nis < prm.gate1 && nd < best[o]) {
+                    best[o] = nd;
+                    jb[o] = j;
+                }
+                if (nis < outer[o]) outer[o] = nis;
+            }
+        }
+        scored += cnt;
+        __syncthreads();
+    }
+    if (prm.stats && threadIdx.x == 0) {
+        if (blockIdx.y == 0) {
+            int mine = 0;
+            for (int base = blockIdx.x * GATE_THREADS; base < Ntot; base += nblocks * GATE_THREADS)
+                mine += min(GATE_THREADS, Ntot - base);
+            atomicAdd(&prm.stats[0], (unsigned long long)mine);
+        }
+        atomicAdd(&prm.stats[1], (unsigned long long)scored);
+    }
+    if (scored == 0) {
+        // no landmark of this CTA survived the pre-gate (the usual case): an empty partial, no reduction
+        if (threadIdx.x < OB && ob0 + threadIdx.x < nz) {
+            size_t slot = (size_t)blockIdx.x * nz + ob0 + threadIdx.x;
+            part_nd[slot] = INFINITY;
+            part_j[slot] = 0;
+            part_outer[slot] = INFINITY;
+        }
+    } else {
+        // warp reduction: (nd, j) lexicographic minimum, and min outer
 #pragma unroll
         for (int o = 0; o < OB; o++) {
-            double nis, nd;
-            score(L, zr[o], zb[o], &nis, &nd);
-            if (nis < prm.gate1 && nd < best[o]) {
-                best[o] = nd;
-                jb[o] = j;
-            }
-            if (nis < outer[o]) outer[o] = nis;
-        }
-    }
-    // warp reduction: (nd, j) lexicographic minimum, and min outer
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
-    for (int o = 0; o < OB; o++) {
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            double nd2 = __shfl_down_sync(0xffffffffu, best[o], off);
-            int j2 = __shfl_down_sync(0xffffffffu, jb[o], off);
-            double ou2 = __shfl_down_sync(0xffffffffu, outer[o], off);
-            if (j2 != 0 && (jb[o] == 0 || nd2 < best[o] || (nd2 == best[o] && j2 < jb[o]))) {
-                best[o] = nd2;
-                jb[o] = j2;
+            for (int off = 16; off > 0; off >>= 1) {
+                double nd2 = __shfl_down_sync(0xffffffffu, best[o], off);
+                int j2 = __shfl_down_sync(0xffffffffu, jb[o], off);
+                double ou2 = __shfl_down_sync(0xffffffffu, outer[o], off);
+                if (j2 != 0 && (jb[o] == 0 || nd2 < best[o] || (nd2 == best[o] && j2 < jb[o]))) {
+                    best[o] = nd2;
+                    jb[o] = j2;
+                }
+                if (ou2 < outer[o]) outer[o] = ou2;
             }
-            if (ou2 < outer[o]) outer[o] = ou2;
-        }
-        if (lane == 0) {
-            s_nd[warp][o] = best[o];
-            s_j[warp][o] = jb[o];
-            s_outer[warp][o] = outer[o];
-        }
-    }
-    __syncthreads();
-    if (threadIdx.x < OB && ob0 + threadIdx.x < nz) {
-        int o = threadIdx.x;
-        double b = s_nd[0][o], ou = s_outer[0][o];
-        int jj = s_j[0][o];
-        for (int w = 1; w < GATE_THREADS / 32; w++) {
-            double nd2 = s_nd[w][o];
-            int j2 = s_j[w][o];
-            if (j2 != 0 && (jj == 0 || nd2 < b || (nd2 == b && j2 < jj))) {
-                b = nd2;
-                jj = j2;
+            if (lane == 0) {
+                s_nd[warp][o] = best[o];
+                s_j[warp][o] = jb[o];
+                s_outer[warp][o] = outer[o];
             }
-            if (s_outer[w][o] < ou) ou = s_outer[w][o];
         }
-        size_t slot = (size_t)blockIdx.x * nz + ob0 + o;
-        part_nd[slot] = b;
-        part_j[slot] = jj;
-        part_outer[slot] = ou;
+        __syncthreads();
+        if (threadIdx.x < OB && ob0 + threadIdx.x < nz) {
+            int o = threadIdx.x;
+            double b = s_nd[0][o], ou = s_outer[0][o];
+            int jj = s_j[0][o];
+            for (int w = 1; w < GATE_THREADS / 32; w++) {
+                double nd2 = s_nd[w][o];
+                int j2 = s_j[w][o];
+                if (j2 != 0 && (jj == 0 || nd2 < b || (nd2 == b && j2 < jj))) {
+                    b = nd2;
+                    jj = j2;
+                }
+                if (s_outer[w][o] < ou) ou = s_outer[w][o];
+            }
+            size_t slot = (size_t)blockIdx.x * nz + ob0 + o;
+            part_nd[slot] = b;
+            part_j[slot] = jj;
+            part_outer[slot] = ou;
+        }
     }
     // last CTA to finish reduces across CTAs, classifies and compacts
     __threadfence();
@@ -277,10 +359,10 @@ k_gate(const double *__restrict__ x, GateSrc src, int Ntot, const double *__rest
     if (!s_last) return;
     __threadfence();
     __shared__ int s_cls[SLAM_MAX_OBS];   // >0: matched landmark id, 0: dropped, -1: new
-    for (int i = threadIdx.x; i < nz; i += GATE_THREADS) {
+    for (int i = warp; i < nz; i += GATE_THREADS / 32) {   // a warp per observation, lanes over the CTAs
         double b = INFINITY, ou = INFINITY;
         int jj = 0;
-        for (int blk = 0; blk < nblocks; blk++) {
+        for (int blk = lane; blk < nblocks; blk += 32) {
             size_t slot = (size_t)blk * nz + i;
             double nd2 = part_nd[slot];
             int j2 = part_j[slot];
@@ -290,11 +372,24 @@ k_gate(const double *__restrict__ x, GateSrc src, int Ntot, const double *__rest
             }
             if (part_outer[slot] < ou) ou = part_outer[slot];
         }
-        s_cls[i] = jj != 0 ? jj : (ou > prm.gate2 ? -1 : 0);
-        if (rank_res) {   // sharded: this rank's result; classification happens after the allgather
-            rank_res[i].nd = b;
-            rank_res[i].outer = ou;
-            rank_res[i].j = jj;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            double nd2 = __shfl_down_sync(0xffffffffu, b, off);
+            int j2 = __shfl_down_sync(0xffffffffu, jj, off);
+            double ou2 = __shfl_down_sync(0xffffffffu, ou, off);
+            if (j2 != 0 && (jj == 0 || nd2 < b || (nd2 == b && j2 < jj))) {
+                b = nd2;
+                jj = j2;
+            }
+            if (ou2 < ou) ou = ou2;
+        }
+        if (lane == 0) {
+            s_cls[i] = jj != 0 ? jj : (ou > prm.gate2 ? -1 : 0);
+            if (rank_res) {   // sharded: this rank's result; classification happens after the allgather
+                rank_res[i].nd = b;
+                rank_res[i].outer = ou;
+                rank_res[i].j = jj;
+            }
         }
     }
     __syncthreads();
@@ -341,9 +436,41 @@ size_t gate_scratch_bytes(int nz) {
     return 256 + per * (8 + 8 + 4);
 }
 
+// sig2max = max(0, max_f P[f, f], f >= 3) as the bit pattern of a non-negative double (ordered like
+// an unsigned integer; a NaN entry gives a pattern above +inf, which switches the pre-gate off).
+__global__ void k_sig2_diag(const double *__restrict__ P, size_t ld, int n, unsigned long long *sig2bits) {
+    unsigned long long mine = 0ull;
+    for (int f = 3 + blockIdx.x * blockDim.x + threadIdx.x; f < n; f += gridDim.x * blockDim.x) {
+        double v = P[(size_t)f * (ld + 1)];
+        unsigned long long b = (unsigned long long)__double_as_longlong(v);
+        if (v != v) b = 0x7ff8000000000000ull;
+        else if (v < 0.0) b = 0ull;
+        mine = b > mine ? b : mine;
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        unsigned long long o = __shfl_down_sync(0xffffffffu, mine, off);
+        mine = o > mine ? o : mine;
+    }
+    if ((threadIdx.x & 31) == 0 && mine) atomicMax(sig2bits, mine);
+}
+
+int launch_sig2_refresh(const double *d_P, size_t ld, int n, unsigned long long *d_sig2bits, cudaStream_t s,
+                        long long *launches) {
+    CUDA_TRY(cudaMemsetAsync(d_sig2bits, 0, sizeof(unsigned long long), s));
+    if (n <= 3) return SLAM_OK;
+    int nb = (n - 3 + 255) / 256;
+    if (nb > 296) nb = 296;
+    k_sig2_diag<<<nb, 256, 0, s>>>(d_P, ld, n, d_sig2bits);
+    if (launches) (*launches)++;
+    CUDA_TRY(cudaGetLastError());
+    return SLAM_OK;
+}
+
 int launch_gate(const double *d_x, const double *d_P, size_t ld, int Nf, const double *d_z, int nz,
                 const double R[4], double gate1, double gate2, void *d_scratch, size_t scratch_bytes,
-                double *d_zf, int64_t *d_idf, double *d_zn, int *d_counts, cudaStream_t s,
+                double *d_zf, int64_t *d_idf, double *d_zn, int *d_counts,
+                const unsigned long long *d_sig2bits, unsigned long long *d_stats, cudaStream_t s,
                 long long *launches) {
     if (scratch_bytes < gate_scratch_bytes(nz)) {
         slam_set_error("launch_gate: scratch too small");
@@ -353,6 +480,8 @@ int launch_gate(const double *d_x, const double *d_P, size_t ld, int Nf, const d
     memcpy(prm.R, R, sizeof(prm.R));
     prm.gate1 = gate1;
     prm.gate2 = gate2;
+    prm.sig2bits = d_sig2bits;
+    prm.stats = d_stats;
     size_t per = (size_t)GATE_MAX_BLOCKS * (size_t)nz;
     unsigned *counter = (unsigned *)d_scratch;
     double *part_nd = (double *)((char *)d_scratch + 256);
@@ -377,6 +506,8 @@ int launch_compute_association(const double *d_x, const double *d_P, size_t ld, 
     GateParams prm;
     memcpy(prm.R, R, sizeof(prm.R));
     prm.gate1 = prm.gate2 = 0;
+    prm.sig2bits = nullptr;
+    prm.stats = nullptr;
     k_compute_association<<<1, 1, 0, s>>>(d_x, d_P, ld, n, z[0], z[1], prm, idf, d_out2, d_err);
     if (launches) (*launches)++;
     CUDA_TRY(cudaGetLastError());
@@ -396,6 +527,8 @@ int launch_gate_shard(const double *d_x, const double *d_P3, int npad, const dou
     memcpy(prm.R, R, sizeof(prm.R));
     prm.gate1 = gate1;
     prm.gate2 = gate2;
+    prm.sig2bits = nullptr;   // sharded scan stays exhaustive
+    prm.stats = nullptr;
     GateSrc src = {};
     src.P3 = d_P3;
     src.npad = npad;

@@ -27,9 +27,14 @@ struct GateOut {           // device-side result of one associate() call
 // Works on rows [lo, hi) landmarks; P addressed through (Pbase, ld) with upper-triangle mirror.
 int launch_gate(const double *d_x, const double *d_P, size_t ld, int Nf, const double *d_z, int nz,
                 const double R[4], double gate1, double gate2, void *d_scratch, size_t scratch_bytes,
-                double *d_zf, int64_t *d_idf, double *d_zn, int *d_counts, cudaStream_t s,
+                double *d_zf, int64_t *d_idf, double *d_zn, int *d_counts,
+                const unsigned long long *d_sig2bits, unsigned long long *d_stats, cudaStream_t s,
                 long long *launches);
 size_t gate_scratch_bytes(int nz);
+// Spatial pre-gate: d_sig2bits holds the bit pattern of an upper bound of the landmarks'
+// diagonal entries of P (nullptr = exhaustive scan); launch_sig2_refresh recomputes it exactly.
+int launch_sig2_refresh(const double *d_P, size_t ld, int n, unsigned long long *d_sig2bits, cudaStream_t s,
+                        long long *launches);
 int launch_compute_association(const double *d_x, const double *d_P, size_t ld, int n, const double z[2],
                                const double R[4], int64_t idf, double *d_out2, int *d_err,
                                cudaStream_t s, long long *launches);

@@ -79,6 +79,8 @@ _sig("slam_vehicle_ellipse", I, vp, D, I, c_double_p)
 _sig("slam_predict", I, vp, D, D, D, c_double_p, D)
 _sig("slam_associate", I, vp, c_double_p, I, c_double_p, D, D, c_double_p, c_int64_p, c_int_p,
      c_double_p, c_int_p)
+_sig("slam_set_pregate", I, vp, I)
+_sig("slam_gate_stats", I, vp, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), c_double_p)
 _sig("slam_compute_association", I, vp, c_double_p, c_double_p, I64, c_double_p, c_double_p)
 _sig("slam_predict_observation", I, vp, I64, c_double_p, c_double_p)
 _sig("slam_update", I, vp, c_double_p, I, c_double_p, c_int64_p)

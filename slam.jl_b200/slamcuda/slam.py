@@ -135,6 +135,16 @@ class _Handle:
         m, k = m.value, k.value
         return (zf[:2 * m].reshape(m, 2).T.copy(), idf[:m].copy(), zn[:2 * k].reshape(k, 2).T.copy())
 
+    def set_pregate(self, on):
+        """Spatial pre-gate of associate; on by default, results identical either way."""
+        check(lib.slam_set_pregate(self.ptr, int(bool(on))))
+
+    def gate_stats(self):
+        """(landmarks scanned, landmarks scored, bound on the landmark variances), cumulative."""
+        a, b, s2 = C.c_longlong(0), C.c_longlong(0), C.c_double(0.0)
+        check(lib.slam_gate_stats(self.ptr, C.byref(a), C.byref(b), C.byref(s2)))
+        return a.value, b.value, s2.value
+
     def update(self, zf, R, idf):
         zc, m = _cols(zf)
         ids = np.ascontiguousarray(np.asarray(idf, dtype=np.int64).reshape(-1))

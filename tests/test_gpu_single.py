@@ -350,6 +350,12 @@ def test_full_size_properties(sc, nl):
     # log det S, so another landmark with a tighter S may legitimately win: most, not all, ids match)
     assert len(idf) == m and sum(int(a) == int(b) for a, b in zip(idf, ids)) >= m - 2
     assert np.array_equal(zf, zf2) and np.array_equal(idf, idf2) and np.array_equal(zn, zn2)
+    # the spatial pre-gate (on by default) against the exhaustive scan at full size
+    both = _assoc_both(h, z2, R, 4.0, 25.0)
+    for a, b in zip(both[1][0], both[0][0]):
+        assert np.array_equal(a, b)
+    print(f"\n[full size n={n}] pre-gate scored {both[1][2]} of {both[0][2]} landmark passes")
+    assert both[0][2] == 2 * nl and both[1][2] < both[0][2] // 50
     # sample: vehicle, observed landmark pairs, four windows
     rng = np.random.default_rng(1)
     seen = sorted({int(i) for i in idf})
@@ -384,4 +390,124 @@ def test_full_size_properties(sc, nl):
     np.linalg.cholesky(P1[:nobs, :nobs])                              # observed block stays PD
     # states outside the sample moved too (the update is dense): spot-check that x changed there
     assert np.any(x1 != x0)
+    h.close()
+
+
+def _assoc_both(h, z, R, g1, g2):
+    """associate with the spatial pre-gate on and off on the same resident state -> both results and
+    the landmarks (scanned, scored) of each call."""
+    out = {}
+    for on in (1, 0):
+        h.set_pregate(on)
+        a0, b0, _ = h.gate_stats()
+        res = h.associate(z, R, g1, g2)
+        a1, b1, _ = h.gate_stats()
+        out[on] = (res, a1 - a0, b1 - b0)
+    h.set_pregate(1)
+    return out
+
+
+@pytest.mark.parametrize("nf,nz,side,gates", [
+    (5000, 12, 1200.0, (4.0, 25.0)),
+    (5000, 64, 1200.0, (4.0, 25.0)),       # eight passes of eight observations
+    (1000, 20, 60.0, (4.0, 25.0)),         # dense field: most landmarks inside some annulus
+    (3000, 9, 900.0, (25.0, 4.0)),         # gate2 < gate1: the radius follows the larger gate
+    (3000, 9, 900.0, (1e6, 1e7)),          # huge gates: radius beyond the field, nothing may be skipped wrongly
+    (3000, 9, 900.0, (-1.0, -2.0)),        # no positive gate: pre-gate switches itself off
+    (2000, 16, 700.0, (4.0, float("inf"))),
+])
+def test_pregate_identical_to_exhaustive(sc, twin, nf, nz, side, gates):
+    """SURVEY 8 f4 (the reference's TODO at src/data-association.jl:18-20): the annulus pre-gate may only
+    skip pairs whose nis is certainly above both gates, so zf / idf / zn must be bit-identical to the
+    exhaustive scan (and to the C twin's sequential scan) -- on observations of mapped landmarks,
+    observations placed next to the gate2 boundary of a landmark (drop zone vs new feature) and far
+    spurious ones."""
+    from slamcuda.slam import _Handle
+    from twin_ffi import Twin
+    k = ref.sim_constants()
+    R = k["R"]
+    rng = np.random.default_rng(nf + 13 * nz)
+    n = 3 + 2 * nf
+    x = np.concatenate([[side / 2, side / 2, 0.3], rng.uniform(0, side, size=2 * nf)])
+    L = rng.normal(0, 0.05, size=(n, 8))
+    P = L @ L.T + np.diag(rng.uniform(0.01, 0.1, size=n))
+    d = np.hypot(x[3::2] - x[0], x[4::2] - x[1])
+    near = np.argsort(d)[:max(nz, 8)] + 1
+    z = np.zeros((2, nz))
+    for c in range(nz):
+        idf = int(near[c % len(near)])
+        zp, H = ref.predict_observation(x, idf)
+        S = H @ P @ H.T + R
+        if c % 3 == 0:      # a genuine observation
+            z[:, c] = zp + rng.normal(0, [0.1, 0.01])
+        elif c % 3 == 1:    # on the gate2 ellipse of that landmark, +-2 %
+            u = rng.normal(size=2)
+            u /= np.linalg.norm(u)
+            z[:, c] = zp + np.linalg.cholesky(S) @ u * math.sqrt(25.0) * rng.choice([0.98, 1.02])
+        else:               # spurious
+            z[:, c] = [rng.uniform(0.3, 0.6) * side, rng.uniform(-3, 3)]
+    h = _Handle(0, n)
+    h.set_state(x, P)
+    out = _assoc_both(h, z, R, *gates)
+    (zf1, idf1, zn1), scan1, score1 = out[1]
+    (zf0, idf0, zn0), scan0, score0 = out[0]
+    h.close()
+    passes = (nz + 7) // 8
+    print(f"\n[pre-gate Nf={nf} nz={nz} gates={gates}] matched {len(idf0)} new {zn0.shape[1]}; scored "
+          f"{score1} of {scan1 * passes} landmark passes with the pre-gate, {score0} without")
+    assert np.array_equal(idf1, idf0) and np.array_equal(zf1, zf0) and np.array_equal(zn1, zn0)
+    assert scan1 == nf and scan0 == nf and score0 == nf * passes
+    if gates == (4.0, 25.0) and side > 100:
+        assert score1 < score0 // 5, "the pre-gate skipped too little"
+        assert len(idf0) >= nz // 3 and 0 < zn0.shape[1]
+    if gates[0] < 0:
+        assert score1 == score0
+    if np.isfinite(gates[1]):
+        zf_t, idf_t, zn_t = Twin(twin).associate(x, P, z, R, *gates)
+        assert np.array_equal(idf1.reshape(-1), idf_t) and np.array_equal(zf1, zf_t) and np.array_equal(zn1, zn_t)
+
+
+def test_pregate_bound_follows_the_state(sc):
+    """The pre-gate's device-resident bound on the landmark variances: exact at set_state, raised by
+    add_features (K7) for far, uncertain new landmarks, never below the diagonal after update; and the
+    association stays identical to the exhaustive scan through such a sequence."""
+    from slamcuda.slam import _Handle
+    k = ref.sim_constants()
+    R = k["R"]
+    rng = np.random.default_rng(21)
+    x, P = _random_state(rng, 400)
+    h = _Handle(0, 3 + 2 * 440)
+    h.set_state(x, P)
+    assert h.gate_stats()[2] == np.max(np.diag(P)[3:])
+    zn = np.array([rng.uniform(300, 900, 30), rng.uniform(-3, 3, 30)])     # variance ~ (r * 1 deg)^2, up to ~250
+    h.add_features(zn, R)
+    x1, P1 = h.get_state()
+    s2 = h.gate_stats()[2]
+    assert s2 == np.max(np.diag(P1)[3:]) and s2 > 10 * np.max(np.diag(P)[3:])
+    # observe some of the far landmarks again (noisy) plus near ones and spurious ones
+    ids = np.concatenate([401 + rng.choice(30, 6, replace=False), rng.choice(400, 4, replace=False) + 1])
+    z = np.zeros((2, 14))
+    for c, idf in enumerate(ids):
+        zp, _ = ref.predict_observation(x1, int(idf))
+        z[:, c] = zp + rng.normal(0, [0.1, 0.01])
+    z[:, 10:] = np.array([rng.uniform(100, 1500, 4), rng.uniform(-3, 3, 4)])
+    out = _assoc_both(h, z, R, 4.0, 25.0)
+    for a, b in zip(out[1][0], out[0][0]):
+        assert np.array_equal(a, b)
+    zf, idf, _ = out[1][0]
+    assert len(idf) >= 8
+    h.update(zf, R, idf)
+    _, P2 = h.get_state()
+    assert h.gate_stats()[2] == s2 >= np.max(np.diag(P2)[3:])           # update only shrinks variances
+    out = _assoc_both(h, z, R, 4.0, 25.0)
+    for a, b in zip(out[1][0], out[0][0]):
+        assert np.array_equal(a, b)
+    # NaN in the state: the bound turns NaN, the annulus test is false everywhere, nothing is skipped
+    P2[7, 7] = float("nan")
+    h.set_state(x1, P2)
+    assert math.isnan(h.gate_stats()[2])
+    out = _assoc_both(h, z, R, 4.0, 25.0)
+    for a, b in zip(out[1][0], out[0][0]):
+        assert np.array_equal(a, b)
+    assert out[1][2] == out[0][2]
     h.close()
