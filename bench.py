@@ -220,6 +220,27 @@ def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_ste
             out["e2e_ms_per_step"] = (time.perf_counter() - t0) / e2e_steps * 1e3
             out["h2d_bytes"] = 16 * m + 8 * m
             out["d2h_bytes"] = 4 + 24
+            # the observation step of sim! (sim/ekfslam-sim.jl:114-117): associate (host z in, zf / idf / zn out,
+            # one k_gate launch with the spatial pre-gate) then update with what it returned, pose out.
+            # add_features is left out: the map fills its capacity, the spurious observations are only classified.
+            zf2, zn2 = np.zeros(2 * nz), np.zeros(2 * nz)
+            idf2 = np.zeros(nz, dtype=np.int64)
+            ta = []
+            t0 = time.perf_counter()
+            for _ in range(e2e_steps):
+                t1 = time.perf_counter()
+                check(lib.slam_associate(h, dptr(z), nz, dptr(R_OBS), 4.0, 25.0, dptr(zf2), iptr(idf2), C.byref(mm),
+                                         dptr(zn2), C.byref(kk)))
+                ta.append(time.perf_counter() - t1)
+                check(lib.slam_update(h, dptr(zf2), mm.value, dptr(R_OBS), iptr(idf2)))
+                check(lib.slam_get_pose(h, dptr(pose)))
+            torch.cuda.synchronize(device)
+            out["obs_step_ms"] = (time.perf_counter() - t0) / e2e_steps * 1e3
+            out["assoc_ms"] = sorted(ta)[len(ta) // 2] * 1e3
+            out["assoc_matched"] = mm.value
+            scanned, scored = C.c_longlong(), C.c_longlong()
+            check(lib.slam_gate_stats(h, C.byref(scanned), C.byref(scored), None))
+            out["gate_scored_frac"] = scored.value / max(scanned.value * ((nz + 7) // 8), 1)
         return out
     finally:
         lib.slam_destroy(h)
@@ -531,6 +552,12 @@ def main():
                      "k6_share_of_step": r["k6_ms"] / ms,
                      **({"phase_ms_over_ranks": r["phase_ms"]} if "phase_ms" in r else {})},
     }
+    if "obs_step_ms" in r:
+        line["observation_step"] = {
+            "what": "slam_associate (nz host observations in, zf / idf / zn out) + slam_update with its result + "
+                    "slam_get_pose, every step (sim/ekfslam-sim.jl:114-117 without add_features)",
+            "value": 1e3 / r["obs_step_ms"], "unit": "observation steps/s", "associate_ms": r["assoc_ms"],
+            "matched": r["assoc_matched"], "landmark_passes_scored_frac": r["gate_scored_frac"]}
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline_block(n, args.m, sample_landmarks=args.sample_landmarks)
     line.update(extras)

@@ -43,6 +43,7 @@ namespace {
 constexpr int GATE_THREADS = 256;
 constexpr int OB = 8;            // observations scored per thread per pass
 constexpr int GATE_MAX_BLOCKS = 592;
+constexpr int GATE_SMS = 148;
 
 struct Innov {     // per-landmark quantities that do not depend on the observation
     double zp0, zp1, i11, i12, i21, i22, logdet;
@@ -162,24 +163,56 @@ struct GateRes {   // one rank's reduction for one observation (24 bytes, allgat
     long long j;
 };
 
-__device__ void gate_compact(const int *cls, const double *z, int nz, double *zf, int64_t *idf, double *zn,
-                             int *counts) {
-    int m = 0, k = 0;
-    for (int i = 0; i < nz; i++) {
-        int c = cls[i];
-        if (c > 0) {
-            zf[2 * m] = z[2 * i];
-            zf[2 * m + 1] = z[2 * i + 1];
-            idf[m] = c;
-            m++;
-        } else if (c < 0) {
-            zn[2 * k] = z[2 * i];
-            zn[2 * k + 1] = z[2 * i + 1];
-            k++;
+// Stable compaction of the classified observations into zf / idf / zn (observation order kept, as the
+// reference appends in scan order, src/data-association.jl:43-48).  Called by every thread of the CTA:
+// ballot ranks inside a warp, warp totals through shared memory, chunks of blockDim observations.
+__device__ void gate_compact(const int *cls, const double *__restrict__ z, int nz, double *zf, int64_t *idf,
+                             double *zn, int *counts) {
+    __shared__ int s_wm[32], s_wk[32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    int m0 = 0, k0 = 0;   // matched / new before this chunk
+    for (int c0 = 0; c0 < nz; c0 += blockDim.x) {
+        const int i = c0 + threadIdx.x;
+        const int c = i < nz ? cls[i] : 0;
+        double z0 = 0, z1 = 0;
+        if (c != 0) {
+            z0 = z[2 * i];
+            z1 = z[2 * i + 1];
         }
+        const unsigned bm = __ballot_sync(0xffffffffu, c > 0), bk = __ballot_sync(0xffffffffu, c < 0);
+        if (lane == 0) {
+            s_wm[warp] = __popc(bm);
+            s_wk[warp] = __popc(bk);
+        }
+        __syncthreads();
+        int mo = m0, ko = k0, mt = 0, kt = 0;
+        for (int w = 0; w < nwarps; w++) {
+            if (w < warp) {
+                mo += s_wm[w];
+                ko += s_wk[w];
+            }
+            mt += s_wm[w];
+            kt += s_wk[w];
+        }
+        const unsigned lt = (1u << lane) - 1u;
+        if (c > 0) {
+            int r = mo + __popc(bm & lt);
+            zf[2 * r] = z0;
+            zf[2 * r + 1] = z1;
+            idf[r] = c;
+        } else if (c < 0) {
+            int r = ko + __popc(bk & lt);
+            zn[2 * r] = z0;
+            zn[2 * r + 1] = z1;
+        }
+        m0 += mt;
+        k0 += kt;
+        __syncthreads();
     }
-    counts[0] = m;
-    counts[1] = k;
+    if (threadIdx.x == 0) {
+        counts[0] = m0;
+        counts[1] = k0;
+    }
 }
 
 // sharded path: every rank reduces the allgathered per-rank results identically
@@ -200,7 +233,7 @@ __global__ void k_gate_finalize(const GateRes *__restrict__ all, int world, cons
         s_cls[i] = jj != 0 ? (int)jj : (ou > prm.gate2 ? -1 : 0);
     }
     __syncthreads();
-    if (threadIdx.x == 0) gate_compact(s_cls, z, nz, zf, idf, zn, counts);
+    gate_compact(s_cls, z, nz, zf, idf, zn, counts);
 }
 
 // scratch: [0] unsigned counter, then part_nd / part_outer (double) and part_j (int) of
@@ -217,17 +250,18 @@ k_gate(const double *__restrict__ x, GateSrc src, int Ntot, const double *__rest
     __shared__ int s_cnt;
     const int nblocks = gridDim.x;
     const int ob0 = blockIdx.y * OB;
+    // every global load that does not depend on another is issued ahead of the first barrier
+    const double xv = x[0], yv = x[1], phi = x[2];
+    const double sig2 = prm.sig2bits ? __longlong_as_double((long long)*prm.sig2bits) : 0.0;
     if (threadIdx.x < 9) {
         int p = threadIdx.x / 3, q = threadIdx.x % 3;
         sPvv[threadIdx.x] = gate_pvv(src, p, q);
     }
     __syncthreads();
-    const double xv = x[0], yv = x[1], phi = x[2];
     // pre-gate radius^2; +inf (keep everything) when there is no bound or no positive gate
     double rho2 = INFINITY;
     if (prm.sig2bits) {
         double G = prm.gate1 > prm.gate2 ? prm.gate1 : prm.gate2;
-        double sig2 = __longlong_as_double((long long)*prm.sig2bits);
         double srr = 2.0 * (fabs(sPvv[0]) + fabs(sPvv[4])) + 4.0 * sig2 + fabs(prm.R[0]);
         double r2 = PREGATE_SAFETY * G * srr;
         if (G > 0.0 && r2 >= 0.0) rho2 = r2;   // NaN fails the test and leaves +inf
@@ -397,10 +431,8 @@ k_gate(const double *__restrict__ x, GateSrc src, int Ntot, const double *__rest
         if (threadIdx.x == 0) *counter = 0;
         return;
     }
-    if (threadIdx.x == 0) {
-        gate_compact(s_cls, z, nz, zf, idf, zn, counts);
-        *counter = 0;
-    }
+    gate_compact(s_cls, z, nz, zf, idf, zn, counts);
+    if (threadIdx.x == 0) *counter = 0;
 }
 
 __global__ void k_compute_association(const double *__restrict__ x, const double *__restrict__ P,
@@ -492,7 +524,16 @@ int launch_gate(const double *d_x, const double *d_P, size_t ld, int Nf, const d
     src.ld = ld;
     src.j_first[0] = 1;
     src.j_count[0] = Nf;
-    dim3 grid(gate_nblocks(Nf), (nz + OB - 1) / OB);
+    const int ny = (nz + OB - 1) / OB;
+    int nb = gate_nblocks(Nf);
+    if (d_sig2bits) {
+        // pre-gated: a landmark costs one coalesced 16-byte load and a sqrt, so the whole grid is kept within
+        // one wave (two CTAs per SM) and a CTA strides over several landmarks per thread
+        int cap = 2 * GATE_SMS / ny;
+        if (cap < 16) cap = 16;
+        if (nb > cap) nb = cap;
+    }
+    dim3 grid(nb, ny);
     k_gate<<<grid, GATE_THREADS, 0, s>>>(d_x, src, Nf, d_z, nz, prm, counter, part_nd, part_outer, part_j, d_zf,
                                         d_idf, d_zn, d_counts, nullptr);
     if (launches) (*launches)++;
