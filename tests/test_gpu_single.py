@@ -444,8 +444,8 @@ def test_pregate_identical_to_exhaustive(sc, twin, nf, nz, side, gates):
             u = rng.normal(size=2)
             u /= np.linalg.norm(u)
             z[:, c] = zp + np.linalg.cholesky(S) @ u * math.sqrt(25.0) * rng.choice([0.98, 1.02])
-        else:               # spurious
-            z[:, c] = [rng.uniform(0.3, 0.6) * side, rng.uniform(-3, 3)]
+        else:               # spurious: inside the field (may match, drop or be new) or beyond it (always new)
+            z[:, c] = [rng.uniform(0.3, 0.6) * side * (1 if c % 2 else 4), rng.uniform(-3, 3)]
     h = _Handle(0, n)
     h.set_state(x, P)
     out = _assoc_both(h, z, R, *gates)
