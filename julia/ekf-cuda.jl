@@ -188,6 +188,14 @@ function associate(state::SlamState, z, R, gate1, gate2)
     return zf[:, 1:m[]], reshape(convert(Vector{Int}, idf[1:m[]]), 1, Int(m[])), zn[:, 1:k[]]
 end
 
+# The spatial pre-gate the reference leaves as a TODO (src/data-association.jl:18-20) is on by default and
+# returns exactly what the exhaustive scan returns; associate_exhaustive!(state, true) switches it off.
+function associate_exhaustive!(state::SlamState, exhaustive::Bool)
+    h = isa(state, CudaEKFSlamState) ? state.h : scratch_handle(length(state.x))   # the flag lives in the handle
+    slam_check(ccall((:slam_set_pregate, libslamcuda), Cint, (Ptr{Void}, Cint), h.ptr, exhaustive ? 0 : 1))
+    return nothing
+end
+
 # compute_association -- replaces src/data-association.jl:53-63 -> (nis, nd)
 function compute_association(x, P, z, R, idf)
     h = scratch_handle(length(x))
