@@ -158,7 +158,7 @@ def cpu_baseline_block(n_workload: int, m: int, steps: int = 3, warmup: int = 1,
 # GPU arm, one filter on one GPU
 # ----------------------------------------------------------------------------------------
 def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_steps: int, device: int = 0,
-                      barrier=None):
+                      barrier=None, host_mirror_steps: int = 0):
     """Returns timing of `update` on a synthetic n_landmarks map resident on `device`."""
     import torch
     from slamcuda._ffi import lib, check, dptr, iptr
@@ -241,6 +241,21 @@ def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_ste
             scanned, scored = C.c_longlong(), C.c_longlong()
             check(lib.slam_gate_stats(h, C.byref(scanned), C.byref(scored), None))
             out["gate_scored_frac"] = scored.value / max(scanned.value * ((nz + 7) // 8), 1)
+        # host-mirror mode, the reference's literal calling convention (`state.x, state.cov = update(state, ...)`
+        # on host arrays, src/ekf.jl:46-77 returns fresh arrays): x and the WHOLE of P cross PCIe both ways every
+        # call.  Reported for transparency; resident mode (above) is what the path is built for.
+        if host_mirror_steps > 0:
+            xh = np.zeros(n)
+            Ph = np.zeros((n, n), order="F")
+            check(lib.slam_get_state(h, dptr(xh), dptr(Ph), n))
+            t0 = time.perf_counter()
+            for _ in range(host_mirror_steps):
+                check(lib.slam_set_state(h, dptr(xh), dptr(Ph), n, n))
+                check(lib.slam_update(h, dptr(zf), m, dptr(R_OBS), iptr(idf)))
+                check(lib.slam_get_state(h, dptr(xh), dptr(Ph), n))
+            out["host_mirror_ms_per_step"] = (time.perf_counter() - t0) / host_mirror_steps * 1e3
+            out["host_mirror_bytes_each_way"] = 8 * n * (n + 1)
+            del Ph
         return out
     finally:
         lib.slam_destroy(h)
@@ -503,14 +518,21 @@ def main():
         ms = r["ms_per_step"]
         alg_bytes = 8.0 * n * (n + 1)
         if not args.no_extras:
-            r10 = gpu_update_single(10000, args.m, max(args.steps, 50), args.warmup, e2e_steps=20)
+            r10 = gpu_update_single(10000, args.m, max(args.steps, 50), args.warmup, e2e_steps=20,
+                                    host_mirror_steps=2)
             b10 = 8.0 * 20003 * 20004
             extras["update_10k"] = {
                 "workload": "BASELINE config 3: single filter, 10k landmarks (n = 20003, P = 3.2 GB), 1 B200",
                 "value": 1e3 / r10["ms_per_step"], "unit": "update steps/s", "m": args.m,
                 "e2e": 1e3 / r10["e2e_ms_per_step"], "k6_ms": r10["k6_ms"],
                 "k6_gbs": b10 / (r10["k6_ms"] * 1e-3) / 1e9, "k6_frac": b10 / (r10["k6_ms"] * 1e-3) / 1e9 / peak,
-                "associate_ms": r10["assoc_ms"]}
+                "associate_ms": r10["assoc_ms"],
+                "host_mirror_e2e": {
+                    "what": "slam_set_state + slam_update + slam_get_state per step: the reference's literal "
+                            "convention, x and all of P (pageable host arrays) over PCIe both ways every call",
+                    "value": 1e3 / r10["host_mirror_ms_per_step"], "unit": "update steps/s",
+                    "h2d_bytes_per_step": r10["host_mirror_bytes_each_way"],
+                    "d2h_bytes_per_step": r10["host_mirror_bytes_each_way"]}}
             extras["ensemble"] = gpu_ensemble(ENS_RUNS_PER_GPU, 0, 1, 0)
             extras["ensemble_4096"] = gpu_ensemble(4096, 0, 1, 0)
             if not args.no_cpu:

@@ -511,3 +511,42 @@ def test_pregate_bound_follows_the_state(sc):
         assert np.array_equal(a, b)
     assert out[1][2] == out[0][2]
     h.close()
+
+
+def test_closed_loop_large_course(sc, twin, course1):
+    """sim! closed loop on a course six times the size of course1 (600 m, 725 landmarks in the field, the
+    map grows to ~320 landmarks over 886 observation steps), state resident on the device, against the C
+    twin's run of the same inputs: every association (pre-gated scan), update and in-place append of a growing
+    map has to agree for the tracks to agree.  End-of-run tolerance 1e-6 as north_star states."""
+    import ctypes as C
+    from slamcuda import sim as gsim
+    from twin_ffi import d
+    scale, extra, ms = 6, 40, 12000
+    wp = course1 * scale
+    rng = np.random.default_rng(11)
+    lo, hi = wp.min(axis=1) - 20, wp.max(axis=1) + 20
+    nl = int(0.0035 * np.prod(hi - lo))
+    lm = np.vstack([rng.uniform(lo[0], hi[0], nl), rng.uniform(lo[1], hi[1], nl)])
+    ctrl = rng.standard_normal((2, ms))
+    obs = rng.standard_normal(200000)
+    ld = 3 + 2 * (nl + extra)
+    tt, st, xo, Po = np.zeros(3 * ms), np.zeros(3 * ms), np.zeros(ld), np.zeros(ld * ld)
+    counts = (C.c_int * 4)()
+    mg = C.c_double()
+    twin.twin_sim_cap.restype = C.c_int
+    rc = twin.twin_sim_cap(d(np.ascontiguousarray(wp.T).reshape(-1)), wp.shape[1],
+                           d(np.ascontiguousarray(lm.T).reshape(-1)), nl, d(np.ascontiguousarray(ctrl.T).reshape(-1)),
+                           d(obs), len(obs), C.c_uint64(0), C.c_uint32(0), 1, ms, d(tt), d(st), d(xo), d(Po), counts,
+                           C.byref(mg), extra)
+    assert rc == 0
+    ns, nupd, nfin = counts[0], counts[1], counts[2]
+    out = gsim.run(wp, lm, ctrl, obs, nlaps=1, n_max=ld, max_steps=ms)
+    assert out["nsteps"] == ns and out["nupdates"] == nupd and len(out["x"]) == nfin
+    trk = st[:3 * ns].reshape(ns, 3).T
+    e_track = float(np.max(np.abs(out["slam_track"] - trk))) / float(np.max(np.abs(trk)))
+    Pt = Po.reshape(ld, ld).T[:nfin, :nfin]
+    print(f"\n[closed loop x{scale}] {ns} steps, {nupd} observation steps, n = {nfin}, twin margin {mg.value:.2e}; "
+          f"track rel {e_track:.2e}, x rel {rel_err(out['x'], xo[:nfin]):.2e}, P rel {rel_err(out['P'], Pt):.2e}, "
+          f"{out['launches']} launches")
+    assert e_track < TRACK_TOL and rel_err(out["x"], xo[:nfin]) < TRACK_TOL and rel_err(out["P"], Pt) < TRACK_TOL
+    assert nfin > 3 + 2 * 250 and mg.value > 1e-9
