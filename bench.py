@@ -254,7 +254,7 @@ def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_ste
                 check(lib.slam_update(h, dptr(zf), m, dptr(R_OBS), iptr(idf)))
                 check(lib.slam_get_state(h, dptr(xh), dptr(Ph), n))
             out["host_mirror_ms_per_step"] = (time.perf_counter() - t0) / host_mirror_steps * 1e3
-            out["host_mirror_bytes_each_way"] = 8 * n * (n + 1)
+            out["host_mirror_bytes_each_way"] = 8 * n * n + 8 * n
             del Ph
         return out
     finally:
