@@ -497,6 +497,11 @@ def main():
     if args.impl == "reference":
         reference_arm(args, rank)
         return
+    # stdout carries exactly ONE JSON line: anything a library writes to fd 1 meanwhile (NCCL prints its version
+    # banner there) is sent to stderr, and the line goes out through the saved descriptor at the end
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
     import torch
     import slamcuda
@@ -586,7 +591,8 @@ def main():
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline_block(n, args.m, sample_landmarks=args.sample_landmarks)
     line.update(extras)
-    print(json.dumps(line), flush=True)
+    real_stdout.write(json.dumps(line) + "\n")
+    real_stdout.flush()
 
 
 if __name__ == "__main__":
