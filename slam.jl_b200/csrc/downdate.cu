@@ -96,7 +96,10 @@ __device__ __forceinline__ void prefetch_batch(const double *warp_col, size_t ld
 // The single-filter path passes r0 = 0, r1 = n, Pb = P.
 // W1r: [n_pad][RC] row-major (column-side rows, staged by one bulk copy per tile);
 // W1t: [RC][n_pad] rank-major (row-side values, coalesced register loads).
-template <int RC, int ROWS, int U, int PD>
+// PIPE = 1 adds a two-deep register pipeline on top of the L2 prefetch: the loads of batch b+1 are issued before
+// the FMAs of batch b.  It pays where the kernel is held at two CTAs per SM by its W1 rows anyway (RC >= 24:
+// 2 x RC doubles per thread), so the second buffer costs no occupancy.
+template <int RC, int ROWS, int U, int PD, int PIPE>
 __global__ void __launch_bounds__(DD_THREADS)
 k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n_pad,
                const double *__restrict__ W1r, const double *__restrict__ W1t) {
@@ -153,15 +156,38 @@ k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n
     double *col = Pb + (size_t)(i - r0) + (size_t)jstart * ldb;
     const double *sWj = sW + (size_t)(jstart - j0) * RC;
     const bool row_ok = i < r1;   // rows past the block end (ragged last warp) do nothing
-    for (int b = 0; b < nfull; b++) {
-        if (PD > 0 && b + PD < nfull) prefetch_batch<ROWS, U>(wcol + (size_t)((b + PD) * U) * ldb, ldb, lane, jend - jstart - (b + PD) * U);
-        if (row_ok) {
-            double a[U][ROWS];
-            load_batch<RC, ROWS, U>(a, col, ldb);
-            fma_store_batch<RC, ROWS, U>(a, wi, sWj, col, ldb);
+    if (PIPE) {
+        double a0[U][ROWS], a1[U][ROWS];
+        if (row_ok && nfull > 0) load_batch<RC, ROWS, U>(a0, col, ldb);
+        for (int b = 0; b < nfull; b += 2) {
+            if (PD > 0) {
+                if (b + PD < nfull) prefetch_batch<ROWS, U>(wcol + (size_t)((b + PD) * U) * ldb, ldb, lane, jend - jstart - (b + PD) * U);
+                if (b + 1 + PD < nfull) prefetch_batch<ROWS, U>(wcol + (size_t)((b + 1 + PD) * U) * ldb, ldb, lane, jend - jstart - (b + 1 + PD) * U);
+            }
+            if (row_ok) {
+                if (b + 1 < nfull) load_batch<RC, ROWS, U>(a1, col + (size_t)U * ldb, ldb);
+                fma_store_batch<RC, ROWS, U>(a0, wi, sWj, col, ldb);
+                if (b + 2 < nfull) load_batch<RC, ROWS, U>(a0, col + (size_t)(2 * U) * ldb, ldb);
+                if (b + 1 < nfull) fma_store_batch<RC, ROWS, U>(a1, wi, sWj + (size_t)U * RC, col + (size_t)U * ldb, ldb);
+            }
+            col += (size_t)(2 * U) * ldb;
+            sWj += (size_t)(2 * U) * RC;
         }
-        col += (size_t)U * ldb;
-        sWj += (size_t)U * RC;
+        if (nfull & 1) {   // the loop stepped one batch past the end
+            col -= (size_t)U * ldb;
+            sWj -= (size_t)U * RC;
+        }
+    } else {
+        for (int b = 0; b < nfull; b++) {
+            if (PD > 0 && b + PD < nfull) prefetch_batch<ROWS, U>(wcol + (size_t)((b + PD) * U) * ldb, ldb, lane, jend - jstart - (b + PD) * U);
+            if (row_ok) {
+                double a[U][ROWS];
+                load_batch<RC, ROWS, U>(a, col, ldb);
+                fma_store_batch<RC, ROWS, U>(a, wi, sWj, col, ldb);
+            }
+            col += (size_t)U * ldb;
+            sWj += (size_t)U * RC;
+        }
     }
     if (row_ok) {
         for (int j = jstart + nfull * U; j < jend; j++) {   // leftover columns of the last tile
@@ -178,39 +204,43 @@ k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n
     }
 }
 
-struct DdCfg { int rows, u, pd; };
+struct DdCfg { int rows, u, pd, pipe; };
 
 // experiment hook: SLAM_K6_CFG="rows,u,pd" overrides the tuned choice
 DdCfg pick_cfg(int RC) {
     // measured on B200 at n = 20003 (profiles/r1_k6_sweep.md): the L2 prefetch pays once the FMA phase
     // is long enough to starve the register-staged loads (rank >= 8)
-    DdCfg c = RC <= 4 ? DdCfg{2, 8, 0} : RC <= 16 ? DdCfg{2, 8, 1} : DdCfg{2, 4, 4};
+    // RC = 32 (254 registers, two CTAs per SM whatever it does): + a two-deep register pipeline, 0.724 -> 0.678 ms
+    DdCfg c = RC <= 4 ? DdCfg{2, 8, 0, 0} : RC <= 16 ? DdCfg{2, 8, 1, 0} : RC <= 24 ? DdCfg{2, 4, 4, 0} : DdCfg{2, 8, 2, 1};
     if (const char *e = getenv("SLAM_K6_CFG")) {
-        int r, u, pd;
-        if (sscanf(e, "%d,%d,%d", &r, &u, &pd) == 3) c = DdCfg{r, u, pd};
+        int r, u, pd, pipe = 0;
+        if (sscanf(e, "%d,%d,%d,%d", &r, &u, &pd, &pipe) >= 3) c = DdCfg{r, u, pd, pipe};
     }
     return c;
 }
 
-template <int RC, int ROWS, int U, int PD>
+template <int RC, int ROWS, int U, int PD, int PIPE>
 void launch_one(double *Pb, size_t ldb, int r0, int r1, int n, int n_pad, const double *W1r,
                 const double *W1t, cudaStream_t s) {
     constexpr int BI = DD_THREADS * ROWS;
     dim3 grid((r1 - r0 + BI - 1) / BI, (n + DD_BJ - 1) / DD_BJ);
-    k_downdate_fma<RC, ROWS, U, PD><<<grid, DD_THREADS, 0, s>>>(Pb, ldb, r0, r1, n, n_pad, W1r, W1t);
+    k_downdate_fma<RC, ROWS, U, PD, PIPE><<<grid, DD_THREADS, 0, s>>>(Pb, ldb, r0, r1, n, n_pad, W1r, W1t);
 }
 
 template <int RC>
 bool launch_cfg(const DdCfg &c, double *Pb, size_t ldb, int r0, int r1, int n, int n_pad, const double *W1r,
                 const double *W1t, cudaStream_t s) {
-#define TRY_CFG(R_, U_, PD_)                                                   \
-    if (c.rows == R_ && c.u == U_ && c.pd == PD_) {                            \
-        launch_one<RC, R_, U_, PD_>(Pb, ldb, r0, r1, n, n_pad, W1r, W1t, s);   \
-        return true;                                                           \
+#define TRY_CFG(R_, U_, PD_, PIPE_)                                                   \
+    if (c.rows == R_ && c.u == U_ && c.pd == PD_ && c.pipe == PIPE_) {                  \
+        launch_one<RC, R_, U_, PD_, PIPE_>(Pb, ldb, r0, r1, n, n_pad, W1r, W1t, s);     \
+        return true;                                                                    \
     }
-    TRY_CFG(2, 8, 0) TRY_CFG(2, 8, 1) TRY_CFG(2, 8, 2)
-    TRY_CFG(2, 4, 1) TRY_CFG(2, 4, 2) TRY_CFG(2, 4, 4)
-    TRY_CFG(1, 8, 2)
+    TRY_CFG(2, 8, 0, 0) TRY_CFG(2, 8, 1, 0) TRY_CFG(2, 8, 2, 0)
+    TRY_CFG(2, 4, 1, 0) TRY_CFG(2, 4, 2, 0) TRY_CFG(2, 4, 4, 0)
+    TRY_CFG(1, 8, 2, 0)
+    if (RC >= 24) {   // register-pipelined variants (two CTAs per SM either way)
+        TRY_CFG(2, 4, 2, 1) TRY_CFG(2, 8, 2, 1)
+    }
 #undef TRY_CFG
     return false;
 }
