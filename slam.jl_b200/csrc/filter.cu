@@ -65,9 +65,9 @@ struct slam_filter {
     int pose_slot = 0;
     int *d_err = nullptr;      // latched device-side error code
     // observation staging (device) and pinned host mirror
-    double *d_z = nullptr, *d_zf = nullptr, *d_zn = nullptr;
-    int64_t *d_idf = nullptr;
-    int *d_counts = nullptr;
+    double *d_z = nullptr, *d_zn = nullptr;
+    char *d_assoc = nullptr;    // associate's result, packed per call: counts[4] | zf 2 x nz | zn 2 x nz | idf nz (one D2H)
+    char *d_upd = nullptr;      // update's host inputs, packed per call: zf 2 x m | idf m (one H2D)
     double *d_small = nullptr;  // 16 doubles of misc outputs
     void *h_pin = nullptr;      // pinned host staging
     size_t h_pin_bytes = 0;
@@ -149,10 +149,9 @@ extern "C" int slam_create(int device, int n_max, slam_t **out) {
     CREATE_TRY(cudaMalloc(&h->d_err, sizeof(int)));
     const size_t no = SLAM_MAX_OBS;
     CREATE_TRY(cudaMalloc(&h->d_z, sizeof(double) * 2 * no));
-    CREATE_TRY(cudaMalloc(&h->d_zf, sizeof(double) * 2 * no));
     CREATE_TRY(cudaMalloc(&h->d_zn, sizeof(double) * 2 * no));
-    CREATE_TRY(cudaMalloc(&h->d_idf, sizeof(int64_t) * no));
-    CREATE_TRY(cudaMalloc(&h->d_counts, sizeof(int) * 4));
+    CREATE_TRY(cudaMalloc(&h->d_assoc, 16 + 40 * no));
+    CREATE_TRY(cudaMalloc(&h->d_upd, 24 * no));
     CREATE_TRY(cudaMalloc(&h->d_small, sizeof(double) * 16));
     h->h_pin_bytes = sizeof(double) * 8 * no + 256;
     CREATE_TRY(cudaMallocHost(&h->h_pin, h->h_pin_bytes));
@@ -176,8 +175,8 @@ extern "C" int slam_destroy(slam_t *h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     cudaFree(h->d_x); cudaFree(h->d_P); cudaFree(h->d_pose); cudaFree(h->d_err);
-    cudaFree(h->d_z); cudaFree(h->d_zf); cudaFree(h->d_zn); cudaFree(h->d_idf);
-    cudaFree(h->d_counts); cudaFree(h->d_small); cudaFree(h->d_gate_scratch); cudaFree(h->d_sig2);
+    cudaFree(h->d_z); cudaFree(h->d_zn); cudaFree(h->d_assoc); cudaFree(h->d_upd);
+    cudaFree(h->d_small); cudaFree(h->d_gate_scratch); cudaFree(h->d_sig2);
     cudaFree(h->d_PHt); cudaFree(h->d_W1c); cudaFree(h->d_S); cudaFree(h->d_C);
     cudaFree(h->d_u); cudaFree(h->d_v); cudaFree(h->d_Hn); cudaFree(h->d_fp);
     cudaFree(h->d_block);
@@ -415,24 +414,25 @@ extern "C" int slam_associate(slam_t *h, const double *z, int nz, const double R
         slam_set_error("slam_associate: nz = %d exceeds SLAM_MAX_OBS = %d", nz, SLAM_MAX_OBS);
         return SLAM_ERR_CAPACITY;
     }
-    double *hz = (double *)((char *)h->h_pin + 256);
+    // pinned staging: [0, 16 + 40 nz) the packed result, the observations behind it
+    const size_t out_bytes = 16 + 40 * (size_t)nz;
+    double *hz = (double *)((char *)h->h_pin + 16 + 40 * (size_t)SLAM_MAX_OBS + 240);
     memcpy(hz, z, sizeof(double) * 2 * nz);
     CUDA_TRY(cudaMemcpyAsync(h->d_z, hz, sizeof(double) * 2 * nz, cudaMemcpyHostToDevice, h->stream));
     int Nf = (h->n - 3) / 2;
+    int *d_counts = (int *)h->d_assoc;
+    double *d_zf = (double *)(h->d_assoc + 16), *d_zn = d_zf + 2 * nz;
+    int64_t *d_idf = (int64_t *)(d_zn + 2 * nz);
     int rc = launch_gate(h->d_x, h->d_P, h->ld, Nf, h->d_z, nz, R, gate1, gate2, h->d_gate_scratch,
-                         h->gate_scratch, h->d_zf, h->d_idf, h->d_zn, h->d_counts,
+                         h->gate_scratch, d_zf, d_idf, d_zn, d_counts,
                          h->pregate ? h->d_sig2 : nullptr, h->d_sig2 + 1, h->stream, &h->launches);
     if (rc) return rc;
-    // results: counts, zf, idf, zn -> pinned staging
-    int *hc = (int *)h->h_pin;
-    double *hzf = hz + 2 * SLAM_MAX_OBS;
-    double *hzn = hzf + 2 * SLAM_MAX_OBS;
-    int64_t *hid = (int64_t *)(hzn + 2 * SLAM_MAX_OBS);
-    CUDA_TRY(cudaMemcpyAsync(hc, h->d_counts, sizeof(int) * 2, cudaMemcpyDeviceToHost, h->stream));
-    CUDA_TRY(cudaMemcpyAsync(hzf, h->d_zf, sizeof(double) * 2 * nz, cudaMemcpyDeviceToHost, h->stream));
-    CUDA_TRY(cudaMemcpyAsync(hzn, h->d_zn, sizeof(double) * 2 * nz, cudaMemcpyDeviceToHost, h->stream));
-    CUDA_TRY(cudaMemcpyAsync(hid, h->d_idf, sizeof(int64_t) * nz, cudaMemcpyDeviceToHost, h->stream));
+    // counts, zf, zn, idf come back in one copy
+    CUDA_TRY(cudaMemcpyAsync(h->h_pin, h->d_assoc, out_bytes, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    const int *hc = (const int *)h->h_pin;
+    const double *hzf = (const double *)((char *)h->h_pin + 16), *hzn = hzf + 2 * nz;
+    const int64_t *hid = (const int64_t *)(hzn + 2 * nz);
     *m = hc[0];
     *k = hc[1];
     memcpy(zf, hzf, sizeof(double) * 2 * (*m));
@@ -1015,13 +1015,12 @@ extern "C" int slam_update(slam_t *h, const double *zf, int m, const double R[4]
         return SLAM_ERR_CAPACITY;
     }
     double *hz = (double *)((char *)h->h_pin + 256);
-    int64_t *hid = (int64_t *)(hz + 6 * SLAM_MAX_OBS);
+    int64_t *hid = (int64_t *)(hz + 2 * m);       // packed behind zf: one H2D
     CUDA_TRY(cudaStreamSynchronize(h->stream));
     memcpy(hz, zf, sizeof(double) * 2 * m);
     memcpy(hid, idf, sizeof(int64_t) * m);
-    CUDA_TRY(cudaMemcpyAsync(h->d_zf, hz, sizeof(double) * 2 * m, cudaMemcpyHostToDevice, h->stream));
-    CUDA_TRY(cudaMemcpyAsync(h->d_idf, hid, sizeof(int64_t) * m, cudaMemcpyHostToDevice, h->stream));
-    int rc = update_device(h, h->d_zf, m, R, h->d_idf);
+    CUDA_TRY(cudaMemcpyAsync(h->d_upd, hz, 24 * (size_t)m, cudaMemcpyHostToDevice, h->stream));
+    int rc = update_device(h, (const double *)h->d_upd, m, R, (const int64_t *)(h->d_upd + 16 * (size_t)m));
     if (rc) return rc;
     return check_latched(h);
 }

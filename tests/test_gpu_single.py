@@ -415,6 +415,7 @@ def _assoc_both(h, z, R, g1, g2):
     (3000, 9, 900.0, (1e6, 1e7)),          # huge gates: radius beyond the field, nothing may be skipped wrongly
     (3000, 9, 900.0, (-1.0, -2.0)),        # no positive gate: pre-gate switches itself off
     (2000, 16, 700.0, (4.0, float("inf"))),
+    (2000, 300, 700.0, (4.0, 25.0)),       # 38 passes; the compaction walks two chunks of 256 observations
 ])
 def test_pregate_identical_to_exhaustive(sc, twin, nf, nz, side, gates):
     """SURVEY 8 f4 (the reference's TODO at src/data-association.jl:18-20): the annulus pre-gate may only
