@@ -566,18 +566,35 @@ struct ShardPeers {
     unsigned long long *flags[SH_MAXW];
 };
 
-// step 2': the owner of row cs[s] stores P[cs[s], j], j >= cs[s], into rowbuf[s] of every rank
-// (entries j < cs[s] are never read: P[i, c] with c >= i comes from the reader's own block)
+// step 2': the owner of row cs[s] stores P[cs[s], j], j >= cs[s], into rowbuf[s] of the ranks that read it
+// (entries j < cs[s] are never read: P[i, c] with c >= i comes from the reader's own block).  Entry j has two
+// kinds of reader: the owner of row j (k_sh_pht forms PHt for its own rows only) and, when j is itself one of
+// the S rows named by H, every rank (k_sh_pht_hset forms the S x 2m block redundantly).  So the x-blocks over
+// j store to ONE rank each, and gridDim.x - hx extra x-blocks broadcast the S entries of the H set: n + 8 S
+// remote stores per row instead of 8 n.
 __global__ void __launch_bounds__(256)
-k_sh_extract_p2p(ShardGeom g, const int *__restrict__ cs, ShardPeers pr) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+k_sh_extract_p2p(ShardGeom g, const int *__restrict__ cs, int S, int hx, ShardPeers pr) {
     const int s = blockIdx.y;
     const int c = cs[s];
     int owner, q, li;
     row_owner(g, c, &owner, &q, &li);
-    if (owner != g.rank || j < c || j >= g.npad) return;
-    const double val = j < g.n ? g.Pb[q][(size_t)(c - g.lo[q]) + (size_t)j * g.ldb] : 0.0;
-    for (int r = 0; r < g.world; r++) pr.rowbuf[r][(size_t)s * g.npad + j] = val;
+    if (owner != g.rank) return;
+    const double *row = g.Pb[q] + (size_t)(c - g.lo[q]);
+    if ((int)blockIdx.x < hx) {
+        const int j = blockIdx.x * blockDim.x + threadIdx.x;
+        if (j < c || j >= g.npad) return;
+        const double val = j < g.n ? row[(size_t)j * g.ldb] : 0.0;
+        int oj, qj, lj;
+        row_owner(g, j, &oj, &qj, &lj);
+        pr.rowbuf[oj][(size_t)s * g.npad + j] = val;
+    } else {
+        const int t = (blockIdx.x - hx) * blockDim.x + threadIdx.x;
+        if (t >= S) return;
+        const int j = cs[t];
+        if (j < c) return;
+        const double val = row[(size_t)j * g.ldb];
+        for (int r = 0; r < g.world; r++) pr.rowbuf[r][(size_t)s * g.npad + j] = val;
+    }
 }
 
 // Barrier over peer memory: rank `rank` publishes `epoch` in flags[rank] of every rank, then waits
@@ -769,7 +786,8 @@ static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const
             k_sh_zero_tail<<<(npad_used - s->n + 127) / 128, 128, 0, st>>>(s->n, npad_used, npad, RC, nch, s->d_W1c);
             s->launches++;
         }
-        k_sh_extract_p2p<<<dim3((npad + 255) / 256, S), 256, 0, st>>>(g, s->d_cs, pr);
+        const int hx = (npad + 255) / 256;
+        k_sh_extract_p2p<<<dim3(hx + (S + 255) / 256, S), 256, 0, st>>>(g, s->d_cs, S, hx, pr);
         k_sh_barrier<<<1, 32, 0, st>>>(pr, s->rank, s->world, ++s->epoch, s->d_err);
         s->launches += 3;
     } else {
