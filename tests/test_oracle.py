@@ -227,3 +227,56 @@ def test_oracle_against_textbook_identities():
         nis, nd = ref.compute_association(x, P, zq, R, j)
         assert abs(nis - vv @ np.linalg.solve(S, vv)) < 1e-9 * max(1.0, nis)
         assert abs(nd - (nis + math.log(np.linalg.det(S)))) < 1e-9 * max(1.0, abs(nd))
+
+
+def test_pregate_bound_against_the_literal_oracle(course1):
+    """The inequality chain behind the CUDA spatial pre-gate (slam.jl_b200/csrc/gate.cu), checked
+    against the literal restatement of compute_association (src/data-association.jl:53-63) with no GPU involved:
+        nis >= v_r^2 / S_rr,   S_rr <= 2 (P_xx + P_yy) + 4 sig2max + R_rr,
+    so a pair with (z_r - d)^2 > 4 G S_rr_max (G = max(gate1, gate2)) has nis > G with a factor 4 to spare and can
+    change neither `nis < gate1` (:30) nor `outer > gate2` (:46).  Random dense states and every observation step
+    of a course1 run (the states an EKF actually produces)."""
+    k = ref.sim_constants()
+    R, g1, g2 = k["R"], k["gate1"], k["gate2"]
+    G = max(g1, g2)
+
+    def check(x, P, z):
+        nf = (len(x) - 3) // 2
+        if nf == 0 or z.shape[1] == 0:
+            return 0, 0
+        sig2 = max(0.0, float(np.max(np.diag(P)[3:])))
+        srr_max = 2.0 * (abs(P[0, 0]) + abs(P[1, 1])) + 4.0 * sig2 + abs(R[0, 0])
+        skipped = total = 0
+        for i in range(z.shape[1]):
+            for j in range(1, nf + 1):
+                zp, H = ref.predict_observation(x, j)
+                S = H @ P @ H.T + R
+                nis, _ = ref.compute_association(x, P, z[:, i], R, j)
+                vr = z[0, i] - zp[0]
+                assert S[0, 0] <= srr_max * (1 + 1e-12)
+                assert nis >= vr * vr / S[0, 0] * (1 - 1e-9)
+                total += 1
+                if vr * vr > 4.0 * G * srr_max:          # what k_gate skips
+                    skipped += 1
+                    assert nis > 3.9 * G                 # far above both gates
+        return skipped, total
+
+    rng = np.random.default_rng(5)
+    sk = tot = 0
+    for nf, side in ((40, 60.0), (120, 400.0)):
+        n = 3 + 2 * nf
+        x = np.concatenate([[side / 2, side / 2, 0.3], rng.uniform(0, side, size=2 * nf)])
+        L = rng.normal(0, 0.05, size=(n, 8))
+        P = L @ L.T + np.diag(rng.uniform(0.01, 0.1, size=n))
+        z = np.array([rng.uniform(1, side / 2, 10), rng.uniform(-3, 3, 10)])
+        a, b = check(x, P, z)
+        sk, tot = sk + a, tot + b
+    lm, ctrl, obs = ref.make_inputs(35, 0, 1)
+    rec = []
+    ref.sim(course1, lm, ctrl, obs, nlaps=1, record=rec)
+    steps = [r for r in rec if r["op"] == "observe"]
+    for r in steps[::6]:
+        a, b = check(r["x"], r["P"], r["z"])
+        sk, tot = sk + a, tot + b
+    print(f"\n[pre-gate bound] {sk} of {tot} pairs skipped")
+    assert tot > 3000 and sk > tot // 4      # the bound is not vacuous: it discards a large share of the pairs
