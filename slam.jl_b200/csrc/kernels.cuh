@@ -20,11 +20,8 @@ int launch_downdate_dmma_rows(double *Pb, size_t ldb, int r0, int r1, int n, con
                               cudaStream_t s, long long *launches);
 
 // ---- K2 (gate.cu, compiled with -fmad=false) ---------------------------------------------
-struct GateOut {           // device-side result of one associate() call
-    int m, k;              // counts
-};
-// z: device 2 x nz. Results: d_zf (2 x nz), d_idf (nz), d_zn (2 x nz), d_counts[2] = {m, k}.
-// Works on rows [lo, hi) landmarks; P addressed through (Pbase, ld) with upper-triangle mirror.
+// z: device 2 x nz. Results: d_zf (2 x nz), d_idf (nz), d_zn (2 x nz), d_counts[2] = {m, k}; P is the full
+// column-major matrix with the upper triangle authoritative.
 int launch_gate(const double *d_x, const double *d_P, size_t ld, int Nf, const double *d_z, int nz,
                 const double R[4], double gate1, double gate2, void *d_scratch, size_t scratch_bytes,
                 double *d_zf, int64_t *d_idf, double *d_zn, int *d_counts,
