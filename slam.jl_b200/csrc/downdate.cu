@@ -76,7 +76,14 @@ __device__ __forceinline__ void fma_store_batch(double (&a)[U][ROWS], const doub
     for (int u = 0; u < U; u++) st_rows<ROWS>(a[u], col + (size_t)u * ld);
 }
 
-constexpr int DD_BJ = 128;    // columns per tile (W1 column-side rows staged in shared memory)
+// columns per tile (W1 column-side rows staged in shared memory): the row-side W1 values a thread keeps in
+// registers are fetched once per tile, so a wider tile amortises them further; bounded by 48 KB of static
+// shared memory (BJ * RC * 8 bytes)
+#ifndef DD_BJ_WIDE
+#define DD_BJ_WIDE 128
+#endif
+template <int RC>
+struct DdBj { static constexpr int value = RC <= 16 ? DD_BJ_WIDE : 128; };
 
 // One warp-wide L2 prefetch covers a whole batch: lane l asks for 128-byte line (l % LINES) of
 // column (l / LINES) of the batch, LINES = lines of this warp's row segment per column.
@@ -105,6 +112,7 @@ k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n
                const double *__restrict__ W1r, const double *__restrict__ W1t) {
     constexpr int BI = DD_THREADS * ROWS;
     const int i0 = r0 + blockIdx.x * BI;
+    constexpr int DD_BJ = DdBj<RC>::value;
     const int j0 = blockIdx.y * DD_BJ;
     const int jend = min(j0 + DD_BJ, n);
     if (i0 >= jend) return;  // tile entirely below the diagonal
@@ -223,6 +231,7 @@ template <int RC, int ROWS, int U, int PD, int PIPE>
 void launch_one(double *Pb, size_t ldb, int r0, int r1, int n, int n_pad, const double *W1r,
                 const double *W1t, cudaStream_t s) {
     constexpr int BI = DD_THREADS * ROWS;
+    constexpr int DD_BJ = DdBj<RC>::value;
     dim3 grid((r1 - r0 + BI - 1) / BI, (n + DD_BJ - 1) / DD_BJ);
     k_downdate_fma<RC, ROWS, U, PD, PIPE><<<grid, DD_THREADS, 0, s>>>(Pb, ldb, r0, r1, n, n_pad, W1r, W1t);
 }
