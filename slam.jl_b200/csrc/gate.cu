@@ -558,8 +558,8 @@ int launch_compute_association(const double *d_x, const double *d_P, size_t ld, 
 // Sharded gating, phase 1: this rank's landmarks -> d_rank_res[nz] (GateRes, 24 bytes each).
 int launch_gate_shard(const double *d_x, const double *d_P3, int npad, const double *const d_Pb[2], size_t ldb,
                       const int lo[2], const int hi[2], const double *d_z, int nz, const double R[4], double gate1,
-                      double gate2, void *d_scratch, size_t scratch_bytes, void *d_rank_res, cudaStream_t s,
-                      long long *launches) {
+                      double gate2, void *d_scratch, size_t scratch_bytes, void *d_rank_res,
+                      const unsigned long long *d_sig2bits, cudaStream_t s, long long *launches) {
     if (scratch_bytes < gate_scratch_bytes(nz)) {
         slam_set_error("launch_gate_shard: scratch too small");
         return SLAM_ERR_ARG;
@@ -568,7 +568,7 @@ int launch_gate_shard(const double *d_x, const double *d_P3, int npad, const dou
     memcpy(prm.R, R, sizeof(prm.R));
     prm.gate1 = gate1;
     prm.gate2 = gate2;
-    prm.sig2bits = nullptr;   // sharded scan stays exhaustive
+    prm.sig2bits = d_sig2bits;   // rank-local bound over the landmarks this rank scans (shard.cu); nullptr = exhaustive
     prm.stats = nullptr;
     GateSrc src = {};
     src.P3 = d_P3;

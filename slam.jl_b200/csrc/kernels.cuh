@@ -51,7 +51,7 @@ int launch_innov_chol(const double *PHt, int npad, const double *Hn, const int *
 constexpr int GATE_RES_BYTES = 24;
 int launch_gate_shard(const double *d_x, const double *d_P3, int npad, const double *const d_Pb[2], size_t ldb,
                       const int lo[2], const int hi[2], const double *d_z, int nz, const double R[4], double gate1,
-                      double gate2, void *d_scratch, size_t scratch_bytes, void *d_rank_res, cudaStream_t s,
-                      long long *launches);
+                      double gate2, void *d_scratch, size_t scratch_bytes, void *d_rank_res,
+                      const unsigned long long *d_sig2bits, cudaStream_t s, long long *launches);
 int launch_gate_finalize(const void *d_all_res, int world, const double *d_z, int nz, double gate2, double *d_zf,
                          int64_t *d_idf, double *d_zn, int *d_counts, cudaStream_t s, long long *launches);

@@ -156,6 +156,10 @@ struct slam_shard {
     void *h_pin = nullptr;
     double *d_zf = nullptr, *d_z = nullptr, *d_zn = nullptr;
     int64_t *d_idf = nullptr;
+    // spatial pre-gate of associate (gate.cu): bit pattern of an upper bound of the diagonal entries of the
+    // landmarks THIS rank scans (those whose 2x2 diagonal block it owns) -- rank-local, no collective
+    unsigned long long *d_sig2 = nullptr;
+    bool pregate = true;
     // update workspace
     int ws_R = 0, npad = 0;
     double *d_rowbuf = nullptr, *d_PHtloc = nullptr, *d_PHtH = nullptr, *d_S = nullptr, *d_C = nullptr,
@@ -244,7 +248,7 @@ extern "C" int slam_shard_destroy(slam_shard_t *s) {
     cudaFree(s->d_PHtloc); cudaFree(s->d_PHtH); cudaFree(s->d_S); cudaFree(s->d_C);
     cudaFree(s->d_u); cudaFree(s->d_v); cudaFree(s->d_Hn); cudaFree(s->d_W1send); cudaFree(s->d_W1gath);
     cudaFree(s->d_fp); cudaFree(s->d_fpH); cudaFree(s->d_cs);
-    cudaFree(s->d_P3); cudaFree(s->d_gate);
+    cudaFree(s->d_P3); cudaFree(s->d_gate); cudaFree(s->d_sig2);
     if (s->h_pin) cudaFreeHost(s->h_pin);
     for (auto &e : s->ev) cudaEventDestroy(e);
     if (s->stream) cudaStreamDestroy(s->stream);
@@ -285,6 +289,9 @@ extern "C" int slam_shard_create(int device, int rank, int world, const char id[
     for (int q = 0; q < 2; q++) SH_TRY(cudaMalloc(&s->d_Pb[q], sizeof(double) * s->ldb * (size_t)n_max));
     SH_TRY(cudaMalloc(&s->d_err, sizeof(int)));
     SH_TRY(cudaMemsetAsync(s->d_err, 0, sizeof(int), s->stream));
+    SH_TRY(cudaMalloc(&s->d_sig2, sizeof(unsigned long long) * 4));
+    SH_TRY(cudaMemsetAsync(s->d_sig2, 0, sizeof(unsigned long long) * 4, s->stream));
+    if (const char *e = getenv("SLAM_SHARD_PREGATE")) s->pregate = atoi(e) != 0;
     SH_TRY(cudaMemsetAsync(s->d_x, 0, sizeof(double) * (size_t)s->npad, s->stream));
     const size_t no = SLAM_MAX_OBS;
     SH_TRY(cudaMalloc(&s->d_z, sizeof(double) * 2 * no));
@@ -353,6 +360,26 @@ extern "C" int slam_shard_sync(slam_shard_t *s) {
     return shard_check_latched(s);
 }
 
+// max over P[f, f], f in [f0, hi), of a row block (element (i, j) at Pb[(i - lo) + j*ldb]) as the bit pattern of a
+// non-negative double (same convention as k_sig2_diag in gate.cu: NaN -> a pattern above +inf, negatives ignored)
+__global__ void k_sh_sig2_diag(const double *__restrict__ Pb, size_t ldb, int lo, int f0, int hi,
+                               unsigned long long *sig2bits) {
+    unsigned long long mine = 0ull;
+    for (int f = f0 + blockIdx.x * blockDim.x + threadIdx.x; f < hi; f += gridDim.x * blockDim.x) {
+        const double v = Pb[(size_t)(f - lo) + (size_t)f * ldb];
+        unsigned long long b = (unsigned long long)__double_as_longlong(v);
+        if (v != v) b = 0x7ff8000000000000ull;
+        else if (v < 0.0) b = 0ull;
+        mine = b > mine ? b : mine;
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        const unsigned long long o = __shfl_down_sync(0xffffffffu, mine, off);
+        mine = o > mine ? o : mine;
+    }
+    if ((threadIdx.x & 31) == 0 && mine) atomicMax(sig2bits, mine);
+}
+
 extern "C" int slam_shard_synth_state(slam_shard_t *s, int n_landmarks, double side, uint64_t seed) {
     S_CHECK(s);
     ARG_CHECK(n_landmarks >= 0 && side > 0, "bad argument");
@@ -364,11 +391,19 @@ extern "C" int slam_shard_synth_state(slam_shard_t *s, int n_landmarks, double s
     s->n = n;
     // block boundaries follow the capacity's block height so that growth never moves rows
     plan_blocks(n, s->hb, s->world, s->rank, s->lo, s->hi);
+    CUDA_TRY(cudaMemsetAsync(s->d_sig2, 0, sizeof(unsigned long long), s->stream));
     for (int q = 0; q < 2; q++) {
         int rc = synth_fill(s->d_x, s->d_Pb[q], s->ldb, s->lo[q], s->hi[q], n_landmarks, side, seed, s->stream,
                             &s->launches);
         if (rc) return rc;
+        const int f0 = std::max(s->lo[q], 3);
+        if (s->hi[q] > f0) {   // the pre-gate's bound: exact maximum over the diagonal entries this rank owns
+            k_sh_sig2_diag<<<std::min((s->hi[q] - f0 + 255) / 256, 296), 256, 0, s->stream>>>(
+                s->d_Pb[q], s->ldb, s->lo[q], f0, s->hi[q], s->d_sig2);
+            s->launches++;
+        }
     }
+    CUDA_TRY(cudaGetLastError());
     return SLAM_OK;
 }
 
@@ -1009,7 +1044,8 @@ extern "C" int slam_shard_associate(slam_shard_t *s, const double *z, int nz, co
     }
     if (s->world > 1) NCCL_TRY(g_nccl.Broadcast(s->d_P3, s->d_P3, (size_t)3 * s->npad, ncclFloat64, 0, s->comm, st));
     int rc = launch_gate_shard(s->d_x, s->d_P3, s->npad, s->d_Pb, s->ldb, s->lo, s->hi, s->d_z, nz, R, gate1, gate2,
-                               s->d_gate, gate_scratch_bytes(SLAM_MAX_OBS), res_mine, st, &s->launches);
+                               s->d_gate, gate_scratch_bytes(SLAM_MAX_OBS), res_mine,
+                               s->pregate ? s->d_sig2 : nullptr, st, &s->launches);
     if (rc) return rc;
     const void *all = res_mine;
     if (s->world > 1) {
@@ -1048,7 +1084,8 @@ constexpr int SHA_THREADS = 256;
 
 __global__ void __launch_bounds__(SHA_THREADS)
 k_sh_augment(double *x, const double *__restrict__ P3, int npad, double *Pb, size_t ldb, int lo, int hi_new, int n0,
-             const double *__restrict__ zn, int kq, double R0, double R1, double R2, double R3, int write_x) {
+             const double *__restrict__ zn, int kq, double R0, double R1, double R2, double R3, int write_x,
+             unsigned long long *sig2bits) {
     __shared__ double sGv[SHA_Q][2];
     __shared__ double sGP[SHA_Q][2][3];
     __shared__ double sPvv[9];
@@ -1085,7 +1122,13 @@ k_sh_augment(double *x, const double *__restrict__ P3, int npad, double *Pb, siz
                 for (int bb = a; bb < 2; bb++) {
                     const double t1 = sGP[q][a][0] * Gv[bb][0] + sGP[q][a][1] * Gv[bb][1] + sGP[q][a][2] * Gv[bb][2];
                     const double t2 = GR[a][0] * Gz[bb][0] + GR[a][1] * Gz[bb][1];
-                    Pb[(size_t)(len + a - lo) + (size_t)(len + bb) * ldb] = t1 + t2;
+                    const double pv = t1 + t2;
+                    Pb[(size_t)(len + a - lo) + (size_t)(len + bb) * ldb] = pv;
+                    if (a == bb) {   // keep this rank's pre-gate bound valid for the landmark it now owns
+                        unsigned long long bits = (unsigned long long)__double_as_longlong(pv);
+                        if (pv != pv) bits = 0x7ff8000000000000ull;
+                        if (!(pv < 0.0)) atomicMax(sig2bits, bits);
+                    }
                 }
         }
     }
@@ -1139,7 +1182,8 @@ extern "C" int slam_shard_add_features(slam_shard_t *s, const double *zn, int k,
             const int rows = std::max(hi[b] - lo[b], 0);
             dim3 grid(std::max(1, (rows + SHA_THREADS - 1) / SHA_THREADS), kq);
             k_sh_augment<<<grid, SHA_THREADS, 0, st>>>(s->d_x, s->d_P3, s->npad, s->d_Pb[b], s->ldb, lo[b], hi[b], n0,
-                                                       s->d_zn + 2 * q0, kq, R[0], R[1], R[2], R[3], b == 0);
+                                                       s->d_zn + 2 * q0, kq, R[0], R[1], R[2], R[3], b == 0,
+                                                       s->d_sig2);
             s->launches++;
         }
         s->n = n1;

@@ -60,6 +60,14 @@ idw = np.array([1 + (7 * c) % nl for c in range(40)], dtype=np.int64)
 zw = np.stack([h.predict_observation(int(i))[0] for i in idw], axis=1) + 0.02
 h.update(zw, R, idw)
 sf.update(zw, R, idw)
+# association again on the grown, updated map: the rank-local bound of the spatial pre-gate has followed
+# add_features on whichever rank owns the new landmarks
+idq = np.array([nl + 1, nl + 3, nl + kk, 2, 5], dtype=np.int64)
+zq2 = np.stack([h.predict_observation(int(i))[0] for i in idq], axis=1) + 0.005
+zq2 = np.concatenate([zq2, np.array([[3 * side, 0.3], [2.5 * side, -1.0]]).T], axis=1)
+a2 = h.associate(zq2, R, 4.0, 25.0)
+b2 = sf.associate(zq2, R, 4.0, 25.0)
+ok = ok and all(np.array_equal(p, q) for p, q in zip(a2, b2)) and len(a2[1]) >= 3 and a2[2].shape[1] == 2
 n = sf.n
 x1, P1 = h.get_state()
 ex = float(np.max(np.abs(sf.get_x() - x1)) / np.max(np.abs(x1)))
