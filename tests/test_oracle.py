@@ -280,3 +280,45 @@ def test_pregate_bound_against_the_literal_oracle(course1):
         sk, tot = sk + a, tot + b
     print(f"\n[pre-gate bound] {sk} of {tot} pairs skipped")
     assert tot > 3000 and sk > tot // 4      # the bound is not vacuous: it discards a large share of the pairs
+
+
+def test_pregate_bound_fuzz_against_the_twin(twin):
+    """The same implication -- outside the annulus => nis > max(gate1, gate2) -- fuzzed over 300 random
+    positive definite states with the plain-C twin's compute_association: strong vehicle / landmark
+    correlations, heading variances up to 1 rad^2, observation covariances from 1e-8 to 1, gates from 0.1
+    to 1e3, landmarks from 0.1 m to 2 km away."""
+    from twin_ffi import Twin
+    tw = Twin(twin)
+    rng = np.random.default_rng(123)
+    pairs = skipped = 0
+    worst = np.inf
+    for trial in range(300):
+        nf = int(rng.integers(1, 40))
+        n = 3 + 2 * nf
+        side = 10.0 ** rng.uniform(0, 3.3)
+        x = np.concatenate([[0.0, 0.0, rng.uniform(-3, 3)], rng.uniform(-side, side, size=2 * nf)])
+        rank = int(rng.integers(1, n + 1))
+        A = rng.normal(0, 10.0 ** rng.uniform(-3, 0), size=(n, rank))
+        A[2, :] *= 10.0 ** rng.uniform(-1, 1)                       # heading
+        P = A @ A.T + np.diag(10.0 ** rng.uniform(-8, -1, size=n))
+        R = np.diag(10.0 ** rng.uniform(-8, 0, size=2))
+        if rng.random() < 0.3:
+            c = rng.uniform(-0.9, 0.9) * math.sqrt(R[0, 0] * R[1, 1])
+            R[0, 1] = R[1, 0] = c
+        g1, g2 = 10.0 ** rng.uniform(-1, 3, size=2)
+        G = max(g1, g2)
+        sig2 = float(np.max(np.diag(P)[3:]))
+        srr_max = 2.0 * (P[0, 0] + P[1, 1]) + 4.0 * sig2 + R[0, 0]
+        rho2 = 4.0 * G * srr_max
+        for _ in range(6):
+            z = np.array([rng.uniform(0, 2 * side), rng.uniform(-3.2, 3.2)])
+            for j in range(1, nf + 1):
+                d = math.hypot(x[3 + 2 * (j - 1)] - x[0], x[4 + 2 * (j - 1)] - x[1])
+                pairs += 1
+                if (z[0] - d) ** 2 > rho2:
+                    skipped += 1
+                    nis, _ = tw.compute_association(x, P, z, R, j)
+                    assert nis > G, (trial, j, nis, G)
+                    worst = min(worst, nis / G)
+    print(f"\n[pre-gate fuzz] {skipped} of {pairs} pairs outside the annulus; smallest nis / G among them {worst:.2f}")
+    assert skipped > pairs // 10 and worst > 3.9
