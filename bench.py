@@ -5,13 +5,17 @@ A "step" is one `update` call (src/ekf.jl:46-77: K3 P*H' gather, K4 innovation C
 K5 gain, K6 in-place symmetric downdate) with m associated observations on a synthetic
 landmark field.  Workload, per GPU count N (see DESIGN.md "Measurement"):
   N = 1 : the 100k-landmark config's per-GPU slice: P of 40 GB on one GPU
-          (n = 70711, 35354 landmarks); `update_10k` (BASELINE config 3) is reported beside it.
+          (n = 70709, 35353 landmarks); `update_10k` (BASELINE config 3) is reported beside it.
   N > 1 : one filter whose P is row-block-sharded over N ranks, 40 GB per rank (N = 8 is the
-          100k-landmark config, P = 320 GB), NCCL allgather of the H rows and of W1.
+          100k-landmark config itself, n = 200003, P = 320 GB); H rows and W1 exchanged through peer memory
+          (NCCL collectives as the fallback).
 `value`    : update steps/s with zf / idf already in HBM, no host sync between steps.
 `e2e`      : the same through the host C ABI call slam_update() with HOST buffers (H2D of
              zf / idf inside, status + pose read back every step).
 `roofline` : K6, algorithmic bytes 8 n (n+1) / ranks over CUDA-event time of the K6 launches.
+`parity`   : BEFORE anything is timed, one update on the very state the timed loop starts from is checked against
+             the CPU oracle (oracle/slam_ref.py, used here as the checker only) on a sampled sub-state; at N > 1
+             for both exchange paths.  The run fails (exit code 3) above 1e-9.
 `--impl reference` times the CPU restatement of the reference (oracle/slam_ref.py, numpy +
 OpenBLAS on all host cores) on a bounded sample; Julia is not available on this box.
 """
@@ -38,6 +42,7 @@ DENSITY = 0.0035            # landmarks per m^2 (course1 with 35 landmarks)
 SEED = 2
 R_OBS = np.array([0.1 ** 2, 0.0, 0.0, (math.pi / 180) ** 2])   # column-major 2x2
 GB_PER_RANK = 40.0          # P bytes per GPU of the 100k-landmark / 8-GPU config
+PARITY_TOL = 1e-9           # north_star: x and P within 1e-9 relative per step
 
 
 def n_for_bytes(gbytes: float) -> int:
@@ -45,6 +50,14 @@ def n_for_bytes(gbytes: float) -> int:
     n = int(math.sqrt(gbytes * 1e9 / 8.0))
     nf = (n - 3) // 2
     return 3 + 2 * nf
+
+
+def workload_n(n_gpus: int) -> int:
+    """State length of the N-GPU workload: 40 GB of P per GPU; N = 8 is BASELINE config 5 as written (100000
+    landmarks, n = 200003, 40.001 GB per GPU)."""
+    if n_gpus == 8 and GB_PER_RANK == 40.0:
+        return 200003
+    return n_for_bytes(GB_PER_RANK * n_gpus)
 
 
 def peaks():
@@ -109,9 +122,7 @@ class ClockSampler:
 # ----------------------------------------------------------------------------------------
 # CPU arm: the reference-literal numpy restatement (oracle/slam_ref.py), timed, never shipped
 # ----------------------------------------------------------------------------------------
-def cpu_reference_update(n_landmarks: int, m: int, steps: int, warmup: int):
-    """Times oracle.slam_ref.update (dense H, P @ H.T, Cholesky, P - W1 @ W1.T) with numpy's
-    OpenBLAS on all host cores.  Returns (median seconds per step, cores)."""
+def cpu_reference_state(n_landmarks: int, m: int):
     from oracle import slam_ref as ref
     rng = np.random.default_rng(SEED)
     n = 3 + 2 * n_landmarks
@@ -128,6 +139,14 @@ def cpu_reference_update(n_landmarks: int, m: int, steps: int, warmup: int):
     for c, idf in enumerate(ids):
         zp, _ = ref.predict_observation(x, int(idf))
         z[:, c] = zp + rng.normal(0, [0.1, 0.01])
+    return x, P, z, ids
+
+
+def cpu_reference_update(n_landmarks: int, m: int, steps: int, warmup: int):
+    """Times oracle.slam_ref.update (dense H, P @ H.T, Cholesky, P - W1 @ W1.T) with numpy's
+    OpenBLAS on all host cores.  Returns (median seconds per step, cores)."""
+    from oracle import slam_ref as ref
+    x, P, z, ids = cpu_reference_state(n_landmarks, m)
     R = R_OBS.reshape(2, 2)
     times = []
     for it in range(warmup + steps):
@@ -154,11 +173,132 @@ def cpu_baseline_block(n_workload: int, m: int, steps: int = 3, warmup: int = 1,
     }
 
 
+def cpu_associate_baseline(n_landmarks: int = 1000, nz: int = 2):
+    """The reference's literal associate (src/data-association.jl:1-63: a dense 2 x n Jacobian and H*P*H' per
+    (observation, landmark) pair) at n = 2003, and what that costs per pair; above that size only an
+    extrapolation (cost per pair is O(n^2), pairs = nz*Nf) is meaningful -- hours at n = 20003."""
+    from oracle import slam_ref as ref
+    x, P, z, _ids = cpu_reference_state(n_landmarks, nz)
+    R = R_OBS.reshape(2, 2)
+    t0 = time.perf_counter()
+    zf, idf, zn = ref.associate(x, P, z, R, 4.0, 25.0)
+    sec = time.perf_counter() - t0
+    pairs = nz * n_landmarks
+    n = 3 + 2 * n_landmarks
+    return {"what": "oracle/slam_ref.py associate (literal: dense H, H @ P @ H.T per pair), numpy + OpenBLAS",
+            "n": n, "nz": nz, "pairs": pairs, "seconds": sec, "pairs_per_s": pairs / sec,
+            "matched": int(len(np.ravel(idf))), "cores": os.cpu_count() or 1,
+            "extrapolated_s_at_10k_landmarks_nz12": sec / pairs * (20003 / n) ** 2 * 12 * 10000,
+            "extrapolation": "seconds per pair x (n / 2003)^2 x nz x Nf; labelled, not measured"}
+
+
+def cpu_course1_baseline():
+    """BASELINE config 1: one course1 run (35 landmarks, 2 laps) of the literal numpy oracle on the host."""
+    from oracle import slam_ref as ref
+    wp = np.loadtxt(ROOT / "tests" / "golden" / "course1.txt", skiprows=1).T.copy()
+    lm, ctrl, obs = ref.make_inputs(35, 0, 0)
+    t0 = time.perf_counter()
+    out = ref.sim(wp, lm, ctrl, obs)
+    sec = time.perf_counter() - t0
+    return {"what": "oracle/slam_ref.py sim: sim! of sim/ekfslam-sim.jl:54-143 on course1, 35 landmarks, 2 laps, numpy",
+            "filter_steps": out["nsteps"], "observation_steps": out["nupdates"], "n_final": int(len(out["x"])),
+            "seconds": sec, "value": out["nsteps"] / sec, "unit": "filter-steps/s", "cores": os.cpu_count() or 1}
+
+
+# ----------------------------------------------------------------------------------------
+# parity against the oracle on a sampled sub-state (the checker; nothing here is timed)
+# ----------------------------------------------------------------------------------------
+def sample_segments(n: int, idf, window: int = 150):
+    """Index segments of the sampled sub-state: vehicle, the observed landmark pairs, four `window`-row windows.
+    H is zero outside the vehicle and the observed landmarks, so the update restricted to a principal submatrix
+    that contains those columns IS the update of that sub-state."""
+    seen = sorted({int(i) for i in idf})
+    segs = [(0, 3)] + [(3 + 2 * (i - 1), 2) for i in seen]
+    taken = {3 + 2 * (i - 1) for i in seen}
+    for w0 in (3, n // 3, 2 * n // 3, n - window):
+        w0 = w0 if (w0 - 3) % 2 == 0 else w0 + 1
+        while any(w0 - 2 <= t < w0 + window for t in taken):
+            w0 = w0 + 200 if w0 + 400 < n else w0 - 200
+        segs.append((w0, window))
+    index = np.concatenate([np.arange(s, s + ln) for s, ln in segs])
+    return seen, segs, index
+
+
+def parity_errors(x1, xo, P1, Po):
+    """max-norm relative errors and the element-wise one with a floor:
+    |a - b| <= tol * (|b| + sqrt(P_ii P_jj))  for every entry of P,  |a - b| <= tol * (|b| + sqrt(P_ii)) for x."""
+    dg = np.sqrt(np.abs(np.diag(Po)))
+    ex = float(np.max(np.abs(x1 - xo)) / np.max(np.abs(xo)))
+    eP = float(np.max(np.abs(P1 - Po)) / np.max(np.abs(Po)))
+    ex_el = float(np.max(np.abs(x1 - xo) / (np.abs(xo) + dg)))
+    eP_el = float(np.max(np.abs(P1 - Po) / (np.abs(Po) + np.outer(dg, dg))))
+    return ex, eP, ex_el, eP_el
+
+
+def parity_check(n: int, zobs, get_x, gather, associate, update, rank: int = 0):
+    """One observation step on the current state against oracle/slam_ref.py (literal numpy), on the sampled
+    sub-state.  zobs: 2 x nz observations.  Every rank calls it (gather / associate / update may be collective);
+    the comparison runs on rank 0.  Returns the parity dict (rank 0) or None."""
+    zf, idf, zn = associate(zobs)
+    seen, segs, index = sample_segments(n, idf)
+    x0 = get_x()
+    P0 = gather(segs, index)
+    update(zf, idf)
+    x1 = get_x()
+    P1 = gather(segs, index)
+    if rank != 0:
+        return None
+    from oracle import slam_ref as ref   # the checker
+    R = R_OBS.reshape(2, 2)
+    pos = {i: 1 + c for c, i in enumerate(seen)}
+    ids_sub = np.array([pos[int(i)] for i in idf], dtype=np.int64)
+    # association on the sub-state (every landmark the CUDA scan chose is in it; a better candidate outside it
+    # would show as a different id here only if it were inside a window -- the exhaustive/pre-gated equality
+    # and the full-size twin comparisons live in tests/)
+    zf_o, idf_o, zn_o = ref.associate(x0[index], P0, zobs, R, 4.0, 25.0)
+    idf_exact = bool(np.array_equal(np.ravel(idf_o), ids_sub) and np.array_equal(zf_o, zf) and np.array_equal(zn_o, zn))
+    xo, Po = ref.update(x0[index], P0, zf, R, ids_sub)
+    ex, eP, ex_el, eP_el = parity_errors(x1[index], xo, P1, Po)
+    moved = float(np.max(np.abs(P1 - P0)) / np.max(np.abs(P0)))
+    ok = idf_exact and max(ex, eP, ex_el, eP_el) < PARITY_TOL and moved > 1e-6
+    return {"ok": bool(ok), "x_rel": ex, "P_rel": eP, "x_rel_elementwise": ex_el, "P_rel_elementwise": eP_el,
+            "idf_exact": idf_exact, "matched": int(len(idf)), "new": int(zn.shape[1]), "sampled_states": int(len(index)),
+            "P_changed_rel": moved, "tol": PARITY_TOL,
+            "checker": "oracle/slam_ref.py associate + update (literal numpy) on the sub-state {vehicle, observed "
+                       "landmarks, four 150-row windows} of the state the timed loop starts from"}
+
+
+def perturbed(z2, m):
+    """The synthetic observations are noise-free: give the checked update an innovation."""
+    z = z2.copy()
+    z[0, :m] += 0.05
+    z[1, :m] += 0.003
+    return z
+
+
 # ----------------------------------------------------------------------------------------
 # GPU arm, one filter on one GPU
 # ----------------------------------------------------------------------------------------
+def gather_single(h, lib, check, dptr):
+    def gather(segs, index):
+        tot = len(index)
+        out = np.empty((tot, tot))
+        oi = 0
+        for i0, ni in segs:
+            oj = 0
+            for j0, nj in segs:
+                blk = np.empty((ni, nj), order="F")
+                check(lib.slam_get_cov_block(h, i0, ni, j0, nj, dptr(blk), ni))
+                out[oi:oi + ni, oj:oj + nj] = blk
+                oj += nj
+            oi += ni
+        return out
+    return gather
+
+
 def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_steps: int, device: int = 0,
-                      barrier=None, host_mirror_steps: int = 0):
+                      barrier=None, host_mirror_steps: int = 0, parity: bool = False, sustained_s: float = 0.0,
+                      sweep_m=()):
     """Returns timing of `update` on a synthetic n_landmarks map resident on `device`."""
     import torch
     from slamcuda._ffi import lib, check, dptr, iptr
@@ -176,6 +316,30 @@ def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_ste
         zf, zn = np.zeros(2 * nz), np.zeros(2 * nz)
         idf = np.zeros(nz, dtype=np.int64)
         mm, kk = C.c_int(), C.c_int()
+
+        def associate(zobs):
+            zc = np.ascontiguousarray(zobs.T).reshape(-1)
+            nzo = zobs.shape[1]
+            a, b = np.zeros(2 * nzo), np.zeros(2 * nzo)
+            i = np.zeros(nzo, dtype=np.int64)
+            check(lib.slam_associate(h, dptr(zc), nzo, dptr(R_OBS), 4.0, 25.0, dptr(a), iptr(i), C.byref(mm), dptr(b),
+                                     C.byref(kk)))
+            return (a[:2 * mm.value].reshape(-1, 2).T.copy(), i[:mm.value].copy(), b[:2 * kk.value].reshape(-1, 2).T.copy())
+
+        def update(zfc, ids_):
+            zc = np.ascontiguousarray(zfc.T).reshape(-1)
+            ii = np.ascontiguousarray(ids_, dtype=np.int64)
+            check(lib.slam_update(h, dptr(zc), zfc.shape[1], dptr(R_OBS), iptr(ii)))
+
+        def get_x():
+            xx = np.empty(n)
+            check(lib.slam_get_state(h, dptr(xx), None, 0))
+            return xx
+
+        out = {}
+        if parity:
+            out["parity"] = parity_check(n, perturbed(z.reshape(nz, 2).T, m), get_x, gather_single(h, lib, check, dptr),
+                                         associate, update)
         t0 = time.perf_counter()
         check(lib.slam_associate(h, dptr(z), nz, dptr(R_OBS), 4.0, 25.0, dptr(zf), iptr(idf), C.byref(mm),
                                  dptr(zn), C.byref(kk)))
@@ -187,26 +351,35 @@ def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_ste
         d_zf = torch.tensor(zf, device=f"cuda:{device}")
         d_idf = torch.tensor(idf, device=f"cuda:{device}")
         torch.cuda.synchronize(device)
-        for _ in range(warmup):
-            check(lib.slam_update_resident(h, d_zf.data_ptr(), m, dptr(R_OBS), d_idf.data_ptr()))
-        check(lib.slam_sync(h))
-        l0 = lib.slam_launch_count(h)
-        check(lib.slam_profile(h, 1))
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        if barrier:
-            barrier()
-        e0.record(stream)
-        for _ in range(steps):
-            check(lib.slam_update_resident(h, d_zf.data_ptr(), m, dptr(R_OBS), d_idf.data_ptr()))
-        e1.record(stream)
-        check(lib.slam_sync(h))
-        ms_total = e0.elapsed_time(e1)
-        k6, cnt = C.c_double(), C.c_int()
-        check(lib.slam_profile_read(h, C.byref(k6), C.byref(cnt)))
-        check(lib.slam_profile(h, 0))
-        launches = lib.slam_launch_count(h) - l0
-        out = dict(n=n, m=m, ms_per_step=ms_total / steps, k6_ms=k6.value / max(cnt.value, 1),
-                   launches=int(launches), assoc_ms=t_assoc * 1e3, nz=nz, new=kk.value)
+
+        def timed(d_z, d_i, mloc, nsteps, nwarm):
+            for _ in range(nwarm):
+                check(lib.slam_update_resident(h, d_z.data_ptr(), mloc, dptr(R_OBS), d_i.data_ptr()))
+            check(lib.slam_sync(h))
+            l0 = lib.slam_launch_count(h)
+            check(lib.slam_profile(h, 1))
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if barrier:
+                barrier()
+            e0.record(stream)
+            for _ in range(nsteps):
+                check(lib.slam_update_resident(h, d_z.data_ptr(), mloc, dptr(R_OBS), d_i.data_ptr()))
+            e1.record(stream)
+            check(lib.slam_sync(h))
+            ms_total = e0.elapsed_time(e1)
+            k6, cnt = C.c_double(), C.c_int()
+            check(lib.slam_profile_read(h, C.byref(k6), C.byref(cnt)))
+            check(lib.slam_profile(h, 0))
+            return ms_total / nsteps, k6.value / max(cnt.value, 1), int(lib.slam_launch_count(h) - l0)
+
+        ms_step, k6_ms, launches = timed(d_zf, d_idf, m, steps, warmup)
+        out.update(n=n, m=m, ms_per_step=ms_step, k6_ms=k6_ms, launches=launches, assoc_ms=t_assoc * 1e3, nz=nz,
+                   new=kk.value)
+        if sustained_s > 0:
+            # seconds of back-to-back updates: the power-capped figure beside the 20-step burst
+            ns = min(4000, max(steps, int(math.ceil(sustained_s * 1e3 / ms_step))))
+            s_ms, s_k6, _ = timed(d_zf, d_idf, m, ns, 0)
+            out["sustained"] = {"steps": ns, "seconds": s_ms * ns / 1e3, "ms_per_step": s_ms, "k6_ms": s_k6}
         # end to end through the host C ABI: host zf / idf in, status and pose out, every step
         if e2e_steps > 0:
             pose = np.zeros(3)
@@ -241,6 +414,17 @@ def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_ste
             scanned, scored = C.c_longlong(), C.c_longlong()
             check(lib.slam_gate_stats(h, C.byref(scanned), C.byref(scored), None))
             out["gate_scored_frac"] = scored.value / max(scanned.value * ((nz + 7) // 8), 1)
+        # other ranks of the update on the same map (m in {1, 4, 16, 64}): whole step and K6
+        sweep = {}
+        for ms_ in sweep_m:
+            zs = np.zeros(2 * ms_)
+            ids_s = np.zeros(ms_, dtype=np.int64)
+            check(lib.slam_synth_observations(h, n_landmarks, side, SEED, ms_, 0, dptr(zs), iptr(ids_s)))
+            dz, di = torch.tensor(zs, device=f"cuda:{device}"), torch.tensor(ids_s, device=f"cuda:{device}")
+            s_ms, s_k6, _ = timed(dz, di, ms_, max(10, min(steps, 20)), 3)
+            sweep[str(ms_)] = {"ms_per_step": s_ms, "k6_ms": s_k6}
+        if sweep:
+            out["sweep"] = sweep
         # host-mirror mode, the reference's literal calling convention (`state.x, state.cov = update(state, ...)`
         # on host arrays, src/ekf.jl:46-77 returns fresh arrays): x and the WHOLE of P cross PCIe both ways every
         # call.  Reported for transparency; resident mode (above) is what the path is built for.
@@ -265,7 +449,7 @@ def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_ste
 # ensemble side measurement (BASELINE configs 2 and 4): filter-steps/s
 # ----------------------------------------------------------------------------------------
 ENS_LANDMARKS = 35
-ENS_RUNS_PER_GPU = 8192     # 8 GPUs -> the 65536-run config; config 2 (4096 runs) is reported at N = 1 too
+ENS_RUNS_TOTAL = 65536      # BASELINE config 4: 65536 runs sharded by run over 1, 2, 4, 8 GPUs (strong scaling)
 
 
 def course1_inputs():
@@ -274,17 +458,19 @@ def course1_inputs():
     return wp, lm
 
 
-def gpu_ensemble(n_runs: int, rank: int, world: int, device: int, reps: int = 3):
-    """n_runs members on this rank (run ids rank*n_runs ..), whole course per launch."""
+def gpu_ensemble(total_runs: int, rank: int, world: int, device: int, reps: int = 3, fp64_peak=None):
+    """total_runs members split contiguously over the ranks (member_range; no collective), whole course per launch."""
     import torch
     from slamcuda._ffi import lib
-    from slamcuda.ensemble import Ensemble
+    from slamcuda.ensemble import Ensemble, member_range
     wp, lm = course1_inputs()
-    ens = Ensemble(wp, lm, n_runs, seed=SEED, run0=rank * n_runs, device=device)
+    run0, n_runs = member_range(total_runs, world, rank)
+    ens = Ensemble(wp, lm, n_runs, seed=SEED, run0=run0, device=device)
     try:
         stream = torch.cuda.ExternalStream(lib.slam_ens_stream(ens.ptr), device=device)
+        ens.count_flops(True)
         ens.run()
-        bad = ens.sync()
+        ens.sync()
         times = []
         for _ in range(reps):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -294,8 +480,9 @@ def gpu_ensemble(n_runs: int, rank: int, world: int, device: int, reps: int = 3)
             torch.cuda.synchronize(device)
             e0.record(stream)
             ens.run()
+            ens.sync()      # waits; would also run the global-memory rounds of members no shared tier can hold
             e1.record(stream)
-            ens.sync()
+            e1.synchronize()
             times.append(e0.elapsed_time(e1))
         # end to end: launch + wait + final poses / status back on the host
         t0 = time.perf_counter()
@@ -304,32 +491,42 @@ def gpu_ensemble(n_runs: int, rank: int, world: int, device: int, reps: int = 3)
         pose, nf, st = ens.results()
         e2e_ms = (time.perf_counter() - t0) * 1e3
         ms = sorted(times)[len(times) // 2]
-        done, _per = ens.steps_done()          # members that outgrow their capacity count only the steps they ran
-        first_extra, redone = ens.pass_info()   # two-pass capacity: work on re-run members is paid once more, counted once
+        done, _per = ens.steps_done()
+        flops = ens.count_flops(True)
+        tiers = ens.tier_info()
         stopped = int((st != 0).sum())
         if world > 1:
             import torch.distributed as dist
             t = torch.tensor([ms, e2e_ms], device=f"cuda:{device}", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms, e2e_ms = (float(v) for v in t.cpu())
-            c = torch.tensor([done, stopped], device=f"cuda:{device}", dtype=torch.int64)
+            c = torch.tensor([float(done), float(stopped), flops], device=f"cuda:{device}", dtype=torch.float64)
             dist.all_reduce(c, op=dist.ReduceOp.SUM)
-            done, stopped = (int(v) for v in c.cpu())
-        total = n_runs * world
-        return {"workload": f"{total} independent course1 runs ({ENS_LANDMARKS} landmarks, 2 laps, {ens.nsteps} steps, "
-                            f"{ens.nupdates} observation steps each), {n_runs} per GPU, one CTA per filter, "
-                            f"Philox noise keyed by (seed, run), capacity {ens.capacity} states per member",
-                "value": done / (ms * 1e-3), "unit": "filter-steps/s", "ms_per_launch": ms,
-                "e2e": done / (e2e_ms * 1e-3), "runs": total, "steps_per_run": ens.nsteps,
-                "filter_steps_done": done, "member_capacity": ens.capacity,
-                "members_stopped_at_capacity": stopped, "gpu_launches_per_run_batch": 1 if first_extra < 0 else 2,
-                "first_pass_extra_landmarks": None if first_extra < 0 else first_extra, "members_rerun_by_second_pass": redone,
-                "streaming_model_hbm_equiv_gbs": done * 12.4e3 / (ms * 1e-3) / 1e9}
+            done, stopped, flops = int(c[0].item()), int(c[1].item()), float(c[2].item())
+        out = {"workload": f"{total_runs} independent course1 runs ({ENS_LANDMARKS} landmarks, 2 laps, {ens.nsteps} steps, "
+                           f"{ens.nupdates} observation steps each) sharded by run over {world} GPU(s) ({n_runs} on rank "
+                           f"{rank}), one CTA per filter, Philox noise keyed by (seed, run); a member whose map outgrows a "
+                           f"launch's capacity is re-run by the next (growth as in the reference, src/ekf.jl:108-109)",
+               "value": done / (ms * 1e-3), "unit": "filter-steps/s", "ms_per_run_batch": ms, "scaling": "strong",
+               "e2e": done / (e2e_ms * 1e-3), "runs": total_runs, "steps_per_run": ens.nsteps,
+               "filter_steps_done": done, "filter_steps_expected": total_runs * ens.nsteps,
+               "members_stopped_at_capacity": stopped,
+               "launches_rank0": [{"capacity_states": c_, "members": m_} for c_, m_ in tiers],
+               "gpu_launches_per_run_batch": len(tiers),
+               "streaming_model_hbm_equiv_gbs": done * 12.4e3 / (ms * 1e-3) / 1e9}
+        if fp64_peak:
+            tf = flops / (ms * 1e-3) / 1e12
+            out["roofline"] = {"bound": "fp64", "achieved": tf, "peak": fp64_peak["dfma_tflops"], "unit": "TFLOP/s",
+                               "frac": tf / fp64_peak["dfma_tflops"], "flops_per_filter_step": flops / max(done, 1),
+                               "flops_counted": flops,
+                               "how": "algorithmic flops tallied in the kernel from every member's own n, nz, m "
+                                      "(SURVEY.md 8d figures); peak = DFMA rate measured in this run (slam_fp64_peak)"}
+        return out
     finally:
         ens.close()
 
 
-def cpu_ensemble_baseline(n_runs: int = 2048, extra: int = 5):
+def cpu_ensemble_baseline(n_runs: int = 2048, extra: int = 200):
     """The oracle's C twin (plain C, -O2 -ffp-contract=off, OpenMP over runs) on the host cores."""
     import ctypes
     lib = ctypes.CDLL(str(ROOT / "oracle" / "libslamtwin.so"))
@@ -344,16 +541,16 @@ def cpu_ensemble_baseline(n_runs: int = 2048, extra: int = 5):
                                       ctypes.c_int, ctypes.c_int, dp, dp, ctypes.POINTER(ctypes.c_int), ctypes.c_int,
                                       ctypes.c_int]
     t0 = time.perf_counter()
-    lib.twin_ensemble_cap(wpf.ctypes.data_as(dp), wp.shape[1], lmf.ctypes.data_as(dp), ENS_LANDMARKS, SEED, 0, n_runs, 2,
-                          10000, fp.ctypes.data_as(dp), None, None, cores, extra)
+    bad = lib.twin_ensemble_cap(wpf.ctypes.data_as(dp), wp.shape[1], lmf.ctypes.data_as(dp), ENS_LANDMARKS, SEED, 0, n_runs, 2,
+                                10000, fp.ctypes.data_as(dp), None, None, cores, extra)
     sec = time.perf_counter() - t0
     return {"value": n_runs * 2802 / sec, "unit": "filter-steps/s", "cores": cores, "kind": "port",
-            "sample": f"oracle/slam_twin.c twin_ensemble_cap, {n_runs} runs (same {extra}-landmark head-room) over {cores} "
-                      f"OpenMP threads, {sec:.2f} s; upper bound: runs that stop at capacity are counted in full"}
+            "sample": f"oracle/slam_twin.c twin_ensemble_cap, {n_runs} runs (room for {extra} extra landmarks: no run "
+                      f"stops, {bad} failed) over {cores} OpenMP threads, {sec:.2f} s"}
 
 
 def gpu_update_sharded(n_landmarks: int, m: int, steps: int, warmup: int, e2e_steps: int, rank: int, world: int,
-                       device: int):
+                       device: int, parity: bool = False, sustained_s: float = 0.0, force_nccl: bool = False):
     """One filter, P row-block-sharded over `world` ranks (one process per GPU)."""
     import torch
     import torch.distributed as dist
@@ -362,15 +559,55 @@ def gpu_update_sharded(n_landmarks: int, m: int, steps: int, warmup: int, e2e_st
 
     n = 3 + 2 * n_landmarks
     side = math.sqrt(n_landmarks / DENSITY)
+    old_env = os.environ.get("SLAM_SHARD_P2P")
+    if force_nccl:
+        os.environ["SLAM_SHARD_P2P"] = "0"
     sf = ShardedFilter(device, rank, world, n)
+    if force_nccl:
+        if old_env is None:
+            del os.environ["SLAM_SHARD_P2P"]
+        else:
+            os.environ["SLAM_SHARD_P2P"] = old_env
     try:
         sf.synth_state(n_landmarks, side, SEED)
         nz = m + 4
         z = np.zeros(2 * nz)
         ids = np.zeros(m, dtype=np.int64)
         check(lib.slam_synth_observations(None, n_landmarks, side, SEED, m, 4, dptr(z), iptr(ids)))
+        R2 = R_OBS.reshape(2, 2)
+        out = {"p2p": sf.p2p}
+        if parity:
+            def gather(segs, index):
+                tot = len(index)
+                blk_all = np.zeros((tot, tot))
+                owned = np.zeros((tot, tot))
+                oi = 0
+                for i0, ni in segs:
+                    oj = 0
+                    for j0, nj in segs:
+                        blk, _cnt = sf.cov_block(i0, ni, j0, nj)
+                        mask = ~np.isnan(blk)
+                        blk_all[oi:oi + ni, oj:oj + nj] = np.where(mask, blk, 0.0)
+                        owned[oi:oi + ni, oj:oj + nj] = mask
+                        oj += nj
+                    oi += ni
+                t = torch.from_numpy(np.stack([blk_all, owned])).to(f"cuda:{device}")
+                dist.all_reduce(t)
+                blk_all, owned = (a.cpu().numpy() for a in (t[0], t[1]))
+                if not np.all(owned == 1.0):
+                    raise RuntimeError("sharded gather: an entry of the sample is not owned by exactly one rank")
+                upper = index[:, None] <= index[None, :]     # rows i <= j are authoritative: mirror them
+                return np.where(upper, blk_all, blk_all.T)
+
+            out["parity"] = parity_check(n, perturbed(z.reshape(nz, 2).T, m), sf.get_x, gather,
+                                         lambda zobs: sf.associate(zobs, R2, 4.0, 25.0),
+                                         lambda zfc, ids_: sf.update(zfc, R2, ids_), rank)
+            if out["parity"] is not None:
+                out["parity"]["exchange"] = "peer memory (P2P stores + flag barrier)" if sf.p2p else "NCCL collectives"
+        if steps <= 0:
+            return out
         t0 = time.perf_counter()
-        zf2, idf, zn2 = sf.associate(z.reshape(nz, 2).T, R_OBS.reshape(2, 2), 4.0, 25.0)
+        zf2, idf, zn2 = sf.associate(z.reshape(nz, 2).T, R2, 4.0, 25.0)
         t_assoc = time.perf_counter() - t0
         # the m true observations come first and must be matched to their landmarks; a spurious
         # observation may legitimately fall inside a gate (large bearing uncertainty) and is not used
@@ -382,53 +619,63 @@ def gpu_update_sharded(n_landmarks: int, m: int, steps: int, warmup: int, e2e_st
         d_zf = torch.tensor(zf, device=f"cuda:{device}")
         d_idf = torch.tensor(idf, device=f"cuda:{device}")
         torch.cuda.synchronize(device)
-        for _ in range(warmup):
-            check(lib.slam_shard_update_resident(sf.ptr, d_zf.data_ptr(), m, dptr(R_OBS), d_idf.data_ptr()))
-        check(lib.slam_shard_sync(sf.ptr))
-        l0 = lib.slam_shard_launch_count(sf.ptr)
-        check(lib.slam_shard_profile(sf.ptr, 1))
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        dist.barrier()
-        torch.cuda.synchronize(device)
-        e0.record(stream)
-        for _ in range(steps):
-            check(lib.slam_shard_update_resident(sf.ptr, d_zf.data_ptr(), m, dptr(R_OBS), d_idf.data_ptr()))
-        e1.record(stream)
-        check(lib.slam_shard_sync(sf.ptr))
-        torch.cuda.synchronize(device)
-        dist.barrier()
-        ms_total = e0.elapsed_time(e1)
-        ph, cnt = (C.c_double * 4)(), C.c_int()
-        check(lib.slam_shard_profile_phases(sf.ptr, ph, C.byref(cnt)))
-        check(lib.slam_shard_profile(sf.ptr, 0))
-        k6 = C.c_double(ph[3])
-        launches = lib.slam_shard_launch_count(sf.ptr) - l0
-        # per-rank phase times (ms per update): H-row exchange, PHt/S/Cholesky, gain + W1 exchange, K6
-        pt = torch.tensor([v / max(cnt.value, 1) for v in ph], device=f"cuda:{device}", dtype=torch.float64)
-        allp = [torch.zeros_like(pt) for _ in range(world)]
-        dist.all_gather(allp, pt)
-        phases = np.array([[float(v) for v in a.cpu()] for a in allp])
-        # end to end: host zf / idf in, status + pose out, every step
-        pose = np.zeros(3)
-        check(lib.slam_shard_update(sf.ptr, dptr(zf), m, dptr(R_OBS), iptr(idf)))
-        dist.barrier()
-        torch.cuda.synchronize(device)
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            check(lib.slam_shard_update(sf.ptr, dptr(zf), m, dptr(R_OBS), iptr(idf)))
-            check(lib.slam_shard_get_pose(sf.ptr, dptr(pose)))
-        torch.cuda.synchronize(device)
-        e2e_ms = (time.perf_counter() - t0) / max(e2e_steps, 1) * 1e3
-        # max over ranks of every timing
-        t = torch.tensor([ms_total / steps, k6.value / max(cnt.value, 1), e2e_ms], device=f"cuda:{device}",
-                         dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, k6ms, e2e_ms = (float(v) for v in t.cpu())
+
+        def timed(nsteps, nwarm):
+            for _ in range(nwarm):
+                check(lib.slam_shard_update_resident(sf.ptr, d_zf.data_ptr(), m, dptr(R_OBS), d_idf.data_ptr()))
+            check(lib.slam_shard_sync(sf.ptr))
+            l0 = lib.slam_shard_launch_count(sf.ptr)
+            check(lib.slam_shard_profile(sf.ptr, 1))
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            dist.barrier()
+            torch.cuda.synchronize(device)
+            e0.record(stream)
+            for _ in range(nsteps):
+                check(lib.slam_shard_update_resident(sf.ptr, d_zf.data_ptr(), m, dptr(R_OBS), d_idf.data_ptr()))
+            e1.record(stream)
+            check(lib.slam_shard_sync(sf.ptr))
+            torch.cuda.synchronize(device)
+            dist.barrier()
+            ms_total = e0.elapsed_time(e1)
+            ph, cnt = (C.c_double * 4)(), C.c_int()
+            check(lib.slam_shard_profile_phases(sf.ptr, ph, C.byref(cnt)))
+            check(lib.slam_shard_profile(sf.ptr, 0))
+            launches = lib.slam_shard_launch_count(sf.ptr) - l0
+            # per-rank phase times (ms per update): H-row exchange, PHt/S/Cholesky, gain + W1 exchange, K6
+            pt = torch.tensor([v / max(cnt.value, 1) for v in ph] + [ms_total / nsteps], device=f"cuda:{device}",
+                              dtype=torch.float64)
+            allp = [torch.zeros_like(pt) for _ in range(world)]
+            dist.all_gather(allp, pt)
+            phases = np.array([[float(v) for v in a.cpu()] for a in allp])
+            return phases, int(launches)
+
+        phases, launches = timed(steps, warmup)
         names = ["h_row_exchange", "pht_s_cholesky", "gain_w1_exchange", "k6"]
         phase_ms = {nm: {"min": float(phases[:, i].min()), "max": float(phases[:, i].max())} for i, nm in enumerate(names)}
-        return dict(n=n, m=m, ms_per_step=ms, k6_ms=k6ms, launches=int(launches) * world, assoc_ms=t_assoc * 1e3, p2p=sf.p2p,
-                    phase_ms=phase_ms,
-                    e2e_ms_per_step=e2e_ms, h2d_bytes=(16 * m + 8 * m) * world, d2h_bytes=(4 + 24) * world)
+        ms, k6ms = float(phases[:, 4].max()), float(phases[:, 3].max())
+        out.update(n=n, m=m, ms_per_step=ms, k6_ms=k6ms, launches=launches * world, assoc_ms=t_assoc * 1e3,
+                   phase_ms=phase_ms)
+        if sustained_s > 0:
+            ns = min(2000, max(steps, int(math.ceil(sustained_s * 1e3 / ms))))
+            ph2, _ = timed(ns, 0)
+            out["sustained"] = {"steps": ns, "seconds": float(ph2[:, 4].max()) * ns / 1e3,
+                                "ms_per_step": float(ph2[:, 4].max()), "k6_ms": float(ph2[:, 3].max())}
+        if e2e_steps > 0:
+            # end to end: host zf / idf in, status + pose out, every step
+            pose = np.zeros(3)
+            check(lib.slam_shard_update(sf.ptr, dptr(zf), m, dptr(R_OBS), iptr(idf)))
+            dist.barrier()
+            torch.cuda.synchronize(device)
+            t0 = time.perf_counter()
+            for _ in range(e2e_steps):
+                check(lib.slam_shard_update(sf.ptr, dptr(zf), m, dptr(R_OBS), iptr(idf)))
+                check(lib.slam_shard_get_pose(sf.ptr, dptr(pose)))
+            torch.cuda.synchronize(device)
+            e2e_ms = (time.perf_counter() - t0) / max(e2e_steps, 1) * 1e3
+            t = torch.tensor([e2e_ms], device=f"cuda:{device}", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            out.update(e2e_ms_per_step=float(t.item()), h2d_bytes=(16 * m + 8 * m) * world, d2h_bytes=(4 + 24) * world)
+        return out
     finally:
         sf.close()
 
@@ -437,22 +684,30 @@ def reference_arm(args, rank: int):
     """--impl reference: the reference's CPU path (numpy restatement; Julia unavailable)."""
     if rank != 0:
         return
-    n_w = n_for_bytes(GB_PER_RANK * args.gpus)
+    n_w = workload_n(args.gpus)
     t0 = time.perf_counter()
     sec, cores = cpu_reference_update(args.sample_landmarks, args.m, max(args.steps, 1), max(args.warmup, 1))
     n_s = 3 + 2 * args.sample_landmarks
+    # the O(n^2) law the extrapolation rests on, measured: the same update at half the sample size
+    half = args.sample_landmarks // 2
+    sec_h, _ = cpu_reference_update(half, args.m, 3, 1)
+    exponent = math.log(sec / sec_h) / math.log(n_s / (3 + 2 * half))
     scale = (n_s / n_w) ** 2
     val = scale / sec
     sample = (f"oracle/slam_ref.py update (numpy literal restatement of src/ekf.jl:46-77; Julia <= 0.6 is not "
               f"installable here) at n = {n_s}, m = {args.m}, OpenBLAS {cores} threads, median of {max(args.steps, 1)} "
-              f"steps; scaled by (n_sample/n)^2 = {scale:.4g} to the workload n = {n_w} (extrapolated)")
+              f"steps; scaled by (n_sample/n)^2 = {scale:.4g} to the workload n = {n_w} (EXTRAPOLATED: three copies of the "
+              f"workload's P do not fit host RAM; measured scaling exponent between n = {3 + 2 * half} and {n_s}: "
+              f"{exponent:.2f}).  The same-size measured pair is update_10k of the GPU arm against "
+              f"measured_steps_per_s_at_sample here")
     line = {
         "impl": "reference", "metric": "EKF update steps/s", "value": val, "unit": "update steps/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / val,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args.gpus, args.m),
         "cpu_baseline": {"value": val, "unit": "update steps/s", "cores": cores, "kind": "port", "sample": sample,
-                         "measured_steps_per_s_at_sample": 1.0 / sec},
+                         "measured_steps_per_s_at_sample": 1.0 / sec, "measured_ms_per_step_at_sample": sec * 1e3,
+                         "extrapolated": True, "scaling_exponent_measured": exponent},
         "e2e": {"value": val, "unit": "update steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "wall_s": time.perf_counter() - t0,
     }
@@ -460,10 +715,11 @@ def reference_arm(args, rank: int):
 
 
 def workload_config(n_gpus: int, m: int, p2p: bool = True):
-    n = n_for_bytes(GB_PER_RANK * n_gpus)
+    n = workload_n(n_gpus)
     return {
         "workload": (f"single EKF-SLAM filter, synthetic {(n - 3) // 2}-landmark 2-D rangefinder field, n = {n}, "
-                     f"P = {8.0 * n * n / 1e9:.1f} GB FP64 ({GB_PER_RANK:.0f} GB per GPU; 8 GPUs = the 100k-landmark config), "
+                     f"P = {8.0 * n * n / 1e9:.1f} GB FP64 ({8.0 * n * n / n_gpus / 1e9:.2f} GB per GPU"
+                     f"{'; BASELINE config 5, the 100k-landmark map' if n == 200003 else '; the per-GPU share of the 100k-landmark / 8-GPU config'}), "
                      f"update with m = {m} associated observations of nz = {m + 4}"),
         "n": n, "landmarks": (n - 3) // 2, "m": m, "P_bytes_per_gpu": 8.0 * n * n / n_gpus,
         "parallelism": "single GPU" if n_gpus == 1 else (
@@ -472,6 +728,11 @@ def workload_config(n_gpus: int, m: int, p2p: bool = True):
             f"P row-block-sharded over {n_gpus} ranks, NCCL allreduce of the H rows and allgather of W1"),
         "cache": "inputs larger than L2 (P per GPU >> 126 MB); no flush needed",
     }
+
+
+def k6_block(alg_bytes, k6_ms, peak):
+    gbs = alg_bytes / (k6_ms * 1e-3) / 1e9
+    return {"k6_ms": k6_ms, "k6_gbs": gbs, "k6_frac_hbm": gbs / peak}
 
 
 def main():
@@ -483,7 +744,9 @@ def main():
     ap.add_argument("--m", type=int, default=8, help="associated observations per update")
     ap.add_argument("--sample-landmarks", type=int, default=10000, help="CPU baseline sample size")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--no-extras", action="store_true", help="skip update_10k / ensemble side measurements")
+    ap.add_argument("--no-extras", action="store_true", help="skip update_10k / ensemble / sweep side measurements")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle check before timing")
+    ap.add_argument("--sustained", type=float, default=5.0, help="seconds of back-to-back updates (0 = skip)")
     ap.add_argument("--gb-per-gpu", type=float, default=None, help="override P bytes per GPU (GB)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -505,64 +768,102 @@ def main():
 
     import torch
     import slamcuda
+    from slamcuda._ffi import lib, check
     if slamcuda.device_count() == 0:
         raise SystemExit("bench.py needs a CUDA device: libslamcuda has no CPU fallback")
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE = {world}: launch with torch.distributed.run")
     torch.cuda.set_device(local_rank)
     peak, peak_src = peaks()
-    n = n_for_bytes(GB_PER_RANK * args.gpus)
+    n = workload_n(args.gpus)
     nl = (n - 3) // 2
     sampler = ClockSampler(local_rank)
     extras = {}
+    dfma, dmma = C.c_double(), C.c_double()
+    check(lib.slam_fp64_peak(local_rank, C.byref(dfma), C.byref(dmma)))
+    fp64 = {"dfma_tflops": dfma.value, "dmma_tflops": dmma.value,
+            "how": "slam_fp64_peak: DFMA chains / mma.sync.m8n8k4.f64 tiles, 4 x 512 threads per SM, best of 2"}
+    parity_all = {}
 
     if args.gpus == 1:
         sampler.start()
-        r = gpu_update_single(nl, args.m, args.steps, args.warmup, e2e_steps=min(args.steps, 20))
+        r = gpu_update_single(nl, args.m, args.steps, args.warmup, e2e_steps=min(args.steps, 20),
+                              parity=not args.no_parity, sustained_s=args.sustained,
+                              sweep_m=() if args.no_extras else (1, 4, 16, 64))
         clocks = sampler.stop()
         ms = r["ms_per_step"]
         alg_bytes = 8.0 * n * (n + 1)
+        if "parity" in r:
+            parity_all["workload"] = r["parity"]
         if not args.no_extras:
             r10 = gpu_update_single(10000, args.m, max(args.steps, 50), args.warmup, e2e_steps=20,
-                                    host_mirror_steps=2)
+                                    host_mirror_steps=2, parity=not args.no_parity, sweep_m=(1, 4, 12, 16, 24, 32, 64))
             b10 = 8.0 * 20003 * 20004
+            if "parity" in r10:
+                parity_all["update_10k"] = r10["parity"]
             extras["update_10k"] = {
                 "workload": "BASELINE config 3: single filter, 10k landmarks (n = 20003, P = 3.2 GB), 1 B200",
                 "value": 1e3 / r10["ms_per_step"], "unit": "update steps/s", "m": args.m,
                 "e2e": 1e3 / r10["e2e_ms_per_step"], "k6_ms": r10["k6_ms"],
                 "k6_gbs": b10 / (r10["k6_ms"] * 1e-3) / 1e9, "k6_frac": b10 / (r10["k6_ms"] * 1e-3) / 1e9 / peak,
+                "whole_step_frac_of_hbm_floor": (b10 / peak / 1e9 * 1e3) / r10["ms_per_step"],
                 "associate_ms": r10["assoc_ms"],
+                "m_sweep": {k: {**v, **k6_block(b10, v["k6_ms"], peak),
+                                "k6_tflops": 2.0 * int(k) * 20003 * 20004 / (v["k6_ms"] * 1e-3) / 1e12}
+                            for k, v in r10.get("sweep", {}).items()},
                 "host_mirror_e2e": {
                     "what": "slam_set_state + slam_update + slam_get_state per step: the reference's literal "
                             "convention, x and all of P (pageable host arrays) over PCIe both ways every call",
                     "value": 1e3 / r10["host_mirror_ms_per_step"], "unit": "update steps/s",
                     "h2d_bytes_per_step": r10["host_mirror_bytes_each_way"],
                     "d2h_bytes_per_step": r10["host_mirror_bytes_each_way"]}}
-            extras["ensemble"] = gpu_ensemble(ENS_RUNS_PER_GPU, 0, 1, 0)
-            extras["ensemble_4096"] = gpu_ensemble(4096, 0, 1, 0)
+            extras["m_sweep_40gb"] = {k: {**v, **k6_block(alg_bytes, v["k6_ms"], peak),
+                                          "k6_tflops": 2.0 * int(k) * n * (n + 1) / (v["k6_ms"] * 1e-3) / 1e12}
+                                      for k, v in r.get("sweep", {}).items()}
+            extras["ensemble"] = gpu_ensemble(ENS_RUNS_TOTAL, 0, 1, 0, fp64_peak=fp64)
+            extras["ensemble_4096"] = gpu_ensemble(4096, 0, 1, 0, fp64_peak=fp64)
             if not args.no_cpu:
                 extras["ensemble"]["cpu_baseline"] = cpu_ensemble_baseline()
     else:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+        if not args.no_parity:
+            # the NCCL exchange path on the same workload: one checked update, nothing timed
+            rn = gpu_update_sharded(nl, args.m, 0, 0, 0, rank, world, local_rank, parity=True, force_nccl=True)
+            if rn.get("parity") is not None:
+                parity_all["workload_nccl_path"] = rn["parity"]
         sampler.start()
         r = gpu_update_sharded(nl, args.m, args.steps, args.warmup, e2e_steps=min(args.steps, 20),
-                               rank=rank, world=world, device=local_rank)
+                               rank=rank, world=world, device=local_rank, parity=not args.no_parity,
+                               sustained_s=args.sustained)
         clocks = sampler.stop()
         ms = r["ms_per_step"]
         alg_bytes = 8.0 * n * (n + 1) / world
+        if r.get("parity") is not None:
+            parity_all["workload"] = r["parity"]
         if not args.no_extras:
-            extras["ensemble"] = gpu_ensemble(ENS_RUNS_PER_GPU, rank, world, local_rank)
+            # strong scaling: the fixed N = 1 map (n = 70709, 40 GB) over the N ranks -- the exchange latency's share
+            # shows where K6 shrinks to 1/N of a step
+            n1 = n_for_bytes(GB_PER_RANK)
+            rs = gpu_update_sharded((n1 - 3) // 2, args.m, max(args.steps, 30), args.warmup, 0, rank, world, local_rank)
+            extras["strong_scaling_40gb"] = {
+                "workload": f"the N = 1 map (n = {n1}, P = 40 GB) row-block-sharded over {world} ranks", "scaling": "strong",
+                "value": 1e3 / rs["ms_per_step"], "unit": "update steps/s", "ms_per_step": rs["ms_per_step"],
+                "k6_ms": rs["k6_ms"], "phase_ms_over_ranks": rs["phase_ms"],
+                **k6_block(8.0 * n1 * (n1 + 1) / world, rs["k6_ms"], peak)}
+            extras["ensemble"] = gpu_ensemble(ENS_RUNS_TOTAL, rank, world, local_rank, fp64_peak=fp64)
 
     if rank != 0:
         return
     k6_gbs = alg_bytes / (r["k6_ms"] * 1e-3) / 1e9
-    traffic = None   # dram bytes per launch from the committed ncu --set full capture of this workload
+    traffic, traffic_src = None, None   # dram bytes per launch from the committed ncu --set full capture of this workload
     tf = ROOT / "profiles" / "k6_traffic.json"
-    if tf.exists():
+    if tf.exists() and args.gpus == 1:
         t = json.loads(tf.read_text())
-        if t.get("n") == n and t.get("m") == args.m and args.gpus == 1:
+        if t.get("n") == n and t.get("m") == args.m:
             traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
+            traffic_src = "committed ncu --set full capture (profiles/k6_traffic.json), not measured in this run"
+    parity_ok = all(p.get("ok") for p in parity_all.values()) if parity_all else None
     line = {
         "metric": "EKF update steps/s", "value": 1e3 / ms, "unit": "update steps/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
@@ -572,16 +873,25 @@ def main():
                 "h2d_bytes_per_step": r["h2d_bytes"], "d2h_bytes_per_step": r["d2h_bytes"],
                 "path": "slam_update() with host zf/idf (resident mode: P stays in HBM, as sim! re-binds it)"},
         "gpu_launches": r["launches"],
+        "parity": {"ok": parity_ok, **parity_all} if parity_all else None,
         "roofline": {"bound": "hbm", "kernel": "k_downdate_fma (K6, P -= W1*W1' over the upper triangle)",
                      "achieved": k6_gbs, "peak": peak, "unit": "GB/s", "frac": k6_gbs / peak,
                      "traffic": traffic, "peak_source": peak_src,
+                     **({"traffic_source": traffic_src} if traffic_src else {}),
                      # the measured peak is torch's copy bandwidth, not a hardware limit: an in-place triangular
                      # read-modify-write can sit a little above it; 8 TB/s is the figure north_star quotes
                      "frac_of_datasheet_8tbs": k6_gbs / 8000.0,
                      "algorithmic_bytes_per_launch": alg_bytes, "k6_ms": r["k6_ms"],
                      "k6_share_of_step": r["k6_ms"] / ms,
+                     "whole_step_frac_of_hbm_floor": (alg_bytes / peak / 1e9 * 1e3) / ms,
                      **({"phase_ms_over_ranks": r["phase_ms"]} if "phase_ms" in r else {})},
+        "fp64_peak": fp64,
     }
+    if "sustained" in r:
+        s = r["sustained"]
+        line["sustained"] = {"what": f"{s['steps']} back-to-back updates ({s['seconds']:.1f} s): the power-capped figure "
+                                     f"beside the {args.steps}-step burst", "value": 1e3 / s["ms_per_step"],
+                             "unit": "update steps/s", **s, **k6_block(alg_bytes, s["k6_ms"], peak)}
     if "obs_step_ms" in r:
         line["observation_step"] = {
             "what": "slam_associate (nz host observations in, zf / idf / zn out) + slam_update with its result + "
@@ -590,9 +900,21 @@ def main():
             "matched": r["assoc_matched"], "landmark_passes_scored_frac": r["gate_scored_frac"]}
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline_block(n, args.m, sample_landmarks=args.sample_landmarks)
+        if args.gpus == 1 and not args.no_extras:
+            cb = line["cpu_baseline"]
+            if "update_10k" in extras and args.sample_landmarks == 10000:
+                # the sample IS config 3's size: a measured same-size pair, no extrapolation
+                extras["update_10k"]["cpu_baseline"] = {
+                    "value": cb["measured_steps_per_s_at_sample"], "unit": "update steps/s", "cores": cb["cores"],
+                    "kind": "port", "sample": "oracle/slam_ref.py update at n = 20003, m = 8: the same size, measured"}
+            line["cpu_baseline"]["associate"] = cpu_associate_baseline()
+            line["cpu_baseline"]["course1_config1"] = cpu_course1_baseline()
     line.update(extras)
     real_stdout.write(json.dumps(line) + "\n")
     real_stdout.flush()
+    if parity_ok is False:
+        sys.stderr.write("bench.py: PARITY FAILED against the oracle: " + json.dumps(parity_all) + "\n")
+        sys.exit(3)
 
 
 if __name__ == "__main__":

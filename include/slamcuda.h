@@ -62,12 +62,25 @@ const char *slam_version(void);
 /* Number of CUDA devices visible (0 when none / no driver); never fails. */
 int slam_device_count(void);
 
+/* Measured FP64 roofs of `device`, TFLOP/s: DFMA chains and mma.sync.m8n8k4.f64 tiles (SASS DMMA).
+ * bench.py quotes K6 above 32 ranks and the ensemble kernel against them.  ~0.1 s. */
+int slam_fp64_peak(int device, double *dfma_tflops, double *dmma_tflops);
+
 /* ---- single filter, state resident on one device ------------------------------------ */
 
 /* EKFSlamState(x, cov) -- src/common.jl:25-28, as built by sim/ekfslam-sim.jl:42.
  * Allocates device state with capacity n_max (>= 3).  State starts as n = 3, x = 0, P = 0. */
 int slam_create(int device, int n_max, slam_t **out);
 int slam_destroy(slam_t *h);
+
+/* Capacity growth: the reference's state grows without bound (hcat / vcat per new landmark,
+ * src/ekf.jl:108-109); a handle's capacity is fixed so that slam_add_features appends in place.
+ * slam_reserve raises it to at least n_max_new states (new device arrays, one device-to-device copy
+ * of x and the live part of P; no-op when already that large; the old state survives a failure).
+ * The host mirrors call it when slam_add_features reports SLAM_ERR_CAPACITY. */
+int slam_reserve(slam_t *h, int n_max_new);
+/* The current capacity n_max; negative on error. */
+int slam_capacity(slam_t *h);
 
 /* state.x / state.cov <- host arrays.  P is n x n column-major with leading dim ldp. */
 int slam_set_state(slam_t *h, const double *x, const double *P, int n, int ldp);
@@ -174,11 +187,31 @@ int slam_ens_destroy(slam_ens_t *e);
 /* Member capacity.  The reference's state grows without bound (hcat / vcat, src/ekf.jl:108-109);
  * a member holds 3 + 2*(nl + extra) states: `extra` (default 5) leaves room for the spurious
  * landmarks the algorithm itself creates when an observation of a mapped landmark fails both gates
- * (src/data-association.jl:45-47).  A member that outgrows it stops with SLAM_ERR_CAPACITY in
- * status[].  Call before slam_ens_run / slam_ens_keep_tracks results are read. */
+ * (src/data-association.jl:45-47).  A member that outgrows it is re-run with more room (slam_ens_set_growth)
+ * or, with growth = 0, stops with SLAM_ERR_CAPACITY in status[].  Call before slam_ens_run. */
 int slam_ens_set_extra_landmarks(slam_ens_t *e, int extra);
 /* 3 + 2*(nl + extra); negative on error. */
 int slam_ens_capacity(slam_ens_t *e);
+/* How a member whose map outgrows that capacity is treated.  The reference's state grows without bound
+ * (hcat / vcat, src/ekf.jl:108-109), and so does a member by default:
+ *   2 (default)  the members a launch cannot hold are re-run -- from their first step; the noise is keyed by the
+ *                run id, so the result is the single-launch result -- by further launches with more
+ *                shared memory per member (two CTAs per SM, then one), and finally with x, P and the
+ *                workspace in global memory, the capacity doubling per round up to 3 + 2*(landmarks +
+ *                observations of the whole run), which no run can exceed: no member ever stops for capacity;
+ *   1            the shared-memory launches only;
+ *   0            fixed capacity: a member that outgrows slam_ens_capacity() stops with SLAM_ERR_CAPACITY. */
+int slam_ens_set_growth(slam_ens_t *e, int mode);
+/* Caps the head-room (landmarks beyond nl) of the shared-memory launches of growth >= 1; -1 (default) = what
+ * one CTA's shared memory holds.  (Tests use it to send members to the global-memory rounds.) */
+int slam_ens_set_max_shared_extra(slam_ens_t *e, int extra);
+/* Algorithmic FP64 operations of a run, tallied by the kernel with SURVEY.md 8d's figures and every member's own
+ * n, nz, m at every step (30 n per predict; 80 nz Nf per observation step, plus 2m n(n+1) + 20 n m + 8 n m^2 +
+ * 8 m^3 with m matches).  on = 1 before slam_ens_run; *total (may be NULL) = the last run's sum; on = 0 frees. */
+int slam_ens_count_flops(slam_ens_t *e, int on, double *total);
+/* Every launch of the last run in order (shared-memory tiers, then global-memory rounds): capacity in states
+ * and members run, at most `max` entries each; returns the number of launches.  Waits for the run. */
+int slam_ens_tier_info(slam_ens_t *e, int *capacity, int *members, int max);
 /* Two-pass capacity.  The kernel's throughput follows the member CTAs resident per SM, which the
  * member's shared memory (i.e. its capacity) decides, and few members ever use the head-room.  A run
  * may therefore take two launches: a first pass with `first_extra` < extra landmarks of head-room,
@@ -207,7 +240,8 @@ int slam_ens_get_results(slam_ens_t *e, double *final_pose, int *n_final, int *s
  * been enabled before the run with slam_ens_keep_tracks(e, 1). */
 int slam_ens_keep_tracks(slam_ens_t *e, int on);
 int slam_ens_get_track(slam_ens_t *e, int member, double *track);
-/* Final x (n_final) and P (n_final^2, ldp, full symmetric) of one member; returns n_final. */
+/* Final x (n_final) and P (n_final^2, ldp, full symmetric) of one member; returns n_final.  x and P may both
+ * be NULL to ask for n_final first (with growth > 0 it is not bounded by slam_ens_capacity()). */
 int slam_ens_get_state(slam_ens_t *e, int member, double *x, double *P, int ldp);
 /* Host-supplied noise instead of Philox (parity runs): ctrl 2 x nsteps per member,
  * obs: pool of `obs_per_member` normals per member consumed in draw order. */

@@ -230,6 +230,13 @@ function add_features(state::SlamState, z, R)
     k = size(z, 2)
     h = with_state(state, 2k)
     if k > 0
+        # the reference's state grows without bound (hcat / vcat, src/ekf.jl:108-109): double the
+        # device capacity when the append would not fit
+        need = slam_length(h) + 2k
+        if need > h.n_max
+            h.n_max = max(need, 2 * h.n_max)
+            slam_check(ccall((:slam_reserve, libslamcuda), Cint, (Ptr{Void}, Cint), h.ptr, h.n_max))
+        end
         slam_check(ccall((:slam_add_features, libslamcuda), Cint,
                          (Ptr{Void}, Ptr{Float64}, Cint, Ptr{Float64}), h.ptr,
                          convert(Matrix{Float64}, z), k, colmajor4(R)))

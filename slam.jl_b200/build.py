@@ -32,6 +32,7 @@ PER_FILE = {
     "ensemble.cu": ["-fmad=false"],
     "downdate.cu": [],
     "downdate_dmma.cu": [],
+    "probe.cu": [],
 }
 
 

@@ -154,7 +154,8 @@ k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n
             wi[ROWS - 1][k] = -t.y;
         } else if (ROWS == 2) {   // row blocks of the sharded path start at odd rows
             wi[0][k] = -__ldg(W1t + (size_t)k * n_pad + i);
-            wi[ROWS - 1][k] = -__ldg(W1t + (size_t)k * n_pad + i + 1);
+            // a ragged last warp may stand on row n_pad - 1: its second row does not exist (and is never used)
+            wi[ROWS - 1][k] = i + 1 < n_pad ? -__ldg(W1t + (size_t)k * n_pad + i + 1) : 0.0;
         } else {
             wi[0][k] = -__ldg(W1t + (size_t)k * n_pad + i);
         }

@@ -179,6 +179,13 @@ struct EnsArgs {
     // a second launch with the full capacity (redo_list / redo_count = the first pass's over_*).
     int *over_list, *over_count;
     const int *redo_list, *redo_count;
+    // Global-memory tier (members that outgrow every shared-memory capacity): x, P, the W1 / association workspace
+    // and the triangle table of redo member i live at gstate + i*gstride; final_x / final_P are then indexed by i too.
+    double *gstate;
+    size_t gstride;
+    // optional [n_runs]: algorithmic FP64 operations of the member's run by the figures of SURVEY.md 8d -- per
+    // predict 30 n; per observation step 80 nz Nf, and with m matches 2m n(n+1) + 20 n m + 8 n m^2 + 8 m^3
+    double *flops;
 };
 
 constexpr int ENS_MAXB = 9;       // steps per block (dt_observe = 8 dt: an observation every 9th step)
@@ -238,20 +245,31 @@ __host__ __device__ inline int ens_ntri(int ncap, int mmax) {
     const int a = R * (R - 1) / 2, b = nb * (nb + 1) / 2;
     return ens_ru4(a > b ? a : b);
 }
-__host__ __device__ inline size_t ens_smem_bytes(int ncap, int mmax) {
+// A member's storage has two parts.  The STATE part grows with the capacity: x, the packed triangle of P, the
+// W1 / association workspace and the triangle table; it lives in shared memory for the shared tiers and in global
+// memory for the last-resort tier.  The FIXED part (the 2m x 2m square and the per-observation vectors) depends on
+// the largest number of observations per step only and is always in shared memory.
+__host__ __device__ inline size_t ens_state_doubles(int ncap, int mmax) {
+    return (size_t)ens_ru4(ncap) + ens_pdoubles(ncap) + ens_wdoubles(ncap, mmax) + ens_ru4((ens_ntri(ncap, mmax) + 3) / 4);
+}
+__host__ __device__ inline size_t ens_fixed_bytes(int mmax) {
     const int R = 2 * mmax;
-    size_t d = ens_ru4(ncap) + ens_pdoubles(ncap) + ens_wdoubles(ncap, mmax) + ens_ru4(R * ens_lds(R)) +
-               3 * ens_ru4(R) + ens_ru4(10 * mmax) + 3 * ens_ru4(2 * mmax) + ENS_MAXB * BS + ENS_PAR;
-    return d * 8 + ens_ru4(3 * mmax) * 4 + ens_ntri(ncap, mmax) * 2 + 64;
+    size_t d = ens_ru4(R * ens_lds(R)) + 3 * ens_ru4(R) + ens_ru4(10 * mmax) + 3 * ens_ru4(2 * mmax) + ENS_MAXB * BS + ENS_PAR;
+    return d * 8 + ens_ru4(3 * mmax) * 4 + 32;
+}
+__host__ __device__ inline size_t ens_smem_bytes(int ncap, int mmax) {
+    return ens_state_doubles(ncap, mmax) * 8 + ens_fixed_bytes(mmax);
 }
 
-__device__ inline EnsSmem ens_carve(double *base, int ncap, int mmax) {
+__device__ inline EnsSmem ens_carve(double *state, double *fixed, int ncap, int mmax) {
     EnsSmem s;
     const int R = 2 * mmax;
-    double *p = base;
+    double *p = state;
     s.x = p;   p += ens_ru4(ncap);
     s.P = p;   p += ens_pdoubles(ncap);
     s.W = p;   p += ens_wdoubles(ncap, mmax);
+    s.tri = reinterpret_cast<unsigned short *>(p);
+    p = fixed;
     s.S = p;   p += ens_ru4(R * ens_lds(R));
     s.cd = p;  p += ens_ru4(R);
     s.u = p;   p += ens_ru4(R);
@@ -265,8 +283,7 @@ __device__ inline EnsSmem ens_carve(double *base, int ncap, int mmax) {
     int *q = reinterpret_cast<int *>(p);
     s.fp = q;  q += mmax;
     s.idf = q; q += mmax;
-    s.cls = q; q += ens_ru4(3 * mmax) - 2 * mmax;
-    s.tri = reinterpret_cast<unsigned short *>(q);
+    s.cls = q;
     return s;
 }
 
@@ -899,7 +916,7 @@ __device__ int ens_add_features(const EnsSmem &sm, int n, int k) {
 }
 
 // One CTA = one member = one whole run of sim!.
-template <int T>
+template <int T, bool GLOBAL>
 __global__ void __launch_bounds__(T, T == 128 ? 5 : 1)
 k_ensemble(EnsArgs a) {
     extern __shared__ __align__(32) double ens_smem[];
@@ -911,7 +928,10 @@ k_ensemble(EnsArgs a) {
         return;
     }
     const int tid = threadIdx.x;
-    const EnsSmem sm = ens_carve(ens_smem, a.ncap, a.mmax);
+    // where this member's results go: the global tier lays its outputs out by redo slot
+    const size_t orow = GLOBAL ? (size_t)blockIdx.x : (size_t)member;
+    const EnsSmem sm = GLOBAL ? ens_carve(a.gstate + (size_t)blockIdx.x * a.gstride, ens_smem, a.ncap, a.mmax)
+                              : ens_carve(ens_smem, ens_smem + ens_state_doubles(a.ncap, a.mmax), a.ncap, a.mmax);
     const uint32_t run = a.run0 + (uint32_t)member;
     for (int idx = tid; idx < a.npk; idx += T) sm.P[idx] = 0.0;   // zeros(3,3); spare capacity zeroed
     for (int idx = tid; idx < a.ncap; idx += T) sm.x[idx] = 0.0;
@@ -934,6 +954,7 @@ k_ensemble(EnsArgs a) {
     __syncthreads();
     int done = 0, staged = -1;
     bool outgrown = false;
+    double flops = 0.0;   // thread 0's tally (bench.py's FP64 roofline entry)
     ENS_MARK(-1);
     int4 dnext = a.blk[0];
     for (int b = 0; b < a.nblocks; b++) {
@@ -948,9 +969,12 @@ k_ensemble(EnsArgs a) {
             __syncthreads();
         }
         ens_predict_block<T>(sm, n, len, nz);
+        if (a.flops) flops += 30.0 * n * len;
         if (nz > 0) {
             ens_associate<T>(sm, n, nz);
             const int m = (int)sm.par[0], k = (int)sm.par[1];
+            if (a.flops)
+                flops += 40.0 * nz * (n - 3) + (m > 0 ? (double)m * (2.0 * n * (n + 1) + 20.0 * n + 8.0 * n * m + 8.0 * m * m) : 0.0);
             if (m > 0) {
                 if (!ens_update<T>(sm, n, a.ldw, m, a, b + 1, run, ctrl, obsn)) { status = SLAM_ERR_NOT_PD; break; }
                 staged = b + 1;
@@ -970,11 +994,11 @@ k_ensemble(EnsArgs a) {
         ENS_MARK(14);
     }
     __syncthreads();
-    for (int idx = tid; idx < a.ocap; idx += T) a.final_x[(size_t)member * a.ocap + idx] = idx < a.ncap ? sm.x[idx] : 0.0;
+    for (int idx = tid; idx < a.ocap; idx += T) a.final_x[orow * a.ocap + idx] = idx < a.ncap ? sm.x[idx] : 0.0;
     if (a.final_P)   // exported as the full symmetric matrix
         for (int idx = tid; idx < a.ocap * a.ocap; idx += T) {
             const int i = idx % a.ocap, j = idx / a.ocap;
-            a.final_P[(size_t)member * a.ocap * a.ocap + idx] = (i < a.ncap && j < a.ncap) ? psym(sm.P, i, j) : 0.0;
+            a.final_P[orow * a.ocap * a.ocap + idx] = (i < a.ncap && j < a.ncap) ? psym(sm.P, i, j) : 0.0;
         }
     ENS_MARK(-2);
     if (tid == 0) {
@@ -982,6 +1006,7 @@ k_ensemble(EnsArgs a) {
         a.n_final[member] = n;
         a.status[member] = status;
         a.steps_done[member] = done;
+        if (a.flops) a.flops[member] = flops;
         if (track)   // steps not run (stopped member) are marked NaN
             for (int s2 = done; s2 < a.nsteps; s2++) track[3 * s2] = track[3 * s2 + 1] = track[3 * s2 + 2] = nan("");
     }
@@ -990,6 +1015,30 @@ k_ensemble(EnsArgs a) {
 // ---------------------------------------------------------------------------------------
 // host API
 // ---------------------------------------------------------------------------------------
+// Capacity tiers.  The reference's state grows without bound (hcat / vcat, src/ekf.jl:108-109; new landmarks
+// from src/data-association.jl:45-47); a member CTA has a fixed capacity, and the kernel's throughput follows
+// the CTAs resident per SM, i.e. the member's shared memory.  A run is therefore a sequence of launches with
+// growing capacity, each re-running -- from their first step; noise is keyed by run id, so the result is
+// the single-launch result -- only the members whose map outgrew the previous one:
+//   tier 0   first pass: the largest head-room that still gives the best occupancy (5 CTAs per SM for course1)
+//   tier 1   `extra` landmarks of head-room (slam_ens_set_extra_landmarks, default 5)
+//   tier 2   the largest head-room with two CTAs per SM          \ growth >= 1
+//   tier 3   the largest head-room one CTA's shared memory holds /
+//   global   x, P and the workspace in global memory, capacity doubled per round up to the bound
+//            3 + 2*(landmarks + observations of the whole run) that no member can exceed (growth == 2)
+// growth = 0 keeps the fixed capacity of tier 1: a member that outgrows it stops with SLAM_ERR_CAPACITY.
+constexpr int ENS_MAX_LISTS = 6;
+
+struct EnsTier {
+    int extra = 0, ncap = 0, occ = 0;
+    size_t smem = 0;
+};
+struct EnsGlobalRound {
+    int ncap = 0;
+    std::vector<int> members;
+    double *d_x = nullptr, *d_P = nullptr;
+};
+
 struct slam_ensemble {
     int device = 0, n_runs = 0, nl = 0, ncap = 0, extra = 0, threads = 128;
     uint64_t seed = 0;
@@ -1002,12 +1051,18 @@ struct slam_ensemble {
     int obs_per_member = 0;
     double *d_final_x = nullptr, *d_tracks = nullptr, *d_final_P = nullptr;
     int *d_n_final = nullptr, *d_status = nullptr;
+    double *d_flops = nullptr;     // per member, allocated by slam_ens_count_flops
     bool keep = false, ran = false;
-    size_t smem = 0;
-    int first_extra = -1;          // first-pass head-room: -1 = chosen by occupancy, >= extra = single pass
-    int *d_over = nullptr;         // [0] = count, [1 + i] = members the first pass could not hold
-    int last_first_extra = -1;     // what the last run used (-1 = single pass)
-    int auto_first = -1, auto_key = -1;   // cached automatic choice and the (extra, threads) it was made for
+    int first_extra = -1;          // first-pass head-room: -1 = chosen by occupancy, >= extra = no first pass
+    int growth = 2;                // 0 fixed capacity, 1 + larger shared-memory tiers, 2 + global-memory tier
+    int max_shared_extra = -1;     // cap on the shared tiers' head-room (-1: what the device holds)
+    std::vector<EnsTier> tiers;
+    bool dirty = true;             // tiers / output layout must be rebuilt before the next run
+    int ocap = 0;                  // capacity d_final_x / d_final_P are laid out for (the largest shared tier)
+    int *d_over = nullptr;         // ENS_MAX_LISTS lists of n_runs + 1 ints: [0] = count, [1 + i] = member
+    bool global_pending = false;
+    std::vector<EnsGlobalRound> grounds;
+    std::vector<int> tier_members; // members each launch of the last run ran (shared tiers, then global rounds)
     long long launches = 0;
 };
 
@@ -1017,24 +1072,34 @@ struct slam_ensemble {
         CUDA_TRY(cudaSetDevice((e)->device));                             \
     } while (0)
 
+static void ens_free_rounds(slam_ens_t *e) {
+    for (auto &r : e->grounds) {
+        cudaFree(r.d_x);
+        cudaFree(r.d_P);
+    }
+    e->grounds.clear();
+}
+
 extern "C" int slam_ens_destroy(slam_ens_t *e) {
     if (!e) return SLAM_OK;
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
+    ens_free_rounds(e);
     cudaFree(e->d_gamma); cudaFree(e->d_ztrue); cudaFree(e->d_blk); cudaFree(e->d_steps_done); cudaFree(e->d_obs_start);
     cudaFree(e->d_ctrl); cudaFree(e->d_obs); cudaFree(e->d_final_x); cudaFree(e->d_tracks);
-    cudaFree(e->d_final_P); cudaFree(e->d_n_final); cudaFree(e->d_status); cudaFree(e->d_over);
+    cudaFree(e->d_final_P); cudaFree(e->d_n_final); cudaFree(e->d_status); cudaFree(e->d_over); cudaFree(e->d_flops);
     if (e->stream) cudaStreamDestroy(e->stream);
     cudaGetLastError();
     delete e;
     return SLAM_OK;
 }
 
-// (re)sizes everything that depends on the member capacity 3 + 2*(nl + extra)
+static int ens_mmax(const slam_ens_t *e) { return std::max(e->t.max_nz, 1); }
+
+// the base capacity 3 + 2*(nl + extra): must fit one CTA's shared memory
 static int ens_resize(slam_ens_t *e, int extra) {
     const int ncap = 3 + 2 * (e->nl + extra);
-    const int mmax = std::max(e->t.max_nz, 1);
-    const size_t smem = ens_smem_bytes(ncap, mmax);
+    const size_t smem = ens_smem_bytes(ncap, ens_mmax(e));
     int max_optin = 0;
     cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, e->device);
     if (smem > (size_t)max_optin) {
@@ -1042,17 +1107,9 @@ static int ens_resize(slam_ens_t *e, int extra) {
                        "observations per step); the device offers %d", smem, e->nl, extra, e->t.max_nz, max_optin);
         return SLAM_ERR_CAPACITY;
     }
-    CUDA_TRY(cudaFuncSetAttribute(k_ensemble<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CUDA_TRY(cudaFuncSetAttribute(k_ensemble<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CUDA_TRY(cudaFuncSetAttribute(k_ensemble<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    cudaFree(e->d_final_x);
-    cudaFree(e->d_final_P);
-    e->d_final_x = e->d_final_P = nullptr;
-    CUDA_TRY(cudaMalloc(&e->d_final_x, sizeof(double) * (size_t)e->n_runs * ncap));
-    if (e->keep) CUDA_TRY(cudaMalloc(&e->d_final_P, sizeof(double) * (size_t)e->n_runs * ncap * ncap));
     e->extra = extra;
     e->ncap = ncap;
-    e->smem = smem;
+    e->dirty = true;
     e->ran = false;
     return SLAM_OK;
 }
@@ -1091,7 +1148,7 @@ extern "C" int slam_ens_create(int device, const double *waypoints, int nwp, con
     EN_TRY(cudaMalloc(&e->d_n_final, sizeof(int) * n_runs));
     EN_TRY(cudaMalloc(&e->d_steps_done, sizeof(int) * n_runs));
     EN_TRY(cudaMalloc(&e->d_status, sizeof(int) * n_runs));
-    EN_TRY(cudaMalloc(&e->d_over, sizeof(int) * (n_runs + 1)));
+    EN_TRY(cudaMalloc(&e->d_over, sizeof(int) * (size_t)ENS_MAX_LISTS * (n_runs + 1)));
     const double pose0[3] = {waypoints[0], waypoints[1],
                              atan2(waypoints[3] - waypoints[1], waypoints[2] - waypoints[0])};
     EN_TRY(cudaMemcpy(e->d_gamma, t.gamma.data(), sizeof(double) * t.nsteps, cudaMemcpyHostToDevice));
@@ -1118,6 +1175,23 @@ extern "C" int slam_ens_set_threads(slam_ens_t *e, int threads) {
     ARG_CHECK(e != nullptr, "NULL handle");
     ARG_CHECK(threads == 64 || threads == 128 || threads == 256, "threads must be 64, 128 or 256");
     e->threads = threads;
+    e->dirty = true;
+    return SLAM_OK;
+}
+
+extern "C" int slam_ens_set_growth(slam_ens_t *e, int mode) {
+    ARG_CHECK(e != nullptr, "NULL handle");
+    ARG_CHECK(mode >= 0 && mode <= 2, "mode must be 0, 1 or 2");
+    e->growth = mode;
+    e->dirty = true;
+    return SLAM_OK;
+}
+
+extern "C" int slam_ens_set_max_shared_extra(slam_ens_t *e, int extra) {
+    ARG_CHECK(e != nullptr, "NULL handle");
+    ARG_CHECK(extra >= -1, "extra < -1");
+    e->max_shared_extra = extra;
+    e->dirty = true;
     return SLAM_OK;
 }
 
@@ -1138,8 +1212,32 @@ extern "C" int slam_ens_keep_tracks(slam_ens_t *e, int on) {
     e->keep = on != 0;
     if (e->keep && !e->d_tracks)
         CUDA_TRY(cudaMalloc(&e->d_tracks, sizeof(double) * (size_t)e->n_runs * 3 * e->t.nsteps));
-    if (e->keep && !e->d_final_P)
-        CUDA_TRY(cudaMalloc(&e->d_final_P, sizeof(double) * (size_t)e->n_runs * e->ncap * e->ncap));
+    e->dirty = true;   // the covariance export is sized with the output layout
+    return SLAM_OK;
+}
+
+// Algorithmic FP64 operations of the last run (SURVEY.md 8d's per-unit figures evaluated with every member's own
+// n, nz and m at every step; a member re-run by a later launch counts once).  on = 1 before the run; *total after.
+extern "C" int slam_ens_count_flops(slam_ens_t *e, int on, double *total) {
+    E_CHECK(e);
+    if (on && !e->d_flops) {
+        CUDA_TRY(cudaMalloc(&e->d_flops, sizeof(double) * e->n_runs));
+        CUDA_TRY(cudaMemset(e->d_flops, 0, sizeof(double) * e->n_runs));
+    }
+    if (total) {
+        *total = 0;
+        if (e->d_flops && e->ran) {
+            CUDA_TRY(cudaStreamSynchronize(e->stream));
+            std::vector<double> f(e->n_runs);
+            CUDA_TRY(cudaMemcpy(f.data(), e->d_flops, sizeof(double) * e->n_runs, cudaMemcpyDeviceToHost));
+            for (double v : f) *total += v;
+        }
+    }
+    if (!on && e->d_flops) {
+        CUDA_TRY(cudaStreamSynchronize(e->stream));
+        cudaFree(e->d_flops);
+        e->d_flops = nullptr;
+    }
     return SLAM_OK;
 }
 
@@ -1160,41 +1258,39 @@ extern "C" int slam_ens_set_noise(slam_ens_t *e, const double *ctrl, const doubl
 template <int T>
 static int ens_occupancy(size_t smem) {
     int nb = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_ensemble<T>, T, smem) != cudaSuccess) {
+    if (cudaFuncSetAttribute(k_ensemble<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_ensemble<T, false>, T, smem) != cudaSuccess) {
         cudaGetLastError();
         return 0;
     }
     return nb;
 }
-static int ens_ctas_per_sm(const slam_ens_t *e, int extra) {
-    const size_t smem = ens_smem_bytes(3 + 2 * (e->nl + extra), std::max(e->t.max_nz, 1));
+static int ens_occ(const slam_ens_t *e, size_t smem) {
     switch (e->threads) {
         case 64: return ens_occupancy<64>(smem);
         case 256: return ens_occupancy<256>(smem);
         default: return ens_occupancy<128>(smem);
     }
 }
-
-static int ens_first_extra_auto(const slam_ens_t *e);
+static EnsTier ens_tier(const slam_ens_t *e, int extra) {
+    EnsTier t;
+    t.extra = extra;
+    t.ncap = 3 + 2 * (e->nl + extra);
+    t.smem = ens_smem_bytes(t.ncap, ens_mmax(e));
+    t.occ = ens_occ(e, t.smem);
+    return t;
+}
 
 // First-pass head-room.  The kernel is latency-bound and its throughput follows the resident CTAs per
 // SM, which the member's shared memory decides; few members ever need the full head-room.  Auto: the
-// largest head-room that still gives the best occupancy, if that beats the full capacity's and the
-// ensemble is longer than one wave (a second pass costs about one member's run time).
-static int ens_first_extra(slam_ens_t *e) {
+// largest head-room that still gives the best occupancy, if that beats the base capacity's and the
+// ensemble is longer than one wave (another pass costs about one member's run time).
+static int ens_first_extra(const slam_ens_t *e) {
     if (e->first_extra >= 0) return std::min(e->first_extra, e->extra);
-    const int key = e->extra * 1024 + e->threads;
-    if (e->auto_key == key) return e->auto_first;
-    e->auto_key = key;
-    e->auto_first = ens_first_extra_auto(e);
-    return e->auto_first;
-}
-
-static int ens_first_extra_auto(const slam_ens_t *e) {
-    const int full = ens_ctas_per_sm(e, e->extra);
+    const int full = ens_tier(e, e->extra).occ;
     int best = e->extra, best_occ = full;
     for (int x = e->extra - 1; x >= 0; x--) {
-        const int occ = ens_ctas_per_sm(e, x);
+        const int occ = ens_tier(e, x).occ;
         if (occ > best_occ) { best = x; best_occ = occ; }
     }
     int sms = 0;
@@ -1203,83 +1299,218 @@ static int ens_first_extra_auto(const slam_ens_t *e) {
     return best;
 }
 
+// builds the tier list and (re)allocates what depends on the output layout
+static int ens_prepare(slam_ens_t *e) {
+    if (!e->dirty) return SLAM_OK;
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    int max_optin = 0;
+    cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, e->device);
+    e->tiers.clear();
+    const int x1 = ens_first_extra(e);
+    if (x1 < e->extra) e->tiers.push_back(ens_tier(e, x1));
+    e->tiers.push_back(ens_tier(e, e->extra));
+    if (e->growth >= 1) {
+        const int limit = e->max_shared_extra >= 0 ? e->max_shared_extra : 1 << 20;
+        int x2 = -1, x3 = -1;   // largest head-room with two CTAs per SM / that fits at all
+        bool two = true;        // occupancy only falls as x grows: stop asking once it is below two
+        for (int x = e->extra + 1; x <= limit; x++) {
+            const size_t smem = ens_smem_bytes(3 + 2 * (e->nl + x), ens_mmax(e));
+            if (smem > (size_t)max_optin || 3 + 2 * (e->nl + x) > 4080) break;
+            x3 = x;
+            if (two) {
+                if (ens_occ(e, smem) >= 2) x2 = x;
+                else two = false;
+            }
+        }
+        if (x2 > e->extra) e->tiers.push_back(ens_tier(e, x2));
+        if (x3 > e->extra && x3 > x2) e->tiers.push_back(ens_tier(e, x3));
+    }
+    for (const EnsTier &t : e->tiers)
+        if (t.occ < 1) {
+            slam_set_error("ensemble: no CTA of %zu bytes of shared memory fits an SM", t.smem);
+            return SLAM_ERR_CAPACITY;
+        }
+    // the opt-in limit of the kernels is the largest tier's
+    const int top = (int)e->tiers.back().smem;
+    CUDA_TRY(cudaFuncSetAttribute(k_ensemble<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, top));
+    CUDA_TRY(cudaFuncSetAttribute(k_ensemble<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, top));
+    CUDA_TRY(cudaFuncSetAttribute(k_ensemble<256, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, top));
+    CUDA_TRY(cudaFuncSetAttribute(k_ensemble<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)ens_fixed_bytes(ens_mmax(e))));
+    e->ocap = e->tiers.back().ncap;
+    cudaFree(e->d_final_x);
+    cudaFree(e->d_final_P);
+    e->d_final_x = e->d_final_P = nullptr;
+    CUDA_TRY(cudaMalloc(&e->d_final_x, sizeof(double) * (size_t)e->n_runs * e->ocap));
+    if (e->keep) CUDA_TRY(cudaMalloc(&e->d_final_P, sizeof(double) * (size_t)e->n_runs * e->ocap * e->ocap));
+    e->dirty = false;
+    e->ran = false;
+    return SLAM_OK;
+}
+
 static void ens_launch(const slam_ens_t *e, const EnsArgs &a, int grid, size_t smem) {
     switch (e->threads) {
-        case 64: k_ensemble<64><<<grid, 64, smem, e->stream>>>(a); break;
-        case 256: k_ensemble<256><<<grid, 256, smem, e->stream>>>(a); break;
-        default: k_ensemble<128><<<grid, 128, smem, e->stream>>>(a); break;
+        case 64: k_ensemble<64, false><<<grid, 64, smem, e->stream>>>(a); break;
+        case 256: k_ensemble<256, false><<<grid, 256, smem, e->stream>>>(a); break;
+        default: k_ensemble<128, false><<<grid, 128, smem, e->stream>>>(a); break;
     }
 }
 
-extern "C" int slam_ens_run(slam_ens_t *e) {
-    E_CHECK(e);
+static EnsArgs ens_args(const slam_ens_t *e) {
     EnsArgs a;
     a.n_runs = e->n_runs; a.nsteps = e->t.nsteps; a.nl = e->nl;
-    a.mmax = std::max(e->t.max_nz, 1);
+    a.mmax = ens_mmax(e);
     a.seed = e->seed; a.run0 = e->run0;
     a.nblocks = (int)e->t.blocks.size() / 4;
     a.gamma = e->d_gamma; a.blk = reinterpret_cast<const int4 *>(e->d_blk); a.z_true = e->d_ztrue + 3;
     a.ctrl_noise = e->d_ctrl; a.obs_noise = e->d_obs; a.obs_per_member = e->obs_per_member;
-    a.ocap = e->ncap;
+    a.ocap = e->ocap;
     a.final_x = e->d_final_x; a.n_final = e->d_n_final; a.status = e->d_status; a.steps_done = e->d_steps_done;
     a.tracks = e->keep ? e->d_tracks : nullptr;
     a.final_P = e->keep ? e->d_final_P : nullptr;
-    auto set_capacity = [&](int ncap) {
-        a.ncap = ncap;
-        a.ldw = ens_ru4(ncap);
-        a.npk = ens_pdoubles(ncap);
-        a.wdoubles = ens_wdoubles(ncap, a.mmax);
-    };
-    const int x1 = ens_first_extra(e);
-    if (x1 >= e->extra) {   // single pass
-        set_capacity(e->ncap);
-        a.over_list = a.over_count = nullptr;
-        a.redo_list = a.redo_count = nullptr;
-        ens_launch(e, a, e->n_runs, e->smem);
+    a.over_list = a.over_count = nullptr;
+    a.redo_list = a.redo_count = nullptr;
+    a.gstate = nullptr;
+    a.gstride = 0;
+    a.flops = e->d_flops;
+    return a;
+}
+static void ens_set_capacity(EnsArgs &a, int ncap) {
+    a.ncap = ncap;
+    a.ldw = ens_ru4(ncap);
+    a.npk = ens_pdoubles(ncap);
+    a.wdoubles = ens_wdoubles(ncap, a.mmax);
+}
+
+extern "C" int slam_ens_run(slam_ens_t *e) {
+    E_CHECK(e);
+    int rc = ens_prepare(e);
+    if (rc) return rc;
+    ens_free_rounds(e);
+    EnsArgs a = ens_args(e);
+    const int nt = (int)e->tiers.size();
+    const size_t lw = (size_t)e->n_runs + 1;
+    CUDA_TRY(cudaMemsetAsync(e->d_over, 0, sizeof(int) * ENS_MAX_LISTS * lw, e->stream));
+    for (int i = 0; i < nt; i++) {
+        ens_set_capacity(a, e->tiers[i].ncap);
+        int *prev = i ? e->d_over + (size_t)(i - 1) * lw : nullptr, *next = e->d_over + (size_t)i * lw;
+        a.redo_count = prev; a.redo_list = prev ? prev + 1 : nullptr;
+        const bool more = i + 1 < nt || e->growth == 2;    // someone will re-run what this launch cannot hold
+        a.over_count = more ? next : nullptr; a.over_list = more ? next + 1 : nullptr;
+        ens_launch(e, a, e->n_runs, e->tiers[i].smem);     // CTAs past the redo count exit at once
         e->launches++;
-        e->last_first_extra = -1;
-    } else {
-        const int ncap1 = 3 + 2 * (e->nl + x1);
-        CUDA_TRY(cudaMemsetAsync(e->d_over, 0, sizeof(int), e->stream));
-        set_capacity(ncap1);
-        a.over_count = e->d_over; a.over_list = e->d_over + 1;
-        a.redo_list = a.redo_count = nullptr;
-        ens_launch(e, a, e->n_runs, ens_smem_bytes(ncap1, a.mmax));
-        set_capacity(e->ncap);
-        a.over_list = a.over_count = nullptr;
-        a.redo_count = e->d_over; a.redo_list = e->d_over + 1;
-        ens_launch(e, a, e->n_runs, e->smem);   // CTAs past the count exit at once
-        e->launches += 2;
-        e->last_first_extra = x1;
     }
+    e->global_pending = true;   // the first sync reads the tiers' counts and, for growth == 2, runs the global rounds
     e->ran = true;
     CUDA_TRY(cudaGetLastError());
     return SLAM_OK;
 }
 
-// Head-room of the first pass: -1 = automatic, >= the full head-room = always a single pass.
+// Last resort of growth == 2: the members the largest shared-memory tier could not hold run with x, P and the
+// workspace in global memory, the capacity doubling per round up to the bound no run can exceed (every
+// observation of the run a new landmark).  Synchronous; called by the first sync after a run.
+static int ens_global_rounds(slam_ens_t *e) {
+    e->global_pending = false;
+    const int nt = (int)e->tiers.size();
+    const size_t lw = (size_t)e->n_runs + 1;
+    e->tier_members.assign(nt, 0);
+    std::vector<int> cnts(ENS_MAX_LISTS);
+    for (int i = 0; i < nt; i++) CUDA_TRY(cudaMemcpy(&cnts[i], e->d_over + (size_t)i * lw, sizeof(int), cudaMemcpyDeviceToHost));
+    e->tier_members[0] = e->n_runs;
+    for (int i = 1; i < nt; i++) e->tier_members[i] = cnts[i - 1];
+    if (e->growth != 2) return SLAM_OK;
+    int cur = nt - 1, spare = nt;   // ping-pong lists (at most four tiers of ENS_MAX_LISTS lists are in use)
+    int count = cnts[cur], cap = e->tiers.back().ncap;
+    const long long bound_ll = 3 + 2 * ((long long)e->nl + (long long)e->t.z_true.size() / 2);
+    const int bound = (int)std::min<long long>(bound_ll, 4080 - 1);   // the triangle table holds 255 blocks of 16 rows
+    const int mmax = ens_mmax(e);
+    while (count > 0 && cap < bound) {
+        const int ncap = (int)std::min<long long>(bound, 3 + 4 * (long long)((cap - 3) / 2));
+        EnsGlobalRound r;
+        r.ncap = ncap;
+        r.members.resize(count);
+        CUDA_TRY(cudaMemcpy(r.members.data(), e->d_over + (size_t)cur * lw + 1, sizeof(int) * count, cudaMemcpyDeviceToHost));
+        const size_t gstride = ens_state_doubles(ncap, mmax);
+        double *d_state = nullptr;
+        if (cudaMalloc(&d_state, sizeof(double) * gstride * count) != cudaSuccess ||
+            cudaMalloc(&r.d_x, sizeof(double) * (size_t)ncap * count) != cudaSuccess ||
+            (e->keep && cudaMalloc(&r.d_P, sizeof(double) * (size_t)ncap * ncap * count) != cudaSuccess)) {
+            cudaGetLastError();
+            cudaFree(d_state); cudaFree(r.d_x); cudaFree(r.d_P);
+            slam_set_error("ensemble: no device memory to re-run %d members with a capacity of %d states", count, ncap);
+            return SLAM_ERR_CUDA;
+        }
+        EnsArgs a = ens_args(e);
+        ens_set_capacity(a, ncap);
+        a.ocap = ncap;
+        a.final_x = r.d_x;
+        a.final_P = e->keep ? r.d_P : nullptr;
+        a.gstate = d_state;
+        a.gstride = gstride;
+        int *prev = e->d_over + (size_t)cur * lw, *next = e->d_over + (size_t)spare * lw;
+        CUDA_TRY(cudaMemsetAsync(next, 0, sizeof(int), e->stream));
+        a.redo_count = prev; a.redo_list = prev + 1;
+        a.over_count = next; a.over_list = next + 1;
+        k_ensemble<128, true><<<count, 128, ens_fixed_bytes(mmax), e->stream>>>(a);
+        e->launches++;
+        CUDA_TRY(cudaGetLastError());
+        CUDA_TRY(cudaStreamSynchronize(e->stream));
+        cudaFree(d_state);
+        e->tier_members.push_back(count);
+        e->grounds.push_back(std::move(r));
+        CUDA_TRY(cudaMemcpy(&count, next, sizeof(int), cudaMemcpyDeviceToHost));
+        std::swap(cur, spare);
+        cap = ncap;
+    }
+    return SLAM_OK;
+}
+
+// Head-room of the first pass: -1 = automatic, >= the base head-room = no separate first pass.
 extern "C" int slam_ens_set_first_pass_extra(slam_ens_t *e, int extra) {
     ARG_CHECK(e != nullptr, "NULL handle");
     ARG_CHECK(extra >= -1, "extra < -1");
     e->first_extra = extra;
+    e->dirty = true;
     return SLAM_OK;
 }
 
-// What the last slam_ens_run did: *first_extra = the first pass's head-room (-1: single pass),
-// *redone = members the second pass ran again.
+static int ens_finish(slam_ens_t *e) {
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    if (e->ran && e->global_pending) return ens_global_rounds(e);
+    return SLAM_OK;
+}
+
+// What the last slam_ens_run did: *first_extra = the first pass's head-room (-1: no separate first pass),
+// *redone = members the pass after it ran again.
 extern "C" int slam_ens_pass_info(slam_ens_t *e, int *first_extra, int *redone) {
     E_CHECK(e);
-    CUDA_TRY(cudaStreamSynchronize(e->stream));
-    int cnt = 0;
-    if (e->ran && e->last_first_extra >= 0) CUDA_TRY(cudaMemcpy(&cnt, e->d_over, sizeof(int), cudaMemcpyDeviceToHost));
-    if (first_extra) *first_extra = e->ran ? e->last_first_extra : -1;
-    if (redone) *redone = cnt;
+    int rc = ens_finish(e);
+    if (rc) return rc;
+    const bool two = e->ran && e->tiers.size() > 1 && e->tiers[0].extra < e->extra;
+    if (first_extra) *first_extra = two ? e->tiers[0].extra : -1;
+    if (redone) *redone = two && e->tier_members.size() > 1 ? e->tier_members[1] : 0;
     return SLAM_OK;
+}
+
+// Every launch of the last run, in order (shared-memory tiers, then global-memory rounds): its capacity in
+// states and the members it ran.  Returns the number of launches; fills at most `max` entries.
+extern "C" int slam_ens_tier_info(slam_ens_t *e, int *capacity, int *members, int max) {
+    E_CHECK(e);
+    int rc = ens_finish(e);
+    if (rc) return rc;
+    if (!e->ran) return 0;
+    const int nt = (int)e->tiers.size(), total = (int)e->tier_members.size();
+    for (int i = 0; i < total && i < max; i++) {
+        if (capacity) capacity[i] = i < nt ? e->tiers[i].ncap : e->grounds[i - nt].ncap;
+        if (members) members[i] = e->tier_members[i];
+    }
+    return total;
 }
 
 extern "C" int slam_ens_sync(slam_ens_t *e) {
     E_CHECK(e);
-    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    int rc = ens_finish(e);
+    if (rc) return rc;
     if (!e->ran) return 0;
     std::vector<int> st(e->n_runs);
     CUDA_TRY(cudaMemcpy(st.data(), e->d_status, sizeof(int) * e->n_runs, cudaMemcpyDeviceToHost));
@@ -1292,7 +1523,8 @@ extern "C" int slam_ens_sync(slam_ens_t *e) {
 // steps they ran), per_member[n_runs] (may be NULL).
 extern "C" int slam_ens_steps_done(slam_ens_t *e, long long *total, int *per_member) {
     E_CHECK(e);
-    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    int rc = ens_finish(e);
+    if (rc) return rc;
     std::vector<int> sd(e->n_runs, 0);
     if (e->ran) CUDA_TRY(cudaMemcpy(sd.data(), e->d_steps_done, sizeof(int) * e->n_runs, cudaMemcpyDeviceToHost));
     long long tot = 0;
@@ -1302,12 +1534,32 @@ extern "C" int slam_ens_steps_done(slam_ens_t *e, long long *total, int *per_mem
     return SLAM_OK;
 }
 
+// the global round (and the slot in it) that holds member's final state, or nullptr: the last round wins
+static const EnsGlobalRound *ens_find_round(const slam_ens_t *e, int member, int *slot) {
+    for (int r = (int)e->grounds.size() - 1; r >= 0; r--) {
+        const auto &mv = e->grounds[r].members;
+        for (size_t i = 0; i < mv.size(); i++)
+            if (mv[i] == member) {
+                *slot = (int)i;
+                return &e->grounds[r];
+            }
+    }
+    return nullptr;
+}
+
 extern "C" int slam_ens_get_results(slam_ens_t *e, double *final_pose, int *n_final, int *status) {
     E_CHECK(e);
-    CUDA_TRY(cudaStreamSynchronize(e->stream));
-    if (final_pose)
-        CUDA_TRY(cudaMemcpy2D(final_pose, sizeof(double) * 3, e->d_final_x, sizeof(double) * e->ncap,
+    int rc = ens_finish(e);
+    if (rc) return rc;
+    if (final_pose) {
+        ARG_CHECK(e->d_final_x != nullptr, "no run yet");
+        CUDA_TRY(cudaMemcpy2D(final_pose, sizeof(double) * 3, e->d_final_x, sizeof(double) * e->ocap,
                               sizeof(double) * 3, e->n_runs, cudaMemcpyDeviceToHost));
+        for (const auto &r : e->grounds)   // later rounds overwrite earlier ones
+            for (size_t i = 0; i < r.members.size(); i++)
+                CUDA_TRY(cudaMemcpy(final_pose + 3 * (size_t)r.members[i], r.d_x + i * (size_t)r.ncap, sizeof(double) * 3,
+                                    cudaMemcpyDeviceToHost));
+    }
     if (n_final) CUDA_TRY(cudaMemcpy(n_final, e->d_n_final, sizeof(int) * e->n_runs, cudaMemcpyDeviceToHost));
     if (status) CUDA_TRY(cudaMemcpy(status, e->d_status, sizeof(int) * e->n_runs, cudaMemcpyDeviceToHost));
     return SLAM_OK;
@@ -1317,24 +1569,35 @@ extern "C" int slam_ens_get_track(slam_ens_t *e, int member, double *track) {
     E_CHECK(e);
     ARG_CHECK(track && member >= 0 && member < e->n_runs, "bad argument");
     ARG_CHECK(e->keep && e->d_tracks, "tracks were not kept: call slam_ens_keep_tracks(e, 1) before the run");
-    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    int rc = ens_finish(e);
+    if (rc) return rc;
     CUDA_TRY(cudaMemcpy(track, e->d_tracks + (size_t)member * 3 * e->t.nsteps, sizeof(double) * 3 * e->t.nsteps,
                         cudaMemcpyDeviceToHost));
     return SLAM_OK;
 }
 
+// Final x (n_final) and P (n_final^2, ldp, full symmetric) of one member; returns n_final (x and P may both be
+// NULL to ask for the size first: the state of a member is not bounded by slam_ens_capacity() when growth > 0).
 extern "C" int slam_ens_get_state(slam_ens_t *e, int member, double *x, double *P, int ldp) {
     E_CHECK(e);
     ARG_CHECK(member >= 0 && member < e->n_runs, "bad member");
-    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    int rc = ens_finish(e);
+    if (rc) return rc;
+    ARG_CHECK(e->ran, "no run yet");
     int n = 0;
     CUDA_TRY(cudaMemcpy(&n, e->d_n_final + member, sizeof(int), cudaMemcpyDeviceToHost));
-    if (x) CUDA_TRY(cudaMemcpy(x, e->d_final_x + (size_t)member * e->ncap, sizeof(double) * n, cudaMemcpyDeviceToHost));
+    int slot = 0;
+    const EnsGlobalRound *r = ens_find_round(e, member, &slot);
+    const int cap = r ? r->ncap : e->ocap;
+    const double *sx = r ? r->d_x + (size_t)slot * cap : e->d_final_x + (size_t)member * cap;
+    const double *sP = r ? r->d_P : e->d_final_P;
+    if (x) CUDA_TRY(cudaMemcpy(x, sx, sizeof(double) * n, cudaMemcpyDeviceToHost));
     if (P) {
-        ARG_CHECK(e->keep && e->d_final_P, "covariances were not kept: call slam_ens_keep_tracks(e, 1) before the run");
+        ARG_CHECK(e->keep && sP, "covariances were not kept: call slam_ens_keep_tracks(e, 1) before the run");
         ARG_CHECK(ldp >= n, "ldp < n");
-        CUDA_TRY(cudaMemcpy2D(P, sizeof(double) * (size_t)ldp, e->d_final_P + (size_t)member * e->ncap * e->ncap,
-                              sizeof(double) * e->ncap, sizeof(double) * n, n, cudaMemcpyDeviceToHost));
+        sP += (size_t)(r ? slot : member) * cap * cap;
+        CUDA_TRY(cudaMemcpy2D(P, sizeof(double) * (size_t)ldp, sP, sizeof(double) * cap, sizeof(double) * n, n,
+                              cudaMemcpyDeviceToHost));
     }
     return n;
 }

@@ -188,6 +188,54 @@ extern "C" int slam_destroy(slam_t *h) {
     return SLAM_OK;
 }
 
+// Capacity growth.  The reference's state grows without bound (hcat / vcat per new landmark,
+// src/ekf.jl:108-109); a handle has a fixed capacity so that add_features is an in-place append.  A
+// host that cannot size the map up front calls this when slam_add_features reports SLAM_ERR_CAPACITY
+// (slamcuda/slam.py and julia/ekf-cuda.jl do): new arrays with the new leading dimension, one
+// device-to-device copy of x and of the live columns of P.  On failure the old state is untouched.
+extern "C" int slam_reserve(slam_t *h, int n_max_new) {
+    H_CHECK(h);
+    ARG_CHECK(n_max_new >= 3, "n_max must be >= 3");
+    if (n_max_new <= h->n_max) return SLAM_OK;
+    const size_t ld_new = (size_t)round_up(n_max_new, 16);
+    double *nx = nullptr, *nP = nullptr;
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (cudaMalloc(&nx, sizeof(double) * ld_new) != cudaSuccess ||
+        cudaMalloc(&nP, sizeof(double) * ld_new * (size_t)n_max_new) != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(nx);
+        slam_set_error("slam_reserve: no device memory for a capacity of %d states", n_max_new);
+        return SLAM_ERR_CUDA;
+    }
+    cudaError_t e = cudaMemsetAsync(nx, 0, sizeof(double) * ld_new, h->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(nx, h->d_x, sizeof(double) * h->n, cudaMemcpyDeviceToDevice, h->stream);
+    if (e == cudaSuccess)
+        e = cudaMemcpy2DAsync(nP, sizeof(double) * ld_new, h->d_P, sizeof(double) * h->ld, sizeof(double) * h->n, h->n,
+                              cudaMemcpyDeviceToDevice, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) {
+        cudaFree(nx);
+        cudaFree(nP);
+        slam_set_error("slam_reserve: copy failed: %s", cudaGetErrorString(e));
+        return SLAM_ERR_CUDA;
+    }
+    cudaFree(h->d_x);
+    cudaFree(h->d_P);
+    h->d_x = nx;
+    h->d_P = nP;
+    h->ld = ld_new;
+    h->n_max = n_max_new;   // the update workspace follows on the next update (ensure_update_ws keys on n_max)
+    return SLAM_OK;
+}
+
+extern "C" int slam_capacity(slam_t *h) {
+    if (!h) {
+        slam_set_error("slam_capacity: NULL handle");
+        return SLAM_ERR_ARG;
+    }
+    return h->n_max;
+}
+
 extern "C" int slam_n(slam_t *h) {
     if (!h) {
         slam_set_error("slam_n: NULL handle");
@@ -260,6 +308,7 @@ extern "C" int slam_set_state(slam_t *h, const double *x, const double *P, int n
         return SLAM_ERR_CAPACITY;
     }
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    CUDA_TRY(cudaMemsetAsync(h->d_gate_scratch, 0, 256, h->stream));   // K2's last-CTA ticket (robust to an aborted launch)
     CUDA_TRY(cudaMemcpyAsync(h->d_x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
     CUDA_TRY(cudaMemcpy2DAsync(h->d_P, sizeof(double) * h->ld, P, sizeof(double) * (size_t)ldp,
                                sizeof(double) * n, n, cudaMemcpyHostToDevice, h->stream));
@@ -595,6 +644,14 @@ k_innov_chol(const double *__restrict__ PHt, int npad, const double *__restrict_
     const int tid = threadIdx.x;
     __shared__ int s_fail;
     if (tid == 0) s_fail = 0;
+    // A latched error (a landmark id out of range found by K3 of THIS update, or an earlier failure nobody has
+    // read yet) turns the update into a no-op before anything is changed: C = 0 gives W1 = 0, x += 0, P -= 0.
+    // The reference throws before any mutation (BoundsError at src/ekf.jl:57, chol at :70).
+    if (*reinterpret_cast<volatile int *>(err) != 0) {
+        for (int idx = tid; idx < R * R; idx += K4_THREADS) C[idx] = 0.0;
+        for (int k = tid; k < R; k += K4_THREADS) u[k] = 0.0;
+        return;
+    }
     for (int idx = tid; idx < m * R; idx += K4_THREADS) {
         int o = idx / R, k = idx % R;
         const double *h = Hn + 10 * o;
@@ -728,6 +785,11 @@ k_innov_chol_wide(const double *__restrict__ PHt, int npad, const double *__rest
     const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
     __shared__ int s_fail;
     if (tid == 0) s_fail = 0;
+    if (*reinterpret_cast<volatile int *>(err) != 0) {   // latched error: no-op (see k_innov_chol)
+        for (int idx = tid; idx < R * R; idx += K4W_THREADS) C[idx] = 0.0;
+        for (int k = tid; k < R; k += K4W_THREADS) u[k] = 0.0;
+        return;
+    }
     for (int idx = tid; idx < m * R; idx += K4W_THREADS) {
         int o = idx / R, k = idx % R;
         const double *h = Hn + 10 * o;
@@ -1014,6 +1076,14 @@ extern "C" int slam_update(slam_t *h, const double *zf, int m, const double R[4]
         slam_set_error("slam_update: m = %d exceeds SLAM_MAX_OBS = %d", m, SLAM_MAX_OBS);
         return SLAM_ERR_CAPACITY;
     }
+    // the ids are host data here: refuse a bad one before anything is launched (the reference's
+    // BoundsError at src/ekf.jl:57 precedes every mutation)
+    const int Nf = (h->n - 3) / 2;
+    for (int o = 0; o < m; o++)
+        if (idf[o] < 1 || idf[o] > Nf) {
+            slam_set_error("slam_update: idf[%d] = %lld outside 1..%d", o, (long long)idf[o], Nf);
+            return SLAM_ERR_BAD_INDEX;
+        }
     double *hz = (double *)((char *)h->h_pin + 256);
     int64_t *hid = (int64_t *)(hz + 2 * m);       // packed behind zf: one H2D
     CUDA_TRY(cudaStreamSynchronize(h->stream));
@@ -1202,6 +1272,7 @@ extern "C" int slam_synth_state(slam_t *h, int n_landmarks, double side, uint64_
         slam_set_error("slam_synth_state: n = %d exceeds capacity n_max = %d", n, h->n_max);
         return SLAM_ERR_CAPACITY;
     }
+    CUDA_TRY(cudaMemsetAsync(h->d_gate_scratch, 0, 256, h->stream));
     int rc = synth_fill(h->d_x, h->d_P, h->ld, 0, n, n_landmarks, side, seed, h->stream, &h->launches);
     if (rc) return rc;
     h->n = n;

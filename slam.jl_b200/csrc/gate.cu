@@ -398,13 +398,15 @@ k_gate(const double *__restrict__ x, GateSrc src, int Ntot, const double *__rest
         int jj = 0;
         for (int blk = lane; blk < nblocks; blk += 32) {
             size_t slot = (size_t)blk * nz + i;
-            double nd2 = part_nd[slot];
-            int j2 = part_j[slot];
+            // other CTAs wrote these: read them at L2 (the threadFenceReduction pattern), never from a stale L1 line
+            double nd2 = __ldcg(part_nd + slot);
+            int j2 = __ldcg(part_j + slot);
+            const double ou1 = __ldcg(part_outer + slot);
             if (j2 != 0 && (jj == 0 || nd2 < b || (nd2 == b && j2 < jj))) {
                 b = nd2;
                 jj = j2;
             }
-            if (part_outer[slot] < ou) ou = part_outer[slot];
+            if (ou1 < ou) ou = ou1;
         }
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) {

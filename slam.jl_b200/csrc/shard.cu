@@ -882,6 +882,12 @@ extern "C" int slam_shard_update(slam_shard_t *s, const double *zf, int m, const
         slam_set_error("slam_shard_update: m = %d exceeds SLAM_MAX_OBS", m);
         return SLAM_ERR_CAPACITY;
     }
+    const int Nf = (s->n - 3) / 2;   // host ids: refuse a bad one before anything is launched (every rank alike)
+    for (int o = 0; o < m; o++)
+        if (idf[o] < 1 || idf[o] > Nf) {
+            slam_set_error("slam_shard_update: idf[%d] = %lld outside 1..%d", o, (long long)idf[o], Nf);
+            return SLAM_ERR_BAD_INDEX;
+        }
     double *hz = (double *)((char *)s->h_pin + 256);
     int64_t *hid = (int64_t *)(hz + 6 * SLAM_MAX_OBS);
     CUDA_TRY(cudaStreamSynchronize(s->stream));

@@ -67,8 +67,11 @@ I, D, U64, U32, I64 = C.c_int, C.c_double, C.c_uint64, C.c_uint32, C.c_int64
 _sig("slam_last_error", C.c_char_p)
 _sig("slam_version", C.c_char_p)
 _sig("slam_device_count", I)
+_sig("slam_fp64_peak", I, I, c_double_p, c_double_p)
 _sig("slam_create", I, I, I, C.POINTER(vp))
 _sig("slam_destroy", I, vp)
+_sig("slam_reserve", I, vp, I)
+_sig("slam_capacity", I, vp)
 _sig("slam_set_state", I, vp, c_double_p, c_double_p, I, I)
 _sig("slam_get_state", I, vp, c_double_p, c_double_p, I)
 _sig("slam_get_pose", I, vp, c_double_p)
@@ -100,6 +103,10 @@ _sig("slam_ens_destroy", I, vp)
 _sig("slam_ens_steps", I, vp, c_int_p, c_int_p)
 _sig("slam_ens_set_extra_landmarks", I, vp, I)
 _sig("slam_ens_capacity", I, vp)
+_sig("slam_ens_set_growth", I, vp, I)
+_sig("slam_ens_set_max_shared_extra", I, vp, I)
+_sig("slam_ens_tier_info", I, vp, c_int_p, c_int_p, I)
+_sig("slam_ens_count_flops", I, vp, I, c_double_p)
 _sig("slam_ens_set_threads", I, vp, I)
 _sig("slam_ens_set_first_pass_extra", I, vp, I)
 _sig("slam_ens_pass_info", I, vp, c_int_p, c_int_p)

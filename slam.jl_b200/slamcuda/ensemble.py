@@ -23,7 +23,7 @@ def member_range(total_runs: int, world: int, rank: int):
 class Ensemble:
     def __init__(self, waypoints, landmarks, n_runs: int, seed: int = 0, run0: int = 0, nlaps: int = 2,
                  device: int = 0, extra_landmarks: int | None = None, threads: int | None = None,
-                 first_pass_extra: int | None = None):
+                 first_pass_extra: int | None = None, growth: int | None = None, max_shared_extra: int | None = None):
         wp = np.ascontiguousarray(np.asarray(waypoints, dtype=np.float64).T).reshape(-1)   # 2 x nwp column-major
         lm = np.asarray(landmarks, dtype=np.float64).reshape(2, -1)
         lmf = np.ascontiguousarray(lm.T).reshape(-1)
@@ -40,11 +40,28 @@ class Ensemble:
             check(lib.slam_ens_set_threads(self.ptr, int(threads)))
         if first_pass_extra is not None:
             check(lib.slam_ens_set_first_pass_extra(self.ptr, int(first_pass_extra)))
+        if growth is not None:     # 2 (default): unbounded like the reference; 1: shared-memory tiers; 0: fixed capacity
+            check(lib.slam_ens_set_growth(self.ptr, int(growth)))
+        if max_shared_extra is not None:
+            check(lib.slam_ens_set_max_shared_extra(self.ptr, int(max_shared_extra)))
 
     @property
     def capacity(self) -> int:
-        """3 + 2*(landmarks + extra_landmarks): the largest state a member can hold."""
+        """3 + 2*(landmarks + extra_landmarks): the base capacity of a member (with growth > 0 a member that
+        outgrows it is re-run with more room, as the reference's state simply grows)."""
         return check(lib.slam_ens_capacity(self.ptr))
+
+    def count_flops(self, on: bool = True) -> float:
+        """Switches the kernel's tally of algorithmic FP64 operations on / off; returns the last run's total."""
+        tot = C.c_double(0.0)
+        check(lib.slam_ens_count_flops(self.ptr, int(on), C.byref(tot)))
+        return tot.value
+
+    def tier_info(self):
+        """[(capacity in states, members run), ...] for every launch of the last run, in order."""
+        caps, mem = (C.c_int * 32)(), (C.c_int * 32)()
+        n = check(lib.slam_ens_tier_info(self.ptr, caps, mem, 32))
+        return [(caps[i], mem[i]) for i in range(min(n, 32))]
 
     def pass_info(self):
         """(head-room of the last run's first pass or -1 for a single pass, members the second pass re-ran)."""
@@ -102,7 +119,7 @@ class Ensemble:
         return t.T.copy()
 
     def state(self, member: int, with_cov: bool = True):
-        cap = self.capacity
+        cap = check(lib.slam_ens_get_state(self.ptr, member, None, None, 0))   # n_final of this member
         x = np.empty(cap)
         P = np.empty((cap, cap), order="F") if with_cov else None
         n = check(lib.slam_ens_get_state(self.ptr, member, dptr(x), dptr(P) if with_cov else None, cap))

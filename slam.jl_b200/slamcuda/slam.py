@@ -66,13 +66,23 @@ def _mat2(M):
 
 
 class _Handle:
-    """Owns a slam_t*; grows capacity by re-creating the device state."""
+    """Owns a slam_t*.  The reference's state grows without bound (hcat / vcat, src/ekf.jl:108-109);
+    with grow=True (the default) add_features doubles the device capacity through slam_reserve when
+    the append would not fit, so a spurious landmark never aborts a resident run.  grow=False keeps
+    the capacity fixed (CapacityError), e.g. for maps sized to the GPU's memory."""
 
-    def __init__(self, device: int = 0, n_max: int = 256):
+    def __init__(self, device: int = 0, n_max: int = 256, grow: bool = True):
         self.device = device
-        self.n_max = n_max
+        self.grow = grow
         self.ptr = C.c_void_p()
         check(lib.slam_create(device, n_max, C.byref(self.ptr)))
+
+    @property
+    def n_max(self) -> int:
+        return check(lib.slam_capacity(self.ptr))
+
+    def reserve(self, n_max: int):
+        check(lib.slam_reserve(self.ptr, int(n_max)))
 
     def close(self):
         if self.ptr:
@@ -155,6 +165,9 @@ class _Handle:
     def add_features(self, zn, R):
         zc, k = _cols(zn)
         r = _mat2(R)
+        need = self.n + 2 * k
+        if self.grow and need > self.n_max:
+            self.reserve(max(need, 2 * self.n_max))
         check(lib.slam_add_features(self.ptr, dptr(zc), k, dptr(r)))
 
     def compute_association(self, z, R, idf):

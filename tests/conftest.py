@@ -60,3 +60,27 @@ def rel_err(a, b):
         return 0.0
     scale = max(float(np.max(np.abs(b))), 1e-300)
     return float(np.max(np.abs(a - b))) / scale
+
+
+def elem_err(x, P, xo, Po):
+    """Element-wise relative error with an absolute floor, the stricter reading of "within 1e-9 relative":
+    |a - b| <= tol * (|b| + sqrt(P_ii P_jj)) for every entry of P and tol * (|b| + sqrt(P_ii)) for x -- a small
+    cross-covariance is judged against the standard deviations it couples, not against the largest entry of
+    the matrix (which is what rel_err's max-norm does: with x ~ 5000 m it cannot see an error in a small entry)."""
+    x, P, xo, Po = (np.asarray(a, dtype=float) for a in (x, P, xo, Po))
+    if x.shape != xo.shape or P.shape != Po.shape:
+        return float("inf")
+    if x.size == 0:
+        return 0.0
+    dg = np.sqrt(np.abs(np.diag(Po)))
+    fx = np.abs(xo) + dg
+    fP = np.abs(Po) + np.outer(dg, dg)
+    ex = np.max(np.where(fx > 0, np.abs(x - xo) / np.where(fx > 0, fx, 1.0), np.abs(x - xo) * 1e300))
+    eP = np.max(np.where(fP > 0, np.abs(P - Po) / np.where(fP > 0, fP, 1.0), np.abs(P - Po) * 1e300))
+    return float(max(ex, eP))
+
+
+def state_err(x, P, xo, Po):
+    """The figure the parity gates use: the larger of the max-norm relative errors of x and P and elem_err."""
+    return max(rel_err(x, xo), rel_err(P, Po), elem_err(x, P, xo, Po))
+

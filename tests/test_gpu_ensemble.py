@@ -3,10 +3,12 @@
 (a) injected noise: member r gets the same numpy PCG64 normals as the numpy literal oracle's
     run r -> end-of-run trajectories within 1e-6, final state within 1e-6, identical map sizes;
 (b) Philox noise: against the oracle's C twin running the same counter-based generator.
-A member holds 3 + 2*(nl + extra) states (the reference's state grows without bound); members
-whose filter outgrows that (spurious landmarks the algorithm itself creates, diverged filters)
-stop with SLAM_ERR_CAPACITY exactly where the twin returns -2, and only the steps they ran are
-counted by steps_done()."""
+The reference's state grows without bound (hcat / vcat, src/ekf.jl:108-109).  A member CTA holds
+3 + 2*(nl + extra) states; by default (growth = 2) members whose filter outgrows that (spurious
+landmarks the algorithm itself creates, diverged filters) are re-run by further launches with more
+room -- larger shared-memory tiers, then global memory -- so every member completes, as in the
+reference.  With growth = 0 such a member stops with SLAM_ERR_CAPACITY exactly where the
+fixed-capacity twin returns -2, and only the steps it ran are counted by steps_done()."""
 import ctypes as C
 
 import numpy as np
@@ -20,11 +22,11 @@ pytestmark = pytest.mark.gpu
 TRACK_TOL = 1e-6
 
 
-@pytest.mark.parametrize("nl,nruns", [(10, 6), (35, 6)])
-def test_ensemble_injected_noise_vs_numpy_oracle(course1, nl, nruns):
+@pytest.mark.parametrize("nl,nruns,growth", [(10, 6, 0), (35, 6, 0), (35, 6, 2), (35, 6, 1)])
+def test_ensemble_injected_noise_vs_numpy_oracle(course1, nl, nruns, growth):
     from slamcuda.ensemble import Ensemble
     lm = ref.make_inputs(nl, 0, 0)[0]
-    ens = Ensemble(course1, lm, nruns)
+    ens = Ensemble(course1, lm, nruns, growth=growth)
     ctrl = np.zeros((nruns, 2, ens.nsteps))
     runs, obs_all = [], []
     for r in range(nruns):
@@ -42,6 +44,8 @@ def test_ensemble_injected_noise_vs_numpy_oracle(course1, nl, nruns):
     assert cap == 3 + 2 * (nl + 5)
     total, per = ens.steps_done()
     worst = 0.0
+    if growth:
+        cap = max(c for c, _m in ens.tier_info())   # the largest capacity any launch offered
     for r, rr in enumerate(runs):
         if len(rr["x"]) > cap:                      # the oracle's map outgrew the fixed capacity
             assert st[r] == -3 and per[r] < ens.nsteps, (r, st[r])
@@ -52,7 +56,10 @@ def test_ensemble_injected_noise_vs_numpy_oracle(course1, nl, nruns):
         x, P = ens.state(r)
         worst = max(worst, e, rel_err(x, rr["x"]), rel_err(P, rr["P"]))
         assert np.array_equal(pose[r], x[:3])
-    print(f"\n[ensemble nl={nl}] {nruns} members, {bad} stopped early, worst rel err {worst:.3e}")
+    print(f"\n[ensemble nl={nl} growth={growth}] {nruns} members, {bad} stopped early, launches (capacity, members) "
+          f"{ens.tier_info()}, worst rel err {worst:.3e}")
+    if growth:
+        assert bad == 0
     assert worst < TRACK_TOL
     assert bad == sum(len(rr["x"]) > cap for rr in runs)
     assert total == int(per.sum())
@@ -68,7 +75,7 @@ def test_ensemble_philox_vs_twin(course1, twin, extra, threads, first):
     nl, nruns, seed, run0 = 35, 48, 1234, 7
     lm = ref.make_inputs(nl, 0, 0)[0]
     ens = Ensemble(course1, lm, nruns, seed=seed, run0=run0, extra_landmarks=extra, threads=threads,
-                   first_pass_extra=first)
+                   first_pass_extra=first, growth=0)
     ens.keep_tracks(True)
     ens.run()
     bad = ens.sync()
@@ -130,9 +137,10 @@ def test_ensemble_full_size_is_batch_invariant(course1):
     pose, nf, st = big.results()
     fe, redone = big.pass_info()
     total, per = big.steps_done()
-    assert fe >= 0 and redone > 0, "the bench-size ensemble is expected to take two passes"
+    assert fe >= 0 and redone > 0, "the bench-size ensemble is expected to take more than one pass"
     assert total == int(per.sum()) and bad == int((st != 0).sum())
-    redo_members = np.flatnonzero((nf > 3 + 2 * (nl + fe)) | (st == -3))
+    assert bad == 0 and total == 8192 * big.nsteps        # growth: every member completes, as in the reference
+    redo_members = np.flatnonzero(nf > 3 + 2 * (nl + fe))
     assert len(redo_members) == redone
     # a window of ordinary members, plus members the second pass re-ran
     for start in (0, 4096, int(redo_members[0]), int(redo_members[-1])):
@@ -147,6 +155,63 @@ def test_ensemble_full_size_is_batch_invariant(course1):
         assert np.array_equal(nf2, nf[start:start + cnt]) and np.array_equal(st2, st[start:start + cnt])
         assert np.array_equal(per2, per[start:start + cnt])
         small.close()
-    print(f"\n[ensemble 8192] first pass extra {fe}, re-ran {redone}, stopped {bad}, "
-          f"{total} of {8192 * big.nsteps} filter-steps done")
+    print(f"\n[ensemble 8192] first pass extra {fe}, re-ran {redone}, stopped {bad}, launches (capacity, members) "
+          f"{big.tier_info()}, {total} of {8192 * big.nsteps} filter-steps done")
     big.close()
+
+
+def test_ensemble_unbounded_growth_vs_twin(course1, twin):
+    """The reference's map grows without bound (src/ekf.jl:108-109, src/data-association.jl:45-47).  2048 members of
+    bench.py's ensemble with the default growth: no member stops, and every member -- the ~3 % whose filter
+    diverges and roughly doubles its map included -- ends with the twin's map size and pose (the twin runs with
+    room for 200 extra landmarks, i.e. unbounded in practice).  Then the same run ids with the shared-memory
+    tiers capped at the base capacity, which sends the outgrown members through the global-memory rounds:
+    bit-equal results (same arithmetic, different memory)."""
+    from slamcuda.ensemble import Ensemble
+    nl, nruns, seed, run0 = 35, 2048, 2, 0
+    lm = np.random.Generator(np.random.PCG64(0)).integers(5, 96, size=(2, nl)).astype(float)
+    ens = Ensemble(course1, lm, nruns, seed=seed, run0=run0)
+    ens.run()
+    bad = ens.sync()
+    pose, nf, st = ens.results()
+    total, per = ens.steps_done()
+    tiers = ens.tier_info()
+    assert bad == 0 and np.all(st == 0) and total == nruns * ens.nsteps and np.all(per == ens.nsteps)
+    ms = ens.nsteps
+    wp = np.ascontiguousarray(course1.T).reshape(-1)
+    lmf = np.ascontiguousarray(lm.T).reshape(-1)
+    fp = np.zeros(3 * nruns)
+    nfin = np.zeros(nruns, dtype=np.int32)
+    twin.twin_ensemble_cap.restype = C.c_int
+    twin.twin_ensemble_cap.argtypes = twin.twin_ensemble.argtypes + [C.c_int]
+    import os
+    tbad = twin.twin_ensemble_cap(d(wp), course1.shape[1], d(lmf), nl, seed, run0, nruns, 2, ms, d(fp), None,
+                                  nfin.ctypes.data_as(C.POINTER(C.c_int)), os.cpu_count() or 8, 200)
+    assert tbad == 0
+    tp = fp.reshape(nruns, 3)
+    grown = np.flatnonzero(nfin > ens.capacity)
+    same_n = nf == nfin
+    err = np.max(np.abs(pose - tp), axis=1) / np.max(np.abs(tp))
+    off = np.flatnonzero(~same_n | (err > TRACK_TOL))
+    print(f"\n[ensemble growth] {nruns} members, launches (capacity, members) {tiers}; {len(grown)} members outgrew "
+          f"{ens.capacity} states (largest map {nfin.max()}); {len(off)} differ from the twin; worst pose rel err "
+          f"among the rest {err[same_n].max():.2e}")
+    assert len(grown) > 10 and nfin.max() > ens.capacity + 20
+    # a diverged filter is chaotic: a decision within rounding of a gate may flip between libm implementations
+    assert len(off) <= max(2, nruns // 500), off[:20]
+    assert len(tiers) >= 3 and tiers[2][1] == int(np.sum(nf > tiers[1][0]))
+    ens.close()
+    # the global-memory rounds
+    g = Ensemble(course1, lm, nruns, seed=seed, run0=run0, max_shared_extra=5)
+    g.keep_tracks(False)
+    g.run()
+    assert g.sync() == 0
+    pose_g, nf_g, st_g = g.results()
+    tg = g.tier_info()
+    print(f"[ensemble growth, global-memory rounds] launches (capacity, members) {tg}")
+    assert len(tg) >= 3 and tg[-1][0] > 3 + 2 * (nl + 5) and tg[2][1] == len(grown)
+    assert np.array_equal(nf_g, nf) and np.array_equal(pose_g, pose) and np.all(st_g == 0)
+    r = int(grown[0])
+    xg, _ = g.state(r, with_cov=False)
+    assert len(xg) == nf[r] and np.array_equal(xg[:3], pose[r])
+    g.close()

@@ -9,7 +9,7 @@ import math
 import numpy as np
 import pytest
 
-from conftest import rel_err
+from conftest import rel_err, state_err
 from oracle import slam_ref as ref
 
 pytestmark = pytest.mark.gpu
@@ -60,7 +60,7 @@ def test_step_reseeded_parity(sc, traces, nl):
             st = sc.EKFSlamState(e["x"], e["P"])
             veh.measured_gamma, veh.measured_speed = e["g"], e["v"]
             x, P = sc.predict(st, veh, Q, dt)
-            worst["predict"] = max(worst["predict"], rel_err(x, e["x_out"]), rel_err(P, e["P_out"]))
+            worst["predict"] = max(worst["predict"], state_err(x, P, e["x_out"], e["P_out"]))
         else:
             n_obs += 1
             st = sc.EKFSlamState(e["x"], e["P"])
@@ -69,11 +69,11 @@ def test_step_reseeded_parity(sc, traces, nl):
             assert np.array_equal(zf, e["zf"]) and np.array_equal(zn, e["zn"])
             min_margin = min(min_margin, e["margin"])
             x, P = sc.update(st, e["zf"], R, e["idf"])
-            worst["update"] = max(worst["update"], rel_err(x, e["x_upd"]), rel_err(P, e["P_upd"]))
+            worst["update"] = max(worst["update"], state_err(x, P, e["x_upd"], e["P_upd"]))
             st2 = sc.EKFSlamState(e["x_upd"], e["P_upd"])
             x, P = sc.add_features(st2, e["zn"], R)
             assert len(x) == len(e["x_out"])
-            worst["add"] = max(worst["add"], rel_err(x, e["x_out"]), rel_err(P, e["P_out"]))
+            worst["add"] = max(worst["add"], state_err(x, P, e["x_out"], e["P_out"]))
     print(f"\n[parity nl={nl}] worst rel err {worst}; {n_obs} observation steps; "
           f"smallest association margin {min_margin:.3e}")
     assert n_obs > 300
@@ -153,11 +153,151 @@ def test_edge_cases(sc):
         sc.update(sc.EKFSlamState(x, -P), zdup[:, :1], -R, np.array([2]))
     # capacity
     from slamcuda.slam import _Handle
-    h = _Handle(0, 5)
+    h = _Handle(0, 5, grow=False)
     h.set_state(x[:5], P[:5, :5])
     with pytest.raises(sc.CapacityError):
         h.add_features(np.array([[5.0], [0.1]]), R)
     h.close()
+
+
+def test_cuda_hand_derived_cases(sc):
+    """The CUDA path against closed-form expected values worked out on paper (tests/handcases.py), independent of
+    the oracle: predict, predict_observation, compute_association, the matched / dropped / new branches of
+    associate, the strict-< tie (lowest id wins), update, add_features (second new landmark sees the first)."""
+    import handcases as hc
+    c = hc.case_predict()
+    veh = sc.Vehicle(wheelbase=c["w"], measured_gamma=c["g"], measured_speed=c["v"])
+    x, P = sc.predict(sc.EKFSlamState(c["x"], c["P"]), veh, c["Q"], c["dt"])
+    assert np.allclose(x, c["x_out"], rtol=0, atol=1e-15) and np.allclose(P, c["P_out"], rtol=1e-14, atol=1e-18)
+    c = hc.case_observe()
+    zp, H = sc.predict_observation(c["x"], c["idf"])
+    assert np.allclose(zp, c["zp"], rtol=0, atol=1e-15) and np.allclose(H, c["H"], rtol=0, atol=1e-16)
+    nis, nd = sc.compute_association(c["x"], c["P"], c["z"], c["R"], c["idf"])
+    assert abs(nis - c["nis"]) < 1e-13 and abs(nd - c["nd"]) < 1e-13
+    for c in (hc.case_associate(), hc.case_tie()):
+        for pregate in (True, False):
+            st = sc.DeviceEKFSlamState(c["x"], c["P"], n_max=len(c["x"]))
+            st.h.set_pregate(pregate)
+            zf, idf, zn = sc.associate(st, c["z"], c["R"], c["gate1"], c["gate2"])
+            st.h.close()
+            assert list(idf.reshape(-1)) == c["idf"] and np.array_equal(zf, c["zf"]) and np.array_equal(zn, c["zn"])
+    c = hc.case_update()
+    x, P = sc.update(sc.EKFSlamState(c["x"], c["P"]), c["z"], c["R"], np.array(c["idf"]))
+    assert np.allclose(x, c["x_out"], rtol=0, atol=1e-15) and np.allclose(P, c["P_out"], rtol=0, atol=1e-16)
+    assert np.array_equal(P[5:, 5:], c["P"][5:, 5:]) and np.array_equal(x[5:], c["x"][5:])   # landmark 2 is uncorrelated
+    c = hc.case_add_features()
+    x, P = sc.add_features(sc.EKFSlamState(c["x"], c["P"]), c["z"], c["R"])
+    assert np.allclose(x, c["x_out"], rtol=0, atol=1e-15) and np.allclose(P, c["P_out"], rtol=0, atol=1e-16)
+
+
+@pytest.mark.parametrize("n", [3, 5, 23])
+def test_cuda_within_1e12_of_the_mpmath_restatement(sc, n):
+    """The 50-digit mpmath restatement of the reference's text (oracle/slam_mp.py, fixture tests/golden/kat_mp.npz
+    generated by tests/golden/make_golden_mp.py) pins the CUDA path to that text, not to the float64 oracle: every
+    function within 1e-12 (max-norm relative and element-wise), association ids equal."""
+    from pathlib import Path
+    gold = Path(__file__).resolve().parent / "golden"
+    kat, mpk = np.load(gold / "kat.npz"), np.load(gold / "kat_mp.npz")
+    k = ref.sim_constants()
+    Q, R, dt = k["Q"], k["R"], k["dt"]
+    t = f"n{n}"
+    x, P, z = kat[f"{t}_x"], kat[f"{t}_P"], kat[f"{t}_z"]
+    TOL = 1e-12
+    veh = sc.Vehicle(wheelbase=4.0, measured_gamma=0.07, measured_speed=7.6)
+    xp, Pp = sc.predict(sc.EKFSlamState(x, P), veh, Q, dt)
+    e_pred = state_err(xp, Pp, mpk[f"{t}_predict_x"], mpk[f"{t}_predict_P"])
+    zf, idf, zn = sc.associate(sc.EKFSlamState(x, P), z, R, k["gate1"], k["gate2"])
+    assert np.array_equal(idf.reshape(-1), mpk[f"{t}_idf"])
+    assert np.array_equal(zf, z[:, mpk[f"{t}_zf_cols"]]) and np.array_equal(zn, z[:, mpk[f"{t}_zn_cols"]])
+    xu, Pu = sc.update(sc.EKFSlamState(x, P), zf, R, idf)
+    e_upd = state_err(xu, Pu, mpk[f"{t}_update_x"].reshape(-1), mpk[f"{t}_update_P"])
+    xa, Pa = sc.add_features(sc.EKFSlamState(kat[f"{t}_update_x"], kat[f"{t}_update_P"]), zn, R)
+    e_add = state_err(xa, Pa, mpk[f"{t}_add_x"].reshape(-1), mpk[f"{t}_add_P"])
+    print(f"\n[cuda vs mpmath n={n}] predict {e_pred:.2e}  update {e_upd:.2e}  add_features {e_add:.2e}")
+    assert max(e_pred, e_upd, e_add) < TOL
+    if n > 3:
+        nf = (n - 3) // 2
+        for j in range(1, nf + 1):
+            nis, nd = sc.compute_association(x, P, z[:, 0], R, j)
+            g = mpk[f"{t}_nis_nd"][j - 1]
+            assert abs(nis - g[0]) <= 1e-11 * max(1.0, abs(g[0])) and abs(nd - g[1]) <= 1e-11 * max(1.0, abs(g[1]))
+        zp, H = sc.predict_observation(x, nf)
+        assert rel_err(zp, mpk[f"{t}_obs_z"]) < 1e-14 and rel_err(H, mpk[f"{t}_obs_H"]) < 1e-14
+
+
+def test_bad_landmark_id_leaves_the_state_untouched(sc):
+    """The reference throws BoundsError (src/ekf.jl:57) before any mutation.  Host ids are refused before any
+    launch; device-resident ids are caught by K3 and turn K4 / K5 / K6 into a bit-exact no-op, the error is
+    returned by the next slam_sync(), and a latched error keeps later resident updates no-ops until it is read."""
+    import torch
+    from slamcuda._ffi import lib, dptr
+    from slamcuda.slam import _Handle, _mat2
+    k = ref.sim_constants()
+    R = k["R"]
+    rng = np.random.default_rng(8)
+    for nf, m in ((40, 3), (900, 20)):          # both K4 kernels (rank <= 32 and wide)
+        x, P = _random_state(rng, nf)
+        h = _Handle(0, 3 + 2 * nf)
+        h.set_state(x, P)
+        x0, P0 = h.get_state()
+        z = np.zeros((2, m))
+        ids = rng.choice(nf, m, replace=False) + 1
+        for c, idf in enumerate(ids):
+            zp, _ = ref.predict_observation(x, int(idf))
+            z[:, c] = zp + rng.normal(0, [0.05, 0.005])
+        bad = ids.copy()
+        bad[m // 2] = nf + 7
+        with pytest.raises(sc.BadIndex):
+            h.update(z, R, bad)
+        x1, P1 = h.get_state()
+        assert np.array_equal(x1, x0) and np.array_equal(P1, P0)
+        # resident entry point: ids live on the device
+        d_zf = torch.tensor(np.ascontiguousarray(z.T).reshape(-1), device="cuda:0")
+        d_bad = torch.tensor(bad, device="cuda:0")
+        d_ok = torch.tensor(ids, device="cuda:0")
+        r = _mat2(R)
+        assert lib.slam_update_resident(h.ptr, d_zf.data_ptr(), m, dptr(r), d_bad.data_ptr()) == 0
+        assert lib.slam_update_resident(h.ptr, d_zf.data_ptr(), m, dptr(r), d_ok.data_ptr()) == 0   # still latched: no-op
+        with pytest.raises(sc.BadIndex):
+            h.sync()
+        x1, P1 = h.get_state()
+        assert np.array_equal(x1, x0) and np.array_equal(P1, P0)
+        # the error is cleared: the same update now runs and matches the oracle
+        assert lib.slam_update_resident(h.ptr, d_zf.data_ptr(), m, dptr(r), d_ok.data_ptr()) == 0
+        h.sync()
+        x2, P2 = h.get_state()
+        xo, Po = ref.update(x, P, z, R, ids)
+        assert rel_err(x2, xo) < STEP_TOL and rel_err(P2, Po) < STEP_TOL
+        h.close()
+
+
+def test_capacity_growth_matches_the_reference(sc):
+    """The reference's state grows without bound (hcat / vcat, src/ekf.jl:108-109).  A resident state created
+    with too little capacity grows through slam_reserve (device-to-device copy, new leading dimension) and the
+    result equals the oracle's; the pre-gate bound and later updates survive the move."""
+    from slamcuda.slam import _Handle
+    k = ref.sim_constants()
+    R, Q = k["R"], k["Q"]
+    rng = np.random.default_rng(9)
+    x, P = _random_state(rng, 6)
+    st = sc.DeviceEKFSlamState(x, P, n_max=len(x))          # no head-room at all
+    zn = np.array([rng.uniform(5, 25, 7), rng.uniform(-1, 1, 7)])
+    st.x, st.cov = sc.add_features(st, zn, R)
+    xo, Po = ref.add_features(x, P, zn, R)
+    assert st.h.n == len(xo) and st.h.n_max >= len(xo)
+    xg, Pg = st.h.get_state()
+    assert rel_err(xg, xo) < STEP_TOL and rel_err(Pg, Po) < STEP_TOL
+    assert st.h.gate_stats()[2] == np.max(np.diag(Pg)[3:])
+    zp, _ = ref.predict_observation(xo, 9)
+    z = (zp + [0.03, 0.004]).reshape(2, 1)
+    zf, idf, zn2 = sc.associate(st, z, R, 4.0, 25.0)
+    zf_o, idf_o, zn_o = ref.associate(xo, Po, z, R, 4.0, 25.0)
+    assert np.array_equal(idf.reshape(-1), idf_o)
+    st.x, st.cov = sc.update(st, zf, R, idf)
+    xo, Po = ref.update(xo, Po, zf_o, R, idf_o)
+    xg, Pg = st.h.get_state()
+    assert rel_err(xg, xo) < STEP_TOL and rel_err(Pg, Po) < STEP_TOL
+    st.h.close()
 
 
 def test_observation_model_and_association_values(sc):
@@ -224,8 +364,9 @@ def test_update_large_parity(sc, nf, m):
     h.update(z, R, ids)
     xg, Pg = h.get_state()
     h.close()
-    print(f"\n[update n={len(x)} m={m}] x rel {rel_err(xg, xo):.2e}  P rel {rel_err(Pg, Po):.2e}")
-    assert rel_err(xg, xo) < STEP_TOL and rel_err(Pg, Po) < STEP_TOL
+    print(f"\n[update n={len(x)} m={m}] x rel {rel_err(xg, xo):.2e}  P rel {rel_err(Pg, Po):.2e}  "
+          f"element-wise {state_err(xg, Pg, xo, Po):.2e}")
+    assert state_err(xg, Pg, xo, Po) < STEP_TOL
     assert np.array_equal(Pg, Pg.T)
 
 
@@ -303,7 +444,7 @@ def test_update_rank_sweep_dmma(sc, nf, m):
           f"P {rel_err(out[2][1], Po):.2e}")
     assert np.array_equal(out[1][0], out[2][0])          # x does not depend on the downdate kernel
     assert e_fd < 1e-12
-    assert rel_err(out[2][0], xo) < STEP_TOL and rel_err(out[2][1], Po) < STEP_TOL
+    assert state_err(out[2][0], out[2][1], xo, Po) < STEP_TOL and state_err(out[1][0], out[1][1], xo, Po) < STEP_TOL
     assert np.array_equal(out[2][1], out[2][1].T)
 
 
@@ -380,9 +521,9 @@ def test_full_size_properties(sc, nl):
     h.update(zf, R, idf)
     x1 = h.get_x()
     P1 = _gather(h, segs)
-    ex, eP = rel_err(x1[index], xo), rel_err(P1, Po)
-    print(f"\n[full size n={n} m={m}] sampled {len(index)} states: x rel {ex:.2e}  P rel {eP:.2e}")
-    assert ex < STEP_TOL and eP < STEP_TOL
+    ex, eP, ee = rel_err(x1[index], xo), rel_err(P1, Po), state_err(x1[index], P1, xo, Po)
+    print(f"\n[full size n={n} m={m}] sampled {len(index)} states: x rel {ex:.2e}  P rel {eP:.2e}  element-wise {ee:.2e}")
+    assert ex < STEP_TOL and eP < STEP_TOL and ee < STEP_TOL
     assert np.array_equal(P1, P1.T)
     d0, d1 = np.diag(P0), np.diag(P1)
     assert np.all(d1 <= d0 * (1 + 1e-12)) and d1.sum() < d0.sum()   # P - W S W' never grows a variance
