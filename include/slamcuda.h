@@ -148,8 +148,10 @@ int slam_update_resident(slam_t *h, const double *d_zf, int m, const double R[4]
 int slam_sync(slam_t *h);
 /* The CUDA stream (cudaStream_t) all work of this handle is issued on. */
 void *slam_stream(slam_t *h);
-/* Downdate kernel choice for update: 0 = auto (FMA kernel below the rank threshold, DMMA
- * tiles above), 1 = force FP64 FMA kernel, 2 = force FP64 DMMA tensor-core kernel. */
+/* Downdate kernel choice for update: 0 = auto (FMA kernel up to 8 ranks, streaming DMMA kernel for 12..64
+ * ranks, tiled DMMA kernel above), 1 = force the FP64 FMA kernel (up to 32 ranks per pass), 2 = force the tiled
+ * FP64 DMMA tensor-core kernel (where its 32-wide chunk layout applies), 3 = force the streaming DMMA kernel
+ * (12..64 ranks).  A forced variant that does not apply to the rank falls through to the automatic choice. */
 int slam_set_downdate_variant(slam_t *h, int variant);
 /* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
 long long slam_launch_count(slam_t *h);

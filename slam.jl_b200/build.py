@@ -33,6 +33,7 @@ PER_FILE = {
     "downdate.cu": [],
     "downdate_dmma.cu": [],
     "probe.cu": [],
+    "downdate_stream.cu": [],
 }
 
 

@@ -151,3 +151,31 @@ __device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gmem_src, u
         "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
         : "memory");
 }
+
+// ---------------------------------------------------------------------------------------
+// Programmatic dependent launch (PDL).  The kernels of one update form a chain on one stream
+// (K3+K4 -> K5 -> K6); launched with the programmatic-stream-serialization attribute, a kernel is
+// scheduled while its predecessor drains, runs its own prologue (index arithmetic, mbarrier
+// init) and blocks in pdl_wait() until the predecessor has completed and flushed its writes.
+// pdl_wait() is a no-op for a kernel launched the ordinary way.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+#endif
+

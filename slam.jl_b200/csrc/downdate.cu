@@ -61,7 +61,7 @@ __device__ __forceinline__ void fma_store_batch(double (&a)[U][ROWS], const doub
                                                 const double *sWj, double *col, size_t ld) {
 #pragma unroll
     for (int u = 0; u < U; u++) {
-        const double2 *wj = reinterpret_cast<const double2 *>(sWj + (size_t)u * RC);
+        const double2 *wj = reinterpret_cast<const double2 *>(sWj + (size_t)u * (RC + W1_PAD));
 #pragma unroll
         for (int k = 0; k < RC / 2; k++) {
             double2 w = wj[k];
@@ -101,7 +101,7 @@ __device__ __forceinline__ void prefetch_batch(const double *warp_col, size_t ld
 
 // Rows [r0, r1) of the upper triangle; element (i, j) lives at Pb[(i - r0) + j*ldb].
 // The single-filter path passes r0 = 0, r1 = n, Pb = P.
-// W1r: [n_pad][RC] row-major (column-side rows, staged by one bulk copy per tile);
+// W1r: [n_pad][RC + W1_PAD] row-major (column-side rows, staged by one bulk copy per tile);
 // W1t: [RC][n_pad] rank-major (row-side values, coalesced register loads).
 // PIPE = 1 adds a two-deep register pipeline on top of the L2 prefetch: the loads of batch b+1 are issued before
 // the FMAs of batch b.  It pays where the kernel is held at two CTAs per SM by its W1 rows anyway (RC >= 24:
@@ -117,16 +117,19 @@ k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n
     const int jend = min(j0 + DD_BJ, n);
     if (i0 >= jend) return;  // tile entirely below the diagonal
 
-    __shared__ __align__(128) double sW[DD_BJ * RC];
+    constexpr int LDK = RC + W1_PAD;
+    __shared__ __align__(128) double sW[DD_BJ * LDK];
     __shared__ __align__(8) uint64_t bar;
     if (threadIdx.x == 0) {
         mbar_init(&bar, 1);
         mbar_fence_init();
     }
     __syncthreads();
+    pdl_wait();                                       // W1 (K5) and P (the previous update) are complete
+    pdl_launch_dependents();
     if (threadIdx.x == 0) {
-        mbar_expect_tx(&bar, DD_BJ * RC * 8);
-        bulk_g2s(sW, W1r + (size_t)j0 * RC, DD_BJ * RC * 8, &bar);
+        mbar_expect_tx(&bar, DD_BJ * LDK * 8);
+        bulk_g2s(sW, W1r + (size_t)j0 * LDK, DD_BJ * LDK * 8, &bar);
     }
 
     const int lane = threadIdx.x & 31;
@@ -163,7 +166,7 @@ k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n
     mbar_wait(&bar, 0);
 
     double *col = Pb + (size_t)(i - r0) + (size_t)jstart * ldb;
-    const double *sWj = sW + (size_t)(jstart - j0) * RC;
+    const double *sWj = sW + (size_t)(jstart - j0) * LDK;
     const bool row_ok = i < r1;   // rows past the block end (ragged last warp) do nothing
     if (PIPE) {
         double a0[U][ROWS], a1[U][ROWS];
@@ -177,14 +180,14 @@ k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n
                 if (b + 1 < nfull) load_batch<RC, ROWS, U>(a1, col + (size_t)U * ldb, ldb);
                 fma_store_batch<RC, ROWS, U>(a0, wi, sWj, col, ldb);
                 if (b + 2 < nfull) load_batch<RC, ROWS, U>(a0, col + (size_t)(2 * U) * ldb, ldb);
-                if (b + 1 < nfull) fma_store_batch<RC, ROWS, U>(a1, wi, sWj + (size_t)U * RC, col + (size_t)U * ldb, ldb);
+                if (b + 1 < nfull) fma_store_batch<RC, ROWS, U>(a1, wi, sWj + (size_t)U * LDK, col + (size_t)U * ldb, ldb);
             }
             col += (size_t)(2 * U) * ldb;
-            sWj += (size_t)(2 * U) * RC;
+            sWj += (size_t)(2 * U) * LDK;
         }
         if (nfull & 1) {   // the loop stepped one batch past the end
             col -= (size_t)U * ldb;
-            sWj -= (size_t)U * RC;
+            sWj -= (size_t)U * LDK;
         }
     } else {
         for (int b = 0; b < nfull; b++) {
@@ -195,7 +198,7 @@ k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n
                 fma_store_batch<RC, ROWS, U>(a, wi, sWj, col, ldb);
             }
             col += (size_t)U * ldb;
-            sWj += (size_t)U * RC;
+            sWj += (size_t)U * LDK;
         }
     }
     if (row_ok) {
@@ -208,7 +211,7 @@ k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n
                 col[r] = acc;
             }
             col += ldb;
-            sWj += RC;
+            sWj += LDK;
         }
     }
 }
@@ -234,7 +237,7 @@ void launch_one(double *Pb, size_t ldb, int r0, int r1, int n, int n_pad, const 
     constexpr int BI = DD_THREADS * ROWS;
     constexpr int DD_BJ = DdBj<RC>::value;
     dim3 grid((r1 - r0 + BI - 1) / BI, (n + DD_BJ - 1) / DD_BJ);
-    k_downdate_fma<RC, ROWS, U, PD, PIPE><<<grid, DD_THREADS, 0, s>>>(Pb, ldb, r0, r1, n, n_pad, W1r, W1t);
+    launch_pdl(k_downdate_fma<RC, ROWS, U, PD, PIPE>, grid, dim3(DD_THREADS), 0, s, Pb, ldb, r0, r1, n, n_pad, W1r, W1t);
 }
 
 template <int RC>
@@ -264,12 +267,16 @@ int downdate_chunk_width(int R) {
     if (R <= 12) return 12;
     if (R <= 16) return 16;
     if (R <= 24) return 24;
-    return 32;
+    if (R <= 32) return 32;
+    if (R <= 40) return 40;    // 33..64 ranks: one chunk, one pass of the streaming DMMA kernel
+    if (R <= 48) return 48;
+    if (R <= 56) return 56;
+    if (R <= 64) return 64;
+    return 32;                 // above: 32-wide chunks for the tile DMMA kernel (all chunks in one pass)
 }
 
-// W1c: per rank chunk c (RC columns, zero padded) two copies of W1's chunk:
-//   W1c + c*2*n_pad*RC              : [n_pad][RC] row-major
-//   W1c + c*2*n_pad*RC + n_pad*RC   : [RC][n_pad] rank-major
+// W1c: per rank chunk c (RC columns, zero padded) two copies of W1's chunk (layout: kernels.cuh):
+//   [n_pad][RC + W1_PAD] row-major, then [RC][n_pad] rank-major.
 // n_pad is a multiple of DD_ROW_PAD and rows >= n are zero.
 int launch_downdate_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad,
                          int R, int variant, cudaStream_t s, long long *launches) {
@@ -278,14 +285,24 @@ int launch_downdate_rows(double *Pb, size_t ldb, int r0, int r1, int n, const do
     // (measured cross-over, profiles/r1_k6_dmma.md), the FMA kernel below it; 1 / 2 force one.
     int min_rank = 33;   // above one FMA pass (32 ranks): 19-30 TFLOP/s DMMA vs 13-18 TFLOP/s FMA
     if (const char *e = getenv("SLAM_K6_DMMA_MIN_RANK")) min_rank = atoi(e);
+    // 8..64 ranks: the streaming DMMA kernel (one pass over P, measured in profiles/r2_k6_stream.md)
+    int stream_min = 8;    // R = 8: 0.505 vs 0.534 ms (FMA) at n = 20003; at 4 ranks the FMA kernel is level or ahead
+    if (const char *e = getenv("SLAM_K6_STREAM_MIN_RANK")) stream_min = atoi(e);
+    const int RC = downdate_chunk_width(R);
+    // (33..64 ranks are laid out as one 48- or 64-wide chunk, which only the streaming kernel reads)
+    if ((variant == 3 || (variant == 0 && R >= stream_min) || RC > 32) && downdate_stream_usable(R, ldb))
+        return launch_downdate_stream_rows(Pb, ldb, r0, r1, n, W1c, n_pad, R, s, launches);
     if ((variant == 2 || (variant == 0 && R >= min_rank)) && downdate_dmma_usable(R, ldb))
         return launch_downdate_dmma_rows(Pb, ldb, r0, r1, n, W1c, n_pad, R, s, launches);
-    const int RC = downdate_chunk_width(R);
+    if (RC > 32) {
+        slam_set_error("launch_downdate: no FMA kernel for a %d-wide rank chunk", RC);
+        return SLAM_ERR_ARG;
+    }
     const int nchunks = (R + RC - 1) / RC;
     const DdCfg cfg = pick_cfg(RC);
     for (int c = 0; c < nchunks; c++) {
-        const double *Wr = W1c + (size_t)c * 2 * n_pad * RC;
-        const double *Wt = Wr + (size_t)n_pad * RC;
+        const double *Wr = W1c + (size_t)c * w1_chunk_doubles(n_pad, RC);
+        const double *Wt = Wr + w1_rank_major_offset(n_pad, RC);
         bool ok = false;
         switch (RC) {
             case 2: ok = launch_cfg<2>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;

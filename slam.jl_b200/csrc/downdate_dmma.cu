@@ -38,7 +38,7 @@ __device__ __forceinline__ void dmma(double &d0, double &d1, double a, double b)
                  : "d"(a), "d"(b));
 }
 
-// W1c: per 32-rank chunk c, [n_pad][32] row-major at W1c + c*2*n_pad*32 (rows >= n are zero).
+// W1c: per 32-rank chunk c, [n_pad][32 + W1_PAD] row-major at W1c + c*w1_chunk_doubles(n_pad, 32) (rows >= n are zero).
 __global__ void __launch_bounds__(MM_THREADS, MM_MIN_CTAS)
 k_downdate_dmma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n_pad,
                 const double *__restrict__ W1c, int nchunks) {
@@ -73,7 +73,7 @@ k_downdate_dmma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int 
     }
 
     for (int c = 0; c < nchunks; c++) {
-        const double *Wr = W1c + (size_t)c * 2 * n_pad * MM_KC;
+        const double *Wr = W1c + (size_t)c * w1_chunk_doubles(n_pad, MM_KC);
         __syncthreads();
         // stage the two 64 x 32 operand tiles (16-byte loads; W1 is small and L2 resident)
 #pragma unroll
@@ -81,8 +81,8 @@ k_downdate_dmma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int 
             const int e = tid + q * MM_THREADS;          // double2 index
             const int row = e >> 4, k2 = (e & 15) * 2;
             const int rj = min(j0 + row, n_pad - 1), ri = min(i0 + row, n_pad - 1);
-            const double2 wj = __ldg(reinterpret_cast<const double2 *>(Wr + (size_t)rj * MM_KC + k2));
-            const double2 wi = __ldg(reinterpret_cast<const double2 *>(Wr + (size_t)ri * MM_KC + k2));
+            const double2 wj = __ldg(reinterpret_cast<const double2 *>(Wr + (size_t)rj * (MM_KC + W1_PAD) + k2));
+            const double2 wi = __ldg(reinterpret_cast<const double2 *>(Wr + (size_t)ri * (MM_KC + W1_PAD) + k2));
             *reinterpret_cast<double2 *>(sJ + row * MM_LDK + k2) = make_double2(-wj.x, -wj.y);
             *reinterpret_cast<double2 *>(sI + row * MM_LDK + k2) = wi;
         }

@@ -110,7 +110,7 @@ static int ensure_update_ws(slam_t *h, int R) {
     h->ws_R = 0;
     int Rw = std::max(Rpad, 32);
     CUDA_TRY(cudaMalloc(&h->d_PHt, sizeof(double) * (size_t)npad * Rw));
-    CUDA_TRY(cudaMalloc(&h->d_W1c, sizeof(double) * 2 * (size_t)npad * Rw));   // both layouts
+    CUDA_TRY(cudaMalloc(&h->d_W1c, sizeof(double) * w1_workspace_doubles(npad, Rw)));   // both layouts, every chunk
     CUDA_TRY(cudaMalloc(&h->d_S, sizeof(double) * (size_t)Rw * Rw));
     CUDA_TRY(cudaMalloc(&h->d_C, sizeof(double) * (size_t)Rw * Rw));
     CUDA_TRY(cudaMalloc(&h->d_u, sizeof(double) * Rw));
@@ -247,7 +247,7 @@ extern "C" void *slam_stream(slam_t *h) { return h ? (void *)h->stream : nullptr
 extern "C" long long slam_launch_count(slam_t *h) { return h ? h->launches : 0; }
 extern "C" int slam_set_downdate_variant(slam_t *h, int variant) {
     ARG_CHECK(h != nullptr, "NULL handle");
-    ARG_CHECK(variant >= 0 && variant <= 2, "variant must be 0, 1 or 2");
+    ARG_CHECK(variant >= 0 && variant <= 3, "variant must be 0, 1, 2 or 3");
     h->variant = variant;
     return SLAM_OK;
 }
@@ -736,13 +736,16 @@ k_gain(const double *__restrict__ PHt, int npad, int n, int R, const double *__r
     const double *Cm = use_s ? sC : C;
     const int i = blockIdx.x * K5_THREADS + threadIdx.x;
     if (i >= npad) return;
-    const int nch = (R + RC - 1) / RC;
+    const int nch = (R + RC - 1) / RC, ldk = w1_ldk(RC);
+    const size_t csz = w1_chunk_doubles(npad, RC), rmo = w1_rank_major_offset(npad, RC);
+    for (int c = 0; c < nch; c++)      // the row-major rows' padding (never used by the arithmetic; kept defined)
+        for (int kk = RC; kk < ldk; kk++) W1c[(size_t)c * csz + (size_t)i * ldk + kk] = 0.0;
     if (i >= n) {
         for (int c = 0; c < nch; c++)
             for (int kk = 0; kk < RC; kk++) {
-                double *chunk = W1c + (size_t)c * 2 * npad * RC;
-                chunk[(size_t)i * RC + kk] = 0.0;                          // [npad][RC] row-major
-                chunk[(size_t)npad * RC + (size_t)kk * npad + i] = 0.0;    // [RC][npad] rank-major
+                double *chunk = W1c + (size_t)c * csz;
+                chunk[(size_t)i * ldk + kk] = 0.0;                  // [npad][RC + W1_PAD] row-major
+                chunk[rmo + (size_t)kk * npad + i] = 0.0;           // [RC][npad] rank-major
             }
         return;
     }
@@ -751,9 +754,9 @@ k_gain(const double *__restrict__ PHt, int npad, int n, int R, const double *__r
         double a = 0;
         if (k < R)
             for (int l = 0; l <= k; l++) a += PHt[(size_t)l * npad + i] * Cm[(size_t)l + (size_t)k * R];
-        double *chunk = W1c + (size_t)(k / RC) * 2 * npad * RC;
-        chunk[(size_t)i * RC + (k % RC)] = a;
-        chunk[(size_t)npad * RC + (size_t)(k % RC) * npad + i] = a;
+        double *chunk = W1c + (size_t)(k / RC) * csz;
+        chunk[(size_t)i * ldk + (k % RC)] = a;
+        chunk[rmo + (size_t)(k % RC) * npad + i] = a;
         if (k < R) dxi += a * u[k];
     }
     double xi = x[i] + dxi;
@@ -915,7 +918,7 @@ constexpr int K5T_ROWS = 128;
 constexpr int K5T_KC = 32;
 
 __global__ void __launch_bounds__(K5T_ROWS)
-k_gain_tiled(const double *__restrict__ PHt, int npad, int n, int R, const double *__restrict__ C,
+k_gain_tiled(const double *__restrict__ PHt, int npad, int n, int R, int RC, const double *__restrict__ C,
              double *__restrict__ W1c) {
     __shared__ __align__(16) double sC[K5T_KC * K5T_KC];   // sC[ll][kk] = C[l0 + ll][k0 + kk], 0 where l > k
     const int i = blockIdx.x * K5T_ROWS + threadIdx.x;
@@ -962,31 +965,248 @@ k_gain_tiled(const double *__restrict__ PHt, int npad, int n, int R, const doubl
         }
     }
     if (i >= npad) return;
-    double *chunk = W1c + (size_t)blockIdx.y * 2 * npad * K5T_KC;
-    double4 *row = reinterpret_cast<double4 *>(chunk + (size_t)i * K5T_KC);      // [npad][32] row-major
+    // the CTA's 32 columns k0 .. k0 + 31 inside the RC-wide chunk layout (RC a multiple of 4: a group of four
+    // columns never straddles two chunks); columns past the padded rank nch*RC do not exist
+    const int ldk = w1_ldk(RC), kend = ((R + RC - 1) / RC) * RC;
+    const size_t csz = w1_chunk_doubles(npad, RC), rmo = w1_rank_major_offset(npad, RC);
 #pragma unroll
-    for (int q = 0; q < K5T_KC / 4; q++)
-        row[q] = live ? make_double4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3])
-                      : make_double4(0.0, 0.0, 0.0, 0.0);
+    for (int q = 0; q < K5T_KC / 4; q++) {
+        const int k = k0 + 4 * q;
+        if (k >= kend) break;
+        double *chunk = W1c + (size_t)(k / RC) * csz;
+        *reinterpret_cast<double4 *>(chunk + (size_t)i * ldk + (k % RC)) =          // [npad][RC + W1_PAD] row-major
+            live ? make_double4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]) : make_double4(0.0, 0.0, 0.0, 0.0);
 #pragma unroll
-    for (int kk = 0; kk < K5T_KC; kk++)                                             // [32][npad] rank-major
-        chunk[(size_t)npad * K5T_KC + (size_t)kk * npad + i] = live ? acc[kk] : 0.0;
+        for (int e = 0; e < 4; e++)                                                 // [RC][npad] rank-major
+            chunk[rmo + (size_t)(k % RC + e) * npad + i] = live ? acc[4 * q + e] : 0.0;
+        if ((k % RC) + 4 == RC)                                                     // the row's padding, kept defined
+            *reinterpret_cast<double4 *>(chunk + (size_t)i * ldk + RC) = make_double4(0.0, 0.0, 0.0, 0.0);
+    }
 }
 
 // x += W1*u (src/ekf.jl:72-74), k ascending over all chunks as k_gain does
 __global__ void __launch_bounds__(128)
-k_gain_x(const double *__restrict__ W1c, int npad, int n, int R, const double *__restrict__ u, double *__restrict__ x,
-         double *pose_snapshot) {
+k_gain_x(const double *__restrict__ W1c, int npad, int n, int R, int RC, const double *__restrict__ u,
+         double *__restrict__ x, double *pose_snapshot) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    const size_t csz = w1_chunk_doubles(npad, RC), rmo = w1_rank_major_offset(npad, RC);
     double dxi = 0;
     for (int k = 0; k < R; k++) {
-        const double *chunk = W1c + (size_t)(k / K5T_KC) * 2 * npad * K5T_KC;
-        dxi += chunk[(size_t)npad * K5T_KC + (size_t)(k % K5T_KC) * npad + i] * u[k];
+        const double *chunk = W1c + (size_t)(k / RC) * csz;
+        dxi += chunk[rmo + (size_t)(k % RC) * npad + i] * u[k];
     }
     const double xi = x[i] + dxi;
     x[i] = xi;
     if (i < 3) pose_snapshot[i] = xi;
+}
+
+// ---------------------------------------------------------------------------------------
+// K3 + K4 in one launch, for up to 32 ranks (the HBM-bound regime where the small kernels' latency shows: at
+// n = 20003 they were 54 us of a 571 us step).  S = H*P*H' + RR depends on P only through the (3 + 2m)^2
+// sub-block of the rows and columns H touches, so the innovation Cholesky does not have to wait for P*H':
+// the LAST CTA of the launch gathers that sub-block itself -- PHt at the 3 + 2m rows named by H, with K3's own
+// expression, so S is bit-identical to what K4 formed from K3's output -- and runs K4 (S, symmetrise,
+// right-looking Cholesky, C = inv(U), u = C'v) entirely in shared memory while the other CTAs stream P*H'.
+// inv(U) column j is built by thread j from shared memory (k_innov_chol kept C in global memory: ~120
+// dependent L2 round trips for the last column, 20 us for a 16 x 16 problem).
+// ---------------------------------------------------------------------------------------
+constexpr int K34_RMAX = 32;
+constexpr int K34_MMAX = K34_RMAX / 2;
+
+__global__ void __launch_bounds__(K3_THREADS)
+k_pht_chol(const double *__restrict__ x, const double *__restrict__ P, size_t ld, int n, int npad,
+           const double *__restrict__ zf, const int64_t *__restrict__ idf, int m, double *__restrict__ PHt,
+           double *__restrict__ v_out, double *__restrict__ Hn_out, int *__restrict__ fp_out, int *err, double R0,
+           double R1, double R2, double R3, double *__restrict__ C, double *__restrict__ u) {
+    __shared__ double sH[K34_MMAX][10];
+    __shared__ int sF[K34_MMAX];
+    __shared__ double sPH[K34_RMAX][K34_RMAX + 3];     // chol CTA: PHt[k][s] at the rows cs[s] named by H
+    __shared__ double sS[K34_RMAX * K34_RMAX], sC[K34_RMAX * K34_RMAX], sv[K34_RMAX];
+    __shared__ int s_fail;
+    pdl_wait();
+    pdl_launch_dependents();
+    const bool chol = blockIdx.x == gridDim.x - 1;
+    const int tid = threadIdx.x;
+    const int Nf = (n - 3) / 2;
+    const int R = 2 * m;
+    const double xv = x[0], yv = x[1], phi = x[2];
+    const int latched = *reinterpret_cast<volatile int *>(err);   // an earlier failure nobody has read yet: no-op
+    if (tid == 0) s_fail = 0;
+    __syncthreads();
+    if (tid < m) {
+        int64_t id = idf[tid];
+        if (id < 1 || id > Nf) {
+            atomicCAS(err, 0, SLAM_ERR_BAD_INDEX);
+            s_fail = 2;
+            id = 1;
+        }
+        const int f = 3 + 2 * ((int)id - 1);
+        double zp[2];
+        observe_model(xv, yv, phi, x[f], x[f + 1], zp, sH[tid]);
+        sF[tid] = f;
+        if (chol) {
+            const double v0 = zf[2 * tid] - zp[0], v1 = mpi_to_pi(zf[2 * tid + 1] - zp[1]);
+            sv[2 * tid] = v0;
+            sv[2 * tid + 1] = v1;
+            v_out[2 * tid] = v0;
+            v_out[2 * tid + 1] = v1;
+            fp_out[tid] = f;
+            for (int q = 0; q < 10; q++) Hn_out[10 * tid + q] = sH[tid][q];
+        }
+    }
+    __syncthreads();
+    if (!chol) {
+        const int i = blockIdx.x * K3_THREADS + tid;
+        if (i >= n) return;
+        const double p0 = sym_at(P, ld, i, 0), p1 = sym_at(P, ld, i, 1), p2 = sym_at(P, ld, i, 2);
+        for (int o = 0; o < m; o++) {
+            const double *hh = sH[o];
+            const int f = sF[o];
+            const double p3 = sym_at(P, ld, i, f), p4 = sym_at(P, ld, i, f + 1);
+            PHt[(size_t)(2 * o) * npad + i] = p0 * hh[0] + p1 * hh[1] + p2 * hh[2] + p3 * hh[6] + p4 * hh[7];
+            PHt[(size_t)(2 * o + 1) * npad + i] = p0 * hh[3] + p1 * hh[4] + p2 * hh[5] + p3 * hh[8] + p4 * hh[9];
+        }
+        return;
+    }
+    // ---- the Cholesky CTA ----
+    if (latched != 0 || s_fail == 2) {   // bad id in this update, or a latched error: C = 0 makes K5 / K6 a no-op
+        for (int idx = tid; idx < R * R; idx += K3_THREADS) C[idx] = 0.0;
+        for (int k = tid; k < R; k += K3_THREADS) u[k] = 0.0;
+        return;
+    }
+    const int SC = 3 + R;                // rows named by H: pose rows, then (f_o, f_o + 1) per observation
+    for (int idx = tid; idx < m * SC; idx += K3_THREADS) {
+        const int o = idx / SC, s = idx % SC;
+        const int i = s < 3 ? s : sF[(s - 3) >> 1] + ((s - 3) & 1);
+        const double *hh = sH[o];
+        const int f = sF[o];
+        const double p0 = sym_at(P, ld, i, 0), p1 = sym_at(P, ld, i, 1), p2 = sym_at(P, ld, i, 2),
+                     p3 = sym_at(P, ld, i, f), p4 = sym_at(P, ld, i, f + 1);
+        sPH[2 * o][s] = p0 * hh[0] + p1 * hh[1] + p2 * hh[2] + p3 * hh[6] + p4 * hh[7];
+        sPH[2 * o + 1][s] = p0 * hh[3] + p1 * hh[4] + p2 * hh[5] + p3 * hh[8] + p4 * hh[9];
+    }
+    __syncthreads();
+    for (int idx = tid; idx < m * R; idx += K3_THREADS) {          // S = H*PHt + RR, as k_innov_chol
+        const int o = idx / R, k = idx % R;
+        const double *h = sH[o];
+        const double *col = sPH[k];
+        const double a0 = col[0], a1 = col[1], a2 = col[2], a3 = col[3 + 2 * o], a4 = col[3 + 2 * o + 1];
+        double s0 = h[0] * a0 + h[1] * a1 + h[2] * a2 + h[6] * a3 + h[7] * a4;
+        double s1 = h[3] * a0 + h[4] * a1 + h[5] * a2 + h[8] * a3 + h[9] * a4;
+        if (k == 2 * o) { s0 += R0; s1 += R1; }
+        if (k == 2 * o + 1) { s0 += R2; s1 += R3; }
+        sS[(2 * o) + k * R] = s0;
+        sS[(2 * o + 1) + k * R] = s1;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < R * R; idx += K3_THREADS) {          // S = (S + S')*0.5
+        const int a = idx % R, b = idx / R;
+        if (a < b) {
+            const double sv2 = (sS[a + b * R] + sS[b + a * R]) * 0.5;
+            sS[a + b * R] = sv2;
+            sS[b + a * R] = sv2;
+        } else if (a == b) {
+            sS[a + a * R] = (sS[a + a * R] + sS[a + a * R]) * 0.5;
+        }
+    }
+    __syncthreads();
+    for (int k = 0; k < R; k++) {                                   // right-looking upper Cholesky
+        if (tid == 0) {
+            const double d = sS[k + k * R];
+            if (!(d > 0)) s_fail = 1;
+            else sS[k + k * R] = sqrt(d);
+        }
+        __syncthreads();
+        if (s_fail) break;
+        const double ukk = sS[k + k * R];
+        for (int j = k + 1 + tid; j < R; j += K3_THREADS) sS[k + j * R] /= ukk;
+        __syncthreads();
+        const int rem = R - k - 1;
+        for (int idx = tid; idx < rem * rem; idx += K3_THREADS) {
+            const int i = k + 1 + idx % rem, j = k + 1 + idx / rem;
+            if (i <= j) sS[i + j * R] -= sS[k + i * R] * sS[k + j * R];
+        }
+        __syncthreads();
+    }
+    if (s_fail) {
+        if (tid == 0) atomicCAS(err, 0, SLAM_ERR_NOT_PD);
+        for (int idx = tid; idx < R * R; idx += K3_THREADS) C[idx] = 0.0;
+        for (int k = tid; k < R; k += K3_THREADS) u[k] = 0.0;
+        return;
+    }
+    if (tid < R) {                                                  // C = inv(U), column j by thread j, in shared memory
+        const int j = tid;
+        sC[j + j * R] = 1.0 / sS[j + j * R];
+        for (int i = j - 1; i >= 0; i--) {
+            double a = 0;
+            for (int k = i + 1; k <= j; k++) a += sS[i + k * R] * sC[k + j * R];
+            sC[i + j * R] = -a / sS[i + i * R];
+        }
+        for (int i = j + 1; i < R; i++) sC[i + j * R] = 0.0;
+        double a = 0;
+        for (int l = 0; l <= j; l++) a += sC[l + j * R] * sv[l];
+        u[j] = a;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < R * R; idx += K3_THREADS) C[idx] = sC[idx];
+}
+
+// K5 for one rank chunk (R <= RC <= 32): a thread owns row i, keeps PHt[i, 0:R] in registers (the loop above
+// re-read it R/2 times) and forms W1[i, k] = sum_{l <= k} PHt[i, l] C[l, k], l ascending, separate multiply and add
+// -- the sums of k_gain, bit for bit -- then writes both K6 layouts and x += W1*u.
+template <int RC>
+__global__ void __launch_bounds__(K5_THREADS)
+k_gain_reg(const double *__restrict__ PHt, int npad, int n, int R, const double *__restrict__ C,
+           const double *__restrict__ u, double *__restrict__ W1c, double *__restrict__ x, double *pose_snapshot) {
+    __shared__ double sCm[RC * RC], su[RC];           // sCm[l + k*RC] = C[l][k]
+    constexpr int LDK = RC + W1_PAD;
+    pdl_wait();
+    pdl_launch_dependents();
+    for (int idx = threadIdx.x; idx < RC * RC; idx += K5_THREADS) {
+        const int l = idx % RC, k = idx / RC;
+        sCm[idx] = (l < R && k < R) ? C[(size_t)l + (size_t)k * R] : 0.0;
+    }
+    if (threadIdx.x < RC) su[threadIdx.x] = threadIdx.x < R ? u[threadIdx.x] : 0.0;
+    __syncthreads();
+    const int i = blockIdx.x * K5_THREADS + threadIdx.x;
+    if (i >= npad) return;
+    double *row = W1c + (size_t)i * LDK;                            // [npad][RC + W1_PAD] row-major
+    double *rk = W1c + w1_rank_major_offset(npad, RC) + i;          // [RC][npad] rank-major
+    const bool live = i < n;
+    double p[RC];
+#pragma unroll
+    for (int l = 0; l < RC; l++) p[l] = (live && l < R) ? PHt[(size_t)l * npad + i] : 0.0;
+    double dxi = 0;
+#pragma unroll
+    for (int k = 0; k < RC; k += 2) {
+        double a[2];
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+            double acc = 0;
+            if (k + e < R) {
+#pragma unroll
+                for (int l = 0; l <= k + e; l++) acc += p[l] * sCm[l + (k + e) * RC];
+                dxi += acc * su[k + e];
+            }
+            a[e] = acc;
+            rk[(size_t)(k + e) * npad] = acc;
+        }
+        *reinterpret_cast<double2 *>(row + k) = make_double2(a[0], a[1]);
+    }
+#pragma unroll
+    for (int k = RC; k < LDK; k += 2) *reinterpret_cast<double2 *>(row + k) = make_double2(0.0, 0.0);
+    if (live) {
+        const double xi = x[i] + dxi;
+        x[i] = xi;
+        if (i < 3) pose_snapshot[i] = xi;
+    }
+}
+
+template <int RC>
+static cudaError_t launch_gain_reg(int blocks, cudaStream_t s, const double *PHt, int npad, int n, int R, const double *C,
+                                   const double *u, double *W1c, double *x, double *pose) {
+    return launch_pdl(k_gain_reg<RC>, dim3(blocks), dim3(K5_THREADS), 0, s, PHt, npad, n, R, C, u, W1c, x, pose);
 }
 
 static int update_device(slam_t *h, const double *d_zf, int m, const double R[4], const int64_t *d_idf) {
@@ -1004,23 +1224,39 @@ static int update_device(slam_t *h, const double *d_zf, int m, const double R[4]
     if (rc) return rc;
     const int n = h->n, npad = h->ws_npad;
     const int RC = downdate_chunk_width(Rk);
-    k_pht<<<(n + K3_THREADS - 1) / K3_THREADS, K3_THREADS, 0, h->stream>>>(
-        h->d_x, h->d_P, h->ld, n, npad, d_zf, d_idf, m, h->d_PHt, h->d_v, h->d_Hn, h->d_fp, h->d_err);
-    rc = launch_innov_chol(h->d_PHt, npad, h->d_Hn, h->d_fp, h->d_v, m, R, h->d_S, h->d_C, h->d_u, h->d_err, h->stream);
-    if (rc) return rc;
-    size_t sm = (size_t)Rk * Rk * sizeof(double) <= 32768 ? (size_t)Rk * Rk * sizeof(double) : 0;
-    int npad_used = round_up(n, DD_ROW_PAD);
-    if (Rk > 32 && RC == K5T_KC) {
-        k_gain_tiled<<<dim3((npad_used + K5T_ROWS - 1) / K5T_ROWS, (Rk + K5T_KC - 1) / K5T_KC), K5T_ROWS, 0, h->stream>>>(
-            h->d_PHt, npad, n, Rk, h->d_C, h->d_W1c);
-        k_gain_x<<<(n + 127) / 128, 128, 0, h->stream>>>(h->d_W1c, npad, n, Rk, h->d_u, h->d_x,
-                                                        h->d_pose + 4 * h->pose_slot);
-        h->launches++;
+    const int npad_used = round_up(n, DD_ROW_PAD);
+    if (Rk <= K34_RMAX) {
+        // up to 32 ranks: K3 + K4 in one launch, K5 with the row of PHt in registers, chained by programmatic
+        // dependent launch (each kernel is scheduled while its predecessor drains)
+        CUDA_TRY(launch_pdl(k_pht_chol, dim3((n + K3_THREADS - 1) / K3_THREADS + 1), dim3(K3_THREADS), 0, h->stream,
+                            (const double *)h->d_x, (const double *)h->d_P, h->ld, n, npad, d_zf, d_idf, m, h->d_PHt,
+                            h->d_v, h->d_Hn, h->d_fp, h->d_err, R[0], R[1], R[2], R[3], h->d_C, h->d_u));
+        const int blocks = (npad_used + K5_THREADS - 1) / K5_THREADS;
+        double *pose = h->d_pose + 4 * h->pose_slot;
+        cudaError_t e;
+        switch (RC) {
+            case 2: e = launch_gain_reg<2>(blocks, h->stream, h->d_PHt, npad, n, Rk, h->d_C, h->d_u, h->d_W1c, h->d_x, pose); break;
+            case 4: e = launch_gain_reg<4>(blocks, h->stream, h->d_PHt, npad, n, Rk, h->d_C, h->d_u, h->d_W1c, h->d_x, pose); break;
+            case 8: e = launch_gain_reg<8>(blocks, h->stream, h->d_PHt, npad, n, Rk, h->d_C, h->d_u, h->d_W1c, h->d_x, pose); break;
+            case 12: e = launch_gain_reg<12>(blocks, h->stream, h->d_PHt, npad, n, Rk, h->d_C, h->d_u, h->d_W1c, h->d_x, pose); break;
+            case 16: e = launch_gain_reg<16>(blocks, h->stream, h->d_PHt, npad, n, Rk, h->d_C, h->d_u, h->d_W1c, h->d_x, pose); break;
+            case 24: e = launch_gain_reg<24>(blocks, h->stream, h->d_PHt, npad, n, Rk, h->d_C, h->d_u, h->d_W1c, h->d_x, pose); break;
+            default: e = launch_gain_reg<32>(blocks, h->stream, h->d_PHt, npad, n, Rk, h->d_C, h->d_u, h->d_W1c, h->d_x, pose); break;
+        }
+        CUDA_TRY(e);
+        h->launches += 2;
     } else {
-        k_gain<<<(npad_used + K5_THREADS - 1) / K5_THREADS, K5_THREADS, sm, h->stream>>>(
-            h->d_PHt, npad, n, Rk, h->d_C, h->d_u, RC, h->d_W1c, h->d_x, h->d_pose + 4 * h->pose_slot);
+        k_pht<<<(n + K3_THREADS - 1) / K3_THREADS, K3_THREADS, 0, h->stream>>>(
+            h->d_x, h->d_P, h->ld, n, npad, d_zf, d_idf, m, h->d_PHt, h->d_v, h->d_Hn, h->d_fp, h->d_err);
+        rc = launch_innov_chol(h->d_PHt, npad, h->d_Hn, h->d_fp, h->d_v, m, R, h->d_S, h->d_C, h->d_u, h->d_err, h->stream);
+        if (rc) return rc;
+        const int Rpad = round_up(Rk, RC);   // RC is 40..64 or (above 64 ranks) 32
+        k_gain_tiled<<<dim3((npad_used + K5T_ROWS - 1) / K5T_ROWS, (Rpad + K5T_KC - 1) / K5T_KC), K5T_ROWS, 0, h->stream>>>(
+            h->d_PHt, npad, n, Rk, RC, h->d_C, h->d_W1c);
+        k_gain_x<<<(n + 127) / 128, 128, 0, h->stream>>>(h->d_W1c, npad, n, Rk, RC, h->d_u, h->d_x,
+                                                        h->d_pose + 4 * h->pose_slot);
+        h->launches += 4;
     }
-    h->launches += 3;
     CUDA_TRY(cudaGetLastError());
     const bool timed = h->profiling && h->ev_used + 2 <= (int)h->ev.size();
     if (timed) CUDA_TRY(cudaEventRecord(h->ev[h->ev_used], h->stream));

@@ -5,6 +5,19 @@
 
 constexpr int DD_ROW_PAD = 256;  // W1 row padding: covers every K6 tile shape
 
+// W1 workspace layout (written by K5, read by K6).  Per rank chunk c of width RC (R zero-padded to a multiple):
+//   row-major copy   [n_pad][RC + W1_PAD]   at W1c + c * w1_chunk_doubles(n_pad, RC)
+//   rank-major copy  [RC][n_pad]            at ... + w1_rank_major_offset(n_pad, RC)
+// The row-major rows carry W1_PAD unused (zero) doubles so that a tile of rows fetched by ONE 1-D bulk copy lands
+// in shared memory with a row stride of RC + 4: the (row = lane / 4, rank = lane % 4) fragment reads of the
+// FP64 MMA are then bank-conflict free (stride 4 mod 16 eight-byte words), with no per-row copies and no swizzle.
+constexpr int W1_PAD = 4;
+__host__ __device__ inline int w1_ldk(int RC) { return RC + W1_PAD; }
+__host__ __device__ inline size_t w1_chunk_doubles(int n_pad, int RC) { return (size_t)n_pad * (2 * RC + W1_PAD); }
+__host__ __device__ inline size_t w1_rank_major_offset(int n_pad, int RC) { return (size_t)n_pad * (RC + W1_PAD); }
+// upper bound of the whole workspace for any R <= Rw (chunks of width >= 4 need 2 Rpad + 4 nch <= 3 Rpad doubles per row)
+inline size_t w1_workspace_doubles(int n_pad, int Rw) { return (size_t)n_pad * (3 * (size_t)Rw + 8); }
+
 // ---- K6 (downdate.cu / downdate_dmma.cu) -------------------------------------------------
 int downdate_chunk_width(int R);
 int launch_downdate(double *P, size_t ld, int n, const double *W1c, int n_pad, int R, int variant,
@@ -14,7 +27,13 @@ int launch_downdate(double *P, size_t ld, int n, const double *W1c, int n_pad, i
 int launch_downdate_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad,
                          int R, int variant, cudaStream_t s, long long *launches);
 
-// FP64 tensor-core variant (downdate_dmma.cu): same contract; usable for the 32-wide chunk layout
+// streaming FP64 tensor-core variant (downdate_stream.cu): ranks 12..64 in ONE pass over P, the row-side W1
+// fragments of a warp in registers, the column-side tile staged once per tile by a bulk copy
+bool downdate_stream_usable(int R, size_t ldb);
+int launch_downdate_stream_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad, int R,
+                                cudaStream_t s, long long *launches);
+
+// FP64 tensor-core tile variant (downdate_dmma.cu): same contract; usable for the 32-wide chunk layout
 bool downdate_dmma_usable(int R, size_t ldb);
 int launch_downdate_dmma_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad, int R,
                               cudaStream_t s, long long *launches);

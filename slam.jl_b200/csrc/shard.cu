@@ -580,12 +580,16 @@ k_sh_unpermute(ShardGeom g, int R, int RC, const double *__restrict__ W1gath, co
     const bool live = i < g.n;
     if (live) row_owner(g, i, &owner, &q, &li);
     double dx = 0;
+    const int ldk = w1_ldk(RC);
+    const size_t csz = w1_chunk_doubles(g.npad, RC), rmo = w1_rank_major_offset(g.npad, RC);
+    for (int c = 0; c < nch; c++)
+        for (int kk = RC; kk < ldk; kk++) W1c[(size_t)c * csz + (size_t)i * ldk + kk] = 0.0;   // row padding, kept defined
     for (int k = 0; k < nch * RC; k++) {
         const int c = k / RC, kk = k % RC;
         double a = live ? W1gath[(((size_t)owner * nch + c) * nloc + li) * RC + kk] : 0.0;
-        double *chunk = W1c + (size_t)c * 2 * g.npad * RC;
-        chunk[(size_t)i * RC + kk] = a;
-        chunk[(size_t)g.npad * RC + (size_t)kk * g.npad + i] = a;
+        double *chunk = W1c + (size_t)c * csz;
+        chunk[(size_t)i * ldk + kk] = a;
+        chunk[rmo + (size_t)kk * g.npad + i] = a;
         if (k < R) dx += a * u[k];
     }
     if (live) x[i] += dx;
@@ -664,7 +668,9 @@ constexpr int SHG_ROWS = 128;
 __global__ void __launch_bounds__(SHG_ROWS)
 k_sh_gain_p2p(ShardGeom g, int R, int RC, const double *__restrict__ PHtloc, const double *__restrict__ Cm,
               const double *__restrict__ u, ShardPeers pr) {
-    extern __shared__ double sh_tile[];          // [SHG_ROWS][RC]
+    extern __shared__ double sh_tile[];          // [SHG_ROWS][RC + W1_PAD]: the row-major layout's rows, padding included
+    const int ldk = w1_ldk(RC);
+    const size_t csz = w1_chunk_doubles(g.npad, RC), rmo = w1_rank_major_offset(g.npad, RC);
     const int q = blockIdx.y;
     const int r0 = blockIdx.x * SHG_ROWS;        // first local row of the CTA inside block q
     const int rows = min(SHG_ROWS, g.hi[q] - g.lo[q] - r0);
@@ -675,22 +681,23 @@ k_sh_gain_p2p(ShardGeom g, int R, int RC, const double *__restrict__ PHtloc, con
     const bool live = t < rows;
     const int nch = (R + RC - 1) / RC;
     double dx = 0;
+    for (int kk = RC; kk < ldk; kk++) sh_tile[t * ldk + kk] = 0.0;
     for (int c = 0; c < nch; c++) {
         for (int kk = 0; kk < RC; kk++) {
             const int k = c * RC + kk;
             double a = 0;
             if (live && k < R)
                 for (int l = 0; l <= k; l++) a += PHtloc[(size_t)l * nloc + li] * Cm[(size_t)l + (size_t)k * R];
-            sh_tile[t * RC + kk] = a;
+            sh_tile[t * ldk + kk] = a;
             if (live) {
-                const size_t o2 = (size_t)c * 2 * g.npad * RC + (size_t)g.npad * RC + (size_t)kk * g.npad + i;
+                const size_t o2 = (size_t)c * csz + rmo + (size_t)kk * g.npad + i;
                 for (int r = 0; r < g.world; r++) pr.W1c[r][o2] = a;      // rank-major copy: lanes = rows
                 if (k < R) dx += a * u[k];
             }
         }
         __syncthreads();
-        const size_t o1 = (size_t)c * 2 * g.npad * RC + (size_t)i0 * RC;   // row-major copy: the tile is contiguous
-        for (int e = t; e < rows * RC; e += SHG_ROWS) {
+        const size_t o1 = (size_t)c * csz + (size_t)i0 * ldk;   // row-major copy: the tile is contiguous
+        for (int e = t; e < rows * ldk; e += SHG_ROWS) {
             const double a = sh_tile[e];
             for (int r = 0; r < g.world; r++) pr.W1c[r][o1 + e] = a;
         }
@@ -706,12 +713,11 @@ k_sh_gain_p2p(ShardGeom g, int R, int RC, const double *__restrict__ PHtloc, con
 __global__ void k_sh_zero_tail(int n, int npad_used, int npad, int RC, int nch, double *W1c) {
     const int i = n + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= npad_used) return;
+    const int ldk = w1_ldk(RC);
     for (int c = 0; c < nch; c++) {
-        double *chunk = W1c + (size_t)c * 2 * npad * RC;
-        for (int kk = 0; kk < RC; kk++) {
-            chunk[(size_t)i * RC + kk] = 0.0;
-            chunk[(size_t)npad * RC + (size_t)kk * npad + i] = 0.0;
-        }
+        double *chunk = W1c + (size_t)c * w1_chunk_doubles(npad, RC);
+        for (int kk = 0; kk < ldk; kk++) chunk[(size_t)i * ldk + kk] = 0.0;
+        for (int kk = 0; kk < RC; kk++) chunk[w1_rank_major_offset(npad, RC) + (size_t)kk * npad + i] = 0.0;
     }
 }
 
@@ -763,7 +769,7 @@ static int shard_ensure_ws(slam_shard_t *s, int R) {
     s->d_fp = s->d_fpH = s->d_cs = nullptr;
     s->ws_R = 0;
     const size_t S = 3 + Rw, nloc = 2 * ((size_t)s->hb + 2), npad = s->npad;
-    CUDA_TRY(cudaMalloc(&s->arenaB, sizeof(double) * (S * npad + 2 * npad * Rw)));
+    CUDA_TRY(cudaMalloc(&s->arenaB, sizeof(double) * (S * npad + w1_workspace_doubles((int)npad, Rw))));
     s->d_rowbuf = (double *)s->arenaB;
     s->d_W1c = s->d_rowbuf + S * npad;
     if (s->world > 1 && s->p2p) {
@@ -839,7 +845,9 @@ static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const
     s->launches += 3;
     if (timed) CUDA_TRY(cudaEventRecord(ev[2], st));
     if (p2p) {
-        k_sh_gain_p2p<<<dim3((s->hb + 2 + SHG_ROWS - 1) / SHG_ROWS, 2), SHG_ROWS, sizeof(double) * SHG_ROWS * RC, st>>>(
+        const size_t gsm = sizeof(double) * SHG_ROWS * w1_ldk(RC);
+        if (gsm > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(k_sh_gain_p2p, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm));
+        k_sh_gain_p2p<<<dim3((s->hb + 2 + SHG_ROWS - 1) / SHG_ROWS, 2), SHG_ROWS, gsm, st>>>(
             g, Rk, RC, s->d_PHtloc, s->d_C, s->d_u, pr);
         k_sh_barrier<<<1, 32, 0, st>>>(pr, s->rank, s->world, ++s->epoch, s->d_err);
         s->launches += 2;
