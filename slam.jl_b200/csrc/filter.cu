@@ -626,93 +626,116 @@ k_pht(const double *__restrict__ x, const double *__restrict__ P, size_t ld, int
 }
 
 // ---------------------------------------------------------------------------------------
-// K4 -- S = H*PHt + RR, S = (S+S')/2, C = inv(chol(S)) (src/ekf.jl:68-70), u = C'v.
-// One CTA.  Right-looking upper Cholesky (same subtraction order per entry as the
-// left-looking twin), then one thread per column of the triangular inverse.
+// K4 -- S = H*PHt + RR, S = (S+S')/2, C = inv(chol(S)) (src/ekf.jl:68-70), u = C'v, for up to 32 ranks, in
+// shared memory by one CTA.  k4_factor is shared by the stand-alone kernel (sharded filter) and the fused
+// K3 + K4 launch (single filter), so both produce the same C bit for bit.
+//   * right-looking upper Cholesky, the same subtraction order per entry as the left-looking twin; two barriers
+//     per step (every thread takes sqrt(d) of the pivot itself; the pivots' roots go to sd, so the step that
+//     reads the diagonal never races with one that writes it);
+//   * C = inv(U) in the order of LAPACK's unblocked dtrti2 with the reciprocals taken up front, thread i building
+//     row i: C[i][j] = (U[i][j] C[i][i] + sum_{i<jj<j} U[jj][j] C[i][jj]) * (-1/U[j][j]) -- the order of the
+//     oracle's twin and of the ensemble kernel;  u[j] = sum_{l<j} C[l][j] v[l] + C[j][j] v[j].
 // ---------------------------------------------------------------------------------------
-constexpr int K4_THREADS = 512;
+constexpr int K4_RMAX = 32;
+constexpr int K4_THREADS = 256;
+
+// sS: R x R column-major (leading dimension R) holding S; sC: R x R; sv: R; sd: 2R scratch.  Returns false (all
+// threads alike) when S is not positive definite.  Ends with a barrier; C and u are written to global memory.
+__device__ __forceinline__ bool k4_factor(double *sS, double *sC, const double *sv, double *sd, int R, int tid, int nt,
+                                          double *__restrict__ C, double *__restrict__ u) {
+    for (int idx = tid; idx < R * R; idx += nt) {                  // S = (S + S')*0.5
+        const int a = idx % R, b = idx / R;
+        if (a < b) {
+            const double s2 = (sS[a + b * R] + sS[b + a * R]) * 0.5;
+            sS[a + b * R] = s2;
+            sS[b + a * R] = s2;
+        } else if (a == b) {
+            sS[a + a * R] = (sS[a + a * R] + sS[a + a * R]) * 0.5;
+        }
+    }
+    __syncthreads();
+    bool ok = true;
+    for (int k = 0; k < R; k++) {
+        const double d = sS[k + k * R];
+        if (!(d > 0)) {          // uniform: every thread reads the same pivot
+            ok = false;
+            break;
+        }
+        const double ukk = sqrt(d);
+        if (tid == 0) sd[k] = ukk;
+        for (int j = k + 1 + tid; j < R; j += nt) sS[k + j * R] /= ukk;
+        __syncthreads();
+        const int rem = R - k - 1;
+        for (int idx = tid; idx < rem * rem; idx += nt) {
+            const int i = k + 1 + idx % rem, j = k + 1 + idx / rem;
+            if (i <= j) sS[i + j * R] -= sS[k + i * R] * sS[k + j * R];
+        }
+        __syncthreads();
+    }
+    if (!ok) return false;
+    double *cd = sd + R;
+    if (tid < R) cd[tid] = 1.0 / sd[tid];
+    for (int idx = tid; idx < R * R; idx += nt) sC[idx] = 0.0;
+    __syncthreads();
+    if (tid < R) {
+        const int i = tid;
+        const double cii = cd[i];
+        sC[i + i * R] = cii;
+        for (int j = i + 1; j < R; j++) {
+            double y = sS[i + j * R] * cii;
+            for (int jj = i + 1; jj < j; jj++) y += sS[jj + j * R] * sC[i + jj * R];
+            sC[i + j * R] = y * (-cd[j]);
+        }
+    }
+    __syncthreads();
+    if (tid < R) {
+        const int j = tid;
+        double a = 0;
+        for (int l = 0; l < j; l++) a += sC[l + j * R] * sv[l];
+        a += cd[j] * sv[j];
+        u[j] = a;
+    }
+    for (int idx = tid; idx < R * R; idx += nt) C[idx] = sC[idx];
+    return true;
+}
+
+__device__ __forceinline__ void k4_noop(int R, int tid, int nt, double *__restrict__ C, double *__restrict__ u) {
+    for (int idx = tid; idx < R * R; idx += nt) C[idx] = 0.0;     // C = 0: W1 = 0, x += 0, P -= 0
+    for (int k = tid; k < R; k += nt) u[k] = 0.0;
+}
 
 __global__ void __launch_bounds__(K4_THREADS)
 k_innov_chol(const double *__restrict__ PHt, int npad, const double *__restrict__ Hn,
              const int *__restrict__ fp, const double *__restrict__ v, int m, double R0, double R1,
-             double R2, double R3, double *Sg, double *C, double *u, int *err, int s_in_smem) {
-    // S (then its Cholesky factor) lives in dynamic shared memory when it fits (the launcher decides):
-    // the factorisation is a chain of R barrier-separated steps whose cost is the latency of S.
-    extern __shared__ __align__(16) double k4_smem[];
-    double *S = s_in_smem ? k4_smem : Sg;
+             double R2, double R3, double *__restrict__ C, double *__restrict__ u, int *err) {
+    __shared__ double sS[K4_RMAX * K4_RMAX], sC[K4_RMAX * K4_RMAX], sv[K4_RMAX], sd[2 * K4_RMAX];
     const int R = 2 * m;
     const int tid = threadIdx.x;
-    __shared__ int s_fail;
-    if (tid == 0) s_fail = 0;
-    // A latched error (a landmark id out of range found by K3 of THIS update, or an earlier failure nobody has
-    // read yet) turns the update into a no-op before anything is changed: C = 0 gives W1 = 0, x += 0, P -= 0.
-    // The reference throws before any mutation (BoundsError at src/ekf.jl:57, chol at :70).
+    // A latched error (a landmark id out of range found earlier in THIS update, or an earlier failure nobody has
+    // read yet) turns the update into a no-op before anything is changed.  The reference throws before any
+    // mutation (BoundsError at src/ekf.jl:57, chol at :70).
     if (*reinterpret_cast<volatile int *>(err) != 0) {
-        for (int idx = tid; idx < R * R; idx += K4_THREADS) C[idx] = 0.0;
-        for (int k = tid; k < R; k += K4_THREADS) u[k] = 0.0;
+        k4_noop(R, tid, K4_THREADS, C, u);
         return;
     }
     for (int idx = tid; idx < m * R; idx += K4_THREADS) {
-        int o = idx / R, k = idx % R;
+        const int o = idx / R, k = idx % R;
         const double *h = Hn + 10 * o;
-        int f = fp[o];
+        const int f = fp[o];
         const double *col = PHt + (size_t)k * npad;
-        double a0 = col[0], a1 = col[1], a2 = col[2], a3 = col[f], a4 = col[f + 1];
+        const double a0 = col[0], a1 = col[1], a2 = col[2], a3 = col[f], a4 = col[f + 1];
         double s0 = h[0] * a0 + h[1] * a1 + h[2] * a2 + h[6] * a3 + h[7] * a4;
         double s1 = h[3] * a0 + h[4] * a1 + h[5] * a2 + h[8] * a3 + h[9] * a4;
         if (k == 2 * o) { s0 += R0; s1 += R1; }          // RR[ii,ii] = R (:60), R column-major
         if (k == 2 * o + 1) { s0 += R2; s1 += R3; }
-        S[(size_t)(2 * o) + (size_t)k * R] = s0;
-        S[(size_t)(2 * o + 1) + (size_t)k * R] = s1;
+        sS[(2 * o) + k * R] = s0;
+        sS[(2 * o + 1) + k * R] = s1;
     }
+    if (tid < R) sv[tid] = v[tid];
     __syncthreads();
-    for (int idx = tid; idx < R * R; idx += K4_THREADS) {
-        int a = idx % R, b = idx / R;
-        if (a < b) {
-            double s = (S[(size_t)a + (size_t)b * R] + S[(size_t)b + (size_t)a * R]) * 0.5;
-            S[(size_t)a + (size_t)b * R] = s;
-            S[(size_t)b + (size_t)a * R] = s;
-        } else if (a == b) {
-            S[(size_t)a + (size_t)a * R] = (S[(size_t)a + (size_t)a * R] + S[(size_t)a + (size_t)a * R]) * 0.5;
-        }
-    }
-    __syncthreads();
-    for (int k = 0; k < R; k++) {
-        if (tid == 0) {
-            double d = S[(size_t)k + (size_t)k * R];
-            if (!(d > 0)) s_fail = 1;
-            else S[(size_t)k + (size_t)k * R] = sqrt(d);
-        }
-        __syncthreads();
-        if (s_fail) break;
-        double ukk = S[(size_t)k + (size_t)k * R];
-        for (int j = k + 1 + tid; j < R; j += K4_THREADS) S[(size_t)k + (size_t)j * R] /= ukk;
-        __syncthreads();
-        int rem = R - k - 1;
-        for (int idx = tid; idx < rem * rem; idx += K4_THREADS) {
-            int i = k + 1 + idx % rem, j = k + 1 + idx / rem;
-            if (i <= j) S[(size_t)i + (size_t)j * R] -= S[(size_t)k + (size_t)i * R] * S[(size_t)k + (size_t)j * R];
-        }
-        __syncthreads();
-    }
-    if (s_fail) {
+    if (!k4_factor(sS, sC, sv, sd, R, tid, K4_THREADS, C, u)) {
         if (tid == 0) atomicCAS(err, 0, SLAM_ERR_NOT_PD);
-        for (int idx = tid; idx < R * R; idx += K4_THREADS) C[idx] = 0.0;   // update becomes a no-op
-        for (int k = tid; k < R; k += K4_THREADS) u[k] = 0.0;
-        return;
-    }
-    // C = inv(U), upper triangular, column by column
-    for (int j = tid; j < R; j += K4_THREADS) {
-        C[(size_t)j + (size_t)j * R] = 1.0 / S[(size_t)j + (size_t)j * R];
-        for (int i = j - 1; i >= 0; i--) {
-            double a = 0;
-            for (int k = i + 1; k <= j; k++) a += S[(size_t)i + (size_t)k * R] * C[(size_t)k + (size_t)j * R];
-            C[(size_t)i + (size_t)j * R] = -a / S[(size_t)i + (size_t)i * R];
-        }
-        for (int i = j + 1; i < R; i++) C[(size_t)i + (size_t)j * R] = 0.0;
-        double a = 0;
-        for (int l = 0; l <= j; l++) a += C[(size_t)l + (size_t)j * R] * v[l];
-        u[j] = a;
+        k4_noop(R, tid, K4_THREADS, C, u);
     }
 }
 
@@ -879,19 +902,11 @@ k_innov_chol_wide(const double *__restrict__ PHt, int npad, const double *__rest
 
 int launch_innov_chol(const double *PHt, int npad, const double *Hn, const int *fp, const double *v, int m,
                       const double R[4], double *S, double *C, double *u, int *err, cudaStream_t s) {
-    const size_t need = sizeof(double) * (size_t)(2 * m) * (2 * m);
-    int in_smem = need <= 48 * 1024;
-    if (!in_smem && need <= 200 * 1024) {   // opt in per call: the attribute belongs to the current device
-        if (cudaFuncSetAttribute(k_innov_chol, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need) == cudaSuccess)
-            in_smem = 1;
-        else
-            cudaGetLastError();
-    }
-    if (2 * m > 32) {
+    if (2 * m > K4_RMAX) {
         const int Rr = 2 * m;
         const size_t needw = sizeof(double) * ((size_t)(Rr | 1) * Rr + Rr);
-        in_smem = needw <= 48 * 1024;
-        if (!in_smem && needw <= 200 * 1024) {
+        int in_smem = needw <= 48 * 1024;
+        if (!in_smem && needw <= 200 * 1024) {   // opt in per call: the attribute belongs to the current device
             if (cudaFuncSetAttribute(k_innov_chol_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)needw) ==
                 cudaSuccess)
                 in_smem = 1;
@@ -901,8 +916,7 @@ int launch_innov_chol(const double *PHt, int npad, const double *Hn, const int *
         k_innov_chol_wide<<<1, K4W_THREADS, in_smem ? needw : 0, s>>>(PHt, npad, Hn, fp, v, m, R[0], R[1], R[2], R[3], S, C,
                                                                       u, err, in_smem);
     } else {
-        k_innov_chol<<<1, K4_THREADS, in_smem ? need : 0, s>>>(PHt, npad, Hn, fp, v, m, R[0], R[1], R[2], R[3], S, C, u,
-                                                             err, in_smem);
+        k_innov_chol<<<1, K4_THREADS, 0, s>>>(PHt, npad, Hn, fp, v, m, R[0], R[1], R[2], R[3], C, u, err);
     }
     CUDA_TRY(cudaGetLastError());
     return SLAM_OK;
@@ -1022,7 +1036,7 @@ k_pht_chol(const double *__restrict__ x, const double *__restrict__ P, size_t ld
     __shared__ double sH[K34_MMAX][10];
     __shared__ int sF[K34_MMAX];
     __shared__ double sPH[K34_RMAX][K34_RMAX + 3];     // chol CTA: PHt[k][s] at the rows cs[s] named by H
-    __shared__ double sS[K34_RMAX * K34_RMAX], sC[K34_RMAX * K34_RMAX], sv[K34_RMAX];
+    __shared__ double sS[K34_RMAX * K34_RMAX], sC[K34_RMAX * K34_RMAX], sv[K34_RMAX], sd[2 * K34_RMAX];
     __shared__ int s_fail;
     pdl_wait();
     pdl_launch_dependents();
@@ -1071,8 +1085,7 @@ k_pht_chol(const double *__restrict__ x, const double *__restrict__ P, size_t ld
     }
     // ---- the Cholesky CTA ----
     if (latched != 0 || s_fail == 2) {   // bad id in this update, or a latched error: C = 0 makes K5 / K6 a no-op
-        for (int idx = tid; idx < R * R; idx += K3_THREADS) C[idx] = 0.0;
-        for (int k = tid; k < R; k += K3_THREADS) u[k] = 0.0;
+        k4_noop(R, tid, K3_THREADS, C, u);
         return;
     }
     const int SC = 3 + R;                // rows named by H: pose rows, then (f_o, f_o + 1) per observation
@@ -1100,56 +1113,10 @@ k_pht_chol(const double *__restrict__ x, const double *__restrict__ P, size_t ld
         sS[(2 * o + 1) + k * R] = s1;
     }
     __syncthreads();
-    for (int idx = tid; idx < R * R; idx += K3_THREADS) {          // S = (S + S')*0.5
-        const int a = idx % R, b = idx / R;
-        if (a < b) {
-            const double sv2 = (sS[a + b * R] + sS[b + a * R]) * 0.5;
-            sS[a + b * R] = sv2;
-            sS[b + a * R] = sv2;
-        } else if (a == b) {
-            sS[a + a * R] = (sS[a + a * R] + sS[a + a * R]) * 0.5;
-        }
-    }
-    __syncthreads();
-    for (int k = 0; k < R; k++) {                                   // right-looking upper Cholesky
-        if (tid == 0) {
-            const double d = sS[k + k * R];
-            if (!(d > 0)) s_fail = 1;
-            else sS[k + k * R] = sqrt(d);
-        }
-        __syncthreads();
-        if (s_fail) break;
-        const double ukk = sS[k + k * R];
-        for (int j = k + 1 + tid; j < R; j += K3_THREADS) sS[k + j * R] /= ukk;
-        __syncthreads();
-        const int rem = R - k - 1;
-        for (int idx = tid; idx < rem * rem; idx += K3_THREADS) {
-            const int i = k + 1 + idx % rem, j = k + 1 + idx / rem;
-            if (i <= j) sS[i + j * R] -= sS[k + i * R] * sS[k + j * R];
-        }
-        __syncthreads();
-    }
-    if (s_fail) {
+    if (!k4_factor(sS, sC, sv, sd, R, tid, K3_THREADS, C, u)) {
         if (tid == 0) atomicCAS(err, 0, SLAM_ERR_NOT_PD);
-        for (int idx = tid; idx < R * R; idx += K3_THREADS) C[idx] = 0.0;
-        for (int k = tid; k < R; k += K3_THREADS) u[k] = 0.0;
-        return;
+        k4_noop(R, tid, K3_THREADS, C, u);
     }
-    if (tid < R) {                                                  // C = inv(U), column j by thread j, in shared memory
-        const int j = tid;
-        sC[j + j * R] = 1.0 / sS[j + j * R];
-        for (int i = j - 1; i >= 0; i--) {
-            double a = 0;
-            for (int k = i + 1; k <= j; k++) a += sS[i + k * R] * sC[k + j * R];
-            sC[i + j * R] = -a / sS[i + i * R];
-        }
-        for (int i = j + 1; i < R; i++) sC[i + j * R] = 0.0;
-        double a = 0;
-        for (int l = 0; l <= j; l++) a += sC[l + j * R] * sv[l];
-        u[j] = a;
-    }
-    __syncthreads();
-    for (int idx = tid; idx < R * R; idx += K3_THREADS) C[idx] = sC[idx];
 }
 
 // K5 for one rank chunk (R <= RC <= 32): a thread owns row i, keeps PHt[i, 0:R] in registers (the loop above

@@ -16,7 +16,7 @@ from slamcuda._ffi import lib, check, dptr, iptr  # noqa: E402
 nl = int(sys.argv[1]) if len(sys.argv) > 1 else 10000
 ms_list = [int(a) for a in sys.argv[2].split(",")] if len(sys.argv) > 2 else [6, 8, 12, 16, 24, 32]
 steps = int(sys.argv[3]) if len(sys.argv) > 3 else 20
-cfgs = sys.argv[4].split(";") if len(sys.argv) > 4 else ["4,8,128,2"]
+cfgs = sys.argv[4].split(";") if len(sys.argv) > 4 else [""]     # "" = the library's tuned default
 n = 3 + 2 * nl
 side = (nl / 0.0035) ** 0.5
 R = np.array([0.01, 0, 0, (np.pi / 180) ** 2])
