@@ -451,6 +451,80 @@ def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_ste
         lib.slam_destroy(h)
 
 
+def gpu_host_mirror(n_landmarks: int, m: int, device: int = 0):
+    """The reference's own calling convention -- `state.x, state.cov = f(state, ...)` on HOST arrays, which is what the
+    unchanged sim! does (sim/ekfslam-sim.jl:42,100,117,120) -- through the incremental host mirror of the wrapper
+    (slamcuda/slam.py; julia/ekf-cuda.jl does the same): no upload when a call is handed the arrays the previous call
+    returned, and only what the call changed comes back."""
+    import slamcuda as sc
+    from slamcuda._ffi import lib, check, dptr, iptr
+    from slamcuda.slam import _Handle
+    n = 3 + 2 * n_landmarks
+    side = math.sqrt(n_landmarks / DENSITY)
+    h0 = _Handle(device, n + 2)
+    check(lib.slam_synth_state(h0.ptr, n_landmarks, side, SEED))
+    z = np.zeros(2 * m)
+    ids = np.zeros(m, dtype=np.int64)
+    check(lib.slam_synth_observations(h0.ptr, n_landmarks, side, SEED, m, 0, dptr(z), iptr(ids)))
+    x, P = h0.get_state(order="F")
+    h0.close()
+    st = sc.EKFSlamState.__new__(sc.EKFSlamState)
+    st.x, st.cov, st.device, st.last_transfer = x, P, device, (0, 0)
+    veh = sc.Vehicle(wheelbase=4.0, measured_gamma=0.02, measured_speed=8.0)
+    Q = np.array([[0.25, 0.0], [0.0, (3 * math.pi / 180) ** 2]])
+    R2 = R_OBS.reshape(2, 2)
+    out = {"n": n, "what": "slamcuda.EKFSlamState (host arrays re-bound by the caller, as sim! does) with the incremental "
+                           "mirror: upload skipped when the call gets the arrays the previous call returned; predict "
+                           "downloads x[0:3] and rows / columns 0..2 of P, update all of P, add_features (k = 0) nothing"}
+    zobs = z.reshape(m, 2).T.copy()
+    t0 = time.perf_counter()
+    zf, idf, _zn = sc.associate(st, zobs, R2, 4.0, 25.0)          # first call: the state is new to the device
+    out["first_call_ms"] = (time.perf_counter() - t0) * 1e3
+    out["first_call_bytes_up_down"] = list(st.last_transfer if st.last_transfer != (0, 0) else (st._up, 0))
+
+    def timed(fn, reps):
+        ts = []
+        for _ in range(reps):
+            t1 = time.perf_counter()
+            fn()
+            ts.append(time.perf_counter() - t1)
+        ts.sort()
+        return ts[len(ts) // 2]
+
+    def do_predict():
+        st.x, st.cov = sc.predict(st, veh, Q, 0.025)
+
+    matched = []
+
+    def do_update():      # the observation step of sim! (sim/ekfslam-sim.jl:114-117) on the still-unmoved vehicle
+        zf, idf, _zn = sc.associate(st, zobs, R2, 4.0, 25.0)
+        matched.append(int(zf.shape[1]))
+        st.x, st.cov = sc.update(st, zf, R2, idf)
+
+    sec = timed(do_update, 3)
+    out["associate_update"] = {"value": 1.0 / sec, "unit": "observation steps/s", "ms": sec * 1e3, "matched": matched,
+                               "bytes_up": st.last_transfer[0], "bytes_down": st.last_transfer[1]}
+    sec = timed(do_predict, 30)
+    out["predict"] = {"value": 1.0 / sec, "unit": "predict steps/s", "ms": sec * 1e3, "bytes_up": st.last_transfer[0],
+                      "bytes_down": st.last_transfer[1]}
+
+    def do_add0():
+        st.x, st.cov = sc.add_features(st, np.zeros((2, 0)), R2)
+
+    sec = timed(do_add0, 30)
+    out["add_features_k0"] = {"value": 1.0 / sec, "unit": "calls/s", "ms": sec * 1e3, "bytes_up": 0, "bytes_down": 0}
+    t1 = time.perf_counter()
+    st.x, st.cov = sc.add_features(st, np.array([[25.0], [0.4]]), R2)
+    out["add_features_k1"] = {"ms": (time.perf_counter() - t1) * 1e3, "bytes_up": st.last_transfer[0],
+                              "bytes_down": st.last_transfer[1], "n_after": int(len(st.x))}
+    sc.slam.invalidate_mirror()
+    from slamcuda.slam import _SCRATCH
+    for hh in list(_SCRATCH.values()):
+        hh.close()
+    _SCRATCH.clear()
+    return out
+
+
 # ----------------------------------------------------------------------------------------
 # ensemble side measurement (BASELINE configs 2 and 4): filter-steps/s
 # ----------------------------------------------------------------------------------------
@@ -823,6 +897,7 @@ def main():
                     "value": 1e3 / r10["host_mirror_ms_per_step"], "unit": "update steps/s",
                     "h2d_bytes_per_step": r10["host_mirror_bytes_each_way"],
                     "d2h_bytes_per_step": r10["host_mirror_bytes_each_way"]}}
+            extras["update_10k"]["host_mirror"] = gpu_host_mirror(10000, args.m)
             extras["m_sweep_40gb"] = {k: {**v, **k6_block(alg_bytes, v["k6_ms"], peak),
                                           "k6_tflops": 2.0 * int(k) * n * (n + 1) / (v["k6_ms"] * 1e-3) / 1e12}
                                       for k, v in r.get("sweep", {}).items()}

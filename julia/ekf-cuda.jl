@@ -39,13 +39,20 @@ end
 type CudaHandle
     ptr::Ptr{Void}
     n_max::Int
+    # incremental host mirror: the host arrays the device state is known to equal (the ones the previous call
+    # returned; holding them here also keeps the garbage collector from recycling their addresses) and an O(n)
+    # digest of their contents taken at that moment
+    last_x::Vector{Float64}
+    last_cov::Matrix{Float64}
+    digest::UInt
+    mirrored::Bool
 end
 
 function CudaHandle(n_max::Integer, device::Integer=0)
     out = Ref{Ptr{Void}}(C_NULL)
     slam_check(ccall((:slam_create, libslamcuda), Cint, (Cint, Cint, Ref{Ptr{Void}}),
                      device, n_max, out))
-    h = CudaHandle(out[], n_max)
+    h = CudaHandle(out[], n_max, Float64[], Array{Float64}(0, 0), UInt(0), false)
     finalizer(h, x -> ccall((:slam_destroy, libslamcuda), Cint, (Ptr{Void},), x.ptr))
     return h
 end
@@ -78,6 +85,7 @@ Base.getindex(c::DeviceCov, rows::UnitRange{Int}, cols::UnitRange{Int}) = cov_bl
 
 function slam_upload(h::CudaHandle, x::Vector{Float64}, cov::Matrix{Float64})
     n = length(x)
+    h.mirrored = false
     slam_check(ccall((:slam_set_state, libslamcuda), Cint,
                      (Ptr{Void}, Ptr{Float64}, Ptr{Float64}, Cint, Cint), h.ptr, x, cov, n, n))
 end
@@ -130,10 +138,43 @@ function scratch_handle(n_needed::Integer)
     return SCRATCH[cap]
 end
 
+# Cheap digest of a host state: all of x, the 3 x 3 vehicle block of cov and up to 512 evenly spaced diagonal entries
+# (what a caller that re-seeds a state in place changes); an arbitrary in-place edit of cov needs forget_mirror!().
+function state_digest(x, cov)
+    n = size(cov, 1)
+    step = max(1, div(n, 512))
+    d = Float64[cov[i, i] for i in 1:step:n]
+    q = min(3, n)
+    return hash(x, hash(d, hash(cov[1:q, 1:q])))
+end
+
+"forget every device shadow: the next host-mirror call uploads its state in full"
+function forget_mirror!()
+    for h in values(SCRATCH)
+        h.mirrored = false
+    end
+end
+
+# Host-mirror mode with an incremental mirror: when the arrays handed in ARE the ones the previous call returned
+# (`state.x, state.cov = f(state, ...)` in sim! re-binds exactly those, sim/ekfslam-sim.jl:100,117,120) and their
+# digest is unchanged, nothing is uploaded.
 function with_state(state::EKFSlamState, extra::Integer=0)
     h = scratch_handle(length(state.x) + extra)
+    if h.mirrored && h.last_x === state.x && h.last_cov === state.cov &&
+       slam_length(h) == length(state.x) && h.digest == state_digest(state.x, state.cov)
+        return h
+    end
+    h.mirrored = false
     slam_upload(h, convert(Vector{Float64}, state.x), convert(Matrix{Float64}, state.cov))
     return h
+end
+
+function adopt!(h::CudaHandle, x::Vector{Float64}, cov::Matrix{Float64})
+    h.last_x = x
+    h.last_cov = cov
+    h.digest = state_digest(x, cov)
+    h.mirrored = true
+    return nothing
 end
 with_state(state::CudaEKFSlamState, extra::Integer=0) = state.h
 
@@ -154,12 +195,27 @@ end
 # host-mirror: download; predict writes through the caller's arrays (the reference aliases
 # state.x / state.cov, src/ekf.jl:10-11), update / add_features return fresh arrays.
 function finish!(state::EKFSlamState, h::CudaHandle, inplace::Bool)
+    n = slam_length(h)
+    if inplace && n == length(state.x) && isa(state.x, Vector{Float64}) && isa(state.cov, Matrix{Float64})
+        # predict changes x[1:3] and rows / columns 1:3 of cov only (src/ekf.jl:32-41): O(n) doubles come back,
+        # written straight into the caller's arrays (column-major, leading dimension n)
+        p = Array{Float64}(3)
+        slam_check(ccall((:slam_get_pose, libslamcuda), Cint, (Ptr{Void}, Ptr{Float64}), h.ptr, p))
+        state.x[1:3] = p
+        slam_check(ccall((:slam_get_cov_block, libslamcuda), Cint,
+                         (Ptr{Void}, Cint, Cint, Cint, Cint, Ptr{Float64}, Cint), h.ptr, 0, 3, 0, n, state.cov, n))
+        slam_check(ccall((:slam_get_cov_block, libslamcuda), Cint,
+                         (Ptr{Void}, Cint, Cint, Cint, Cint, Ptr{Float64}, Cint), h.ptr, 0, n, 0, 3, state.cov, n))
+        adopt!(h, state.x, state.cov)
+        return state.x, state.cov
+    end
     x, P = slam_download(h)
     if inplace && length(x) == length(state.x)
         state.x[:] = x
         state.cov[:, :] = P
         return state.x, state.cov
     end
+    adopt!(h, x, P)      # update / add_features return fresh arrays (src/ekf.jl:76,121): the next call gets these
     return x, P
 end
 # resident: P does not move; x (n doubles) is refreshed and `state.x, state.cov = f(...)` in
@@ -213,6 +269,9 @@ end
 # ---------------------------------------------------------------------------------------
 function update(state::SlamState, z, R, idf)
     m = size(z, 2)
+    if m == 0 && isa(state, EKFSlamState)
+        return state.x, state.cov          # no associated observation (first observation step of every run): no-op
+    end
     h = with_state(state)
     if m > 0
         slam_check(ccall((:slam_update, libslamcuda), Cint,
@@ -228,6 +287,9 @@ end
 # ---------------------------------------------------------------------------------------
 function add_features(state::SlamState, z, R)
     k = size(z, 2)
+    if k == 0 && isa(state, EKFSlamState)
+        return state.x, state.cov          # the reference's loop body never runs (src/ekf.jl:90)
+    end
     h = with_state(state, 2k)
     if k > 0
         # the reference's state grows without bound (hcat / vcat, src/ekf.jl:108-109): double the

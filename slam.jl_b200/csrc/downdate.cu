@@ -278,24 +278,31 @@ int downdate_chunk_width(int R) {
 // W1c: per rank chunk c (RC columns, zero padded) two copies of W1's chunk (layout: kernels.cuh):
 //   [n_pad][RC + W1_PAD] row-major, then [RC][n_pad] rank-major.
 // n_pad is a multiple of DD_ROW_PAD and rows >= n are zero.
-int launch_downdate_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad,
-                         int R, int variant, cudaStream_t s, long long *launches) {
-    if (r1 <= r0) return SLAM_OK;
-    // variant 0 = auto: the DMMA tile kernel once the rank makes the update a dense contraction
-    // (measured cross-over, profiles/r1_k6_dmma.md), the FMA kernel below it; 1 / 2 force one.
-    int min_rank = 33;   // above one FMA pass (32 ranks): 19-30 TFLOP/s DMMA vs 13-18 TFLOP/s FMA
+// Which kernel runs the downdate of R ranks: 1 = FMA, 2 = tiled DMMA, 3 = streaming DMMA (0 = none applies).
+// variant 0 = automatic (measured cross-overs, profiles/r2_k6_stream.md): FMA up to 4 ranks, streaming DMMA for 8..64,
+// tiled DMMA above; 1 / 2 / 3 force a kernel where it applies.  K5 asks too: only the FMA kernel reads the
+// rank-major W1 copy.
+int downdate_kernel_choice(int R, int variant, size_t ldb) {
+    int min_rank = 33;     // above one FMA pass (32 ranks): 19-30 TFLOP/s DMMA vs 13-18 TFLOP/s FMA
     if (const char *e = getenv("SLAM_K6_DMMA_MIN_RANK")) min_rank = atoi(e);
-    // 8..64 ranks: the streaming DMMA kernel (one pass over P, measured in profiles/r2_k6_stream.md)
     int stream_min = 8;    // R = 8: 0.505 vs 0.534 ms (FMA) at n = 20003; at 4 ranks the FMA kernel is level or ahead
     if (const char *e = getenv("SLAM_K6_STREAM_MIN_RANK")) stream_min = atoi(e);
     const int RC = downdate_chunk_width(R);
-    // (33..64 ranks are laid out as one 48- or 64-wide chunk, which only the streaming kernel reads)
-    if ((variant == 3 || (variant == 0 && R >= stream_min) || RC > 32) && downdate_stream_usable(R, ldb))
-        return launch_downdate_stream_rows(Pb, ldb, r0, r1, n, W1c, n_pad, R, s, launches);
-    if ((variant == 2 || (variant == 0 && R >= min_rank)) && downdate_dmma_usable(R, ldb))
-        return launch_downdate_dmma_rows(Pb, ldb, r0, r1, n, W1c, n_pad, R, s, launches);
-    if (RC > 32) {
-        slam_set_error("launch_downdate: no FMA kernel for a %d-wide rank chunk", RC);
+    // (33..64 ranks are laid out as one 40..64-wide chunk, which only the streaming kernel reads)
+    if ((variant == 3 || (variant == 0 && R >= stream_min) || RC > 32) && downdate_stream_usable(R, ldb)) return 3;
+    if ((variant == 2 || (variant == 0 && R >= min_rank)) && downdate_dmma_usable(R, ldb)) return 2;
+    return RC <= 32 ? 1 : 0;
+}
+
+int launch_downdate_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad,
+                         int R, int variant, cudaStream_t s, long long *launches) {
+    if (r1 <= r0) return SLAM_OK;
+    const int RC = downdate_chunk_width(R);
+    const int which = downdate_kernel_choice(R, variant, ldb);
+    if (which == 3) return launch_downdate_stream_rows(Pb, ldb, r0, r1, n, W1c, n_pad, R, s, launches);
+    if (which == 2) return launch_downdate_dmma_rows(Pb, ldb, r0, r1, n, W1c, n_pad, R, s, launches);
+    if (which == 0) {
+        slam_set_error("launch_downdate: no kernel for a %d-wide rank chunk", RC);
         return SLAM_ERR_ARG;
     }
     const int nchunks = (R + RC - 1) / RC;

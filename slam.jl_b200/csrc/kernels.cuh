@@ -20,6 +20,8 @@ inline size_t w1_workspace_doubles(int n_pad, int Rw) { return (size_t)n_pad * (
 
 // ---- K6 (downdate.cu / downdate_dmma.cu) -------------------------------------------------
 int downdate_chunk_width(int R);
+// 1 = FMA kernel, 2 = tiled DMMA, 3 = streaming DMMA, 0 = none; only the FMA kernel reads the rank-major W1 copy
+int downdate_kernel_choice(int R, int variant, size_t ldb);
 int launch_downdate(double *P, size_t ld, int n, const double *W1c, int n_pad, int R, int variant,
                     cudaStream_t s, long long *launches);
 // Rectangular form used by the row-block-sharded path: rows [r0, r1) of the upper triangle

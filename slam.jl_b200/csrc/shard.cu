@@ -509,6 +509,7 @@ __device__ __forceinline__ double sh_get(const ShardGeom &g, const double *rowbu
 __global__ void __launch_bounds__(256)
 k_sh_pht(ShardGeom g, const double *__restrict__ rowbuf, const double *__restrict__ Hn, const int *__restrict__ fp,
          int m, double *__restrict__ PHtloc) {
+    pdl_wait();   // launched behind the exchange barrier with programmatic serialization
     const int li = blockIdx.x * blockDim.x + threadIdx.x;
     const int nloc = 2 * g.slot;
     if (li >= nloc) return;
@@ -641,6 +642,7 @@ k_sh_extract_p2p(ShardGeom g, const int *__restrict__ cs, int S, int hx, ShardPe
 // stores to its peers; the release / acquire pair at system scope makes them visible to whoever
 // sees the flag.  A rank that never arrives turns into SLAM_ERR_NCCL after ~60 s instead of a hang.
 __global__ void k_sh_barrier(ShardPeers pr, int rank, int world, unsigned long long epoch, int *err) {
+    pdl_launch_dependents();   // the consumer (k_sh_pht / K6) is scheduled while this kernel spins, and waits in pdl_wait()
     const int t = threadIdx.x;
     if (t >= world) return;
     __threadfence_system();
@@ -667,7 +669,7 @@ __global__ void k_sh_barrier(ShardPeers pr, int rank, int world, unsigned long l
 constexpr int SHG_ROWS = 128;
 __global__ void __launch_bounds__(SHG_ROWS)
 k_sh_gain_p2p(ShardGeom g, int R, int RC, const double *__restrict__ PHtloc, const double *__restrict__ Cm,
-              const double *__restrict__ u, ShardPeers pr) {
+              const double *__restrict__ u, ShardPeers pr, int rank_major) {
     extern __shared__ double sh_tile[];          // [SHG_ROWS][RC + W1_PAD]: the row-major layout's rows, padding included
     const int ldk = w1_ldk(RC);
     const size_t csz = w1_chunk_doubles(g.npad, RC), rmo = w1_rank_major_offset(g.npad, RC);
@@ -690,8 +692,10 @@ k_sh_gain_p2p(ShardGeom g, int R, int RC, const double *__restrict__ PHtloc, con
                 for (int l = 0; l <= k; l++) a += PHtloc[(size_t)l * nloc + li] * Cm[(size_t)l + (size_t)k * R];
             sh_tile[t * ldk + kk] = a;
             if (live) {
-                const size_t o2 = (size_t)c * csz + rmo + (size_t)kk * g.npad + i;
-                for (int r = 0; r < g.world; r++) pr.W1c[r][o2] = a;      // rank-major copy: lanes = rows
+                if (rank_major) {   // only the FMA downdate kernel (up to 4 ranks) reads the rank-major copy
+                    const size_t o2 = (size_t)c * csz + rmo + (size_t)kk * g.npad + i;
+                    for (int r = 0; r < g.world; r++) pr.W1c[r][o2] = a;      // lanes = rows
+                }
                 if (k < R) dx += a * u[k];
             }
         }
@@ -838,7 +842,8 @@ static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const
             NCCL_TRY(g_nccl.AllReduce(s->d_rowbuf, s->d_rowbuf, (size_t)S * npad, ncclFloat64, ncclSum, s->comm, st));
     }
     if (timed) CUDA_TRY(cudaEventRecord(ev[1], st));
-    k_sh_pht<<<(nloc + 255) / 256, 256, 0, st>>>(g, s->d_rowbuf, s->d_Hn, s->d_fp, m, s->d_PHtloc);
+    CUDA_TRY(launch_pdl(k_sh_pht, dim3((nloc + 255) / 256), dim3(256), 0, st, g, (const double *)s->d_rowbuf,
+                        (const double *)s->d_Hn, (const int *)s->d_fp, m, s->d_PHtloc));
     k_sh_pht_hset<<<(S * m + 127) / 128, 128, 0, st>>>(npad, S, s->d_cs, s->d_rowbuf, s->d_Hn, m, s->d_PHtH);
     rc = launch_innov_chol(s->d_PHtH, S, s->d_Hn, s->d_fpH, s->d_v, m, R, s->d_S, s->d_C, s->d_u, s->d_err, st);
     if (rc) return rc;
@@ -848,7 +853,7 @@ static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const
         const size_t gsm = sizeof(double) * SHG_ROWS * w1_ldk(RC);
         if (gsm > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(k_sh_gain_p2p, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm));
         k_sh_gain_p2p<<<dim3((s->hb + 2 + SHG_ROWS - 1) / SHG_ROWS, 2), SHG_ROWS, gsm, st>>>(
-            g, Rk, RC, s->d_PHtloc, s->d_C, s->d_u, pr);
+            g, Rk, RC, s->d_PHtloc, s->d_C, s->d_u, pr, downdate_kernel_choice(Rk, 0, s->ldb) == 1);
         k_sh_barrier<<<1, 32, 0, st>>>(pr, s->rank, s->world, ++s->epoch, s->d_err);
         s->launches += 2;
     } else {

@@ -74,6 +74,7 @@ class _Handle:
     def __init__(self, device: int = 0, n_max: int = 256, grow: bool = True):
         self.device = device
         self.grow = grow
+        self.mirror = None      # host arrays this handle's device state is known to equal (incremental host mirror)
         self.ptr = C.c_void_p()
         check(lib.slam_create(device, n_max, C.byref(self.ptr)))
 
@@ -104,14 +105,22 @@ class _Handle:
         n = x.shape[0]
         Pf = np.asfortranarray(np.asarray(P, dtype=np.float64))
         assert Pf.shape == (n, n)
+        self.mirror = None
         check(lib.slam_set_state(self.ptr, dptr(x), dptr(Pf), n, n))
 
-    def get_state(self):
+    def get_state(self, order: str = "C"):
+        """(x, P) as fresh host arrays.  order="F" hands P back in the library's own column-major layout (no host-side
+        re-layout: what the incremental host mirror uses for large maps); "C" (default) as a C-contiguous array."""
         n = self.n
         x = np.empty(n)
         P = np.empty((n, n), order="F")
         check(lib.slam_get_state(self.ptr, dptr(x), dptr(P), n))
-        return x, np.ascontiguousarray(P)
+        return x, (P if order == "F" else np.ascontiguousarray(P))
+
+    def pose_rows(self):
+        """What predict changes (src/ekf.jl:32-41): x[0:3], rows 0..2 and columns 0..2 of P -- O(n) doubles instead of n^2."""
+        n = self.n
+        return self.get_pose(), self.cov_block(0, 3, 0, n), self.cov_block(0, n, 0, 3)
 
     def get_x(self):
         x = np.empty(self.n)
@@ -218,22 +227,61 @@ def _scratch_handle(n_needed: int, device: int = 0) -> _Handle:
     return h
 
 
+def _fingerprint(x, P):
+    """Cheap digest of a host state: all of x, the 3 x 3 vehicle block of P and up to 512 evenly spaced diagonal
+    entries (a strided gather: it must stay far below the O(n) transfer a predict makes).  The incremental host mirror
+    skips the upload when the arrays handed in ARE the ones the previous call returned (object identity) and this digest
+    still matches what was recorded then -- which catches the usual ways a caller re-seeds a state in place (new pose
+    or landmarks, reset vehicle covariance), though not an arbitrary in-place edit of P: call invalidate_mirror()
+    after one."""
+    n = P.shape[0]
+    step = max(1, n // 512)
+    d = np.ascontiguousarray(np.diagonal(P)[::step])
+    return hash((x.tobytes(), np.ascontiguousarray(P[:3, :3]).tobytes(), d.tobytes()))
+
+
+def invalidate_mirror():
+    """Forget every device shadow: the next host-mirror call uploads its state in full."""
+    for h in _SCRATCH.values():
+        h.mirror = None
+
+
 class SlamState:
     """abstract SlamState (src/common.jl:22)."""
 
 
 class EKFSlamState(SlamState):
-    """EKFSlamState{T}(x, cov) -- src/common.jl:25-28.  Host-mirror mode."""
+    """EKFSlamState{T}(x, cov) -- src/common.jl:25-28.  Host-mirror mode: x / cov are host arrays, as sim! builds and
+    re-binds them (sim/ekfslam-sim.jl:42,100,117,120).
+
+    Incremental mirror.  The device keeps a shadow of the state the previous call returned; when the next call is
+    handed those very arrays (`state.x, state.cov = f(state, ...)` re-binds them), nothing is uploaded, and only what
+    the call changed comes back: predict x[0:3] and rows / columns 0..2 of P (O(n)), update all of P, add_features
+    with k = 0 nothing.  Any other arrays (a re-seeded state) are uploaded in full, as before."""
 
     def __init__(self, x, cov, device: int = 0):
         self.x = np.array(x, dtype=np.float64).reshape(-1)
         self.cov = np.array(cov, dtype=np.float64)
         self.device = device
+        self.last_transfer = (0, 0)     # (bytes uploaded, bytes downloaded) by the last call
 
     def _upload(self, extra: int = 0) -> _Handle:
-        h = _scratch_handle(len(self.x) + extra, self.device)
+        n = len(self.x)
+        h = _scratch_handle(n + extra, self.device)
+        m = getattr(h, "mirror", None)
+        if (m is not None and m[0] is self.x and m[1] is self.cov and h.n == n and self.cov.shape == (n, n)
+                and m[2] == _fingerprint(self.x, self.cov)):
+            self._up = 0
+            return h
+        h.mirror = None
         h.set_state(self.x, self.cov)
+        self._up = 8 * n * n + 8 * n
         return h
+
+    def _adopt(self, h: _Handle, x, P, down: int):
+        """The device now mirrors the host arrays (x, P)."""
+        h.mirror = (x, P, _fingerprint(x, P))
+        self.last_transfer = (getattr(self, "_up", 0), down)
 
 
 class DeviceEKFSlamState(SlamState):
@@ -264,9 +312,13 @@ class DeviceEKFSlamState(SlamState):
 
 
 def _result(state, h: _Handle):
+    """update / add_features return fresh arrays (src/ekf.jl:76,121); resident states return themselves."""
     if isinstance(state, DeviceEKFSlamState):
         return state, state       # placeholders accepted by the setters above
-    return h.get_state()
+    n = h.n
+    x, P = h.get_state(order="F" if n > 512 else "C")
+    state._adopt(h, x, P, 8 * n * n + 8 * n)
+    return x, P
 
 
 def predict(state, vehicle, Q, dt):
@@ -275,9 +327,12 @@ def predict(state, vehicle, Q, dt):
     h.predict(vehicle.measured_gamma, vehicle.measured_speed, vehicle.wheelbase, Q, dt)
     if isinstance(state, DeviceEKFSlamState):
         return state, state
-    x, P = h.get_state()
-    state.x[:] = x
-    state.cov[:, :] = P
+    n = h.n
+    pose, rows, cols = h.pose_rows()          # all predict touches: O(n), not n^2
+    state.x[0:3] = pose
+    state.cov[0:3, :] = rows
+    state.cov[:, 0:3] = cols
+    state._adopt(h, state.x, state.cov, 8 * (3 + 6 * n))
     return state.x, state.cov
 
 
@@ -285,19 +340,28 @@ def associate(state, z, R, gate1, gate2):
     """src/data-association.jl:1-51 -> (zf 2 x m, idf 1 x m Int (1-based), zn 2 x k)."""
     h = state._upload()
     zf, idf, zn = h.associate(z, R, gate1, gate2)
+    if isinstance(state, EKFSlamState):
+        state._adopt(h, state.x, state.cov, 0)
     return zf, idf.reshape(1, -1), zn
 
 
 def update(state, z, R, idf):
-    """src/ekf.jl:46-77 -> new (x, P)."""
+    """src/ekf.jl:46-77 -> new (x, P); with no associated observation (the first observation step of every run) the
+    state as it is."""
+    if np.size(z) == 0 and isinstance(state, EKFSlamState):
+        state.last_transfer = (0, 0)
+        return state.x, state.cov
     h = state._upload()
     h.update(z, R, idf)
     return _result(state, h)
 
 
 def add_features(state, z, R):
-    """src/ekf.jl:84-122 -> augmented (x, P)."""
+    """src/ekf.jl:84-122 -> augmented (x, P); with no new observation the inputs themselves (:91 never runs)."""
     k = 0 if np.size(z) == 0 else np.asarray(z).reshape(2, -1).shape[1]
+    if k == 0 and isinstance(state, EKFSlamState):
+        state.last_transfer = (0, 0)
+        return state.x, state.cov
     h = state._upload(extra=2 * k)
     h.add_features(z, R)
     return _result(state, h)

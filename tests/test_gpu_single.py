@@ -300,6 +300,78 @@ def test_capacity_growth_matches_the_reference(sc):
     st.h.close()
 
 
+def test_incremental_host_mirror(sc):
+    """Host-mirror mode as sim! uses it (`state.x, state.cov = f(state, ...)` on host arrays, sim/ekfslam-sim.jl:100,
+    117,120): the device keeps a shadow of what the previous call returned, so a call handed those very arrays uploads
+    nothing and predict brings back O(n) doubles.  Results are bit-equal to full upload / download on every call;
+    arrays edited in place or replaced are uploaded again."""
+    from slamcuda import slam as S
+    k = ref.sim_constants()
+    Q, R, dt = k["Q"], k["R"], k["dt"]
+    rng = np.random.default_rng(12)
+    x0, P0 = _random_state(rng, 300)
+    n = len(x0)
+    full = 8 * n * n + 8 * n
+    veh = sc.Vehicle(wheelbase=4.0, measured_gamma=0.04, measured_speed=7.8)
+    ids = rng.choice(300, 5, replace=False) + 1
+
+    def obs(x):
+        z = np.zeros((2, 5))
+        for c, idf in enumerate(ids):
+            zp, _ = ref.predict_observation(x, int(idf))
+            z[:, c] = zp + rng.normal(0, [0.05, 0.005])
+        return z
+
+    z1, z2 = obs(x0), obs(x0)
+    zn = np.array([[40.0], [0.3]])
+    # A: the incremental mirror, arrays re-bound like sim!
+    st = sc.EKFSlamState(x0, P0)
+    log = []
+    for _ in range(3):
+        st.x, st.cov = sc.predict(st, veh, Q, dt); log.append(("predict",) + st.last_transfer)
+    zf, idf, _zn = sc.associate(st, z1, R, 4.0, 25.0)
+    st.x, st.cov = sc.update(st, zf, R, idf); log.append(("update",) + st.last_transfer)
+    st.x, st.cov = sc.add_features(st, np.zeros((2, 0)), R); log.append(("add0",) + st.last_transfer)
+    st.x, st.cov = sc.predict(st, veh, Q, dt); log.append(("predict",) + st.last_transfer)
+    st.x, st.cov = sc.add_features(st, zn, R); log.append(("add1",) + st.last_transfer)
+    st.x, st.cov = sc.predict(st, veh, Q, dt); log.append(("predict",) + st.last_transfer)
+    # B: the same calls with the mirror dropped before each one (full upload and download every time)
+    sb = sc.EKFSlamState(x0, P0)
+    for _ in range(3):
+        S.invalidate_mirror(); sb.x, sb.cov = sc.predict(sb, veh, Q, dt)
+    S.invalidate_mirror(); zfb, idfb, _ = sc.associate(sb, z1, R, 4.0, 25.0)
+    S.invalidate_mirror(); sb.x, sb.cov = sc.update(sb, zfb, R, idfb)
+    S.invalidate_mirror(); sb.x, sb.cov = sc.predict(sb, veh, Q, dt)
+    S.invalidate_mirror(); sb.x, sb.cov = sc.add_features(sb, zn, R)
+    S.invalidate_mirror(); sb.x, sb.cov = sc.predict(sb, veh, Q, dt)
+    assert np.array_equal(idf, idfb) and np.array_equal(st.x, sb.x) and np.array_equal(st.cov, sb.cov)
+    # ... and equal to the oracle's run of the same calls
+    xo, Po = x0.copy(), P0.copy()
+    for _ in range(3):
+        xo, Po = ref.predict(xo, Po, 0.04, 7.8, 4.0, Q, dt)
+    zfo, idfo, _ = ref.associate(xo, Po, z1, R, 4.0, 25.0)
+    xo, Po = ref.update(xo, Po, zfo, R, idfo)
+    xo, Po = ref.predict(xo, Po, 0.04, 7.8, 4.0, Q, dt)
+    xo, Po = ref.add_features(xo, Po, zn, R)
+    xo, Po = ref.predict(xo, Po, 0.04, 7.8, 4.0, Q, dt)
+    assert state_err(st.x, st.cov, xo, Po) < STEP_TOL
+    print(f"\n[host mirror n={n}] (call, bytes up, bytes down): {log}")
+    small = 8 * (3 + 6 * n)
+    assert log[0] == ("predict", full, small)                 # first call: the state is new to the device
+    assert log[1] == ("predict", 0, small) and log[2] == ("predict", 0, small)
+    assert log[3] == ("update", 0, full) and log[4] == ("add0", 0, 0) and log[5] == ("predict", 0, small)
+    assert log[6][0] == "add1" and log[7][1] == 0             # (add_features moves to a larger handle: one upload)
+    # an in-place edit of the pose is seen (digest), a replaced array is seen (identity)
+    st.x[0] += 1.0
+    st.x, st.cov = sc.predict(st, veh, Q, dt)
+    assert st.last_transfer[0] > 0
+    st.cov = st.cov.copy()
+    st.x, st.cov = sc.predict(st, veh, Q, dt)
+    assert st.last_transfer[0] > 0
+    st.x, st.cov = sc.predict(st, veh, Q, dt)
+    assert st.last_transfer[0] == 0
+
+
 def test_observation_model_and_association_values(sc):
     k = ref.sim_constants()
     R = k["R"]
