@@ -108,10 +108,13 @@ __device__ __forceinline__ void prefetch_batch(const double *warp_col, size_t ld
 // 2 x RC doubles per thread), so the second buffer costs no occupancy.
 template <int RC, int ROWS, int U, int PD, int PIPE>
 __global__ void __launch_bounds__(DD_THREADS)
-k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n_pad,
+k_downdate_fma(double *__restrict__ Pb, size_t ldb, RowMap map, int n, int n_pad,
                const double *__restrict__ W1r, const double *__restrict__ W1t) {
     constexpr int BI = DD_THREADS * ROWS;
-    const int i0 = r0 + blockIdx.x * BI;
+    static_assert(SH_PH % BI == 0, "a CTA's rows must not straddle two row panels");
+    int i0, loc0, r1;
+    if (!rowmap_tile(map, blockIdx.x, BI, n, &i0, &loc0, &r1)) return;
+    const int r0 = i0 - loc0;                         // local row of global row i is i - r0 inside this tile
     constexpr int DD_BJ = DdBj<RC>::value;
     const int j0 = blockIdx.y * DD_BJ;
     const int jend = min(j0 + DD_BJ, n);
@@ -151,11 +154,11 @@ k_downdate_fma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n
     double wi[ROWS][RC];
 #pragma unroll
     for (int k = 0; k < RC; k++) {
-        if (ROWS == 2 && (r0 & 1) == 0) {
+        if (ROWS == 2 && (i & 1) == 0) {              // (uniform over the CTA: i0 and the tile height are fixed)
             double2 t = __ldg(reinterpret_cast<const double2 *>(W1t + (size_t)k * n_pad + i));
             wi[0][k] = -t.x;
             wi[ROWS - 1][k] = -t.y;
-        } else if (ROWS == 2) {   // row blocks of the sharded path start at odd rows
+        } else if (ROWS == 2) {   // row panels of the sharded path start at odd rows
             wi[0][k] = -__ldg(W1t + (size_t)k * n_pad + i);
             // a ragged last warp may stand on row n_pad - 1: its second row does not exist (and is never used)
             wi[ROWS - 1][k] = i + 1 < n_pad ? -__ldg(W1t + (size_t)k * n_pad + i + 1) : 0.0;
@@ -232,20 +235,20 @@ DdCfg pick_cfg(int RC) {
 }
 
 template <int RC, int ROWS, int U, int PD, int PIPE>
-void launch_one(double *Pb, size_t ldb, int r0, int r1, int n, int n_pad, const double *W1r,
+void launch_one(double *Pb, size_t ldb, const RowMap &map, int n, int n_pad, const double *W1r,
                 const double *W1t, cudaStream_t s) {
     constexpr int BI = DD_THREADS * ROWS;
     constexpr int DD_BJ = DdBj<RC>::value;
-    dim3 grid((r1 - r0 + BI - 1) / BI, (n + DD_BJ - 1) / DD_BJ);
-    launch_pdl(k_downdate_fma<RC, ROWS, U, PD, PIPE>, grid, dim3(DD_THREADS), 0, s, Pb, ldb, r0, r1, n, n_pad, W1r, W1t);
+    dim3 grid((rowmap_local_rows(map) + BI - 1) / BI, (n + DD_BJ - 1) / DD_BJ);
+    launch_pdl(k_downdate_fma<RC, ROWS, U, PD, PIPE>, grid, dim3(DD_THREADS), 0, s, Pb, ldb, map, n, n_pad, W1r, W1t);
 }
 
 template <int RC>
-bool launch_cfg(const DdCfg &c, double *Pb, size_t ldb, int r0, int r1, int n, int n_pad, const double *W1r,
+bool launch_cfg(const DdCfg &c, double *Pb, size_t ldb, const RowMap &map, int n, int n_pad, const double *W1r,
                 const double *W1t, cudaStream_t s) {
 #define TRY_CFG(R_, U_, PD_, PIPE_)                                                   \
     if (c.rows == R_ && c.u == U_ && c.pd == PD_ && c.pipe == PIPE_) {                  \
-        launch_one<RC, R_, U_, PD_, PIPE_>(Pb, ldb, r0, r1, n, n_pad, W1r, W1t, s);     \
+        launch_one<RC, R_, U_, PD_, PIPE_>(Pb, ldb, map, n, n_pad, W1r, W1t, s);        \
         return true;                                                                    \
     }
     TRY_CFG(2, 8, 0, 0) TRY_CFG(2, 8, 1, 0) TRY_CFG(2, 8, 2, 0)
@@ -296,11 +299,16 @@ int downdate_kernel_choice(int R, int variant, size_t ldb) {
 
 int launch_downdate_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad,
                          int R, int variant, cudaStream_t s, long long *launches) {
-    if (r1 <= r0) return SLAM_OK;
+    return launch_downdate_map(Pb, ldb, rowmap_rows(r0, r1), n, W1c, n_pad, R, variant, s, launches);
+}
+
+int launch_downdate_map(double *Pb, size_t ldb, RowMap map, int n, const double *W1c, int n_pad, int R, int variant,
+                        cudaStream_t s, long long *launches) {
+    if (rowmap_local_rows(map) <= 0) return SLAM_OK;
     const int RC = downdate_chunk_width(R);
     const int which = downdate_kernel_choice(R, variant, ldb);
-    if (which == 3) return launch_downdate_stream_rows(Pb, ldb, r0, r1, n, W1c, n_pad, R, s, launches);
-    if (which == 2) return launch_downdate_dmma_rows(Pb, ldb, r0, r1, n, W1c, n_pad, R, s, launches);
+    if (which == 3) return launch_downdate_stream_rows(Pb, ldb, map, n, W1c, n_pad, R, s, launches);
+    if (which == 2) return launch_downdate_dmma_rows(Pb, ldb, map, n, W1c, n_pad, R, s, launches);
     if (which == 0) {
         slam_set_error("launch_downdate: no kernel for a %d-wide rank chunk", RC);
         return SLAM_ERR_ARG;
@@ -312,13 +320,13 @@ int launch_downdate_rows(double *Pb, size_t ldb, int r0, int r1, int n, const do
         const double *Wt = Wr + w1_rank_major_offset(n_pad, RC);
         bool ok = false;
         switch (RC) {
-            case 2: ok = launch_cfg<2>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
-            case 4: ok = launch_cfg<4>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
-            case 8: ok = launch_cfg<8>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
-            case 12: ok = launch_cfg<12>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
-            case 16: ok = launch_cfg<16>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
-            case 24: ok = launch_cfg<24>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
-            default: ok = launch_cfg<32>(cfg, Pb, ldb, r0, r1, n, n_pad, Wr, Wt, s); break;
+            case 2: ok = launch_cfg<2>(cfg, Pb, ldb, map, n, n_pad, Wr, Wt, s); break;
+            case 4: ok = launch_cfg<4>(cfg, Pb, ldb, map, n, n_pad, Wr, Wt, s); break;
+            case 8: ok = launch_cfg<8>(cfg, Pb, ldb, map, n, n_pad, Wr, Wt, s); break;
+            case 12: ok = launch_cfg<12>(cfg, Pb, ldb, map, n, n_pad, Wr, Wt, s); break;
+            case 16: ok = launch_cfg<16>(cfg, Pb, ldb, map, n, n_pad, Wr, Wt, s); break;
+            case 24: ok = launch_cfg<24>(cfg, Pb, ldb, map, n, n_pad, Wr, Wt, s); break;
+            default: ok = launch_cfg<32>(cfg, Pb, ldb, map, n, n_pad, Wr, Wt, s); break;
         }
         if (!ok) {
             slam_set_error("launch_downdate: no kernel for config rows=%d u=%d pd=%d", cfg.rows, cfg.u, cfg.pd);

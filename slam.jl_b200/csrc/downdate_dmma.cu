@@ -40,11 +40,14 @@ __device__ __forceinline__ void dmma(double &d0, double &d1, double a, double b)
 
 // W1c: per 32-rank chunk c, [n_pad][32 + W1_PAD] row-major at W1c + c*w1_chunk_doubles(n_pad, 32) (rows >= n are zero).
 __global__ void __launch_bounds__(MM_THREADS, MM_MIN_CTAS)
-k_downdate_dmma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n_pad,
+k_downdate_dmma(double *__restrict__ Pb, size_t ldb, RowMap map, int n, int n_pad,
                 const double *__restrict__ W1c, int nchunks) {
-    const int i0 = r0 + blockIdx.x * MM_TILE;
+    static_assert(SH_PH % MM_TILE == 0, "a tile's rows must not straddle two row panels");
+    int i0, loc0, r1;
+    if (!rowmap_tile(map, blockIdx.x, MM_TILE, n, &i0, &loc0, &r1)) return;   // past the rows of the map
+    const int r0 = i0 - loc0;                     // local row of global row i is i - r0 inside this tile
     const int j0 = blockIdx.y * MM_TILE;
-    if (i0 >= j0 + MM_TILE || i0 >= r1) return;   // below the diagonal / past the row block
+    if (i0 >= j0 + MM_TILE) return;               // below the diagonal
 
     __shared__ __align__(16) double sJ[MM_TILE * MM_LDK];   // -W1 rows of the tile's columns
     __shared__ __align__(16) double sI[MM_TILE * MM_LDK];   //  W1 rows of the tile's rows
@@ -126,12 +129,12 @@ k_downdate_dmma(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int 
 // even local row origin / leading dimension for the 16-byte accesses.
 bool downdate_dmma_usable(int R, size_t ldb) { return downdate_chunk_width(R) == MM_KC && (ldb % 2) == 0; }
 
-int launch_downdate_dmma_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad, int R,
+int launch_downdate_dmma_rows(double *Pb, size_t ldb, RowMap map, int n, const double *W1c, int n_pad, int R,
                               cudaStream_t s, long long *launches) {
-    if (r1 <= r0) return SLAM_OK;
+    if (rowmap_local_rows(map) <= 0) return SLAM_OK;
     const int nchunks = (R + MM_KC - 1) / MM_KC;
-    dim3 grid((r1 - r0 + MM_TILE - 1) / MM_TILE, (n + MM_TILE - 1) / MM_TILE);
-    k_downdate_dmma<<<grid, MM_THREADS, 0, s>>>(Pb, ldb, r0, r1, n, n_pad, W1c, nchunks);
+    dim3 grid((rowmap_local_rows(map) + MM_TILE - 1) / MM_TILE, (n + MM_TILE - 1) / MM_TILE);
+    k_downdate_dmma<<<grid, MM_THREADS, 0, s>>>(Pb, ldb, map, n, n_pad, W1c, nchunks);
     if (launches) (*launches)++;
     CUDA_TRY(cudaGetLastError());
     return SLAM_OK;

@@ -85,17 +85,20 @@ __device__ __forceinline__ void st_block(const double2 (&v)[IB], double *p, bool
     }
 }
 
-// Rows [r0, r1) of the upper triangle; element (i, j) lives at Pb[(i - r0) + j*ldb] (the single filter passes
-// r0 = 0, r1 = n, Pb = P; the sharded filter its row blocks).  W1r: [n_pad][RC + W1_PAD] row-major, rows >= n zero.
+// The rows of `map` of the upper triangle; element (i, j) lives at Pb[local row of i + j*ldb] (the single filter
+// passes rows [0, n) of P itself; the sharded filter its stack of row panels).  W1r: [n_pad][RC + W1_PAD] row-major,
+// rows >= n zero.
 template <int RC, int IB, int WARPS, int BJ, int MINB>
 __global__ void __launch_bounds__(WARPS * 32, MINB)
-k_downdate_stream(double *__restrict__ Pb, size_t ldb, int r0, int r1, int n, int n_pad, const double *__restrict__ W1r,
+k_downdate_stream(double *__restrict__ Pb, size_t ldb, RowMap map, int n, int n_pad, const double *__restrict__ W1r,
                   int pd) {
     constexpr int LDK = RC + W1_PAD, KS = RC / 4, ROWS_W = 8 * IB, BI = WARPS * ROWS_W;
-    static_assert(RC % 4 == 0 && BJ % 8 == 0 && 256 % BJ == 0, "tile shape");
+    static_assert(RC % 4 == 0 && BJ % 8 == 0 && 256 % BJ == 0 && SH_PH % BI == 0, "tile shape");
     extern __shared__ __align__(128) double sA[];               // [BJ][LDK], then the mbarrier
     uint64_t *bar = reinterpret_cast<uint64_t *>(sA + BJ * LDK);
-    const int i0 = r0 + blockIdx.x * BI;
+    int i0, loc0, r1;
+    if (!rowmap_tile(map, blockIdx.x, BI, n, &i0, &loc0, &r1)) return;
+    const int r0 = i0 - loc0;                                    // local row of global row i is i - r0 inside this tile
     const int j0 = blockIdx.y * BJ;
     const int jend = min(j0 + BJ, n);
     if (i0 >= jend) return;                                      // tile entirely below the diagonal
@@ -180,27 +183,24 @@ SCfg pick_scfg(int RC) {
 }
 
 template <int RC, int IB, int WARPS, int BJ, int MINB>
-int launch_one(double *Pb, size_t ldb, int r0, int r1, int n, int n_pad, const double *W1r, int pd, cudaStream_t s) {
+int launch_one(double *Pb, size_t ldb, const RowMap &map, int n, int n_pad, const double *W1r, int pd, cudaStream_t s) {
     constexpr int BI = WARPS * 8 * IB;
     const size_t smem = sizeof(double) * BJ * (RC + W1_PAD) + 16;
     auto kern = k_downdate_stream<RC, IB, WARPS, BJ, MINB>;
     if (smem > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid((r1 - r0 + BI - 1) / BI, (n + BJ - 1) / BJ);
-    CUDA_TRY(launch_pdl(kern, grid, dim3(WARPS * 32), smem, s, Pb, ldb, r0, r1, n, n_pad, W1r, pd));
+    dim3 grid((rowmap_local_rows(map) + BI - 1) / BI, (n + BJ - 1) / BJ);
+    CUDA_TRY(launch_pdl(kern, grid, dim3(WARPS * 32), smem, s, Pb, ldb, map, n, n_pad, W1r, pd));
     return SLAM_OK;
 }
 
 template <int RC>
-int launch_rc(const SCfg &c, double *Pb, size_t ldb, int r0, int r1, int n, int n_pad, const double *W1r, cudaStream_t s) {
+int launch_rc(const SCfg &c, double *Pb, size_t ldb, const RowMap &map, int n, int n_pad, const double *W1r, cudaStream_t s) {
     // minb = 0 in the configuration takes the first entry with matching (ib, warps, bj)
 #define TRY_S(IB_, W_, BJ_, MINB_)                                                                       \
     if (c.ib == IB_ && c.warps == W_ && c.bj == BJ_ && (c.minb == 0 || c.minb == MINB_))                 \
-        return launch_one<RC, IB_, W_, BJ_, MINB_>(Pb, ldb, r0, r1, n, n_pad, W1r, c.pd, s);
+        return launch_one<RC, IB_, W_, BJ_, MINB_>(Pb, ldb, map, n, n_pad, W1r, c.pd, s);
     if constexpr (RC <= 32) {
         TRY_S(4, 8, 64, 2) TRY_S(4, 8, 128, 2) TRY_S(4, 4, 128, 4) TRY_S(4, 4, 64, 4)
-    }
-    if constexpr (RC <= 16) {
-        TRY_S(8, 8, 64, 1)
     }
     if constexpr (RC > 16) {
         TRY_S(2, 8, 128, 2) TRY_S(2, 4, 128, 4) TRY_S(2, 8, 64, 2) TRY_S(2, 4, 64, 4)
@@ -219,23 +219,23 @@ bool downdate_stream_usable(int R, size_t ldb) {
     return R <= 64 && RC >= 4 && RC % 4 == 0 && RC >= R && (ldb % 2) == 0;
 }
 
-int launch_downdate_stream_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad, int R,
+int launch_downdate_stream_rows(double *Pb, size_t ldb, RowMap map, int n, const double *W1c, int n_pad, int R,
                                 cudaStream_t s, long long *launches) {
-    if (r1 <= r0) return SLAM_OK;
+    if (rowmap_local_rows(map) <= 0) return SLAM_OK;
     const int RC = downdate_chunk_width(R);
     const SCfg c = pick_scfg(RC);
     int rc;
     switch (RC) {
-        case 4: rc = launch_rc<4>(c, Pb, ldb, r0, r1, n, n_pad, W1c, s); break;
-        case 8: rc = launch_rc<8>(c, Pb, ldb, r0, r1, n, n_pad, W1c, s); break;
-        case 12: rc = launch_rc<12>(c, Pb, ldb, r0, r1, n, n_pad, W1c, s); break;
-        case 16: rc = launch_rc<16>(c, Pb, ldb, r0, r1, n, n_pad, W1c, s); break;
-        case 24: rc = launch_rc<24>(c, Pb, ldb, r0, r1, n, n_pad, W1c, s); break;
-        case 32: rc = launch_rc<32>(c, Pb, ldb, r0, r1, n, n_pad, W1c, s); break;
-        case 40: rc = launch_rc<40>(c, Pb, ldb, r0, r1, n, n_pad, W1c, s); break;
-        case 48: rc = launch_rc<48>(c, Pb, ldb, r0, r1, n, n_pad, W1c, s); break;
-        case 56: rc = launch_rc<56>(c, Pb, ldb, r0, r1, n, n_pad, W1c, s); break;
-        case 64: rc = launch_rc<64>(c, Pb, ldb, r0, r1, n, n_pad, W1c, s); break;
+        case 4: rc = launch_rc<4>(c, Pb, ldb, map, n, n_pad, W1c, s); break;
+        case 8: rc = launch_rc<8>(c, Pb, ldb, map, n, n_pad, W1c, s); break;
+        case 12: rc = launch_rc<12>(c, Pb, ldb, map, n, n_pad, W1c, s); break;
+        case 16: rc = launch_rc<16>(c, Pb, ldb, map, n, n_pad, W1c, s); break;
+        case 24: rc = launch_rc<24>(c, Pb, ldb, map, n, n_pad, W1c, s); break;
+        case 32: rc = launch_rc<32>(c, Pb, ldb, map, n, n_pad, W1c, s); break;
+        case 40: rc = launch_rc<40>(c, Pb, ldb, map, n, n_pad, W1c, s); break;
+        case 48: rc = launch_rc<48>(c, Pb, ldb, map, n, n_pad, W1c, s); break;
+        case 56: rc = launch_rc<56>(c, Pb, ldb, map, n, n_pad, W1c, s); break;
+        case 64: rc = launch_rc<64>(c, Pb, ldb, map, n, n_pad, W1c, s); break;
         default:
             slam_set_error("launch_downdate_stream: %d ranks are not a single chunk of 4..64", R);
             return SLAM_ERR_ARG;

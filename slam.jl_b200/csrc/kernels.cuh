@@ -18,6 +18,51 @@ __host__ __device__ inline size_t w1_rank_major_offset(int n_pad, int RC) { retu
 // upper bound of the whole workspace for any R <= Rw (chunks of width >= 4 need 2 Rpad + 4 nch <= 3 Rpad doubles per row)
 inline size_t w1_workspace_doubles(int n_pad, int Rw) { return (size_t)n_pad * (3 * (size_t)Rw + 8); }
 
+// ---- row maps: which global rows of P a launch covers and where they live in the local array -------------
+// Contiguous (single filter: r0 = 0, r1 = n): global row i at local row i - r0.
+// Panel-cyclic (large-map mode, shard.cu): P is cut into panels of SH_PH = 256 rows -- panel 0 = rows [0, 255),
+// panel p >= 1 = rows [256 p - 1, 256 p + 255): every boundary is odd, so a landmark's two rows (3 + 2k, 4 + 2k)
+// never straddle two panels -- dealt to the ranks boustrophedon, b = p mod 2W -> rank b (b < W) or 2W-1-b:
+// every group of 2W panels gives every rank one "early" and one "late" panel, so the upper-triangle work is
+// balanced at ANY state size n, not only at capacity.  A rank stacks its panels in the order they come: local
+// panel lp = 2 (p div 2W) + (b >= W), local row = 256 lp + (i - first row of p).
+constexpr int SH_PH = 256;
+__host__ __device__ inline int panel_first(int p) { return p > 0 ? SH_PH * p - 1 : 0; }
+__host__ __device__ inline int panel_of_row(int i) { return (i + 1) / SH_PH; }
+__host__ __device__ inline int panel_owner(int p, int W) {
+    const int b = p % (2 * W);
+    return b < W ? b : 2 * W - 1 - b;
+}
+__host__ __device__ inline int panel_local(int p, int W) { return 2 * (p / (2 * W)) + ((p % (2 * W)) < W ? 0 : 1); }
+__host__ __device__ inline int panel_global(int lp, int rank, int W) {
+    return (lp >> 1) * 2 * W + ((lp & 1) ? 2 * W - 1 - rank : rank);
+}
+struct RowMap {
+    int r0, r1;        // contiguous mode (world == 0): rows [r0, r1)
+    int rank, world;   // panel-cyclic mode (world >= 1)
+    int nlp;           // local panels in use
+};
+inline RowMap rowmap_rows(int r0, int r1) { return RowMap{r0, r1, 0, 0, 0}; }
+inline RowMap rowmap_panels(int rank, int world, int nlp) { return RowMap{0, 0, rank, world, nlp}; }
+// local rows a launch has to cover (grid.x = ceil(rowmap_local_rows / rows per CTA))
+inline int rowmap_local_rows(const RowMap &m) { return m.world ? m.nlp * SH_PH : m.r1 - m.r0; }
+// CTA row tile bx of BI rows (BI divides SH_PH in cyclic mode): first global row *i0, its local row *loc0, and the
+// end *r1 of the rows the tile may touch.  False when the tile is empty.
+__device__ __forceinline__ bool rowmap_tile(const RowMap &m, int bx, int BI, int n, int *i0, int *loc0, int *r1) {
+    if (m.world == 0) {
+        *i0 = m.r0 + bx * BI;
+        *loc0 = bx * BI;
+        *r1 = m.r1;
+    } else {
+        const int lrow = bx * BI, lp = lrow / SH_PH;
+        const int p = panel_global(lp, m.rank, m.world);
+        *i0 = panel_first(p) + (lrow % SH_PH);
+        *loc0 = lrow;
+        *r1 = min(panel_first(p + 1), n);
+    }
+    return *i0 < *r1;
+}
+
 // ---- K6 (downdate.cu / downdate_dmma.cu) -------------------------------------------------
 int downdate_chunk_width(int R);
 // 1 = FMA kernel, 2 = tiled DMMA, 3 = streaming DMMA, 0 = none; only the FMA kernel reads the rank-major W1 copy
@@ -28,16 +73,19 @@ int launch_downdate(double *P, size_t ld, int n, const double *W1c, int n_pad, i
 // stored as a local block Pb (element (i, j) at Pb[(i - r0) + j*ldb]), W1 rows global.
 int launch_downdate_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad,
                          int R, int variant, cudaStream_t s, long long *launches);
+// General form: the rows of `map` (element (i, j) at Pb[local row + j*ldb]).
+int launch_downdate_map(double *Pb, size_t ldb, RowMap map, int n, const double *W1c, int n_pad, int R, int variant,
+                        cudaStream_t s, long long *launches);
 
 // streaming FP64 tensor-core variant (downdate_stream.cu): ranks 12..64 in ONE pass over P, the row-side W1
 // fragments of a warp in registers, the column-side tile staged once per tile by a bulk copy
 bool downdate_stream_usable(int R, size_t ldb);
-int launch_downdate_stream_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad, int R,
+int launch_downdate_stream_rows(double *Pb, size_t ldb, RowMap map, int n, const double *W1c, int n_pad, int R,
                                 cudaStream_t s, long long *launches);
 
 // FP64 tensor-core tile variant (downdate_dmma.cu): same contract; usable for the 32-wide chunk layout
 bool downdate_dmma_usable(int R, size_t ldb);
-int launch_downdate_dmma_rows(double *Pb, size_t ldb, int r0, int r1, int n, const double *W1c, int n_pad, int R,
+int launch_downdate_dmma_rows(double *Pb, size_t ldb, RowMap map, int n, const double *W1c, int n_pad, int R,
                               cudaStream_t s, long long *launches);
 
 // ---- K2 (gate.cu, compiled with -fmad=false) ---------------------------------------------
