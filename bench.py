@@ -596,8 +596,9 @@ def gpu_ensemble(total_runs: int, rank: int, world: int, device: int, reps: int 
                "streaming_model_hbm_equiv_gbs": done * 12.4e3 / (ms * 1e-3) / 1e9}
         if fp64_peak:
             tf = flops / (ms * 1e-3) / 1e12
-            out["roofline"] = {"bound": "fp64", "achieved": tf, "peak": fp64_peak["dfma_tflops"], "unit": "TFLOP/s",
-                               "frac": tf / fp64_peak["dfma_tflops"], "flops_per_filter_step": flops / max(done, 1),
+            pk = fp64_peak["dfma_tflops"] * world     # whole-job flops against the N GPUs' DFMA rate
+            out["roofline"] = {"bound": "fp64", "achieved": tf, "peak": pk, "unit": "TFLOP/s",
+                               "frac": tf / pk, "flops_per_filter_step": flops / max(done, 1),
                                "flops_counted": flops,
                                "how": "algorithmic flops tallied in the kernel from every member's own n, nz, m "
                                       "(SURVEY.md 8d figures); peak = DFMA rate measured in this run (slam_fp64_peak)"}

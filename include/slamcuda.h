@@ -198,7 +198,8 @@ int slam_ens_capacity(slam_ens_t *e);
  * (hcat / vcat, src/ekf.jl:108-109), and so does a member by default:
  *   2 (default)  the members a launch cannot hold are re-run -- from their first step; the noise is keyed by the
  *                run id, so the result is the single-launch result -- by further launches with more
- *                shared memory per member (two CTAs per SM, then one), and finally with x, P and the
+ *                shared memory per member (two CTAs per SM, then one; when a first pass with less head-room runs
+ *                in front, the launch at slam_ens_capacity() itself is skipped), and finally with x, P and the
  *                workspace in global memory, the capacity doubling per round up to 3 + 2*(landmarks +
  *                observations of the whole run), which no run can exceed: no member ever stops for capacity;
  *   1            the shared-memory launches only;
@@ -258,14 +259,17 @@ typedef struct slam_shard slam_shard_t;
 /* 128-byte NCCL unique id created on rank 0 and handed to every rank by the host
  * launcher (torch.distributed / MPI / a file). */
 int slam_shard_unique_id(char id[128]);
-/* Rank `rank` of `world` owns row blocks rank and 2*world-1-rank of the 2*world equal row
- * blocks of P (balanced upper-triangle work).  world == 1 needs no NCCL. */
+/* P is sharded by row panels of 256 rows (panel 0 = rows [0, 255), panel p >= 1 = rows [256 p - 1, 256 p + 255): odd
+ * boundaries, a landmark's two rows never straddle), dealt boustrophedon: panel p goes to rank b = p mod 2*world when
+ * b < world, else to 2*world-1-b, so the upper-triangle work is balanced at any state size, not only at capacity
+ * (the map grows one landmark at a time, src/ekf.jl:84-122).  world == 1 needs no NCCL. */
 int slam_shard_create(int device, int rank, int world, const char id[128], int n_max,
                       slam_shard_t **out);
 int slam_shard_destroy(slam_shard_t *s);
-/* Pure partition arithmetic (no device needed): rows [lo[b], hi[b]) of the two blocks b = 0, 1
- * owned by `rank` for state size n. */
-int slam_shard_plan(int n, int world, int rank, int lo[2], int hi[2]);
+/* Pure partition arithmetic (no device needed): rows [lo[k], hi[k]) of the k-th panel `rank` owns at state size n,
+ * in the order the rank stacks them (at most `max` entries are written; lo / hi may be NULL); returns the number of
+ * panels the rank owns. */
+int slam_shard_plan(int n, int world, int rank, int *lo, int *hi, int max);
 int slam_shard_synth_state(slam_shard_t *s, int n_landmarks, double side, uint64_t seed);
 int slam_shard_n(slam_shard_t *s);
 int slam_shard_get_pose(slam_shard_t *s, double pose[3]);
@@ -284,7 +288,8 @@ int slam_shard_update(slam_shard_t *s, const double *zf, int m, const double R[4
  * collectives (SLAM_SHARD_P2P=0, world = 1, or IPC refused).  Both give bit-identical results. */
 int slam_shard_p2p(slam_shard_t *s);
 /* add_features -- src/ekf.jl:84-122 on the sharded covariance: rows 0..2 of P are broadcast from
- * rank 0, every rank fills its own rows of the 2k new columns.  Collective: call on every rank. */
+ * rank 0, every rank fills its own rows of the 2k new columns, the owner of the new rows' panel the diagonal
+ * blocks.  Collective: call on every rank. */
 int slam_shard_add_features(slam_shard_t *s, const double *zn, int k, const double R[4]);
 int slam_shard_update_resident(slam_shard_t *s, const double *d_zf, int m, const double R[4],
                                const int64_t *d_idf);

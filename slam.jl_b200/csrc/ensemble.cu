@@ -1309,6 +1309,7 @@ static int ens_prepare(slam_ens_t *e) {
     const int x1 = ens_first_extra(e);
     if (x1 < e->extra) e->tiers.push_back(ens_tier(e, x1));
     e->tiers.push_back(ens_tier(e, e->extra));
+    const bool have_first = x1 < e->extra;
     if (e->growth >= 1) {
         const int limit = e->max_shared_extra >= 0 ? e->max_shared_extra : 1 << 20;
         int x2 = -1, x3 = -1;   // largest head-room with two CTAs per SM / that fits at all
@@ -1322,6 +1323,10 @@ static int ens_prepare(slam_ens_t *e) {
                 else two = false;
             }
         }
+        // With a first pass in front and a two-CTA tier behind, the base tier is dropped: on course1 four in five of
+        // the members that outgrow the first pass outgrow the base capacity too (diverged filters roughly double
+        // their map), so that launch was a whole wave -- 5 ms of a 67 ms batch -- for 54 of 8192 members.
+        if (x2 > e->extra && have_first) e->tiers.pop_back();
         if (x2 > e->extra) e->tiers.push_back(ens_tier(e, x2));
         if (x3 > e->extra && x3 > x2) e->tiers.push_back(ens_tier(e, x3));
     }

@@ -51,17 +51,26 @@ struct Innov {     // per-landmark quantities that do not depend on the observat
 
 // Where a landmark's 5x5 sub-block comes from.  Single filter: everything from the one
 // column-major P.  Sharded filter: rows 0..2 of every column from P3 (broadcast from rank 0,
-// P3[p*npad + j]) and the landmark's 2x2 diagonal block from the owning row block.
+// P3[p*npad + j]) and the landmark's 2x2 diagonal block from the owning rank's panel stack.
 struct GateSrc {
     const double *P;      // single: full matrix; sharded: nullptr
     size_t ld;
     const double *P3;     // sharded: rows 0..2, stride npad
     int npad;
-    const double *Pb[2];  // sharded: the rank's two row blocks
-    size_t ldb;
-    int lo[2];
-    int j_first[2], j_count[2];   // landmark ids (1-based) owned: j_first[q] .. j_first[q]+j_count[q]-1
+    const double *Pl;     // sharded: the rank's row panels (kernels.cuh), leading dimension ldl
+    size_t ldl;
+    int rank, world, n;   // sharded: scan slot t = 128 * local panel + k is the k-th landmark pair of that panel
+    int Nf;               // single: landmarks 1..Nf, slot t = landmark t + 1
 };
+
+// landmark id (1-based) of scan slot t, or 0 when the slot holds no landmark of the current state
+__device__ __forceinline__ int gate_slot_landmark(const GateSrc &g, int t) {
+    if (g.P) return t < g.Nf ? t + 1 : 0;
+    const int p = panel_global(t / (SH_PH / 2), g.rank, g.world);
+    const int f = (p == 0 ? 3 : panel_first(p)) + 2 * (t % (SH_PH / 2));      // panels start on a landmark's first row
+    if (f + 1 >= min(panel_first(p + 1), g.n)) return 0;
+    return (f - 3) / 2 + 1;
+}
 
 __device__ __forceinline__ double gate_pvv(const GateSrc &g, int p, int q) {
     int a = p <= q ? p : q, b = p <= q ? q : p;
@@ -69,7 +78,7 @@ __device__ __forceinline__ double gate_pvv(const GateSrc &g, int p, int q) {
 }
 
 // 2x2 innovation covariance from the 5x5 sub-block; Pvv is the symmetric 3x3 pose block.
-__device__ __forceinline__ Innov landmark_innov(const double *__restrict__ x, const GateSrc &g, int blk, int f,
+__device__ __forceinline__ Innov landmark_innov(const double *__restrict__ x, const GateSrc &g, int f,
                                                 const double *Pvv, double xv, double yv, double phi,
                                                 const double *R) {
     double zp[2], h[10];
@@ -96,10 +105,11 @@ __device__ __forceinline__ Innov landmark_innov(const double *__restrict__ x, co
             P5[p][3] = g.P3[(size_t)p * g.npad + f];
             P5[p][4] = g.P3[(size_t)p * g.npad + f + 1];
         }
-        const double *d0 = g.Pb[blk] + (size_t)(f - g.lo[blk]) + (size_t)f * g.ldb;
+        const int p = panel_of_row(f);
+        const double *d0 = g.Pl + (size_t)panel_local(p, g.world) * SH_PH + (f - panel_first(p)) + (size_t)f * g.ldl;
         P5[3][3] = d0[0];
-        P5[3][4] = d0[g.ldb];
-        P5[4][4] = d0[g.ldb + 1];
+        P5[3][4] = d0[g.ldl];
+        P5[4][4] = d0[g.ldl + 1];
     }
 #pragma unroll
     for (int p = 0; p < 3; p++) {
@@ -285,8 +295,8 @@ k_gate(const double *__restrict__ x, GateSrc src, int Ntot, const double *__rest
         // phase A: the annulus test on x alone; survivors are compacted (warp-aggregated)
         const int t = base + threadIdx.x;
         bool keep = false;
-        if (t < Ntot) {
-            const int j = t < src.j_count[0] ? src.j_first[0] + t : src.j_first[1] + (t - src.j_count[0]);
+        const int j = t < Ntot ? gate_slot_landmark(src, t) : 0;
+        if (j > 0) {
             const int f = 3 + 2 * (j - 1);
             const double dx = x[f] - xv, dy = x[f + 1] - yv;
             const double d = sqrt(dx * dx + dy * dy);
@@ -305,10 +315,8 @@ k_gate(const double *__restrict__ x, GateSrc src, int Ntot, const double *__rest
         // phase B: full scoring of the survivors, one per thread
         const int cnt = s_cnt;
         if (threadIdx.x < cnt) {
-            const int tt = s_list[threadIdx.x];
-            const int blk = tt < src.j_count[0] ? 0 : 1;
-            const int j = blk == 0 ? src.j_first[0] + tt : src.j_first[1] + (tt - src.j_count[0]);
-            Innov L = landmark_innov(x, src, blk, 3 + 2 * (j - 1), sPvv, xv, yv, phi, prm.R);
+            const int j = gate_slot_landmark(src, s_list[threadIdx.x]);
+            Innov L = landmark_innov(x, src, 3 + 2 * (j - 1), sPvv, xv, yv, phi, prm.R);
 #pragma unroll
             for (int o = 0; o < OB; o++) {
                 double nis, nd;
@@ -452,7 +460,7 @@ __global__ void k_compute_association(const double *__restrict__ x, const double
     double Pvv[9];
     for (int p = 0; p < 3; p++)
         for (int q = 0; q < 3; q++) Pvv[p * 3 + q] = gate_pvv(src, p, q);
-    Innov L = landmark_innov(x, src, 0, 3 + 2 * ((int)idf - 1), Pvv, x[0], x[1], x[2], prm.R);
+    Innov L = landmark_innov(x, src, 3 + 2 * ((int)idf - 1), Pvv, x[0], x[1], x[2], prm.R);
     score(L, z0, z1, &out[0], &out[1]);
 }
 
@@ -524,8 +532,7 @@ int launch_gate(const double *d_x, const double *d_P, size_t ld, int Nf, const d
     GateSrc src = {};
     src.P = d_P;
     src.ld = ld;
-    src.j_first[0] = 1;
-    src.j_count[0] = Nf;
+    src.Nf = Nf;
     const int ny = (nz + OB - 1) / OB;
     int nb = gate_nblocks(Nf);
     if (d_sig2bits) {
@@ -558,8 +565,8 @@ int launch_compute_association(const double *d_x, const double *d_P, size_t ld, 
 }
 
 // Sharded gating, phase 1: this rank's landmarks -> d_rank_res[nz] (GateRes, 24 bytes each).
-int launch_gate_shard(const double *d_x, const double *d_P3, int npad, const double *const d_Pb[2], size_t ldb,
-                      const int lo[2], const int hi[2], const double *d_z, int nz, const double R[4], double gate1,
+int launch_gate_shard(const double *d_x, const double *d_P3, int npad, const double *d_Pl, size_t ldl, int rank, int world,
+                      int nlp, int n, const double *d_z, int nz, const double R[4], double gate1,
                       double gate2, void *d_scratch, size_t scratch_bytes, void *d_rank_res,
                       const unsigned long long *d_sig2bits, cudaStream_t s, long long *launches) {
     if (scratch_bytes < gate_scratch_bytes(nz)) {
@@ -575,17 +582,12 @@ int launch_gate_shard(const double *d_x, const double *d_P3, int npad, const dou
     GateSrc src = {};
     src.P3 = d_P3;
     src.npad = npad;
-    src.ldb = ldb;
-    int total = 0;
-    for (int q = 0; q < 2; q++) {
-        src.Pb[q] = d_Pb[q];
-        src.lo[q] = lo[q];
-        int f0 = lo[q] < 3 ? 3 : lo[q];          // block starts are 0 or odd; landmark rows start at 3
-        int cnt = hi[q] > f0 ? (hi[q] - f0) / 2 : 0;
-        src.j_first[q] = (f0 - 3) / 2 + 1;
-        src.j_count[q] = cnt;
-        total += cnt;
-    }
+    src.Pl = d_Pl;
+    src.ldl = ldl;
+    src.rank = rank;
+    src.world = world;
+    src.n = n;
+    const int total = nlp * (SH_PH / 2);   // scan slots: 128 landmark pairs per local panel (some empty)
     size_t per = (size_t)GATE_MAX_BLOCKS * (size_t)nz;
     unsigned *counter = (unsigned *)d_scratch;
     double *part_nd = (double *)((char *)d_scratch + 256);

@@ -108,6 +108,8 @@ int launch_compute_association(const double *d_x, const double *d_P, size_t ld, 
 // ---- synthetic state (synth.cu) -----------------------------------------------------------
 int synth_fill(double *d_x, double *d_Pb, size_t ldb, int r0, int r1, int n_landmarks, double side,
                uint64_t seed, cudaStream_t s, long long *launches);
+int synth_fill_map(double *d_x, double *d_Pl, size_t ldl, RowMap map, int n_landmarks, double side, uint64_t seed,
+                   cudaStream_t s, long long *launches);
 int synth_observations_host(int n_landmarks, double side, uint64_t seed, int m, int spurious, double *z,
                             int64_t *ids);
 int slam_require_device(int device);
@@ -118,8 +120,8 @@ int launch_innov_chol(const double *PHt, int npad, const double *Hn, const int *
 
 // ---- K2 on a row-block-sharded filter (gate.cu) ------------------------------------------
 constexpr int GATE_RES_BYTES = 24;
-int launch_gate_shard(const double *d_x, const double *d_P3, int npad, const double *const d_Pb[2], size_t ldb,
-                      const int lo[2], const int hi[2], const double *d_z, int nz, const double R[4], double gate1,
+int launch_gate_shard(const double *d_x, const double *d_P3, int npad, const double *d_Pl, size_t ldl, int rank, int world,
+                      int nlp, int n, const double *d_z, int nz, const double R[4], double gate1,
                       double gate2, void *d_scratch, size_t scratch_bytes, void *d_rank_res,
                       const unsigned long long *d_sig2bits, cudaStream_t s, long long *launches);
 int launch_gate_finalize(const void *d_all_res, int world, const double *d_z, int nz, double gate2, double *d_zf,

@@ -1,7 +1,10 @@
-// Large-map mode: one EKF-SLAM filter whose covariance is row-block-sharded over the ranks of
-// one NCCL communicator (one process per GPU).  Rank r of W owns row blocks r and 2W-1-r of
-// 2W equal blocks, so the upper-triangle work of K6 is balanced.  Each block stores rows
-// [lo, hi) of every column (element (i, j) at Pb[(i - lo) + j*ldb]); only i <= j is live.
+// Large-map mode: one EKF-SLAM filter whose covariance is sharded by ROW PANELS over the ranks of one NCCL
+// communicator (one process per GPU).  P is cut into panels of 256 rows (panel 0 = rows [0, 255), panel p >= 1 =
+// rows [256 p - 1, 256 p + 255): odd boundaries, so a landmark's two rows never straddle) dealt boustrophedon --
+// panel p goes to rank b = p mod 2W if b < W, else 2W-1-b -- so every group of 2W panels gives each rank one early
+// and one late panel and the upper-triangle work of K6 is balanced at ANY state size (the map grows one landmark
+// at a time, src/ekf.jl:84-122), not only at capacity.  A rank stacks its panels in one array: local panel
+// lp = 2 (p div 2W) + (b >= W), element (i, j) at Pl[256 lp + (i - first row of p) + j*ldl]; only i <= j is live.
 //
 // update (src/ekf.jl:46-77) per rank:
 //   1. prep      Hn / fp / v from the replicated x (every rank, identical)
@@ -13,14 +16,14 @@
 //   5. W1 = PHt*C for the rank's rows                                           -> send buffer
 //   6. ncclAllGather of W1 (n x 2m doubles in total)
 //   7. unpermute into K6's two W1 layouts, x += W1*u for every row (x stays replicated)
-//   8. K6 on the two owned row blocks.
+//   8. K6 on the rank's panels (one launch, kernels.cuh RowMap).
 //
 // Peer-memory exchange (default when the ranks can map each other's memory: CUDA IPC over NVLink /
 // NVSwitch).  Steps 2+3 and 5+6+7 become one kernel each that STORES its result into every rank's
 // buffer, followed by a flag barrier in peer memory:
 //   2'. extract_p2p   the owner of row c writes P[c, c:n] into rowbuf[s] of every rank (1.6 MB per row at
 //                     n = 200k, instead of an allreduce of S x n mostly-zero doubles)
-//   5'. gain_p2p      W1 for the rank's own rows, written straight into every rank's two K6 layouts, and
+//   5'. gain_p2p      W1 for the rank's own rows, written straight into every rank's K6 layouts, and
 //                     x += W1*u into every rank's x (no send buffer, no gathered copy, no unpermute pass)
 // The arithmetic per element is the NCCL path's, so both give bit-identical x and P; SLAM_SHARD_P2P=0
 // keeps the NCCL path (also the fallback when IPC is refused).
@@ -92,34 +95,29 @@ int load_nccl() {
     } while (0)
 
 // ---------------------------------------------------------------------------------------
-// partition arithmetic (no device needed)
+// partition arithmetic (no device needed); the panel functions themselves are in kernels.cuh
 // ---------------------------------------------------------------------------------------
-static int block_height(int n, int world) {
-    int hb = (n + 2 * world - 1) / (2 * world);
-    return round_up(hb, 256);   // K6 row tiles never straddle two blocks
+// local panels rank `rank` of `world` holds when the state has n rows
+static int local_panels(int n, int world, int rank) {
+    if (n <= 0) return 0;
+    const int np = panel_of_row(n - 1) + 1;           // global panels in use
+    int cnt = 0;                                      // panel_global grows with the local index
+    while (panel_global(cnt, rank, world) < np) cnt++;
+    return cnt;
 }
 
-// Block b covers rows [block_lo(b), block_lo(b+1)).  Boundaries other than 0 are odd, so a
-// landmark's two rows (3 + 2k, 4 + 2k) never straddle two blocks (the gating kernel reads the
-// landmark's 2x2 diagonal block from one owner).
-__host__ __device__ static inline int block_lo(int b, int hb, int n) {
-    if (b <= 0) return 0;
-    long long v = (long long)b * hb + 1;
-    return v < n ? (int)v : n;
-}
-
-static void plan_blocks(int n, int hb, int world, int rank, int lo[2], int hi[2]) {
-    const int b[2] = {rank, 2 * world - 1 - rank};
-    for (int q = 0; q < 2; q++) {
-        lo[q] = block_lo(b[q], hb, n);
-        hi[q] = b[q] == 2 * world - 1 ? n : block_lo(b[q] + 1, hb, n);
+// Rows [lo[k], hi[k]) of every panel rank owns at state size n, in local order (empty panels included as lo == hi
+// so that index k is the local panel number); returns the number of local panels, fills at most `max` entries.
+extern "C" int slam_shard_plan(int n, int world, int rank, int *lo, int *hi, int max) {
+    ARG_CHECK(n >= 3 && world >= 1 && rank >= 0 && rank < world, "bad argument");
+    const int nlp = local_panels(n, world, rank);
+    for (int lp = 0; lp < nlp && lp < max; lp++) {
+        const int p = panel_global(lp, rank, world);
+        const int a = std::min(panel_first(p), n), b = std::min(panel_first(p + 1), n);
+        if (lo) lo[lp] = a;
+        if (hi) hi[lp] = b;
     }
-}
-
-extern "C" int slam_shard_plan(int n, int world, int rank, int lo[2], int hi[2]) {
-    ARG_CHECK(n >= 3 && world >= 1 && rank >= 0 && rank < world && lo && hi, "bad argument");
-    plan_blocks(n, block_height(n, world), world, rank, lo, hi);
-    return SLAM_OK;
+    return nlp;
 }
 
 extern "C" int slam_shard_unique_id(char id[128]) {
@@ -137,7 +135,8 @@ constexpr int SH_MAXW = 16;   // ranks the peer-memory exchange handles (one NVS
 
 struct slam_shard {
     int device = 0, rank = 0, world = 1;
-    int n_max = 0, n = 3, hb = 0;
+    int n_max = 0, n = 3;
+    int nloc = 0, nlp = 0;      // local row capacity (256 x local panels at n_max) and local panels in use at n
     // peer-memory exchange
     bool p2p = false;
     void *arenaA = nullptr, *arenaB = nullptr;          // peer-visible: [x | flags], [rowbuf | W1c]
@@ -146,12 +145,11 @@ struct slam_shard {
     unsigned long long epoch = 0;
     char *d_ipc = nullptr;
     int *d_agree = nullptr;
-    int lo[2] = {0, 0}, hi[2] = {0, 0};
-    size_t ldb = 0;
+    size_t ldl = 0;             // leading dimension of the local panel stack
     ncclComm_t comm = nullptr;
     cudaStream_t stream = nullptr;
     double *d_x = nullptr;
-    double *d_Pb[2] = {nullptr, nullptr};
+    double *d_Pl = nullptr;     // the rank's row panels, stacked: [ldl][n_max] column-major
     int *d_err = nullptr;
     void *h_pin = nullptr;
     double *d_zf = nullptr, *d_z = nullptr, *d_zn = nullptr;
@@ -243,7 +241,7 @@ extern "C" int slam_shard_destroy(slam_shard_t *s) {
     }
     if (s->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(s->comm);   // the ranks meet here before anything is freed
     cudaFree(s->arenaA); cudaFree(s->arenaB); cudaFree(s->d_ipc); cudaFree(s->d_agree);
-    cudaFree(s->d_Pb[0]); cudaFree(s->d_Pb[1]); cudaFree(s->d_err);
+    cudaFree(s->d_Pl); cudaFree(s->d_err);
     cudaFree(s->d_zf); cudaFree(s->d_z); cudaFree(s->d_zn); cudaFree(s->d_idf);
     cudaFree(s->d_PHtloc); cudaFree(s->d_PHtH); cudaFree(s->d_S); cudaFree(s->d_C);
     cudaFree(s->d_u); cudaFree(s->d_v); cudaFree(s->d_Hn); cudaFree(s->d_W1send); cudaFree(s->d_W1gath);
@@ -267,8 +265,13 @@ extern "C" int slam_shard_create(int device, int rank, int world, const char id[
     if (rc) return rc;
     slam_shard_t *s = new slam_shard();
     s->device = device; s->rank = rank; s->world = world; s->n_max = n_max;
-    s->hb = block_height(n_max, world);
-    s->ldb = (size_t)s->hb + 16;
+    s->nloc = SH_PH * local_panels(n_max, world, rank);
+    {   // the same local capacity on every rank (buffers indexed by local row are exchanged): the largest count
+        int mx = 0;
+        for (int r = 0; r < world; r++) mx = std::max(mx, local_panels(n_max, world, r));
+        s->nloc = SH_PH * mx;
+    }
+    s->ldl = (size_t)s->nloc + 16;
     s->npad = round_up(n_max, DD_ROW_PAD);
 #define SH_TRY(expr)                                                                             \
     do {                                                                                         \
@@ -286,7 +289,7 @@ extern "C" int slam_shard_create(int device, int rank, int world, const char id[
     SH_TRY(cudaMemsetAsync(s->flags, 0, sizeof(unsigned long long) * SH_MAXW, s->stream));
     SH_TRY(cudaMalloc(&s->d_ipc, (size_t)SH_MAXW * sizeof(cudaIpcMemHandle_t)));
     SH_TRY(cudaMalloc(&s->d_agree, sizeof(int)));
-    for (int q = 0; q < 2; q++) SH_TRY(cudaMalloc(&s->d_Pb[q], sizeof(double) * s->ldb * (size_t)n_max));
+    SH_TRY(cudaMalloc(&s->d_Pl, sizeof(double) * s->ldl * (size_t)n_max));
     SH_TRY(cudaMalloc(&s->d_err, sizeof(int)));
     SH_TRY(cudaMemsetAsync(s->d_err, 0, sizeof(int), s->stream));
     SH_TRY(cudaMalloc(&s->d_sig2, sizeof(unsigned long long) * 4));
@@ -321,8 +324,8 @@ extern "C" int slam_shard_create(int device, int rank, int world, const char id[
         rc = shard_share(s, s->arenaA, s->peerA, want, &s->p2p);
         if (rc) { slam_shard_destroy(s); return rc; }
     }
-    plan_blocks(3, s->hb, world, rank, s->lo, s->hi);
     s->n = 3;
+    s->nlp = local_panels(3, world, rank);
     *out = s;
     return SLAM_OK;
 }
@@ -360,13 +363,16 @@ extern "C" int slam_shard_sync(slam_shard_t *s) {
     return shard_check_latched(s);
 }
 
-// max over P[f, f], f in [f0, hi), of a row block (element (i, j) at Pb[(i - lo) + j*ldb]) as the bit pattern of a
-// non-negative double (same convention as k_sig2_diag in gate.cu: NaN -> a pattern above +inf, negatives ignored)
-__global__ void k_sh_sig2_diag(const double *__restrict__ Pb, size_t ldb, int lo, int f0, int hi,
+// max over P[f, f] of the landmark rows f this rank owns, as the bit pattern of a non-negative double (same
+// convention as k_sig2_diag in gate.cu: NaN -> a pattern above +inf, negatives ignored)
+__global__ void k_sh_sig2_diag(const double *__restrict__ Pl, size_t ldl, int rank, int world, int nlp, int n,
                                unsigned long long *sig2bits) {
     unsigned long long mine = 0ull;
-    for (int f = f0 + blockIdx.x * blockDim.x + threadIdx.x; f < hi; f += gridDim.x * blockDim.x) {
-        const double v = Pb[(size_t)(f - lo) + (size_t)f * ldb];
+    for (int li = blockIdx.x * blockDim.x + threadIdx.x; li < nlp * SH_PH; li += gridDim.x * blockDim.x) {
+        const int p = panel_global(li / SH_PH, rank, world);
+        const int f = panel_first(p) + li % SH_PH;
+        if (f < 3 || f >= min(panel_first(p + 1), n)) continue;
+        const double v = Pl[(size_t)li + (size_t)f * ldl];
         unsigned long long b = (unsigned long long)__double_as_longlong(v);
         if (v != v) b = 0x7ff8000000000000ull;
         else if (v < 0.0) b = 0ull;
@@ -389,19 +395,15 @@ extern "C" int slam_shard_synth_state(slam_shard_t *s, int n_landmarks, double s
         return SLAM_ERR_CAPACITY;
     }
     s->n = n;
-    // block boundaries follow the capacity's block height so that growth never moves rows
-    plan_blocks(n, s->hb, s->world, s->rank, s->lo, s->hi);
+    s->nlp = local_panels(n, s->world, s->rank);
     CUDA_TRY(cudaMemsetAsync(s->d_sig2, 0, sizeof(unsigned long long), s->stream));
-    for (int q = 0; q < 2; q++) {
-        int rc = synth_fill(s->d_x, s->d_Pb[q], s->ldb, s->lo[q], s->hi[q], n_landmarks, side, seed, s->stream,
-                            &s->launches);
-        if (rc) return rc;
-        const int f0 = std::max(s->lo[q], 3);
-        if (s->hi[q] > f0) {   // the pre-gate's bound: exact maximum over the diagonal entries this rank owns
-            k_sh_sig2_diag<<<std::min((s->hi[q] - f0 + 255) / 256, 296), 256, 0, s->stream>>>(
-                s->d_Pb[q], s->ldb, s->lo[q], f0, s->hi[q], s->d_sig2);
-            s->launches++;
-        }
+    int rc = synth_fill_map(s->d_x, s->d_Pl, s->ldl, rowmap_panels(s->rank, s->world, s->nlp), n_landmarks, side, seed,
+                            s->stream, &s->launches);
+    if (rc) return rc;
+    if (s->nlp > 0) {   // the pre-gate's bound: exact maximum over the diagonal entries this rank owns
+        k_sh_sig2_diag<<<std::min((s->nlp * SH_PH + 255) / 256, 296), 256, 0, s->stream>>>(
+            s->d_Pl, s->ldl, s->rank, s->world, s->nlp, n, s->d_sig2);
+        s->launches++;
     }
     CUDA_TRY(cudaGetLastError());
     return SLAM_OK;
@@ -425,20 +427,22 @@ extern "C" int slam_shard_get_x(slam_shard_t *s, double *x) {
     return SLAM_OK;
 }
 
-// owned entries (i <= j, row i in one of this rank's blocks) of the requested window; others untouched
+// owned entries (row i in one of this rank's panels) of the requested window; others untouched
 extern "C" int slam_shard_get_cov_block(slam_shard_t *s, int i0, int ni, int j0, int nj, double *out, int ldo) {
     S_CHECK(s);
     ARG_CHECK(out && i0 >= 0 && j0 >= 0 && ni >= 0 && nj >= 0 && i0 + ni <= s->n && j0 + nj <= s->n && ldo >= ni,
               "bad window");
     int copied = 0;
     CUDA_TRY(cudaStreamSynchronize(s->stream));
-    for (int q = 0; q < 2; q++) {
-        int a = std::max(i0, s->lo[q]), b = std::min(i0 + ni, s->hi[q]);
+    if (ni == 0 || nj == 0) return 0;
+    for (int p = panel_of_row(i0); p <= panel_of_row(i0 + ni - 1); p++) {
+        if (panel_owner(p, s->world) != s->rank) continue;
+        const int a = std::max(i0, panel_first(p)), b = std::min(i0 + ni, std::min(panel_first(p + 1), s->n));
         if (a >= b) continue;
-        // rows [a, b) of columns [j0, j0+nj): strided 2-D copy out of the block
-        CUDA_TRY(cudaMemcpy2D(out + (a - i0), sizeof(double) * (size_t)ldo,
-                              s->d_Pb[q] + (size_t)(a - s->lo[q]) + (size_t)j0 * s->ldb, sizeof(double) * s->ldb,
-                              sizeof(double) * (b - a), nj, cudaMemcpyDeviceToHost));
+        const size_t li = (size_t)panel_local(p, s->world) * SH_PH + (a - panel_first(p));
+        // rows [a, b) of columns [j0, j0+nj): strided 2-D copy out of the panel stack
+        CUDA_TRY(cudaMemcpy2D(out + (a - i0), sizeof(double) * (size_t)ldo, s->d_Pl + li + (size_t)j0 * s->ldl,
+                              sizeof(double) * s->ldl, sizeof(double) * (b - a), nj, cudaMemcpyDeviceToHost));
         copied += (b - a) * nj;
     }
     return copied;
@@ -448,18 +452,24 @@ extern "C" int slam_shard_get_cov_block(slam_shard_t *s, int i0, int ni, int j0,
 // update kernels
 // ---------------------------------------------------------------------------------------
 struct ShardGeom {
-    int rank, world, hb, slot, n, npad;   // slot = rows reserved per block in rank-local buffers
-    int lo[2], hi[2];
-    size_t ldb;
-    double *Pb[2];
+    int rank, world, n, npad;
+    int nloc;          // local row capacity = rows reserved per rank in rank-local buffers (PHtloc, W1send)
+    int nlp;           // local panels in use at this n
+    size_t ldl;
+    double *Pl;        // the rank's panel stack: element (i, j) at Pl[local row of i + j*ldl]
 };
 
-__device__ __forceinline__ void row_owner(const ShardGeom &g, int i, int *owner, int *q, int *li) {
-    int b = i <= 0 ? 0 : (i - 1) / g.hb;
-    if (b > 2 * g.world - 1) b = 2 * g.world - 1;
-    *q = b < g.world ? 0 : 1;
-    *owner = b < g.world ? b : 2 * g.world - 1 - b;
-    *li = *q * g.slot + (i - block_lo(b, g.hb, g.n));
+// owner and local row of global row i
+__device__ __forceinline__ void row_owner(const ShardGeom &g, int i, int *owner, int *li) {
+    const int p = panel_of_row(i);
+    *owner = panel_owner(p, g.world);
+    *li = panel_local(p, g.world) * SH_PH + (i - panel_first(p));
+}
+// global row of local row li of this rank, or -1 when that slot holds no row of the current state
+__device__ __forceinline__ int local_row_global(const ShardGeom &g, int li) {
+    const int p = panel_global(li / SH_PH, g.rank, g.world);
+    const int i = panel_first(p) + li % SH_PH;
+    return i < min(panel_first(p + 1), g.n) ? i : -1;
 }
 
 // step 1: observation model for every associated observation, innovation v, and the list cs of
@@ -493,16 +503,16 @@ __global__ void k_sh_extract(ShardGeom g, const int *__restrict__ cs, double *__
     const int s = blockIdx.y;
     if (j >= g.npad) return;
     const int c = cs[s];
-    int owner, q, li;
-    row_owner(g, c, &owner, &q, &li);
+    int owner, li;
+    row_owner(g, c, &owner, &li);
     double val = 0.0;
-    if (owner == g.rank && j >= c && j < g.n) val = g.Pb[q][(size_t)(c - g.lo[q]) + (size_t)j * g.ldb];
+    if (owner == g.rank && j >= c && j < g.n) val = g.Pl[(size_t)li + (size_t)j * g.ldl];
     rowbuf[(size_t)s * g.npad + j] = val;
 }
 
-// P[i, cs[s]] for a row i this rank owns (block q): local when cs[s] >= i, else from the gathered row
-__device__ __forceinline__ double sh_get(const ShardGeom &g, const double *rowbuf, int q, int i, int s, int c) {
-    return c >= i ? g.Pb[q][(size_t)(i - g.lo[q]) + (size_t)c * g.ldb] : rowbuf[(size_t)s * g.npad + i];
+// P[i, cs[s]] for a row i this rank owns (local row li): local when cs[s] >= i, else from the gathered row
+__device__ __forceinline__ double sh_get(const ShardGeom &g, const double *rowbuf, int li, int i, int s, int c) {
+    return c >= i ? g.Pl[(size_t)li + (size_t)c * g.ldl] : rowbuf[(size_t)s * g.npad + i];
 }
 
 // step 4a: PHt rows of the rank's own rows (src/ekf.jl:67), rank-major over the local row index
@@ -511,24 +521,23 @@ k_sh_pht(ShardGeom g, const double *__restrict__ rowbuf, const double *__restric
          int m, double *__restrict__ PHtloc) {
     pdl_wait();   // launched behind the exchange barrier with programmatic serialization
     const int li = blockIdx.x * blockDim.x + threadIdx.x;
-    const int nloc = 2 * g.slot;
+    const int nloc = g.nloc;
     if (li >= nloc) return;
-    const int q = li / g.slot;
-    const int i = g.lo[q] + (li - q * g.slot);
-    const bool live = i < g.hi[q];
+    const int i = li < g.nlp * SH_PH ? local_row_global(g, li) : -1;
+    const bool live = i >= 0;
     double p0 = 0, p1 = 0, p2 = 0;
     if (live) {
-        p0 = sh_get(g, rowbuf, q, i, 0, 0);
-        p1 = sh_get(g, rowbuf, q, i, 1, 1);
-        p2 = sh_get(g, rowbuf, q, i, 2, 2);
+        p0 = sh_get(g, rowbuf, li, i, 0, 0);
+        p1 = sh_get(g, rowbuf, li, i, 1, 1);
+        p2 = sh_get(g, rowbuf, li, i, 2, 2);
     }
     for (int o = 0; o < m; o++) {
         double a0 = 0, a1 = 0;
         if (live) {
             const double *hh = Hn + 10 * o;
             const int f = fp[o];
-            double p3 = sh_get(g, rowbuf, q, i, 3 + 2 * o, f);
-            double p4 = sh_get(g, rowbuf, q, i, 3 + 2 * o + 1, f + 1);
+            double p3 = sh_get(g, rowbuf, li, i, 3 + 2 * o, f);
+            double p4 = sh_get(g, rowbuf, li, i, 3 + 2 * o + 1, f + 1);
             a0 = p0 * hh[0] + p1 * hh[1] + p2 * hh[2] + p3 * hh[6] + p4 * hh[7];
             a1 = p0 * hh[3] + p1 * hh[4] + p2 * hh[5] + p3 * hh[8] + p4 * hh[9];
         }
@@ -576,10 +585,10 @@ k_sh_unpermute(ShardGeom g, int R, int RC, const double *__restrict__ W1gath, co
                double *__restrict__ W1c, double *__restrict__ x) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.npad) return;
-    const int nch = (R + RC - 1) / RC, nloc = 2 * g.slot;
-    int owner = 0, q = 0, li = 0;
+    const int nch = (R + RC - 1) / RC, nloc = g.nloc;
+    int owner = 0, li = 0;
     const bool live = i < g.n;
-    if (live) row_owner(g, i, &owner, &q, &li);
+    if (live) row_owner(g, i, &owner, &li);
     double dx = 0;
     const int ldk = w1_ldk(RC);
     const size_t csz = w1_chunk_doubles(g.npad, RC), rmo = w1_rank_major_offset(g.npad, RC);
@@ -616,23 +625,23 @@ __global__ void __launch_bounds__(256)
 k_sh_extract_p2p(ShardGeom g, const int *__restrict__ cs, int S, int hx, ShardPeers pr) {
     const int s = blockIdx.y;
     const int c = cs[s];
-    int owner, q, li;
-    row_owner(g, c, &owner, &q, &li);
+    int owner, li;
+    row_owner(g, c, &owner, &li);
     if (owner != g.rank) return;
-    const double *row = g.Pb[q] + (size_t)(c - g.lo[q]);
+    const double *row = g.Pl + (size_t)li;
     if ((int)blockIdx.x < hx) {
         const int j = blockIdx.x * blockDim.x + threadIdx.x;
         if (j < c || j >= g.npad) return;
-        const double val = j < g.n ? row[(size_t)j * g.ldb] : 0.0;
-        int oj, qj, lj;
-        row_owner(g, j, &oj, &qj, &lj);
+        const double val = j < g.n ? row[(size_t)j * g.ldl] : 0.0;
+        int oj, lj;
+        row_owner(g, j, &oj, &lj);
         pr.rowbuf[oj][(size_t)s * g.npad + j] = val;
     } else {
         const int t = (blockIdx.x - hx) * blockDim.x + threadIdx.x;
         if (t >= S) return;
         const int j = cs[t];
         if (j < c) return;
-        const double val = row[(size_t)j * g.ldb];
+        const double val = row[(size_t)j * g.ldl];
         for (int r = 0; r < g.world; r++) pr.rowbuf[r][(size_t)s * g.npad + j] = val;
     }
 }
@@ -673,13 +682,15 @@ k_sh_gain_p2p(ShardGeom g, int R, int RC, const double *__restrict__ PHtloc, con
     extern __shared__ double sh_tile[];          // [SHG_ROWS][RC + W1_PAD]: the row-major layout's rows, padding included
     const int ldk = w1_ldk(RC);
     const size_t csz = w1_chunk_doubles(g.npad, RC), rmo = w1_rank_major_offset(g.npad, RC);
-    const int q = blockIdx.y;
-    const int r0 = blockIdx.x * SHG_ROWS;        // first local row of the CTA inside block q
-    const int rows = min(SHG_ROWS, g.hi[q] - g.lo[q] - r0);
+    // a CTA = SHG_ROWS consecutive local rows, all inside one panel (SHG_ROWS divides the panel height)
+    const int l0 = blockIdx.x * SHG_ROWS;        // first local row of the CTA
+    const int p = panel_global(l0 / SH_PH, g.rank, g.world);
+    const int i0 = panel_first(p) + l0 % SH_PH;
+    const int rows = min(SHG_ROWS, min(panel_first(p + 1), g.n) - i0);
     if (rows <= 0) return;
     const int t = threadIdx.x;
-    const int li = q * g.slot + r0 + t, nloc = 2 * g.slot;
-    const int i0 = g.lo[q] + r0, i = i0 + t;
+    const int li = l0 + t, nloc = g.nloc;
+    const int i = i0 + t;
     const bool live = t < rows;
     const int nch = (R + RC - 1) / RC;
     double dx = 0;
@@ -741,9 +752,8 @@ static ShardPeers shard_peers(const slam_shard_t *s, size_t rowbuf_doubles) {
 }
 static ShardGeom geom(const slam_shard_t *s) {
     ShardGeom g;
-    g.rank = s->rank; g.world = s->world; g.hb = s->hb; g.slot = s->hb + 2; g.n = s->n; g.npad = s->npad;
-    for (int q = 0; q < 2; q++) { g.lo[q] = s->lo[q]; g.hi[q] = s->hi[q]; g.Pb[q] = s->d_Pb[q]; }
-    g.ldb = s->ldb;
+    g.rank = s->rank; g.world = s->world; g.n = s->n; g.npad = s->npad;
+    g.nloc = s->nloc; g.nlp = s->nlp; g.ldl = s->ldl; g.Pl = s->d_Pl;
     return g;
 }
 
@@ -772,7 +782,7 @@ static int shard_ensure_ws(slam_shard_t *s, int R) {
     cudaFree(s->d_fp); cudaFree(s->d_fpH); cudaFree(s->d_cs);
     s->d_fp = s->d_fpH = s->d_cs = nullptr;
     s->ws_R = 0;
-    const size_t S = 3 + Rw, nloc = 2 * ((size_t)s->hb + 2), npad = s->npad;
+    const size_t S = 3 + Rw, nloc = (size_t)s->nloc, npad = s->npad;
     CUDA_TRY(cudaMalloc(&s->arenaB, sizeof(double) * (S * npad + w1_workspace_doubles((int)npad, Rw))));
     s->d_rowbuf = (double *)s->arenaB;
     s->d_W1c = s->d_rowbuf + S * npad;
@@ -813,7 +823,7 @@ static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const
     int rc = shard_ensure_ws(s, Rk);
     if (rc) return rc;
     const int RC = downdate_chunk_width(Rk), nch = (Rk + RC - 1) / RC;
-    const int nloc = 2 * (s->hb + 2), npad = s->npad;
+    const int nloc = s->nloc, npad = s->npad;
     const ShardGeom g = geom(s);
     cudaStream_t st = s->stream;
     // profiling: five events per update -- start, H rows exchanged, before the gain, K6 start, end
@@ -852,8 +862,8 @@ static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const
     if (p2p) {
         const size_t gsm = sizeof(double) * SHG_ROWS * w1_ldk(RC);
         if (gsm > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(k_sh_gain_p2p, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm));
-        k_sh_gain_p2p<<<dim3((s->hb + 2 + SHG_ROWS - 1) / SHG_ROWS, 2), SHG_ROWS, gsm, st>>>(
-            g, Rk, RC, s->d_PHtloc, s->d_C, s->d_u, pr, downdate_kernel_choice(Rk, 0, s->ldb) == 1);
+        k_sh_gain_p2p<<<dim3(std::max(s->nlp * SH_PH / SHG_ROWS, 1)), SHG_ROWS, gsm, st>>>(
+            g, Rk, RC, s->d_PHtloc, s->d_C, s->d_u, pr, downdate_kernel_choice(Rk, 0, s->ldl) == 1);
         k_sh_barrier<<<1, 32, 0, st>>>(pr, s->rank, s->world, ++s->epoch, s->d_err);
         s->launches += 2;
     } else {
@@ -868,9 +878,8 @@ static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const
     }
     CUDA_TRY(cudaGetLastError());
     if (timed) CUDA_TRY(cudaEventRecord(ev[3], st));
-    for (int q = 0; q < 2 && rc == SLAM_OK; q++)
-        rc = launch_downdate_rows(s->d_Pb[q], s->ldb, s->lo[q], s->hi[q], s->n, s->d_W1c, npad, Rk, 0, st,
-                                  &s->launches);
+    rc = launch_downdate_map(s->d_Pl, s->ldl, rowmap_panels(s->rank, s->world, s->nlp), s->n, s->d_W1c, npad, Rk, 0, st,
+                             &s->launches);
     if (timed) {
         CUDA_TRY(cudaEventRecord(ev[4], st));
         s->ev_used += 5;
@@ -1013,7 +1022,7 @@ extern "C" int slam_shard_predict(slam_shard_t *s, double g, double v, double wh
     memcpy(p.Q, Q, sizeof(p.Q));
     if (s->rank == 0) {
         int blocks = std::max(1, (s->n - 3 + 255) / 256);
-        k_sh_predict_P<<<blocks, 256, 0, s->stream>>>(s->d_x, s->d_Pb[0], s->ldb, s->n, p);
+        k_sh_predict_P<<<blocks, 256, 0, s->stream>>>(s->d_x, s->d_Pl, s->ldl, s->n, p);   // panel 0 = rank 0's local rows 0..
         s->launches++;
     }
     k_sh_predict_x<<<1, 1, 0, s->stream>>>(s->d_x, p);   // stream order: after the columns read x[2]
@@ -1058,11 +1067,11 @@ extern "C" int slam_shard_associate(slam_shard_t *s, const double *z, int nz, co
     memcpy(hz, z, sizeof(double) * 2 * nz);
     CUDA_TRY(cudaMemcpyAsync(s->d_z, hz, sizeof(double) * 2 * nz, cudaMemcpyHostToDevice, st));
     if (s->rank == 0) {
-        k_sh_rows012<<<(s->npad + 255) / 256, 256, 0, st>>>(s->d_Pb[0], s->ldb, s->n, s->npad, s->d_P3);
+        k_sh_rows012<<<(s->npad + 255) / 256, 256, 0, st>>>(s->d_Pl, s->ldl, s->n, s->npad, s->d_P3);
         s->launches++;
     }
     if (s->world > 1) NCCL_TRY(g_nccl.Broadcast(s->d_P3, s->d_P3, (size_t)3 * s->npad, ncclFloat64, 0, s->comm, st));
-    int rc = launch_gate_shard(s->d_x, s->d_P3, s->npad, s->d_Pb, s->ldb, s->lo, s->hi, s->d_z, nz, R, gate1, gate2,
+    int rc = launch_gate_shard(s->d_x, s->d_P3, s->npad, s->d_Pl, s->ldl, s->rank, s->world, s->nlp, s->n, s->d_z, nz, R, gate1, gate2,
                                s->d_gate, gate_scratch_bytes(SLAM_MAX_OBS), res_mine,
                                s->pregate ? s->d_sig2 : nullptr, st, &s->launches);
     if (rc) return rc;
@@ -1101,9 +1110,10 @@ extern "C" int slam_shard_associate(slam_shard_t *s, const double *z, int nz, co
 constexpr int SHA_Q = 32;        // new landmarks per launch
 constexpr int SHA_THREADS = 256;
 
+// grid.x = local row tiles of SHA_THREADS rows (one panel each), grid.y = new landmark q of this launch
 __global__ void __launch_bounds__(SHA_THREADS)
-k_sh_augment(double *x, const double *__restrict__ P3, int npad, double *Pb, size_t ldb, int lo, int hi_new, int n0,
-             const double *__restrict__ zn, int kq, double R0, double R1, double R2, double R3, int write_x,
+k_sh_augment(double *x, const double *__restrict__ P3, int npad, double *Pl, size_t ldl, int rank, int world, int n0,
+             const double *__restrict__ zn, int kq, double R0, double R1, double R2, double R3,
              unsigned long long *sig2bits) {
     __shared__ double sGv[SHA_Q][2];
     __shared__ double sGP[SHA_Q][2][3];
@@ -1126,37 +1136,41 @@ k_sh_augment(double *x, const double *__restrict__ P3, int npad, double *Pb, siz
             for (int j = 0; j < 3; j++)
                 sGP[q][a][j] = Gv[a][0] * sPvv[0 * 3 + j] + Gv[a][1] * sPvv[1 * 3 + j] + Gv[a][2] * sPvv[2 * 3 + j];
         const int len = n0 + 2 * q;
-        if (write_x && blockIdx.x == 0 && blockIdx.y == q) {
-            x[len] = xv + r * c;
+        if (blockIdx.x == 0 && blockIdx.y == q) {
+            x[len] = xv + r * c;        // x is replicated: every rank appends the same values
             x[len + 1] = yv + r * s;
-        }
-        // the 2x2 diagonal block, by the owner of row len (a landmark's two rows never straddle blocks)
-        if (blockIdx.x == 0 && blockIdx.y == q && len >= lo && len < hi_new) {
-            const double Gz[2][2] = {{c, -r * s}, {s, r * c}};
-            const double Rm[4] = {R0, R1, R2, R3};
-            double GR[2][2];
-            for (int a = 0; a < 2; a++)
-                for (int j = 0; j < 2; j++) GR[a][j] = Gz[a][0] * Rm[0 + 2 * j] + Gz[a][1] * Rm[1 + 2 * j];
-            for (int a = 0; a < 2; a++)
-                for (int bb = a; bb < 2; bb++) {
-                    const double t1 = sGP[q][a][0] * Gv[bb][0] + sGP[q][a][1] * Gv[bb][1] + sGP[q][a][2] * Gv[bb][2];
-                    const double t2 = GR[a][0] * Gz[bb][0] + GR[a][1] * Gz[bb][1];
-                    const double pv = t1 + t2;
-                    Pb[(size_t)(len + a - lo) + (size_t)(len + bb) * ldb] = pv;
-                    if (a == bb) {   // keep this rank's pre-gate bound valid for the landmark it now owns
-                        unsigned long long bits = (unsigned long long)__double_as_longlong(pv);
-                        if (pv != pv) bits = 0x7ff8000000000000ull;
-                        if (!(pv < 0.0)) atomicMax(sig2bits, bits);
+            // the 2x2 diagonal block, by the owner of row len (a landmark's two rows never straddle panels)
+            const int p = panel_of_row(len);
+            if (panel_owner(p, world) == rank) {
+                const size_t li = (size_t)panel_local(p, world) * SH_PH + (len - panel_first(p));
+                const double Gz[2][2] = {{c, -r * s}, {s, r * c}};
+                const double Rm[4] = {R0, R1, R2, R3};
+                double GR[2][2];
+                for (int a = 0; a < 2; a++)
+                    for (int j = 0; j < 2; j++) GR[a][j] = Gz[a][0] * Rm[0 + 2 * j] + Gz[a][1] * Rm[1 + 2 * j];
+                for (int a = 0; a < 2; a++)
+                    for (int bb = a; bb < 2; bb++) {
+                        const double t1 = sGP[q][a][0] * Gv[bb][0] + sGP[q][a][1] * Gv[bb][1] + sGP[q][a][2] * Gv[bb][2];
+                        const double t2 = GR[a][0] * Gz[bb][0] + GR[a][1] * Gz[bb][1];
+                        const double pv = t1 + t2;
+                        Pl[li + a + (size_t)(len + bb) * ldl] = pv;
+                        if (a == bb) {   // keep this rank's pre-gate bound valid for the landmark it now owns
+                            unsigned long long bits = (unsigned long long)__double_as_longlong(pv);
+                            if (pv != pv) bits = 0x7ff8000000000000ull;
+                            if (!(pv < 0.0)) atomicMax(sig2bits, bits);
+                        }
                     }
-                }
+            }
         }
     }
     __syncthreads();
     const int q = blockIdx.y;
     if (q >= kq) return;
     const int len = n0 + 2 * q;
-    const int j = lo + blockIdx.x * SHA_THREADS + threadIdx.x;   // an existing row of this block
-    if (j >= len || j >= hi_new) return;
+    const int li = blockIdx.x * SHA_THREADS + threadIdx.x;      // a local row of this rank
+    const int p = panel_global(li / SH_PH, rank, world);
+    const int j = panel_first(p) + li % SH_PH;                   // its global row
+    if (j >= len || j >= panel_first(p + 1)) return;             // rows of the state before landmark q only
     double c0, c1, c2;   // P[1:3, j]
     if (j < 3) {
         c0 = sPvv[0 * 3 + j]; c1 = sPvv[1 * 3 + j]; c2 = sPvv[2 * 3 + j];
@@ -1169,8 +1183,8 @@ k_sh_augment(double *x, const double *__restrict__ P3, int npad, double *Pb, siz
     const double g0 = sGv[q][0], g1 = sGv[q][1];
     const double t0 = 1.0 * c0 + 0.0 * c1 + g0 * c2;
     const double t1 = 0.0 * c0 + 1.0 * c1 + g1 * c2;
-    Pb[(size_t)(j - lo) + (size_t)len * ldb] = t0;
-    Pb[(size_t)(j - lo) + (size_t)(len + 1) * ldb] = t1;
+    Pl[(size_t)li + (size_t)len * ldl] = t0;
+    Pl[(size_t)li + (size_t)(len + 1) * ldl] = t1;
 }
 
 extern "C" int slam_shard_add_features(slam_shard_t *s, const double *zn, int k, const double R[4]) {
@@ -1191,22 +1205,17 @@ extern "C" int slam_shard_add_features(slam_shard_t *s, const double *zn, int k,
         const int kq = std::min(SHA_Q, k - q0);
         const int n0 = s->n, n1 = n0 + 2 * kq;
         if (s->rank == 0) {
-            k_sh_rows012<<<(s->npad + 255) / 256, 256, 0, st>>>(s->d_Pb[0], s->ldb, n0, s->npad, s->d_P3);
+            k_sh_rows012<<<(s->npad + 255) / 256, 256, 0, st>>>(s->d_Pl, s->ldl, n0, s->npad, s->d_P3);
             s->launches++;
         }
         if (s->world > 1) NCCL_TRY(g_nccl.Broadcast(s->d_P3, s->d_P3, (size_t)3 * s->npad, ncclFloat64, 0, s->comm, st));
-        int lo[2], hi[2];
-        plan_blocks(n1, s->hb, s->world, s->rank, lo, hi);   // ownership once the new rows exist
-        for (int b = 0; b < 2; b++) {
-            const int rows = std::max(hi[b] - lo[b], 0);
-            dim3 grid(std::max(1, (rows + SHA_THREADS - 1) / SHA_THREADS), kq);
-            k_sh_augment<<<grid, SHA_THREADS, 0, st>>>(s->d_x, s->d_P3, s->npad, s->d_Pb[b], s->ldb, lo[b], hi[b], n0,
-                                                       s->d_zn + 2 * q0, kq, R[0], R[1], R[2], R[3], b == 0,
-                                                       s->d_sig2);
-            s->launches++;
-        }
+        const int nlp1 = local_panels(n1, s->world, s->rank);    // panels once the new rows exist
+        dim3 grid(std::max(nlp1 * SH_PH / SHA_THREADS, 1), kq);
+        k_sh_augment<<<grid, SHA_THREADS, 0, st>>>(s->d_x, s->d_P3, s->npad, s->d_Pl, s->ldl, s->rank, s->world, n0,
+                                                   s->d_zn + 2 * q0, kq, R[0], R[1], R[2], R[3], s->d_sig2);
+        s->launches++;
         s->n = n1;
-        s->lo[0] = lo[0]; s->lo[1] = lo[1]; s->hi[0] = hi[0]; s->hi[1] = hi[1];
+        s->nlp = nlp1;
     }
     CUDA_TRY(cudaGetLastError());
     return SLAM_OK;

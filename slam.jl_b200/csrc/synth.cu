@@ -82,6 +82,44 @@ int synth_fill(double *d_x, double *d_Pb, size_t ldb, int r0, int r1, int n_land
     return SLAM_OK;
 }
 
+// The rows of a row map (kernels.cuh) into a local array: a CTA row of 256 threads = one 256-row tile of the map.
+__global__ void k_synth_P_map(double *Pl, size_t ldl, RowMap map, int n, const double *__restrict__ L,
+                              const double *__restrict__ D) {
+    int i0, loc0, r1;
+    if (!rowmap_tile(map, blockIdx.y, 256, n, &i0, &loc0, &r1)) return;
+    const int i = i0 + threadIdx.x, j = blockIdx.x;
+    if (i >= r1 || j >= n) return;
+    const double *li = L + (size_t)i * 8, *lj = L + (size_t)j * 8;
+    double a = 0;
+#pragma unroll
+    for (int c = 0; c < 8; c++) a += li[c] * lj[c];
+    if (i == j) a += D[i];
+    Pl[(size_t)(loc0 + threadIdx.x) + (size_t)j * ldl] = a;
+}
+
+int synth_fill_map(double *d_x, double *d_Pl, size_t ldl, RowMap map, int n_landmarks, double side, uint64_t seed,
+                   cudaStream_t s, long long *launches) {
+    int n = 3 + 2 * n_landmarks;
+    double *L = nullptr, *D = nullptr;
+    CUDA_TRY(cudaMalloc(&L, sizeof(double) * (size_t)n * 8));
+    CUDA_TRY(cudaMalloc(&D, sizeof(double) * (size_t)n));
+    k_synth_x<<<(std::max(n_landmarks, 1) + 255) / 256, 256, 0, s>>>(d_x, n_landmarks, side, seed);
+    k_synth_L<<<(n + 255) / 256, 256, 0, s>>>(L, D, n, seed);
+    const int rows = rowmap_local_rows(map);
+    if (rows > 0) {
+        dim3 grid(n, (rows + 255) / 256);
+        k_synth_P_map<<<grid, 256, 0, s>>>(d_Pl, ldl, map, n, L, D);
+        if (launches) (*launches)++;
+    }
+    if (launches) (*launches) += 2;
+    cudaError_t e = cudaStreamSynchronize(s);
+    cudaFree(L);
+    cudaFree(D);
+    CUDA_TRY(e);
+    CUDA_TRY(cudaGetLastError());
+    return SLAM_OK;
+}
+
 // Host side: the m nearest landmarks ahead of the vehicle (truth positions) followed by
 // `spurious` observations of points at least 6 m from every landmark.
 int synth_observations_host(int n_landmarks, double side, uint64_t seed, int m, int spurious, double *z,

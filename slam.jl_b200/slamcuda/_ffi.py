@@ -124,7 +124,7 @@ _sig("slam_ens_launch_count", C.c_longlong, vp)
 _sig("slam_shard_unique_id", I, C.c_char_p)
 _sig("slam_shard_create", I, I, I, I, C.c_char_p, I, C.POINTER(vp))
 _sig("slam_shard_destroy", I, vp)
-_sig("slam_shard_plan", I, I, I, I, c_int_p, c_int_p)
+_sig("slam_shard_plan", I, I, I, I, c_int_p, c_int_p, I)
 _sig("slam_shard_synth_state", I, vp, I, D, U64)
 _sig("slam_shard_n", I, vp)
 _sig("slam_shard_get_pose", I, vp, c_double_p)

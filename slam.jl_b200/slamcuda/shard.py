@@ -12,11 +12,13 @@ from ._ffi import lib, check, dptr, iptr
 
 
 def shard_plan(n: int, world: int, rank: int):
-    """Rows [lo[q], hi[q]) of the two blocks rank owns (pure arithmetic, no device)."""
-    lo = (C.c_int * 2)()
-    hi = (C.c_int * 2)()
-    check(lib.slam_shard_plan(n, world, rank, lo, hi))
-    return [(lo[0], hi[0]), (lo[1], hi[1])]
+    """Rows [lo, hi) of every 256-row panel rank owns at state size n, in the order the rank stacks them (pure
+    arithmetic, no device)."""
+    cnt = check(lib.slam_shard_plan(n, world, rank, None, None, 0))
+    lo = (C.c_int * max(cnt, 1))()
+    hi = (C.c_int * max(cnt, 1))()
+    check(lib.slam_shard_plan(n, world, rank, lo, hi, cnt))
+    return [(lo[k], hi[k]) for k in range(cnt)]
 
 
 def exchange_unique_id(rank: int, world: int) -> bytes:

@@ -1,6 +1,6 @@
 """Worker of tests/test_dist_cpu.py: one of W gloo ranks on CPU (launched by torch.distributed.run).
 Checks the host-side logic of the two multi-GPU modes without a device:
-  plan      the row-block partition of the sharded covariance (slam_shard_plan) over the ranks
+  plan      the row-panel partition of the sharded covariance (slam_shard_plan) over the ranks
   uid       the NCCL unique id handed from rank 0 to every rank through torch.distributed
   members   the ensemble's run-id split, with the oracle's C twin standing in for the kernel:
             the ranks' members together equal one process running all of them
@@ -28,7 +28,7 @@ out = {}
 
 # -- plan ---------------------------------------------------------------------------------
 plans = {}
-for n in (3, 4, 259, 1003, 20003, 200003):
+for n in (3, 5, 255, 257, 259, 1003, 6083, 20003, 60001, 120001, 200003):   # incl. 0.1 / 0.3 / 0.6 / 1.0 of 200003
     mine = shard_plan(n, world, rank)
     got = [None] * world
     dist.all_gather_object(got, mine)

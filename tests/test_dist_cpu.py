@@ -40,24 +40,25 @@ def dist_result(request):
     return world, json.loads(lines[0][len("DIST_CHECK "):])
 
 
-def test_row_block_partition(dist_result):
-    """2W blocks, rank r owns blocks r and 2W-1-r: rows covered exactly once, block edges never
-    split a landmark's two rows, and the upper-triangle work per rank is balanced."""
+def test_row_panel_partition(dist_result):
+    """256-row panels dealt boustrophedon (panel p -> rank b = p mod 2W if b < W else 2W-1-b): rows covered exactly
+    once, panel edges never split a landmark's two rows, and the upper-triangle work per rank is balanced at ANY
+    state size -- 10 %, 30 %, 60 % and 100 % of a 100k-landmark capacity -- not only when the map is full (the
+    reference's state grows one landmark at a time, src/ekf.jl:84-122)."""
     world, res = dist_result
     for n_str, plans in res["plans"].items():
         n = int(n_str)
         owner = np.full(n, -1)
         work = np.zeros(world)
-        for r, blocks in enumerate(plans):
-            assert len(blocks) == 2
-            for lo, hi in blocks:
+        for r, panels in enumerate(plans):
+            for lo, hi in panels:
                 if hi <= lo:
                     continue
-                assert 0 <= lo < hi <= n
+                assert 0 <= lo < hi <= n and hi - lo <= 256
                 assert np.all(owner[lo:hi] == -1), (n, r, lo, hi)
                 owner[lo:hi] = r
                 if lo > 0:
-                    assert (lo - 3) % 2 == 0 or lo < 3, (n, lo)      # lo is a landmark's first row
+                    assert lo >= 3 and (lo - 3) % 2 == 0, (n, lo)      # lo is a landmark's first row
                 work[r] += sum(n - i for i in (lo, hi - 1)) * (hi - lo) / 2.0   # entries j >= i
         assert np.all(owner >= 0), n
         if n >= 20003:

@@ -1,5 +1,5 @@
-"""GPU parity of the row-block-sharded path.  world = 1 exercises the whole sharded code path
-(two row blocks, rank-local buffers, unpermute, block-wise K6, sharded gating) on one device
+"""GPU parity of the row-panel-sharded path.  world = 1 exercises the whole sharded code path
+(256-row panels, rank-local buffers, unpermute, panel-mapped K6, sharded gating) on one device
 without NCCL; tools/shard_check.py runs the same comparison under torchrun on 2+ GPUs."""
 import ctypes as C
 import math
@@ -54,7 +54,7 @@ def test_sharded_world1_matches_single_filter(nl, m):
     x1, P1 = h.get_state()
     blk, _ = sf.cov_block(0, n, 0, n)
     ex, eP = rel_err(sf.get_x(), x1), rel_err(np.triu(blk), np.triu(P1))
-    print(f"\n[shard world=1 n={n} m={m}] x rel {ex:.2e}  P rel {eP:.2e}; blocks {shard_plan(n, 1, 0)}")
+    print(f"\n[shard world=1 n={n} m={m}] x rel {ex:.2e}  P rel {eP:.2e}; {len(shard_plan(n, 1, 0))} panels")
     assert ex < 1e-12 and eP < 1e-12
     sf.close()
     h.close()
@@ -109,7 +109,7 @@ def test_sharded_add_features_matches_single_filter(nl, knew):
     xb, Pb = h.get_state()
     blk, _ = sf.cov_block(0, nn, 0, nn)
     ex, eP = rel_err(sf.get_x(), xb), rel_err(np.triu(blk), np.triu(Pb))
-    print(f"\n[shard add_features n0={n0} k={k}] x rel {ex:.2e}  P rel {eP:.2e}; blocks {shard_plan(ncap, 1, 0)}")
+    print(f"\n[shard add_features n0={n0} k={k}] x rel {ex:.2e}  P rel {eP:.2e}; {len(shard_plan(ncap, 1, 0))} panels")
     assert ex < 1e-12 and eP < 1e-12
     with pytest.raises(Exception):
         sf.add_features(np.tile(zn_b[:, :1], (1, knew + 1)), R)   # more than the capacity left

@@ -15,12 +15,15 @@ from slamcuda.ensemble import Ensemble  # noqa: E402
 n_runs = int(sys.argv[1]) if len(sys.argv) > 1 else 444
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 nl = int(sys.argv[3]) if len(sys.argv) > 3 else 35
-threads = int(sys.argv[4]) if len(sys.argv) > 4 else None
-extra = int(sys.argv[5]) if len(sys.argv) > 5 else None
-first = int(sys.argv[6]) if len(sys.argv) > 6 else None
+threads = int(sys.argv[4]) if len(sys.argv) > 4 and sys.argv[4] != "-" else None
+extra = int(sys.argv[5]) if len(sys.argv) > 5 and sys.argv[5] != "-" else None
+first = int(sys.argv[6]) if len(sys.argv) > 6 and sys.argv[6] != "-" else None
+growth = int(sys.argv[7]) if len(sys.argv) > 7 and sys.argv[7] != "-" else None
+max_shared = int(sys.argv[8]) if len(sys.argv) > 8 and sys.argv[8] != "-" else None
 wp = np.loadtxt(ROOT / "tests" / "golden" / "course1.txt", skiprows=1).T.copy()
 lm = np.random.Generator(np.random.PCG64(0)).integers(5, 96, size=(2, nl)).astype(float)
-ens = Ensemble(wp, lm, n_runs, seed=2, run0=0, threads=threads, extra_landmarks=extra, first_pass_extra=first)
+ens = Ensemble(wp, lm, n_runs, seed=2, run0=0, threads=threads, extra_landmarks=extra, first_pass_extra=first,
+               growth=growth, max_shared_extra=max_shared)
 stream = torch.cuda.ExternalStream(lib.slam_ens_stream(ens.ptr))
 ens.run()
 bad = ens.sync()
@@ -29,13 +32,14 @@ for _ in range(reps):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     ens.run()
-    e1.record(stream)
     ens.sync()
+    e1.record(stream)
+    e1.synchronize()
     ts.append(e0.elapsed_time(e1))
 ms = sorted(ts)[len(ts) // 2]
 pose, nf, st = ens.results()
 total, per = ens.steps_done()
 print(f"runs {n_runs} nl {nl} steps {ens.nsteps} threads {threads} cap {ens.capacity}: {ms:.3f} ms/launch, "
       f"{total / ms / 1e3:.2f} M filter-steps/s ({total} steps done of {n_runs * ens.nsteps}), "
-      f"passes {ens.pass_info()}, stopped early {bad}, n_final max {nf.max()}, status counts {dict(zip(*np.unique(st, return_counts=True)))}")
+      f"growth {growth}, launches (capacity, members) {ens.tier_info()}, stopped early {bad}, n_final max {nf.max()}, status counts {dict(zip(*np.unique(st, return_counts=True)))}")
 ens.close()

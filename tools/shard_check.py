@@ -81,10 +81,10 @@ for lo, hi in shard_plan(n, world, rank):
         mask = np.arange(n)[None, :] >= np.arange(lo, hi)[:, None]
         eP = max(eP, float(np.max(np.abs(blk - ref)[mask]) / np.max(np.abs(P1))))
 res = [None] * world
-dist.all_gather_object(res, (rank, ok, ex, eP, cnt_total, shard_plan(n, world, rank)))
+dist.all_gather_object(res, (rank, ok, ex, eP, cnt_total, len(shard_plan(n, world, rank))))
 if rank == 0:
     for r in res:
-        print("rank %d assoc_ok=%s x_rel=%.2e P_rel=%.2e rows*cols=%d blocks=%s" % r)
+        print("rank %d assoc_ok=%s x_rel=%.2e P_rel=%.2e rows*cols=%d panels=%d" % r)
     good = all(r[1] and r[2] < 1e-12 and r[3] < 1e-12 for r in res)
     print("SHARD_CHECK", "PASS" if good else "FAIL", f"world={world} n={n} m={m} p2p={sf.p2p}")
 sf.close()
