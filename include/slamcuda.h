@@ -103,6 +103,20 @@ int slam_compute_landmark_ellipses(slam_t *h, double nsigma, int nsegs, double *
  * sim/gr-draw.jl:112-117: out is 2 x (nsegs+1) column-major. */
 int slam_vehicle_ellipse(slam_t *h, double nsigma, int nsegs, double *out);
 
+/* Front-end payloads of the browser monitor (sim/browser/wsserver.jl:31-85) as headless buffers computed on the
+ * device, so that a monitor of a large resident map never pulls P:
+ *  slam_feature_ellipses       "feature-ellipses": out is 5 x Nf column-major, [cx; cy; sqrt(l1); sqrt(l2); phi] with
+ *                              l, u = eig(cov[j, j]) ascending and phi = atan2(u[2,1], u[1,1]) normalised to
+ *                              (-pi/2, pi/2] (wsserver.jl:72-85; an eigenvector's sign is LAPACK's choice there:
+ *                              same ellipse).  Returns Nf.
+ *  slam_vehicle_ellipse_params "vehicle-ellipse": [cx, cy, vehicle_phi, rx, ry, phi] (wsserver.jl:58-63).
+ *  slam_laser_lines            "lidar": laser_lines(z, state.x[1:3]) of src/common.jl:265-283: lines is 4 x nz,
+ *                              [vx; vy; fx; fy] per observation (range, bearing) of z (2 x nz, host).
+ * ("tracks" is slam_get_pose per step, "state" is slam_get_state / slam_get_cov_block.) */
+int slam_feature_ellipses(slam_t *h, double *out);
+int slam_vehicle_ellipse_params(slam_t *h, double out[6]);
+int slam_laser_lines(slam_t *h, const double *z, int nz, double *lines);
+
 /* predict -- src/ekf.jl:8-43.  g, v = vehicle.measured_gamma / measured_speed (:14-15),
  * wheelbase = vehicle.wheelbase (:16), Q 2x2 control covariance, dt timestep. In place. */
 int slam_predict(slam_t *h, double g, double v, double wheelbase, const double Q[4], double dt);

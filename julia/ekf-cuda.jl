@@ -321,6 +321,28 @@ function compute_landmark_ellipses(s::CudaEKFSlamState)
     return ellipses
 end
 
+# The browser monitor's payloads for a resident state (sim/browser/wsserver.jl:31-85) without pulling P:
+# feature_ellipses -> 5 x nf [cx; cy; sqrt(l1); sqrt(l2); phi] (wsserver.jl:72-85; phi in (-pi/2, pi/2]),
+# laser_lines -> 4 x nz [vx; vy; fx; fy] (src/common.jl:265-283).
+function feature_ellipses(s::CudaEKFSlamState)
+    nf = div(length(s) - 3, 2)
+    out = Array{Float64}(5, nf)
+    if nf > 0
+        slam_check(ccall((:slam_feature_ellipses, libslamcuda), Cint, (Ptr{Void}, Ptr{Float64}), s.h.ptr, out))
+    end
+    return out
+end
+
+function laser_lines(z, s::CudaEKFSlamState)
+    nz = size(z, 2)
+    lines = Array{Float64}(4, nz)
+    if nz > 0
+        slam_check(ccall((:slam_laser_lines, libslamcuda), Cint, (Ptr{Void}, Ptr{Float64}, Cint, Ptr{Float64}),
+                         s.h.ptr, convert(Matrix{Float64}, z), nz, lines))
+    end
+    return lines
+end
+
 function vehicle_ellipse(s::CudaEKFSlamState, nsigma::Real=2, nsegs::Integer=12)
     ell = Array{Float64}(2, nsegs + 1)
     slam_check(ccall((:slam_vehicle_ellipse, libslamcuda), Cint,

@@ -294,6 +294,41 @@ def compute_landmark_ellipses(x, P):
     return out
 
 
+def local_to_global(l, g):
+    """src/common.jl:112-128: rotate the 2 x n local positions by the pose heading and translate."""
+    l = np.asarray(l, dtype=float)
+    phi = g[2]
+    Rm = np.array([[math.cos(phi), -math.sin(phi)], [math.sin(phi), math.cos(phi)]])
+    q = np.zeros_like(l)
+    q[0:2, :] = Rm @ l[0:2, :] + np.asarray(g[0:2], dtype=float).reshape(2, 1)
+    return q
+
+
+def laser_lines(z, vehicle_pose):
+    """src/common.jl:265-283: 4 x nz, columns [vx; vy; fx; fy]."""
+    z = np.asarray(z, dtype=float).reshape(2, -1)
+    nl = z.shape[1]
+    lines = np.zeros((4, nl))
+    lines[0, :] = vehicle_pose[0]
+    lines[1, :] = vehicle_pose[1]
+    r, b = z[0, :], z[1, :]
+    xy_local = np.vstack([r * np.cos(b), r * np.sin(b)])
+    lines[2:4, :] = local_to_global(xy_local, vehicle_pose)
+    return lines
+
+
+def feature_ellipses(x, cov):
+    """sim/browser/wsserver.jl:72-85: 5 x nf, [x_j; sqrt(l); atan2(u[2,1], u[1,1])] with l, u = eig(cov[j, j])
+    (ascending eigenvalues; the eigenvector's sign -- hence phi modulo pi -- is LAPACK's choice)."""
+    nf = (len(x) - 3) // 2
+    out = np.zeros((5, nf))
+    for i in range(1, nf + 1):
+        j0 = 2 * i + 1          # 0-based start of 1-based (2i+2):(2i+3)
+        lam, u = np.linalg.eigh(cov[j0:j0 + 2, j0:j0 + 2])
+        out[:, i - 1] = [x[j0], x[j0 + 1], math.sqrt(lam[0]), math.sqrt(lam[1]), math.atan2(u[1, 0], u[0, 0])]
+    return out
+
+
 def nearby_landmark_indices(pose, lm, rmax):
     """sim/sim-utils.jl:12-28 (returns 0-based indices)."""
     phi = pose[2]

@@ -1465,6 +1465,114 @@ extern "C" int slam_vehicle_ellipse(slam_t *h, double nsigma, int nsegs, double 
 }
 
 // ---------------------------------------------------------------------------------------
+// Front-end payloads of the browser monitor (sim/browser/wsserver.jl:31-85) as headless
+// buffers, computed on the device from the resident state so that a monitor never pulls P:
+//   "feature-ellipses"  5 x Nf: [cx; cy; sqrt(l1); sqrt(l2); phi], l, u = eig(cov[j, j]) ascending,
+//                       phi = atan2(u[2,1], u[1,1]) (wsserver.jl:72-85); block 0 = the vehicle's position block
+//                       ("vehicle-ellipse", :58-63).  An eigenvector's sign is LAPACK's choice in the reference;
+//                       here phi is normalised to (-pi/2, pi/2] -- the same ellipse.
+//   "lidar"             4 x nz: [vx; vy; fx; fy] per observation, laser_lines (src/common.jl:265-283) with
+//                       local_to_global (:112-128) on the device pose.
+// ("tracks" is state.x[1:3] per step = slam_get_pose; "state" is pose + cov = slam_get_state / slam_get_cov_block.)
+// ---------------------------------------------------------------------------------------
+__global__ void k_ellipse_params(const double *__restrict__ x, const double *__restrict__ P, size_t ld, int b0, int nb,
+                                 double *__restrict__ out) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nb) return;
+    const int blk = b0 + b;
+    const int r = blk == 0 ? 0 : 3 + 2 * (blk - 1);
+    const double a = P[(size_t)r + (size_t)r * ld], c = P[(size_t)r + (size_t)(r + 1) * ld],
+                 d = P[(size_t)(r + 1) + (size_t)(r + 1) * ld];
+    const double mean = 0.5 * (a + d), diff = 0.5 * (a - d);
+    const double rad = sqrt(diff * diff + c * c);
+    const double l1 = mean - rad, l2 = mean + rad;
+    // eigenvector of l1: (c, l1 - a) or (l1 - d, c), whichever is longer
+    double vx = c, vy = l1 - a;
+    if (fabs(l1 - d) > fabs(vy)) { vx = l1 - d; vy = c; }
+    if (vx == 0.0 && vy == 0.0) { vx = a <= d ? 1.0 : 0.0; vy = a <= d ? 0.0 : 1.0; }   // already diagonal
+    double phi = atan2(vy, vx);
+    if (phi > SLAM_PI / 2) phi -= SLAM_PI;
+    if (phi <= -SLAM_PI / 2) phi += SLAM_PI;
+    double *o = out + 5 * (size_t)b;
+    o[0] = x[r]; o[1] = x[r + 1]; o[2] = sqrt(l1); o[3] = sqrt(l2); o[4] = phi;
+}
+
+__global__ void k_laser_lines(const double *__restrict__ x, const double *__restrict__ z, int nz, double *__restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nz) return;
+    const double xv = x[0], yv = x[1], phi = x[2];
+    const double r = z[2 * i], b = z[2 * i + 1];
+    const double lx = r * cos(b), ly = r * sin(b);          // observation in the vehicle frame (:277)
+    const double cp = cos(phi), sp = sin(phi);
+    out[4 * i] = xv;
+    out[4 * i + 1] = yv;
+    out[4 * i + 2] = (cp * lx + (-sp) * ly) + xv;           // R*l .+ g (:121)
+    out[4 * i + 3] = (sp * lx + cp * ly) + yv;
+}
+
+static int front_buffer(slam_t *h, size_t need) {
+    if (need > h->block_cap) {
+        cudaFree(h->d_block);
+        h->d_block = nullptr;
+        h->block_cap = 0;
+        CUDA_TRY(cudaMalloc(&h->d_block, sizeof(double) * need));
+        h->block_cap = need;
+    }
+    return SLAM_OK;
+}
+
+extern "C" int slam_feature_ellipses(slam_t *h, double *out) {
+    H_CHECK(h);
+    const int nf = (h->n - 3) / 2;
+    if (nf == 0) return 0;
+    ARG_CHECK(out != nullptr, "NULL out");
+    int rc = front_buffer(h, (size_t)5 * nf);
+    if (rc) return rc;
+    k_ellipse_params<<<(nf + 127) / 128, 128, 0, h->stream>>>(h->d_x, h->d_P, h->ld, 1, nf, h->d_block);
+    h->launches++;
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(out, h->d_block, sizeof(double) * 5 * nf, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return nf;
+}
+
+extern "C" int slam_vehicle_ellipse_params(slam_t *h, double out[6]) {
+    H_CHECK(h);
+    ARG_CHECK(out != nullptr, "NULL out");
+    int rc = front_buffer(h, 8);
+    if (rc) return rc;
+    k_ellipse_params<<<1, 32, 0, h->stream>>>(h->d_x, h->d_P, h->ld, 0, 1, h->d_block);
+    h->launches++;
+    CUDA_TRY(cudaGetLastError());
+    double e[5], pose[3];
+    CUDA_TRY(cudaMemcpyAsync(e, h->d_block, sizeof(e), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaMemcpyAsync(pose, h->d_x, sizeof(pose), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    out[0] = pose[0]; out[1] = pose[1]; out[2] = pose[2];   // [cx, cy, vehicle_phi, rx, ry, phi] (wsserver.jl:60-61)
+    out[3] = e[2]; out[4] = e[3]; out[5] = e[4];
+    return SLAM_OK;
+}
+
+extern "C" int slam_laser_lines(slam_t *h, const double *z, int nz, double *lines) {
+    H_CHECK(h);
+    ARG_CHECK(nz >= 0 && nz <= SLAM_MAX_OBS, "bad nz");
+    if (nz == 0) return SLAM_OK;
+    ARG_CHECK(z && lines, "NULL argument");
+    int rc = front_buffer(h, (size_t)4 * nz);
+    if (rc) return rc;
+    double *hz = (double *)((char *)h->h_pin + 256);
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    memcpy(hz, z, sizeof(double) * 2 * nz);
+    CUDA_TRY(cudaMemcpyAsync(h->d_z, hz, sizeof(double) * 2 * nz, cudaMemcpyHostToDevice, h->stream));
+    k_laser_lines<<<(nz + 127) / 128, 128, 0, h->stream>>>(h->d_x, h->d_z, nz, h->d_block);
+    h->launches++;
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(lines, h->d_block, sizeof(double) * 4 * nz, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return SLAM_OK;
+}
+
+// ---------------------------------------------------------------------------------------
 // synthetic large-map state (synth.cu)
 // ---------------------------------------------------------------------------------------
 extern "C" int slam_synth_state(slam_t *h, int n_landmarks, double side, uint64_t seed) {

@@ -79,6 +79,9 @@ _sig("slam_n", I, vp)
 _sig("slam_get_cov_block", I, vp, I, I, I, I, c_double_p, I)
 _sig("slam_compute_landmark_ellipses", I, vp, D, I, c_double_p, I)
 _sig("slam_vehicle_ellipse", I, vp, D, I, c_double_p)
+_sig("slam_feature_ellipses", I, vp, c_double_p)
+_sig("slam_vehicle_ellipse_params", I, vp, c_double_p)
+_sig("slam_laser_lines", I, vp, c_double_p, I, c_double_p)
 _sig("slam_predict", I, vp, D, D, D, c_double_p, D)
 _sig("slam_associate", I, vp, c_double_p, I, c_double_p, D, D, c_double_p, c_int64_p, c_int_p,
      c_double_p, c_int_p)

@@ -204,6 +204,26 @@ class _Handle:
         check(lib.slam_vehicle_ellipse(self.ptr, float(nsigma), int(nsegs), dptr(out)))
         return np.ascontiguousarray(out)
 
+    def feature_ellipses(self):
+        """5 x Nf [cx; cy; rx; ry; phi] of sim/browser/wsserver.jl:72-85, from the 2 x 2 diagonal blocks on the device."""
+        nf = (self.n - 3) // 2
+        out = np.zeros((5, nf), order="F")
+        check(lib.slam_feature_ellipses(self.ptr, dptr(out)))
+        return np.ascontiguousarray(out)
+
+    def vehicle_ellipse_params(self):
+        """[cx, cy, vehicle_phi, rx, ry, phi] of sim/browser/wsserver.jl:58-63."""
+        out = np.zeros(6)
+        check(lib.slam_vehicle_ellipse_params(self.ptr, dptr(out)))
+        return out
+
+    def laser_lines(self, z):
+        """laser_lines(z, state.x[1:3]) -- src/common.jl:265-283 -> 4 x nz [vx; vy; fx; fy]."""
+        zc, nz = _cols(z)
+        out = np.zeros((4, max(nz, 1)), order="F")
+        check(lib.slam_laser_lines(self.ptr, dptr(zc), nz, dptr(out)))
+        return np.ascontiguousarray(out[:, :nz])
+
     def sync(self):
         check(lib.slam_sync(self.ptr))
 
@@ -393,6 +413,25 @@ def compute_landmark_ellipses(x, P=None):
     h = _scratch_handle(len(x))
     h.set_state(x, P)
     return h.landmark_ellipses()
+
+
+def feature_ellipses(x, P=None):
+    """sim/browser/wsserver.jl:72-85 -> 5 x nf [cx; cy; sqrt(l1); sqrt(l2); phi]; accepts (x, P) or a state object."""
+    if isinstance(x, SlamState):
+        return x._upload().feature_ellipses()
+    x = np.asarray(x, dtype=np.float64).reshape(-1)
+    h = _scratch_handle(len(x))
+    h.set_state(x, P)
+    return h.feature_ellipses()
+
+
+def laser_lines(z, vehicle_pose):
+    """src/common.jl:265-283 -> 4 x nz line segments vehicle -> observed point."""
+    xs = np.zeros(3)
+    xs[:] = np.asarray(vehicle_pose, dtype=np.float64).reshape(-1)[:3]
+    h = _scratch_handle(3)
+    h.set_state(xs, np.zeros((3, 3)))
+    return h.laser_lines(z)
 
 
 def ellipse(x, P, nsigma, nsegs):

@@ -486,6 +486,36 @@ def test_landmark_ellipses(sc, nf):
     st.h.close()
 
 
+def test_front_end_payloads(sc):
+    """The browser monitor's payloads as headless device buffers (sim/browser/wsserver.jl:31-85): the five-parameter
+    feature ellipses (eig of the 2 x 2 diagonal blocks) and the lidar line segments (laser_lines,
+    src/common.jl:265-283) of a resident state, against the oracle; phi modulo pi (an eigenvector's sign is LAPACK's)."""
+    rng = np.random.default_rng(31)
+    x, P = _random_state(rng, 300)
+    P[3, 3], P[3, 4], P[4, 3], P[4, 4] = 0.3, 0.0, 0.0, 0.1        # a diagonal block, larger variance first
+    P[5, 5], P[5, 6], P[6, 5], P[6, 6] = 0.1, 0.0, 0.0, 0.3        # ... and smaller first
+    st = sc.DeviceEKFSlamState(x, P, n_max=len(x))
+    e = st.h.feature_ellipses()
+    eo = ref.feature_ellipses(x, P)
+    assert e.shape == eo.shape == (5, 300)
+    assert rel_err(e[:4], eo[:4]) < STEP_TOL
+    dphi = np.abs(e[4] - eo[4])
+    dphi = np.minimum(dphi, np.abs(dphi - math.pi))
+    assert np.max(dphi) < 1e-9 and np.all(e[4] > -math.pi / 2 - 1e-15) and np.all(e[4] <= math.pi / 2 + 1e-15)
+    assert np.array_equal(sc.feature_ellipses(x, P), e)
+    v = st.h.vehicle_ellipse_params()
+    lam, u = np.linalg.eigh(P[0:2, 0:2])
+    assert np.array_equal(v[:3], x[:3]) and rel_err(v[3:5], np.sqrt(lam)) < STEP_TOL
+    dv = abs(v[5] - math.atan2(u[1, 0], u[0, 0]))
+    assert min(dv, abs(dv - math.pi)) < 1e-9
+    z = np.array([rng.uniform(1, 30, 9), rng.uniform(-1.5, 1.5, 9)])
+    lines = st.h.laser_lines(z)
+    assert rel_err(lines, ref.laser_lines(z, x[:3])) < 1e-14
+    assert np.array_equal(sc.laser_lines(z, x[:3]), lines)
+    assert st.h.laser_lines(np.zeros((2, 0))).shape == (4, 0)
+    st.h.close()
+
+
 @pytest.mark.parametrize("nf,m", [(1000, 6), (1000, 8), (1000, 10), (1000, 12), (1000, 13), (1000, 16), (1000, 20),
                                   (1000, 24), (1000, 28), (1000, 32), (1000, 40), (1000, 64), (333, 16), (517, 24),
                                   (130, 6), (61, 30)])
