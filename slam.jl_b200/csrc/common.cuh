@@ -36,6 +36,17 @@ static inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
 static inline size_t round_up_sz(size_t a, size_t b) { return (a + b - 1) / b * b; }
 
 // ---------------------------------------------------------------------------------------
+// NVTX ranges around the C entry points (tracing): header-only nvtx3, a no-op unless a profiler
+// (nsys / ncu --nvtx) injects itself.  One range per reference-level operation, named after the entry point.
+// ---------------------------------------------------------------------------------------
+#include <nvtx3/nvToolsExt.h>
+struct SlamNvtxRange {
+    explicit SlamNvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~SlamNvtxRange() { nvtxRangePop(); }
+};
+#define SLAM_NVTX() SlamNvtxRange nvtx_range__(__func__)
+
+// ---------------------------------------------------------------------------------------
 // device math shared by the single-filter, ensemble and sharded paths
 // ---------------------------------------------------------------------------------------
 #define SLAM_PI 3.14159265358979323846

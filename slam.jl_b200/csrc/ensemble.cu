@@ -16,6 +16,8 @@
 // The device functions follow the operation order of the oracle's plain-C twin; compiled with
 // -fmad=false, so the only differences from the twin are the device libm's sin/cos/atan2/log.
 // Members are sharded by run across GPUs by the caller (one handle per GPU, no collective).
+#include <stdlib.h>
+
 #include <algorithm>
 #include <vector>
 
@@ -183,6 +185,15 @@ struct EnsArgs {
     // and the triangle table of redo member i live at gstate + i*gstride; final_x / final_P are then indexed by i too.
     double *gstate;
     size_t gstride;
+    // Checkpoints: a member that outgrows this launch's capacity leaves its state (taken after the update of the block
+    // in which the append no longer fits) in slot = its index in over_list, and the next launch -- whose redo_list is
+    // that over_list -- resumes it there instead of re-running it from its first step (the median diverged filter
+    // outgrows the first pass at step ~1540 of 2802).  Same arithmetic on the same operands: bit-identical to a
+    // re-run.  Members beyond the slots available are re-run from the start.
+    double *ckpt_out;          // [ckpt_out_slots][ckpt_out_stride] or nullptr
+    int ckpt_out_slots, ckpt_out_stride;
+    const double *ckpt_in;     // the previous launch's checkpoints (taken at capacity ckpt_in_ncap) or nullptr
+    int ckpt_in_slots, ckpt_in_stride, ckpt_in_ncap;
     // optional [n_runs]: algorithmic FP64 operations of the member's run by the figures of SURVEY.md 8d -- per
     // predict 30 n; per observation step 80 nz Nf, and with m matches 2m n(n+1) + 20 n m + 8 n m^2 + 8 m^3
     double *flops;
@@ -217,6 +228,9 @@ __device__ __forceinline__ void ens_mark(int k) {
 #define ENS_MARK(k)
 #endif
 constexpr int LM_STRIDE = 17;     // association table per landmark: zp[2], inv(S)[4], log det, h[10]
+// checkpoint layout (doubles): [1] n, [2] k, [3] block, [4] flops, [5] steps of the block; [8, 35) the block's poses;
+// [CK_ZN, ..) zn (2 mmax); then x (ncap of the writer, rounded to 4); then the packed P (ens_pdoubles(n) of them)
+constexpr int CK_POSE = 8, CK_ZN = 40;
 
 struct EnsSmem {
     double *x, *P, *W, *S, *cd, *u, *v, *Hn, *z, *zf, *zn, *bs, *par;   // cd: diagonal of inv(U)
@@ -256,6 +270,9 @@ __host__ __device__ inline size_t ens_fixed_bytes(int mmax) {
     const int R = 2 * mmax;
     size_t d = ens_ru4(R * ens_lds(R)) + 3 * ens_ru4(R) + ens_ru4(10 * mmax) + 3 * ens_ru4(2 * mmax) + ENS_MAXB * BS + ENS_PAR;
     return d * 8 + ens_ru4(3 * mmax) * 4 + 32;
+}
+__host__ __device__ inline int ens_ckpt_doubles(int ncap, int mmax) {
+    return CK_ZN + ens_ru4(2 * mmax) + ens_ru4(ncap) + ens_pdoubles(ncap);
 }
 __host__ __device__ inline size_t ens_smem_bytes(int ncap, int mmax) {
     return ens_state_doubles(ncap, mmax) * 8 + ens_fixed_bytes(mmax);
@@ -948,46 +965,88 @@ k_ensemble(EnsArgs a) {
     const double *ctrl = a.ctrl_noise ? a.ctrl_noise + (size_t)member * 2 * a.nsteps : nullptr;
     const double *obsn = a.obs_noise ? a.obs_noise + (size_t)member * a.obs_per_member : nullptr;
     double *track = a.tracks ? a.tracks + (size_t)member * 3 * a.nsteps : nullptr;
-    // state.x = vehicle.pose = initial_pose (sim/ekfslam-sim.jl:37,42); the host stores it in the
-    // three doubles in front of z_true
-    if (tid < 3) sm.x[tid] = a.z_true[-3 + tid];
-    __syncthreads();
-    int done = 0, staged = -1;
-    bool outgrown = false;
+    int done = 0, staged = -1, b0 = 0, rk = 0, over_idx = -1;
+    bool outgrown = false, resume = false;
     double flops = 0.0;   // thread 0's tally (bench.py's FP64 roofline entry)
+    const int ck_xo = CK_ZN + ens_ru4(2 * a.mmax);
+    if (a.ckpt_in && (int)blockIdx.x < a.ckpt_in_slots) {
+        // resume where the previous launch had to stop: state after that block's update, its new observations pending
+        const double *c = a.ckpt_in + (size_t)blockIdx.x * a.ckpt_in_stride;
+        n = (int)c[1]; rk = (int)c[2]; b0 = (int)c[3]; flops = c[4];
+        const int rlen = (int)c[5], po = ck_xo + ens_ru4(a.ckpt_in_ncap);
+        for (int idx = tid; idx < n; idx += T) sm.x[idx] = c[ck_xo + idx];
+        for (int idx = tid; idx < ens_pdoubles(n); idx += T) sm.P[idx] = c[po + idx];
+        for (int idx = tid; idx < 2 * rk; idx += T) sm.zn[idx] = c[CK_ZN + idx];
+        if (tid < 3 * rlen) sm.bs[(tid / 3) * BS + B_X0 + tid % 3] = c[CK_POSE + tid];
+        resume = true;
+        done = a.blk[b0].x;
+    } else if (tid < 3) {
+        // state.x = vehicle.pose = initial_pose (sim/ekfslam-sim.jl:37,42); the host stores it in the
+        // three doubles in front of z_true
+        sm.x[tid] = a.z_true[-3 + tid];
+    }
+    __syncthreads();
     ENS_MARK(-1);
-    int4 dnext = a.blk[0];
-    for (int b = 0; b < a.nblocks; b++) {
+    int4 dnext = a.blk[b0];
+    for (int b = b0; b < a.nblocks; b++) {
         ENS_MARK(0);
         const int4 d = dnext;      // the next block's descriptor is fetched a whole block ahead
         if (b + 1 < a.nblocks) dnext = a.blk[b + 1];
         const int s0 = d.x, s1 = d.y, len = d.y - d.x, nz = d.w;
-        if (obsn && 2 * d.z + 2 * nz > a.obs_per_member) { status = SLAM_ERR_CAPACITY; break; }
-        if (staged != b) {   // not staged during the previous block's update (first block, blocks after
-                             // an observation step without matches): do it now
-            if (tid >= 32) ens_stage_block<T>(sm, a, b, run, ctrl, obsn);
-            __syncthreads();
-        }
-        ens_predict_block<T>(sm, n, len, nz);
-        if (a.flops) flops += 30.0 * n * len;
-        if (nz > 0) {
-            ens_associate<T>(sm, n, nz);
-            const int m = (int)sm.par[0], k = (int)sm.par[1];
-            if (a.flops)
-                flops += 40.0 * nz * (n - 3) + (m > 0 ? (double)m * (2.0 * n * (n + 1) + 20.0 * n + 8.0 * n * m + 8.0 * m * m) : 0.0);
-            if (m > 0) {
-                if (!ens_update<T>(sm, n, a.ldw, m, a, b + 1, run, ctrl, obsn)) { status = SLAM_ERR_NOT_PD; break; }
-                staged = b + 1;
+        int k = rk;
+        if (!resume) {
+            if (obsn && 2 * d.z + 2 * nz > a.obs_per_member) { status = SLAM_ERR_CAPACITY; break; }
+            if (staged != b) {   // not staged during the previous block's update (first block, blocks after
+                                 // an observation step without matches): do it now
+                if (tid >= 32) ens_stage_block<T>(sm, a, b, run, ctrl, obsn);
+                __syncthreads();
             }
-            if (n + 2 * k > a.ncap) { status = SLAM_ERR_CAPACITY; outgrown = true; break; }
+            ens_predict_block<T>(sm, n, len, nz);
+            if (a.flops) flops += 30.0 * n * len;
+            if (nz > 0) {
+                ens_associate<T>(sm, n, nz);
+                const int m = (int)sm.par[0];
+                k = (int)sm.par[1];
+                if (a.flops)
+                    flops += 40.0 * nz * (n - 3) + (m > 0 ? (double)m * (2.0 * n * (n + 1) + 20.0 * n + 8.0 * n * m + 8.0 * m * m) : 0.0);
+                if (m > 0) {
+                    if (!ens_update<T>(sm, n, a.ldw, m, a, b + 1, run, ctrl, obsn)) { status = SLAM_ERR_NOT_PD; break; }
+                    staged = b + 1;
+                }
+            }
+        }
+        if (nz > 0) {
+            if (n + 2 * k > a.ncap) {
+                status = SLAM_ERR_CAPACITY;
+                outgrown = true;
+                if (a.over_list) {
+                    if (tid == 0) sm.par[3] = (double)atomicAdd(a.over_count, 1);
+                    __syncthreads();
+                    over_idx = (int)sm.par[3];
+                    if (a.ckpt_out && over_idx < a.ckpt_out_slots) {
+                        double *c = a.ckpt_out + (size_t)over_idx * a.ckpt_out_stride;
+                        const int po = ck_xo + ens_ru4(a.ncap);
+                        for (int idx = tid; idx < n; idx += T) c[ck_xo + idx] = sm.x[idx];
+                        for (int idx = tid; idx < ens_pdoubles(n); idx += T) c[po + idx] = sm.P[idx];
+                        for (int idx = tid; idx < 2 * k; idx += T) c[CK_ZN + idx] = sm.zn[idx];
+                        if (tid < 3 * len) {
+                            const int st = tid / 3, comp = tid - 3 * st;
+                            c[CK_POSE + tid] = st == len - 1 ? sm.x[comp] : sm.bs[st * BS + B_X0 + comp];
+                        }
+                        if (tid == 0) { c[1] = n; c[2] = k; c[3] = b; c[4] = flops; c[5] = len; }
+                    }
+                }
+                break;
+            }
             n = ens_add_features<T>(sm, n, k);
             ENS_MARK(13);
         }
+        resume = false;
         // slam_track[:, step] = state.x[1:3] (sim/ekfslam-sim.jl:128): after predict for the inner
         // steps, after update / add_features for the block's last step
         if (track && tid < 3 * len) {
-            const int s = tid / 3, comp = tid - 3 * s;
-            track[3 * (s0 + s) + comp] = s == len - 1 ? sm.x[comp] : sm.bs[s * BS + B_X0 + comp];
+            const int st = tid / 3, comp = tid - 3 * st;
+            track[3 * (s0 + st) + comp] = st == len - 1 ? sm.x[comp] : sm.bs[st * BS + B_X0 + comp];
         }
         done = s1;
         __syncthreads();
@@ -1002,7 +1061,7 @@ k_ensemble(EnsArgs a) {
         }
     ENS_MARK(-2);
     if (tid == 0) {
-        if (outgrown && a.over_list) a.over_list[atomicAdd(a.over_count, 1)] = member;
+        if (outgrown && a.over_list) a.over_list[over_idx] = member;
         a.n_final[member] = n;
         a.status[member] = status;
         a.steps_done[member] = done;
@@ -1060,6 +1119,8 @@ struct slam_ensemble {
     bool dirty = true;             // tiers / output layout must be rebuilt before the next run
     int ocap = 0;                  // capacity d_final_x / d_final_P are laid out for (the largest shared tier)
     int *d_over = nullptr;         // ENS_MAX_LISTS lists of n_runs + 1 ints: [0] = count, [1 + i] = member
+    double *d_ckpt[ENS_MAX_LISTS] = {nullptr};   // checkpoints written by tier i for tier i + 1 (or the first global round)
+    int ckpt_slots[ENS_MAX_LISTS] = {0}, ckpt_stride[ENS_MAX_LISTS] = {0};
     bool global_pending = false;
     std::vector<EnsGlobalRound> grounds;
     std::vector<int> tier_members; // members each launch of the last run ran (shared tiers, then global rounds)
@@ -1085,6 +1146,7 @@ extern "C" int slam_ens_destroy(slam_ens_t *e) {
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     ens_free_rounds(e);
+    for (auto &c : e->d_ckpt) cudaFree(c);
     cudaFree(e->d_gamma); cudaFree(e->d_ztrue); cudaFree(e->d_blk); cudaFree(e->d_steps_done); cudaFree(e->d_obs_start);
     cudaFree(e->d_ctrl); cudaFree(e->d_obs); cudaFree(e->d_final_x); cudaFree(e->d_tracks);
     cudaFree(e->d_final_P); cudaFree(e->d_n_final); cudaFree(e->d_status); cudaFree(e->d_over); cudaFree(e->d_flops);
@@ -1342,6 +1404,27 @@ static int ens_prepare(slam_ens_t *e) {
     CUDA_TRY(cudaFuncSetAttribute(k_ensemble<256, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, top));
     CUDA_TRY(cudaFuncSetAttribute(k_ensemble<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)ens_fixed_bytes(ens_mmax(e))));
+    // checkpoint slots of every tier that has a successor: an eighth of the members behind the first pass, a
+    // sixty-fourth behind the others (course1: 3.6 % / 0.4 % outgrow them); members past the slots are re-run
+    for (int i = 0; i < ENS_MAX_LISTS; i++) {
+        cudaFree(e->d_ckpt[i]);
+        e->d_ckpt[i] = nullptr;
+        e->ckpt_slots[i] = e->ckpt_stride[i] = 0;
+    }
+    const char *ck_env = getenv("SLAM_ENS_CKPT");          // SLAM_ENS_CKPT=0: re-run outgrown members from their first step
+    const bool ck_on = !(ck_env && atoi(ck_env) == 0);
+    for (int i = 0; i < (int)e->tiers.size() && ck_on; i++) {
+        if (!(i + 1 < (int)e->tiers.size() || e->growth == 2)) continue;
+        const int slots = std::min(e->n_runs, std::max(64, e->n_runs / (i == 0 ? 8 : 64)));
+        const int stride = ens_ckpt_doubles(e->tiers[i].ncap, ens_mmax(e));
+        if (cudaMalloc(&e->d_ckpt[i], sizeof(double) * (size_t)slots * stride) != cudaSuccess) {
+            cudaGetLastError();      // no room for checkpoints: those members are re-run from their first step
+            e->d_ckpt[i] = nullptr;
+            continue;
+        }
+        e->ckpt_slots[i] = slots;
+        e->ckpt_stride[i] = stride;
+    }
     e->ocap = e->tiers.back().ncap;
     cudaFree(e->d_final_x);
     cudaFree(e->d_final_P);
@@ -1377,6 +1460,8 @@ static EnsArgs ens_args(const slam_ens_t *e) {
     a.redo_list = a.redo_count = nullptr;
     a.gstate = nullptr;
     a.gstride = 0;
+    a.ckpt_out = nullptr; a.ckpt_out_slots = a.ckpt_out_stride = 0;
+    a.ckpt_in = nullptr; a.ckpt_in_slots = a.ckpt_in_stride = a.ckpt_in_ncap = 0;
     a.flops = e->d_flops;
     return a;
 }
@@ -1388,6 +1473,7 @@ static void ens_set_capacity(EnsArgs &a, int ncap) {
 }
 
 extern "C" int slam_ens_run(slam_ens_t *e) {
+    SLAM_NVTX();
     E_CHECK(e);
     int rc = ens_prepare(e);
     if (rc) return rc;
@@ -1402,6 +1488,11 @@ extern "C" int slam_ens_run(slam_ens_t *e) {
         a.redo_count = prev; a.redo_list = prev ? prev + 1 : nullptr;
         const bool more = i + 1 < nt || e->growth == 2;    // someone will re-run what this launch cannot hold
         a.over_count = more ? next : nullptr; a.over_list = more ? next + 1 : nullptr;
+        a.ckpt_out = more ? e->d_ckpt[i] : nullptr;
+        a.ckpt_out_slots = e->ckpt_slots[i]; a.ckpt_out_stride = e->ckpt_stride[i];
+        a.ckpt_in = i ? e->d_ckpt[i - 1] : nullptr;
+        a.ckpt_in_slots = i ? e->ckpt_slots[i - 1] : 0; a.ckpt_in_stride = i ? e->ckpt_stride[i - 1] : 0;
+        a.ckpt_in_ncap = i ? e->tiers[i - 1].ncap : 0;
         ens_launch(e, a, e->n_runs, e->tiers[i].smem);     // CTAs past the redo count exit at once
         e->launches++;
     }
@@ -1456,6 +1547,11 @@ static int ens_global_rounds(slam_ens_t *e) {
         CUDA_TRY(cudaMemsetAsync(next, 0, sizeof(int), e->stream));
         a.redo_count = prev; a.redo_list = prev + 1;
         a.over_count = next; a.over_list = next + 1;
+        if (e->grounds.empty() && e->d_ckpt[nt - 1]) {    // the first round resumes from the last shared tier's checkpoints
+            a.ckpt_in = e->d_ckpt[nt - 1];
+            a.ckpt_in_slots = e->ckpt_slots[nt - 1]; a.ckpt_in_stride = e->ckpt_stride[nt - 1];
+            a.ckpt_in_ncap = e->tiers.back().ncap;
+        }
         k_ensemble<128, true><<<count, 128, ens_fixed_bytes(mmax), e->stream>>>(a);
         e->launches++;
         CUDA_TRY(cudaGetLastError());
@@ -1513,6 +1609,7 @@ extern "C" int slam_ens_tier_info(slam_ens_t *e, int *capacity, int *members, in
 }
 
 extern "C" int slam_ens_sync(slam_ens_t *e) {
+    SLAM_NVTX();
     E_CHECK(e);
     int rc = ens_finish(e);
     if (rc) return rc;

@@ -299,6 +299,7 @@ __global__ void k_set_pose_snapshot(const double *x, double *pose_slot) {
 }
 
 extern "C" int slam_set_state(slam_t *h, const double *x, const double *P, int n, int ldp) {
+    SLAM_NVTX();
     H_CHECK(h);
     ARG_CHECK(x && P, "NULL x or P");
     ARG_CHECK(n >= 3 && (n - 3) % 2 == 0, "n must be 3 + 2*Nf");
@@ -323,6 +324,7 @@ extern "C" int slam_set_state(slam_t *h, const double *x, const double *P, int n
 }
 
 extern "C" int slam_get_state(slam_t *h, double *x, double *P, int ldp) {
+    SLAM_NVTX();
     H_CHECK(h);
     int n = h->n;
     if (P) {
@@ -432,6 +434,7 @@ k_predict(double *x, double *P, size_t ld, int n, PredictParams p, const double 
 }
 
 extern "C" int slam_predict(slam_t *h, double g, double v, double wheelbase, const double Q[4], double dt) {
+    SLAM_NVTX();
     H_CHECK(h);
     ARG_CHECK(Q != nullptr, "NULL Q");
     PredictParams p;
@@ -452,6 +455,7 @@ extern "C" int slam_predict(slam_t *h, double g, double v, double wheelbase, con
 // ---------------------------------------------------------------------------------------
 extern "C" int slam_associate(slam_t *h, const double *z, int nz, const double R[4], double gate1,
                               double gate2, double *zf, int64_t *idf, int *m, double *zn, int *k) {
+    SLAM_NVTX();
     H_CHECK(h);
     ARG_CHECK(R && m && k, "NULL argument");
     ARG_CHECK(nz >= 0, "nz < 0");
@@ -1264,6 +1268,7 @@ extern "C" int slam_profile_read(slam_t *h, double *k6_ms, int *k6_updates) {
 
 extern "C" int slam_update_resident(slam_t *h, const double *d_zf, int m, const double R[4],
                                     const int64_t *d_idf) {
+    SLAM_NVTX();
     H_CHECK(h);
     ARG_CHECK(m >= 0 && R, "bad argument");
     ARG_CHECK(m == 0 || (d_zf && d_idf), "NULL device buffer");
@@ -1271,6 +1276,7 @@ extern "C" int slam_update_resident(slam_t *h, const double *d_zf, int m, const 
 }
 
 extern "C" int slam_update(slam_t *h, const double *zf, int m, const double R[4], const int64_t *idf) {
+    SLAM_NVTX();
     H_CHECK(h);
     ARG_CHECK(m >= 0 && R, "bad argument");
     if (m == 0) return SLAM_OK;
@@ -1376,6 +1382,7 @@ k_augment(double *x, double *P, size_t ld, int n0, const double *__restrict__ zn
 }
 
 extern "C" int slam_add_features(slam_t *h, const double *zn, int k, const double R[4]) {
+    SLAM_NVTX();
     H_CHECK(h);
     ARG_CHECK(k >= 0 && R, "bad argument");
     if (k == 0) return SLAM_OK;

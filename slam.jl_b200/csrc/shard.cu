@@ -889,6 +889,7 @@ static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const
 
 extern "C" int slam_shard_update_resident(slam_shard_t *s, const double *d_zf, int m, const double R[4],
                                           const int64_t *d_idf) {
+    SLAM_NVTX();
     S_CHECK(s);
     ARG_CHECK(m >= 0 && R, "bad argument");
     ARG_CHECK(m == 0 || (d_zf && d_idf), "NULL device buffer");
@@ -896,6 +897,7 @@ extern "C" int slam_shard_update_resident(slam_shard_t *s, const double *d_zf, i
 }
 
 extern "C" int slam_shard_update(slam_shard_t *s, const double *zf, int m, const double R[4], const int64_t *idf) {
+    SLAM_NVTX();
     S_CHECK(s);
     ARG_CHECK(m >= 0 && R, "bad argument");
     if (m == 0) return SLAM_OK;
@@ -1015,6 +1017,7 @@ __global__ void k_sh_predict_x(double *x, ShPredict p) {
 
 extern "C" int slam_shard_predict(slam_shard_t *s, double g, double v, double wheelbase, const double Q[4],
                                   double dt) {
+    SLAM_NVTX();
     S_CHECK(s);
     ARG_CHECK(Q != nullptr, "NULL Q");
     ShPredict p;
@@ -1043,6 +1046,7 @@ __global__ void k_sh_rows012(const double *__restrict__ Pb0, size_t ldb, int n, 
 
 extern "C" int slam_shard_associate(slam_shard_t *s, const double *z, int nz, const double R[4], double gate1,
                                     double gate2, double *zf, int64_t *idf, int *m, double *zn, int *k) {
+    SLAM_NVTX();
     S_CHECK(s);
     ARG_CHECK(R && m && k && nz >= 0, "bad argument");
     *m = 0;
@@ -1188,6 +1192,7 @@ k_sh_augment(double *x, const double *__restrict__ P3, int npad, double *Pl, siz
 }
 
 extern "C" int slam_shard_add_features(slam_shard_t *s, const double *zn, int k, const double R[4]) {
+    SLAM_NVTX();
     S_CHECK(s);
     ARG_CHECK(k >= 0 && R, "bad argument");
     if (k == 0) return SLAM_OK;
