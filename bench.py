@@ -173,6 +173,38 @@ def cpu_baseline_block(n_workload: int, m: int, steps: int = 3, warmup: int = 1,
     }
 
 
+def mem_available_gb() -> float:
+    try:
+        for ln in open("/proc/meminfo"):
+            if ln.startswith("MemAvailable:"):
+                return float(ln.split()[1]) / 1e6
+    except OSError:
+        pass
+    return 0.0
+
+
+def cpu_full_size_step(n_landmarks: int, m: int, need_gb: float):
+    """ONE update of the literal numpy restatement at the workload's own size (no extrapolation), when the host has
+    the memory for numpy's three copies of P (old P, W1 W1', the difference).  Validates the (n_sample / n)^2 scaling
+    the cpu_baseline / reference-arm figures rest on."""
+    avail = mem_available_gb()
+    n = 3 + 2 * n_landmarks
+    if avail < need_gb:
+        return {"ran": False, "why": f"needs ~{need_gb:.0f} GB of host memory for three copies of P, {avail:.0f} GB available"}
+    from oracle import slam_ref as ref
+    t0 = time.perf_counter()
+    x, P, z, ids = cpu_reference_state(n_landmarks, m)
+    t_setup = time.perf_counter() - t0
+    R = R_OBS.reshape(2, 2)
+    t0 = time.perf_counter()
+    x, P = ref.update(x, P, z, R, ids)
+    sec = time.perf_counter() - t0
+    del P
+    return {"ran": True, "n": n, "m": m, "seconds_per_step": sec, "value": 1.0 / sec, "unit": "update steps/s",
+            "cores": os.cpu_count() or 1, "setup_seconds": t_setup,
+            "what": "oracle/slam_ref.py update, ONE step at the workload's own size (measured, not extrapolated)"}
+
+
 def cpu_associate_baseline(n_landmarks: int = 1000, nz: int = 2):
     """The reference's literal associate (src/data-association.jl:1-63: a dense 2 x n Jacobian and H*P*H' per
     (observation, landmark) pair) at n = 2003, and what that costs per pair; above that size only an
@@ -827,6 +859,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extras", action="store_true", help="skip update_10k / ensemble / sweep side measurements")
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle check before timing")
+    ap.add_argument("--no-full-cpu", action="store_true", help="skip the one full-size CPU step of cpu_baseline")
     ap.add_argument("--sustained", type=float, default=5.0, help="seconds of back-to-back updates (0 = skip)")
     ap.add_argument("--gb-per-gpu", type=float, default=None, help="override P bytes per GPU (GB)")
     args = ap.parse_args()
@@ -989,6 +1022,11 @@ def main():
                 extras["update_10k"]["cpu_baseline"] = {
                     "value": cb["measured_steps_per_s_at_sample"], "unit": "update steps/s", "cores": cb["cores"],
                     "kind": "port", "sample": "oracle/slam_ref.py update at n = 20003, m = 8: the same size, measured"}
+            if not args.no_full_cpu:
+                fs = cpu_full_size_step(nl, args.m, need_gb=3.4 * 8.0 * n * n / 1e9)
+                line["cpu_baseline"]["full_size_step"] = fs
+                if fs.get("ran"):
+                    fs["extrapolated_over_measured"] = cb["value"] / fs["value"]
             line["cpu_baseline"]["associate"] = cpu_associate_baseline()
             line["cpu_baseline"]["course1_config1"] = cpu_course1_baseline()
     line.update(extras)

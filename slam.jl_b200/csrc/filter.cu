@@ -86,6 +86,10 @@ struct slam_filter {
     size_t block_cap = 0;
     int variant = 0;
     long long launches = 0;
+    // x[0:3] as read back with the last host-path update's status (one synchronisation for both): sim! reads
+    // state.x[1:3] right after every call (sim/ekfslam-sim.jl:128); valid until the next call that changes the state
+    double pose_cache[3] = {0, 0, 0};
+    bool pose_valid = false;
     // K6 event timing (slam_profile)
     bool profiling = false;
     std::vector<cudaEvent_t> ev;   // pairs
@@ -254,8 +258,12 @@ extern "C" int slam_set_downdate_variant(slam_t *h, int variant) {
 
 static int check_latched(slam_t *h) {
     int *he = (int *)h->h_pin;
+    double *hp = (double *)h->h_pin + 8;
     CUDA_TRY(cudaMemcpyAsync(he, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaMemcpyAsync(hp, h->d_x, sizeof(double) * 3, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    h->pose_cache[0] = hp[0]; h->pose_cache[1] = hp[1]; h->pose_cache[2] = hp[2];
+    h->pose_valid = true;      // everything issued so far is complete: the pose is current
     int e = *he;
     if (e != 0) {
         CUDA_TRY(cudaMemsetAsync(h->d_err, 0, sizeof(int), h->stream));
@@ -309,6 +317,7 @@ extern "C" int slam_set_state(slam_t *h, const double *x, const double *P, int n
         return SLAM_ERR_CAPACITY;
     }
     CUDA_TRY(cudaStreamSynchronize(h->stream));
+    h->pose_valid = false;
     CUDA_TRY(cudaMemsetAsync(h->d_gate_scratch, 0, 256, h->stream));   // K2's last-CTA ticket (robust to an aborted launch)
     CUDA_TRY(cudaMemcpyAsync(h->d_x, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
     CUDA_TRY(cudaMemcpy2DAsync(h->d_P, sizeof(double) * h->ld, P, sizeof(double) * (size_t)ldp,
@@ -343,6 +352,10 @@ extern "C" int slam_get_state(slam_t *h, double *x, double *P, int ldp) {
 extern "C" int slam_get_pose(slam_t *h, double pose[3]) {
     H_CHECK(h);
     ARG_CHECK(pose != nullptr, "NULL pose");
+    if (h->pose_valid) {       // read back together with the status of the call that produced it
+        pose[0] = h->pose_cache[0]; pose[1] = h->pose_cache[1]; pose[2] = h->pose_cache[2];
+        return SLAM_OK;
+    }
     double *hp = (double *)h->h_pin + 8;
     CUDA_TRY(cudaMemcpyAsync(hp, h->d_x, sizeof(double) * 3, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
@@ -437,6 +450,7 @@ extern "C" int slam_predict(slam_t *h, double g, double v, double wheelbase, con
     SLAM_NVTX();
     H_CHECK(h);
     ARG_CHECK(Q != nullptr, "NULL Q");
+    h->pose_valid = false;
     PredictParams p;
     p.g = g; p.v = v; p.w = wheelbase; p.dt = dt;
     memcpy(p.Q, Q, sizeof(p.Q));
@@ -1190,6 +1204,7 @@ static int update_device(slam_t *h, const double *d_zf, int m, const double R[4]
         slam_set_error("slam_update: %d observations but the map is empty", m);
         return SLAM_ERR_BAD_INDEX;
     }
+    h->pose_valid = false;
     const int Rk = 2 * m;
     int rc = ensure_update_ws(h, Rk);
     if (rc) return rc;
@@ -1590,6 +1605,7 @@ extern "C" int slam_synth_state(slam_t *h, int n_landmarks, double side, uint64_
         slam_set_error("slam_synth_state: n = %d exceeds capacity n_max = %d", n, h->n_max);
         return SLAM_ERR_CAPACITY;
     }
+    h->pose_valid = false;
     CUDA_TRY(cudaMemsetAsync(h->d_gate_scratch, 0, 256, h->stream));
     int rc = synth_fill(h->d_x, h->d_P, h->ld, 0, n, n_landmarks, side, seed, h->stream, &h->launches);
     if (rc) return rc;
