@@ -93,6 +93,11 @@ int slam_n(slam_t *h);
 /* A sub-block cov[i0:i0+ni, j0:j0+nj] (0-based, full symmetric view) for front ends that
  * must not pull all of P (resident mode). */
 int slam_get_cov_block(slam_t *h, int i0, int ni, int j0, int nj, double *out, int ldo);
+/* Diagnostic, no counterpart in the reference (its arrays have no capacity padding): arm != 0 paints every element of
+ * the device slab (ld x n_max) and of x outside the live state [0, n) with a NaN payload; arm == 0 writes to *changed
+ * how many painted elements have been overwritten since.  predict / associate / update must leave it at 0;
+ * add_features moves n and owns the rows and columns it adds.  Used by the tests in place of a memory checker. */
+int slam_debug_guard(slam_t *h, int arm, long long *changed);
 
 /* compute_landmark_ellipses -- src/common.jl:236-262 (with ellipse, :236-244), computed on the
  * device from the 2x2 diagonal blocks only: out is (2*Nf) x (nsegs+1) column-major with leading

@@ -394,6 +394,51 @@ extern "C" int slam_get_cov_block(slam_t *h, int i0, int ni, int j0, int nj, dou
     return SLAM_OK;
 }
 
+// Padding guard (diagnostic; stands in for compute-sanitizer, which this pool does not offer).  The slab is ld x n_max
+// doubles and x is ld doubles; predict / associate / update own only [0, n) x [0, n) and x[0, n).  arm = 1 paints every
+// other element with a quiet-NaN payload, arm = 0 counts the painted elements whose bits have changed since.
+static constexpr unsigned long long GUARD_BITS = 0x7FF8C0DEC0DEC0DEull;
+
+__global__ void k_guard(double *x, double *P, size_t ld, int n, int n_max, int arm, unsigned long long *changed) {
+    const size_t total = ld * (size_t)n_max + ld;                // the slab, then x
+    unsigned long long bad = 0;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        double *p;
+        if (e < ld * (size_t)n_max) {
+            const size_t i = e % ld, j = e / ld;
+            if (i < (size_t)n && j < (size_t)n) continue;
+            p = P + e;
+        } else {
+            const size_t i = e - ld * (size_t)n_max;
+            if (i < (size_t)n) continue;
+            p = x + i;
+        }
+        if (arm) *p = __longlong_as_double((long long)GUARD_BITS);
+        else if ((unsigned long long)__double_as_longlong(*p) != GUARD_BITS) bad++;
+    }
+    if (!arm && bad) atomicAdd(changed, bad);
+}
+
+extern "C" int slam_debug_guard(slam_t *h, int arm, long long *changed) {
+    H_CHECK(h);
+    ARG_CHECK(arm || changed != nullptr, "NULL changed");
+    unsigned long long *d_cnt = nullptr;
+    CUDA_TRY(cudaMalloc(&d_cnt, sizeof(unsigned long long)));
+    cudaError_t e = cudaMemsetAsync(d_cnt, 0, sizeof(unsigned long long), h->stream);
+    if (e == cudaSuccess) {
+        k_guard<<<148 * 8, 256, 0, h->stream>>>(h->d_x, h->d_P, h->ld, h->n, h->n_max, arm, d_cnt);
+        h->launches++;
+        e = cudaGetLastError();
+    }
+    unsigned long long cnt = 0;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&cnt, d_cnt, sizeof(cnt), cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(d_cnt);
+    CUDA_TRY(e);
+    if (changed) *changed = (long long)cnt;
+    return SLAM_OK;
+}
+
 // ---------------------------------------------------------------------------------------
 // K1 predict -- src/ekf.jl:8-43.  O(n): rows 1:3 of every column.
 // Bytes: 24 read + 16 written per map column (+ the 3x3 block and x[1:3]).

@@ -137,6 +137,16 @@ class _Handle:
         check(lib.slam_get_cov_block(self.ptr, i0, ni, j0, nj, dptr(out), max(ni, 1)))
         return np.ascontiguousarray(out)
 
+    def guard_arm(self):
+        """Paint the device slab and x outside the live state (slam_debug_guard): see guard_changed."""
+        check(lib.slam_debug_guard(self.ptr, 1, None))
+
+    def guard_changed(self) -> int:
+        """How many painted padding elements have been overwritten since guard_arm()."""
+        c = C.c_longlong(-1)
+        check(lib.slam_debug_guard(self.ptr, 0, C.byref(c)))
+        return int(c.value)
+
     # -- raw operations ------------------------------------------------------------------
     def predict(self, g, v, w, Q, dt):
         q = _mat2(Q)

@@ -810,3 +810,83 @@ def test_closed_loop_large_course(sc, twin, course1):
           f"{out['launches']} launches")
     assert e_track < TRACK_TOL and rel_err(out["x"], xo[:nfin]) < TRACK_TOL and rel_err(out["P"], Pt) < TRACK_TOL
     assert nfin > 3 + 2 * 250 and mg.value > 1e-9
+
+
+@pytest.mark.parametrize("nf,m,spare", [(333, 1, 5), (333, 4, 8), (333, 7, 21), (333, 10, 1), (517, 16, 37), (517, 24, 3),
+                                        (130, 30, 77), (200, 36, 10), (61, 30, 2)])
+def test_padding_guard_no_stray_writes(sc, nf, m, spare):
+    """Own memory check (compute-sanitizer is closed on this pool).  The slab has capacity n + spare (ragged, so tiles
+    of every kernel straddle the edge of the live state); slam_debug_guard paints the slab and x outside [0, n) with a
+    NaN payload, then predict, associate (pre-gate on and off), update with every downdate kernel the rank admits, the
+    ellipse / block read-outs and add_features run.  No painted element may change (add_features moves n and owns what
+    it adds), and the results still match the oracle to STEP_TOL: a kernel that READ the padding into a result would
+    carry the NaN into it."""
+    from slamcuda._ffi import lib, check
+    from slamcuda.slam import _Handle
+    k = ref.sim_constants()
+    R, Q = k["R"], k["Q"]
+    rng = np.random.default_rng(1000 * nf + 10 * m + spare)
+    x, P = _random_state(rng, nf)
+    n = len(x)
+    ids = rng.choice(nf, size=m, replace=False) + 1
+    z = np.zeros((2, m))
+    for c, idf in enumerate(ids):
+        zp, _ = ref.predict_observation(x, int(idf))
+        z[:, c] = zp + rng.normal(0, [0.1, 0.01])
+    rank = 2 * m
+    variants = [0] + ([1] if rank <= 32 or rank > 64 else []) + ([2] if 24 < rank <= 32 or rank > 64 else []) \
+        + ([3] if 12 <= rank <= 64 else [])
+    for variant in variants:
+        h = _Handle(0, n + spare, grow=False)
+        check(lib.slam_set_downdate_variant(h.ptr, variant))
+        h.set_state(x, P)
+        h.guard_arm()
+        assert h.guard_changed() == 0
+        h.predict(0.02, 3.0, 4.0, Q, 0.025)
+        xr, Pr = ref.predict(x.copy(), P.copy(), 0.02, 3.0, 4.0, Q, 0.025)     # the oracle's predict works in place
+        for pg in (True, False):
+            h.set_pregate(pg)
+            h.associate(z, R, 4.0, 25.0)
+        assert h.guard_changed() == 0, "predict / associate wrote outside the live state"
+        h.update(z, R, ids)
+        xr, Pr = ref.update(xr, Pr, z, R, ids)
+        h.cov_block(0, n, max(n - 5, 0), min(5, n))
+        h.landmark_ellipses()
+        h.feature_ellipses()
+        changed = h.guard_changed()
+        assert changed == 0, f"update (variant {variant}, rank {rank}) overwrote {changed} padding elements"
+        xg, Pg = h.get_state()
+        assert np.isfinite(xg).all() and np.isfinite(Pg).all()
+        assert state_err(xg, Pg, xr, Pr) < STEP_TOL
+        knew = min(spare // 2, 3)
+        if knew:
+            zn = np.array([rng.uniform(5, 25, knew), rng.uniform(-1, 1, knew)])
+            h.add_features(zn, R)
+            xr, Pr = ref.add_features(xr, Pr, zn, R)
+            assert h.n == n + 2 * knew
+            assert h.guard_changed() == 0, "add_features wrote beyond the rows and columns it adds"
+            h.update(z, R, ids)                                  # the grown state through the same kernels
+            xr, Pr = ref.update(xr, Pr, z, R, ids)
+            assert h.guard_changed() == 0
+            xg, Pg = h.get_state()
+            assert np.isfinite(Pg).all() and state_err(xg, Pg, xr, Pr) < STEP_TOL
+        h.close()
+
+
+def test_padding_guard_detects_a_write(sc):
+    """Positive control for slam_debug_guard: after arming at n, a state of n - 2 set into the same handle leaves the
+    band that used to be live (never painted) outside the new live state, so the guard must count exactly
+    n^2 - (n - 2)^2 elements of the slab + 2 of x; re-arming clears it."""
+    from slamcuda.slam import _Handle
+    rng = np.random.default_rng(3)
+    x, P = _random_state(rng, 20)
+    n = len(x)
+    h = _Handle(0, n + 9, grow=False)
+    h.set_state(x, P)
+    h.guard_arm()
+    assert h.guard_changed() == 0
+    h.set_state(x[:n - 2], np.ascontiguousarray(P[:n - 2, :n - 2]))
+    assert h.guard_changed() == n * n - (n - 2) * (n - 2) + 2
+    h.guard_arm()
+    assert h.guard_changed() == 0
+    h.close()
