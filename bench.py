@@ -331,6 +331,10 @@ def gather_single(h, lib, check, dptr):
     return gather
 
 
+# slam_downdate_kernel / slam_shard_downdate_kernel: the kernel the library's dispatcher ran for the last update
+K6_KERNELS = {1: "k_downdate_fma", 2: "k_downdate_dmma", 3: "k_downdate_stream"}
+
+
 def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_steps: int, device: int = 0,
                       barrier=None, host_mirror_steps: int = 0, parity: bool = False, sustained_s: float = 0.0,
                       sweep_m=()):
@@ -412,7 +416,7 @@ def gpu_update_single(n_landmarks: int, m: int, steps: int, warmup: int, e2e_ste
 
         ms_step, k6_ms, launches = timed(d_zf, d_idf, m, steps, warmup)
         out.update(n=n, m=m, ms_per_step=ms_step, k6_ms=k6_ms, launches=launches, assoc_ms=t_assoc * 1e3, nz=nz,
-                   new=n_new)
+                   new=n_new, k6_kernel=K6_KERNELS.get(int(lib.slam_downdate_kernel(h)), "unknown"))
         if sustained_s > 0:
             # seconds of back-to-back updates: the power-capped figure beside the 20-step burst
             ns = min(4000, max(steps, int(math.ceil(sustained_s * 1e3 / ms_step))))
@@ -767,7 +771,7 @@ def gpu_update_sharded(n_landmarks: int, m: int, steps: int, warmup: int, e2e_st
         phase_ms = {nm: {"min": float(phases[:, i].min()), "max": float(phases[:, i].max())} for i, nm in enumerate(names)}
         ms, k6ms = float(phases[:, 4].max()), float(phases[:, 3].max())
         out.update(n=n, m=m, ms_per_step=ms, k6_ms=k6ms, launches=launches * world, assoc_ms=t_assoc * 1e3,
-                   phase_ms=phase_ms)
+                   phase_ms=phase_ms, k6_kernel=K6_KERNELS.get(int(lib.slam_shard_downdate_kernel(sf.ptr)), "unknown"))
         if sustained_s > 0:
             ns = min(2000, max(steps, int(math.ceil(sustained_s * 1e3 / ms))))
             ph2, _ = timed(ns, 0)
@@ -989,7 +993,7 @@ def main():
                 "path": "slam_update() with host zf/idf (resident mode: P stays in HBM, as sim! re-binds it)"},
         "gpu_launches": r["launches"],
         "parity": {"ok": parity_ok, **parity_all} if parity_all else None,
-        "roofline": {"bound": "hbm", "kernel": "k_downdate_fma (K6, P -= W1*W1' over the upper triangle)",
+        "roofline": {"bound": "hbm", "kernel": r.get("k6_kernel", "unknown") + " (K6, P -= W1*W1' over the upper triangle)",
                      "achieved": k6_gbs, "peak": peak, "unit": "GB/s", "frac": k6_gbs / peak,
                      "traffic": traffic, "peak_source": peak_src,
                      **({"traffic_source": traffic_src} if traffic_src else {}),

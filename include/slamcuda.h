@@ -172,6 +172,8 @@ void *slam_stream(slam_t *h);
  * FP64 DMMA tensor-core kernel (where its 32-wide chunk layout applies), 3 = force the streaming DMMA kernel
  * (12..64 ranks).  A forced variant that does not apply to the rank falls through to the automatic choice. */
 int slam_set_downdate_variant(slam_t *h, int variant);
+/* Which kernel the last update's downdate ran: 0 none yet, 1 k_downdate_fma, 2 k_downdate_dmma (tiled), 3 k_downdate_stream. */
+int slam_downdate_kernel(slam_t *h);
 /* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
 long long slam_launch_count(slam_t *h);
 /* Kernel timing for roofline reports: while on, every update records a CUDA event pair
@@ -306,6 +308,8 @@ int slam_shard_update(slam_shard_t *s, const double *zf, int m, const double R[4
  * into every rank's buffers over NVLink, CUDA IPC mappings, flag barrier), 0 when it uses NCCL
  * collectives (SLAM_SHARD_P2P=0, world = 1, or IPC refused).  Both give bit-identical results. */
 int slam_shard_p2p(slam_shard_t *s);
+/* As slam_downdate_kernel, for the sharded filter's last update. */
+int slam_shard_downdate_kernel(slam_shard_t *s);
 /* add_features -- src/ekf.jl:84-122 on the sharded covariance: rows 0..2 of P are broadcast from
  * rank 0, every rank fills its own rows of the 2k new columns, the owner of the new rows' panel the diagonal
  * blocks.  Collective: call on every rank. */

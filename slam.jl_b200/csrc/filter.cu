@@ -85,6 +85,7 @@ struct slam_filter {
     double *d_block = nullptr;  // cov-block staging
     size_t block_cap = 0;
     int variant = 0;
+    int last_k6 = 0;               // downdate kernel of the last update: 1 FMA, 2 tiled DMMA, 3 streaming DMMA
     long long launches = 0;
     // x[0:3] as read back with the last host-path update's status (one synchronisation for both): sim! reads
     // state.x[1:3] right after every call (sim/ekfslam-sim.jl:128); valid until the next call that changes the state
@@ -254,6 +255,10 @@ extern "C" int slam_set_downdate_variant(slam_t *h, int variant) {
     ARG_CHECK(variant >= 0 && variant <= 3, "variant must be 0, 1, 2 or 3");
     h->variant = variant;
     return SLAM_OK;
+}
+extern "C" int slam_downdate_kernel(slam_t *h) {
+    ARG_CHECK(h != nullptr, "NULL handle");
+    return h->last_k6;
 }
 
 static int check_latched(slam_t *h) {
@@ -1291,6 +1296,7 @@ static int update_device(slam_t *h, const double *d_zf, int m, const double R[4]
     CUDA_TRY(cudaGetLastError());
     const bool timed = h->profiling && h->ev_used + 2 <= (int)h->ev.size();
     if (timed) CUDA_TRY(cudaEventRecord(h->ev[h->ev_used], h->stream));
+    h->last_k6 = downdate_kernel_choice(Rk, h->variant, h->ld);
     rc = launch_downdate(h->d_P, h->ld, n, h->d_W1c, npad, Rk, h->variant, h->stream, &h->launches);
     if (timed) {
         CUDA_TRY(cudaEventRecord(h->ev[h->ev_used + 1], h->stream));

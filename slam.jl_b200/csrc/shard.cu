@@ -139,6 +139,7 @@ struct slam_shard {
     int nloc = 0, nlp = 0;      // local row capacity (256 x local panels at n_max) and local panels in use at n
     // peer-memory exchange
     bool p2p = false;
+    int last_k6 = 0;               // downdate kernel of the last update (slam_shard_downdate_kernel)
     void *arenaA = nullptr, *arenaB = nullptr;          // peer-visible: [x | flags], [rowbuf | W1c]
     void *peerA[SH_MAXW] = {nullptr}, *peerB[SH_MAXW] = {nullptr};
     unsigned long long *flags = nullptr;                // [SH_MAXW] in arena A: flags[r] = rank r's last epoch
@@ -334,6 +335,11 @@ extern "C" int slam_shard_create(int device, int rank, int world, const char id[
 extern "C" int slam_shard_p2p(slam_shard_t *s) {
     if (!s) { slam_set_error("slam_shard_p2p: NULL handle"); return SLAM_ERR_ARG; }
     return s->p2p ? 1 : 0;
+}
+
+extern "C" int slam_shard_downdate_kernel(slam_shard_t *s) {
+    if (!s) { slam_set_error("slam_shard_downdate_kernel: NULL handle"); return SLAM_ERR_ARG; }
+    return s->last_k6;
 }
 
 extern "C" int slam_shard_n(slam_shard_t *s) {
@@ -878,6 +884,7 @@ static int shard_update_device(slam_shard_t *s, const double *d_zf, int m, const
     }
     CUDA_TRY(cudaGetLastError());
     if (timed) CUDA_TRY(cudaEventRecord(ev[3], st));
+    s->last_k6 = downdate_kernel_choice(Rk, 0, s->ldl);
     rc = launch_downdate_map(s->d_Pl, s->ldl, rowmap_panels(s->rank, s->world, s->nlp), s->n, s->d_W1c, npad, Rk, 0, st,
                              &s->launches);
     if (timed) {

@@ -890,3 +890,26 @@ def test_padding_guard_detects_a_write(sc):
     h.guard_arm()
     assert h.guard_changed() == 0
     h.close()
+
+
+def test_downdate_kernel_choice_is_reported(sc):
+    """slam_downdate_kernel names the kernel the dispatcher ran for the last update (bench.py labels its roofline with
+    it): FMA up to 4 ranks, streaming DMMA for 8..64, tiled DMMA above; a forced variant is reported as forced."""
+    from slamcuda._ffi import lib, check
+    from slamcuda.slam import _Handle
+    R = ref.sim_constants()["R"]
+    rng = np.random.default_rng(11)
+    x, P = _random_state(rng, 120)
+    h = _Handle(0, len(x))
+    assert lib.slam_downdate_kernel(h.ptr) == 0
+    for m, want in [(1, 1), (2, 1), (4, 3), (8, 3), (16, 3), (32, 3), (40, 2)]:
+        h.set_state(x, P)
+        ids = rng.choice(120, size=m, replace=False) + 1
+        z = np.stack([ref.predict_observation(x, int(i))[0] for i in ids], axis=1)
+        h.update(z, R, ids)
+        assert lib.slam_downdate_kernel(h.ptr) == want, (m, lib.slam_downdate_kernel(h.ptr))
+    check(lib.slam_set_downdate_variant(h.ptr, 1))
+    h.set_state(x, P)
+    h.update(z[:, :8], R, ids[:8])
+    assert lib.slam_downdate_kernel(h.ptr) == 1
+    h.close()
