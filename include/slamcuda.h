@@ -296,7 +296,9 @@ int slam_shard_n(slam_shard_t *s);
 int slam_shard_get_pose(slam_shard_t *s, double pose[3]);
 int slam_shard_get_x(slam_shard_t *s, double *x);
 /* Rows [i0, i0+ni) x cols [j0, j0+nj) of the authoritative upper triangle owned by this
- * rank (entries not owned / below the diagonal are left untouched); returns count copied. */
+ * rank: rows this rank does not own are left untouched in `out`; of the rows it owns the whole
+ * window is copied as stored, so entries below the diagonal are overwritten with unspecified
+ * values (the lower triangle is never maintained).  Returns the count copied. */
 int slam_shard_get_cov_block(slam_shard_t *s, int i0, int ni, int j0, int nj, double *out, int ldo);
 int slam_shard_predict(slam_shard_t *s, double g, double v, double wheelbase, const double Q[4],
                        double dt);
@@ -310,6 +312,9 @@ int slam_shard_update(slam_shard_t *s, const double *zf, int m, const double R[4
 int slam_shard_p2p(slam_shard_t *s);
 /* As slam_downdate_kernel, for the sharded filter's last update. */
 int slam_shard_downdate_kernel(slam_shard_t *s);
+/* As slam_debug_guard, for this rank's row-panel stack (ldl x n_max) and its copy of x: a slot is live when its local
+ * row holds a global row < n of the current state and its column is < n.  Rank-local, no collective. */
+int slam_shard_debug_guard(slam_shard_t *s, int arm, long long *changed);
 /* add_features -- src/ekf.jl:84-122 on the sharded covariance: rows 0..2 of P are broadcast from
  * rank 0, every rank fills its own rows of the 2k new columns, the owner of the new rows' panel the diagonal
  * blocks.  Collective: call on every rank. */

@@ -763,6 +763,51 @@ static ShardGeom geom(const slam_shard_t *s) {
     return g;
 }
 
+// Padding guard of the rank's panel stack and of x (diagnostic, as slam_debug_guard; rank-local, no collective).  A
+// slot (li, j) of the ldl x n_max stack is live when local row li holds a global row i < n of the current state and
+// j < n; arm = 1 paints every other slot and x[n, npad) with a NaN payload, arm = 0 counts the painted ones that changed.
+static constexpr unsigned long long SH_GUARD_BITS = 0x7FF8C0DEC0DEC0DEull;
+
+__global__ void k_sh_guard(ShardGeom g, double *x, int n_max, int arm, unsigned long long *changed) {
+    const size_t slab = g.ldl * (size_t)n_max, total = slab + (size_t)g.npad;
+    unsigned long long bad = 0;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        double *p;
+        if (e < slab) {
+            const int li = (int)(e % g.ldl), j = (int)(e / g.ldl);
+            if (j < g.n && li < g.nlp * SH_PH && local_row_global(g, li) >= 0) continue;
+            p = g.Pl + e;
+        } else {
+            const size_t i = e - slab;
+            if (i < (size_t)g.n) continue;
+            p = x + i;
+        }
+        if (arm) *p = __longlong_as_double((long long)SH_GUARD_BITS);
+        else if ((unsigned long long)__double_as_longlong(*p) != SH_GUARD_BITS) bad++;
+    }
+    if (!arm && bad) atomicAdd(changed, bad);
+}
+
+extern "C" int slam_shard_debug_guard(slam_shard_t *s, int arm, long long *changed) {
+    S_CHECK(s);
+    ARG_CHECK(arm || changed != nullptr, "NULL changed");
+    unsigned long long *d_cnt = nullptr;
+    CUDA_TRY(cudaMalloc(&d_cnt, sizeof(unsigned long long)));
+    cudaError_t e = cudaMemsetAsync(d_cnt, 0, sizeof(unsigned long long), s->stream);
+    if (e == cudaSuccess) {
+        k_sh_guard<<<148 * 8, 256, 0, s->stream>>>(geom(s), s->d_x, s->n_max, arm, d_cnt);
+        s->launches++;
+        e = cudaGetLastError();
+    }
+    unsigned long long cnt = 0;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&cnt, d_cnt, sizeof(cnt), cudaMemcpyDeviceToHost, s->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+    cudaFree(d_cnt);
+    CUDA_TRY(e);
+    if (changed) *changed = (long long)cnt;
+    return SLAM_OK;
+}
+
 static int shard_ensure_ws(slam_shard_t *s, int R) {
     const int RC = downdate_chunk_width(R);
     const int Rw = std::max(round_up(R, RC), 32);

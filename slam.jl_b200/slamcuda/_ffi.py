@@ -79,6 +79,7 @@ _sig("slam_n", I, vp)
 _sig("slam_get_cov_block", I, vp, I, I, I, I, c_double_p, I)
 _sig("slam_downdate_kernel", I, vp)
 _sig("slam_shard_downdate_kernel", I, vp)
+_sig("slam_shard_debug_guard", I, vp, I, C.POINTER(C.c_longlong))
 _sig("slam_debug_guard", I, vp, I, C.POINTER(C.c_longlong))
 _sig("slam_compute_landmark_ellipses", I, vp, D, I, c_double_p, I)
 _sig("slam_vehicle_ellipse", I, vp, D, I, c_double_p)

@@ -62,6 +62,16 @@ class ShardedFilter:
         """True when the update exchanges rows / W1 through peer memory instead of NCCL collectives."""
         return check(lib.slam_shard_p2p(self.ptr)) == 1
 
+    def guard_arm(self):
+        """Paint this rank's panel stack and x outside the live state (slam_shard_debug_guard)."""
+        check(lib.slam_shard_debug_guard(self.ptr, 1, None))
+
+    def guard_changed(self) -> int:
+        """How many painted padding slots of this rank have been overwritten since guard_arm()."""
+        c = C.c_longlong(-1)
+        check(lib.slam_shard_debug_guard(self.ptr, 0, C.byref(c)))
+        return int(c.value)
+
     def synth_state(self, n_landmarks: int, side: float, seed: int):
         check(lib.slam_shard_synth_state(self.ptr, n_landmarks, float(side), seed))
 

@@ -140,3 +140,81 @@ def test_sharded_two_ranks_match_single_filter(p2p):
     assert out.returncode == 0, tail
     assert "SHARD_CHECK PASS" in out.stdout, tail
     assert f"p2p={'True' if p2p == '1' else 'False'}" in out.stdout, tail
+
+
+@pytest.mark.parametrize("nl,m,spare", [(300, 5, 7), (700, 8, 40), (700, 20, 1), (1500, 36, 130)])
+def test_sharded_padding_guard_no_stray_writes(nl, m, spare):
+    """Own memory check of the panel-sharded path (compute-sanitizer is closed on this pool), world = 1: the whole
+    sharded code path (256-row panels, rank-local buffers, panel-mapped K6, sharded gating, augment) on one device.
+    slam_shard_debug_guard paints every slot of the ldl x n_max panel stack that holds no element of the live state,
+    and x[n, npad), with a NaN payload; predict, associate, update and add_features must leave every painted slot as it
+    was (add_features moves n and owns what it adds), and x / P must stay equal to the single filter's and finite."""
+    from slamcuda._ffi import lib, check, dptr, iptr
+    from slamcuda.shard import ShardedFilter
+    from slamcuda.slam import _Handle
+    n = 3 + 2 * nl
+    side = math.sqrt(nl / 0.0035)
+    h = _Handle(0, n + spare, grow=False)
+    check(lib.slam_synth_state(h.ptr, nl, side, 9))
+    sf = ShardedFilter(0, 0, 1, n + spare)
+    sf.synth_state(nl, side, 9)
+    sf.guard_arm()
+    assert sf.guard_changed() == 0
+    nz = m + 3
+    z = np.zeros(2 * nz)
+    ids = np.zeros(m, dtype=np.int64)
+    check(lib.slam_synth_observations(h.ptr, nl, side, 9, m, 3, dptr(z), iptr(ids)))
+    z2 = z.reshape(nz, 2).T
+    zf, idf, zn = sf.associate(z2, R, 4.0, 25.0)
+    # (a synthetic "new" observation may fall inside an existing landmark's gate at this density: the single filter
+    # on the same state is the judge of the association, not the generator's intent)
+    zf_a, idf_a, zn_a = h.associate(z2, R, 4.0, 25.0)
+    assert np.array_equal(idf, idf_a) and np.array_equal(zf, zf_a) and np.array_equal(zn, zn_a)
+    assert set(ids) <= set(idf) and len(idf) >= m
+    assert sf.guard_changed() == 0, "sharded associate wrote outside the live state"
+    for _ in range(2):
+        sf.predict(0.03, 7.7, 4.0, Q, 0.025)
+        h.predict(0.03, 7.7, 4.0, Q, 0.025)
+        sf.update(zf, R, idf)
+        h.update(zf, R, idf)
+    changed = sf.guard_changed()
+    assert changed == 0, f"sharded predict / update (rank {2 * len(idf)}) overwrote {changed} padding slots"
+    knew = min(spare // 2, zn.shape[1])
+    if knew:
+        sf.add_features(zn[:, :knew], R)
+        h.add_features(zn[:, :knew], R)
+        assert sf.n == n + 2 * knew
+        assert sf.guard_changed() == 0, "sharded add_features wrote beyond the rows and columns it adds"
+        sf.update(zf, R, idf)
+        h.update(zf, R, idf)
+        assert sf.guard_changed() == 0
+    x1, P1 = h.get_state()
+    blk, _ = sf.cov_block(0, sf.n, 0, sf.n)
+    # only the upper triangle is authoritative (include/slamcuda.h): the rows add_features appended keep the NaN paint
+    # below the diagonal, so a kernel that read below the diagonal in the update above would show up here
+    assert np.isfinite(np.triu(blk)).all() and np.isfinite(sf.get_x()).all()
+    assert rel_err(sf.get_x(), x1) < 1e-12 and rel_err(np.triu(blk), np.triu(P1)) < 1e-12
+    sf.close()
+    h.close()
+
+
+def test_sharded_padding_guard_detects_a_write():
+    """Positive control for slam_shard_debug_guard: after arming at n0, a smaller synthetic state (n1) leaves the band
+    that used to be live outside the new live state.  Its upper triangle was written by the first synth_state (never
+    painted), so at least those slots + x[n1, n0) must be counted, and at most the whole band; re-arming clears it."""
+    from slamcuda.shard import ShardedFilter
+    nl0, nl1 = 400, 390
+    n0, n1 = 3 + 2 * nl0, 3 + 2 * nl1
+    sf = ShardedFilter(0, 0, 1, n0 + 11)
+    sf.synth_state(nl0, math.sqrt(nl0 / 0.0035), 4)
+    sf.guard_arm()
+    assert sf.guard_changed() == 0
+    sf.synth_state(nl1, math.sqrt(nl1 / 0.0035), 4)
+    assert sf.n == n1
+    lo = (n0 * (n0 + 1) - n1 * (n1 + 1)) // 2 + (n0 - n1)
+    hi = n0 * n0 - n1 * n1 + (n0 - n1)
+    changed = sf.guard_changed()
+    assert lo <= changed <= hi, (lo, changed, hi)
+    sf.guard_arm()
+    assert sf.guard_changed() == 0
+    sf.close()
