@@ -99,6 +99,21 @@ int slam_get_cov_block(slam_t *h, int i0, int ni, int j0, int nj, double *out, i
  * add_features moves n and owns the rows and columns it adds.  Used by the tests in place of a memory checker. */
 int slam_debug_guard(slam_t *h, int arm, long long *changed);
 
+/* slam_get_cov_block without any allocation.  This entry point has no counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments, checks and result as slam_get_cov_block: `out` receives
+ * cov[i0:i0+ni, j0:j0+nj] (0-based, full symmetric view, column-major, leading dimension ldo >= ni).
+ *  - The gather kernel's scratch is a static device array of SLAM_COV_BLOCK_STATIC_MAX doubles (512 KiB) that every
+ *    GPU loading the library holds until the process exits; the call issues no cudaMalloc / cudaFree and calls no
+ *    allocating library routine.
+ *  - ni * nj > SLAM_COV_BLOCK_STATIC_MAX is rejected with SLAM_ERR_CAPACITY and a message naming the limit (`out` is
+ *    not written): read a larger window in pieces, or use slam_get_cov_block.
+ *  - The array is shared by EVERY call on the device, whatever the handle, and keeps the last call's contents.  The
+ *    kernel writes the whole window before it is read back, so nothing needs clearing; but calls that overlap on
+ *    the GPU (two handles, two host threads) race on it -- serialise them. */
+#define SLAM_COV_BLOCK_STATIC_MAX 65536
+int slam_get_cov_block_static(slam_t *h, int i0, int ni, int j0, int nj, double *out, int ldo);
+
 /* compute_landmark_ellipses -- src/common.jl:236-262 (with ellipse, :236-244), computed on the
  * device from the 2x2 diagonal blocks only: out is (2*Nf) x (nsegs+1) column-major with leading
  * dimension ldo >= 2*Nf; rows 2i-1:2i hold nsigma*sqrtm(P_ii)*[cos(phi)'; sin(phi)'] .+ x_i for

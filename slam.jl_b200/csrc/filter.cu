@@ -6,6 +6,7 @@
 #include <stdarg.h>
 
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -394,6 +395,68 @@ extern "C" int slam_get_cov_block(slam_t *h, int i0, int ni, int j0, int nj, dou
     h->launches++;
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaMemcpy2DAsync(out, sizeof(double) * (size_t)ldo, h->d_block, sizeof(double) * ni,
+                               sizeof(double) * ni, nj, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    return SLAM_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// slam_get_cov_block_static -- slam_get_cov_block for callers that must not allocate (code under CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The gather kernel is k_cov_block, unchanged; its scratch is the file-scope array below
+// instead of the handle's cudaMalloc'ed d_block.
+//   * SLAM_COV_BLOCK_STATIC_MAX doubles = 512 KiB, held by every GPU that loads the library until the process exits.
+//   * In HOST code the array's name is a host-side stand-in, not a device address: the address comes from
+//     cudaGetSymbolAddress, once per device with that device current (cov_block_static_scratch), and only that
+//     pointer is ever handed to a kernel.
+//   * Every call on a device shares the array, whatever the handle, and the array keeps the last call's contents.
+//     k_cov_block writes all ni * nj elements of the window before the copy reads them, so nothing has to start at
+//     zero and nothing is cleared.  Calls that overlap on the GPU (two handles' streams, two host threads) race on it.
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_cov_block_static[SLAM_COV_BLOCK_STATIC_MAX];
+
+constexpr int COV_STATIC_MAX_DEVICES = 64;
+
+// the device address of g_cov_block_static on `device`, which must be the current device
+static int cov_block_static_scratch(int device, double **ptr) {
+    static std::mutex mu;
+    static double *addr[COV_STATIC_MAX_DEVICES] = {nullptr};
+    ARG_CHECK(device >= 0 && device < COV_STATIC_MAX_DEVICES, "device ordinal outside 0..63");
+    std::lock_guard<std::mutex> lock(mu);
+    if (addr[device] == nullptr) {
+        double *p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress((void **)&p, g_cov_block_static));
+        if (p == nullptr) {
+            slam_set_error("slam_get_cov_block_static: cudaGetSymbolAddress gave a NULL address on device %d", device);
+            return SLAM_ERR_CUDA;
+        }
+        addr[device] = p;
+    }
+    *ptr = addr[device];
+    return SLAM_OK;
+}
+
+extern "C" int slam_get_cov_block_static(slam_t *h, int i0, int ni, int j0, int nj, double *out, int ldo) {
+    H_CHECK(h);                                                  // makes h->device current
+    ARG_CHECK(out != nullptr, "NULL out");
+    ARG_CHECK(i0 >= 0 && j0 >= 0 && ni >= 0 && nj >= 0 && i0 + ni <= h->n && j0 + nj <= h->n,
+              "block outside the state");
+    ARG_CHECK(ldo >= ni, "ldo < ni");
+    if ((long long)ni * nj > (long long)SLAM_COV_BLOCK_STATIC_MAX) {
+        slam_set_error("slam_get_cov_block_static: a %d x %d window is %lld elements, more than the static scratch of "
+                       "SLAM_COV_BLOCK_STATIC_MAX = %d; read it in pieces or use slam_get_cov_block",
+                       ni, nj, (long long)ni * nj, SLAM_COV_BLOCK_STATIC_MAX);
+        return SLAM_ERR_CAPACITY;
+    }
+    if (ni == 0 || nj == 0) return SLAM_OK;
+    double *scratch = nullptr;
+    int rc = cov_block_static_scratch(h->device, &scratch);
+    if (rc) return rc;
+    dim3 grid(nj, (ni + 127) / 128);
+    k_cov_block<<<grid, 128, 0, h->stream>>>(h->d_P, h->ld, i0, ni, j0, nj, scratch);
+    h->launches++;
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpy2DAsync(out, sizeof(double) * (size_t)ldo, scratch, sizeof(double) * ni,
                                sizeof(double) * ni, nj, cudaMemcpyDeviceToHost, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
     return SLAM_OK;

@@ -77,6 +77,8 @@ _sig("slam_get_state", I, vp, c_double_p, c_double_p, I)
 _sig("slam_get_pose", I, vp, c_double_p)
 _sig("slam_n", I, vp)
 _sig("slam_get_cov_block", I, vp, I, I, I, I, c_double_p, I)
+_sig("slam_get_cov_block_static", I, vp, I, I, I, I, c_double_p, I)
+COV_BLOCK_STATIC_MAX = 65536    # SLAM_COV_BLOCK_STATIC_MAX of include/slamcuda.h
 _sig("slam_downdate_kernel", I, vp)
 _sig("slam_shard_downdate_kernel", I, vp)
 _sig("slam_shard_debug_guard", I, vp, I, C.POINTER(C.c_longlong))
