@@ -772,6 +772,96 @@ constexpr int K4_THREADS = 256;
 
 // sS: R x R column-major (leading dimension R) holding S; sC: R x R; sv: R; sd: 2R scratch.  Returns false (all
 // threads alike) when S is not positive definite.  Ends with a barrier; C and u are written to global memory.
+// nt is a multiple of 32 and at least 32 (both callers launch 256 threads); R <= 32.
+//
+// Warp-synchronous form (r2): the block-wide right-looking loop spent two __syncthreads, an integer division and
+// stride-R (16- to 32-way bank-conflicted) accesses per step, and the inverse was one thread per row walking
+// R^2/2 dependent shared-memory round trips: +8.6 / +19.7 / +36.5 us per update at R = 16 / 24 / 32
+// (tools/k4_probe.py).  Now
+//   * Cholesky: warp 0 alone, row by row (the twin's left-looking order: U[i][j] = (S[i][j] - sum_{k<i}
+//     U[k][i] U[k][j]) / U[i][i], k ascending -- per entry the same multiply / subtract sequence as the right-looking
+//     loop; this file is built with -fmad=false, so no explicit fma() here: it would round differently), lane j
+//     owns column j.  U[i][j] overwrites S at sS[j + i*R], the transposed position (S is symmetric there), so every
+//     lane access is contiguous; one __syncwarp per row, no block barrier;
+//   * C = inv(U): one WARP per row i, lane j accumulates C[i][j].  As soon as C[i][jj] is final it is broadcast by
+//     shuffle and every lane j > jj adds U[jj][j] C[i][jj] -- jj ascending per entry, dtrti2's order exactly -- so a
+//     row costs R - i dependent steps instead of (R - i)^2 / 2, and the rows run side by side on the warps.
+// Measured on one box against the -DK4_LEGACY build (which keeps the block-wide body for exactly that), per update:
+// 8.4 -> 7.0 us at R = 16, 19.9 -> 17.5 at R = 24, 37.6 -> 31.4 at R = 32 on a tiny map; 26.9 -> 25.6 us (m = 8) and
+// 58.5 -> 52.8 us (m = 16) of exposed small-kernel time at n = 20003 -- a modest gain: most of the rank-dependent
+// latency of an update is outside this function.  Same bits as the legacy body (digests of x and P after updates at
+// R = 2..32, tools/k4_hash.py) and as the twin (test_update_P_bitwise_vs_twin).
+#ifndef K4_LEGACY
+__device__ __forceinline__ bool k4_factor(double *sS, double *sC, const double *sv, double *sd, int R, int tid, int nt,
+                                          double *__restrict__ C, double *__restrict__ u) {
+    constexpr unsigned FULL = 0xffffffffu;
+    for (int idx = tid; idx < R * R; idx += nt) {                  // S = (S + S')*0.5
+        const int a = idx % R, b = idx / R;
+        if (a < b) {
+            const double s2 = (sS[a + b * R] + sS[b + a * R]) * 0.5;
+            sS[a + b * R] = s2;
+            sS[b + a * R] = s2;
+        } else if (a == b) {
+            sS[a + a * R] = (sS[a + a * R] + sS[a + a * R]) * 0.5;
+        }
+    }
+    __syncthreads();
+    double *cd = sd + R;                                           // cd[j] = 1 / U[j][j]; sd[0] = "positive definite"
+    const int lane = tid & 31, warp = tid >> 5, nw = nt >> 5;
+    if (warp == 0) {
+        const int j = lane;
+        bool ok = true;
+        for (int i = 0; i < R; i++) {
+            double s = 0.0;
+            if (j >= i && j < R) {
+                s = sS[j + i * R];                                 // S[i][j] (= S[j][i])
+#pragma unroll 4
+                for (int k = 0; k < i; k++) s -= sS[i + k * R] * sS[j + k * R];   // U[k][i] (broadcast), U[k][j]; product
+                                                                                  // and difference round separately (-fmad=false)
+            }
+            const double d = __shfl_sync(FULL, s, i);              // the pivot, from lane i
+            if (!(d > 0)) {                                        // uniform across the warp
+                ok = false;
+                break;
+            }
+            const double ukk = sqrt(d);                            // every lane takes the root itself
+            if (j == i) {
+                sS[i + i * R] = ukk;
+                cd[i] = 1.0 / ukk;
+            } else if (j > i && j < R) {
+                sS[j + i * R] = s / ukk;                           // U[i][j]
+            }
+            __syncwarp();
+        }
+        if (lane == 0) sd[0] = ok ? 1.0 : 0.0;
+    }
+    __syncthreads();
+    if (sd[0] == 0.0) return false;
+    for (int i = warp; i < R; i += nw) {                           // C = inv(U), row i on this warp
+        const int j = lane;
+        const double cii = cd[i];
+        const double ncdj = j < R ? -cd[j] : 0.0;
+        double y = (j > i && j < R) ? sS[j + i * R] * cii : 0.0;   // U[i][j] C[i][i]
+        if (j < i) sC[i + j * R] = 0.0;                            // below the diagonal
+        if (j == i) sC[i + i * R] = cii;
+        for (int jj = i + 1; jj < R; jj++) {
+            const double c = __shfl_sync(FULL, y * ncdj, jj);      // C[i][jj], final in lane jj
+            if (j == jj) sC[i + jj * R] = c;
+            if (j > jj && j < R) y += sS[j + jj * R] * c;          // + U[jj][j] C[i][jj] (separate multiply and add)
+        }
+    }
+    __syncthreads();
+    if (tid < R) {
+        const int j = tid;
+        double a = 0;
+        for (int l = 0; l < j; l++) a += sC[l + j * R] * sv[l];
+        a += cd[j] * sv[j];
+        u[j] = a;
+    }
+    for (int idx = tid; idx < R * R; idx += nt) C[idx] = sC[idx];
+    return true;
+}
+#else
 __device__ __forceinline__ bool k4_factor(double *sS, double *sC, const double *sv, double *sd, int R, int tid, int nt,
                                           double *__restrict__ C, double *__restrict__ u) {
     for (int idx = tid; idx < R * R; idx += nt) {                  // S = (S + S')*0.5
@@ -829,6 +919,7 @@ __device__ __forceinline__ bool k4_factor(double *sS, double *sC, const double *
     for (int idx = tid; idx < R * R; idx += nt) C[idx] = sC[idx];
     return true;
 }
+#endif
 
 __device__ __forceinline__ void k4_noop(int R, int tid, int nt, double *__restrict__ C, double *__restrict__ u) {
     for (int idx = tid; idx < R * R; idx += nt) C[idx] = 0.0;     // C = 0: W1 = 0, x += 0, P -= 0
