@@ -168,7 +168,12 @@ int slam_predict_observation(slam_t *h, int64_t idf, double zp[2], double *H);
 
 /* update -- src/ekf.jl:46-77: batch Cholesky-form update with all m associated
  * observations.  m == 0 is a no-op (first observation step of every run).  Duplicate ids
- * in idf are legal.  In place on the device state. */
+ * in idf are legal.  In place on the device state.
+ * Completion: the call returns once the step's result is final -- the status (not-PD / bad id, decided by the
+ * innovation Cholesky) and x, which slam_get_pose then serves without another wait -- while the downdate of P may
+ * still be running on the handle's stream.  Every later call on the handle, and every read-out (slam_get_state,
+ * slam_get_cov_block, ...), is ordered behind it, and slam_sync waits for everything; SLAM_UPDATE_EARLY=0 in the
+ * environment makes the call itself wait for the downdate as well. */
 int slam_update(slam_t *h, const double *zf, int m, const double R[4], const int64_t *idf);
 
 /* add_features -- src/ekf.jl:84-122: append k new landmarks in place (n += 2k). */

@@ -87,6 +87,12 @@ struct slam_filter {
     size_t block_cap = 0;
     int variant = 0;
     int last_k6 = 0;               // downdate kernel of the last update: 1 FMA, 2 tiled DMMA, 3 streaming DMMA
+    // host-buffer slam_update returns when the step's RESULT is final (status after K3 + K4, x after K5), not when the
+    // downdate is: ev_x is recorded behind K5 and read back on copy_stream, so the next call's copy and launches queue
+    // up behind a K6 that is still running.  ev_stage: the pinned staging buffer's last H2D.  SLAM_UPDATE_EARLY=0 disables.
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_x = nullptr, ev_stage = nullptr;
+    bool early_return = true;
     long long launches = 0;
     // x[0:3] as read back with the last host-path update's status (one synchronisation for both): sim! reads
     // state.x[1:3] right after every call (sim/ekfslam-sim.jl:128); valid until the next call that changes the state
@@ -149,6 +155,10 @@ extern "C" int slam_create(int device, int n_max, slam_t **out) {
         }                                                                                        \
     } while (0)
     CREATE_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CREATE_TRY(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    CREATE_TRY(cudaEventCreateWithFlags(&h->ev_x, cudaEventDisableTiming));
+    CREATE_TRY(cudaEventCreateWithFlags(&h->ev_stage, cudaEventDisableTiming));
+    if (const char *e = getenv("SLAM_UPDATE_EARLY")) h->early_return = atoi(e) != 0;
     CREATE_TRY(cudaMalloc(&h->d_x, sizeof(double) * h->ld));
     CREATE_TRY(cudaMalloc(&h->d_P, sizeof(double) * h->ld * (size_t)n_max));
     CREATE_TRY(cudaMalloc(&h->d_pose, sizeof(double) * 8));
@@ -187,6 +197,9 @@ extern "C" int slam_destroy(slam_t *h) {
     cudaFree(h->d_u); cudaFree(h->d_v); cudaFree(h->d_Hn); cudaFree(h->d_fp);
     cudaFree(h->d_block);
     if (h->h_pin) cudaFreeHost(h->h_pin);
+    if (h->ev_x) cudaEventDestroy(h->ev_x);
+    if (h->ev_stage) cudaEventDestroy(h->ev_stage);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     for (auto &e : h->ev) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     cudaGetLastError();
@@ -270,6 +283,31 @@ static int check_latched(slam_t *h) {
     CUDA_TRY(cudaStreamSynchronize(h->stream));
     h->pose_cache[0] = hp[0]; h->pose_cache[1] = hp[1]; h->pose_cache[2] = hp[2];
     h->pose_valid = true;      // everything issued so far is complete: the pose is current
+    int e = *he;
+    if (e != 0) {
+        CUDA_TRY(cudaMemsetAsync(h->d_err, 0, sizeof(int), h->stream));
+        slam_set_error(e == SLAM_ERR_NOT_PD      ? "innovation covariance not positive definite"
+                       : e == SLAM_ERR_BAD_INDEX ? "landmark id out of range"
+                                                 : "device-side error %d",
+                       e);
+        return e;
+    }
+    return SLAM_OK;
+}
+
+// check_latched for the host-buffer update: waits for ev_x (behind K5) instead of the whole stream.  The status was
+// decided by K3 + K4 and x by K5; K6 neither fails nor touches x, and every later call is ordered behind it on the
+// handle's stream, so nothing the caller can observe differs from a full synchronisation -- except that it returns
+// while the downdate runs.  slam_sync() and every read-out still wait for everything.
+static int check_after_x(slam_t *h) {
+    int *he = (int *)h->h_pin;
+    double *hp = (double *)h->h_pin + 8;
+    CUDA_TRY(cudaStreamWaitEvent(h->copy_stream, h->ev_x, 0));
+    CUDA_TRY(cudaMemcpyAsync(he, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, h->copy_stream));
+    CUDA_TRY(cudaMemcpyAsync(hp, h->d_x, sizeof(double) * 3, cudaMemcpyDeviceToHost, h->copy_stream));
+    CUDA_TRY(cudaStreamSynchronize(h->copy_stream));
+    h->pose_cache[0] = hp[0]; h->pose_cache[1] = hp[1]; h->pose_cache[2] = hp[2];
+    h->pose_valid = true;      // x is final behind K5 and nothing queued behind it changes x
     int e = *he;
     if (e != 0) {
         CUDA_TRY(cudaMemsetAsync(h->d_err, 0, sizeof(int), h->stream));
@@ -1398,7 +1436,8 @@ static cudaError_t launch_gain_reg(int blocks, cudaStream_t s, const double *PHt
     return launch_pdl(k_gain_reg<RC>, dim3(blocks), dim3(K5_THREADS), 0, s, PHt, npad, n, R, C, u, W1c, x, pose);
 }
 
-static int update_device(slam_t *h, const double *d_zf, int m, const double R[4], const int64_t *d_idf) {
+static int update_device(slam_t *h, const double *d_zf, int m, const double R[4], const int64_t *d_idf,
+                         bool mark_x = false) {
     if (m == 0) return SLAM_OK;   // first observation step of every run (sim/ekfslam-sim.jl:114-117)
     if (m > SLAM_MAX_OBS) {
         slam_set_error("slam_update: m = %d exceeds SLAM_MAX_OBS = %d", m, SLAM_MAX_OBS);
@@ -1448,6 +1487,7 @@ static int update_device(slam_t *h, const double *d_zf, int m, const double R[4]
         h->launches += 4;
     }
     CUDA_TRY(cudaGetLastError());
+    if (mark_x) CUDA_TRY(cudaEventRecord(h->ev_x, h->stream));   // status and x are final here; only P is still to come
     const bool timed = h->profiling && h->ev_used + 2 <= (int)h->ev.size();
     if (timed) CUDA_TRY(cudaEventRecord(h->ev[h->ev_used], h->stream));
     h->last_k6 = downdate_kernel_choice(Rk, h->variant, h->ld);
@@ -1515,13 +1555,17 @@ extern "C" int slam_update(slam_t *h, const double *zf, int m, const double R[4]
         }
     double *hz = (double *)((char *)h->h_pin + 256);
     int64_t *hid = (int64_t *)(hz + 2 * m);       // packed behind zf: one H2D
-    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    // the staging buffer is free once its last H2D is done; d_upd is only read by kernels ordered before this copy
+    if (h->early_return) CUDA_TRY(cudaEventSynchronize(h->ev_stage));
+    else CUDA_TRY(cudaStreamSynchronize(h->stream));
     memcpy(hz, zf, sizeof(double) * 2 * m);
     memcpy(hid, idf, sizeof(int64_t) * m);
     CUDA_TRY(cudaMemcpyAsync(h->d_upd, hz, 24 * (size_t)m, cudaMemcpyHostToDevice, h->stream));
-    int rc = update_device(h, (const double *)h->d_upd, m, R, (const int64_t *)(h->d_upd + 16 * (size_t)m));
+    CUDA_TRY(cudaEventRecord(h->ev_stage, h->stream));
+    int rc = update_device(h, (const double *)h->d_upd, m, R, (const int64_t *)(h->d_upd + 16 * (size_t)m),
+                           h->early_return);
     if (rc) return rc;
-    return check_latched(h);
+    return h->early_return ? check_after_x(h) : check_latched(h);
 }
 
 // ---------------------------------------------------------------------------------------
