@@ -951,3 +951,64 @@ def test_update_P_bitwise_vs_twin(sc, twin, nf, m):
         assert ndiff == 0
         assert rel_err(xg, xt) < 1e-12
     h.close()
+
+
+def test_update_early_return_is_unobservable(sc, monkeypatch):
+    """Host-buffer slam_update returns once the status and x are final, while the downdate of P is still running
+    (n = 10003: K6 is ~0.13 ms, the call returns ~30 us after its launches).  Nothing a caller can observe may differ
+    from waiting for everything: a handle created with SLAM_UPDATE_EARLY=0 (full wait) and a default one go through the
+    same calls -- back-to-back updates with different observations (the pinned staging buffer and d_upd are reused while
+    the previous K6 runs), the pose, a block read-out, predict, add_features, the not-PD path -- and every result is
+    bit-equal."""
+    from slamcuda._ffi import lib, check, dptr, iptr
+    from slamcuda.slam import _Handle
+    k = ref.sim_constants()
+    R, Q = k["R"], k["Q"]
+    nl, m = 5000, 8
+    side = math.sqrt(nl / 0.0035)
+
+    def drive(early):
+        if early:
+            monkeypatch.delenv("SLAM_UPDATE_EARLY", raising=False)
+        else:
+            monkeypatch.setenv("SLAM_UPDATE_EARLY", "0")
+        h = _Handle(0, 3 + 2 * nl + 8, grow=False)               # the switch is read when the handle is created
+        monkeypatch.delenv("SLAM_UPDATE_EARLY", raising=False)
+        check(lib.slam_synth_state(h.ptr, nl, side, 3))
+        obs = []
+        for seed in (3, 4, 5):
+            z = np.zeros(2 * (m + 2))
+            ids = np.zeros(m, dtype=np.int64)
+            check(lib.slam_synth_observations(h.ptr, nl, side, seed, m, 2, dptr(z), iptr(ids)))
+            obs.append((z.reshape(m + 2, 2).T[:, :m].copy(), ids.copy(), z.reshape(m + 2, 2).T[:, m:].copy()))
+        out = []
+        for rnd in range(2):
+            for zf, ids, _ in obs:                              # three updates with no read-out in between
+                h.update(zf, R, ids)
+                out.append(h.get_pose())
+            out.append(h.cov_block(0, 40, 3 + 2 * (int(obs[0][1][0]) - 1), 2))   # ordered behind the running K6
+            h.predict(0.01, 6.0, 4.0, Q, 0.025)
+            out.append(h.get_pose())
+        h.add_features(obs[0][2], R)
+        h.update(obs[1][0], R, obs[1][1])
+        x, P = h.get_state()
+        out += [x, P]
+        h.close()
+        return out
+
+    a, b = drive(True), drive(False)
+    assert len(a) == len(b)
+    for i, (u, v) in enumerate(zip(a, b)):
+        assert np.array_equal(u, v), f"result {i} differs between early return and full wait"
+    assert np.isfinite(a[-1]).all()
+    # the error path through the early check: S not positive definite is reported by the call itself, state untouched
+    x0 = np.array([0.0, 0.0, 0.0, 10.0, 5.0])
+    P0 = -np.eye(5)
+    h = _Handle(0, 5)
+    h.set_state(x0, P0)
+    with pytest.raises(sc.NotPositiveDefinite):
+        h.update(np.array([[11.0], [0.4]]), R, np.array([1]))
+    xe, Pe = h.get_state()
+    assert np.array_equal(xe, x0) and np.array_equal(Pe, P0)
+    h.update(np.zeros((2, 0)), R, np.zeros(0, dtype=np.int64))  # and the handle is usable afterwards
+    h.close()
