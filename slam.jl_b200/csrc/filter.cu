@@ -1298,8 +1298,17 @@ k_pht_chol(const double *__restrict__ x, const double *__restrict__ P, size_t ld
     __shared__ double sPH[K34_RMAX][K34_RMAX + 3];     // chol CTA: PHt[k][s] at the rows cs[s] named by H
     __shared__ double sS[K34_RMAX * K34_RMAX], sC[K34_RMAX * K34_RMAX], sv[K34_RMAX], sd[2 * K34_RMAX];
     __shared__ int s_fail;
+#ifdef NO_PDL_PREFETCH
     pdl_wait();
     pdl_launch_dependents();
+#endif
+    // Before the wait: x, the ids and the observation model.  Launched behind a K6 that is still running, the only
+    // thing this kernel must wait for is P; x was finalised by the previous update's K5 (complete before that K6
+    // passed its own wait), the status word by its K3 + K4, and any other predecessor (predict, add_features, the
+    // gate, a copy) serialises fully.  The dependent global round trips x -> id -> x[f] and the sqrt / atan2 of the
+    // model so overlap K6's tail: -1.5 us per update on a tiny map (13.4 -> 11.9), -2.0 us at n = 20003 (531.7 -> 529.7,
+    // same box against -DNO_PDL_PREFETCH, profiles/r2_k4_warp.md), same bits.  (Moving the downdate's first P loads ahead
+    // of ITS wait was tried too and reverted: it put every CTA's P loads in front of its W1 copy, K6 +2..15 us.)
     const bool chol = blockIdx.x == gridDim.x - 1;
     const int tid = threadIdx.x;
     const int Nf = (n - 3) / 2;
@@ -1330,6 +1339,10 @@ k_pht_chol(const double *__restrict__ x, const double *__restrict__ P, size_t ld
         }
     }
     __syncthreads();
+#ifndef NO_PDL_PREFETCH
+    pdl_wait();                          // P (the previous update's downdate) is complete
+    pdl_launch_dependents();
+#endif
     if (!chol) {
         const int i = blockIdx.x * K3_THREADS + tid;
         if (i >= n) return;
