@@ -140,6 +140,8 @@ def test_sharded_two_ranks_match_single_filter(p2p):
     assert out.returncode == 0, tail
     assert "SHARD_CHECK PASS" in out.stdout, tail
     assert f"p2p={'True' if p2p == '1' else 'False'}" in out.stdout, tail
+    # the padding guard of each rank's panel stack (slam_shard_debug_guard) ran and counted nothing
+    assert out.stdout.count("padding_slots_overwritten=0") == 2, tail
 
 
 @pytest.mark.parametrize("nl,m,spare", [(300, 5, 7), (700, 8, 40), (700, 20, 1), (1500, 36, 130)])

@@ -28,6 +28,8 @@ knew = 40
 ncap = n + 2 * knew
 sf = ShardedFilter(lr, rank, world, ncap)
 sf.synth_state(nl, side, 7)
+sf.guard_arm()              # padding guard of this rank's panel stack and x (slam_shard_debug_guard)
+guard = [sf.guard_changed()]
 h = _Handle(lr, ncap)
 check(lib.slam_synth_state(h.ptr, nl, side, 7))
 nz = m + knew
@@ -43,6 +45,7 @@ for _ in range(2):
     sf.predict(0.03, 7.7, 4.0, Q, 0.025)
     h.update(zf_a, R, idf_a)
     sf.update(zf_a, R, idf_a)
+guard.append(sf.guard_changed())     # after associate + 2 x (predict, update), 2 * knew states of padding still spare
 zn_all = z2[:, m:].copy()
 h.add_features(zn_all, R)
 sf.add_features(zn_all, R)
@@ -68,6 +71,7 @@ zq2 = np.concatenate([zq2, np.array([[3 * side, 0.3], [2.5 * side, -1.0]]).T], a
 a2 = h.associate(zq2, R, 4.0, 25.0)
 b2 = sf.associate(zq2, R, 4.0, 25.0)
 ok = ok and all(np.array_equal(p, q) for p, q in zip(a2, b2)) and len(a2[1]) >= 3 and a2[2].shape[1] == 2
+guard.append(sf.guard_changed())     # after add_features, the rank-80 update (arena re-shared) and the second associate
 n = sf.n
 x1, P1 = h.get_state()
 ex = float(np.max(np.abs(sf.get_x() - x1)) / np.max(np.abs(x1)))
@@ -81,11 +85,11 @@ for lo, hi in shard_plan(n, world, rank):
         mask = np.arange(n)[None, :] >= np.arange(lo, hi)[:, None]
         eP = max(eP, float(np.max(np.abs(blk - ref)[mask]) / np.max(np.abs(P1))))
 res = [None] * world
-dist.all_gather_object(res, (rank, ok, ex, eP, cnt_total, len(shard_plan(n, world, rank))))
+dist.all_gather_object(res, (rank, ok, ex, eP, cnt_total, len(shard_plan(n, world, rank)), sum(guard)))
 if rank == 0:
     for r in res:
-        print("rank %d assoc_ok=%s x_rel=%.2e P_rel=%.2e rows*cols=%d panels=%d" % r)
-    good = all(r[1] and r[2] < 1e-12 and r[3] < 1e-12 for r in res)
+        print("rank %d assoc_ok=%s x_rel=%.2e P_rel=%.2e rows*cols=%d panels=%d padding_slots_overwritten=%d" % r)
+    good = all(r[1] and r[2] < 1e-12 and r[3] < 1e-12 and r[6] == 0 for r in res)
     print("SHARD_CHECK", "PASS" if good else "FAIL", f"world={world} n={n} m={m} p2p={sf.p2p}")
 sf.close()
 h.close()
