@@ -924,7 +924,10 @@ def test_update_P_bitwise_vs_twin(sc, twin, nf, m):
     ascending, the downdate one k-ascending fma chain per element.  H is built from IEEE sqrt and divisions only, and P
     depends on the observation through H alone, so P must come out BIT-EQUAL to the twin's at every rank K4 handles
     (R = 2..32; FMA and streaming-DMMA downdate kernels).  x also takes atan2, which CUDA's libm and glibc round
-    differently, so x is held to 1e-12.  (An explicit fma() in K4 passes every tolerance test and fails this one.)"""
+    differently, so x is held to 1e-12.  (An explicit fma() in K4 passes every tolerance test and fails this one.)
+    Scope: R <= 32 only.  Above that the update takes k_innov_chol_wide, the tiled gain and (past 64 ranks) the chunked
+    downdate, whose sums run in another order: measured against the twin at R = 34..128, nearly every element of P
+    differs in the last place (max-norm relative 4e-16 .. 5e-15), which test_update_rank_sweep_dmma holds to 1e-9."""
     from twin_ffi import Twin
     from slamcuda.slam import _Handle
     R = ref.sim_constants()["R"]
