@@ -667,7 +667,8 @@ def cpu_ensemble_baseline(n_runs: int = 2048, extra: int = 200):
 
 
 def gpu_update_sharded(n_landmarks: int, m: int, steps: int, warmup: int, e2e_steps: int, rank: int, world: int,
-                       device: int, parity: bool = False, sustained_s: float = 0.0, force_nccl: bool = False):
+                       device: int, parity: bool = False, sustained_s: float = 0.0, force_nccl: bool = False,
+                       sweep_m=()):
     """One filter, P row-block-sharded over `world` ranks (one process per GPU)."""
     import torch
     import torch.distributed as dist
@@ -737,7 +738,7 @@ def gpu_update_sharded(n_landmarks: int, m: int, steps: int, warmup: int, e2e_st
         d_idf = torch.tensor(idf, device=f"cuda:{device}")
         torch.cuda.synchronize(device)
 
-        def timed(nsteps, nwarm):
+        def timed(nsteps, nwarm, d_zf=d_zf, d_idf=d_idf, m=m):
             for _ in range(nwarm):
                 check(lib.slam_shard_update_resident(sf.ptr, d_zf.data_ptr(), m, dptr(R_OBS), d_idf.data_ptr()))
             check(lib.slam_shard_sync(sf.ptr))
@@ -777,6 +778,20 @@ def gpu_update_sharded(n_landmarks: int, m: int, steps: int, warmup: int, e2e_st
             ph2, _ = timed(ns, 0)
             out["sustained"] = {"steps": ns, "seconds": float(ph2[:, 4].max()) * ns / 1e3,
                                 "ms_per_step": float(ph2[:, 4].max()), "k6_ms": float(ph2[:, 3].max())}
+        # other ranks of the update on the same sharded map (m in {1, 4, 16, 64}): whole step and
+        # K6, max over ranks like the headline
+        sweep = {}
+        for ms_ in sweep_m:
+            zs = np.zeros(2 * ms_)
+            ids_s = np.zeros(ms_, dtype=np.int64)
+            check(lib.slam_synth_observations(None, n_landmarks, side, SEED, ms_, 0, dptr(zs), iptr(ids_s)))
+            dz, di = torch.tensor(zs, device=f"cuda:{device}"), torch.tensor(ids_s, device=f"cuda:{device}")
+            torch.cuda.synchronize(device)
+            phs, _ = timed(max(10, min(steps, 20)), 3, dz, di, ms_)
+            sweep[str(ms_)] = {"ms_per_step": float(phs[:, 4].max()), "k6_ms": float(phs[:, 3].max()),
+                               "k6_kernel": K6_KERNELS.get(int(lib.slam_shard_downdate_kernel(sf.ptr)), "unknown")}
+        if sweep:
+            out["sweep"] = sweep
         if e2e_steps > 0:
             # end to end: host zf / idf in, status + pose out, every step
             pose = np.zeros(3)
@@ -954,12 +969,19 @@ def main():
         sampler.start()
         r = gpu_update_sharded(nl, args.m, args.steps, args.warmup, e2e_steps=min(args.steps, 20),
                                rank=rank, world=world, device=local_rank, parity=not args.no_parity,
-                               sustained_s=args.sustained)
+                               sustained_s=args.sustained, sweep_m=() if args.no_extras else (1, 4, 16, 64))
         clocks = sampler.stop()
         ms = r["ms_per_step"]
         alg_bytes = 8.0 * n * (n + 1) / world
         if r.get("parity") is not None:
             parity_all["workload"] = r["parity"]
+        if r.get("sweep"):
+            # SURVEY.md 8d, config 5's other ranks on the sharded map: steps/s, K6 against the copy bandwidth (per-rank share
+            # of the triangle) and, above 32 ranks, against the DMMA rate measured in this run
+            extras["m_sweep_sharded"] = {
+                k: {**v, "value": 1e3 / v["ms_per_step"], **k6_block(alg_bytes, v["k6_ms"], peak),
+                    "k6_tflops_per_gpu": 2.0 * int(k) * n * (n + 1) / world / (v["k6_ms"] * 1e-3) / 1e12}
+                for k, v in r["sweep"].items()}
         if not args.no_extras:
             # strong scaling: the fixed N = 1 map (n = 70709, 40 GB) over the N ranks -- the exchange latency's share
             # shows where K6 shrinks to 1/N of a step
