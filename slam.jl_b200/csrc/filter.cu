@@ -808,6 +808,13 @@ k_pht(const double *__restrict__ x, const double *__restrict__ P, size_t ld, int
 constexpr int K4_RMAX = 32;
 constexpr int K4_THREADS = 256;
 
+#ifdef K4_TIMING   // developer build (SLAMCUDA_DEFS=-DK4_TIMING): cycles per phase of the CTA that runs K4, printed by its thread 0
+__device__ long long g_k4_mark[16];
+#define K4_MARK(k) do { if (threadIdx.x == 0) g_k4_mark[k] = clock64(); } while (0)
+#else
+#define K4_MARK(k)
+#endif
+
 // sS: R x R column-major (leading dimension R) holding S; sC: R x R; sv: R; sd: 2R scratch.  Returns false (all
 // threads alike) when S is not positive definite.  Ends with a barrier; C and u are written to global memory.
 // nt is a multiple of 32 and at least 32 (both callers launch 256 threads); R <= 32.
@@ -844,8 +851,58 @@ __device__ __forceinline__ bool k4_factor(double *sS, double *sC, const double *
         }
     }
     __syncthreads();
+    K4_MARK(4);   // symmetrised
     double *cd = sd + R;                                           // cd[j] = 1 / U[j][j]; sd[0] = "positive definite"
     const int lane = tid & 31, warp = tid >> 5, nw = nt >> 5;
+#ifdef K4_RIGHT_LOOKING   // measured, NOT adopted: off by default (profiles/r2_k4_warp.md)
+    if (warp == 0) {
+        // Right-looking, the running sums in shared memory: entry (i, j), i <= j, lives at sS[j + i*R] (the transposed
+        // position: S is symmetric there, lanes j are contiguous) and holds S[i][j] - sum_{k finished} U[k][i] U[k][j].
+        // When row k is final every remaining row takes its term at once; eight rows are loaded before any is stored,
+        // so the updates pipeline instead of forming one dependent chain per row (measured with the left-looking
+        // loop: ~700 cycles per row fixed plus ~55 per term of its sum, tools/k4_phases.py).  Per entry the terms
+        // still arrive k ascending, product and difference rounded separately: the same bits.  (The same scheme with
+        // the column in REGISTERS and everything unrolled was 3x slower: ~2000 instructions executed once each.)
+        // Result: the Cholesky phase itself -14 % at R = 16, -27 % at R = 32 in the -DK4_TIMING build, but whole updates
+        // on one box: +0.4 / +1.2 us on a tiny map (R = 16 / 32), no change at n = 20003 with events, -4..-12 us without
+        // (inside that loop's scatter).  Not a demonstrable gain, so the row-by-row loop below stays the default.
+        const int j = lane;
+        bool ok = true;
+        for (int k = 0; k < R; k++) {
+            const double d = sS[k + k * R];                        // the pivot: every lane reads it (broadcast)
+            if (!(d > 0)) {                                        // uniform across the warp
+                ok = false;
+                break;
+            }
+            const double ukk = sqrt(d);                            // every lane takes the root itself
+            const bool mine = j > k && j < R;
+            const double ukj = mine ? sS[j + k * R] / ukk : 0.0;   // U[k][j]
+            __syncwarp();                                          // the pivot has been read by all before lane k replaces it
+            if (j == k) {
+                sS[k + k * R] = ukk;
+                cd[k] = 1.0 / ukk;
+            } else if (mine) {
+                sS[j + k * R] = ukj;
+            }
+            __syncwarp();
+            for (int i0 = k + 1; i0 < R; i0 += 8) {                // rows i0 .. i0 + 7 of the trailing block
+                double uki[8], a[8];
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    const int ii = i0 + q;
+                    const bool on = ii < R && mine && ii <= j;
+                    uki[q] = ii < R ? sS[ii + k * R] : 0.0;        // U[k][ii], a broadcast read
+                    a[q] = on ? sS[j + ii * R] : 0.0;
+                }
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    const int ii = i0 + q;
+                    if (ii < R && mine && ii <= j) sS[j + ii * R] = a[q] - uki[q] * ukj;
+                }
+            }
+            __syncwarp();
+        }
+#else
     if (warp == 0) {
         const int j = lane;
         bool ok = true;
@@ -854,8 +911,7 @@ __device__ __forceinline__ bool k4_factor(double *sS, double *sC, const double *
             if (j >= i && j < R) {
                 s = sS[j + i * R];                                 // S[i][j] (= S[j][i])
 #pragma unroll 4
-                for (int k = 0; k < i; k++) s -= sS[i + k * R] * sS[j + k * R];   // U[k][i] (broadcast), U[k][j]; product
-                                                                                  // and difference round separately (-fmad=false)
+                for (int k = 0; k < i; k++) s -= sS[i + k * R] * sS[j + k * R];   // U[k][i] (broadcast), U[k][j]
             }
             const double d = __shfl_sync(FULL, s, i);              // the pivot, from lane i
             if (!(d > 0)) {                                        // uniform across the warp
@@ -871,9 +927,11 @@ __device__ __forceinline__ bool k4_factor(double *sS, double *sC, const double *
             }
             __syncwarp();
         }
+#endif
         if (lane == 0) sd[0] = ok ? 1.0 : 0.0;
     }
     __syncthreads();
+    K4_MARK(5);   // Cholesky done
     if (sd[0] == 0.0) return false;
     for (int i = warp; i < R; i += nw) {                           // C = inv(U), row i on this warp
         const int j = lane;
@@ -889,6 +947,7 @@ __device__ __forceinline__ bool k4_factor(double *sS, double *sC, const double *
         }
     }
     __syncthreads();
+    K4_MARK(6);   // inverse done
     if (tid < R) {
         const int j = tid;
         double a = 0;
@@ -897,6 +956,7 @@ __device__ __forceinline__ bool k4_factor(double *sS, double *sC, const double *
         u[j] = a;
     }
     for (int idx = tid; idx < R * R; idx += nt) C[idx] = sC[idx];
+    K4_MARK(7);   // u and C written
     return true;
 }
 #else
@@ -1310,6 +1370,9 @@ k_pht_chol(const double *__restrict__ x, const double *__restrict__ P, size_t ld
     // same box against -DNO_PDL_PREFETCH, profiles/r2_k4_warp.md), same bits.  (Moving the downdate's first P loads ahead
     // of ITS wait was tried too and reverted: it put every CTA's P loads in front of its W1 copy, K6 +2..15 us.)
     const bool chol = blockIdx.x == gridDim.x - 1;
+#ifdef K4_TIMING
+    if (chol) K4_MARK(0);   // entry
+#endif
     const int tid = threadIdx.x;
     const int Nf = (n - 3) / 2;
     const int R = 2 * m;
@@ -1339,9 +1402,38 @@ k_pht_chol(const double *__restrict__ x, const double *__restrict__ P, size_t ld
         }
     }
     __syncthreads();
+#if defined(GATHER_PREFETCH) && !defined(NO_PDL_PREFETCH)   // measured, NOT adopted: off by default (profiles/r2_k4_warp.md)
+    // The K4 CTA's gather touches P at rows / columns {0, 1, 2, f_o, f_o + 1}: 3 + 2m columns on as many 2 MB pages
+    // that the downdate has just streamed past -- measured 7.8 k cycles for ONE batch of five loads per thread at
+    // R = 16 (-DK4_TIMING, tools/k4_phases.py), i.e. serialised TLB / HBM misses.  The addresses are known here, ~2 us
+    // before the wait ends: prefetch them into L2.  L2 is the point of coherence, so a line the running downdate still
+    // writes is current when the loads behind the wait read it (nothing is brought into L1).  The gather phase fell to
+    // 3-6 k cycles, but same-box A/B of whole updates showed no gain (+0.1 us on a tiny map, nothing at n = 20003).
+    if (chol && latched == 0 && s_fail != 2) {
+        const int SCp = 3 + R;
+        for (int idx = tid; idx < m * SCp; idx += K3_THREADS) {
+            const int o = idx / SCp, sx = idx % SCp;
+            const int i = sx < 3 ? sx : sF[(sx - 3) >> 1] + ((sx - 3) & 1);
+            const int f = sF[o];
+            const int cols[5] = {0, 1, 2, f, f + 1};
+#pragma unroll
+            for (int q = 0; q < 5; q++) {
+                const int c = cols[q];
+                const double *pa = i <= c ? P + (size_t)i + (size_t)c * ld : P + (size_t)c + (size_t)i * ld;
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(pa));
+            }
+        }
+    }
+#endif
+#ifdef K4_TIMING
+    if (chol) K4_MARK(1);   // ids, x, observation model done, gather prefetched
+#endif
 #ifndef NO_PDL_PREFETCH
     pdl_wait();                          // P (the previous update's downdate) is complete
     pdl_launch_dependents();
+#endif
+#ifdef K4_TIMING
+    if (chol) K4_MARK(2);   // wait for the previous downdate over
 #endif
     if (!chol) {
         const int i = blockIdx.x * K3_THREADS + tid;
@@ -1373,6 +1465,7 @@ k_pht_chol(const double *__restrict__ x, const double *__restrict__ P, size_t ld
         sPH[2 * o + 1][s] = p0 * hh[3] + p1 * hh[4] + p2 * hh[5] + p3 * hh[8] + p4 * hh[9];
     }
     __syncthreads();
+    K4_MARK(3);   // sub-block of P gathered
     for (int idx = tid; idx < m * R; idx += K3_THREADS) {          // S = H*PHt + RR, as k_innov_chol
         const int o = idx / R, k = idx % R;
         const double *h = sH[o];
@@ -1390,6 +1483,13 @@ k_pht_chol(const double *__restrict__ x, const double *__restrict__ P, size_t ld
         if (tid == 0) atomicCAS(err, 0, SLAM_ERR_NOT_PD);
         k4_noop(R, tid, K3_THREADS, C, u);
     }
+#ifdef K4_TIMING
+    if (tid == 0) {
+        const long long *t = g_k4_mark;
+        printf("K4_TIMING R=%d n=%d cycles: model %lld | wait %lld | gather %lld | S+symm %lld | chol %lld | inverse %lld | u+C out %lld | total %lld\n",
+               R, n, t[1] - t[0], t[2] - t[1], t[3] - t[2], t[4] - t[3], t[5] - t[4], t[6] - t[5], t[7] - t[6], t[7] - t[0]);
+    }
+#endif
 }
 
 // K5 for one rank chunk (R <= RC <= 32): a thread owns row i, keeps PHt[i, 0:R] in registers (the loop above
