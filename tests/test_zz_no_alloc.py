@@ -103,3 +103,28 @@ def test_static_cov_block_is_shared_between_handles():
         assert np.array_equal(a, b) and np.array_equal(b, P2[50:90, 20:180])
     check(lib.slam_destroy(h1))
     check(lib.slam_destroy(h2))
+
+
+def test_static_cov_block_per_device_scratch():
+    """The static array exists once per GPU and its device address is resolved per device (cudaGetSymbolAddress with that
+    device current): handles on devices 0 and 1 interleaved, each window equal to the allocating entry point's and to
+    the state set on that device.  Skipped on a one-GPU box."""
+    import slamcuda
+    from slamcuda._ffi import lib, check, dptr
+    if slamcuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    states = [_state(31, 70), _state(32, 110)]
+    hs = []
+    for dev, (x, P) in enumerate(states):
+        h = C.c_void_p()
+        check(lib.slam_create(dev, len(x) + 5, C.byref(h)))
+        check(lib.slam_set_state(h, dptr(x), dptr(P), len(x), len(x)))
+        hs.append(h)
+    for rnd in range(3):
+        for dev in (1, 0, 1, 0):
+            x, P = states[dev]
+            i0, ni, j0, nj = 3 + rnd, 90 + 10 * dev, rnd, 120 + 7 * dev
+            a, b = _both(lib, check, dptr, hs[dev], i0, ni, j0, nj, ni)
+            assert np.array_equal(a, b) and np.array_equal(b, P[i0:i0 + ni, j0:j0 + nj]), (rnd, dev)
+    for h in hs:
+        check(lib.slam_destroy(h))
