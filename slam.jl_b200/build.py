@@ -23,13 +23,19 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall",
           "-Xcompiler", "-fno-strict-aliasing", f"-I{INCLUDE}"]
 # -fmad=false: products and sums round separately, matching the plain-C oracle twin
-# (oracle/slam_twin.c is built with -ffp-contract=off).  downdate*.cu use explicit fma().
+# (oracle/slam_twin.c is built with -ffp-contract=off): the single filter's update is BIT-EQUAL to the twin's for up to
+# 32 ranks (tests/test_gpu_single.py::test_update_P_bitwise_vs_twin).  downdate*.cu use explicit fma().
 PER_FILE = {
     "filter.cu": ["-fmad=false"],
     "gate.cu": ["-fmad=false"],
     "synth.cu": ["-fmad=false"],
     "shard.cu": ["-fmad=false"],
-    "ensemble.cu": ["-fmad=false"],
+    # The ensemble kernel is the exception: contraction ON.  It never was bit-equal to the twin (sincos / atan2 of CUDA's
+    # libm vs glibc already separate them at 1e-15, and its downdate is an fma / DMMA chain like the twin's), so separate
+    # rounding bought nothing there and cost instructions in an instruction-bound kernel: same box, 8192 runs,
+    # 64.18 -> 61.37 ms (+4.6 %), every map size still equal to the twin's, errors unchanged or smaller
+    # (profiles/r2_ensemble.md).  SLAMCUDA_ENS_FMAD=false restores separate rounding.
+    "ensemble.cu": ["-fmad=" + os.environ.get("SLAMCUDA_ENS_FMAD", "true")],
     "downdate.cu": [],
     "downdate_dmma.cu": [],
     "probe.cu": [],
