@@ -142,10 +142,28 @@ def cpu_reference_state(n_landmarks: int, m: int):
     return x, P, z, ids
 
 
+def cpu_use_all_cores() -> int:
+    """Give numpy's BLAS every host core and return the thread count it then really has.  torch.distributed.run exports
+    OMP_NUM_THREADS=1 to every rank, and OpenBLAS reads it when numpy is imported: without this the reference arm at
+    N > 1 timed a ONE-thread CPU while reporting all cores (measured here: the same matmul 0.88 s vs 0.17 s)."""
+    want = os.cpu_count() or 1
+    try:
+        from threadpoolctl import threadpool_info, threadpool_limits
+        threadpool_limits(limits=want)            # process-wide, stays in force
+        got = [i["num_threads"] for i in threadpool_info() if i.get("user_api") == "blas"]
+        return max(got) if got else want
+    except Exception as e:  # noqa: BLE001 -- threadpoolctl missing: say so rather than claim cores we may not have
+        sys.stderr.write(f"bench.py: cannot set the BLAS thread count ({e}); OMP_NUM_THREADS="
+                         f"{os.environ.get('OMP_NUM_THREADS')!r} decides\n")
+        env = os.environ.get("OMP_NUM_THREADS") or os.environ.get("OPENBLAS_NUM_THREADS")
+        return int(env) if env and env.isdigit() else want
+
+
 def cpu_reference_update(n_landmarks: int, m: int, steps: int, warmup: int):
     """Times oracle.slam_ref.update (dense H, P @ H.T, Cholesky, P - W1 @ W1.T) with numpy's
     OpenBLAS on all host cores.  Returns (median seconds per step, cores)."""
     from oracle import slam_ref as ref
+    cores = cpu_use_all_cores()
     x, P, z, ids = cpu_reference_state(n_landmarks, m)
     R = R_OBS.reshape(2, 2)
     times = []
@@ -156,7 +174,7 @@ def cpu_reference_update(n_landmarks: int, m: int, steps: int, warmup: int):
         if it >= warmup:
             times.append(dt)
     times.sort()
-    return times[len(times) // 2], os.cpu_count() or 1
+    return times[len(times) // 2], cores
 
 
 def cpu_baseline_block(n_workload: int, m: int, steps: int = 3, warmup: int = 1, sample_landmarks: int = 10000):
@@ -192,6 +210,7 @@ def cpu_full_size_step(n_landmarks: int, m: int, need_gb: float):
     if avail < need_gb:
         return {"ran": False, "why": f"needs ~{need_gb:.0f} GB of host memory for three copies of P, {avail:.0f} GB available"}
     from oracle import slam_ref as ref
+    cores = cpu_use_all_cores()
     t0 = time.perf_counter()
     x, P, z, ids = cpu_reference_state(n_landmarks, m)
     t_setup = time.perf_counter() - t0
@@ -201,7 +220,7 @@ def cpu_full_size_step(n_landmarks: int, m: int, need_gb: float):
     sec = time.perf_counter() - t0
     del P
     return {"ran": True, "n": n, "m": m, "seconds_per_step": sec, "value": 1.0 / sec, "unit": "update steps/s",
-            "cores": os.cpu_count() or 1, "setup_seconds": t_setup,
+            "cores": cores, "setup_seconds": t_setup,
             "what": "oracle/slam_ref.py update, ONE step at the workload's own size (measured, not extrapolated)"}
 
 
@@ -210,6 +229,7 @@ def cpu_associate_baseline(n_landmarks: int = 1000, nz: int = 2):
     (observation, landmark) pair) at n = 2003, and what that costs per pair; above that size only an
     extrapolation (cost per pair is O(n^2), pairs = nz*Nf) is meaningful -- hours at n = 20003."""
     from oracle import slam_ref as ref
+    cpu_use_all_cores()
     x, P, z, _ids = cpu_reference_state(n_landmarks, nz)
     R = R_OBS.reshape(2, 2)
     t0 = time.perf_counter()
@@ -219,7 +239,7 @@ def cpu_associate_baseline(n_landmarks: int = 1000, nz: int = 2):
     n = 3 + 2 * n_landmarks
     return {"what": "oracle/slam_ref.py associate (literal: dense H, H @ P @ H.T per pair), numpy + OpenBLAS",
             "n": n, "nz": nz, "pairs": pairs, "seconds": sec, "pairs_per_s": pairs / sec,
-            "matched": int(len(np.ravel(idf))), "cores": os.cpu_count() or 1,
+            "matched": int(len(np.ravel(idf))), "cores": cpu_use_all_cores(),
             "extrapolated_s_at_10k_landmarks_nz12": sec / pairs * (20003 / n) ** 2 * 12 * 10000,
             "extrapolation": "seconds per pair x (n / 2003)^2 x nz x Nf; labelled, not measured"}
 
@@ -234,7 +254,7 @@ def cpu_course1_baseline():
     sec = time.perf_counter() - t0
     return {"what": "oracle/slam_ref.py sim: sim! of sim/ekfslam-sim.jl:54-143 on course1, 35 landmarks, 2 laps, numpy",
             "filter_steps": out["nsteps"], "observation_steps": out["nupdates"], "n_final": int(len(out["x"])),
-            "seconds": sec, "value": out["nsteps"] / sec, "unit": "filter-steps/s", "cores": os.cpu_count() or 1}
+            "seconds": sec, "value": out["nsteps"] / sec, "unit": "filter-steps/s", "cores": cpu_use_all_cores()}
 
 
 # ----------------------------------------------------------------------------------------
@@ -853,6 +873,22 @@ def reference_arm(args, rank: int):
                       f"{max(args.steps, 1)} timed steps at n = {n_s} (median {sec * 1e3:.0f} ms) scaled by (n_sample/n)^2 give "
                       f"{val_extrapolated:.4g} steps/s, {val_extrapolated / val:.2f} of the measured figure (scaling exponent "
                       f"measured between n = {3 + 2 * half} and {n_s}: {exponent:.2f})")
+    # At N > 1 the workload's P (80 .. 320 GB) cannot be held three times over by any host here, so the value stays an
+    # extrapolation -- but from the largest size the host CAN run: the 40 GB map (n = 70709, the N = 1 workload), a
+    # factor (n / 70709)^2 = 2 .. 8 away instead of (n / 20003)^2 = 25 .. 100.
+    if args.gpus > 1 and not args.no_full_cpu:
+        n1 = n_for_bytes(GB_PER_RANK)
+        full = cpu_full_size_step((n1 - 3) // 2, args.m, need_gb=3.4 * 8.0 * n1 * n1 / 1e9)
+        if full.get("ran"):
+            val_from_sample = val_extrapolated
+            val = (n1 / n_w) ** 2 * full["value"]
+            sample = (f"oracle/slam_ref.py update (numpy literal restatement of src/ekf.jl:46-77; Julia <= 0.6 is not "
+                      f"installable here): ONE measured step at n = {n1} (P = 40 GB, the largest map this host holds three "
+                      f"times over), m = {args.m}, OpenBLAS {cores} threads, {full['seconds_per_step']:.1f} s, scaled by "
+                      f"(n1/n)^2 = {(n1 / n_w) ** 2:.4g} to the workload n = {n_w} (EXTRAPOLATED, factor "
+                      f"{(n_w / n1) ** 2:.1f}; the workload's P does not fit host RAM).  From the {max(args.steps, 1)} timed steps "
+                      f"at n = {n_s} the same law gives {val_from_sample:.4g} steps/s, {val_from_sample / val:.2f} of this "
+                      f"(scaling exponent measured between n = {3 + 2 * half} and {n_s}: {exponent:.2f})")
     line = {
         "impl": "reference", "metric": "EKF update steps/s", "value": val, "unit": "update steps/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / val,

@@ -105,4 +105,31 @@ def test_reference_arm_prints_once_under_torchrun():
     assert len(lines) == 1
     line = lines[0]
     assert line["impl"] == "reference" and line["n_gpus"] == 2 and line["value"] > 0
+    # torch.distributed.run exports OMP_NUM_THREADS=1 to every rank and numpy's OpenBLAS obeys it at import: the arm must
+    # put the BLAS back on every host core (and report the count it really has), or it times a one-thread CPU
+    import os
+    assert line["cpu_baseline"]["cores"] == (os.cpu_count() or 1), line["cpu_baseline"]["cores"]
     assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["cpu_baseline"]["kind"] == "port"
+
+
+def test_cpu_legs_get_every_core_despite_omp_num_threads():
+    """The behaviour behind the assertion above: in a process that inherits OMP_NUM_THREADS=1 (what torch.distributed.run
+    exports) numpy's BLAS has ONE thread; bench.cpu_use_all_cores() puts it on every host core and returns the count the
+    BLAS then really has.  (Before this helper existed the reference arm at N > 1 timed a one-thread CPU and reported
+    os.cpu_count() cores.)"""
+    import os
+    import subprocess
+    import sys
+    code = ("import json, os, numpy, bench\n"
+            "from threadpoolctl import threadpool_info\n"
+            "blas = lambda: [i['num_threads'] for i in threadpool_info() if i.get('user_api') == 'blas']\n"
+            "before = blas(); n = bench.cpu_use_all_cores(); after = blas()\n"
+            "print(json.dumps({'before': before, 'returned': n, 'after': after, 'cpus': os.cpu_count()}))\n")
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    env.pop("OPENBLAS_NUM_THREADS", None)
+    out = subprocess.run([sys.executable, "-c", code], cwd=ROOT, env=env, capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr[-800:]
+    r = json.loads(out.stdout.strip().splitlines()[-1])
+    cpus = r["cpus"] or 1
+    assert r["before"] and all(t == 1 for t in r["before"]), r          # the inherited setting does throttle the BLAS
+    assert r["returned"] == cpus and r["after"] and all(t == cpus for t in r["after"]), r
