@@ -896,7 +896,11 @@ def reference_arm(args, rank: int):
         "config": workload_config(args.gpus, args.m),
         "cpu_baseline": {"value": val, "unit": "update steps/s", "cores": cores, "kind": "port", "sample": sample,
                          "measured_steps_per_s_at_sample": 1.0 / sec, "measured_ms_per_step_at_sample": sec * 1e3,
-                         "extrapolated": not (full and full.get("ran")), "extrapolated_value": val_extrapolated,
+                         # measured only at N = 1 (the workload itself ran); at N > 1 the measured 40 GB step is scaled
+                         "extrapolated": not (args.gpus == 1 and full and full.get("ran")),
+                         "extrapolated_from_n": (n_s if not (full and full.get("ran")) else full["n"]) if not (
+                             args.gpus == 1 and full and full.get("ran")) else None,
+                         "extrapolated_value": val_extrapolated,
                          "scaling_exponent_measured": exponent, **({"full_size_step": full} if full else {})},
         "e2e": {"value": val, "unit": "update steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "wall_s": time.perf_counter() - t0,
